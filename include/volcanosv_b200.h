@@ -1,0 +1,174 @@
+/* volcanosv_b200 -- C-ABI of the B200-native large-indel hot path of VolcanoSV-vc.
+ *
+ * The reference (maiziezhoulab/VolcanoSV) is pure Python: it has no FFI for this path.
+ * Each entry point below replaces the body of one reference FUNCTION; the Python
+ * operators of volcanosv_b200/ keep the reference scripts' argv and file contracts
+ * and bind these symbols through ctypes (INTEGRATION.md shows the stub a maintainer
+ * of the reference would add).  Paths: LI/ = bin/VolcanoSV-vc/Large_INDEL/.
+ *
+ * Conventions
+ *  - every function returns 0 on success, <0 on error (VSV_E_*); vsv_last_error(ctx)
+ *    returns the message.  No exceptions cross the ABI.
+ *  - one vsv_ctx per (thread, GPU); a ctx is not thread-safe.
+ *  - buffers are caller-owned.  By default they are HOST pointers (pinned memory from
+ *    vsv_alloc_pinned makes the copies asynchronous); after
+ *    vsv_ctx_set_device_io(ctx,1) every data pointer is a DEVICE pointer on the ctx's
+ *    GPU and nothing is copied (inputs stay resident in HBM; used by the pipeline
+ *    driver and by bench.py's resident timing).  Scalar outputs (counts) are always
+ *    host pointers.
+ *  - variable-size outputs use caller-provided capacity; if the result does not fit,
+ *    the call returns VSV_E_CAPACITY and *n_out holds the required count.
+ *  - there is NO CPU fallback: without a CUDA device vsv_ctx_create fails.
+ */
+#ifndef VOLCANOSV_B200_H
+#define VOLCANOSV_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VSV_OK 0
+#define VSV_E_CUDA (-1)
+#define VSV_E_ARG (-2)
+#define VSV_E_CAPACITY (-3)
+#define VSV_E_NOMEM (-4)
+
+/* scan modes (which reference scanner is reproduced) */
+#define VSV_MODE_CONTIG 0 /* LI/extract_contig_signature_{Hifi,ONT,CLR}.py:53-85  */
+#define VSV_MODE_READS 1  /* LI/extract_reads_signature.py:47-83                  */
+#define VSV_MODE_CUTE 2   /* LI/sig_extract.py:438-478                            */
+
+#define VSV_DEL 0
+#define VSV_INS 1
+
+/* split-pair rule sets */
+#define VSV_SPLIT_HIFI 0  /* LI/extract_contig_signature_Hifi.py:307-371 */
+#define VSV_SPLIT_ONT 1   /* LI/extract_contig_signature_ONT.py:307-382  */
+#define VSV_SPLIT_CLR 2   /* LI/extract_contig_signature_CLR.py:328-402  */
+#define VSV_SPLIT_READS 3 /* LI/extract_reads_signature.py:147-197       */
+
+/* One signature, 32 bytes.  Mirrors the reference's 10-field contig sig / 8-field
+ * read sig (ECS_H:80,84; ERS:74,78): chrom/qname/strand/mapq are looked up by the
+ * host from `rec`. */
+typedef struct vsv_sig {
+  int32_t rec;   /* record index in the scanned batch (split pairs: first record)  */
+  int32_t type;  /* VSV_DEL / VSV_INS                                               */
+  int32_t pos;   /* reference position                                              */
+  int32_t len;   /* SV length                                                       */
+  int32_t q0;    /* query start (contig: offset_contig+hardclip; cute: index in SEQ) */
+  int32_t q1;    /* query end                                                       */
+  int32_t first; /* merge: index of first pre-merge sig of this type folded in;
+                    split pairs: second record index                               */
+  int32_t count; /* merge: number of pre-merge sigs folded in (>=1)                 */
+} vsv_sig;
+
+typedef struct vsv_ctx vsv_ctx;
+
+/* ---- context ---------------------------------------------------------------- */
+int vsv_ctx_create(int device, vsv_ctx** out);
+void vsv_ctx_destroy(vsv_ctx* ctx);
+const char* vsv_last_error(vsv_ctx* ctx);
+int vsv_ctx_set_device_io(vsv_ctx* ctx, int on);
+int vsv_sync(vsv_ctx* ctx);
+int vsv_alloc_pinned(void** p, size_t bytes);
+int vsv_free_pinned(void* p);
+/* CUDA-event time (ms) of the kernels of the last call on this ctx, and number of
+ * kernel launches since the ctx was created. */
+int vsv_get_timing(vsv_ctx* ctx, float* kernel_ms, int64_t* launches);
+const char* vsv_version(void);
+
+/* ---- stage 1: signature scan -------------------------------------------------- */
+/* Replaces extract_sig_from_cigar (ECS_H:53-85, ERS:47-83) and the CIGAR walk of
+ * parse_read (SE:438-478).  ops[i] = len<<4|op (BAM-native), op_off[n_rec+1].
+ * Records with mapq<min_mapq or enable[r]==0 (enable may be NULL) emit nothing.
+ * out: signatures in (record, op) order.  ref/qry/aux_total (each may be NULL):
+ * per-record sums of op lengths over the mode's reference / query / auxiliary op
+ * sets (aux = H for CONTIG/READS so readlen = qry+aux; aux = N for CUTE so
+ * reference_end = pos+ref+aux). */
+int vsv_scan_cigar(vsv_ctx* ctx, int mode, int min_len, int min_mapq, const uint32_t* ops,
+                   const int64_t* op_off, const int32_t* pos, const uint8_t* mapq,
+                   const uint8_t* enable, int64_t n_rec, vsv_sig* out, int64_t cap,
+                   int64_t* n_out, int32_t* ref_total, int32_t* qry_total, int32_t* aux_total);
+
+/* Replaces cluster_ins_one_read / cluster_del_one_read (ECS_H:87-164) for
+ * VSV_MODE_CONTIG and generate_combine_sigs (SE:373-435) for VSV_MODE_CUTE
+ * (VSV_MODE_READS: identity split by type).  Input: scan output.  out_del/out_ins
+ * need capacity n each. */
+int vsv_merge_in_record(vsv_ctx* ctx, int mode, const vsv_sig* sigs, int64_t n, vsv_sig* out_del,
+                        int64_t* n_del, vsv_sig* out_ins, int64_t* n_ins);
+
+/* Replaces extract_sig_from_split + its driver loop (ECS_H:307-371,421-457;
+ * ERS:147-237).  select[r] = the reference's membership filter; name_id = interned
+ * qname in first-appearance order.  Output order = (name first appearance, pair). */
+int vsv_split_pairs(vsv_ctx* ctx, int variant, int min_mapq, const int32_t* pos,
+                    const int32_t* ref_end, const int32_t* readlen, const uint32_t* first_op,
+                    const uint32_t* last_op, const uint8_t* mapq, const uint8_t* is_rev,
+                    const int32_t* name_id, const uint8_t* select, int64_t n_rec, vsv_sig* out,
+                    int64_t cap, int64_t* n_out);
+
+/* ---- stage 2: sort / cluster / pair / window joins ---------------------------- */
+/* sort_sig (ECS_H:170-179) with the tie order pinned to stable: order[i] = index of
+ * the i-th smallest key. */
+int vsv_argsort_stable(vsv_ctx* ctx, const int32_t* key, int64_t n, int32_t* order);
+
+/* cluster_del / cluster_ins (ECS_H:196-288) on a pos-sorted list: kept indices in
+ * leader order. */
+int vsv_cluster(vsv_ctx* ctx, int is_del, const int32_t* pos, const int32_t* len, int64_t n,
+                int32_t* keep, int64_t* n_keep);
+
+/* pair_sig matching part (ECS_H:548-569): partner index or -1 for each side. */
+int vsv_pair_haps(vsv_ctx* ctx, const int32_t* pos1, const int32_t* len1, const int32_t* typ1,
+                  int64_t n1, const int32_t* pos2, const int32_t* len2, const int32_t* typ2,
+                  int64_t n2, int32_t* partner1, int32_t* partner2);
+
+/* eval_sig (FPF:106-123): read-signature support per raw call (60 if len>250). */
+int vsv_fp_support(vsv_ctx* ctx, const int32_t* call_pos, const int32_t* call_len, int64_t n_call,
+                   const int32_t* sig_pos, const int32_t* sig_len, int64_t n_sig, int32_t* support);
+
+/* calc_ins_call_cov (CSS:81-125) / calc_del_call_cov (CSS:138-253), flanking 1000.
+ * cov[i] = sum of sig lengths (DEL: negated) in the call's window. */
+int vsv_ins_cov(vsv_ctx* ctx, const int32_t* call_pos, int64_t n_call, const int32_t* sig_pos,
+                const int32_t* sig_len, int64_t n_sig, int flanking, int64_t* cov);
+int vsv_del_cov(vsv_ctx* ctx, const int32_t* call_start, const int32_t* call_end, int64_t n_call,
+                const int32_t* sig_pos, const int32_t* sig_len, int64_t n_sig, int flanking,
+                int64_t* cov);
+
+/* ---- stage 3: genotyping ------------------------------------------------------ */
+/* load_sig (GTD:65-86) / load_sig_file (GTI:67-101) on a (chrom,pos)-sorted table:
+ * unique (chrom,pos,len) rows with read counts.  Outputs need capacity n. */
+int vsv_group_sigs(vsv_ctx* ctx, const int32_t* chrom, const int32_t* pos, const int32_t* len,
+                   int64_t n, int32_t* u_chrom, int32_t* u_pos, int32_t* u_len, int32_t* u_cnt,
+                   int64_t* n_unique);
+
+/* match_varlist_siglist (GTD:92-137) / extract_sig_support (GTI:107-166), including
+ * the double count at last_match_idx.  last_in/last_out carry last_match_idx across
+ * shards (0 for the first).  match_id may be NULL. */
+int vsv_sig_support(vsv_ctx* ctx, const int32_t* cand_chrom, const int32_t* cand_pos,
+                    const int32_t* cand_svlen, int64_t n_cand, const int32_t* sig_chrom,
+                    const int32_t* sig_pos, const int32_t* sig_len, const int32_t* sig_cnt,
+                    int64_t n_sig, int32_t last_in, int32_t* support, int32_t* match_id,
+                    int32_t* last_out);
+
+/* count_reads_span_region (GTD:140-146; GTI:188-196): per window, number of records
+ * with start < S and end > E.  Reads sorted by start. */
+int vsv_span_depth(vsv_ctx* ctx, const int32_t* read_start, const int32_t* read_end,
+                   int64_t n_reads, const int32_t* S, const int32_t* E, int64_t n_win,
+                   int32_t* depth);
+
+/* check_full_cover_reads + ratio + correct_gt_eval (GTD:149-170,206-217,291-318;
+ * GTI:188-196,228,258-283) for candidates on one chromosome.  vtype per call:
+ * VSV_DEL / VSV_INS array; call_gt 0='0/1', 1='1/1', other = pass through.
+ * thr_del/thr_ins = {t_large_11,t_small_11,t_large_01,t_small_01} (NaN = leave).
+ * Outputs: depth2 (= 2*depth, exact), ratio (double), new_gt. */
+int vsv_genotype(vsv_ctx* ctx, const int32_t* read_start, const int32_t* read_end, int64_t n_reads,
+                 const int32_t* cand_pos, const int32_t* cand_svlen, const int32_t* cand_type,
+                 const int32_t* call_gt, const int32_t* n_support, int64_t n_cand,
+                 const double* thr_del, const double* thr_ins, int32_t* depth2, double* ratio,
+                 int32_t* new_gt);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

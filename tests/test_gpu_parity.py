@@ -1,0 +1,133 @@
+"""Parity of the CUDA path (through the C-ABI, ctypes) against the oracle and the
+reference-generated golden vectors.  Integer work: bit-exact."""
+import numpy as np
+import pytest
+
+import oracle as O
+import volcanosv_b200 as V
+from volcanosv_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = V.Context(0)
+    yield c
+    c.close()
+
+
+def sig_tuples(a, fields=("rec", "type", "pos", "len", "q0", "q1")):
+    return [tuple(int(x[f]) for f in fields) for x in a]
+
+
+# ------------------------------------------------------------------ stage 1
+@pytest.mark.parametrize("name,mode,minlen", [("contig_scan", V.MODE_CONTIG, 30), ("reads_scan", V.MODE_READS, 30)])
+def test_scan_golden(ctx, golden, name, mode, minlen):
+    g = golden(name)
+    ops, off = O.pack_cigar([c["cigar"] for c in g])
+    pos = np.array([c["pos"] for c in g], np.int32)
+    mapq = np.full(len(g), 60, np.uint8)
+    sigs, rt, qt, xt = ctx.scan_cigar(mode, ops, off, pos, mapq, min_len=minlen)
+    for r, c in enumerate(g):
+        assert int(pos[r]) + int(rt[r]) == c["oref"] and int(qt[r]) == c["oq"]
+    if mode == V.MODE_CONTIG:
+        d, s = ctx.merge_in_record(mode, sigs)
+        for r, c in enumerate(g):
+            assert [[int(x["pos"]), int(x["len"]), int(x["q0"]), int(x["q1"])] for x in d[d["rec"] == r]] == c["dels"]
+            assert [[int(x["pos"]), int(x["len"]), int(x["q0"]), int(x["q1"])] for x in s[s["rec"] == r]] == c["inss"]
+    else:
+        for r, c in enumerate(g):
+            m = sigs[sigs["rec"] == r]
+            assert [[int(x["pos"]), int(x["len"]), int(x["q0"])] for x in m[m["type"] == V.DEL]] == c["dels"]
+            assert [[int(x["pos"]), int(x["len"]), int(x["q0"])] for x in m[m["type"] == V.INS]] == c["inss"]
+
+
+def test_cute_scan_merge_golden(ctx, golden):
+    g = [c for c in golden("parse_read") if len(c["seq"]) >= 500]
+    ops, off = O.pack_cigar([c["cigar"] for c in g])
+    pos = np.array([c["pos"] for c in g], np.int32)
+    mapq = np.array([c["mapq"] for c in g], np.uint8)
+    sigs, rt, qt, xt = ctx.scan_cigar(V.MODE_CUTE, ops, off, pos, mapq, min_len=10, min_mapq=20)
+    d, s = ctx.merge_in_record(V.MODE_CUTE, sigs)
+    inss = sigs[sigs["type"] == V.INS]
+    for r, c in enumerate(g):
+        rows = []
+        for m in s[s["rec"] == r]:
+            piece = "".join(c["seq"][int(inss[k]["q0"]):int(inss[k]["q1"])] for k in range(m["first"], m["first"] + m["count"]))
+            rows.append(["INS", int(m["pos"]), int(m["len"]), piece])
+        for m in d[d["rec"] == r]:
+            rows.append(["DEL", int(m["pos"]), int(m["len"])])
+        # golden rows = cigar-derived rows first, then SA-derived rows (checked in the oracle test)
+        assert rows == c["rows"][: len(rows)]
+
+
+@pytest.mark.parametrize("profile,mode,minlen,minmq,eqx", [
+    ("hifi", V.MODE_READS, 30, 50, True), ("ont", V.MODE_CUTE, 10, 20, True), ("contig", V.MODE_CONTIG, 30, 50, False),
+    ("hifi", V.MODE_CUTE, 10, 20, False)])
+def test_scan_vs_oracle_random(ctx, profile, mode, minlen, minmq, eqx):
+    n = {"hifi": 300, "ont": 40, "contig": 30}[profile]
+    b = synth.synth_records(7, n, profile, eqx=eqx)
+    en = (np.arange(n) % 7 != 3).astype(np.uint8)
+    sigs, rt, qt, xt = ctx.scan_cigar(mode, b["ops"], b["op_off"], b["pos"], b["mapq"], enable=en, min_len=minlen,
+                                      min_mapq=minmq)
+    es, ert, eqt, ext = O.scan_cigar(b["ops"], b["op_off"], b["pos"], b["mapq"], mode, minlen, minmq, enable=en)
+    assert sig_tuples(sigs) == es
+    assert len(es) > 0
+    assert np.array_equal(rt, ert) and np.array_equal(qt, eqt) and np.array_equal(xt, ext)
+    d, s = ctx.merge_in_record(mode, sigs)
+    ed, ei = O.merge_in_record(es, mode)
+    f8 = ("rec", "type", "pos", "len", "q0", "q1", "first", "count")
+    assert sig_tuples(d, f8) == ed and sig_tuples(s, f8) == ei
+
+
+def test_scan_edge_cases(ctx):
+    # empty records, a record of one op, a record spanning many tiles, capacity growth
+    cig = [[], [(0, 5)], [(2, 40)], [], [(5, 7), (0, 3), (1, 31), (0, 2)]]
+    big = []
+    for i in range(9000):
+        big += [(0, 10), (1, 30 + (i % 5)), (0, 7), (2, 10 + (i % 40))]
+    cig.append(big)
+    cig.append([(4, 3), (0, 100), (2, 30), (0, 1)])
+    cig.append([])
+    ops, off = O.pack_cigar(cig)
+    pos = np.arange(len(cig), dtype=np.int32) * 1000
+    mapq = np.full(len(cig), 60, np.uint8)
+    for mode in (V.MODE_CONTIG, V.MODE_READS, V.MODE_CUTE):
+        sigs, rt, qt, xt = ctx.scan_cigar(mode, ops, off, pos, mapq, min_len=30, cap=16)
+        es, ert, eqt, ext = O.scan_cigar(ops, off, pos, mapq, mode, 30, 0)
+        assert sig_tuples(sigs) == es and len(es) > 9000
+        assert np.array_equal(rt, ert) and np.array_equal(qt, eqt) and np.array_equal(xt, ext)
+    # nothing at all
+    sigs, rt, qt, xt = ctx.scan_cigar(V.MODE_READS, np.zeros(0, np.uint32), np.zeros(1, np.int64), np.zeros(0, np.int32),
+                                      np.zeros(0, np.uint8))
+    assert len(sigs) == 0
+    # records but zero ops
+    sigs, rt, qt, xt = ctx.scan_cigar(V.MODE_READS, np.zeros(0, np.uint32), np.zeros(4, np.int64), np.zeros(3, np.int32),
+                                      np.zeros(3, np.uint8))
+    assert len(sigs) == 0 and rt.tolist() == [0, 0, 0]
+
+
+def test_scan_full_size_properties(ctx):
+    """chr10 HiFi-shaped batch (BASELINE config 1 scale / 10): size-independent checks."""
+    n = 27000
+    b = synth.synth_records(11, n, "hifi", eqx=True)
+    sigs, rt, qt, xt = ctx.scan_cigar(V.MODE_READS, b["ops"], b["op_off"], b["pos"], b["mapq"], min_len=30, min_mapq=50)
+    code = b["ops"] & 15
+    ln = (b["ops"] >> 4).astype(np.int64)
+    rec_of = np.repeat(np.arange(n), np.diff(b["op_off"]))
+    # totals == segmented sums computed with numpy
+    ref = np.zeros(n, np.int64)
+    np.add.at(ref, rec_of[np.isin(code, [0, 2, 3, 7, 8])], ln[np.isin(code, [0, 2, 3, 7, 8])])
+    assert np.array_equal(ref, rt)
+    qry = np.zeros(n, np.int64)
+    np.add.at(qry, rec_of[np.isin(code, [0, 1, 4, 7, 8])], ln[np.isin(code, [0, 1, 4, 7, 8])])
+    assert np.array_equal(qry, qt)
+    # emitted set == ops with len>=30 and code in {I,D} of records with mapq>=50, in order
+    sel = np.isin(code, [1, 2]) & (ln >= 30) & (b["mapq"][rec_of] >= 50)
+    assert len(sigs) == int(sel.sum())
+    assert np.array_equal(sigs["rec"], rec_of[sel]) and np.array_equal(sigs["len"], ln[sel])
+    assert np.array_equal(sigs["type"], (code[sel] == 1).astype(np.int32))
+    # idempotence
+    sigs2, *_ = ctx.scan_cigar(V.MODE_READS, b["ops"], b["op_off"], b["pos"], b["mapq"], min_len=30, min_mapq=50)
+    assert np.array_equal(sigs.view(np.uint8), sigs2.view(np.uint8))

@@ -1,0 +1,197 @@
+"""CUDA stage 2 (split pairs, sort, cluster, pair, window joins) and stage 3 (group,
+support, depth, genotype) against the reference-generated goldens and the oracle."""
+import math
+
+import numpy as np
+import pytest
+
+import oracle as O
+import volcanosv_b200 as V
+from volcanosv_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = V.Context(0)
+    yield c
+    c.close()
+
+
+def _info(cg, pos, readsmode):
+    ref_end = pos + sum(l for o, l in cg if o in (0, 2, 3, 7, 8))
+    rlset = (0, 7, 8, 1, 4, 5) if readsmode else (0, 1, 4, 5)
+    rl = sum(l for o, l in cg if o in rlset)
+    return ref_end, rl, (cg[0][1] << 4) | cg[0][0], (cg[-1][1] << 4) | cg[-1][0]
+
+
+def test_split_pairs_golden(ctx, golden):
+    g = golden("split_pair")
+    var = dict(hifi=V.SPLIT_HIFI, ont=V.SPLIT_ONT, clr=V.SPLIT_CLR, reads=V.SPLIT_READS)
+    for key, cases in g.items():
+        pos, end, rl, fo, lo, mq, rv, nm = [], [], [], [], [], [], [], []
+        for i, c in enumerate(cases):
+            for cg, p, m, r in ((c["c1"], c["p1"], c["m1"], c["rev1"]), (c["c2"], c["p2"], c["m2"], c["rev2"])):
+                e, l, f, la = _info(cg, p, key == "reads")
+                pos.append(p); end.append(e); rl.append(l); fo.append(f); lo.append(la); mq.append(m); rv.append(r); nm.append(i)
+        out = ctx.split_pairs(var[key], cases[0]["min_mapq"], pos, end, rl, fo, lo, mq, rv, nm)
+        got = {int(s["rec"]) // 2: [("DEL", "INS")[s["type"]], int(s["pos"]), int(s["len"]), int(s["q0"]), int(s["q1"])] for s in out}
+        assert all(int(s["first"]) == int(s["rec"]) + 1 for s in out)
+        assert list(got) == sorted(got)
+        for i, c in enumerate(cases):
+            assert got.get(i) == c["res"], (key, i)
+
+
+def test_split_pairs_driver_vs_oracle(ctx):
+    rng = np.random.default_rng(5)
+    n = 4000
+    b = synth.synth_records(21, n, "hifi", clip_rate=0.8, n_names=1500)
+    _, rt, qt, xt = ctx.scan_cigar(V.MODE_CONTIG, b["ops"], b["op_off"], b["pos"], b["mapq"])
+    ref_end = b["pos"] + rt
+    rl = qt + xt
+    first_op = b["ops"][b["op_off"][:-1]]
+    last_op = b["ops"][b["op_off"][1:] - 1]
+    rev = (b["flag"] & 16) != 0
+    # make read lengths of same-name records agree often enough to produce signatures
+    sel = (b["mapq"] >= 50) & (b["hp"] == 1)
+    # re-intern names in first-appearance order over the selected records (host contract)
+    remap, nid = {}, np.full(n, -1, np.int32)
+    for r in range(n):
+        if sel[r]:
+            nid[r] = remap.setdefault(int(b["name_id"][r]), len(remap))
+    for variant in (V.SPLIT_HIFI, V.SPLIT_ONT, V.SPLIT_CLR, V.SPLIT_READS):
+        out = ctx.split_pairs(variant, 50, b["pos"], ref_end, rl, first_op, last_op, b["mapq"], rev, nid, sel)
+        exp = O.split_pairs(variant, b["pos"], ref_end, rl, first_op, last_op, b["mapq"], rev, nid, sel, 50)
+        got = [tuple(int(s[f]) for f in ("rec", "first", "type", "pos", "len", "q0", "q1")) for s in out]
+        assert got == exp
+    assert len(exp) > 0
+
+
+def test_argsort_stable(ctx):
+    rng = np.random.default_rng(1)
+    k = rng.integers(-50, 50, 5000).astype(np.int32)
+    assert np.array_equal(ctx.argsort_stable(k), np.argsort(k, kind="stable"))
+
+
+def test_cluster_pair_golden(ctx, golden):
+    g = golden("cluster_pair")
+    for c in g["cluster"]:
+        assert ctx.cluster(c["type"] == "DEL", c["pos"], c["len"]).tolist() == c["kept"]
+    t = {"DEL": 0, "INS": 1}
+    for c in g["pair"]:
+        h1, h2 = c["h1"], c["h2"]
+        a = ([s[2] for s in h1], [s[3] for s in h1], [t[s[1]] for s in h1])
+        b = ([s[2] for s in h2], [s[3] for s in h2], [t[s[1]] for s in h2])
+        p1, p2 = ctx.pair_haps(*a, *b)
+        e1, e2 = O.pair_haps(*a, *b)
+        assert p1.tolist() == e1 and p2.tolist() == e2
+
+
+def test_cluster_pair_large_vs_oracle(ctx):
+    rng = np.random.default_rng(3)
+    n = 3000
+    pos = np.sort(rng.integers(0, 200000, n)).astype(np.int32)
+    ln = rng.choice([30, 45, 60, 61, 90, 120, 121, 300, 1000], n).astype(np.int32)
+    for is_del in (False, True):
+        assert ctx.cluster(is_del, pos, ln).tolist() == O.cluster_leader(pos, ln, is_del)
+    typ = rng.integers(0, 2, n).astype(np.int32)
+    pos2 = np.sort(np.clip(pos + rng.integers(-250, 250, n), 0, None)).astype(np.int32)
+    ln2 = rng.choice([30, 45, 60, 61, 90, 120, 121, 300, 1000], n).astype(np.int32)
+    typ2 = rng.integers(0, 2, n).astype(np.int32)
+    p1, p2 = ctx.pair_haps(pos, ln, typ, pos2, ln2, typ2)
+    e1, e2 = O.pair_haps(pos, ln, typ, pos2, ln2, typ2)
+    assert p1.tolist() == e1 and p2.tolist() == e2
+    assert sum(1 for x in e1 if x >= 0) > 100
+
+
+def test_window_joins_golden(ctx, golden):
+    g = golden("window")
+    for c in g["fp"]:
+        assert ctx.fp_support(c["call_pos"], c["call_len"], c["sig_pos"], c["sig_len"]).tolist() == c["support"]
+    for c in g["cov"]:
+        assert [float(x) for x in ctx.ins_cov(c["ins_call_pos"], c["ins_sig_pos"], c["ins_sig_len"])] == c["ins_cov"]
+        assert [float(x) for x in ctx.del_cov(c["del_call_start"], c["del_call_end"], c["del_sig_pos"], c["del_sig_len"])] == c["del_cov"]
+    # empty signature table
+    assert ctx.fp_support([5, 9], [30, 300], [], []).tolist() == [0, 60]
+    assert ctx.ins_cov([5], [], []).tolist() == [0]
+    assert ctx.del_cov([5], [9], [], []).tolist() == [0]
+
+
+def test_support_depth_thresholds_golden(ctx, golden):
+    g = golden("genotype")
+    cid = lambda s: int(s[3:])
+    for c in g["support"]:
+        rows = [r for r in c["rows"] if c["vtype"] == "DEL" or r[2] >= 30]
+        uc, up, ul, un = ctx.group_sigs([cid(r[0]) for r in rows], [r[1] for r in rows], [r[2] for r in rows])
+        assert [[cid(u[0]), u[1], u[2], u[3]] for u in c["uniq"]] == [list(map(int, x)) for x in zip(uc, up, ul, un)]
+        sup, mid, last = ctx.sig_support([cid(x[0]) for x in c["cands"]], [x[1] for x in c["cands"]],
+                                         [x[2] for x in c["cands"]], uc, up, ul, un)
+        assert sup.tolist() == c["support"]
+        if c["match_id"] is not None:
+            assert mid.tolist() == c["match_id"]
+        # sharded by candidate halves with the carried last_match_idx == unsharded
+        h = len(c["cands"]) // 2
+        cc, cp, cl = [cid(x[0]) for x in c["cands"]], [x[1] for x in c["cands"]], [x[2] for x in c["cands"]]
+        s1, _, l1 = ctx.sig_support(cc[:h], cp[:h], cl[:h], uc, up, ul, un)
+        s2, _, l2 = ctx.sig_support(cc[h:], cp[h:], cl[h:], uc, up, ul, un, last_in=l1)
+        assert s1.tolist() + s2.tolist() == c["support"] and l2 == last
+    d = g["depth"]
+    S, E, exp = [], [], []
+    for c in d["cases"]:
+        S.append(c["pos"] - 100); E.append(c["pos"] + 100); exp.append(c["ins_depth"])
+    assert ctx.span_depth(d["read_start"], d["read_end"], S, E).tolist() == exp
+    nan = float("nan")
+    pos = [c["pos"] for c in d["cases"]]
+    sv = [c["svlen"] for c in d["cases"]]
+    z = [0] * len(pos)
+    d2, ratio, ng = ctx.genotype(d["read_start"], d["read_end"], pos, sv, z, z, z, [nan] * 4, [nan] * 4)
+    assert d2.tolist() == [int(round(2 * c["del_depth"])) for c in d["cases"]]
+    d2, ratio, ng = ctx.genotype(d["read_start"], d["read_end"], pos, sv, [1] * len(pos), z, z, [nan] * 4, [nan] * 4)
+    assert d2.tolist() == [2 * c["ins_depth"] for c in d["cases"]]
+
+
+def test_genotype_thresholds_vs_oracle(ctx, golden):
+    """Threshold decision incl. exact-tie ratios (3/5 vs 0.6, 69/100 vs 0.69), depth 0,
+    inf/nan for INS; compared with the oracle that is pinned by the golden file."""
+    g = golden("genotype")["thresholds"]
+    rng = np.random.default_rng(9)
+    # reads: k identical spanning reads over [0, 100000) -> depth k for any window
+    for c in g:
+        thr = [float("nan") if x is None else x for x in c["thr"]]
+        vt = O.DEL if c["vtype"] == "DEL" else O.INS
+        for depth in (0, 5, 100):
+            rs = np.zeros(depth, np.int32)
+            re = np.full(depth, 10**6, np.int32)
+            n = 64
+            sv = rng.choice([30, 1000, 1001, 5000], n).astype(np.int32)
+            gt = rng.choice([0, 1, 2], n).astype(np.int32)
+            ns = rng.choice([0, 1, 3, 6, 59, 60, 61, 69, 71, 79, 91, 100], n).astype(np.int32)
+            pos = np.full(n, 5000, np.int32)
+            tp = np.full(n, vt, np.int32)
+            d2, ratio, ng = ctx.genotype(rs, re, pos, sv, tp, gt, ns, thr if vt == O.DEL else [float("nan")] * 4,
+                                         thr if vt == O.INS else [float("nan")] * 4)
+            for i in range(n):
+                er, eg = O.genotype(vt, int(sv[i]), int(gt[i]), int(ns[i]), 2 * depth, thr)
+                assert int(d2[i]) == 2 * depth and int(ng[i]) == eg
+                assert (math.isnan(er) and math.isnan(ratio[i])) or er == ratio[i]
+
+
+def test_depth_stress_properties(ctx):
+    """10^6 reads x 10^5 windows: compare with a numpy evaluation on a sample and check
+    monotonicity properties on all."""
+    rs, re = synth.synth_intervals(3, 1_000_000)
+    pos, svlen, typ, gt = synth.synth_candidates(4, 100_000)
+    S, E = pos.copy(), (pos + np.minimum(svlen, 1000)).astype(np.int32)
+    d = ctx.span_depth(rs, re, S, E)
+    idx = np.random.default_rng(0).integers(0, len(S), 300)
+    for i in idx:
+        assert d[i] == O.span_count(rs, re, int(S[i]), int(E[i]))
+    # widening the window can only lower the count
+    d_wide = ctx.span_depth(rs, re, S - 500, E + 500)
+    assert np.all(d_wide <= d)
+    # dense windows (tiled path) == sparse evaluation of the same windows one by one
+    Sd = np.arange(5_000_000, 5_000_000 + 4096, dtype=np.int32)
+    dd = ctx.span_depth(rs, re, Sd, Sd + 50)
+    for i in range(0, 4096, 257):
+        assert dd[i] == O.span_count(rs, re, int(Sd[i]), int(Sd[i]) + 50)

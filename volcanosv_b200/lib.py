@@ -1,0 +1,270 @@
+"""ctypes binding of libvolcano_b200.so (include/volcanosv_b200.h).
+
+There is no CPU fallback: if the shared library is missing or no CUDA device is
+present, creating a Context raises.  Host-IO methods take/return numpy arrays; the
+`*_dev` variants take raw device pointers (ints) for resident pipelines.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libvolcano_b200.so")
+
+MODE_CONTIG, MODE_READS, MODE_CUTE = 0, 1, 2
+DEL, INS = 0, 1
+SPLIT_HIFI, SPLIT_ONT, SPLIT_CLR, SPLIT_READS = 0, 1, 2, 3
+E_CUDA, E_ARG, E_CAPACITY, E_NOMEM = -1, -2, -3, -4
+
+SIG_DTYPE = np.dtype([("rec", "<i4"), ("type", "<i4"), ("pos", "<i4"), ("len", "<i4"),
+                      ("q0", "<i4"), ("q1", "<i4"), ("first", "<i4"), ("count", "<i4")])
+assert SIG_DTYPE.itemsize == 32
+
+
+class VsvError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("volcanosv_b200 error %d: %s" % (code, msg))
+        self.code = code
+
+
+_lib = None
+_vp, _i64, _i32, _int = C.c_void_p, C.c_int64, C.c_int32, C.c_int
+
+# name -> argtypes (restype is always int unless listed in _RESTYPE)
+SIGNATURES = {
+    "vsv_ctx_create": [_int, C.POINTER(_vp)],
+    "vsv_ctx_destroy": [_vp],
+    "vsv_last_error": [_vp],
+    "vsv_ctx_set_device_io": [_vp, _int],
+    "vsv_sync": [_vp],
+    "vsv_alloc_pinned": [C.POINTER(_vp), C.c_size_t],
+    "vsv_free_pinned": [_vp],
+    "vsv_get_timing": [_vp, C.POINTER(C.c_float), C.POINTER(_i64)],
+    "vsv_version": [],
+    "vsv_scan_cigar": [_vp, _int, _int, _int, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _i64, C.POINTER(_i64), _vp, _vp, _vp],
+    "vsv_merge_in_record": [_vp, _int, _vp, _i64, _vp, C.POINTER(_i64), _vp, C.POINTER(_i64)],
+    "vsv_split_pairs": [_vp, _int, _int, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _i64, C.POINTER(_i64)],
+    "vsv_argsort_stable": [_vp, _vp, _i64, _vp],
+    "vsv_cluster": [_vp, _int, _vp, _vp, _i64, _vp, C.POINTER(_i64)],
+    "vsv_pair_haps": [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _i64, _vp, _vp],
+    "vsv_fp_support": [_vp, _vp, _vp, _i64, _vp, _vp, _i64, _vp],
+    "vsv_ins_cov": [_vp, _vp, _i64, _vp, _vp, _i64, _int, _vp],
+    "vsv_del_cov": [_vp, _vp, _vp, _i64, _vp, _vp, _i64, _int, _vp],
+    "vsv_group_sigs": [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, C.POINTER(_i64)],
+    "vsv_sig_support": [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _i64, _i32, _vp, _vp, C.POINTER(_i32)],
+    "vsv_span_depth": [_vp, _vp, _vp, _i64, _vp, _vp, _i64, _vp],
+    "vsv_genotype": [_vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp],
+}
+_RESTYPE = {"vsv_ctx_destroy": None, "vsv_last_error": C.c_char_p, "vsv_version": C.c_char_p}
+
+
+def load_library(path: Optional[str] = None):
+    """dlopen the in-tree CUDA library.  Raises (never falls back) if it is absent."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = path or LIB_PATH
+    if not os.path.exists(path):
+        raise VsvError(E_CUDA, "CUDA extension %s not built; run `python -m volcanosv_b200.build` "
+                               "(there is no CPU fallback)" % path)
+    lib = C.CDLL(path)
+    for name, args in SIGNATURES.items():
+        fn = getattr(lib, name)
+        fn.argtypes = args
+        fn.restype = _RESTYPE.get(name, _int)
+    _lib = lib
+    return lib
+
+
+def _arr(a, dtype):
+    if a is None:
+        return None
+    return np.ascontiguousarray(a, dtype=dtype)
+
+
+def _p(a):
+    if a is None:
+        return None
+    if isinstance(a, int):
+        return C.c_void_p(a)
+    return C.c_void_p(a.ctypes.data)
+
+
+class Context:
+    """One vsv_ctx (one GPU, one stream).  Not thread-safe."""
+
+    def __init__(self, device: int = 0):
+        self.lib = load_library()
+        h = _vp()
+        rc = self.lib.vsv_ctx_create(device, C.byref(h))
+        if rc != 0:
+            raise VsvError(rc, "vsv_ctx_create(device=%d) failed: no usable CUDA device "
+                               "(this library has no CPU path)" % device)
+        self.h = h
+        self.device = device
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.vsv_ctx_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _chk(self, rc):
+        if rc != 0:
+            raise VsvError(rc, (self.lib.vsv_last_error(self.h) or b"").decode())
+
+    def set_device_io(self, on: bool):
+        self._chk(self.lib.vsv_ctx_set_device_io(self.h, 1 if on else 0))
+
+    def sync(self):
+        self._chk(self.lib.vsv_sync(self.h))
+
+    def timing(self):
+        ms, n = C.c_float(), _i64()
+        self._chk(self.lib.vsv_get_timing(self.h, C.byref(ms), C.byref(n)))
+        return ms.value, n.value
+
+    # ---- stage 1 ---------------------------------------------------------------
+    def scan_cigar(self, mode, ops, op_off, pos, mapq, enable=None, min_len=30, min_mapq=0,
+                   cap=None, totals=True):
+        """-> (sigs[SIG_DTYPE], ref_total, qry_total, aux_total)."""
+        ops = _arr(ops, np.uint32)
+        op_off = _arr(op_off, np.int64)
+        pos = _arr(pos, np.int32)
+        mapq = _arr(mapq, np.uint8)
+        enable = _arr(enable, np.uint8)
+        n = len(pos)
+        if ops.ctypes.data % 16:
+            ops = _aligned_copy(ops)
+        if cap is None:
+            cap = max(1024, len(ops) // 16)
+        rt = np.zeros(n, np.int32) if totals else None
+        qt = np.zeros(n, np.int32) if totals else None
+        xt = np.zeros(n, np.int32) if totals else None
+        while True:
+            out = _aligned_empty(cap, SIG_DTYPE)
+            n_out = _i64()
+            rc = self.lib.vsv_scan_cigar(self.h, mode, min_len, min_mapq, _p(ops), _p(op_off), _p(pos), _p(mapq),
+                                         _p(enable), n, _p(out), cap, C.byref(n_out), _p(rt), _p(qt), _p(xt))
+            if rc == E_CAPACITY:
+                cap = int(n_out.value)
+                continue
+            self._chk(rc)
+            return out[: n_out.value], rt, qt, xt
+
+    def merge_in_record(self, mode, sigs):
+        sigs = np.ascontiguousarray(sigs, dtype=SIG_DTYPE)
+        n = len(sigs)
+        od, oi = np.empty(n, SIG_DTYPE), np.empty(n, SIG_DTYPE)
+        nd, ni = _i64(), _i64()
+        self._chk(self.lib.vsv_merge_in_record(self.h, mode, _p(sigs), n, _p(od), C.byref(nd), _p(oi), C.byref(ni)))
+        return od[: nd.value], oi[: ni.value]
+
+    def split_pairs(self, variant, min_mapq, pos, ref_end, readlen, first_op, last_op, mapq, is_rev, name_id,
+                    select=None):
+        n = len(pos)
+        a = [_arr(pos, np.int32), _arr(ref_end, np.int32), _arr(readlen, np.int32), _arr(first_op, np.uint32),
+             _arr(last_op, np.uint32), _arr(mapq, np.uint8), _arr(is_rev, np.uint8), _arr(name_id, np.int32),
+             _arr(select, np.uint8)]
+        out = np.empty(max(n, 1), SIG_DTYPE)
+        n_out = _i64()
+        self._chk(self.lib.vsv_split_pairs(self.h, variant, min_mapq, *[_p(x) for x in a], n, _p(out), len(out),
+                                           C.byref(n_out)))
+        return out[: n_out.value]
+
+    # ---- stage 2 ---------------------------------------------------------------
+    def argsort_stable(self, key):
+        key = _arr(key, np.int32)
+        order = np.empty(len(key), np.int32)
+        self._chk(self.lib.vsv_argsort_stable(self.h, _p(key), len(key), _p(order)))
+        return order
+
+    def cluster(self, is_del, pos, length):
+        pos, length = _arr(pos, np.int32), _arr(length, np.int32)
+        keep = np.empty(len(pos), np.int32)
+        nk = _i64()
+        self._chk(self.lib.vsv_cluster(self.h, 1 if is_del else 0, _p(pos), _p(length), len(pos), _p(keep), C.byref(nk)))
+        return keep[: nk.value]
+
+    def pair_haps(self, pos1, len1, typ1, pos2, len2, typ2):
+        a = [_arr(x, np.int32) for x in (pos1, len1, typ1)]
+        b = [_arr(x, np.int32) for x in (pos2, len2, typ2)]
+        p1, p2 = np.empty(len(a[0]), np.int32), np.empty(len(b[0]), np.int32)
+        self._chk(self.lib.vsv_pair_haps(self.h, _p(a[0]), _p(a[1]), _p(a[2]), len(a[0]), _p(b[0]), _p(b[1]), _p(b[2]),
+                                         len(b[0]), _p(p1), _p(p2)))
+        return p1, p2
+
+    def fp_support(self, call_pos, call_len, sig_pos, sig_len):
+        cp, cl, sp, sl = (_arr(x, np.int32) for x in (call_pos, call_len, sig_pos, sig_len))
+        out = np.empty(len(cp), np.int32)
+        self._chk(self.lib.vsv_fp_support(self.h, _p(cp), _p(cl), len(cp), _p(sp), _p(sl), len(sp), _p(out)))
+        return out
+
+    def ins_cov(self, call_pos, sig_pos, sig_len, flanking=1000):
+        cp, sp, sl = (_arr(x, np.int32) for x in (call_pos, sig_pos, sig_len))
+        out = np.empty(len(cp), np.int64)
+        self._chk(self.lib.vsv_ins_cov(self.h, _p(cp), len(cp), _p(sp), _p(sl), len(sp), flanking, _p(out)))
+        return out
+
+    def del_cov(self, call_start, call_end, sig_pos, sig_len, flanking=1000):
+        cs, ce, sp, sl = (_arr(x, np.int32) for x in (call_start, call_end, sig_pos, sig_len))
+        out = np.empty(len(cs), np.int64)
+        self._chk(self.lib.vsv_del_cov(self.h, _p(cs), _p(ce), len(cs), _p(sp), _p(sl), len(sp), flanking, _p(out)))
+        return out
+
+    # ---- stage 3 ---------------------------------------------------------------
+    def group_sigs(self, chrom, pos, length):
+        c, p, l = (_arr(x, np.int32) for x in (chrom, pos, length))
+        n = len(c)
+        o = [np.empty(n, np.int32) for _ in range(4)]
+        nu = _i64()
+        self._chk(self.lib.vsv_group_sigs(self.h, _p(c), _p(p), _p(l), n, _p(o[0]), _p(o[1]), _p(o[2]), _p(o[3]),
+                                          C.byref(nu)))
+        return tuple(x[: nu.value] for x in o)
+
+    def sig_support(self, cand_chrom, cand_pos, cand_svlen, sig_chrom, sig_pos, sig_len, sig_cnt, last_in=0):
+        cc, cp, cl = (_arr(x, np.int32) for x in (cand_chrom, cand_pos, cand_svlen))
+        sc, sp, sl, sn = (_arr(x, np.int32) for x in (sig_chrom, sig_pos, sig_len, sig_cnt))
+        sup, mid = np.empty(len(cc), np.int32), np.empty(len(cc), np.int32)
+        last = _i32()
+        self._chk(self.lib.vsv_sig_support(self.h, _p(cc), _p(cp), _p(cl), len(cc), _p(sc), _p(sp), _p(sl), _p(sn),
+                                           len(sc), last_in, _p(sup), _p(mid), C.byref(last)))
+        return sup, mid, last.value
+
+    def span_depth(self, read_start, read_end, S, E):
+        rs, re, s, e = (_arr(x, np.int32) for x in (read_start, read_end, S, E))
+        out = np.empty(len(s), np.int32)
+        self._chk(self.lib.vsv_span_depth(self.h, _p(rs), _p(re), len(rs), _p(s), _p(e), len(s), _p(out)))
+        return out
+
+    def genotype(self, read_start, read_end, cand_pos, cand_svlen, cand_type, call_gt, n_support, thr_del, thr_ins):
+        rs, re = _arr(read_start, np.int32), _arr(read_end, np.int32)
+        cp, cl, ct, cg, ns = (_arr(x, np.int32) for x in (cand_pos, cand_svlen, cand_type, call_gt, n_support))
+        td, ti = _arr(thr_del, np.float64), _arr(thr_ins, np.float64)
+        n = len(cp)
+        d2, ratio, ng = np.empty(n, np.int32), np.empty(n, np.float64), np.empty(n, np.int32)
+        self._chk(self.lib.vsv_genotype(self.h, _p(rs), _p(re), len(rs), _p(cp), _p(cl), _p(ct), _p(cg), _p(ns), n,
+                                        _p(td), _p(ti), _p(d2), _p(ratio), _p(ng)))
+        return d2, ratio, ng
+
+
+def _aligned_empty(n, dtype, align=64):
+    dtype = np.dtype(dtype)
+    raw = np.empty(n * dtype.itemsize + align, np.uint8)
+    off = (-raw.ctypes.data) % align
+    return raw[off: off + n * dtype.itemsize].view(dtype)
+
+
+def _aligned_copy(a, align=64):
+    out = _aligned_empty(len(a), a.dtype, align)
+    out[:] = a
+    return out
