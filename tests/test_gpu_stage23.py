@@ -43,29 +43,34 @@ def test_split_pairs_golden(ctx, golden):
             assert got.get(i) == c["res"], (key, i)
 
 
-def test_split_pairs_driver_vs_oracle(ctx):
+def test_split_pairs_driver_vs_oracle(ctx, golden):
+    """Driver semantics (ECS_H:421-457): select filter, names in first-appearance order,
+    consecutive records of a name in coordinate order -- records of the golden pairs are
+    interleaved in BAM order, some names get a third record, some records are deselected."""
     rng = np.random.default_rng(5)
-    n = 4000
-    b = synth.synth_records(21, n, "hifi", clip_rate=0.8, n_names=1500)
-    _, rt, qt, xt = ctx.scan_cigar(V.MODE_CONTIG, b["ops"], b["op_off"], b["pos"], b["mapq"])
-    ref_end = b["pos"] + rt
-    rl = qt + xt
-    first_op = b["ops"][b["op_off"][:-1]]
-    last_op = b["ops"][b["op_off"][1:] - 1]
-    rev = (b["flag"] & 16) != 0
-    # make read lengths of same-name records agree often enough to produce signatures
-    sel = (b["mapq"] >= 50) & (b["hp"] == 1)
-    # re-intern names in first-appearance order over the selected records (host contract)
+    cases = golden("split_pair")["hifi"]
+    recs = []
+    for i, c in enumerate(cases):
+        nm = i if i % 7 else max(0, i - 1)          # every 7th pair shares the previous name
+        for cg, p, m, r in ((c["c1"], c["p1"], c["m1"], c["rev1"]), (c["c2"], c["p2"], c["m2"], c["rev2"])):
+            e, l, f, la = _info(cg, p, False)
+            recs.append((p, e, l, f, la, m, r, nm))
+    recs.sort(key=lambda t: t[0])
+    pos, end, rl, fo, lo, mq, rv, raw = (np.array(x) for x in zip(*recs))
+    n = len(pos)
+    sel = (mq >= 50) & (rng.random(n) < 0.9)
     remap, nid = {}, np.full(n, -1, np.int32)
     for r in range(n):
         if sel[r]:
-            nid[r] = remap.setdefault(int(b["name_id"][r]), len(remap))
+            nid[r] = remap.setdefault(int(raw[r]), len(remap))
+    tot = 0
     for variant in (V.SPLIT_HIFI, V.SPLIT_ONT, V.SPLIT_CLR, V.SPLIT_READS):
-        out = ctx.split_pairs(variant, 50, b["pos"], ref_end, rl, first_op, last_op, b["mapq"], rev, nid, sel)
-        exp = O.split_pairs(variant, b["pos"], ref_end, rl, first_op, last_op, b["mapq"], rev, nid, sel, 50)
+        out = ctx.split_pairs(variant, 50, pos, end, rl, fo, lo, mq, rv, nid, sel)
+        exp = O.split_pairs(variant, pos, end, rl, fo, lo, mq, rv, nid, sel, 50)
         got = [tuple(int(s[f]) for f in ("rec", "first", "type", "pos", "len", "q0", "q1")) for s in out]
         assert got == exp
-    assert len(exp) > 0
+        tot += len(exp)
+    assert tot > 50
 
 
 def test_argsort_stable(ctx):
