@@ -78,6 +78,11 @@ int vsv_free_pinned(void* p);
  * kernel launches since the ctx was created. */
 int vsv_get_timing(vsv_ctx* ctx, float* kernel_ms, int64_t* launches);
 const char* vsv_version(void);
+/* CUDA-event stopwatch on the ctx stream (bench.py brackets K steps with it), and the
+ * event time of the dominant kernel (k_scan_cigar) of the last vsv_scan_cigar call. */
+int vsv_timer_start(vsv_ctx* ctx);
+int vsv_timer_stop(vsv_ctx* ctx, float* ms);
+int vsv_get_main_kernel_ms(vsv_ctx* ctx, float* ms);
 
 /* ---- stage 1: signature scan -------------------------------------------------- */
 /* Replaces extract_sig_from_cigar (ECS_H:53-85, ERS:47-83) and the CIGAR walk of
@@ -113,6 +118,22 @@ int vsv_split_pairs(vsv_ctx* ctx, int variant, int min_mapq, const int32_t* pos,
  * the i-th smallest key. */
 int vsv_argsort_stable(vsv_ctx* ctx, const int32_t* key, int64_t n, int32_t* order);
 
+/* Sort a signature array.  tie_mode 0: stable by pos (sort_sig, ECS_H:170-179);
+ * tie_mode 1: the `.sigs` file order of SE:637-638 (`sort -k2,2 -k3,3n`, C locale): pos
+ * numeric, ties by len compared as a decimal STRING. */
+int vsv_sort_sigs(vsv_ctx* ctx, const vsv_sig* sigs, int64_t n, int tie_mode, vsv_sig* out);
+/* Struct-of-arrays view of a signature array (any output may be NULL). */
+int vsv_sig_columns(vsv_ctx* ctx, const vsv_sig* sigs, int64_t n, int32_t* pos, int32_t* len,
+                    int32_t* rec);
+
+/* Elementwise glue so a device-resident pipeline never leaves the ctx stream:
+ * out = a + b (reference_end = pos + ref_total); out = (a >= thr) (SE:439 read-length
+ * gate); out = key == val ? a : b (DEL/INS support select). */
+int vsv_add_i32(vsv_ctx* ctx, const int32_t* a, const int32_t* b, int64_t n, int32_t* out);
+int vsv_ge_u8(vsv_ctx* ctx, const int32_t* a, int32_t thr, int64_t n, uint8_t* out);
+int vsv_select_i32(vsv_ctx* ctx, const int32_t* key, int32_t val, const int32_t* a, const int32_t* b,
+                   int64_t n, int32_t* out);
+
 /* cluster_del / cluster_ins (ECS_H:196-288) on a pos-sorted list: kept indices in
  * leader order. */
 int vsv_cluster(vsv_ctx* ctx, int is_del, const int32_t* pos, const int32_t* len, int64_t n,
@@ -137,10 +158,12 @@ int vsv_del_cov(vsv_ctx* ctx, const int32_t* call_start, const int32_t* call_end
 
 /* ---- stage 3: genotyping ------------------------------------------------------ */
 /* load_sig (GTD:65-86) / load_sig_file (GTI:67-101) on a (chrom,pos)-sorted table:
- * unique (chrom,pos,len) rows with read counts.  Outputs need capacity n. */
+ * unique (chrom,pos,len) rows with read counts.  Outputs need capacity n.  chrom may be
+ * NULL (single chromosome: u_chrom is then filled with 0).  Rows with len < min_len are
+ * dropped first (GTI:81 keeps INS signatures >= 30 bp; DEL: pass 0). */
 int vsv_group_sigs(vsv_ctx* ctx, const int32_t* chrom, const int32_t* pos, const int32_t* len,
-                   int64_t n, int32_t* u_chrom, int32_t* u_pos, int32_t* u_len, int32_t* u_cnt,
-                   int64_t* n_unique);
+                   int64_t n, int min_len, int32_t* u_chrom, int32_t* u_pos, int32_t* u_len,
+                   int32_t* u_cnt, int64_t* n_unique);
 
 /* match_varlist_siglist (GTD:92-137) / extract_sig_support (GTI:107-166), including
  * the double count at last_match_idx.  last_in/last_out carry last_match_idx across

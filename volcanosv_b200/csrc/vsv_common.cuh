@@ -18,6 +18,10 @@ struct vsv_ctx {
   int sm_count = VSV_SM_COUNT_B200;
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  cudaEvent_t evt0 = nullptr, evt1 = nullptr;  // user stopwatch
+  cudaEvent_t evk0 = nullptr, evk1 = nullptr;  // dominant kernel of the last scan call
+  bool main_open = false;
+  float last_main_ms = 0.f;
   bool device_io = false;
   bool timing_open = false;
   float last_kernel_ms = 0.f;

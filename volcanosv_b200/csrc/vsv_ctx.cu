@@ -22,7 +22,9 @@ extern "C" int vsv_ctx_create(int device, vsv_ctx** out) {
   cudaDeviceProp prop;
   if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) c->sm_count = prop.multiProcessorCount;
   if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess ||
-      cudaEventCreate(&c->ev0) != cudaSuccess || cudaEventCreate(&c->ev1) != cudaSuccess) {
+      cudaEventCreate(&c->ev0) != cudaSuccess || cudaEventCreate(&c->ev1) != cudaSuccess ||
+      cudaEventCreate(&c->evt0) != cudaSuccess || cudaEventCreate(&c->evt1) != cudaSuccess ||
+      cudaEventCreate(&c->evk0) != cudaSuccess || cudaEventCreate(&c->evk1) != cudaSuccess) {
     delete c;
     return VSV_E_CUDA;
   }
@@ -43,6 +45,10 @@ extern "C" void vsv_ctx_destroy(vsv_ctx* c) {
   if (c->arena) cudaFree(c->arena);
   if (c->ev0) cudaEventDestroy(c->ev0);
   if (c->ev1) cudaEventDestroy(c->ev1);
+  if (c->evt0) cudaEventDestroy(c->evt0);
+  if (c->evt1) cudaEventDestroy(c->evt1);
+  if (c->evk0) cudaEventDestroy(c->evk0);
+  if (c->evk1) cudaEventDestroy(c->evk1);
   if (c->stream) cudaStreamDestroy(c->stream);
   delete c;
 }
@@ -76,6 +82,31 @@ extern "C" int vsv_get_timing(vsv_ctx* c, float* kernel_ms, int64_t* launches) {
   }
   if (kernel_ms) *kernel_ms = c->last_kernel_ms;
   if (launches) *launches = c->launches;
+  return VSV_OK;
+}
+
+extern "C" int vsv_timer_start(vsv_ctx* c) {
+  if (!c) return VSV_E_ARG;
+  VSV_CUDA(c, cudaSetDevice(c->device));
+  VSV_CUDA(c, cudaStreamSynchronize(c->stream));
+  VSV_CUDA(c, cudaEventRecord(c->evt0, c->stream));
+  return VSV_OK;
+}
+extern "C" int vsv_timer_stop(vsv_ctx* c, float* ms) {
+  if (!c || !ms) return VSV_E_ARG;
+  VSV_CUDA(c, cudaEventRecord(c->evt1, c->stream));
+  VSV_CUDA(c, cudaEventSynchronize(c->evt1));
+  VSV_CUDA(c, cudaEventElapsedTime(ms, c->evt0, c->evt1));
+  return VSV_OK;
+}
+extern "C" int vsv_get_main_kernel_ms(vsv_ctx* c, float* ms) {
+  if (!c || !ms) return VSV_E_ARG;
+  if (c->main_open) {
+    VSV_CUDA(c, cudaEventSynchronize(c->evk1));
+    VSV_CUDA(c, cudaEventElapsedTime(&c->last_main_ms, c->evk0, c->evk1));
+    c->main_open = false;
+  }
+  *ms = c->last_main_ms;
   return VSV_OK;
 }
 

@@ -429,11 +429,14 @@ extern "C" int vsv_scan_cigar(vsv_ctx* ctx, int mode, int min_len, int min_mapq,
     }
     VSV_LAUNCH(ctx, k_tile_records, (unsigned)vsv_cdiv(n_tiles, 256), 256, 0, p.op_off, n_rec, n_ops, n_tiles, d_rf,
                d_rl);
+    VSV_CUDA(ctx, cudaEventRecord(ctx->evk0, ctx->stream));
     switch (mode) {
       case VSV_MODE_CONTIG: VSV_LAUNCH(ctx, k_scan_cigar<VSV_MODE_CONTIG>, (unsigned)n_tiles, SCAN_THREADS, 0, p); break;
       case VSV_MODE_READS: VSV_LAUNCH(ctx, k_scan_cigar<VSV_MODE_READS>, (unsigned)n_tiles, SCAN_THREADS, 0, p); break;
       default: VSV_LAUNCH(ctx, k_scan_cigar<VSV_MODE_CUTE>, (unsigned)n_tiles, SCAN_THREADS, 0, p); break;
     }
+    VSV_CUDA(ctx, cudaEventRecord(ctx->evk1, ctx->stream));
+    ctx->main_open = true;
   } else if (want_tot) {
     VSV_CUDA(ctx, cudaMemsetAsync(d_rt, 0, sizeof(int32_t) * (size_t)n_rec, ctx->stream));
     VSV_CUDA(ctx, cudaMemsetAsync(d_qt, 0, sizeof(int32_t) * (size_t)n_rec, ctx->stream));

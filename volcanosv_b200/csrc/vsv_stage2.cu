@@ -515,3 +515,174 @@ extern "C" int vsv_del_cov(vsv_ctx* ctx, const int32_t* call_start, const int32_
   VSV_TRY(vsv_out_done(ctx, cov, dc, (size_t)n_call));
   return vsv_end(ctx);
 }
+
+// --------------------------------------------------------------------------------
+// signature sort + column extraction (device-resident pipeline plumbing)
+// --------------------------------------------------------------------------------
+// tie_mode 0: stable by pos (sort_sig, ECS_H:170-179).
+// tie_mode 1: `.sigs` order (SE:637-638 `sort -k2,2 -k3,3n`, LC_ALL=C): pos numeric, ties by
+//             the rest of the line, whose first field is len as a DECIMAL STRING
+//             ("100" < "95", "10" < "100").
+__global__ void k_len_string_key(const vsv_sig* __restrict__ s, int64_t n, unsigned long long* __restrict__ key,
+                                 int32_t* __restrict__ idx) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  unsigned long long v = (unsigned long long)(uint32_t)max(s[i].len, 0);
+  int digits = 1;
+  for (unsigned long long t = v; t >= 10ull; t /= 10ull) ++digits;
+  unsigned long long scaled = v;
+  for (int d = digits; d < 10; ++d) scaled *= 10ull;  // left-justify to 10 digits
+  key[i] = (scaled << 4) | (unsigned long long)digits;
+  idx[i] = (int32_t)i;
+}
+__global__ void k_gather_pos(const vsv_sig* __restrict__ s, const int32_t* __restrict__ idx, int64_t n,
+                             int32_t* __restrict__ pos) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) pos[i] = s[idx ? idx[i] : i].pos;
+}
+__global__ void k_gather_sigs(const vsv_sig* __restrict__ s, const int32_t* __restrict__ idx, int64_t n,
+                              vsv_sig* __restrict__ out) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int4* src = reinterpret_cast<const int4*>(s + idx[i]);
+  int4* dst = reinterpret_cast<int4*>(out + i);
+  dst[0] = src[0];
+  dst[1] = src[1];
+}
+
+extern "C" int vsv_sort_sigs(vsv_ctx* ctx, const vsv_sig* sigs, int64_t n, int tie_mode, vsv_sig* out) {
+  VSV_TRY(vsv_begin(ctx));
+  if (n < 0 || n >= (int64_t(1) << 31) || tie_mode < 0 || tie_mode > 1) VSV_FAIL(ctx, VSV_E_ARG, "vsv_sort_sigs: bad argument");
+  if (n == 0) return VSV_OK;
+  const vsv_sig* din;
+  vsv_sig* dout;
+  VSV_TRY(vsv_in(ctx, sigs, (size_t)n, &din));
+  VSV_TRY(vsv_out(ctx, out, (size_t)n, &dout));
+  int32_t *idx0 = nullptr, *idx1 = nullptr, *pos, *order;
+  VSV_TRY(vsv_tmp(ctx, (size_t)n, &pos));
+  VSV_TRY(vsv_tmp(ctx, (size_t)n, &order));
+  const unsigned g = (unsigned)vsv_cdiv(n, 256);
+  VSV_TRY(vsv_t0(ctx));
+  if (tie_mode == 1) {
+    unsigned long long *k0, *k1;
+    VSV_TRY(vsv_tmp(ctx, (size_t)n, &k0));
+    VSV_TRY(vsv_tmp(ctx, (size_t)n, &k1));
+    VSV_TRY(vsv_tmp(ctx, (size_t)n, &idx0));
+    VSV_TRY(vsv_tmp(ctx, (size_t)n, &idx1));
+    VSV_LAUNCH(ctx, k_len_string_key, g, 256, 0, din, n, k0, idx0);
+    size_t tb = 0;
+    VSV_CUDA(ctx, cub::DeviceRadixSort::SortPairs(nullptr, tb, k0, k1, idx0, idx1, (int)n, 0, 40, ctx->stream));
+    void* tmp = nullptr;
+    VSV_TRY(vsv_arena_alloc(ctx, tb, &tmp));
+    VSV_CUDA(ctx, cub::DeviceRadixSort::SortPairs(tmp, tb, k0, k1, idx0, idx1, (int)n, 0, 40, ctx->stream));
+    ctx->launches += 2;
+  }
+  VSV_LAUNCH(ctx, k_gather_pos, g, 256, 0, din, (const int32_t*)idx1, n, pos);
+  {
+    int32_t* ks;
+    VSV_TRY(vsv_tmp(ctx, (size_t)n, &ks));
+    if (!idx1) {
+      VSV_TRY(argsort_dev(ctx, pos, n, order, ks));
+    } else {
+      size_t tb = 0;
+      VSV_CUDA(ctx, cub::DeviceRadixSort::SortPairs(nullptr, tb, pos, ks, idx1, order, (int)n, 0, 32, ctx->stream));
+      void* tmp = nullptr;
+      VSV_TRY(vsv_arena_alloc(ctx, tb, &tmp));
+      VSV_CUDA(ctx, cub::DeviceRadixSort::SortPairs(tmp, tb, pos, ks, idx1, order, (int)n, 0, 32, ctx->stream));
+      ctx->launches += 2;
+    }
+  }
+  VSV_LAUNCH(ctx, k_gather_sigs, g, 256, 0, din, order, n, dout);
+  VSV_TRY(vsv_t1(ctx));
+  VSV_TRY(vsv_out_done(ctx, out, dout, (size_t)n));
+  return vsv_end(ctx);
+}
+
+__global__ void k_sig_columns(const vsv_sig* __restrict__ s, int64_t n, int32_t* __restrict__ pos,
+                              int32_t* __restrict__ len, int32_t* __restrict__ rec) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int4 a = *reinterpret_cast<const int4*>(s + i);  // rec, type, pos, len
+  if (pos) pos[i] = a.z;
+  if (len) len[i] = a.w;
+  if (rec) rec[i] = a.x;
+}
+
+extern "C" int vsv_sig_columns(vsv_ctx* ctx, const vsv_sig* sigs, int64_t n, int32_t* pos, int32_t* len,
+                               int32_t* rec) {
+  VSV_TRY(vsv_begin(ctx));
+  if (n < 0) VSV_FAIL(ctx, VSV_E_ARG, "vsv_sig_columns: bad argument");
+  if (n == 0) return VSV_OK;
+  const vsv_sig* din;
+  int32_t *dp, *dl, *dr;
+  VSV_TRY(vsv_in(ctx, sigs, (size_t)n, &din));
+  VSV_TRY(vsv_out(ctx, pos, (size_t)n, &dp));
+  VSV_TRY(vsv_out(ctx, len, (size_t)n, &dl));
+  VSV_TRY(vsv_out(ctx, rec, (size_t)n, &dr));
+  VSV_TRY(vsv_t0(ctx));
+  VSV_LAUNCH(ctx, k_sig_columns, (unsigned)vsv_cdiv(n, 256), 256, 0, din, n, dp, dl, dr);
+  VSV_TRY(vsv_t1(ctx));
+  VSV_TRY(vsv_out_done(ctx, pos, dp, (size_t)n));
+  VSV_TRY(vsv_out_done(ctx, len, dl, (size_t)n));
+  VSV_TRY(vsv_out_done(ctx, rec, dr, (size_t)n));
+  return vsv_end(ctx);
+}
+
+// --------------------------------------------------------------------------------
+// elementwise glue for the device-resident pipeline (keeps everything on the ctx stream)
+// --------------------------------------------------------------------------------
+__global__ void k_add_i32(const int32_t* __restrict__ a, const int32_t* __restrict__ b, int64_t n,
+                          int32_t* __restrict__ out) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = a[i] + b[i];
+}
+__global__ void k_ge_u8(const int32_t* __restrict__ a, int32_t thr, int64_t n, uint8_t* __restrict__ out) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = a[i] >= thr ? 1 : 0;
+}
+__global__ void k_select_i32(const int32_t* __restrict__ key, int32_t val, const int32_t* __restrict__ a,
+                             const int32_t* __restrict__ b, int64_t n, int32_t* __restrict__ out) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = key[i] == val ? a[i] : b[i];
+}
+
+extern "C" int vsv_add_i32(vsv_ctx* ctx, const int32_t* a, const int32_t* b, int64_t n, int32_t* out) {
+  VSV_TRY(vsv_begin(ctx));
+  if (n < 0) VSV_FAIL(ctx, VSV_E_ARG, "vsv_add_i32: bad n");
+  if (n == 0) return VSV_OK;
+  const int32_t *da, *db;
+  int32_t* dout;
+  VSV_TRY(vsv_in(ctx, a, (size_t)n, &da));
+  VSV_TRY(vsv_in(ctx, b, (size_t)n, &db));
+  VSV_TRY(vsv_out(ctx, out, (size_t)n, &dout));
+  VSV_LAUNCH(ctx, k_add_i32, (unsigned)vsv_cdiv(n, 256), 256, 0, da, db, n, dout);
+  VSV_TRY(vsv_out_done(ctx, out, dout, (size_t)n));
+  return vsv_end(ctx);
+}
+extern "C" int vsv_ge_u8(vsv_ctx* ctx, const int32_t* a, int32_t thr, int64_t n, uint8_t* out) {
+  VSV_TRY(vsv_begin(ctx));
+  if (n < 0) VSV_FAIL(ctx, VSV_E_ARG, "vsv_ge_u8: bad n");
+  if (n == 0) return VSV_OK;
+  const int32_t* da;
+  uint8_t* dout;
+  VSV_TRY(vsv_in(ctx, a, (size_t)n, &da));
+  VSV_TRY(vsv_out(ctx, out, (size_t)n, &dout));
+  VSV_LAUNCH(ctx, k_ge_u8, (unsigned)vsv_cdiv(n, 256), 256, 0, da, thr, n, dout);
+  VSV_TRY(vsv_out_done(ctx, out, dout, (size_t)n));
+  return vsv_end(ctx);
+}
+extern "C" int vsv_select_i32(vsv_ctx* ctx, const int32_t* key, int32_t val, const int32_t* a, const int32_t* b,
+                              int64_t n, int32_t* out) {
+  VSV_TRY(vsv_begin(ctx));
+  if (n < 0) VSV_FAIL(ctx, VSV_E_ARG, "vsv_select_i32: bad n");
+  if (n == 0) return VSV_OK;
+  const int32_t *dk, *da, *db;
+  int32_t* dout;
+  VSV_TRY(vsv_in(ctx, key, (size_t)n, &dk));
+  VSV_TRY(vsv_in(ctx, a, (size_t)n, &da));
+  VSV_TRY(vsv_in(ctx, b, (size_t)n, &db));
+  VSV_TRY(vsv_out(ctx, out, (size_t)n, &dout));
+  VSV_LAUNCH(ctx, k_select_i32, (unsigned)vsv_cdiv(n, 256), 256, 0, dk, val, da, db, n, dout);
+  VSV_TRY(vsv_out_done(ctx, out, dout, (size_t)n));
+  return vsv_end(ctx);
+}

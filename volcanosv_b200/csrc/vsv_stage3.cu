@@ -8,10 +8,12 @@
 // group_sigs: run-length encode adjacent equal (chrom,pos,len)
 // --------------------------------------------------------------------------------
 __global__ void k_group_heads(const int32_t* __restrict__ c, const int32_t* __restrict__ p,
-                              const int32_t* __restrict__ l, int64_t n, int32_t* __restrict__ head) {
+                              const int32_t* __restrict__ l, int64_t n, int min_len,
+                              int32_t* __restrict__ head) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  head[i] = (i == 0 || c[i] != c[i - 1] || p[i] != p[i - 1] || l[i] != l[i - 1]) ? 1 : 0;
+  // rows shorter than min_len are dropped before grouping (GTI:81); equal keys share a len
+  head[i] = (l[i] < min_len) ? 0 : (i == 0 || (c && c[i] != c[i - 1]) || p[i] != p[i - 1] || l[i] != l[i - 1]) ? 1 : 0;
 }
 __global__ void k_group_write(const int32_t* __restrict__ c, const int32_t* __restrict__ p,
                               const int32_t* __restrict__ l, int64_t n, const int32_t* __restrict__ head,
@@ -20,14 +22,14 @@ __global__ void k_group_write(const int32_t* __restrict__ c, const int32_t* __re
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n || !head[i]) return;
   int64_t e = i + 1;
-  while (e < n && !head[e]) ++e;
+  while (e < n && !head[e] && p[e] == p[i] && l[e] == l[i] && (!c || c[e] == c[i])) ++e;
   int64_t o = excl[i];
-  uc[o] = c[i]; up[o] = p[i]; ul[o] = l[i]; ucnt[o] = (int32_t)(e - i);
+  uc[o] = c ? c[i] : 0; up[o] = p[i]; ul[o] = l[i]; ucnt[o] = (int32_t)(e - i);
 }
 
 extern "C" int vsv_group_sigs(vsv_ctx* ctx, const int32_t* chrom, const int32_t* pos, const int32_t* len,
-                              int64_t n, int32_t* u_chrom, int32_t* u_pos, int32_t* u_len, int32_t* u_cnt,
-                              int64_t* n_unique) {
+                              int64_t n, int min_len, int32_t* u_chrom, int32_t* u_pos, int32_t* u_len,
+                              int32_t* u_cnt, int64_t* n_unique) {
   VSV_TRY(vsv_begin(ctx));
   if (n < 0 || !n_unique) VSV_FAIL(ctx, VSV_E_ARG, "vsv_group_sigs: bad argument");
   *n_unique = 0;
@@ -47,7 +49,7 @@ extern "C" int vsv_group_sigs(vsv_ctx* ctx, const int32_t* chrom, const int32_t*
   VSV_TRY(vsv_tmp(ctx, 1, &tot));
   const unsigned g = (unsigned)vsv_cdiv(n, 256);
   VSV_TRY(vsv_t0(ctx));
-  VSV_LAUNCH(ctx, k_group_heads, g, 256, 0, dc, dp, dl, n, head);
+  VSV_LAUNCH(ctx, k_group_heads, g, 256, 0, dc, dp, dl, n, min_len, head);
   VSV_TRY(vsv_exclusive_scan_i32(ctx, head, n, excl, tot));
   VSV_LAUNCH(ctx, k_group_write, g, 256, 0, dc, dp, dl, n, head, excl, oc, op, ol, on);
   VSV_TRY(vsv_t1(ctx));
@@ -77,6 +79,10 @@ __global__ void k_chrom_runs(const int32_t* __restrict__ sc, int64_t n, int32_t*
   if (i == n - 1 || sc[i + 1] != c) seg_hi[c] = (int32_t)(i + 1);
 }
 
+__global__ void k_single_chrom(int64_t n, int32_t* __restrict__ seg_lo, int32_t* __restrict__ seg_hi) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) { seg_lo[0] = 0; seg_hi[0] = (int32_t)n; }
+}
+
 #define SUP_GROUP 8  // lanes cooperating on one candidate
 __global__ void k_support_window(const int32_t* __restrict__ cc, const int32_t* __restrict__ cp,
                                  const int32_t* __restrict__ cl, int64_t n_cand,
@@ -89,7 +95,7 @@ __global__ void k_support_window(const int32_t* __restrict__ cc, const int32_t* 
   const int g = threadIdx.x % SUP_GROUP;
   const unsigned gmask = 0xFFu << ((threadIdx.x & 31) / SUP_GROUP * SUP_GROUP);
   if (k >= n_cand) return;  // whole groups exit together (blockDim multiple of SUP_GROUP)
-  const int32_t c = cc[k];
+  const int32_t c = cc ? cc[k] : 0;
   const double sv = (double)cl[k];
   const double max_size = sv / min_size_sim;      // GTD:103
   const double min_size = sv * min_size_sim;      // GTD:104
@@ -127,7 +133,7 @@ __global__ void k_support_fixup(const int32_t* __restrict__ cc, const int32_t* _
   if (k > 0 && last_scan[k - 1] >= 0) idx0 = last_scan[k - 1];
   if (match_id) match_id[k] = idx0;
   // both of the reference's scans visit last_match_idx itself (GTD:112-130): double count
-  if (idx0 >= lb[k] && idx0 < ub[k] && idx0 < n_sig && sc[idx0] == cc[k]) {
+  if (idx0 >= lb[k] && idx0 < ub[k] && idx0 < n_sig && (sc == nullptr || cc == nullptr || sc[idx0] == cc[k])) {
     const double sv = (double)cl[k];
     const double L = (double)sl[idx0];
     if (sv * min_size_sim <= L && L <= sv / min_size_sim) support[k] += sn[idx0];
@@ -169,7 +175,10 @@ extern "C" int vsv_sig_support(vsv_ctx* ctx, const int32_t* cand_chrom, const in
   VSV_TRY(vsv_t0(ctx));
   VSV_CUDA(ctx, cudaMemsetAsync(seg, 0xFF, sizeof(int32_t) * 2 * VSV_MAX_CHROM, ctx->stream));
   VSV_CUDA(ctx, cudaMemsetAsync(bad, 0, 2 * sizeof(int32_t), ctx->stream));
-  if (n_sig > 0) VSV_LAUNCH(ctx, k_chrom_runs, (unsigned)vsv_cdiv(n_sig, 256), 256, 0, sc, n_sig, seg_lo, seg_hi, bad);
+  if ((cand_chrom == nullptr) != (sig_chrom == nullptr))
+    VSV_FAIL(ctx, VSV_E_ARG, "vsv_sig_support: pass both chromosome arrays or neither");
+  if (n_sig > 0 && sig_chrom == nullptr) VSV_LAUNCH(ctx, k_single_chrom, 1, 32, 0, n_sig, seg_lo, seg_hi);
+  else if (n_sig > 0) VSV_LAUNCH(ctx, k_chrom_runs, (unsigned)vsv_cdiv(n_sig, 256), 256, 0, sc, n_sig, seg_lo, seg_hi, bad);
   VSV_LAUNCH(ctx, k_support_window, (unsigned)vsv_cdiv(n_cand * SUP_GROUP, 256), 256, 0, cc, cp, cl, n_cand, sp, sl, sn,
              seg_lo, seg_hi, 0.6, 2.3, lb, ub, vlb, d_sup);
   VSV_TRY(inclusive_scan_i32(ctx, vlb, lscan, n_cand, LastValid()));

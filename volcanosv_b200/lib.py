@@ -45,16 +45,24 @@ SIGNATURES = {
     "vsv_free_pinned": [_vp],
     "vsv_get_timing": [_vp, C.POINTER(C.c_float), C.POINTER(_i64)],
     "vsv_version": [],
+    "vsv_timer_start": [_vp],
+    "vsv_timer_stop": [_vp, C.POINTER(C.c_float)],
+    "vsv_get_main_kernel_ms": [_vp, C.POINTER(C.c_float)],
     "vsv_scan_cigar": [_vp, _int, _int, _int, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _i64, C.POINTER(_i64), _vp, _vp, _vp],
     "vsv_merge_in_record": [_vp, _int, _vp, _i64, _vp, C.POINTER(_i64), _vp, C.POINTER(_i64)],
     "vsv_split_pairs": [_vp, _int, _int, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _i64, C.POINTER(_i64)],
     "vsv_argsort_stable": [_vp, _vp, _i64, _vp],
+    "vsv_sort_sigs": [_vp, _vp, _i64, _int, _vp],
+    "vsv_sig_columns": [_vp, _vp, _i64, _vp, _vp, _vp],
+    "vsv_add_i32": [_vp, _vp, _vp, _i64, _vp],
+    "vsv_ge_u8": [_vp, _vp, _i32, _i64, _vp],
+    "vsv_select_i32": [_vp, _vp, _i32, _vp, _vp, _i64, _vp],
     "vsv_cluster": [_vp, _int, _vp, _vp, _i64, _vp, C.POINTER(_i64)],
     "vsv_pair_haps": [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _i64, _vp, _vp],
     "vsv_fp_support": [_vp, _vp, _vp, _i64, _vp, _vp, _i64, _vp],
     "vsv_ins_cov": [_vp, _vp, _i64, _vp, _vp, _i64, _int, _vp],
     "vsv_del_cov": [_vp, _vp, _vp, _i64, _vp, _vp, _i64, _int, _vp],
-    "vsv_group_sigs": [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, C.POINTER(_i64)],
+    "vsv_group_sigs": [_vp, _vp, _vp, _vp, _i64, _int, _vp, _vp, _vp, _vp, C.POINTER(_i64)],
     "vsv_sig_support": [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _i64, _i32, _vp, _vp, C.POINTER(_i32)],
     "vsv_span_depth": [_vp, _vp, _vp, _i64, _vp, _vp, _i64, _vp],
     "vsv_genotype": [_vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp],
@@ -128,6 +136,19 @@ class Context:
     def sync(self):
         self._chk(self.lib.vsv_sync(self.h))
 
+    def timer_start(self):
+        self._chk(self.lib.vsv_timer_start(self.h))
+
+    def timer_stop(self):
+        ms = C.c_float()
+        self._chk(self.lib.vsv_timer_stop(self.h, C.byref(ms)))
+        return ms.value
+
+    def main_kernel_ms(self):
+        ms = C.c_float()
+        self._chk(self.lib.vsv_get_main_kernel_ms(self.h, C.byref(ms)))
+        return ms.value
+
     def timing(self):
         ms, n = C.c_float(), _i64()
         self._chk(self.lib.vsv_get_timing(self.h, C.byref(ms), C.byref(n)))
@@ -188,6 +209,12 @@ class Context:
         self._chk(self.lib.vsv_argsort_stable(self.h, _p(key), len(key), _p(order)))
         return order
 
+    def sort_sigs(self, sigs, tie_mode=0):
+        sigs = np.ascontiguousarray(sigs, dtype=SIG_DTYPE)
+        out = np.empty(len(sigs), SIG_DTYPE)
+        self._chk(self.lib.vsv_sort_sigs(self.h, _p(sigs), len(sigs), tie_mode, _p(out)))
+        return out
+
     def cluster(self, is_del, pos, length):
         pos, length = _arr(pos, np.int32), _arr(length, np.int32)
         keep = np.empty(len(pos), np.int32)
@@ -222,12 +249,12 @@ class Context:
         return out
 
     # ---- stage 3 ---------------------------------------------------------------
-    def group_sigs(self, chrom, pos, length):
+    def group_sigs(self, chrom, pos, length, min_len=0):
         c, p, l = (_arr(x, np.int32) for x in (chrom, pos, length))
-        n = len(c)
+        n = len(p)
         o = [np.empty(n, np.int32) for _ in range(4)]
         nu = _i64()
-        self._chk(self.lib.vsv_group_sigs(self.h, _p(c), _p(p), _p(l), n, _p(o[0]), _p(o[1]), _p(o[2]), _p(o[3]),
+        self._chk(self.lib.vsv_group_sigs(self.h, _p(c), _p(p), _p(l), n, min_len, _p(o[0]), _p(o[1]), _p(o[2]), _p(o[3]),
                                           C.byref(nu)))
         return tuple(x[: nu.value] for x in o)
 

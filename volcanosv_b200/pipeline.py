@@ -1,0 +1,240 @@
+"""Device-resident large-indel hot path for one chromosome shard.
+
+`ChromShard.run()` chains the C-ABI calls of include/volcanosv_b200.h with every
+intermediate staying in HBM (the ctx is in device-IO mode): read scan (ERS), cuteSV-style
+scan + in-read merge (SE), `.sigs` ordering and grouping, FP-filter support, coverage
+support, supporting-signature count, spanning depth and the genotype decision.
+torch is used only for device / pinned allocations and the H2D / D2H copies.
+
+Reference call chain reproduced: LI/Raw_variant_call.py:83-96 (ERS -> FPF) and
+LI/filter_GT_correction.py:111-172 (SE -> CSS -> GTD/GTI).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field
+from typing import Dict, Optional
+
+import numpy as np
+import torch
+
+from . import lib as L
+
+NAN = float("nan")
+# LI/para/GT_correction_para_<dtype>_<type>.txt : t_large_11, t_small_11, t_large_01, t_small_01
+GT_THRESHOLDS = {
+    "Hifi": dict(DEL=[0.6, 0.69, 0.71, 0.91], INS=[NAN, 0.59, 0.63, 0.79]),
+    "ONT": dict(DEL=[0.61, 0.61, 0.68, 0.79], INS=[NAN, NAN, 0.67, 0.72]),
+    "CLR": dict(DEL=[0.55, 0.59, 0.65, 0.75], INS=[NAN, NAN, 0.64, 0.75]),
+}
+
+
+def _dp(t: Optional[torch.Tensor]):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+@dataclass
+class ShardResult:
+    n_rec: int = 0
+    n_ops: int = 0
+    n_read_sigs: int = 0
+    n_cute_sigs: int = 0
+    n_del: int = 0
+    n_ins: int = 0
+    n_udel: int = 0
+    n_uins: int = 0
+    n_cand: int = 0
+    scan_ms: list = field(default_factory=list)      # dominant kernel, per scan call
+    out: Dict[str, torch.Tensor] = field(default_factory=dict)
+
+
+class ChromShard:
+    """Buffers and call chain for one (chromosome, GPU) shard."""
+
+    def __init__(self, device: int = 0, dtype: str = "ONT"):
+        if not torch.cuda.is_available():
+            raise L.VsvError(L.E_CUDA, "no CUDA device: volcanosv_b200 has no CPU path")
+        self.device = torch.device("cuda", device)
+        torch.cuda.set_device(self.device)
+        self.ctx = L.Context(device)
+        self.ctx.set_device_io(True)
+        self.lib = self.ctx.lib
+        self.h = self.ctx.h
+        self.dtype = dtype
+        self.thr_del = (C.c_double * 4)(*GT_THRESHOLDS[dtype]["DEL"])
+        self.thr_ins = (C.c_double * 4)(*GT_THRESHOLDS[dtype]["INS"])
+        self.d: Dict[str, torch.Tensor] = {}
+        self.sig_cap = 0
+        self.h2d_bytes = 0
+        self.d2h_bytes = 0
+
+    # ---- allocation ------------------------------------------------------------------
+    def _buf(self, name, n, dtype):
+        t = self.d.get(name)
+        if t is None or t.numel() < n or t.dtype != dtype:
+            t = torch.empty(max(int(n), 1), dtype=dtype, device=self.device)
+            self.d[name] = t
+        return t
+
+    def upload(self, batch, cands, n_ops: Optional[int] = None):
+        """H2D of one shard's inputs (packed records + candidate table).  Values are numpy
+        arrays or (pinned) torch CPU tensors; `ops` may be uint32 numpy or an int32 tensor."""
+        self.h2d_bytes = 0
+
+        def put(name, src):
+            if isinstance(src, np.ndarray):
+                if src.dtype == np.uint32:
+                    src = src.view(np.int32)
+                src = torch.from_numpy(np.ascontiguousarray(src))
+            dst = self._buf(name, src.numel(), src.dtype)
+            dst[: src.numel()].copy_(src, non_blocking=True)
+            self.h2d_bytes += src.numel() * src.element_size()
+            return src
+
+        for k in ("ops", "op_off", "pos", "mapq", "qlen"):
+            put("in_" + k, batch[k])
+        for k in ("pos", "svlen", "type", "gt"):
+            put("cand_" + k, cands[k])
+        self.n_rec = len(batch["pos"])
+        self.n_ops = int(n_ops) if n_ops is not None else int(batch["op_off"][-1])
+        self.n_cand = len(cands["pos"])
+        torch.cuda.current_stream().synchronize()
+
+    def _chk(self, rc):
+        if rc != 0:
+            raise L.VsvError(rc, (self.lib.vsv_last_error(self.h) or b"").decode())
+
+    # ---- the hot path ----------------------------------------------------------------
+    def run(self) -> ShardResult:
+        lib, h, d = self.lib, self.h, self.d
+        n_rec, n_ops, n_cand = self.n_rec, self.n_ops, self.n_cand
+        res = ShardResult(n_rec=n_rec, n_ops=n_ops, n_cand=n_cand)
+        i32, u8, i64, f64 = torch.int32, torch.uint8, torch.int64, torch.float64
+        ops, op_off, pos, mapq, qlen = (d["in_" + k] for k in ("ops", "op_off", "pos", "mapq", "qlen"))
+        cap = max(self.sig_cap, 1 << 16, n_ops // 64)
+        sig = lambda name: self._buf(name, cap * 8, i32)  # vsv_sig = 8 x int32
+        rt, qt, xt = (self._buf(k, n_rec, i32) for k in ("ref_total", "qry_total", "aux_total"))
+        n_out = C.c_int64()
+
+        def scan(mode, min_len, min_mapq, enable, out, totals):
+            nonlocal cap
+            while True:
+                rc = lib.vsv_scan_cigar(h, mode, min_len, min_mapq, _dp(ops), _dp(op_off), _dp(pos), _dp(mapq),
+                                        _dp(enable), n_rec, _dp(out), cap, C.byref(n_out),
+                                        _dp(rt) if totals else None, _dp(qt) if totals else None,
+                                        _dp(xt) if totals else None)
+                if rc == L.E_CAPACITY:
+                    cap = int(n_out.value * 1.25) + 1024
+                    self.sig_cap = cap
+                    raise _Regrow()
+                self._chk(rc)
+                res.scan_ms.append(self.ctx.main_kernel_ms())
+                return int(n_out.value)
+
+        # -- stage 1a: reads, simple scanner (ERS:107-145), mapq>=50, >=30 bp ------------
+        s_reads = sig("sig_reads")
+        n_r = scan(L.MODE_READS, 30, 50, None, s_reads, True)
+        res.n_read_sigs = n_r
+        # read intervals for the depth join: [pos, pos + ref_total)  (reference_end)
+        rend = self._buf("read_end", n_rec, i32)
+        self._chk(lib.vsv_add_i32(h, _dp(pos), _dp(rt), n_rec, _dp(rend)))
+        s_reads_sorted = sig("sig_reads_sorted")
+        self._chk(lib.vsv_sort_sigs(h, _dp(s_reads), n_r, 0, _dp(s_reads_sorted)))       # merge_all (ERS:254-258)
+        rs_pos, rs_len = self._buf("rs_pos", cap, i32), self._buf("rs_len", cap, i32)
+        self._chk(lib.vsv_sig_columns(h, _dp(s_reads_sorted), n_r, _dp(rs_pos), _dp(rs_len), None))
+
+        # -- stage 1b: reads, cuteSV-style scanner (SE:438-478) + in-read merge (SE:373-435)
+        enable = self._buf("enable", n_rec, u8)
+        self._chk(lib.vsv_ge_u8(h, _dp(qlen), 500, n_rec, _dp(enable)))                 # SE:439
+        s_cute = sig("sig_cute")
+        n_c = scan(L.MODE_CUTE, 10, 20, enable, s_cute, False)
+        res.n_cute_sigs = n_c
+        s_del, s_ins = sig("sig_del"), sig("sig_ins")
+        nd, ni = C.c_int64(), C.c_int64()
+        self._chk(lib.vsv_merge_in_record(h, L.MODE_CUTE, _dp(s_cute), n_c, _dp(s_del), C.byref(nd), _dp(s_ins),
+                                          C.byref(ni)))
+        res.n_del, res.n_ins = int(nd.value), int(ni.value)
+
+        # -- stage 2: `.sigs` order (SE:637-638), unique signatures (GTD:65-86 / GTI:67-101)
+        uniq = {}
+        for name, src, n, min_len in (("del", s_del, res.n_del, 0), ("ins", s_ins, res.n_ins, 30)):
+            srt = sig("sig_%s_sorted" % name)
+            self._chk(lib.vsv_sort_sigs(h, _dp(src), n, 1, _dp(srt)))
+            p_, l_ = self._buf(name + "_pos", cap, i32), self._buf(name + "_len", cap, i32)
+            self._chk(lib.vsv_sig_columns(h, _dp(srt), n, _dp(p_), _dp(l_), None))
+            uc, up, ul, un = (self._buf("%s_u%s" % (name, k), cap, i32) for k in "cpln")
+            nu = C.c_int64()
+            self._chk(lib.vsv_group_sigs(h, None, _dp(p_), _dp(l_), n, min_len, _dp(uc), _dp(up), _dp(ul), _dp(un),
+                                         C.byref(nu)))
+            uniq[name] = (p_, l_, n, up, ul, un, int(nu.value))
+        res.n_udel, res.n_uins = uniq["del"][6], uniq["ins"][6]
+
+        # -- candidate-side joins ------------------------------------------------------
+        cpos, clen, ctyp, cgt = (d["cand_" + k] for k in ("pos", "svlen", "type", "gt"))
+        fp = self._buf("fp_support", n_cand, i32)
+        self._chk(lib.vsv_fp_support(h, _dp(cpos), _dp(clen), n_cand, _dp(rs_pos), _dp(rs_len), n_r, _dp(fp)))  # FPF
+        cend = self._buf("cand_end", n_cand, i32)
+        self._chk(lib.vsv_add_i32(h, _dp(cpos), _dp(clen), n_cand, _dp(cend)))
+        cov_i, cov_d = self._buf("cov_ins", n_cand, i64), self._buf("cov_del", n_cand, i64)
+        p_, l_, n, *_ = uniq["ins"]
+        self._chk(lib.vsv_ins_cov(h, _dp(cpos), n_cand, _dp(p_), _dp(l_), n, 1000, _dp(cov_i)))                 # CSS:81
+        p_, l_, n, *_ = uniq["del"]
+        self._chk(lib.vsv_del_cov(h, _dp(cpos), _dp(cend), n_cand, _dp(p_), _dp(l_), n, 1000, _dp(cov_d)))      # CSS:138
+        sup_d, sup_i = self._buf("sup_del", n_cand, i32), self._buf("sup_ins", n_cand, i32)
+        last = C.c_int32()
+        _, _, _, up, ul, un, nu = uniq["del"]
+        self._chk(lib.vsv_sig_support(h, None, _dp(cpos), _dp(clen), n_cand, None, _dp(up), _dp(ul), _dp(un), nu, 0,
+                                      _dp(sup_d), None, C.byref(last)))                                         # GTD:92
+        _, _, _, up, ul, un, nu = uniq["ins"]
+        self._chk(lib.vsv_sig_support(h, None, _dp(cpos), _dp(clen), n_cand, None, _dp(up), _dp(ul), _dp(un), nu, 0,
+                                      _dp(sup_i), None, C.byref(last)))                                         # GTI:107
+        nsup = self._buf("n_support", n_cand, i32)
+        self._chk(lib.vsv_select_i32(h, _dp(ctyp), L.DEL, _dp(sup_d), _dp(sup_i), n_cand, _dp(nsup)))
+
+        # -- stage 3: spanning depth + genotype (GTD:140-170,291-318; GTI:188-196,258-283)
+        d2, ratio, ngt = self._buf("depth2", n_cand, i32), self._buf("ratio", n_cand, f64), self._buf("new_gt", n_cand, i32)
+        self._chk(lib.vsv_genotype(h, _dp(pos), _dp(rend), n_rec, _dp(cpos), _dp(clen), _dp(ctyp), _dp(cgt),
+                                   _dp(nsup), n_cand, self.thr_del, self.thr_ins, _dp(d2), _dp(ratio), _dp(ngt)))
+        res.out = dict(fp_support=fp[:n_cand], cov_ins=cov_i[:n_cand], cov_del=cov_d[:n_cand], n_support=nsup[:n_cand],
+                       depth2=d2[:n_cand], ratio=ratio[:n_cand], new_gt=ngt[:n_cand],
+                       sig_reads=s_reads_sorted[: n_r * 8], sig_del=self.d["sig_del_sorted"][: res.n_del * 8],
+                       sig_ins=self.d["sig_ins_sorted"][: res.n_ins * 8])
+        return res
+
+    def run_safe(self) -> ShardResult:
+        """run() with one retry if a signature buffer had to grow."""
+        for _ in range(4):
+            try:
+                return self.run()
+            except _Regrow:
+                for k in list(self.d):
+                    if k.startswith(("sig_", "rs_", "del_", "ins_")):
+                        del self.d[k]
+        raise L.VsvError(L.E_CAPACITY, "signature buffers kept growing")
+
+    def sync(self):
+        self.ctx.sync()
+        torch.cuda.current_stream().synchronize()
+
+    def download(self, res: ShardResult, pinned: Optional[Dict[str, torch.Tensor]] = None) -> Dict[str, np.ndarray]:
+        """D2H of the shard's results (per-candidate table + signature arrays)."""
+        self.ctx.sync()
+        out = {}
+        self.d2h_bytes = 0
+        for k, t in res.out.items():
+            if pinned is not None:
+                dst = pinned.get(k)
+                if dst is None or dst.numel() < t.numel():
+                    dst = torch.empty(max(t.numel(), 1), dtype=t.dtype, pin_memory=True)
+                    pinned[k] = dst
+                dst[: t.numel()].copy_(t, non_blocking=True)
+                out[k] = dst[: t.numel()]
+            else:
+                out[k] = t.cpu()
+            self.d2h_bytes += t.numel() * t.element_size()
+        torch.cuda.current_stream().synchronize()
+        return {k: v.numpy() for k, v in out.items()}
+
+
+class _Regrow(Exception):
+    pass
