@@ -265,13 +265,13 @@ def main():
         peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
     else:
         peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
-    n_sig_avg = (res.n_read_sigs + res.n_cute_sigs) / 2.0
-    alg_bytes = 4.0 * n_ops + 24.0 * n_rec + 32.0 * n_sig_avg       # SURVEY.md §8d B1, per launch
+    n_sig_out = res.n_read_sigs + res.n_cute_sigs            # both streams of the fused pass
+    alg_bytes = 4.0 * n_ops + 24.0 * n_rec + 32.0 * n_sig_out       # SURVEY.md §8d B1, per launch
     k_ms = float(np.mean(scan_ms)) if scan_ms else float("nan")
     achieved = alg_bytes / (k_ms * 1e-3) / 1e9
-    roof = dict(bound="hbm", kernel="k_scan_cigar", achieved=achieved, peak=peak, unit="GB/s", frac=achieved / peak,
+    roof = dict(bound="hbm", kernel="k_scan_tiles<FUSED>", achieved=achieved, peak=peak, unit="GB/s", frac=achieved / peak,
                 traffic=None, peak_source=peak_src, alg_bytes_per_launch=alg_bytes, kernel_ms=k_ms,
-                launches_per_step=2, share_of_step=2 * k_ms / ms_per_step)
+                launches_per_step=1, share_of_step=k_ms / ms_per_step)
     line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=args.steps, warmup=max(args.warmup, 3),
                 ms_per_step=ms_per_step, higher_is_better=True, scaling="weak", vs_baseline=None, dtype="int32",
                 data="synthetic",

@@ -97,6 +97,18 @@ int vsv_scan_cigar(vsv_ctx* ctx, int mode, int min_len, int min_mapq, const uint
                    const uint8_t* enable, int64_t n_rec, vsv_sig* out, int64_t cap,
                    int64_t* n_out, int32_t* ref_total, int32_t* qry_total, int32_t* aux_total);
 
+/* The two READ-BAM scanners in ONE pass over the packed ops (the ops are the bulk of the
+ * bytes, so this halves HBM traffic of stage 1): stream "reads" == vsv_scan_cigar(
+ * VSV_MODE_READS, min_len_reads, min_mapq_reads, enable=NULL) (ERS:47-83,107-145) and
+ * stream "cute" == vsv_scan_cigar(VSV_MODE_CUTE, min_len_cute, min_mapq_cute,
+ * enable_cute) (SE:438-478), bit for bit.  Totals follow VSV_MODE_READS. */
+int vsv_scan_reads_fused(vsv_ctx* ctx, int min_len_reads, int min_mapq_reads, int min_len_cute,
+                         int min_mapq_cute, const uint32_t* ops, const int64_t* op_off,
+                         const int32_t* pos, const uint8_t* mapq, const uint8_t* enable_cute,
+                         int64_t n_rec, vsv_sig* out_reads, int64_t cap_reads, int64_t* n_reads,
+                         vsv_sig* out_cute, int64_t cap_cute, int64_t* n_cute, int32_t* ref_total,
+                         int32_t* qry_total, int32_t* aux_total);
+
 /* Replaces cluster_ins_one_read / cluster_del_one_read (ECS_H:87-164) for
  * VSV_MODE_CONTIG and generate_combine_sigs (SE:373-435) for VSV_MODE_CUTE
  * (VSV_MODE_READS: identity split by type).  Input: scan output.  out_del/out_ins

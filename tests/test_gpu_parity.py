@@ -131,3 +131,59 @@ def test_scan_full_size_properties(ctx):
     # idempotence
     sigs2, *_ = ctx.scan_cigar(V.MODE_READS, b["ops"], b["op_off"], b["pos"], b["mapq"], min_len=30, min_mapq=50)
     assert np.array_equal(sigs.view(np.uint8), sigs2.view(np.uint8))
+
+
+def _rand_ops_batch(seed, n_rec, mean_ops, codes, big_rate=0.02):
+    """Random records over an arbitrary op-code alphabet (incl. N, P, H, reserved codes)."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    nops = rng.poisson(mean_ops, n_rec).astype(np.int64)
+    off = np.zeros(n_rec + 1, np.int64)
+    np.cumsum(nops, out=off[1:])
+    tot = int(off[-1])
+    code = rng.choice(np.array(codes, np.uint32), tot)
+    ln = rng.integers(0, 25, tot).astype(np.uint32)
+    big = rng.random(tot) < big_rate
+    ln[big] = rng.integers(25, 4000, int(big.sum()))
+    ops = (ln << 4) | code
+    pos = np.sort(rng.integers(0, 10_000_000, n_rec)).astype(np.int32)
+    mapq = rng.integers(0, 61, n_rec).astype(np.uint8)
+    return ops.astype(np.uint32), off, pos, mapq
+
+
+@pytest.mark.parametrize("n_rec,mean_ops,codes", [
+    (60, 900, list(range(9))),                 # every BAM op incl. N, P, mid-record H
+    (20000, 2, [0, 1, 2, 4, 5, 3]),            # > 128 records per tile: global record-table path
+    (300, 120, list(range(16))),               # reserved codes 9..15
+])
+def test_scan_rare_ops_and_dense_records(ctx, n_rec, mean_ops, codes):
+    ops, off, pos, mapq = _rand_ops_batch(n_rec, n_rec, mean_ops, codes)
+    en = (np.arange(n_rec) % 5 != 1).astype(np.uint8)
+    for mode, minlen, minmq in ((V.MODE_CONTIG, 30, 50), (V.MODE_READS, 30, 50), (V.MODE_CUTE, 10, 20)):
+        sigs, rt, qt, xt = ctx.scan_cigar(mode, ops, off, pos, mapq, enable=en, min_len=minlen, min_mapq=minmq)
+        es, ert, eqt, ext = O.scan_cigar(ops, off, pos, mapq, mode, minlen, minmq, enable=en)
+        assert sig_tuples(sigs) == es and len(es) > 0
+        assert np.array_equal(rt, ert) and np.array_equal(qt, eqt) and np.array_equal(xt, ext)
+        assert (sigs["count"] == 1).all()
+
+
+@pytest.mark.parametrize("case", ["ont", "hifi", "rare", "dense"])
+def test_scan_reads_fused_equals_two_scans(ctx, case):
+    """vsv_scan_reads_fused == (READS scan, CUTE scan), bit for bit, and == the oracle."""
+    if case in ("ont", "hifi"):
+        n = {"ont": 60, "hifi": 600}[case]
+        b = synth.synth_records(21, n, case, eqx=True)
+        ops, off, pos, mapq, qlen = b["ops"], b["op_off"], b["pos"], b["mapq"], b["qlen"]
+    else:
+        n = 20000 if case == "dense" else 80
+        ops, off, pos, mapq = _rand_ops_batch(5, n, 2 if case == "dense" else 700, list(range(9)))
+        qlen = np.random.Generator(np.random.PCG64(1)).integers(0, 1000, n).astype(np.int32)
+    en = (qlen >= 500).astype(np.uint8)
+    r, c, rt, qt, xt = ctx.scan_reads_fused(ops, off, pos, mapq, enable_cute=en, cap=64)
+    er, ert, eqt, ext = O.scan_cigar(ops, off, pos, mapq, V.MODE_READS, 30, 50)
+    ec, *_ = O.scan_cigar(ops, off, pos, mapq, V.MODE_CUTE, 10, 20, enable=en)
+    assert sig_tuples(r) == er and sig_tuples(c) == ec
+    assert len(ec) > 0
+    assert np.array_equal(rt, ert) and np.array_equal(qt, eqt) and np.array_equal(xt, ext)
+    r2, *_ = ctx.scan_cigar(V.MODE_READS, ops, off, pos, mapq, min_len=30, min_mapq=50)
+    c2, *_ = ctx.scan_cigar(V.MODE_CUTE, ops, off, pos, mapq, enable=en, min_len=10, min_mapq=20, totals=False)
+    assert np.array_equal(r.view(np.uint8), r2.view(np.uint8)) and np.array_equal(c.view(np.uint8), c2.view(np.uint8))

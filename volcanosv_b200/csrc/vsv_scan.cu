@@ -1,88 +1,190 @@
-// Stage 1: CIGAR signature scan (K1) and per-record merge (K2).
+// Stage 1: CIGAR signature scan (K1).
 //
 // K1 replaces extract_sig_from_cigar (LI/extract_contig_signature_Hifi.py:53-85,
 // LI/extract_reads_signature.py:47-83) and the CIGAR walk of parse_read
-// (LI/sig_extract.py:438-478).
+// (LI/sig_extract.py:438-478).  VSV_MODE_FUSED runs the two READ scanners (ERS + SE)
+// in ONE pass over the packed ops and fills two output streams.
 //
-// Design (B200-first, HBM-bound): the packed ops of ALL records form one flat u32
-// array that is cut into fixed tiles of 4096 ops, independent of record boundaries,
-// so every load is a coalesced, 16-byte aligned 128-bit access and the work per CTA is
-// identical whether a record has 150 ops (HiFi) or 10^5 (contigs).  Reference/query
-// offsets are prefix sums restarted at record starts: inside a tile they come from a
-// thread-sequential pass over 16 ops + one block scan; across tiles the open record's
-// running sums and the number of signatures emitted so far travel by a single-pass
-// decoupled look-back (chained scan), which also gives every signature its final,
-// deterministic (record, op)-ordered output slot: ordered stream compaction without a
-// second pass over the ops and without unordered atomics.
+// Design v2 (B200-first, HBM/issue-bound streaming kernel, no inter-CTA dependency):
+//  * the packed ops of ALL records are one flat u32 array cut into fixed tiles of 4096
+//    ops, independent of record boundaries; a persistent CTA per SM slot walks tiles
+//    round-robin and pulls each 16 KB tile into shared memory with ONE 1-D TMA bulk copy
+//    (cp.async.bulk + mbarrier), double buffered, so loads of tile i+1 overlap the work on
+//    tile i and no thread spends instructions on staging;
+//  * fast path: every thread folds 16 consecutive ops (bank-conflict-free rotated
+//    LDS.128) into two running sums (reference / query advance) plus a 16-bit candidate
+//    mask; rare op codes (N, P, H, ...) are summed in a slow path only by warps that saw
+//    one;
+//  * candidates (D/I >= min_len: well under 1 % of the ops) are pushed to a per-warp
+//    shared-memory list and finished densely by warp 0: record lookup in a prefetched
+//    per-tile record table, mapq/enable gate, exact offsets from the block prefix, ordered
+//    write to a STAGING buffer whose slots are reserved per CTA in chunks (one global
+//    atomic per ~256 signatures);
+//  * every tile publishes a 32-byte aggregate (sums since the last record start inside
+//    the tile, signature counts).  A segmented exclusive scan over the tile aggregates
+//    (n_ops/4096 elements) and a warp-per-tile fix-up kernel then move the staged
+//    signatures to their final, deterministic (record, op)-ordered slot and add the carry
+//    of a record that began in an earlier tile.  The ops are read from HBM exactly once.
+//
+// v1 (single-pass chained look-back) is described in profiles/r01a_scan_v1.md: it was
+// bound by the tile chain at 7 % of HBM.
+#include <cub/device/device_scan.cuh>
+
 #include "vsv_common.cuh"
 
 #define SCAN_THREADS 256
+#define SCAN_WARPS (SCAN_THREADS / 32)
 #define SCAN_VPT 16
 #define SCAN_TILE (SCAN_THREADS * SCAN_VPT)
-#define SCAN_ROW 20  // 16 ops + 4 pad words per thread row: conflict-free LDS.128
-#define SCAN_SMEM_WORDS (SCAN_THREADS * SCAN_ROW)
+#define SCAN_STAGES 2
+#define SCAN_RT 128           // records per tile kept in the shared-memory record table
+#define SCAN_WCAND 512        // per-warp candidate list capacity (= ops per warp)
+#define SCAN_CHUNK 256        // staging slots reserved per global atomic
+#define SCAN_CTAS_PER_SM 4
 
-#define ST_AGG 1u
-#define ST_INCL 2u
-#define ST_BOUND 4u
+#define VSV_MODE_FUSED 3      // internal: READS (stream A) + CUTE (stream B) in one pass
+
+#define BIT(c) (1u << (c))
 
 template <int MODE>
 struct ModeTraits;
-// contig: only M,S,D,I are walked (ECS_H:72-85); aux = H
+// contig: only M,S,D,I are walked (ECS_H:72-85); H is needed for readlen
 template <>
 struct ModeTraits<VSV_MODE_CONTIG> {
-  static constexpr uint32_t REF = (1u << 0) | (1u << 2);
-  static constexpr uint32_t QRY = (1u << 0) | (1u << 1) | (1u << 4);
-  static constexpr uint32_t AUX = (1u << 5);
-  static constexpr int HSIGN = 1;
+  static constexpr uint32_t REF = BIT(0) | BIT(2);
+  static constexpr uint32_t QRY = BIT(0) | BIT(1) | BIT(4);
+  static constexpr uint32_t X1 = BIT(5), X2 = 0, X3 = 0;
+  static constexpr int NX = 1;
 };
-// reads: M,=,X both; S,I query; D,N reference (ERS:66-81); aux = H
+// reads: M,=,X both; S,I query; D,N reference (ERS:66-81)
 template <>
 struct ModeTraits<VSV_MODE_READS> {
-  static constexpr uint32_t REF = (1u << 0) | (1u << 7) | (1u << 8) | (1u << 2) | (1u << 3);
-  static constexpr uint32_t QRY = (1u << 0) | (1u << 7) | (1u << 8) | (1u << 4) | (1u << 1);
-  static constexpr uint32_t AUX = (1u << 5);
-  static constexpr int HSIGN = 1;
+  static constexpr uint32_t REF = BIT(0) | BIT(7) | BIT(8) | BIT(2) | BIT(3);
+  static constexpr uint32_t QRY = BIT(0) | BIT(7) | BIT(8) | BIT(4) | BIT(1);
+  static constexpr uint32_t X1 = BIT(5), X2 = 0, X3 = 0;
+  static constexpr int NX = 1;
 };
 // cute: shift_del == shift_ins == sum{M,D,=,X}; shift_ins_read = every op but D
-// (SE:461-478); N moves neither reference counter (quirk) -> aux = N
+// (SE:461-478); N moves neither reference counter (quirk).  x1 = N, x2 = other non-D ops.
 template <>
 struct ModeTraits<VSV_MODE_CUTE> {
-  static constexpr uint32_t REF = (1u << 0) | (1u << 2) | (1u << 7) | (1u << 8);
-  static constexpr uint32_t QRY = 0xFFFFu & ~(1u << 2);
-  static constexpr uint32_t AUX = (1u << 3);
-  static constexpr int HSIGN = -1;
+  static constexpr uint32_t REF = BIT(0) | BIT(2) | BIT(7) | BIT(8);
+  static constexpr uint32_t QRY = BIT(0) | BIT(7) | BIT(8) | BIT(1) | BIT(4);
+  static constexpr uint32_t X1 = BIT(3), X2 = 0xFFFFu & ~(REF | QRY | BIT(3)), X3 = 0;
+  static constexpr int NX = 2;
+};
+// fused READS + CUTE: r = {M,D,=,X}, q = {M,=,X,I,S}, x1 = N, x2 = H, x3 = P and codes 9..15
+template <>
+struct ModeTraits<VSV_MODE_FUSED> {
+  static constexpr uint32_t REF = BIT(0) | BIT(2) | BIT(7) | BIT(8);
+  static constexpr uint32_t QRY = BIT(0) | BIT(7) | BIT(8) | BIT(1) | BIT(4);
+  static constexpr uint32_t X1 = BIT(3), X2 = BIT(5), X3 = 0xFFFFu & ~(REF | QRY | BIT(3) | BIT(5));
+  static constexpr int NX = 3;
+};
+
+struct Sums {
+  uint32_t r, q, x1, x2, x3;
+};
+__device__ __forceinline__ Sums operator-(const Sums& a, const Sums& b) {
+  return Sums{a.r - b.r, a.q - b.q, a.x1 - b.x1, a.x2 - b.x2, a.x3 - b.x3};
+}
+
+// Per (mode, stream): the reference scanner's reference offset, query offset, the sign
+// of the leading hard clip in q0 and the per-record totals (ref, qry, aux).
+template <int MODE, int STREAM>
+__device__ __forceinline__ uint32_t ref_of(const Sums& s) {
+  if (MODE == VSV_MODE_FUSED && STREAM == 0) return s.r + s.x1;  // READS counts N on the reference
+  return s.r;
+}
+template <int MODE, int STREAM>
+__device__ __forceinline__ uint32_t qry_of(const Sums& s) {
+  if (MODE == VSV_MODE_CUTE) return s.q + s.x1 + s.x2;
+  if (MODE == VSV_MODE_FUSED && STREAM == 1) return s.q + s.x1 + s.x2 + s.x3;
+  return s.q;
+}
+template <int MODE, int STREAM>
+__device__ __forceinline__ int hsign() {
+  return (MODE == VSV_MODE_CUTE || (MODE == VSV_MODE_FUSED && STREAM == 1)) ? -1 : 1;
+}
+template <int MODE>
+__device__ __forceinline__ uint32_t aux_of(const Sums& s) {  // CONTIG/READS/FUSED: H; CUTE: N
+  if (MODE == VSV_MODE_FUSED) return s.x2;
+  return s.x1;
+}
+
+// One tile's aggregate / scanned state (32 bytes).
+struct __align__(16) TileState {
+  uint32_t r, q, x1, x2, x3;  // sums since the last record start (or since the segment start)
+  uint32_t cnt_a, cnt_b;      // signatures of stream A / B
+  uint32_t flag;              // a record starts inside (aggregate) / before here (scanned)
+};
+struct TileStateOp {
+  __host__ __device__ TileState operator()(const TileState& a, const TileState& b) const {
+    TileState o;
+    o.cnt_a = a.cnt_a + b.cnt_a;
+    o.cnt_b = a.cnt_b + b.cnt_b;
+    if (b.flag) {
+      o.r = b.r; o.q = b.q; o.x1 = b.x1; o.x2 = b.x2; o.x3 = b.x3; o.flag = 1u;
+    } else {
+      o.r = a.r + b.r; o.q = a.q + b.q; o.x1 = a.x1 + b.x1; o.x2 = a.x2 + b.x2; o.x3 = a.x3 + b.x3;
+      o.flag = a.flag;
+    }
+    return o;
+  }
 };
 
 struct ScanParams {
   const uint32_t* ops;
   const int64_t* op_off;
   const int32_t* pos;
-  const uint8_t* mapq;
-  const uint8_t* enable;
+  const uint32_t* rec_info;  // hc << 2 | gate_b << 1 | gate_a
   int64_t n_rec, n_ops;
   int32_t n_tiles;
-  int min_len, min_mapq;
-  // tile descriptors
-  const int32_t* tile_rfirst;
-  const int32_t* tile_rlast;
-  uint32_t* status;
-  uint4* agg;
-  uint4* incl;
-  uint32_t* ticket;
-  // outputs
-  vsv_sig* out;
-  int64_t cap;
-  int64_t* n_out;
+  uint32_t min_w;            // min candidate length << 4
+  int32_t min_len_a, min_len_b;
+  const int2* tile_rec;      // first / last record touching each tile
+  TileState* tile_agg;       // per tile aggregate (kernel output)
+  uint2* tile_stage;         // staging base of the tile's signatures per stream
+  unsigned long long* stage_ctr;  // [2] staging allocation counters
+  vsv_sig* stage_a;
+  vsv_sig* stage_b;
+  uint32_t stage_cap_a, stage_cap_b;
   uint32_t* ref_total;
   uint32_t* qry_total;
   uint32_t* aux_total;
 };
 
-// last record r with op_off[r] <= x  (op_off[0]=0, op_off[n_rec]=n_ops > x)
-__device__ __forceinline__ int32_t rec_of_op(const int64_t* __restrict__ op_off, int32_t lo, int32_t hi,
-                                             int64_t x) {
-  // invariant: op_off[lo] <= x, answer in [lo, hi]
+// ---- PTX wrappers: mbarrier + 1-D TMA bulk copy (sm_90+/sm_100a) ------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_1d(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst_smem)),
+      "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+      : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// last record r in [lo,hi] with op_off[r] <= x  (op_off[lo] <= x assumed)
+__device__ __forceinline__ int32_t rec_of_op(const int64_t* __restrict__ op_off, int32_t lo, int32_t hi, int64_t x) {
   while (lo < hi) {
     int32_t mid = (lo + hi + 1) >> 1;
     if (__ldg(op_off + mid) <= x) lo = mid; else hi = mid - 1;
@@ -90,515 +192,649 @@ __device__ __forceinline__ int32_t rec_of_op(const int64_t* __restrict__ op_off,
   return lo;
 }
 
-__global__ void k_tile_records(const int64_t* __restrict__ op_off, int64_t n_rec, int64_t n_ops,
-                               int32_t n_tiles, int32_t* __restrict__ rfirst, int32_t* __restrict__ rlast) {
+__global__ void k_tile_records(const int64_t* __restrict__ op_off, int64_t n_rec, int64_t n_ops, int32_t n_tiles,
+                               int2* __restrict__ tile_rec) {
   int32_t t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= n_tiles) return;
   int64_t x0 = (int64_t)t * SCAN_TILE;
   int64_t x1 = min(x0 + SCAN_TILE, n_ops) - 1;
   int32_t a = rec_of_op(op_off, 0, (int32_t)n_rec - 1, x0);
-  rfirst[t] = a;
-  rlast[t] = rec_of_op(op_off, a, (int32_t)n_rec - 1, x1);
+  tile_rec[t] = make_int2(a, rec_of_op(op_off, a, (int32_t)n_rec - 1, x1));
 }
 
+// per record: leading hard clip and the record gates of both streams
+__global__ void k_rec_info(const uint32_t* __restrict__ ops, const int64_t* __restrict__ op_off,
+                           const uint8_t* __restrict__ mapq, const uint8_t* __restrict__ enable_a,
+                           const uint8_t* __restrict__ enable_b, int64_t n_rec, int min_mapq_a, int min_mapq_b,
+                           uint32_t* __restrict__ info) {
+  int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= n_rec) return;
+  const int64_t a = op_off[r], b = op_off[r + 1];
+  uint32_t hc = 0;
+  if (b > a) {
+    const uint32_t f = __ldg(ops + a);
+    if ((f & 15u) == 5u) hc = f >> 4;
+  }
+  const int mq = mapq[r];
+  const uint32_t ga = (mq >= min_mapq_a && (enable_a == nullptr || enable_a[r] != 0)) ? 1u : 0u;
+  const uint32_t gb = (mq >= min_mapq_b && (enable_b == nullptr || enable_b[r] != 0)) ? 2u : 0u;
+  info[r] = (hc << 2) | gb | ga;
+}
+
+// ---- shared memory of the streaming kernel -------------------------------------------
+struct ScanSmem {
+  uint32_t ops[SCAN_STAGES][SCAN_TILE];   // TMA destinations (linear tiles)
+  uint32_t tx[5][SCAN_THREADS];           // warp-relative thread-exclusive prefixes (r,q,x1,x2,x3)
+  uint16_t cand[SCAN_WARPS][SCAN_WCAND];  // per-warp candidate op indices, in op order
+  int32_t t_off[2][SCAN_RT + 4];          // record table: op_off - tile_start, clamped to [-1, TILE+1]
+  int32_t t_pos[2][SCAN_RT];
+  uint32_t t_info[2][SCAN_RT];
+  uint32_t w[6][SCAN_WARPS];              // warp totals (r,q,x1,x2,x3,cand)
+  uint32_t wx[6][SCAN_WARPS];             // warp exclusive offsets
+  uint32_t tot[6];
+  uint32_t wrare[SCAN_WARPS];
+  uint64_t bar[SCAN_STAGES];
+};
+
 template <int MODE>
-__device__ __forceinline__ void op_contrib(uint32_t w, uint32_t& r, uint32_t& q, uint32_t& x) {
+__device__ __forceinline__ void add_op(uint32_t w, Sums& s) {
   typedef ModeTraits<MODE> M;
-  uint32_t code = w & 15u, len = w >> 4;
-  r += ((M::REF >> code) & 1u) ? len : 0u;
-  q += ((M::QRY >> code) & 1u) ? len : 0u;
-  x += ((M::AUX >> code) & 1u) ? len : 0u;
+  const uint32_t bit = 1u << (w & 15u), len = w >> 4;
+  s.r += (bit & M::REF) ? len : 0u;
+  s.q += (bit & M::QRY) ? len : 0u;
+  s.x1 += (bit & M::X1) ? len : 0u;
+  if (M::NX > 1) s.x2 += (bit & M::X2) ? len : 0u;
+  if (M::NX > 2) s.x3 += (bit & M::X3) ? len : 0u;
 }
 
-// prefix of (ref,qry,aux) over tile ops [0, j)
+// View of the records touching one tile: shared-memory table when it fits, else global.
+struct RecTab {
+  const ScanSmem* sm;
+  const ScanParams* p;
+  int64_t tile_start;
+  int32_t rf, nrt, slot;
+  bool fast;
+  __device__ __forceinline__ int32_t off(int k) const {  // start of record rf+k relative to the tile
+    if (fast) return sm->t_off[slot][k];
+    const int64_t d = __ldg(p->op_off + rf + k) - tile_start;
+    return (int32_t)max((int64_t)-1, min(d, (int64_t)SCAN_TILE + 1));
+  }
+  __device__ __forceinline__ int32_t pos(int k) const { return fast ? sm->t_pos[slot][k] : __ldg(p->pos + rf + k); }
+  __device__ __forceinline__ uint32_t info(int k) const {
+    return fast ? sm->t_info[slot][k] : __ldg(p->rec_info + rf + k);
+  }
+  __device__ __forceinline__ int lookup(int j) const {  // last k with off(k) <= j
+    int lo = 0, hi = nrt - 1;
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (off(mid) <= j) lo = mid; else hi = mid - 1;
+    }
+    return lo;
+  }
+};
+
+// sums over tile ops [0, j)
 template <int MODE>
-__device__ __forceinline__ void prefix_at(const uint32_t* s_ops, const uint32_t (*s_tx)[SCAN_THREADS],
-                                          const uint32_t* s_tot, int j, uint32_t& r, uint32_t& q,
-                                          uint32_t& x) {
+__device__ __forceinline__ Sums prefix_at(const ScanSmem& sm, const uint32_t* tile, int j) {
+  Sums s;
   if (j >= SCAN_TILE) {
-    r = s_tot[0]; q = s_tot[1]; x = s_tot[2];
-    return;
+    s.r = sm.tot[0]; s.q = sm.tot[1]; s.x1 = sm.tot[2]; s.x2 = sm.tot[3]; s.x3 = sm.tot[4];
+    return s;
   }
-  int t = j >> 4, n = j & 15;
-  r = s_tx[0][t]; q = s_tx[1][t]; x = s_tx[2][t];
-  const uint32_t* row = s_ops + t * SCAN_ROW;
-  for (int s = 0; s < n; ++s) op_contrib<MODE>(row[s], r, q, x);
+  const int t = j >> 4, n = j & 15, wp = t >> 5;
+  s.r = sm.wx[0][wp] + sm.tx[0][t];
+  s.q = sm.wx[1][wp] + sm.tx[1][t];
+  s.x1 = sm.wx[2][wp]; s.x2 = sm.wx[3][wp]; s.x3 = sm.wx[4][wp];
+  if (sm.wrare[wp]) { s.x1 += sm.tx[2][t]; s.x2 += sm.tx[3][t]; s.x3 += sm.tx[4][t]; }
+  const uint32_t* row = tile + t * SCAN_VPT;
+  for (int i = 0; i < n; ++i) add_op<MODE>(row[i], s);
+  return s;
 }
 
+template <int MODE, int STREAM>
+__device__ __forceinline__ void write_sig(vsv_sig* dst, int32_t rec, uint32_t w, int32_t rpos, uint32_t hc,
+                                          const Sums& part, bool carry) {
+  const int32_t len = (int32_t)(w >> 4);
+  const int32_t type = ((w & 15u) == 1u) ? VSV_INS : VSV_DEL;
+  const int32_t q0 = (int32_t)qry_of<MODE, STREAM>(part) + hsign<MODE, STREAM>() * (int32_t)hc;
+  int4* o = reinterpret_cast<int4*>(dst);
+  o[0] = make_int4(rec, type, rpos + (int32_t)ref_of<MODE, STREAM>(part), len);
+  o[1] = make_int4(q0, q0 + (type == VSV_INS ? len : 1), 0, carry ? 0 : 1);  // count==0: carry pending
+}
+
+// ---- K1: the streaming kernel ---------------------------------------------------------
 template <int MODE>
-__device__ __noinline__ void emit_sig(const ScanParams& p, const uint32_t* s_ops,
-                                      const uint32_t (*s_tx)[SCAN_THREADS], const uint32_t* s_tot,
-                                      int64_t tile_start, int32_t rfirst, int32_t rlast, int j,
-                                      uint32_t pr, uint32_t pq, uint32_t w, uint32_t carry_r,
-                                      uint32_t carry_q, int64_t out_idx) {
+__global__ void __launch_bounds__(SCAN_THREADS, SCAN_CTAS_PER_SM) k_scan_tiles(const ScanParams p) {
   typedef ModeTraits<MODE> M;
-  if (out_idx >= p.cap) return;
-  int32_t r = rec_of_op(p.op_off, rfirst, rlast, tile_start + j);
-  int64_t off_r = __ldg(p.op_off + r);
-  uint32_t ro, qo;
-  if (off_r < tile_start) {
-    ro = carry_r + pr;
-    qo = carry_q + pq;
-  } else {
-    uint32_t br, bq, bx;
-    prefix_at<MODE>(s_ops, s_tx, s_tot, (int)(off_r - tile_start), br, bq, bx);
-    ro = pr - br;
-    qo = pq - bq;
+  constexpr uint32_t RARE = M::X1 | M::X2 | M::X3;
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  ScanSmem& sm = *reinterpret_cast<ScanSmem*>(smem_raw);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int G = gridDim.x;
+  const int32_t n_tiles = p.n_tiles;
+  const int32_t n_full = (int32_t)(p.n_ops / SCAN_TILE);  // tiles below n_full are complete
+
+  if (tid == 0) {
+    for (int s = 0; s < SCAN_STAGES; ++s) mbar_init(&sm.bar[s], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    fence_proxy_async();
   }
-  uint32_t f = __ldg(p.ops + off_r);
-  int32_t hc = ((f & 15u) == 5u) ? (int32_t)(f >> 4) : 0;
-  int32_t len = (int32_t)(w >> 4);
-  int32_t type = ((w & 15u) == 1u) ? VSV_INS : VSV_DEL;
-  int32_t q0 = (int32_t)qo + M::HSIGN * hc;
-  int4 a = make_int4(r, type, __ldg(p.pos + r) + (int32_t)ro, len);
-  int4 b = make_int4(q0, q0 + (type == VSV_INS ? len : 1), 0, 1);
-  int4* o = reinterpret_cast<int4*>(p.out + out_idx);
-  o[0] = a;
-  o[1] = b;
+  __syncthreads();
+  if (tid == 0) {
+    for (int s = 0; s < SCAN_STAGES; ++s) {
+      const int64_t t = (int64_t)blockIdx.x + (int64_t)s * G;
+      if (t < n_full) {
+        mbar_expect_tx(&sm.bar[s], SCAN_TILE * 4);
+        tma_load_1d(sm.ops[s], p.ops + t * SCAN_TILE, SCAN_TILE * 4, &sm.bar[s]);
+      }
+    }
+  }
+  // record-table registers: desc of the current / next tile, prefetched one iteration ahead
+  int2 cur = make_int2(0, -1), nxt = make_int2(0, -1);
+  if ((int32_t)blockIdx.x < n_tiles) cur = __ldg(p.tile_rec + blockIdx.x);
+  if ((int64_t)blockIdx.x + G < n_tiles) nxt = __ldg(p.tile_rec + blockIdx.x + G);
+  {  // first tile's table, synchronously
+    const int nrt = cur.y - cur.x + 1;
+    if (nrt <= SCAN_RT && tid <= nrt) {
+      const int64_t d = __ldg(p.op_off + cur.x + tid) - (int64_t)blockIdx.x * SCAN_TILE;
+      sm.t_off[0][tid] = (int32_t)max((int64_t)-1, min(d, (int64_t)SCAN_TILE + 1));
+      if (tid < nrt) { sm.t_pos[0][tid] = __ldg(p.pos + cur.x + tid); sm.t_info[0][tid] = __ldg(p.rec_info + cur.x + tid); }
+    }
+  }
+  __syncthreads();
+
+  // staging chunks of this CTA (live in warp 0 / lane 0 registers)
+  unsigned long long ch_next[2] = {0, 0}, ch_end[2] = {0, 0};
+
+  int it = 0;
+  for (int64_t tile64 = blockIdx.x; tile64 < n_tiles; tile64 += G, ++it) {
+    const int32_t tile = (int32_t)tile64;
+    const int stage = it % SCAN_STAGES, slot = it & 1;
+    const uint32_t parity = (uint32_t)(it / SCAN_STAGES) & 1u;
+    const int64_t tile_start = (int64_t)tile * SCAN_TILE;
+    uint32_t* tl = sm.ops[stage];
+
+    // -- prefetch the next tile's record table into registers (stored at the bottom) ----
+    const int nrt_next = nxt.y - nxt.x + 1;
+    int32_t pf_off = 0, pf_pos = 0;
+    uint32_t pf_info = 0;
+    const bool pf_on = (tile64 + G < n_tiles) && nrt_next <= SCAN_RT && tid <= nrt_next;
+    if (pf_on) {
+      const int64_t d = __ldg(p.op_off + nxt.x + tid) - (tile_start + (int64_t)G * SCAN_TILE);
+      pf_off = (int32_t)max((int64_t)-1, min(d, (int64_t)SCAN_TILE + 1));
+      if (tid < nrt_next) { pf_pos = __ldg(p.pos + nxt.x + tid); pf_info = __ldg(p.rec_info + nxt.x + tid); }
+    }
+    int2 nn = make_int2(0, -1);
+    if (tile64 + 2 * (int64_t)G < n_tiles) nn = __ldg(p.tile_rec + tile64 + 2 * (int64_t)G);
+
+    // -- the tile's ops: TMA (full tiles) or a guarded copy (the one partial tile) ------
+    if (tile < n_full) {
+      mbar_wait(&sm.bar[stage], parity);
+    } else {
+      const int64_t rem = p.n_ops - tile_start;
+      for (int i = tid; i < SCAN_TILE; i += SCAN_THREADS) tl[i] = (i < rem) ? __ldg(p.ops + tile_start + i) : 0u;
+      __syncthreads();
+    }
+
+    // -- fast path: 16 consecutive ops per thread, rotated so LDS.128 is conflict free ---
+    uint32_t r = 0, q = 0, bits = 0, em = 0;
+    {
+      const int rot = (tid >> 1) & 3;
+      const uint4* row = reinterpret_cast<const uint4*>(tl + tid * SCAN_VPT);
+      const uint32_t min_w = p.min_w;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const uint4 v = row[(k + rot) & 3];
+        const uint32_t ww[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const uint32_t w = ww[i];
+          const uint32_t bit = 1u << (w & 15u), len = w >> 4;
+          bits |= bit;
+          r += (bit & M::REF) ? len : 0u;
+          q += (bit & M::QRY) ? len : 0u;
+          em |= ((bit & 6u) && w >= min_w) ? (1u << (k * 4 + i)) : 0u;
+        }
+      }
+      // un-rotate the candidate mask: chunk k of the loop is logical chunk (k+rot)&3
+      em = ((em << (4 * rot)) | (em >> (16 - 4 * rot))) & 0xFFFFu;
+    }
+    const uint32_t c = __popc(em);
+
+    // -- warp scans (inclusive); warp-relative exclusive prefixes go to shared memory ----
+    uint32_t ir = r, iq = q, ic = c;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t a = __shfl_up_sync(0xffffffffu, ir, d);
+      const uint32_t b = __shfl_up_sync(0xffffffffu, iq, d);
+      const uint32_t e = __shfl_up_sync(0xffffffffu, ic, d);
+      if (lane >= d) { ir += a; iq += b; ic += e; }
+    }
+    sm.tx[0][tid] = ir - r;
+    sm.tx[1][tid] = iq - q;
+    const bool anyrare = __any_sync(0xffffffffu, (bits & RARE) != 0u);
+    uint32_t ix1 = 0, ix2 = 0, ix3 = 0;
+    if (anyrare) {  // slow path: this warp saw N / H / P / ...
+      Sums xs = {0, 0, 0, 0, 0};
+      if (bits & RARE)
+        for (int i = 0; i < SCAN_VPT; ++i) add_op<MODE>(tl[tid * SCAN_VPT + i], xs);
+      ix1 = xs.x1; ix2 = xs.x2; ix3 = xs.x3;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t a = __shfl_up_sync(0xffffffffu, ix1, d);
+        const uint32_t b = __shfl_up_sync(0xffffffffu, ix2, d);
+        const uint32_t e = __shfl_up_sync(0xffffffffu, ix3, d);
+        if (lane >= d) { ix1 += a; ix2 += b; ix3 += e; }
+      }
+      sm.tx[2][tid] = ix1 - xs.x1; sm.tx[3][tid] = ix2 - xs.x2; sm.tx[4][tid] = ix3 - xs.x3;
+    }
+    if (lane == 31) {
+      sm.w[0][warp] = ir; sm.w[1][warp] = iq; sm.w[2][warp] = ix1; sm.w[3][warp] = ix2; sm.w[4][warp] = ix3;
+      sm.w[5][warp] = ic;
+      sm.wrare[warp] = anyrare ? 1u : 0u;
+    }
+    if (em) {  // push this thread's candidates, op order, warp-relative slot
+      uint32_t idx = ic - c, m = em;
+      while (m) {
+        const int s = __ffs(m) - 1;
+        m &= m - 1;
+        sm.cand[warp][idx++] = (uint16_t)(tid * SCAN_VPT + s);
+      }
+    }
+    __syncthreads();  // B1: warp totals, candidate lists, tx visible
+
+    if (warp == 0) {  // second level: exclusive offsets of the 8 warps
+      uint32_t v[6], own[6];
+#pragma unroll
+      for (int k = 0; k < 6; ++k) { own[k] = lane < SCAN_WARPS ? sm.w[k][lane] : 0u; v[k] = own[k]; }
+#pragma unroll
+      for (int d = 1; d < SCAN_WARPS; d <<= 1) {
+#pragma unroll
+        for (int k = 0; k < 6; ++k) {
+          const uint32_t a = __shfl_up_sync(0xffffffffu, v[k], d);
+          if (lane >= d) v[k] += a;
+        }
+      }
+      if (lane < SCAN_WARPS) {
+#pragma unroll
+        for (int k = 0; k < 6; ++k) sm.wx[k][lane] = v[k] - own[k];
+      }
+      if (lane == SCAN_WARPS - 1) {
+#pragma unroll
+        for (int k = 0; k < 6; ++k) sm.tot[k] = v[k];
+      }
+    }
+    __syncthreads();  // B2: block prefixes complete
+
+    RecTab rt;
+    rt.sm = &sm; rt.p = &p; rt.tile_start = tile_start; rt.rf = cur.x; rt.nrt = cur.y - cur.x + 1; rt.slot = slot;
+    rt.fast = rt.nrt <= SCAN_RT;
+
+    if (warp == 0) {
+      // -- dense candidate phase: gate, count, reserve staging, ordered write ------------
+      const uint32_t ncand = sm.tot[5];
+      uint32_t cnt_a = 0, cnt_b = 0;
+      unsigned long long base_a = 0, base_b = 0;
+      for (int pass = 0; pass < 2; ++pass) {
+        uint32_t run_a = 0, run_b = 0;
+        for (uint32_t g0 = 0; g0 < ncand; g0 += 32) {
+          const uint32_t i = g0 + lane;
+          bool ok_a = false, ok_b = false;
+          int j = 0, k = 0;
+          uint32_t w = 0, info = 0;
+          if (i < ncand) {
+            int wp = 0;
+#pragma unroll
+            for (int u = 1; u < SCAN_WARPS; ++u) wp += (sm.wx[5][u] <= i) ? 1 : 0;
+            j = sm.cand[wp][i - sm.wx[5][wp]];
+            w = tl[j];
+            k = rt.lookup(j);
+            info = rt.info(k);
+            const int32_t len = (int32_t)(w >> 4);
+            ok_a = (info & 1u) && len >= p.min_len_a;
+            if (MODE == VSV_MODE_FUSED) ok_b = (info & 2u) && len >= p.min_len_b;
+          }
+          const uint32_t ba = __ballot_sync(0xffffffffu, ok_a);
+          const uint32_t bb = __ballot_sync(0xffffffffu, ok_b);
+          if (pass == 0) {
+            cnt_a += __popc(ba);
+            cnt_b += __popc(bb);
+          } else {
+            if (ok_a || ok_b) {
+              const Sums pre = prefix_at<MODE>(sm, tl, j);
+              const int32_t o = rt.off(k);
+              const bool carry = o < 0;
+              const Sums part = carry ? pre : pre - prefix_at<MODE>(sm, tl, o);
+              const uint32_t lt = (1u << lane) - 1u;
+              if (ok_a && base_a != ~0ull)
+                write_sig<MODE, 0>(p.stage_a + base_a + run_a + __popc(ba & lt), rt.rf + k, w, rt.pos(k), info >> 2,
+                                   part, carry);
+              if (MODE == VSV_MODE_FUSED && ok_b && base_b != ~0ull)
+                write_sig<MODE, 1>(p.stage_b + base_b + run_b + __popc(bb & lt), rt.rf + k, w, rt.pos(k), info >> 2,
+                                   part, carry);
+            }
+            run_a += __popc(ba);
+            run_b += __popc(bb);
+          }
+        }
+        if (pass == 0) {
+          if (cnt_a == 0 && cnt_b == 0) break;
+          if (lane == 0) {  // reserve contiguous staging slots (chunked: few global atomics)
+            const uint32_t cn[2] = {cnt_a, cnt_b};
+            unsigned long long bs[2] = {0, 0};
+#pragma unroll
+            for (int s = 0; s < 2; ++s) {
+              if (cn[s] == 0) continue;
+              if (ch_next[s] + cn[s] > ch_end[s]) {
+                const unsigned long long n = cn[s] > SCAN_CHUNK ? cn[s] : SCAN_CHUNK;
+                ch_next[s] = atomicAdd(p.stage_ctr + s, n);
+                ch_end[s] = ch_next[s] + n;
+              }
+              bs[s] = ch_next[s];
+              ch_next[s] += cn[s];
+              if (bs[s] + cn[s] > (s == 0 ? p.stage_cap_a : p.stage_cap_b)) bs[s] = ~0ull;  // staging full
+            }
+            base_a = bs[0]; base_b = bs[1];
+          }
+          base_a = __shfl_sync(0xffffffffu, base_a, 0);
+          base_b = __shfl_sync(0xffffffffu, base_b, 0);
+        }
+      }
+      if (lane == 0) {  // tile aggregate: sums since the last record start inside the tile
+        Sums a = {sm.tot[0], sm.tot[1], sm.tot[2], sm.tot[3], sm.tot[4]};
+        const int32_t o = rt.off(rt.nrt - 1);
+        const bool bound = o >= 0;
+        if (bound) a = a - prefix_at<MODE>(sm, tl, o);
+        TileState ts;
+        ts.r = a.r; ts.q = a.q; ts.x1 = a.x1; ts.x2 = a.x2; ts.x3 = a.x3;
+        ts.cnt_a = cnt_a; ts.cnt_b = cnt_b; ts.flag = bound ? 1u : 0u;
+        p.tile_agg[tile] = ts;
+        p.tile_stage[tile] = make_uint2(base_a == ~0ull ? 0xFFFFFFFFu : (uint32_t)base_a,
+                                        base_b == ~0ull ? 0xFFFFFFFFu : (uint32_t)base_b);
+      }
+    } else if (p.ref_total != nullptr) {
+      // -- warps 1..7: per-record totals of the records touching this tile ---------------
+      for (int k = tid - 32; k < rt.nrt; k += SCAN_THREADS - 32) {
+        const int32_t a = rt.off(k), b = rt.off(k + 1);
+        const Sums d = prefix_at<MODE>(sm, tl, min(b, SCAN_TILE)) - prefix_at<MODE>(sm, tl, max(a, 0));
+        Sums rd = d;  // per-record totals follow stream A's semantics
+        const uint32_t tr = ref_of<MODE, 0>(rd), tq = qry_of<MODE, 0>(rd), tx = aux_of<MODE>(rd);
+        const int64_t rr = (int64_t)rt.rf + k;
+        if (a >= 0 && b <= SCAN_TILE) {
+          p.ref_total[rr] = tr; p.qry_total[rr] = tq; p.aux_total[rr] = tx;
+        } else {
+          atomicAdd(p.ref_total + rr, tr); atomicAdd(p.qry_total + rr, tq); atomicAdd(p.aux_total + rr, tx);
+        }
+      }
+    }
+    // -- store the prefetched record table of the next tile -------------------------------
+    if (pf_on) {
+      sm.t_off[slot ^ 1][tid] = pf_off;
+      if (tid < nrt_next) { sm.t_pos[slot ^ 1][tid] = pf_pos; sm.t_info[slot ^ 1][tid] = pf_info; }
+    }
+    __syncthreads();  // B3: everyone is done with this stage and this table slot
+    if (tid == 0) {
+      const int64_t t2 = tile64 + (int64_t)SCAN_STAGES * G;
+      if (t2 < n_full) {
+        fence_proxy_async();
+        mbar_expect_tx(&sm.bar[stage], SCAN_TILE * 4);
+        tma_load_1d(sm.ops[stage], p.ops + t2 * SCAN_TILE, SCAN_TILE * 4, &sm.bar[stage]);
+      }
+    }
+    cur = nxt;
+    nxt = nn;
+  }
+}
+
+// ---- fix-up: staged signatures -> final ordered slots (+ carry of an open record) -----
+template <int MODE, int STREAM>
+__device__ __forceinline__ void fix_stream(const vsv_sig* __restrict__ stage, uint32_t base, uint32_t cnt,
+                                           uint64_t dst0, const Sums& carry, vsv_sig* __restrict__ out, int64_t cap,
+                                           int lane) {
+  if (base == 0xFFFFFFFFu) return;  // staging overflowed: the call reports VSV_E_CAPACITY
+  const int32_t cr = (int32_t)ref_of<MODE, STREAM>(carry), cq = (int32_t)qry_of<MODE, STREAM>(carry);
+  for (uint32_t i = lane; i < cnt; i += 32) {
+    if ((int64_t)(dst0 + i) >= cap) break;
+    const int4* s = reinterpret_cast<const int4*>(stage + base + i);
+    int4 a = s[0], b = s[1];
+    if (b.w == 0) { a.z += cr; b.x += cq; b.y += cq; b.w = 1; }
+    int4* o = reinterpret_cast<int4*>(out + dst0 + i);
+    o[0] = a;
+    o[1] = b;
+  }
 }
 
 template <int MODE>
-__global__ void __launch_bounds__(SCAN_THREADS) k_scan_cigar(const ScanParams p) {
-  __shared__ __align__(16) uint32_t s_ops[SCAN_SMEM_WORDS];
-  __shared__ uint32_t s_tx[3][SCAN_THREADS];
-  __shared__ uint32_t s_w[4][SCAN_THREADS / 32];
-  __shared__ uint32_t s_tot[4];
-  __shared__ uint32_t s_b[4];  // tile, carry_ref, carry_qry, cnt_in
-
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  if (tid == 0) s_b[0] = atomicAdd(p.ticket, 1u);
-  __syncthreads();
-  const int32_t tile = (int32_t)s_b[0];
-  const int64_t tile_start = (int64_t)tile * SCAN_TILE;
-  const int64_t remaining = p.n_ops - tile_start;
-
-  // ---- stage the tile in shared memory (coalesced 128-bit loads, L1 bypass) -------
-  {
-    const uint4* g = reinterpret_cast<const uint4*>(p.ops + tile_start);
-#pragma unroll
-    for (int k = 0; k < SCAN_VPT / 4; ++k) {
-      int i4 = k * SCAN_THREADS + tid;
-      int i = i4 * 4;
-      uint4 v;
-      if (i + 4 <= remaining) {
-        v = ld_cg_u4(g + i4);
-      } else {
-        const uint32_t* gs = p.ops + tile_start;
-        v.x = (i + 0 < remaining) ? gs[i + 0] : 0u;
-        v.y = (i + 1 < remaining) ? gs[i + 1] : 0u;
-        v.z = (i + 2 < remaining) ? gs[i + 2] : 0u;
-        v.w = (i + 3 < remaining) ? gs[i + 3] : 0u;
-      }
-      *reinterpret_cast<uint4*>(s_ops + i + ((i >> 4) << 2)) = v;
-    }
+__global__ void __launch_bounds__(256) k_scan_fixup(const TileState* __restrict__ agg, const TileState* __restrict__ excl,
+                                                   const uint2* __restrict__ tile_stage, int32_t n_tiles,
+                                                   const vsv_sig* __restrict__ stage_a, const vsv_sig* __restrict__ stage_b,
+                                                   vsv_sig* __restrict__ out_a, int64_t cap_a, vsv_sig* __restrict__ out_b,
+                                                   int64_t cap_b, int64_t* __restrict__ n_out) {
+  const int lane = threadIdx.x & 31;
+  const int64_t t = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (t >= n_tiles) return;
+  const TileState a = agg[t], e = excl[t];
+  if (t == n_tiles - 1 && lane == 0) {
+    n_out[0] = (int64_t)e.cnt_a + a.cnt_a;
+    n_out[1] = (int64_t)e.cnt_b + a.cnt_b;
   }
-  const int32_t rfirst = __ldg(p.tile_rfirst + tile);
-  const int32_t rlast = __ldg(p.tile_rlast + tile);
-  __syncthreads();
-
-  // ---- pass 1: 16 consecutive ops per thread -------------------------------------
-  uint32_t w[SCAN_VPT];
-  {
-    const uint4* row = reinterpret_cast<const uint4*>(s_ops + tid * SCAN_ROW);
-#pragma unroll
-    for (int k = 0; k < SCAN_VPT / 4; ++k) {
-      uint4 v = row[k];
-      w[4 * k + 0] = v.x; w[4 * k + 1] = v.y; w[4 * k + 2] = v.z; w[4 * k + 3] = v.w;
-    }
-  }
-  uint32_t sr = 0, sq = 0, sx = 0, emask = 0;
-  const uint32_t min_w = (uint32_t)p.min_len << 4;
-#pragma unroll
-  for (int s = 0; s < SCAN_VPT; ++s) {
-    op_contrib<MODE>(w[s], sr, sq, sx);
-    bool cand = (((w[s] & 15u) - 1u) < 2u) && (w[s] >= min_w);
-    emask |= cand ? (1u << s) : 0u;
-  }
-  if (emask) {  // rare: apply the record gate (mapq / enable) now so counts are final
-    uint32_t m = emask;
-    while (m) {
-      int s = __ffs(m) - 1;
-      m &= m - 1;
-      int32_t r = rec_of_op(p.op_off, rfirst, rlast, tile_start + tid * SCAN_VPT + s);
-      bool ok = (int)__ldg(p.mapq + r) >= p.min_mapq && (p.enable == nullptr || __ldg(p.enable + r) != 0);
-      if (!ok) emask &= ~(1u << s);
-    }
-  }
-  uint32_t cnt = __popc(emask);
-
-  // ---- block exclusive scan of (ref, qry, aux, cnt) -------------------------------
-  uint32_t ir = sr, iq = sq, ix = sx, ic = cnt;
-#pragma unroll
-  for (int d = 1; d < 32; d <<= 1) {
-    uint32_t a = __shfl_up_sync(0xffffffffu, ir, d);
-    uint32_t b = __shfl_up_sync(0xffffffffu, iq, d);
-    uint32_t c = __shfl_up_sync(0xffffffffu, ix, d);
-    uint32_t e = __shfl_up_sync(0xffffffffu, ic, d);
-    if (lane >= d) { ir += a; iq += b; ix += c; ic += e; }
-  }
-  if (lane == 31) { s_w[0][warp] = ir; s_w[1][warp] = iq; s_w[2][warp] = ix; s_w[3][warp] = ic; }
-  __syncthreads();
-  uint32_t wr = 0, wq = 0, wx = 0, wc = 0, tr = 0, tq = 0, tx = 0, tc = 0;
-#pragma unroll
-  for (int k = 0; k < SCAN_THREADS / 32; ++k) {
-    uint32_t a = s_w[0][k], b = s_w[1][k], c = s_w[2][k], e = s_w[3][k];
-    if (k < warp) { wr += a; wq += b; wx += c; wc += e; }
-    tr += a; tq += b; tx += c; tc += e;
-  }
-  const uint32_t er = wr + ir - sr, eq = wq + iq - sq, ex = wx + ix - sx;  // thread exclusive
-  const uint32_t ec = wc + ic - cnt;
-  s_tx[0][tid] = er; s_tx[1][tid] = eq; s_tx[2][tid] = ex;
-  if (tid == 0) { s_tot[0] = tr; s_tot[1] = tq; s_tot[2] = tx; s_tot[3] = tc; }
-  __syncthreads();
-
-  // ---- warp 0: publish the tile aggregate, then decoupled look-back ----------------
-  if (warp == 0) {
-    const int64_t last_start = __ldg(p.op_off + rlast);
-    const bool bound = last_start >= tile_start;  // a record starts inside this tile
-    uint32_t lr = tr, lq = tq;
-    if (bound) {
-      uint32_t br, bq, bx;
-      prefix_at<MODE>(s_ops, s_tx, s_tot, (int)(last_start - tile_start), br, bq, bx);
-      lr = tr - br;
-      lq = tq - bq;
-    }
-    const uint32_t fl = bound ? ST_BOUND : 0u;
-    uint32_t cr = 0, cq = 0, cc = 0;
-    if (tile == 0) {
-      if (lane == 0) {
-        p.incl[0] = make_uint4(lr, lq, tc, fl);
-        st_release_u32(p.status, ST_INCL | fl);
-      }
-    } else {
-      if (lane == 0) {
-        p.agg[tile] = make_uint4(lr, lq, tc, fl);
-        st_release_u32(p.status + tile, ST_AGG | fl);
-      }
-      bool ref_open = true;
-      int32_t pred = tile - 1 - lane;
-      while (true) {
-        uint32_t st = ST_INCL | ST_BOUND;
-        uint4 v = make_uint4(0, 0, 0, 0);
-        if (pred >= 0) {
-          do { st = ld_acquire_u32(p.status + pred); } while (st == 0u);
-          v = ld_cg_u4((st & ST_INCL) ? (p.incl + pred) : (p.agg + pred));
-        }
-        const bool is_incl = (st & ST_INCL) != 0u;
-        const bool closes = is_incl || (st & ST_BOUND) != 0u;
-        const uint32_t incl_mask = __ballot_sync(0xffffffffu, is_incl);
-        const uint32_t close_mask = __ballot_sync(0xffffffffu, closes);
-        const int first_incl = incl_mask ? (__ffs(incl_mask) - 1) : 32;
-        const int first_close = close_mask ? (__ffs(close_mask) - 1) : 32;
-        uint32_t ac = (lane <= first_incl) ? v.z : 0u;
-        const bool take = ref_open && lane <= first_close;
-        uint32_t ar = take ? v.x : 0u, aq = take ? v.y : 0u;
-#pragma unroll
-        for (int d = 16; d >= 1; d >>= 1) {
-          ac += __shfl_xor_sync(0xffffffffu, ac, d);
-          ar += __shfl_xor_sync(0xffffffffu, ar, d);
-          aq += __shfl_xor_sync(0xffffffffu, aq, d);
-        }
-        cc += ac; cr += ar; cq += aq;
-        if (first_close < 32) ref_open = false;
-        if (first_incl < 32) break;
-        pred -= 32;
-      }
-      if (lane == 0) {
-        p.incl[tile] = make_uint4(bound ? lr : cr + tr, bound ? lq : cq + tq, cc + tc, fl);
-        st_release_u32(p.status + tile, ST_INCL | fl);
-      }
-    }
-    if (lane == 0) {
-      s_b[1] = cr; s_b[2] = cq; s_b[3] = cc;
-      if (tile == p.n_tiles - 1) *p.n_out = (int64_t)cc + tc;
-    }
-  } else if (p.ref_total != nullptr) {
-    // ---- warps 1..7: per-record totals of the records that touch this tile ---------
-    const int64_t tile_end = tile_start + SCAN_TILE;
-    for (int32_t r = rfirst + (tid - 32); r <= rlast; r += SCAN_THREADS - 32) {
-      int64_t a = __ldg(p.op_off + r), b = __ldg(p.op_off + r + 1);
-      int j0 = (int)(max(a, tile_start) - tile_start);
-      int j1 = (int)(min(b, tile_end) - tile_start);
-      uint32_t r0, q0, x0, r1, q1, x1;
-      prefix_at<MODE>(s_ops, s_tx, s_tot, j0, r0, q0, x0);
-      prefix_at<MODE>(s_ops, s_tx, s_tot, j1, r1, q1, x1);
-      if (a >= tile_start && b <= tile_end) {
-        p.ref_total[r] = r1 - r0; p.qry_total[r] = q1 - q0; p.aux_total[r] = x1 - x0;
-      } else {
-        atomicAdd(p.ref_total + r, r1 - r0);
-        atomicAdd(p.qry_total + r, q1 - q0);
-        atomicAdd(p.aux_total + r, x1 - x0);
-      }
-    }
-  }
-  __syncthreads();
-
-  // ---- pass 2: ordered emission ----------------------------------------------------
-  if (emask) {
-    const uint32_t carry_r = s_b[1], carry_q = s_b[2];
-    int64_t out_idx = (int64_t)s_b[3] + ec;
-    uint32_t pr = er, pq = eq, px = 0;
-#pragma unroll
-    for (int s = 0; s < SCAN_VPT; ++s) {
-      if ((emask >> s) & 1u) {
-        emit_sig<MODE>(p, s_ops, s_tx, s_tot, tile_start, rfirst, rlast, tid * SCAN_VPT + s, pr, pq, w[s],
-                       carry_r, carry_q, out_idx);
-        ++out_idx;
-      }
-      op_contrib<MODE>(w[s], pr, pq, px);
-    }
-  }
+  if (a.cnt_a == 0 && a.cnt_b == 0) return;
+  const uint2 st = tile_stage[t];
+  const Sums carry = {e.r, e.q, e.x1, e.x2, e.x3};
+  if (a.cnt_a) fix_stream<MODE, 0>(stage_a, st.x, a.cnt_a, e.cnt_a, carry, out_a, cap_a, lane);
+  if (MODE == VSV_MODE_FUSED && a.cnt_b) fix_stream<MODE, 1>(stage_b, st.y, a.cnt_b, e.cnt_b, carry, out_b, cap_b, lane);
 }
 
-// --------------------------------------------------------------------------------
+// ---- host side ---------------------------------------------------------------------------
+struct ScanCall {
+  int mode;
+  int min_len_a, min_mapq_a, min_len_b, min_mapq_b;
+  const uint32_t* ops; const int64_t* op_off; const int32_t* pos; const uint8_t* mapq;
+  const uint8_t* enable_a; const uint8_t* enable_b;
+  int64_t n_rec;
+  vsv_sig* out_a; int64_t cap_a; int64_t* n_a;
+  vsv_sig* out_b; int64_t cap_b; int64_t* n_b;
+  int32_t *ref_total, *qry_total, *aux_total;
+};
+
+template <int MODE>
+static int launch_scan(vsv_ctx* ctx, const ScanParams& p, int grid) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    VSV_CUDA(ctx, cudaFuncSetAttribute(k_scan_tiles<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)sizeof(ScanSmem)));
+    attr_set = true;
+  }
+  VSV_LAUNCH(ctx, k_scan_tiles<MODE>, (unsigned)grid, SCAN_THREADS, sizeof(ScanSmem), p);
+  return VSV_OK;
+}
+
+static int scan_impl(vsv_ctx* ctx, const ScanCall& c) {
+  const char* fn = c.mode == VSV_MODE_FUSED ? "vsv_scan_reads_fused" : "vsv_scan_cigar";
+  const bool fused = c.mode == VSV_MODE_FUSED;
+  if (c.n_rec < 0 || c.cap_a < 0 || !c.n_a || (fused && (c.cap_b < 0 || !c.n_b)) ||
+      (c.n_rec > 0 && (!c.op_off || !c.pos || !c.mapq)))
+    VSV_FAIL(ctx, VSV_E_ARG, std::string(fn) + ": bad argument");
+  if (c.min_len_a < 0 || c.min_len_a >= (1 << 27) || c.min_len_b < 0 || c.min_len_b >= (1 << 27))
+    VSV_FAIL(ctx, VSV_E_ARG, std::string(fn) + ": min_len out of range");
+  if (c.n_rec >= (int64_t(1) << 31)) VSV_FAIL(ctx, VSV_E_ARG, std::string(fn) + ": more than 2^31-1 records per call");
+  if (c.cap_a >= (int64_t(1) << 30) || c.cap_b >= (int64_t(1) << 30))
+    VSV_FAIL(ctx, VSV_E_ARG, std::string(fn) + ": capacity must be below 2^30 signatures per call");
+  const bool want_tot = c.ref_total || c.qry_total || c.aux_total;
+  if (want_tot && !(c.ref_total && c.qry_total && c.aux_total))
+    VSV_FAIL(ctx, VSV_E_ARG, std::string(fn) + ": pass all three totals or none");
+  *c.n_a = 0;
+  if (fused) *c.n_b = 0;
+  if (c.n_rec == 0) return VSV_OK;
+
+  // number of ops = op_off[n_rec] (host knows it in host-IO mode; fetch it in device-IO mode)
+  int64_t n_ops = 0;
+  if (ctx->device_io) {
+    VSV_CUDA(ctx, cudaMemcpyAsync(&n_ops, c.op_off + c.n_rec, sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
+    VSV_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  } else {
+    n_ops = c.op_off[c.n_rec];
+  }
+  if (n_ops < 0) VSV_FAIL(ctx, VSV_E_ARG, std::string(fn) + ": negative op count");
+  const int64_t n_tiles64 = vsv_cdiv(n_ops, SCAN_TILE);
+  if (n_tiles64 >= (int64_t(1) << 31)) VSV_FAIL(ctx, VSV_E_ARG, std::string(fn) + ": too many ops per call");
+  const int32_t n_tiles = (int32_t)n_tiles64;
+
+  ScanParams p;
+  memset(&p, 0, sizeof(p));
+  const uint8_t *d_mapq = nullptr, *d_ena = nullptr, *d_enb = nullptr;
+  VSV_TRY(vsv_in(ctx, c.ops, (size_t)n_ops, &p.ops));
+  VSV_TRY(vsv_in(ctx, c.op_off, (size_t)c.n_rec + 1, &p.op_off));
+  VSV_TRY(vsv_in(ctx, c.pos, (size_t)c.n_rec, &p.pos));
+  VSV_TRY(vsv_in(ctx, c.mapq, (size_t)c.n_rec, &d_mapq));
+  VSV_TRY(vsv_in(ctx, c.enable_a, (size_t)c.n_rec, &d_ena));
+  VSV_TRY(vsv_in(ctx, c.enable_b, (size_t)c.n_rec, &d_enb));
+  if (n_ops > 0 && (reinterpret_cast<uintptr_t>(p.ops) & 15u))
+    VSV_FAIL(ctx, VSV_E_ARG, std::string(fn) + ": ops must be 16-byte aligned");
+  vsv_sig *d_out_a = nullptr, *d_out_b = nullptr;
+  VSV_TRY(vsv_out(ctx, c.out_a, (size_t)c.cap_a, &d_out_a));
+  if (fused) VSV_TRY(vsv_out(ctx, c.out_b, (size_t)c.cap_b, &d_out_b));
+  if ((c.cap_a > 0 && (reinterpret_cast<uintptr_t>(d_out_a) & 15u)) ||
+      (fused && c.cap_b > 0 && (reinterpret_cast<uintptr_t>(d_out_b) & 15u)))
+    VSV_FAIL(ctx, VSV_E_ARG, std::string(fn) + ": out must be 16-byte aligned");
+  int32_t *d_rt = nullptr, *d_qt = nullptr, *d_xt = nullptr;
+  if (want_tot) {
+    VSV_TRY(vsv_out(ctx, c.ref_total, (size_t)c.n_rec, &d_rt));
+    VSV_TRY(vsv_out(ctx, c.qry_total, (size_t)c.n_rec, &d_qt));
+    VSV_TRY(vsv_out(ctx, c.aux_total, (size_t)c.n_rec, &d_xt));
+  }
+  const int grid = (int)std::min<int64_t>(n_tiles, (int64_t)ctx->sm_count * SCAN_CTAS_PER_SM);
+  // staging: chunked reservation wastes < 1x the used slots plus one chunk per CTA
+  const int64_t scap_a = 2 * c.cap_a + (int64_t)grid * SCAN_CHUNK + SCAN_CHUNK;
+  const int64_t scap_b = fused ? 2 * c.cap_b + (int64_t)grid * SCAN_CHUNK + SCAN_CHUNK : 0;
+  int64_t* d_nout = nullptr;
+  uint32_t* d_info = nullptr;
+  int2* d_trec = nullptr;
+  TileState *d_agg = nullptr, *d_excl = nullptr;
+  uint2* d_tstage = nullptr;
+  unsigned long long* d_ctr = nullptr;
+  vsv_sig *d_sa = nullptr, *d_sb = nullptr;
+  VSV_TRY(vsv_tmp(ctx, 2, &d_nout));
+  VSV_TRY(vsv_tmp(ctx, (size_t)c.n_rec, &d_info));
+  VSV_TRY(vsv_tmp(ctx, (size_t)n_tiles, &d_trec));
+  VSV_TRY(vsv_tmp(ctx, (size_t)n_tiles, &d_agg));
+  VSV_TRY(vsv_tmp(ctx, (size_t)n_tiles, &d_excl));
+  VSV_TRY(vsv_tmp(ctx, (size_t)n_tiles, &d_tstage));
+  VSV_TRY(vsv_tmp(ctx, 2, &d_ctr));
+  VSV_TRY(vsv_tmp(ctx, (size_t)scap_a, &d_sa));
+  if (fused) VSV_TRY(vsv_tmp(ctx, (size_t)scap_b, &d_sb));
+
+  p.rec_info = d_info;
+  p.n_rec = c.n_rec; p.n_ops = n_ops; p.n_tiles = n_tiles;
+  p.min_len_a = c.min_len_a; p.min_len_b = c.min_len_b;
+  p.min_w = (uint32_t)(fused ? std::min(c.min_len_a, c.min_len_b) : c.min_len_a) << 4;
+  p.tile_rec = d_trec; p.tile_agg = d_agg; p.tile_stage = d_tstage; p.stage_ctr = d_ctr;
+  p.stage_a = d_sa; p.stage_b = d_sb;
+  p.stage_cap_a = (uint32_t)scap_a; p.stage_cap_b = (uint32_t)scap_b;
+  p.ref_total = (uint32_t*)d_rt; p.qry_total = (uint32_t*)d_qt; p.aux_total = (uint32_t*)d_xt;
+
+  VSV_TRY(vsv_t0(ctx));
+  VSV_CUDA(ctx, cudaMemsetAsync(d_nout, 0, 2 * sizeof(int64_t), ctx->stream));
+  VSV_CUDA(ctx, cudaMemsetAsync(d_ctr, 0, 2 * sizeof(unsigned long long), ctx->stream));
+  if (want_tot) {
+    VSV_CUDA(ctx, cudaMemsetAsync(d_rt, 0, sizeof(int32_t) * (size_t)c.n_rec, ctx->stream));
+    VSV_CUDA(ctx, cudaMemsetAsync(d_qt, 0, sizeof(int32_t) * (size_t)c.n_rec, ctx->stream));
+    VSV_CUDA(ctx, cudaMemsetAsync(d_xt, 0, sizeof(int32_t) * (size_t)c.n_rec, ctx->stream));
+  }
+  if (n_tiles > 0) {
+    VSV_LAUNCH(ctx, k_rec_info, (unsigned)vsv_cdiv(c.n_rec, 256), 256, 0, p.ops, p.op_off, d_mapq, d_ena, d_enb, c.n_rec,
+               c.min_mapq_a, c.min_mapq_b, d_info);
+    VSV_LAUNCH(ctx, k_tile_records, (unsigned)vsv_cdiv(n_tiles, 256), 256, 0, p.op_off, c.n_rec, n_ops, n_tiles, d_trec);
+    VSV_CUDA(ctx, cudaEventRecord(ctx->evk0, ctx->stream));
+    switch (c.mode) {
+      case VSV_MODE_CONTIG: VSV_TRY(launch_scan<VSV_MODE_CONTIG>(ctx, p, grid)); break;
+      case VSV_MODE_READS: VSV_TRY(launch_scan<VSV_MODE_READS>(ctx, p, grid)); break;
+      case VSV_MODE_CUTE: VSV_TRY(launch_scan<VSV_MODE_CUTE>(ctx, p, grid)); break;
+      default: VSV_TRY(launch_scan<VSV_MODE_FUSED>(ctx, p, grid)); break;
+    }
+    VSV_CUDA(ctx, cudaEventRecord(ctx->evk1, ctx->stream));
+    ctx->main_open = true;
+    {  // segmented exclusive scan of the tile aggregates
+      TileState init;
+      memset(&init, 0, sizeof(init));
+      size_t tb = 0;
+      VSV_CUDA(ctx, cub::DeviceScan::ExclusiveScan(nullptr, tb, d_agg, d_excl, TileStateOp(), init, n_tiles, ctx->stream));
+      void* tmp = nullptr;
+      VSV_TRY(vsv_arena_alloc(ctx, tb, &tmp));
+      VSV_CUDA(ctx, cub::DeviceScan::ExclusiveScan(tmp, tb, d_agg, d_excl, TileStateOp(), init, n_tiles, ctx->stream));
+      ctx->launches += 2;
+    }
+    const unsigned gf = (unsigned)vsv_cdiv((int64_t)n_tiles * 32, 256);
+    switch (c.mode) {
+      case VSV_MODE_CONTIG:
+        VSV_LAUNCH(ctx, k_scan_fixup<VSV_MODE_CONTIG>, gf, 256, 0, d_agg, d_excl, d_tstage, n_tiles, d_sa, d_sb, d_out_a,
+                   c.cap_a, d_out_b, c.cap_b, d_nout);
+        break;
+      case VSV_MODE_READS:
+        VSV_LAUNCH(ctx, k_scan_fixup<VSV_MODE_READS>, gf, 256, 0, d_agg, d_excl, d_tstage, n_tiles, d_sa, d_sb, d_out_a,
+                   c.cap_a, d_out_b, c.cap_b, d_nout);
+        break;
+      case VSV_MODE_CUTE:
+        VSV_LAUNCH(ctx, k_scan_fixup<VSV_MODE_CUTE>, gf, 256, 0, d_agg, d_excl, d_tstage, n_tiles, d_sa, d_sb, d_out_a,
+                   c.cap_a, d_out_b, c.cap_b, d_nout);
+        break;
+      default:
+        VSV_LAUNCH(ctx, k_scan_fixup<VSV_MODE_FUSED>, gf, 256, 0, d_agg, d_excl, d_tstage, n_tiles, d_sa, d_sb, d_out_a,
+                   c.cap_a, d_out_b, c.cap_b, d_nout);
+        break;
+    }
+  }
+  VSV_TRY(vsv_t1(ctx));
+  // the counts are needed on the host to size the copy-out: one small sync
+  int64_t h_n[2] = {0, 0};
+  VSV_CUDA(ctx, cudaMemcpyAsync(h_n, d_nout, 2 * sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
+  VSV_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  *c.n_a = h_n[0];
+  if (fused) *c.n_b = h_n[1];
+  if (want_tot) {
+    VSV_TRY(vsv_out_done(ctx, c.ref_total, d_rt, (size_t)c.n_rec));
+    VSV_TRY(vsv_out_done(ctx, c.qry_total, d_qt, (size_t)c.n_rec));
+    VSV_TRY(vsv_out_done(ctx, c.aux_total, d_xt, (size_t)c.n_rec));
+  }
+  if (h_n[0] > c.cap_a || (fused && h_n[1] > c.cap_b)) {
+    vsv_end(ctx, true);
+    VSV_FAIL(ctx, VSV_E_CAPACITY, std::string(fn) + ": output capacity too small");
+  }
+  VSV_TRY(vsv_out_done(ctx, c.out_a, d_out_a, (size_t)h_n[0]));
+  if (fused) VSV_TRY(vsv_out_done(ctx, c.out_b, d_out_b, (size_t)h_n[1]));
+  return vsv_end(ctx);
+}
+
 extern "C" int vsv_scan_cigar(vsv_ctx* ctx, int mode, int min_len, int min_mapq, const uint32_t* ops,
                               const int64_t* op_off, const int32_t* pos, const uint8_t* mapq,
                               const uint8_t* enable, int64_t n_rec, vsv_sig* out, int64_t cap,
                               int64_t* n_out, int32_t* ref_total, int32_t* qry_total,
                               int32_t* aux_total) {
   VSV_TRY(vsv_begin(ctx));
-  if (mode < 0 || mode > 2 || n_rec < 0 || cap < 0 || !n_out || (n_rec > 0 && (!op_off || !pos || !mapq)))
-    VSV_FAIL(ctx, VSV_E_ARG, "vsv_scan_cigar: bad argument");
-  if (min_len < 0 || min_len >= (1 << 27)) VSV_FAIL(ctx, VSV_E_ARG, "vsv_scan_cigar: min_len out of range");
-  if (n_rec >= (int64_t(1) << 31)) VSV_FAIL(ctx, VSV_E_ARG, "vsv_scan_cigar: more than 2^31-1 records per call");
-  const bool want_tot = ref_total || qry_total || aux_total;
-  if (want_tot && !(ref_total && qry_total && aux_total))
-    VSV_FAIL(ctx, VSV_E_ARG, "vsv_scan_cigar: pass all three totals or none");
-  *n_out = 0;
-  if (n_rec == 0) return VSV_OK;
-
-  // number of ops = op_off[n_rec] (host knows it in host-IO mode; fetch it in device-IO mode)
-  int64_t n_ops = 0;
-  if (ctx->device_io) {
-    VSV_CUDA(ctx, cudaMemcpyAsync(&n_ops, op_off + n_rec, sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
-    VSV_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-  } else {
-    n_ops = op_off[n_rec];
-  }
-  if (n_ops < 0) VSV_FAIL(ctx, VSV_E_ARG, "vsv_scan_cigar: negative op count");
-  const int64_t n_tiles64 = vsv_cdiv(n_ops, SCAN_TILE);
-  if (n_tiles64 >= (int64_t(1) << 31)) VSV_FAIL(ctx, VSV_E_ARG, "vsv_scan_cigar: too many ops per call");
-  const int32_t n_tiles = (int32_t)n_tiles64;
-
-  ScanParams p;
-  memset(&p, 0, sizeof(p));
-  VSV_TRY(vsv_in(ctx, ops, (size_t)n_ops, &p.ops));
-  VSV_TRY(vsv_in(ctx, op_off, (size_t)n_rec + 1, &p.op_off));
-  VSV_TRY(vsv_in(ctx, pos, (size_t)n_rec, &p.pos));
-  VSV_TRY(vsv_in(ctx, mapq, (size_t)n_rec, &p.mapq));
-  VSV_TRY(vsv_in(ctx, enable, (size_t)n_rec, &p.enable));
-  if (n_ops > 0 && (reinterpret_cast<uintptr_t>(p.ops) & 15u))
-    VSV_FAIL(ctx, VSV_E_ARG, "vsv_scan_cigar: ops must be 16-byte aligned");
-  vsv_sig* d_out = nullptr;
-  VSV_TRY(vsv_out(ctx, out, (size_t)cap, &d_out));
-  if (cap > 0 && (reinterpret_cast<uintptr_t>(d_out) & 15u))
-    VSV_FAIL(ctx, VSV_E_ARG, "vsv_scan_cigar: out must be 16-byte aligned");
-  int32_t *d_rt = nullptr, *d_qt = nullptr, *d_xt = nullptr;
-  if (want_tot) {
-    VSV_TRY(vsv_out(ctx, ref_total, (size_t)n_rec, &d_rt));
-    VSV_TRY(vsv_out(ctx, qry_total, (size_t)n_rec, &d_qt));
-    VSV_TRY(vsv_out(ctx, aux_total, (size_t)n_rec, &d_xt));
-  }
-  int64_t* d_nout = nullptr;
-  VSV_TRY(vsv_tmp(ctx, 1, &d_nout));
-  int32_t *d_rf = nullptr, *d_rl = nullptr;
-  uint32_t *d_status = nullptr, *d_ticket = nullptr;
-  uint4 *d_agg = nullptr, *d_incl = nullptr;
-  VSV_TRY(vsv_tmp(ctx, (size_t)n_tiles, &d_rf));
-  VSV_TRY(vsv_tmp(ctx, (size_t)n_tiles, &d_rl));
-  VSV_TRY(vsv_tmp(ctx, (size_t)n_tiles + 1, &d_status));  // [n_tiles] = ticket
-  VSV_TRY(vsv_tmp(ctx, (size_t)n_tiles, &d_agg));
-  VSV_TRY(vsv_tmp(ctx, (size_t)n_tiles, &d_incl));
-  d_ticket = d_status + n_tiles;
-
-  p.n_rec = n_rec; p.n_ops = n_ops; p.n_tiles = n_tiles;
-  p.min_len = min_len; p.min_mapq = min_mapq;
-  p.tile_rfirst = d_rf; p.tile_rlast = d_rl;
-  p.status = d_status; p.agg = d_agg; p.incl = d_incl; p.ticket = d_ticket;
-  p.out = d_out; p.cap = cap; p.n_out = d_nout;
-  p.ref_total = (uint32_t*)d_rt; p.qry_total = (uint32_t*)d_qt; p.aux_total = (uint32_t*)d_xt;
-
-  VSV_TRY(vsv_t0(ctx));
-  VSV_CUDA(ctx, cudaMemsetAsync(d_nout, 0, sizeof(int64_t), ctx->stream));
-  if (n_tiles > 0) {
-    VSV_CUDA(ctx, cudaMemsetAsync(d_status, 0, sizeof(uint32_t) * ((size_t)n_tiles + 1), ctx->stream));
-    if (want_tot) {
-      VSV_CUDA(ctx, cudaMemsetAsync(d_rt, 0, sizeof(int32_t) * (size_t)n_rec, ctx->stream));
-      VSV_CUDA(ctx, cudaMemsetAsync(d_qt, 0, sizeof(int32_t) * (size_t)n_rec, ctx->stream));
-      VSV_CUDA(ctx, cudaMemsetAsync(d_xt, 0, sizeof(int32_t) * (size_t)n_rec, ctx->stream));
-    }
-    VSV_LAUNCH(ctx, k_tile_records, (unsigned)vsv_cdiv(n_tiles, 256), 256, 0, p.op_off, n_rec, n_ops, n_tiles, d_rf,
-               d_rl);
-    VSV_CUDA(ctx, cudaEventRecord(ctx->evk0, ctx->stream));
-    switch (mode) {
-      case VSV_MODE_CONTIG: VSV_LAUNCH(ctx, k_scan_cigar<VSV_MODE_CONTIG>, (unsigned)n_tiles, SCAN_THREADS, 0, p); break;
-      case VSV_MODE_READS: VSV_LAUNCH(ctx, k_scan_cigar<VSV_MODE_READS>, (unsigned)n_tiles, SCAN_THREADS, 0, p); break;
-      default: VSV_LAUNCH(ctx, k_scan_cigar<VSV_MODE_CUTE>, (unsigned)n_tiles, SCAN_THREADS, 0, p); break;
-    }
-    VSV_CUDA(ctx, cudaEventRecord(ctx->evk1, ctx->stream));
-    ctx->main_open = true;
-  } else if (want_tot) {
-    VSV_CUDA(ctx, cudaMemsetAsync(d_rt, 0, sizeof(int32_t) * (size_t)n_rec, ctx->stream));
-    VSV_CUDA(ctx, cudaMemsetAsync(d_qt, 0, sizeof(int32_t) * (size_t)n_rec, ctx->stream));
-    VSV_CUDA(ctx, cudaMemsetAsync(d_xt, 0, sizeof(int32_t) * (size_t)n_rec, ctx->stream));
-  }
-  VSV_TRY(vsv_t1(ctx));
-  // the count is needed on the host to size the copy-out: one small sync
-  VSV_CUDA(ctx, cudaMemcpyAsync(n_out, d_nout, sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
-  VSV_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-  if (want_tot) {
-    VSV_TRY(vsv_out_done(ctx, ref_total, d_rt, (size_t)n_rec));
-    VSV_TRY(vsv_out_done(ctx, qry_total, d_qt, (size_t)n_rec));
-    VSV_TRY(vsv_out_done(ctx, aux_total, d_xt, (size_t)n_rec));
-  }
-  if (*n_out > cap) {
-    vsv_end(ctx, true);
-    VSV_FAIL(ctx, VSV_E_CAPACITY, "vsv_scan_cigar: output capacity too small");
-  }
-  VSV_TRY(vsv_out_done(ctx, out, d_out, (size_t)*n_out));
-  return vsv_end(ctx);
+  if (mode < 0 || mode > 2) VSV_FAIL(ctx, VSV_E_ARG, "vsv_scan_cigar: bad mode");
+  ScanCall c;
+  memset(&c, 0, sizeof(c));
+  c.mode = mode; c.min_len_a = min_len; c.min_mapq_a = min_mapq;
+  c.ops = ops; c.op_off = op_off; c.pos = pos; c.mapq = mapq; c.enable_a = enable; c.n_rec = n_rec;
+  c.out_a = out; c.cap_a = cap; c.n_a = n_out;
+  c.ref_total = ref_total; c.qry_total = qry_total; c.aux_total = aux_total;
+  return scan_impl(ctx, c);
 }
 
-// ================================================================================
-// K2: per-record merge.  cluster_ins_one_read / cluster_del_one_read (ECS_H:87-164),
-// generate_combine_sigs (SE:373-435).  Signatures are sparse (<= a few per record), so
-// this is one thread per record run walking its (already ordered) signatures; two
-// passes (count, exclusive scan, write) keep the output order deterministic.
-// ================================================================================
-__global__ void k_type_flags(const vsv_sig* __restrict__ s, int64_t n, int32_t* __restrict__ is_del) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) is_del[i] = s[i].type == VSV_DEL ? 1 : 0;
-}
-
-__global__ void k_type_split(const vsv_sig* __restrict__ s, int64_t n, const int64_t* __restrict__ del_excl,
-                             vsv_sig* __restrict__ dels, vsv_sig* __restrict__ inss) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  vsv_sig v = s[i];
-  int64_t d = del_excl[i];
-  if (v.type == VSV_DEL) dels[d] = v; else inss[i - d] = v;
-}
-
-// Walk one record's run [i0,i1) of same-type signatures; calls f(merged) per output.
-template <typename F>
-__device__ __forceinline__ void merge_walk(const vsv_sig* __restrict__ s, int64_t i0, int64_t i1, int mode,
-                                           int type, F f) {
-  vsv_sig cur = s[i0];
-  cur.first = (int32_t)i0;
-  cur.count = 1;
-  if (mode == VSV_MODE_READS) {
-    f(cur);
-    for (int64_t k = i0 + 1; k < i1; ++k) {
-      cur = s[k]; cur.first = (int32_t)k; cur.count = 1;
-      f(cur);
-    }
-    return;
-  }
-  int32_t mark = (type == VSV_INS) ? cur.pos : cur.pos + cur.len;  // cute: last INS pos / DEL end
-  for (int64_t k = i0 + 1; k < i1; ++k) {
-    const vsv_sig n = s[k];
-    bool hit;
-    if (mode == VSV_MODE_CONTIG) {
-      int32_t d = abs(n.pos - cur.pos);
-      if (type == VSV_INS) {
-        hit = (cur.len > 250 && n.len > 250 && d < 250) || (cur.len > 320 && n.len > 320 && d < 380) ||
-              (cur.len > 100 && n.len > 100 && d < 250);           // ECS_H:112-135
-        if (hit) { cur.q1 = n.q1; cur.len = cur.q1 - cur.q0; }     // ECS_H:91-97
-      } else {
-        hit = cur.len > 150 && n.len > 150 && d < 150;             // ECS_H:148-150
-        if (hit) { cur.len = n.pos + n.len - cur.pos; cur.q1 = cur.q0 + 1; }  // ECS_H:99-106
-      }
-    } else {  // VSV_MODE_CUTE
-      if (type == VSV_INS) {
-        hit = n.pos - mark <= 100;                                 // SE:396-399
-        if (hit) { cur.len += n.len; mark = n.pos; }
-      } else {
-        hit = n.pos - mark <= 0;                                   // SE:420
-        if (hit) { cur.len += n.len; mark = n.pos + n.len; }
-      }
-    }
-    if (hit) {
-      cur.count++;
-    } else {
-      f(cur);
-      cur = n; cur.first = (int32_t)k; cur.count = 1;
-      mark = n.pos;                                                // SE:412-413 / SE:429-430 (end := start quirk)
-    }
-  }
-  f(cur);
-}
-
-__global__ void k_merge_count(const vsv_sig* __restrict__ s, int64_t n, int mode, int type,
-                              int32_t* __restrict__ cnt) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  int32_t c = 0;
-  if (i == 0 || s[i - 1].rec != s[i].rec) {
-    int64_t e = i + 1;
-    const int32_t r = s[i].rec;
-    while (e < n && s[e].rec == r) ++e;
-    merge_walk(s, i, e, mode, type, [&](const vsv_sig&) { ++c; });
-  }
-  cnt[i] = c;
-}
-
-__global__ void k_merge_write(const vsv_sig* __restrict__ s, int64_t n, int mode, int type,
-                              const int64_t* __restrict__ excl, vsv_sig* __restrict__ out) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  if (i == 0 || s[i - 1].rec != s[i].rec) {
-    int64_t e = i + 1;
-    const int32_t r = s[i].rec;
-    while (e < n && s[e].rec == r) ++e;
-    int64_t o = excl[i];
-    merge_walk(s, i, e, mode, type, [&](const vsv_sig& v) { out[o++] = v; });
-  }
-}
-
-extern "C" int vsv_merge_in_record(vsv_ctx* ctx, int mode, const vsv_sig* sigs, int64_t n, vsv_sig* out_del,
-                                   int64_t* n_del, vsv_sig* out_ins, int64_t* n_ins) {
+extern "C" int vsv_scan_reads_fused(vsv_ctx* ctx, int min_len_reads, int min_mapq_reads, int min_len_cute,
+                                    int min_mapq_cute, const uint32_t* ops, const int64_t* op_off,
+                                    const int32_t* pos, const uint8_t* mapq, const uint8_t* enable_cute,
+                                    int64_t n_rec, vsv_sig* out_reads, int64_t cap_reads, int64_t* n_reads,
+                                    vsv_sig* out_cute, int64_t cap_cute, int64_t* n_cute, int32_t* ref_total,
+                                    int32_t* qry_total, int32_t* aux_total) {
   VSV_TRY(vsv_begin(ctx));
-  if (mode < 0 || mode > 2 || n < 0 || !n_del || !n_ins || n >= (int64_t(1) << 31))
-    VSV_FAIL(ctx, VSV_E_ARG, "vsv_merge_in_record: bad argument");
-  *n_del = *n_ins = 0;
-  if (n == 0) return VSV_OK;
-  const vsv_sig* d_in = nullptr;
-  VSV_TRY(vsv_in(ctx, sigs, (size_t)n, &d_in));
-  vsv_sig *d_od = nullptr, *d_oi = nullptr, *t_del = nullptr, *t_ins = nullptr;
-  VSV_TRY(vsv_out(ctx, out_del, (size_t)n, &d_od));
-  VSV_TRY(vsv_out(ctx, out_ins, (size_t)n, &d_oi));
-  VSV_TRY(vsv_tmp(ctx, (size_t)n, &t_del));
-  VSV_TRY(vsv_tmp(ctx, (size_t)n, &t_ins));
-  int32_t* flags = nullptr;
-  int64_t *excl = nullptr, *tot = nullptr;
-  VSV_TRY(vsv_tmp(ctx, (size_t)n, &flags));
-  VSV_TRY(vsv_tmp(ctx, (size_t)n, &excl));
-  VSV_TRY(vsv_tmp(ctx, 3, &tot));
-  const unsigned g = (unsigned)vsv_cdiv(n, 256);
-  VSV_TRY(vsv_t0(ctx));
-  VSV_LAUNCH(ctx, k_type_flags, g, 256, 0, d_in, n, flags);
-  VSV_TRY(vsv_exclusive_scan_i32(ctx, flags, n, excl, tot));
-  VSV_LAUNCH(ctx, k_type_split, g, 256, 0, d_in, n, excl, t_del, t_ins);
-  int64_t h_tot[3] = {0, 0, 0};
-  VSV_CUDA(ctx, cudaMemcpyAsync(h_tot, tot, sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
-  VSV_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-  const int64_t nd = h_tot[0], ni = n - h_tot[0];
-  for (int type = 0; type < 2; ++type) {
-    const int64_t m = type == VSV_DEL ? nd : ni;
-    if (m == 0) continue;
-    const vsv_sig* src = type == VSV_DEL ? t_del : t_ins;
-    vsv_sig* dst = type == VSV_DEL ? d_od : d_oi;
-    const unsigned gm = (unsigned)vsv_cdiv(m, 128);
-    VSV_LAUNCH(ctx, k_merge_count, gm, 128, 0, src, m, mode, type, flags);
-    VSV_TRY(vsv_exclusive_scan_i32(ctx, flags, m, excl, tot + 1 + type));
-    VSV_LAUNCH(ctx, k_merge_write, gm, 128, 0, src, m, mode, type, excl, dst);
-  }
-  VSV_TRY(vsv_t1(ctx));
-  VSV_CUDA(ctx, cudaMemcpyAsync(h_tot + 1, tot + 1, 2 * sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
-  VSV_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-  *n_del = nd ? h_tot[1] : 0;
-  *n_ins = ni ? h_tot[2] : 0;
-  VSV_TRY(vsv_out_done(ctx, out_del, d_od, (size_t)*n_del));
-  VSV_TRY(vsv_out_done(ctx, out_ins, d_oi, (size_t)*n_ins));
-  return vsv_end(ctx);
+  ScanCall c;
+  memset(&c, 0, sizeof(c));
+  c.mode = VSV_MODE_FUSED;
+  c.min_len_a = min_len_reads; c.min_mapq_a = min_mapq_reads; c.min_len_b = min_len_cute; c.min_mapq_b = min_mapq_cute;
+  c.ops = ops; c.op_off = op_off; c.pos = pos; c.mapq = mapq; c.enable_b = enable_cute; c.n_rec = n_rec;
+  c.out_a = out_reads; c.cap_a = cap_reads; c.n_a = n_reads;
+  c.out_b = out_cute; c.cap_b = cap_cute; c.n_b = n_cute;
+  c.ref_total = ref_total; c.qry_total = qry_total; c.aux_total = aux_total;
+  return scan_impl(ctx, c);
 }

@@ -49,6 +49,8 @@ SIGNATURES = {
     "vsv_timer_stop": [_vp, C.POINTER(C.c_float)],
     "vsv_get_main_kernel_ms": [_vp, C.POINTER(C.c_float)],
     "vsv_scan_cigar": [_vp, _int, _int, _int, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _i64, C.POINTER(_i64), _vp, _vp, _vp],
+    "vsv_scan_reads_fused": [_vp, _int, _int, _int, _int, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _i64, C.POINTER(_i64),
+                             _vp, _i64, C.POINTER(_i64), _vp, _vp, _vp],
     "vsv_merge_in_record": [_vp, _int, _vp, _i64, _vp, C.POINTER(_i64), _vp, C.POINTER(_i64)],
     "vsv_split_pairs": [_vp, _int, _int, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _i64, C.POINTER(_i64)],
     "vsv_argsort_stable": [_vp, _vp, _i64, _vp],
@@ -181,6 +183,33 @@ class Context:
                 continue
             self._chk(rc)
             return out[: n_out.value], rt, qt, xt
+
+    def scan_reads_fused(self, ops, op_off, pos, mapq, enable_cute=None, min_len_reads=30, min_mapq_reads=50,
+                         min_len_cute=10, min_mapq_cute=20, cap=None, totals=True):
+        """ERS + SE scanners in one pass -> (reads_sigs, cute_sigs, ref_total, qry_total, aux_total)."""
+        ops = _arr(ops, np.uint32)
+        op_off = _arr(op_off, np.int64)
+        pos = _arr(pos, np.int32)
+        mapq = _arr(mapq, np.uint8)
+        enable_cute = _arr(enable_cute, np.uint8)
+        n = len(pos)
+        if ops.ctypes.data % 16:
+            ops = _aligned_copy(ops)
+        cap_r = cap_c = cap if cap is not None else max(1024, len(ops) // 16)
+        rt = np.zeros(n, np.int32) if totals else None
+        qt = np.zeros(n, np.int32) if totals else None
+        xt = np.zeros(n, np.int32) if totals else None
+        while True:
+            out_r, out_c = _aligned_empty(cap_r, SIG_DTYPE), _aligned_empty(cap_c, SIG_DTYPE)
+            n_r, n_c = _i64(), _i64()
+            rc = self.lib.vsv_scan_reads_fused(self.h, min_len_reads, min_mapq_reads, min_len_cute, min_mapq_cute,
+                                               _p(ops), _p(op_off), _p(pos), _p(mapq), _p(enable_cute), n, _p(out_r),
+                                               cap_r, C.byref(n_r), _p(out_c), cap_c, C.byref(n_c), _p(rt), _p(qt), _p(xt))
+            if rc == E_CAPACITY:
+                cap_r, cap_c = max(cap_r, int(n_r.value)), max(cap_c, int(n_c.value))
+                continue
+            self._chk(rc)
+            return out_r[: n_r.value], out_c[: n_c.value], rt, qt, xt
 
     def merge_in_record(self, mode, sigs):
         sigs = np.ascontiguousarray(sigs, dtype=SIG_DTYPE)

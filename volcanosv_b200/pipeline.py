@@ -114,27 +114,23 @@ class ChromShard:
         cap = max(self.sig_cap, 1 << 16, n_ops // 64)
         sig = lambda name: self._buf(name, cap * 8, i32)  # vsv_sig = 8 x int32
         rt, qt, xt = (self._buf(k, n_rec, i32) for k in ("ref_total", "qry_total", "aux_total"))
-        n_out = C.c_int64()
-
-        def scan(mode, min_len, min_mapq, enable, out, totals):
-            nonlocal cap
-            while True:
-                rc = lib.vsv_scan_cigar(h, mode, min_len, min_mapq, _dp(ops), _dp(op_off), _dp(pos), _dp(mapq),
-                                        _dp(enable), n_rec, _dp(out), cap, C.byref(n_out),
-                                        _dp(rt) if totals else None, _dp(qt) if totals else None,
-                                        _dp(xt) if totals else None)
-                if rc == L.E_CAPACITY:
-                    cap = int(n_out.value * 1.25) + 1024
-                    self.sig_cap = cap
-                    raise _Regrow()
-                self._chk(rc)
-                res.scan_ms.append(self.ctx.main_kernel_ms())
-                return int(n_out.value)
-
-        # -- stage 1a: reads, simple scanner (ERS:107-145), mapq>=50, >=30 bp ------------
-        s_reads = sig("sig_reads")
-        n_r = scan(L.MODE_READS, 30, 50, None, s_reads, True)
-        res.n_read_sigs = n_r
+        # -- stage 1: BOTH read scanners in one pass over the ops -------------------------
+        #    stream "reads": ERS:107-145 (mapq>=50, >=30 bp); stream "cute": SE:438-478
+        #    (query_length>=500, mapq>=20, >=10 bp)
+        enable = self._buf("enable", n_rec, u8)
+        self._chk(lib.vsv_ge_u8(h, _dp(qlen), 500, n_rec, _dp(enable)))                 # SE:439
+        s_reads, s_cute = sig("sig_reads"), sig("sig_cute")
+        n_r_, n_c_ = C.c_int64(), C.c_int64()
+        rc = lib.vsv_scan_reads_fused(h, 30, 50, 10, 20, _dp(ops), _dp(op_off), _dp(pos), _dp(mapq), _dp(enable), n_rec,
+                                      _dp(s_reads), cap, C.byref(n_r_), _dp(s_cute), cap, C.byref(n_c_), _dp(rt), _dp(qt),
+                                      _dp(xt))
+        if rc == L.E_CAPACITY:
+            self.sig_cap = int(max(n_r_.value, n_c_.value) * 1.25) + 1024
+            raise _Regrow()
+        self._chk(rc)
+        res.scan_ms.append(self.ctx.main_kernel_ms())
+        n_r, n_c = int(n_r_.value), int(n_c_.value)
+        res.n_read_sigs, res.n_cute_sigs = n_r, n_c
         # read intervals for the depth join: [pos, pos + ref_total)  (reference_end)
         rend = self._buf("read_end", n_rec, i32)
         self._chk(lib.vsv_add_i32(h, _dp(pos), _dp(rt), n_rec, _dp(rend)))
@@ -143,12 +139,7 @@ class ChromShard:
         rs_pos, rs_len = self._buf("rs_pos", cap, i32), self._buf("rs_len", cap, i32)
         self._chk(lib.vsv_sig_columns(h, _dp(s_reads_sorted), n_r, _dp(rs_pos), _dp(rs_len), None))
 
-        # -- stage 1b: reads, cuteSV-style scanner (SE:438-478) + in-read merge (SE:373-435)
-        enable = self._buf("enable", n_rec, u8)
-        self._chk(lib.vsv_ge_u8(h, _dp(qlen), 500, n_rec, _dp(enable)))                 # SE:439
-        s_cute = sig("sig_cute")
-        n_c = scan(L.MODE_CUTE, 10, 20, enable, s_cute, False)
-        res.n_cute_sigs = n_c
+        # -- in-read merge of the cuteSV-style signals (SE:373-435) -------------------------
         s_del, s_ins = sig("sig_del"), sig("sig_ins")
         nd, ni = C.c_int64(), C.c_int64()
         self._chk(lib.vsv_merge_in_record(h, L.MODE_CUTE, _dp(s_cute), n_c, _dp(s_del), C.byref(nd), _dp(s_ins),
