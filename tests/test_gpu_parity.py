@@ -187,3 +187,30 @@ def test_scan_reads_fused_equals_two_scans(ctx, case):
     r2, *_ = ctx.scan_cigar(V.MODE_READS, ops, off, pos, mapq, min_len=30, min_mapq=50)
     c2, *_ = ctx.scan_cigar(V.MODE_CUTE, ops, off, pos, mapq, enable=en, min_len=10, min_mapq=20, totals=False)
     assert np.array_equal(r.view(np.uint8), r2.view(np.uint8)) and np.array_equal(c.view(np.uint8), c2.view(np.uint8))
+
+
+def test_scan_staging_retry_and_candidate_overflow(ctx):
+    """(a) most records fail the mapq gate, so the raw candidate count is far above the
+    output count: with cap == n_out the internal staging must grow and retry; (b) a tile
+    whose per-warp candidate lists overflow (every op is a candidate) takes the rescan path."""
+    ops, off, pos, mapq = _rand_ops_batch(9, 400, 600, [0, 1, 2, 4], big_rate=0.3)
+    mapq[:] = 0
+    mapq[::40] = 60
+    es, *_ = O.scan_cigar(ops, off, pos, mapq, V.MODE_READS, 30, 50)
+    assert 0 < len(es) < 0.1 * int(((ops >> 4) >= 30).sum())
+    sigs, *_ = ctx.scan_cigar(V.MODE_READS, ops, off, pos, mapq, min_len=30, min_mapq=50, cap=len(es))
+    assert sig_tuples(sigs) == es
+    en = np.ones(400, np.uint8)
+    r, c, *_ = ctx.scan_reads_fused(ops, off, pos, mapq, enable_cute=en, cap=len(es))
+    ec, *_ = O.scan_cigar(ops, off, pos, mapq, V.MODE_CUTE, 10, 20, enable=en)
+    assert sig_tuples(r) == es and sig_tuples(c) == ec
+    # (b) dense candidates: alternating 40I / 35D only
+    cig = [[(1, 40), (2, 35)] * 3000, [(0, 5)], [(2, 31), (1, 32)] * 2500]
+    ops, off = O.pack_cigar(cig)
+    pos = np.array([10, 20, 30], np.int32)
+    mapq = np.full(3, 60, np.uint8)
+    for mode in (V.MODE_CONTIG, V.MODE_READS, V.MODE_CUTE):
+        sigs, rt, qt, xt = ctx.scan_cigar(mode, ops, off, pos, mapq, min_len=30)
+        es, ert, eqt, ext = O.scan_cigar(ops, off, pos, mapq, mode, 30, 0)
+        assert sig_tuples(sigs) == es and len(es) == 11000
+        assert np.array_equal(rt, ert) and np.array_equal(qt, eqt)

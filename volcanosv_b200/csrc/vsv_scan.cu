@@ -38,7 +38,7 @@
 #define SCAN_TILE (SCAN_THREADS * SCAN_VPT)
 #define SCAN_STAGES 2
 #define SCAN_RT 128           // records per tile kept in the shared-memory record table
-#define SCAN_WCAND 512        // per-warp candidate list capacity (= ops per warp)
+#define SCAN_WCAND 64         // per-warp candidate list capacity (overflow: dense phase rescans the tile)
 #define SCAN_CHUNK 256        // staging slots reserved per global atomic
 #define SCAN_CTAS_PER_SM 4
 
@@ -229,10 +229,12 @@ struct ScanSmem {
   int32_t t_off[2][SCAN_RT + 4];          // record table: op_off - tile_start, clamped to [-1, TILE+1]
   int32_t t_pos[2][SCAN_RT];
   uint32_t t_info[2][SCAN_RT];
+  uint32_t P[5][SCAN_RT + 4];             // prefix sums at the (clamped) start of every table record
   uint32_t w[6][SCAN_WARPS];              // warp totals (r,q,x1,x2,x3,cand)
   uint32_t wx[6][SCAN_WARPS];             // warp exclusive offsets
   uint32_t tot[6];
   uint32_t wrare[SCAN_WARPS];
+  uint32_t ovf;                           // a warp's candidate list overflowed in this tile
   uint64_t bar[SCAN_STAGES];
 };
 
@@ -276,6 +278,7 @@ struct RecTab {
 // sums over tile ops [0, j)
 template <int MODE>
 __device__ __forceinline__ Sums prefix_at(const ScanSmem& sm, const uint32_t* tile, int j) {
+  typedef ModeTraits<MODE> M;
   Sums s;
   if (j >= SCAN_TILE) {
     s.r = sm.tot[0]; s.q = sm.tot[1]; s.x1 = sm.tot[2]; s.x2 = sm.tot[3]; s.x3 = sm.tot[4];
@@ -285,9 +288,23 @@ __device__ __forceinline__ Sums prefix_at(const ScanSmem& sm, const uint32_t* ti
   s.r = sm.wx[0][wp] + sm.tx[0][t];
   s.q = sm.wx[1][wp] + sm.tx[1][t];
   s.x1 = sm.wx[2][wp]; s.x2 = sm.wx[3][wp]; s.x3 = sm.wx[4][wp];
-  if (sm.wrare[wp]) { s.x1 += sm.tx[2][t]; s.x2 += sm.tx[3][t]; s.x3 += sm.tx[4][t]; }
   const uint32_t* row = tile + t * SCAN_VPT;
-  for (int i = 0; i < n; ++i) add_op<MODE>(row[i], s);
+  if (sm.wrare[wp]) {  // this warp saw N / H / P ...: full walk
+    s.x1 += sm.tx[2][t]; s.x2 += sm.tx[3][t]; s.x3 += sm.tx[4][t];
+    for (int i = 0; i < n; ++i) add_op<MODE>(row[i], s);
+  } else {
+    uint32_t r = 0, q = 0;
+    const uint4* row4 = reinterpret_cast<const uint4*>(row);
+    const uint4 v0 = row4[0], v1 = row4[1], v2 = row4[2], v3 = row4[3];
+    const uint32_t ww[16] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w, v2.x, v2.y, v2.z, v2.w, v3.x, v3.y, v3.z, v3.w};
+#pragma unroll
+    for (int i = 0; i < 15; ++i) {
+      const uint32_t w = ww[i], bit = (i < n) ? (1u << (w & 15u)) : 0u, len = w >> 4;
+      r += (bit & M::REF) ? len : 0u;
+      q += (bit & M::QRY) ? len : 0u;
+    }
+    s.r += r; s.q += q;
+  }
   return s;
 }
 
@@ -315,6 +332,7 @@ __global__ void __launch_bounds__(SCAN_THREADS, SCAN_CTAS_PER_SM) k_scan_tiles(c
   const int32_t n_full = (int32_t)(p.n_ops / SCAN_TILE);  // tiles below n_full are complete
 
   if (tid == 0) {
+    sm.ovf = 0u;
     for (int s = 0; s < SCAN_STAGES; ++s) mbar_init(&sm.bar[s], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     fence_proxy_async();
@@ -358,7 +376,7 @@ __global__ void __launch_bounds__(SCAN_THREADS, SCAN_CTAS_PER_SM) k_scan_tiles(c
     const int nrt_next = nxt.y - nxt.x + 1;
     int32_t pf_off = 0, pf_pos = 0;
     uint32_t pf_info = 0;
-    const bool pf_on = (tile64 + G < n_tiles) && nrt_next <= SCAN_RT && tid <= nrt_next;
+    const bool pf_on = tid <= nrt_next && nrt_next <= SCAN_RT && (tile64 + G < n_tiles);
     if (pf_on) {
       const int64_t d = __ldg(p.op_off + nxt.x + tid) - (tile_start + (int64_t)G * SCAN_TILE);
       pf_off = (int32_t)max((int64_t)-1, min(d, (int64_t)SCAN_TILE + 1));
@@ -438,7 +456,9 @@ __global__ void __launch_bounds__(SCAN_THREADS, SCAN_CTAS_PER_SM) k_scan_tiles(c
       while (m) {
         const int s = __ffs(m) - 1;
         m &= m - 1;
-        sm.cand[warp][idx++] = (uint16_t)(tid * SCAN_VPT + s);
+        if (idx < SCAN_WCAND) sm.cand[warp][idx] = (uint16_t)(tid * SCAN_VPT + s);
+        else sm.ovf = 1u;
+        ++idx;
       }
     }
     __syncthreads();  // B1: warp totals, candidate lists, tx visible
@@ -464,29 +484,81 @@ __global__ void __launch_bounds__(SCAN_THREADS, SCAN_CTAS_PER_SM) k_scan_tiles(c
         for (int k = 0; k < 6; ++k) sm.tot[k] = v[k];
       }
     }
-    __syncthreads();  // B2: block prefixes complete
-
     RecTab rt;
     rt.sm = &sm; rt.p = &p; rt.tile_start = tile_start; rt.rf = cur.x; rt.nrt = cur.y - cur.x + 1; rt.slot = slot;
     rt.fast = rt.nrt <= SCAN_RT;
+    // B2 (block prefixes complete) is only needed when warps 1..7 take part in what follows
+    if (!rt.fast) __syncthreads(); else __syncwarp();
 
     if (warp == 0) {
-      // -- dense candidate phase: gate, count, reserve staging, ordered write ------------
+      // -- prefix sums at every record start (lanes = records), then the per-record totals --
+      if (rt.fast) {
+        for (int k = lane; k <= rt.nrt; k += 32) {
+          const Sums ps = prefix_at<MODE>(sm, tl, min(max(rt.off(k), 0), SCAN_TILE));
+          sm.P[0][k] = ps.r; sm.P[1][k] = ps.q; sm.P[2][k] = ps.x1; sm.P[3][k] = ps.x2; sm.P[4][k] = ps.x3;
+        }
+        __syncwarp();
+        if (p.ref_total != nullptr) {
+          for (int k = lane; k < rt.nrt; k += 32) {
+            const Sums d = {sm.P[0][k + 1] - sm.P[0][k], sm.P[1][k + 1] - sm.P[1][k], sm.P[2][k + 1] - sm.P[2][k],
+                            sm.P[3][k + 1] - sm.P[3][k], sm.P[4][k + 1] - sm.P[4][k]};
+            const uint32_t tr = ref_of<MODE, 0>(d), tq = qry_of<MODE, 0>(d), tx = aux_of<MODE>(d);
+            const int64_t rr = (int64_t)rt.rf + k;
+            if (rt.off(k) >= 0 && rt.off(k + 1) <= SCAN_TILE) {
+              p.ref_total[rr] = tr; p.qry_total[rr] = tq; p.aux_total[rr] = tx;
+            } else {
+              atomicAdd(p.ref_total + rr, tr); atomicAdd(p.qry_total + rr, tq); atomicAdd(p.aux_total + rr, tx);
+            }
+          }
+        }
+      }
+      // -- dense candidate phase (one pass): staging slots are reserved for the RAW candidate
+      //    count (an upper bound of what passes the record gates), then each group of 32
+      //    candidates is looked up, gated and written in op order.
       const uint32_t ncand = sm.tot[5];
+      const bool ovf = sm.ovf != 0u;
       uint32_t cnt_a = 0, cnt_b = 0;
-      unsigned long long base_a = 0, base_b = 0;
-      for (int pass = 0; pass < 2; ++pass) {
-        uint32_t run_a = 0, run_b = 0;
-        for (uint32_t g0 = 0; g0 < ncand; g0 += 32) {
-          const uint32_t i = g0 + lane;
-          bool ok_a = false, ok_b = false;
-          int j = 0, k = 0;
-          uint32_t w = 0, info = 0;
-          if (i < ncand) {
+      unsigned long long base_a = ~0ull, base_b = ~0ull;
+      if (ncand) {
+        if (lane == 0) {  // chunked reservation: one global atomic per ~SCAN_CHUNK signatures
+#pragma unroll
+          for (int s = 0; s < (MODE == VSV_MODE_FUSED ? 2 : 1); ++s) {
+            if (ch_next[s] + ncand > ch_end[s]) {
+              const unsigned long long n = ncand > SCAN_CHUNK ? ncand : SCAN_CHUNK;
+              ch_next[s] = atomicAdd(p.stage_ctr + s, n);
+              ch_end[s] = ch_next[s] + n;
+            }
+            unsigned long long b0 = ch_next[s];
+            ch_next[s] += ncand;
+            if (b0 + ncand > (s == 0 ? p.stage_cap_a : p.stage_cap_b)) {  // staging full: host retries
+              b0 = ~0ull;
+              p.stage_ctr[2] = 1ull;
+            }
+            if (s == 0) base_a = b0; else base_b = b0;
+          }
+        }
+        base_a = __shfl_sync(0xffffffffu, base_a, 0);
+        base_b = __shfl_sync(0xffffffffu, base_b, 0);
+        const uint32_t ngroups = ovf ? SCAN_TILE / 32 : (ncand + 31) / 32;
+        for (uint32_t g = 0; g < ngroups; ++g) {
+          bool valid;
+          int j;
+          if (!ovf) {
+            const uint32_t i = g * 32 + lane;
+            valid = i < ncand;
             int wp = 0;
 #pragma unroll
             for (int u = 1; u < SCAN_WARPS; ++u) wp += (sm.wx[5][u] <= i) ? 1 : 0;
-            j = sm.cand[wp][i - sm.wx[5][wp]];
+            j = valid ? sm.cand[wp][i - sm.wx[5][wp]] : 0;
+          } else {  // a list overflowed: enumerate the candidates straight from the tile
+            j = g * 32 + lane;
+            const uint32_t w0 = tl[j];
+            valid = ((1u << (w0 & 15u)) & 6u) && w0 >= p.min_w;
+          }
+          bool ok_a = false, ok_b = false;
+          int k = 0;
+          uint32_t w = 0, info = 0;
+          if (valid) {
             w = tl[j];
             k = rt.lookup(j);
             info = rt.info(k);
@@ -495,65 +567,47 @@ __global__ void __launch_bounds__(SCAN_THREADS, SCAN_CTAS_PER_SM) k_scan_tiles(c
             if (MODE == VSV_MODE_FUSED) ok_b = (info & 2u) && len >= p.min_len_b;
           }
           const uint32_t ba = __ballot_sync(0xffffffffu, ok_a);
-          const uint32_t bb = __ballot_sync(0xffffffffu, ok_b);
-          if (pass == 0) {
-            cnt_a += __popc(ba);
-            cnt_b += __popc(bb);
-          } else {
-            if (ok_a || ok_b) {
-              const Sums pre = prefix_at<MODE>(sm, tl, j);
-              const int32_t o = rt.off(k);
-              const bool carry = o < 0;
-              const Sums part = carry ? pre : pre - prefix_at<MODE>(sm, tl, o);
-              const uint32_t lt = (1u << lane) - 1u;
-              if (ok_a && base_a != ~0ull)
-                write_sig<MODE, 0>(p.stage_a + base_a + run_a + __popc(ba & lt), rt.rf + k, w, rt.pos(k), info >> 2,
-                                   part, carry);
-              if (MODE == VSV_MODE_FUSED && ok_b && base_b != ~0ull)
-                write_sig<MODE, 1>(p.stage_b + base_b + run_b + __popc(bb & lt), rt.rf + k, w, rt.pos(k), info >> 2,
-                                   part, carry);
+          const uint32_t bb = (MODE == VSV_MODE_FUSED) ? __ballot_sync(0xffffffffu, ok_b) : 0u;
+          if (ok_a || ok_b) {
+            const Sums pre = prefix_at<MODE>(sm, tl, j);
+            const int32_t o = rt.off(k);
+            const bool carry = o < 0;
+            Sums part = pre;
+            if (!carry) {
+              if (rt.fast) part = pre - Sums{sm.P[0][k], sm.P[1][k], sm.P[2][k], sm.P[3][k], sm.P[4][k]};
+              else part = pre - prefix_at<MODE>(sm, tl, o);
             }
-            run_a += __popc(ba);
-            run_b += __popc(bb);
+            const uint32_t lt = (1u << lane) - 1u;
+            if (ok_a && base_a != ~0ull)
+              write_sig<MODE, 0>(p.stage_a + base_a + cnt_a + __popc(ba & lt), rt.rf + k, w, rt.pos(k), info >> 2, part,
+                                 carry);
+            if (MODE == VSV_MODE_FUSED && ok_b && base_b != ~0ull)
+              write_sig<MODE, 1>(p.stage_b + base_b + cnt_b + __popc(bb & lt), rt.rf + k, w, rt.pos(k), info >> 2, part,
+                                 carry);
           }
-        }
-        if (pass == 0) {
-          if (cnt_a == 0 && cnt_b == 0) break;
-          if (lane == 0) {  // reserve contiguous staging slots (chunked: few global atomics)
-            const uint32_t cn[2] = {cnt_a, cnt_b};
-            unsigned long long bs[2] = {0, 0};
-#pragma unroll
-            for (int s = 0; s < 2; ++s) {
-              if (cn[s] == 0) continue;
-              if (ch_next[s] + cn[s] > ch_end[s]) {
-                const unsigned long long n = cn[s] > SCAN_CHUNK ? cn[s] : SCAN_CHUNK;
-                ch_next[s] = atomicAdd(p.stage_ctr + s, n);
-                ch_end[s] = ch_next[s] + n;
-              }
-              bs[s] = ch_next[s];
-              ch_next[s] += cn[s];
-              if (bs[s] + cn[s] > (s == 0 ? p.stage_cap_a : p.stage_cap_b)) bs[s] = ~0ull;  // staging full
-            }
-            base_a = bs[0]; base_b = bs[1];
-          }
-          base_a = __shfl_sync(0xffffffffu, base_a, 0);
-          base_b = __shfl_sync(0xffffffffu, base_b, 0);
+          cnt_a += __popc(ba);
+          cnt_b += __popc(bb);
         }
       }
       if (lane == 0) {  // tile aggregate: sums since the last record start inside the tile
         Sums a = {sm.tot[0], sm.tot[1], sm.tot[2], sm.tot[3], sm.tot[4]};
         const int32_t o = rt.off(rt.nrt - 1);
         const bool bound = o >= 0;
-        if (bound) a = a - prefix_at<MODE>(sm, tl, o);
+        if (bound) {
+          const int kl = rt.nrt - 1;
+          if (rt.fast) a = a - Sums{sm.P[0][kl], sm.P[1][kl], sm.P[2][kl], sm.P[3][kl], sm.P[4][kl]};
+          else a = a - prefix_at<MODE>(sm, tl, o);
+        }
         TileState ts;
         ts.r = a.r; ts.q = a.q; ts.x1 = a.x1; ts.x2 = a.x2; ts.x3 = a.x3;
         ts.cnt_a = cnt_a; ts.cnt_b = cnt_b; ts.flag = bound ? 1u : 0u;
         p.tile_agg[tile] = ts;
         p.tile_stage[tile] = make_uint2(base_a == ~0ull ? 0xFFFFFFFFu : (uint32_t)base_a,
                                         base_b == ~0ull ? 0xFFFFFFFFu : (uint32_t)base_b);
+        sm.ovf = 0u;  // for the next tile (pushers write it only after B3)
       }
-    } else if (p.ref_total != nullptr) {
-      // -- warps 1..7: per-record totals of the records touching this tile ---------------
+    } else if (!rt.fast && p.ref_total != nullptr) {
+      // -- warps 1..7, only for tiles with more than SCAN_RT records: per-record totals ----
       for (int k = tid - 32; k < rt.nrt; k += SCAN_THREADS - 32) {
         const int32_t a = rt.off(k), b = rt.off(k + 1);
         const Sums d = prefix_at<MODE>(sm, tl, min(b, SCAN_TILE)) - prefix_at<MODE>(sm, tl, max(a, 0));
@@ -704,47 +758,54 @@ static int scan_impl(vsv_ctx* ctx, const ScanCall& c) {
     VSV_TRY(vsv_out(ctx, c.aux_total, (size_t)c.n_rec, &d_xt));
   }
   const int grid = (int)std::min<int64_t>(n_tiles, (int64_t)ctx->sm_count * SCAN_CTAS_PER_SM);
-  // staging: chunked reservation wastes < 1x the used slots plus one chunk per CTA
-  const int64_t scap_a = 2 * c.cap_a + (int64_t)grid * SCAN_CHUNK + SCAN_CHUNK;
-  const int64_t scap_b = fused ? 2 * c.cap_b + (int64_t)grid * SCAN_CHUNK + SCAN_CHUNK : 0;
-  int64_t* d_nout = nullptr;
+  // staging: slots are reserved per tile for the RAW candidate count in chunks, so the exact
+  // need is only known after a run; start from the caller's capacities and retry (rare) with
+  // the measured reservation if a tile found the staging full.
+  const int64_t slack = (int64_t)grid * SCAN_CHUNK + SCAN_CHUNK;
+  int64_t scap_a = (fused ? std::max(c.cap_a, c.cap_b) : c.cap_a) * 5 / 4 + slack;
+  int64_t scap_b = fused ? scap_a : 0;
+  int64_t* d_nout = nullptr;  // [0..1] signature counts, [2..3] staging counters, [4] staging-full flag
   uint32_t* d_info = nullptr;
   int2* d_trec = nullptr;
   TileState *d_agg = nullptr, *d_excl = nullptr;
   uint2* d_tstage = nullptr;
-  unsigned long long* d_ctr = nullptr;
-  vsv_sig *d_sa = nullptr, *d_sb = nullptr;
-  VSV_TRY(vsv_tmp(ctx, 2, &d_nout));
+  VSV_TRY(vsv_tmp(ctx, 5, &d_nout));
   VSV_TRY(vsv_tmp(ctx, (size_t)c.n_rec, &d_info));
   VSV_TRY(vsv_tmp(ctx, (size_t)n_tiles, &d_trec));
   VSV_TRY(vsv_tmp(ctx, (size_t)n_tiles, &d_agg));
   VSV_TRY(vsv_tmp(ctx, (size_t)n_tiles, &d_excl));
   VSV_TRY(vsv_tmp(ctx, (size_t)n_tiles, &d_tstage));
-  VSV_TRY(vsv_tmp(ctx, 2, &d_ctr));
-  VSV_TRY(vsv_tmp(ctx, (size_t)scap_a, &d_sa));
-  if (fused) VSV_TRY(vsv_tmp(ctx, (size_t)scap_b, &d_sb));
 
   p.rec_info = d_info;
   p.n_rec = c.n_rec; p.n_ops = n_ops; p.n_tiles = n_tiles;
   p.min_len_a = c.min_len_a; p.min_len_b = c.min_len_b;
   p.min_w = (uint32_t)(fused ? std::min(c.min_len_a, c.min_len_b) : c.min_len_a) << 4;
-  p.tile_rec = d_trec; p.tile_agg = d_agg; p.tile_stage = d_tstage; p.stage_ctr = d_ctr;
-  p.stage_a = d_sa; p.stage_b = d_sb;
-  p.stage_cap_a = (uint32_t)scap_a; p.stage_cap_b = (uint32_t)scap_b;
+  p.tile_rec = d_trec; p.tile_agg = d_agg; p.tile_stage = d_tstage;
+  p.stage_ctr = reinterpret_cast<unsigned long long*>(d_nout + 2);
   p.ref_total = (uint32_t*)d_rt; p.qry_total = (uint32_t*)d_qt; p.aux_total = (uint32_t*)d_xt;
 
+  int64_t h_n[5] = {0, 0, 0, 0, 0};
   VSV_TRY(vsv_t0(ctx));
-  VSV_CUDA(ctx, cudaMemsetAsync(d_nout, 0, 2 * sizeof(int64_t), ctx->stream));
-  VSV_CUDA(ctx, cudaMemsetAsync(d_ctr, 0, 2 * sizeof(unsigned long long), ctx->stream));
-  if (want_tot) {
-    VSV_CUDA(ctx, cudaMemsetAsync(d_rt, 0, sizeof(int32_t) * (size_t)c.n_rec, ctx->stream));
-    VSV_CUDA(ctx, cudaMemsetAsync(d_qt, 0, sizeof(int32_t) * (size_t)c.n_rec, ctx->stream));
-    VSV_CUDA(ctx, cudaMemsetAsync(d_xt, 0, sizeof(int32_t) * (size_t)c.n_rec, ctx->stream));
-  }
   if (n_tiles > 0) {
     VSV_LAUNCH(ctx, k_rec_info, (unsigned)vsv_cdiv(c.n_rec, 256), 256, 0, p.ops, p.op_off, d_mapq, d_ena, d_enb, c.n_rec,
                c.min_mapq_a, c.min_mapq_b, d_info);
     VSV_LAUNCH(ctx, k_tile_records, (unsigned)vsv_cdiv(n_tiles, 256), 256, 0, p.op_off, c.n_rec, n_ops, n_tiles, d_trec);
+  }
+  for (int attempt = 0; attempt < 3; ++attempt) {
+    if (scap_a >= (int64_t(1) << 32) - 1 || scap_b >= (int64_t(1) << 32) - 1)
+      VSV_FAIL(ctx, VSV_E_ARG, std::string(fn) + ": too many candidate signatures for one call; split the batch");
+    vsv_sig *d_sa = nullptr, *d_sb = nullptr;
+    VSV_TRY(vsv_tmp(ctx, (size_t)scap_a, &d_sa));
+    if (fused) VSV_TRY(vsv_tmp(ctx, (size_t)scap_b, &d_sb));
+    p.stage_a = d_sa; p.stage_b = d_sb;
+    p.stage_cap_a = (uint32_t)scap_a; p.stage_cap_b = (uint32_t)scap_b;
+    VSV_CUDA(ctx, cudaMemsetAsync(d_nout, 0, 5 * sizeof(int64_t), ctx->stream));
+    if (want_tot) {
+      VSV_CUDA(ctx, cudaMemsetAsync(d_rt, 0, sizeof(int32_t) * (size_t)c.n_rec, ctx->stream));
+      VSV_CUDA(ctx, cudaMemsetAsync(d_qt, 0, sizeof(int32_t) * (size_t)c.n_rec, ctx->stream));
+      VSV_CUDA(ctx, cudaMemsetAsync(d_xt, 0, sizeof(int32_t) * (size_t)c.n_rec, ctx->stream));
+    }
+    if (n_tiles == 0) break;
     VSV_CUDA(ctx, cudaEventRecord(ctx->evk0, ctx->stream));
     switch (c.mode) {
       case VSV_MODE_CONTIG: VSV_TRY(launch_scan<VSV_MODE_CONTIG>(ctx, p, grid)); break;
@@ -783,12 +844,16 @@ static int scan_impl(vsv_ctx* ctx, const ScanCall& c) {
                    c.cap_a, d_out_b, c.cap_b, d_nout);
         break;
     }
+    // the counts are needed on the host to size the copy-out: one small sync
+    VSV_CUDA(ctx, cudaMemcpyAsync(h_n, d_nout, 5 * sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
+    VSV_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    const bool fits = h_n[0] <= c.cap_a && (!fused || h_n[1] <= c.cap_b);
+    if (h_n[4] == 0 || !fits) break;  // done, or the caller has to grow its buffers anyway
+    if (attempt == 2) VSV_FAIL(ctx, VSV_E_NOMEM, std::string(fn) + ": staging kept overflowing");
+    scap_a = 2 * h_n[2] + slack;      // reservation of the failed run bounds the raw count
+    if (fused) scap_b = 2 * h_n[3] + slack;
   }
   VSV_TRY(vsv_t1(ctx));
-  // the counts are needed on the host to size the copy-out: one small sync
-  int64_t h_n[2] = {0, 0};
-  VSV_CUDA(ctx, cudaMemcpyAsync(h_n, d_nout, 2 * sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
-  VSV_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   *c.n_a = h_n[0];
   if (fused) *c.n_b = h_n[1];
   if (want_tot) {
