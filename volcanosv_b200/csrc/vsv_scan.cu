@@ -5,42 +5,41 @@
 // (LI/sig_extract.py:438-478).  VSV_MODE_FUSED runs the two READ scanners (ERS + SE)
 // in ONE pass over the packed ops and fills two output streams.
 //
-// Design v2 (B200-first, HBM/issue-bound streaming kernel, no inter-CTA dependency):
-//  * the packed ops of ALL records are one flat u32 array cut into fixed tiles of 4096
-//    ops, independent of record boundaries; a persistent CTA per SM slot walks tiles
-//    round-robin and pulls each 16 KB tile into shared memory with ONE 1-D TMA bulk copy
-//    (cp.async.bulk + mbarrier), double buffered, so loads of tile i+1 overlap the work on
-//    tile i and no thread spends instructions on staging;
-//  * fast path: every thread folds 16 consecutive ops (bank-conflict-free rotated
-//    LDS.128) into two running sums (reference / query advance) plus a 16-bit candidate
-//    mask; rare op codes (N, P, H, ...) are summed in a slow path only by warps that saw
-//    one;
-//  * candidates (D/I >= min_len: well under 1 % of the ops) are pushed to a per-warp
-//    shared-memory list and finished densely by warp 0: record lookup in a prefetched
-//    per-tile record table, mapq/enable gate, exact offsets from the block prefix, ordered
-//    write to a STAGING buffer whose slots are reserved per CTA in chunks (one global
-//    atomic per ~256 signatures);
-//  * every tile publishes a 32-byte aggregate (sums since the last record start inside
-//    the tile, signature counts).  A segmented exclusive scan over the tile aggregates
-//    (n_ops/4096 elements) and a warp-per-tile fix-up kernel then move the staged
-//    signatures to their final, deterministic (record, op)-ordered slot and add the carry
-//    of a record that began in an earlier tile.  The ops are read from HBM exactly once.
+// Design v5 (B200-first; the streaming kernel has NO block-level synchronisation):
+//  * the packed ops of ALL records are one flat u32 array cut into "warp tiles" of 1024
+//    ops (4 KB), independent of record boundaries.  Every WARP is an independent worker: it
+//    pulls its warp tiles round-robin into its own double-buffered shared-memory slot with
+//    1-D TMA bulk copies (cp.async.bulk + mbarrier), folds 32 consecutive ops per lane
+//    (bank-conflict-free rotated LDS.128) into two running sums (reference / query
+//    advance) and a 32-bit candidate mask, and warp-scans them with shuffles.  Rare op
+//    codes (N, P, H, ...) are summed only by warps that saw one.
+//  * what the streaming kernel leaves behind per warp tile: a 32-byte aggregate (sums since
+//    the last record start inside the tile), the in-tile prefix at every record start
+//    (`fstart`, one 32-byte row per record), and one 32-byte staging entry per RAW
+//    candidate (D/I >= min_len: well under 1 % of the ops) holding the lane's exclusive
+//    prefix.  Staging slots are reserved per warp in chunks (one global atomic per ~128
+//    candidates).
+//  * everything that is sparse runs afterwards in small, lane-dense kernels: k_gate (one
+//    thread per warp tile: record lookup, mapq/enable gate, exact in-record offsets),
+//    a segmented exclusive scan over the tile aggregates (CUB, n_ops/1024 elements),
+//    k_emit (final, deterministic (record, op)-ordered slots + carry of a record that
+//    began in an earlier tile) and k_rec_totals (reference_end / read length per record).
+//    The ops are read from HBM exactly once.
 //
-// v1 (single-pass chained look-back) is described in profiles/r01a_scan_v1.md: it was
-// bound by the tile chain at 7 % of HBM.
+// History: v1 (single-pass chained look-back) was bound by the tile chain at 7 % of HBM
+// (profiles/r01a_scan_v1.md); v2-v4 (CTA tiles, candidates finished by warp 0 behind
+// __syncthreads) were bound by that serial phase at 23-25 % (profiles/r01b_scan_v4.md).
 #include <cub/device/device_scan.cuh>
 
 #include "vsv_common.cuh"
 
-#define SCAN_THREADS 256
-#define SCAN_WARPS (SCAN_THREADS / 32)
-#define SCAN_VPT 16
-#define SCAN_TILE (SCAN_THREADS * SCAN_VPT)
+#define WT_OPS 1024           // ops per warp tile
+#define WT_VPT 32             // ops per lane
+#define SCAN_WARPS 4          // warps (independent workers) per CTA
+#define SCAN_THREADS (SCAN_WARPS * 32)
 #define SCAN_STAGES 2
-#define SCAN_RT 128           // records per tile kept in the shared-memory record table
-#define SCAN_WCAND 64         // per-warp candidate list capacity (overflow: dense phase rescans the tile)
-#define SCAN_CHUNK 256        // staging slots reserved per global atomic
-#define SCAN_CTAS_PER_SM 4
+#define SCAN_CTAS_PER_SM 6
+#define SCAN_CHUNK 128        // staging slots reserved per global atomic
 
 #define VSV_MODE_FUSED 3      // internal: READS (stream A) + CUTE (stream B) in one pass
 
@@ -133,25 +132,32 @@ struct TileStateOp {
   }
 };
 
+// Staging entry of one raw candidate (32 bytes).  Written by the streaming kernel as
+// {j, ex.r, ex.q, ex.x1, ex.x2, ex.x3, -, -} (j = op index in the warp tile, ex = the lane's
+// exclusive prefix in the warp tile); rewritten in place by k_gate as
+// {rec, w, part.r, part.q, part.x1, part.x2, part.x3, flags} (part = sums since the record
+// start or since the tile start when the record began earlier; flags: 1 stream A, 2 stream
+// B, 4 carry pending).
+struct __align__(16) StageEntry {
+  uint32_t a, b, r, q, x1, x2, x3, f;
+};
+
 struct ScanParams {
   const uint32_t* ops;
   const int64_t* op_off;
   const int32_t* pos;
   const uint32_t* rec_info;  // hc << 2 | gate_b << 1 | gate_a
   int64_t n_rec, n_ops;
-  int32_t n_tiles;
+  int32_t n_wt;              // number of warp tiles
   uint32_t min_w;            // min candidate length << 4
   int32_t min_len_a, min_len_b;
-  const int2* tile_rec;      // first / last record touching each tile
-  TileState* tile_agg;       // per tile aggregate (kernel output)
-  uint2* tile_stage;         // staging base of the tile's signatures per stream
-  unsigned long long* stage_ctr;  // [2] staging allocation counters
-  vsv_sig* stage_a;
-  vsv_sig* stage_b;
-  uint32_t stage_cap_a, stage_cap_b;
-  uint32_t* ref_total;
-  uint32_t* qry_total;
-  uint32_t* aux_total;
+  const int2* wt_starts;     // [first,last] record (index in 0..n_rec) whose start lies in the tile
+  TileState* wt_agg;         // [n_wt + 1] aggregates (last = identity), counts filled by k_gate
+  uint2* wt_stage;           // staging base / raw candidate count of each tile
+  unsigned long long* stage_ctr;  // [0] staging allocation counter, [2] staging-full flag
+  StageEntry* stage;
+  uint32_t stage_cap;
+  uint4* fstart;             // [n_rec + 1][2] in-tile prefix at each record start
 };
 
 // ---- PTX wrappers: mbarrier + 1-D TMA bulk copy (sm_90+/sm_100a) ------------------
@@ -192,14 +198,28 @@ __device__ __forceinline__ int32_t rec_of_op(const int64_t* __restrict__ op_off,
   return lo;
 }
 
-__global__ void k_tile_records(const int64_t* __restrict__ op_off, int64_t n_rec, int64_t n_ops, int32_t n_tiles,
-                               int2* __restrict__ tile_rec) {
-  int32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= n_tiles) return;
-  int64_t x0 = (int64_t)t * SCAN_TILE;
-  int64_t x1 = min(x0 + SCAN_TILE, n_ops) - 1;
-  int32_t a = rec_of_op(op_off, 0, (int32_t)n_rec - 1, x0);
-  tile_rec[t] = make_int2(a, rec_of_op(op_off, a, (int32_t)n_rec - 1, x1));
+
+// ---- small pre-kernels ---------------------------------------------------------------
+// per warp tile: the records (indices in 0..n_rec, n_rec = end sentinel) whose START offset
+// lies inside the tile: first = lower_bound(op_off, tile_start), last = upper_bound(op_off,
+// tile_end - 1) - 1; first > last when no record starts here.
+__global__ void k_wt_starts(const int64_t* __restrict__ op_off, int64_t n_rec, int64_t n_ops, int32_t n_wt,
+                            int2* __restrict__ wt_starts) {
+  const int32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n_wt) return;
+  const int64_t x0 = (int64_t)t * WT_OPS, x1 = x0 + WT_OPS - 1;
+  int64_t lo = 0, hi = n_rec + 1;  // first index with op_off >= x0
+  while (lo < hi) {
+    const int64_t mid = (lo + hi) >> 1;
+    if (__ldg(op_off + mid) < x0) lo = mid + 1; else hi = mid;
+  }
+  const int32_t first = (int32_t)lo;
+  hi = n_rec + 1;                  // first index with op_off > x1
+  while (lo < hi) {
+    const int64_t mid = (lo + hi) >> 1;
+    if (__ldg(op_off + mid) <= x1) lo = mid + 1; else hi = mid;
+  }
+  wt_starts[t] = make_int2(first, (int32_t)lo - 1);
 }
 
 // per record: leading hard clip and the record gates of both streams
@@ -221,23 +241,6 @@ __global__ void k_rec_info(const uint32_t* __restrict__ ops, const int64_t* __re
   info[r] = (hc << 2) | gb | ga;
 }
 
-// ---- shared memory of the streaming kernel -------------------------------------------
-struct ScanSmem {
-  uint32_t ops[SCAN_STAGES][SCAN_TILE];   // TMA destinations (linear tiles)
-  uint32_t tx[5][SCAN_THREADS];           // warp-relative thread-exclusive prefixes (r,q,x1,x2,x3)
-  uint16_t cand[SCAN_WARPS][SCAN_WCAND];  // per-warp candidate op indices, in op order
-  int32_t t_off[2][SCAN_RT + 4];          // record table: op_off - tile_start, clamped to [-1, TILE+1]
-  int32_t t_pos[2][SCAN_RT];
-  uint32_t t_info[2][SCAN_RT];
-  uint32_t P[5][SCAN_RT + 4];             // prefix sums at the (clamped) start of every table record
-  uint32_t w[6][SCAN_WARPS];              // warp totals (r,q,x1,x2,x3,cand)
-  uint32_t wx[6][SCAN_WARPS];             // warp exclusive offsets
-  uint32_t tot[6];
-  uint32_t wrare[SCAN_WARPS];
-  uint32_t ovf;                           // a warp's candidate list overflowed in this tile
-  uint64_t bar[SCAN_STAGES];
-};
-
 template <int MODE>
 __device__ __forceinline__ void add_op(uint32_t w, Sums& s) {
   typedef ModeTraits<MODE> M;
@@ -249,160 +252,97 @@ __device__ __forceinline__ void add_op(uint32_t w, Sums& s) {
   if (M::NX > 2) s.x3 += (bit & M::X3) ? len : 0u;
 }
 
-// View of the records touching one tile: shared-memory table when it fits, else global.
-struct RecTab {
-  const ScanSmem* sm;
-  const ScanParams* p;
-  int64_t tile_start;
-  int32_t rf, nrt, slot;
-  bool fast;
-  __device__ __forceinline__ int32_t off(int k) const {  // start of record rf+k relative to the tile
-    if (fast) return sm->t_off[slot][k];
-    const int64_t d = __ldg(p->op_off + rf + k) - tile_start;
-    return (int32_t)max((int64_t)-1, min(d, (int64_t)SCAN_TILE + 1));
-  }
-  __device__ __forceinline__ int32_t pos(int k) const { return fast ? sm->t_pos[slot][k] : __ldg(p->pos + rf + k); }
-  __device__ __forceinline__ uint32_t info(int k) const {
-    return fast ? sm->t_info[slot][k] : __ldg(p->rec_info + rf + k);
-  }
-  __device__ __forceinline__ int lookup(int j) const {  // last k with off(k) <= j
-    int lo = 0, hi = nrt - 1;
-    while (lo < hi) {
-      const int mid = (lo + hi + 1) >> 1;
-      if (off(mid) <= j) lo = mid; else hi = mid - 1;
-    }
-    return lo;
-  }
-};
-
-// sums over tile ops [0, j)
+// sums over row[0, n)  (row = the 32 ops of one lane; shared or global memory)
 template <int MODE>
-__device__ __forceinline__ Sums prefix_at(const ScanSmem& sm, const uint32_t* tile, int j) {
+__device__ __forceinline__ Sums walk(const uint32_t* row, int n, bool with_rare) {
   typedef ModeTraits<MODE> M;
-  Sums s;
-  if (j >= SCAN_TILE) {
-    s.r = sm.tot[0]; s.q = sm.tot[1]; s.x1 = sm.tot[2]; s.x2 = sm.tot[3]; s.x3 = sm.tot[4];
-    return s;
-  }
-  const int t = j >> 4, n = j & 15, wp = t >> 5;
-  s.r = sm.wx[0][wp] + sm.tx[0][t];
-  s.q = sm.wx[1][wp] + sm.tx[1][t];
-  s.x1 = sm.wx[2][wp]; s.x2 = sm.wx[3][wp]; s.x3 = sm.wx[4][wp];
-  const uint32_t* row = tile + t * SCAN_VPT;
-  if (sm.wrare[wp]) {  // this warp saw N / H / P ...: full walk
-    s.x1 += sm.tx[2][t]; s.x2 += sm.tx[3][t]; s.x3 += sm.tx[4][t];
+  Sums s = {0, 0, 0, 0, 0};
+  if (with_rare) {
     for (int i = 0; i < n; ++i) add_op<MODE>(row[i], s);
   } else {
-    uint32_t r = 0, q = 0;
-    const uint4* row4 = reinterpret_cast<const uint4*>(row);
-    const uint4 v0 = row4[0], v1 = row4[1], v2 = row4[2], v3 = row4[3];
-    const uint32_t ww[16] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w, v2.x, v2.y, v2.z, v2.w, v3.x, v3.y, v3.z, v3.w};
-#pragma unroll
-    for (int i = 0; i < 15; ++i) {
-      const uint32_t w = ww[i], bit = (i < n) ? (1u << (w & 15u)) : 0u, len = w >> 4;
-      r += (bit & M::REF) ? len : 0u;
-      q += (bit & M::QRY) ? len : 0u;
+    for (int i = 0; i < n; ++i) {
+      const uint32_t w = row[i], bit = 1u << (w & 15u), len = w >> 4;
+      s.r += (bit & M::REF) ? len : 0u;
+      s.q += (bit & M::QRY) ? len : 0u;
     }
-    s.r += r; s.q += q;
   }
   return s;
 }
 
-template <int MODE, int STREAM>
-__device__ __forceinline__ void write_sig(vsv_sig* dst, int32_t rec, uint32_t w, int32_t rpos, uint32_t hc,
-                                          const Sums& part, bool carry) {
-  const int32_t len = (int32_t)(w >> 4);
-  const int32_t type = ((w & 15u) == 1u) ? VSV_INS : VSV_DEL;
-  const int32_t q0 = (int32_t)qry_of<MODE, STREAM>(part) + hsign<MODE, STREAM>() * (int32_t)hc;
-  int4* o = reinterpret_cast<int4*>(dst);
-  o[0] = make_int4(rec, type, rpos + (int32_t)ref_of<MODE, STREAM>(part), len);
-  o[1] = make_int4(q0, q0 + (type == VSV_INS ? len : 1), 0, carry ? 0 : 1);  // count==0: carry pending
+__device__ __forceinline__ void store_sums(uint4* dst, const Sums& s) {
+  dst[0] = make_uint4(s.r, s.q, s.x1, s.x2);
+  dst[1] = make_uint4(s.x3, 0u, 0u, 0u);
+}
+__device__ __forceinline__ Sums load_sums(const uint4* src) {
+  const uint4 a = __ldg(src), b = __ldg(src + 1);
+  return Sums{a.x, a.y, a.z, a.w, b.x};
 }
 
-// ---- K1: the streaming kernel ---------------------------------------------------------
+// ---- K1: the streaming kernel (every warp is an independent worker) --------------------
 template <int MODE>
-__global__ void __launch_bounds__(SCAN_THREADS, SCAN_CTAS_PER_SM) k_scan_tiles(const ScanParams p) {
+__global__ void __launch_bounds__(SCAN_THREADS, SCAN_CTAS_PER_SM) k_scan_wt(const ScanParams p) {
   typedef ModeTraits<MODE> M;
   constexpr uint32_t RARE = M::X1 | M::X2 | M::X3;
-  extern __shared__ __align__(128) unsigned char smem_raw[];
-  ScanSmem& sm = *reinterpret_cast<ScanSmem*>(smem_raw);
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int G = gridDim.x;
-  const int32_t n_tiles = p.n_tiles;
-  const int32_t n_full = (int32_t)(p.n_ops / SCAN_TILE);  // tiles below n_full are complete
+  constexpr uint32_t FULL = 0xffffffffu;
+  __shared__ __align__(128) uint32_t s_ops[SCAN_WARPS][SCAN_STAGES][WT_OPS];
+  __shared__ __align__(8) uint64_t s_bar[SCAN_WARPS][SCAN_STAGES];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t TW = (int64_t)gridDim.x * SCAN_WARPS;
+  const int64_t gw = (int64_t)blockIdx.x * SCAN_WARPS + warp;
+  const int64_t n_wt = p.n_wt;
+  const int64_t n_full = p.n_ops / WT_OPS;  // tiles below n_full are complete
 
-  if (tid == 0) {
-    sm.ovf = 0u;
-    for (int s = 0; s < SCAN_STAGES; ++s) mbar_init(&sm.bar[s], 1);
+  if (lane == 0) {
+    for (int s = 0; s < SCAN_STAGES; ++s) mbar_init(&s_bar[warp][s], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     fence_proxy_async();
   }
-  __syncthreads();
-  if (tid == 0) {
+  __syncwarp();
+  if (lane == 0) {
     for (int s = 0; s < SCAN_STAGES; ++s) {
-      const int64_t t = (int64_t)blockIdx.x + (int64_t)s * G;
+      const int64_t t = gw + (int64_t)s * TW;
       if (t < n_full) {
-        mbar_expect_tx(&sm.bar[s], SCAN_TILE * 4);
-        tma_load_1d(sm.ops[s], p.ops + t * SCAN_TILE, SCAN_TILE * 4, &sm.bar[s]);
+        mbar_expect_tx(&s_bar[warp][s], WT_OPS * 4);
+        tma_load_1d(s_ops[warp][s], p.ops + t * WT_OPS, WT_OPS * 4, &s_bar[warp][s]);
       }
     }
   }
-  // record-table registers: desc of the current / next tile, prefetched one iteration ahead
   int2 cur = make_int2(0, -1), nxt = make_int2(0, -1);
-  if ((int32_t)blockIdx.x < n_tiles) cur = __ldg(p.tile_rec + blockIdx.x);
-  if ((int64_t)blockIdx.x + G < n_tiles) nxt = __ldg(p.tile_rec + blockIdx.x + G);
-  {  // first tile's table, synchronously
-    const int nrt = cur.y - cur.x + 1;
-    if (nrt <= SCAN_RT && tid <= nrt) {
-      const int64_t d = __ldg(p.op_off + cur.x + tid) - (int64_t)blockIdx.x * SCAN_TILE;
-      sm.t_off[0][tid] = (int32_t)max((int64_t)-1, min(d, (int64_t)SCAN_TILE + 1));
-      if (tid < nrt) { sm.t_pos[0][tid] = __ldg(p.pos + cur.x + tid); sm.t_info[0][tid] = __ldg(p.rec_info + cur.x + tid); }
-    }
-  }
-  __syncthreads();
-
-  // staging chunks of this CTA (live in warp 0 / lane 0 registers)
-  unsigned long long ch_next[2] = {0, 0}, ch_end[2] = {0, 0};
+  if (gw < n_wt) cur = __ldg(p.wt_starts + gw);
+  if (gw + TW < n_wt) nxt = __ldg(p.wt_starts + gw + TW);
+  unsigned long long ch_next = 0, ch_end = 0;  // this warp's staging chunk (lane 0)
 
   int it = 0;
-  for (int64_t tile64 = blockIdx.x; tile64 < n_tiles; tile64 += G, ++it) {
-    const int32_t tile = (int32_t)tile64;
-    const int stage = it % SCAN_STAGES, slot = it & 1;
+  for (int64_t wt = gw; wt < n_wt; wt += TW, ++it) {
+    const int stage = it % SCAN_STAGES;
     const uint32_t parity = (uint32_t)(it / SCAN_STAGES) & 1u;
-    const int64_t tile_start = (int64_t)tile * SCAN_TILE;
-    uint32_t* tl = sm.ops[stage];
+    const int64_t wt_start = wt * WT_OPS;
+    uint32_t* tl = s_ops[warp][stage];
 
-    // -- prefetch the next tile's record table into registers (stored at the bottom) ----
-    const int nrt_next = nxt.y - nxt.x + 1;
-    int32_t pf_off = 0, pf_pos = 0;
-    uint32_t pf_info = 0;
-    const bool pf_on = tid <= nrt_next && nrt_next <= SCAN_RT && (tile64 + G < n_tiles);
-    if (pf_on) {
-      const int64_t d = __ldg(p.op_off + nxt.x + tid) - (tile_start + (int64_t)G * SCAN_TILE);
-      pf_off = (int32_t)max((int64_t)-1, min(d, (int64_t)SCAN_TILE + 1));
-      if (tid < nrt_next) { pf_pos = __ldg(p.pos + nxt.x + tid); pf_info = __ldg(p.rec_info + nxt.x + tid); }
-    }
+    // record starts inside this tile: issue the offset loads before waiting for the ops
+    const int nst = cur.y - cur.x + 1;
+    int32_t sx = 0;
+    if (lane < nst) sx = (int32_t)(__ldg(p.op_off + cur.x + lane) - wt_start);
     int2 nn = make_int2(0, -1);
-    if (tile64 + 2 * (int64_t)G < n_tiles) nn = __ldg(p.tile_rec + tile64 + 2 * (int64_t)G);
+    if (wt + 2 * TW < n_wt) nn = __ldg(p.wt_starts + wt + 2 * TW);
 
-    // -- the tile's ops: TMA (full tiles) or a guarded copy (the one partial tile) ------
-    if (tile < n_full) {
-      mbar_wait(&sm.bar[stage], parity);
-    } else {
-      const int64_t rem = p.n_ops - tile_start;
-      for (int i = tid; i < SCAN_TILE; i += SCAN_THREADS) tl[i] = (i < rem) ? __ldg(p.ops + tile_start + i) : 0u;
-      __syncthreads();
+    if (wt < n_full) {
+      mbar_wait(&s_bar[warp][stage], parity);
+    } else {  // the one partial tile: guarded copy, zero filled (op 0 = "0M": contributes nothing)
+      const int64_t rem = p.n_ops - wt_start;
+      for (int i = lane; i < WT_OPS; i += 32) tl[i] = (i < rem) ? __ldg(p.ops + wt_start + i) : 0u;
+      __syncwarp();
     }
 
-    // -- fast path: 16 consecutive ops per thread, rotated so LDS.128 is conflict free ---
+    // -- fast path: 32 consecutive ops per lane, rotated so LDS.128 is conflict free -------
     uint32_t r = 0, q = 0, bits = 0, em = 0;
     {
-      const int rot = (tid >> 1) & 3;
-      const uint4* row = reinterpret_cast<const uint4*>(tl + tid * SCAN_VPT);
+      const int rot = lane & 7;
+      const uint4* row = reinterpret_cast<const uint4*>(tl + lane * WT_VPT);
       const uint32_t min_w = p.min_w;
 #pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        const uint4 v = row[(k + rot) & 3];
+      for (int k = 0; k < 8; ++k) {
+        const uint4 v = row[(k + rot) & 7];
         const uint32_t ww[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
@@ -414,225 +354,109 @@ __global__ void __launch_bounds__(SCAN_THREADS, SCAN_CTAS_PER_SM) k_scan_tiles(c
           em |= ((bit & 6u) && w >= min_w) ? (1u << (k * 4 + i)) : 0u;
         }
       }
-      // un-rotate the candidate mask: chunk k of the loop is logical chunk (k+rot)&3
-      em = ((em << (4 * rot)) | (em >> (16 - 4 * rot))) & 0xFFFFu;
+      em = __funnelshift_l(em, em, 4 * rot);  // loop chunk k is logical chunk (k+rot)&7
     }
     const uint32_t c = __popc(em);
 
-    // -- warp scans (inclusive); warp-relative exclusive prefixes go to shared memory ----
+    // -- warp scans (inclusive) ---------------------------------------------------------------
     uint32_t ir = r, iq = q, ic = c;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
-      const uint32_t a = __shfl_up_sync(0xffffffffu, ir, d);
-      const uint32_t b = __shfl_up_sync(0xffffffffu, iq, d);
-      const uint32_t e = __shfl_up_sync(0xffffffffu, ic, d);
+      const uint32_t a = __shfl_up_sync(FULL, ir, d);
+      const uint32_t b = __shfl_up_sync(FULL, iq, d);
+      const uint32_t e = __shfl_up_sync(FULL, ic, d);
       if (lane >= d) { ir += a; iq += b; ic += e; }
     }
-    sm.tx[0][tid] = ir - r;
-    sm.tx[1][tid] = iq - q;
-    const bool anyrare = __any_sync(0xffffffffu, (bits & RARE) != 0u);
-    uint32_t ix1 = 0, ix2 = 0, ix3 = 0;
+    Sums ex = {ir - r, iq - q, 0, 0, 0};  // this lane's exclusive prefix inside the tile
+    Sums tot = {__shfl_sync(FULL, ir, 31), __shfl_sync(FULL, iq, 31), 0, 0, 0};
+    const bool anyrare = __any_sync(FULL, (bits & RARE) != 0u);
     if (anyrare) {  // slow path: this warp saw N / H / P / ...
       Sums xs = {0, 0, 0, 0, 0};
       if (bits & RARE)
-        for (int i = 0; i < SCAN_VPT; ++i) add_op<MODE>(tl[tid * SCAN_VPT + i], xs);
-      ix1 = xs.x1; ix2 = xs.x2; ix3 = xs.x3;
+        for (int i = 0; i < WT_VPT; ++i) add_op<MODE>(tl[lane * WT_VPT + i], xs);
+      uint32_t i1 = xs.x1, i2 = xs.x2, i3 = xs.x3;
 #pragma unroll
       for (int d = 1; d < 32; d <<= 1) {
-        const uint32_t a = __shfl_up_sync(0xffffffffu, ix1, d);
-        const uint32_t b = __shfl_up_sync(0xffffffffu, ix2, d);
-        const uint32_t e = __shfl_up_sync(0xffffffffu, ix3, d);
-        if (lane >= d) { ix1 += a; ix2 += b; ix3 += e; }
+        const uint32_t a = __shfl_up_sync(FULL, i1, d);
+        const uint32_t b = __shfl_up_sync(FULL, i2, d);
+        const uint32_t e = __shfl_up_sync(FULL, i3, d);
+        if (lane >= d) { i1 += a; i2 += b; i3 += e; }
       }
-      sm.tx[2][tid] = ix1 - xs.x1; sm.tx[3][tid] = ix2 - xs.x2; sm.tx[4][tid] = ix3 - xs.x3;
+      ex.x1 = i1 - xs.x1; ex.x2 = i2 - xs.x2; ex.x3 = i3 - xs.x3;
+      tot.x1 = __shfl_sync(FULL, i1, 31); tot.x2 = __shfl_sync(FULL, i2, 31); tot.x3 = __shfl_sync(FULL, i3, 31);
     }
-    if (lane == 31) {
-      sm.w[0][warp] = ir; sm.w[1][warp] = iq; sm.w[2][warp] = ix1; sm.w[3][warp] = ix2; sm.w[4][warp] = ix3;
-      sm.w[5][warp] = ic;
-      sm.wrare[warp] = anyrare ? 1u : 0u;
-    }
-    if (em) {  // push this thread's candidates, op order, warp-relative slot
-      uint32_t idx = ic - c, m = em;
-      while (m) {
-        const int s = __ffs(m) - 1;
-        m &= m - 1;
-        if (idx < SCAN_WCAND) sm.cand[warp][idx] = (uint16_t)(tid * SCAN_VPT + s);
-        else sm.ovf = 1u;
-        ++idx;
-      }
-    }
-    __syncthreads();  // B1: warp totals, candidate lists, tx visible
 
-    if (warp == 0) {  // second level: exclusive offsets of the 8 warps
-      uint32_t v[6], own[6];
-#pragma unroll
-      for (int k = 0; k < 6; ++k) { own[k] = lane < SCAN_WARPS ? sm.w[k][lane] : 0u; v[k] = own[k]; }
-#pragma unroll
-      for (int d = 1; d < SCAN_WARPS; d <<= 1) {
-#pragma unroll
-        for (int k = 0; k < 6; ++k) {
-          const uint32_t a = __shfl_up_sync(0xffffffffu, v[k], d);
-          if (lane >= d) v[k] += a;
-        }
+    // -- record starts in this tile: in-tile prefix at each start -> fstart[rec] -------------
+    Sums f_last = {0, 0, 0, 0, 0};
+    for (int k0 = 0; k0 < nst; k0 += 32) {
+      const int k = k0 + lane;
+      const bool on = k < nst;
+      int32_t x = sx;
+      if (k0 > 0) x = on ? (int32_t)(__ldg(p.op_off + cur.x + k) - wt_start) : 0;
+      if (!on) x = 0;
+      const int t = x >> 5, n = x & 31;
+      Sums f;
+      f.r = __shfl_sync(FULL, ex.r, t); f.q = __shfl_sync(FULL, ex.q, t);
+      f.x1 = __shfl_sync(FULL, ex.x1, t); f.x2 = __shfl_sync(FULL, ex.x2, t); f.x3 = __shfl_sync(FULL, ex.x3, t);
+      if (on) {
+        const Sums wk = walk<MODE>(tl + t * WT_VPT, n, anyrare);
+        f.r += wk.r; f.q += wk.q; f.x1 += wk.x1; f.x2 += wk.x2; f.x3 += wk.x3;
+        store_sums(p.fstart + 2 * ((int64_t)cur.x + k), f);
       }
-      if (lane < SCAN_WARPS) {
-#pragma unroll
-        for (int k = 0; k < 6; ++k) sm.wx[k][lane] = v[k] - own[k];
-      }
-      if (lane == SCAN_WARPS - 1) {
-#pragma unroll
-        for (int k = 0; k < 6; ++k) sm.tot[k] = v[k];
+      if (k0 + 32 >= nst) {  // last group: the last start's prefix goes to the aggregate
+        const int ll = (nst - 1) & 31;
+        f_last.r = __shfl_sync(FULL, f.r, ll); f_last.q = __shfl_sync(FULL, f.q, ll);
+        f_last.x1 = __shfl_sync(FULL, f.x1, ll); f_last.x2 = __shfl_sync(FULL, f.x2, ll);
+        f_last.x3 = __shfl_sync(FULL, f.x3, ll);
       }
     }
-    RecTab rt;
-    rt.sm = &sm; rt.p = &p; rt.tile_start = tile_start; rt.rf = cur.x; rt.nrt = cur.y - cur.x + 1; rt.slot = slot;
-    rt.fast = rt.nrt <= SCAN_RT;
-    // B2 (block prefixes complete) is only needed when warps 1..7 take part in what follows
-    if (!rt.fast) __syncthreads(); else __syncwarp();
 
-    if (warp == 0) {
-      // -- prefix sums at every record start (lanes = records), then the per-record totals --
-      if (rt.fast) {
-        for (int k = lane; k <= rt.nrt; k += 32) {
-          const Sums ps = prefix_at<MODE>(sm, tl, min(max(rt.off(k), 0), SCAN_TILE));
-          sm.P[0][k] = ps.r; sm.P[1][k] = ps.q; sm.P[2][k] = ps.x1; sm.P[3][k] = ps.x2; sm.P[4][k] = ps.x3;
+    // -- raw candidates -> staging entries (op order), chunked slot reservation ---------------
+    const uint32_t ncand = __shfl_sync(FULL, ic, 31);
+    unsigned long long base = ~0ull;
+    if (ncand) {
+      if (lane == 0) {
+        if (ch_next + ncand > ch_end) {
+          const unsigned long long n = ncand > SCAN_CHUNK ? ncand : SCAN_CHUNK;
+          ch_next = atomicAdd(p.stage_ctr, n);
+          ch_end = ch_next + n;
         }
-        __syncwarp();
-        if (p.ref_total != nullptr) {
-          for (int k = lane; k < rt.nrt; k += 32) {
-            const Sums d = {sm.P[0][k + 1] - sm.P[0][k], sm.P[1][k + 1] - sm.P[1][k], sm.P[2][k + 1] - sm.P[2][k],
-                            sm.P[3][k + 1] - sm.P[3][k], sm.P[4][k + 1] - sm.P[4][k]};
-            const uint32_t tr = ref_of<MODE, 0>(d), tq = qry_of<MODE, 0>(d), tx = aux_of<MODE>(d);
-            const int64_t rr = (int64_t)rt.rf + k;
-            if (rt.off(k) >= 0 && rt.off(k + 1) <= SCAN_TILE) {
-              p.ref_total[rr] = tr; p.qry_total[rr] = tq; p.aux_total[rr] = tx;
-            } else {
-              atomicAdd(p.ref_total + rr, tr); atomicAdd(p.qry_total + rr, tq); atomicAdd(p.aux_total + rr, tx);
-            }
-          }
+        base = ch_next;
+        ch_next += ncand;
+        if (base + ncand > p.stage_cap) {  // staging full: the host retries with a larger one
+          base = ~0ull;
+          p.stage_ctr[2] = 1ull;
         }
       }
-      // -- dense candidate phase (one pass): staging slots are reserved for the RAW candidate
-      //    count (an upper bound of what passes the record gates), then each group of 32
-      //    candidates is looked up, gated and written in op order.
-      const uint32_t ncand = sm.tot[5];
-      const bool ovf = sm.ovf != 0u;
-      uint32_t cnt_a = 0, cnt_b = 0;
-      unsigned long long base_a = ~0ull, base_b = ~0ull;
-      if (ncand) {
-        if (lane == 0) {  // chunked reservation: one global atomic per ~SCAN_CHUNK signatures
-#pragma unroll
-          for (int s = 0; s < (MODE == VSV_MODE_FUSED ? 2 : 1); ++s) {
-            if (ch_next[s] + ncand > ch_end[s]) {
-              const unsigned long long n = ncand > SCAN_CHUNK ? ncand : SCAN_CHUNK;
-              ch_next[s] = atomicAdd(p.stage_ctr + s, n);
-              ch_end[s] = ch_next[s] + n;
-            }
-            unsigned long long b0 = ch_next[s];
-            ch_next[s] += ncand;
-            if (b0 + ncand > (s == 0 ? p.stage_cap_a : p.stage_cap_b)) {  // staging full: host retries
-              b0 = ~0ull;
-              p.stage_ctr[2] = 1ull;
-            }
-            if (s == 0) base_a = b0; else base_b = b0;
-          }
-        }
-        base_a = __shfl_sync(0xffffffffu, base_a, 0);
-        base_b = __shfl_sync(0xffffffffu, base_b, 0);
-        const uint32_t ngroups = ovf ? SCAN_TILE / 32 : (ncand + 31) / 32;
-        for (uint32_t g = 0; g < ngroups; ++g) {
-          bool valid;
-          int j;
-          if (!ovf) {
-            const uint32_t i = g * 32 + lane;
-            valid = i < ncand;
-            int wp = 0;
-#pragma unroll
-            for (int u = 1; u < SCAN_WARPS; ++u) wp += (sm.wx[5][u] <= i) ? 1 : 0;
-            j = valid ? sm.cand[wp][i - sm.wx[5][wp]] : 0;
-          } else {  // a list overflowed: enumerate the candidates straight from the tile
-            j = g * 32 + lane;
-            const uint32_t w0 = tl[j];
-            valid = ((1u << (w0 & 15u)) & 6u) && w0 >= p.min_w;
-          }
-          bool ok_a = false, ok_b = false;
-          int k = 0;
-          uint32_t w = 0, info = 0;
-          if (valid) {
-            w = tl[j];
-            k = rt.lookup(j);
-            info = rt.info(k);
-            const int32_t len = (int32_t)(w >> 4);
-            ok_a = (info & 1u) && len >= p.min_len_a;
-            if (MODE == VSV_MODE_FUSED) ok_b = (info & 2u) && len >= p.min_len_b;
-          }
-          const uint32_t ba = __ballot_sync(0xffffffffu, ok_a);
-          const uint32_t bb = (MODE == VSV_MODE_FUSED) ? __ballot_sync(0xffffffffu, ok_b) : 0u;
-          if (ok_a || ok_b) {
-            const Sums pre = prefix_at<MODE>(sm, tl, j);
-            const int32_t o = rt.off(k);
-            const bool carry = o < 0;
-            Sums part = pre;
-            if (!carry) {
-              if (rt.fast) part = pre - Sums{sm.P[0][k], sm.P[1][k], sm.P[2][k], sm.P[3][k], sm.P[4][k]};
-              else part = pre - prefix_at<MODE>(sm, tl, o);
-            }
-            const uint32_t lt = (1u << lane) - 1u;
-            if (ok_a && base_a != ~0ull)
-              write_sig<MODE, 0>(p.stage_a + base_a + cnt_a + __popc(ba & lt), rt.rf + k, w, rt.pos(k), info >> 2, part,
-                                 carry);
-            if (MODE == VSV_MODE_FUSED && ok_b && base_b != ~0ull)
-              write_sig<MODE, 1>(p.stage_b + base_b + cnt_b + __popc(bb & lt), rt.rf + k, w, rt.pos(k), info >> 2, part,
-                                 carry);
-          }
-          cnt_a += __popc(ba);
-          cnt_b += __popc(bb);
-        }
-      }
-      if (lane == 0) {  // tile aggregate: sums since the last record start inside the tile
-        Sums a = {sm.tot[0], sm.tot[1], sm.tot[2], sm.tot[3], sm.tot[4]};
-        const int32_t o = rt.off(rt.nrt - 1);
-        const bool bound = o >= 0;
-        if (bound) {
-          const int kl = rt.nrt - 1;
-          if (rt.fast) a = a - Sums{sm.P[0][kl], sm.P[1][kl], sm.P[2][kl], sm.P[3][kl], sm.P[4][kl]};
-          else a = a - prefix_at<MODE>(sm, tl, o);
-        }
-        TileState ts;
-        ts.r = a.r; ts.q = a.q; ts.x1 = a.x1; ts.x2 = a.x2; ts.x3 = a.x3;
-        ts.cnt_a = cnt_a; ts.cnt_b = cnt_b; ts.flag = bound ? 1u : 0u;
-        p.tile_agg[tile] = ts;
-        p.tile_stage[tile] = make_uint2(base_a == ~0ull ? 0xFFFFFFFFu : (uint32_t)base_a,
-                                        base_b == ~0ull ? 0xFFFFFFFFu : (uint32_t)base_b);
-        sm.ovf = 0u;  // for the next tile (pushers write it only after B3)
-      }
-    } else if (!rt.fast && p.ref_total != nullptr) {
-      // -- warps 1..7, only for tiles with more than SCAN_RT records: per-record totals ----
-      for (int k = tid - 32; k < rt.nrt; k += SCAN_THREADS - 32) {
-        const int32_t a = rt.off(k), b = rt.off(k + 1);
-        const Sums d = prefix_at<MODE>(sm, tl, min(b, SCAN_TILE)) - prefix_at<MODE>(sm, tl, max(a, 0));
-        Sums rd = d;  // per-record totals follow stream A's semantics
-        const uint32_t tr = ref_of<MODE, 0>(rd), tq = qry_of<MODE, 0>(rd), tx = aux_of<MODE>(rd);
-        const int64_t rr = (int64_t)rt.rf + k;
-        if (a >= 0 && b <= SCAN_TILE) {
-          p.ref_total[rr] = tr; p.qry_total[rr] = tq; p.aux_total[rr] = tx;
-        } else {
-          atomicAdd(p.ref_total + rr, tr); atomicAdd(p.qry_total + rr, tq); atomicAdd(p.aux_total + rr, tx);
+      base = __shfl_sync(FULL, base, 0);
+      if (em && base != ~0ull) {
+        uint4* dst = reinterpret_cast<uint4*>(p.stage + base + (ic - c));
+        uint32_t m = em;
+        while (m) {
+          const int s = __ffs(m) - 1;
+          m &= m - 1;
+          dst[0] = make_uint4((uint32_t)(lane * WT_VPT + s), 0u, ex.r, ex.q);
+          dst[1] = make_uint4(ex.x1, ex.x2, ex.x3, 0u);
+          dst += 2;
         }
       }
     }
-    // -- store the prefetched record table of the next tile -------------------------------
-    if (pf_on) {
-      sm.t_off[slot ^ 1][tid] = pf_off;
-      if (tid < nrt_next) { sm.t_pos[slot ^ 1][tid] = pf_pos; sm.t_info[slot ^ 1][tid] = pf_info; }
+    if (lane == 0) {
+      Sums a = tot;
+      if (nst > 0) a = a - f_last;
+      TileState ts;
+      ts.r = a.r; ts.q = a.q; ts.x1 = a.x1; ts.x2 = a.x2; ts.x3 = a.x3;
+      ts.cnt_a = 0; ts.cnt_b = 0; ts.flag = nst > 0 ? 1u : 0u;
+      p.wt_agg[wt] = ts;
+      p.wt_stage[wt] = make_uint2(base == ~0ull ? 0xFFFFFFFFu : (uint32_t)base, ncand);
     }
-    __syncthreads();  // B3: everyone is done with this stage and this table slot
-    if (tid == 0) {
-      const int64_t t2 = tile64 + (int64_t)SCAN_STAGES * G;
+    __syncwarp();  // every lane is done with this stage
+    if (lane == 0) {
+      const int64_t t2 = wt + (int64_t)SCAN_STAGES * TW;
       if (t2 < n_full) {
         fence_proxy_async();
-        mbar_expect_tx(&sm.bar[stage], SCAN_TILE * 4);
-        tma_load_1d(sm.ops[stage], p.ops + t2 * SCAN_TILE, SCAN_TILE * 4, &sm.bar[stage]);
+        mbar_expect_tx(&s_bar[warp][stage], WT_OPS * 4);
+        tma_load_1d(s_ops[warp][stage], p.ops + t2 * WT_OPS, WT_OPS * 4, &s_bar[warp][stage]);
       }
     }
     cur = nxt;
@@ -640,43 +464,122 @@ __global__ void __launch_bounds__(SCAN_THREADS, SCAN_CTAS_PER_SM) k_scan_tiles(c
   }
 }
 
-// ---- fix-up: staged signatures -> final ordered slots (+ carry of an open record) -----
+// ---- sparse follow-up kernels (lane-dense: one thread per warp tile / per record) --------
+// k_gate: for each raw candidate of a tile: record lookup, gates, exact sums since the record
+// start (or since the tile start when the record began earlier); counts per stream.
+template <int MODE>
+__global__ void __launch_bounds__(128) k_gate(const ScanParams p) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= p.n_wt) return;
+  const uint2 st = p.wt_stage[t];
+  uint32_t cnt_a = 0, cnt_b = 0;
+  if (st.y != 0u && st.x != 0xFFFFFFFFu) {
+    const int64_t wt_start = t * WT_OPS;
+    const int2 ss = __ldg(p.wt_starts + t);
+    const int32_t lo = max(ss.x - 1, 0);
+    const int32_t hi = max(lo, min(ss.y, (int32_t)p.n_rec - 1));
+    StageEntry* e = p.stage + st.x;
+    for (uint32_t i = 0; i < st.y; ++i) {
+      const uint4 e0 = reinterpret_cast<const uint4*>(e + i)[0], e1 = reinterpret_cast<const uint4*>(e + i)[1];
+      const int j = (int)e0.x;
+      const uint32_t* row = p.ops + wt_start + (j & ~31);
+      const int n = j & 31;
+      Sums f = {e0.z, e0.w, e1.x, e1.y, e1.z};
+      {
+        Sums wk = {0, 0, 0, 0, 0};
+        for (int u = 0; u < n; ++u) add_op<MODE>(__ldg(row + u), wk);
+        f.r += wk.r; f.q += wk.q; f.x1 += wk.x1; f.x2 += wk.x2; f.x3 += wk.x3;
+      }
+      const uint32_t w = __ldg(row + n);
+      const int32_t rec = rec_of_op(p.op_off, lo, hi, wt_start + j);
+      const bool carry = __ldg(p.op_off + rec) < wt_start;
+      const Sums part = carry ? f : f - load_sums(p.fstart + 2 * (int64_t)rec);
+      const uint32_t info = __ldg(p.rec_info + rec);
+      const int32_t len = (int32_t)(w >> 4);
+      const bool ok_a = (info & 1u) && len >= p.min_len_a;
+      const bool ok_b = (MODE == VSV_MODE_FUSED) && (info & 2u) && len >= p.min_len_b;
+      cnt_a += ok_a ? 1u : 0u;
+      cnt_b += ok_b ? 1u : 0u;
+      uint4* o = reinterpret_cast<uint4*>(e + i);
+      o[0] = make_uint4((uint32_t)rec, w, part.r, part.q);
+      o[1] = make_uint4(part.x1, part.x2, part.x3, (ok_a ? 1u : 0u) | (ok_b ? 2u : 0u) | (carry ? 4u : 0u));
+    }
+  }
+  p.wt_agg[t].cnt_a = cnt_a;
+  p.wt_agg[t].cnt_b = cnt_b;
+}
+
 template <int MODE, int STREAM>
-__device__ __forceinline__ void fix_stream(const vsv_sig* __restrict__ stage, uint32_t base, uint32_t cnt,
-                                           uint64_t dst0, const Sums& carry, vsv_sig* __restrict__ out, int64_t cap,
-                                           int lane) {
-  if (base == 0xFFFFFFFFu) return;  // staging overflowed: the call reports VSV_E_CAPACITY
-  const int32_t cr = (int32_t)ref_of<MODE, STREAM>(carry), cq = (int32_t)qry_of<MODE, STREAM>(carry);
-  for (uint32_t i = lane; i < cnt; i += 32) {
-    if ((int64_t)(dst0 + i) >= cap) break;
-    const int4* s = reinterpret_cast<const int4*>(stage + base + i);
-    int4 a = s[0], b = s[1];
-    if (b.w == 0) { a.z += cr; b.x += cq; b.y += cq; b.w = 1; }
-    int4* o = reinterpret_cast<int4*>(out + dst0 + i);
-    o[0] = a;
-    o[1] = b;
+__device__ __forceinline__ void emit_sig(const ScanParams& p, vsv_sig* dst, uint32_t rec, uint32_t w, const Sums& s) {
+  const int32_t len = (int32_t)(w >> 4);
+  const int32_t type = ((w & 15u) == 1u) ? VSV_INS : VSV_DEL;
+  const int32_t hc = (int32_t)(__ldg(p.rec_info + rec) >> 2);
+  const int32_t q0 = (int32_t)qry_of<MODE, STREAM>(s) + hsign<MODE, STREAM>() * hc;
+  int4* o = reinterpret_cast<int4*>(dst);
+  o[0] = make_int4((int32_t)rec, type, __ldg(p.pos + rec) + (int32_t)ref_of<MODE, STREAM>(s), len);
+  o[1] = make_int4(q0, q0 + (type == VSV_INS ? len : 1), 0, 1);
+}
+
+// k_emit: final ordered slots (exclusive scan of the counts) + carry of an open record.
+template <int MODE>
+__global__ void __launch_bounds__(128) k_emit(const ScanParams p, const TileState* __restrict__ excl,
+                                              vsv_sig* __restrict__ out_a, int64_t cap_a, vsv_sig* __restrict__ out_b,
+                                              int64_t cap_b, int64_t* __restrict__ n_out) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t == 0) {  // exclusive scan at the identity sentinel == totals
+    n_out[0] = excl[p.n_wt].cnt_a;
+    n_out[1] = excl[p.n_wt].cnt_b;
+  }
+  if (t >= p.n_wt) return;
+  const uint2 st = p.wt_stage[t];
+  if (st.y == 0u || st.x == 0xFFFFFFFFu) return;
+  const TileState E = excl[t];
+  int64_t ia = E.cnt_a, ib = E.cnt_b;
+  const StageEntry* e = p.stage + st.x;
+  for (uint32_t i = 0; i < st.y; ++i) {
+    const uint4 e1 = reinterpret_cast<const uint4*>(e + i)[1];
+    if ((e1.w & 3u) == 0u) continue;
+    const uint4 e0 = reinterpret_cast<const uint4*>(e + i)[0];
+    Sums s = {e0.z, e0.w, e1.x, e1.y, e1.z};
+    if (e1.w & 4u) { s.r += E.r; s.q += E.q; s.x1 += E.x1; s.x2 += E.x2; s.x3 += E.x3; }
+    if (e1.w & 1u) {
+      if (ia < cap_a) emit_sig<MODE, 0>(p, out_a + ia, e0.x, e0.y, s);
+      ++ia;
+    }
+    if (MODE == VSV_MODE_FUSED && (e1.w & 2u)) {
+      if (ib < cap_b) emit_sig<MODE, 1>(p, out_b + ib, e0.x, e0.y, s);
+      ++ib;
+    }
   }
 }
 
+// k_rec_totals: per-record sums of op lengths (reference_end, read length) from the
+// in-tile prefixes at record starts and the scanned tile carries.
 template <int MODE>
-__global__ void __launch_bounds__(256) k_scan_fixup(const TileState* __restrict__ agg, const TileState* __restrict__ excl,
-                                                   const uint2* __restrict__ tile_stage, int32_t n_tiles,
-                                                   const vsv_sig* __restrict__ stage_a, const vsv_sig* __restrict__ stage_b,
-                                                   vsv_sig* __restrict__ out_a, int64_t cap_a, vsv_sig* __restrict__ out_b,
-                                                   int64_t cap_b, int64_t* __restrict__ n_out) {
-  const int lane = threadIdx.x & 31;
-  const int64_t t = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  if (t >= n_tiles) return;
-  const TileState a = agg[t], e = excl[t];
-  if (t == n_tiles - 1 && lane == 0) {
-    n_out[0] = (int64_t)e.cnt_a + a.cnt_a;
-    n_out[1] = (int64_t)e.cnt_b + a.cnt_b;
+__global__ void __launch_bounds__(256) k_rec_totals(const ScanParams p, const TileState* __restrict__ excl,
+                                                    uint32_t* __restrict__ ref_total, uint32_t* __restrict__ qry_total,
+                                                    uint32_t* __restrict__ aux_total) {
+  const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= p.n_rec) return;
+  const int64_t a = __ldg(p.op_off + r), b = __ldg(p.op_off + r + 1);
+  Sums s = {0, 0, 0, 0, 0};
+  if (b > a) {
+    if ((b % WT_OPS) == 0) {  // ends on a tile edge: the next tile's carry is the whole record
+      const TileState E = excl[b / WT_OPS];
+      s = Sums{E.r, E.q, E.x1, E.x2, E.x3};
+    } else {
+      const Sums fb = load_sums(p.fstart + 2 * (r + 1));
+      if (a / WT_OPS == b / WT_OPS) {
+        s = fb - load_sums(p.fstart + 2 * r);
+      } else {
+        const TileState E = excl[b / WT_OPS];
+        s = Sums{E.r + fb.r, E.q + fb.q, E.x1 + fb.x1, E.x2 + fb.x2, E.x3 + fb.x3};
+      }
+    }
   }
-  if (a.cnt_a == 0 && a.cnt_b == 0) return;
-  const uint2 st = tile_stage[t];
-  const Sums carry = {e.r, e.q, e.x1, e.x2, e.x3};
-  if (a.cnt_a) fix_stream<MODE, 0>(stage_a, st.x, a.cnt_a, e.cnt_a, carry, out_a, cap_a, lane);
-  if (MODE == VSV_MODE_FUSED && a.cnt_b) fix_stream<MODE, 1>(stage_b, st.y, a.cnt_b, e.cnt_b, carry, out_b, cap_b, lane);
+  ref_total[r] = ref_of<MODE, 0>(s);
+  qry_total[r] = qry_of<MODE, 0>(s);
+  aux_total[r] = aux_of<MODE>(s);
 }
 
 // ---- host side ---------------------------------------------------------------------------
@@ -692,14 +595,26 @@ struct ScanCall {
 };
 
 template <int MODE>
-static int launch_scan(vsv_ctx* ctx, const ScanParams& p, int grid) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    VSV_CUDA(ctx, cudaFuncSetAttribute(k_scan_tiles<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)sizeof(ScanSmem)));
-    attr_set = true;
+static int run_scan_kernels(vsv_ctx* ctx, const ScanParams& p, int grid, TileState* d_excl, vsv_sig* out_a, int64_t cap_a,
+                            vsv_sig* out_b, int64_t cap_b, int64_t* d_nout, uint32_t* rt, uint32_t* qt, uint32_t* xt) {
+  VSV_CUDA(ctx, cudaEventRecord(ctx->evk0, ctx->stream));
+  VSV_LAUNCH(ctx, k_scan_wt<MODE>, (unsigned)grid, SCAN_THREADS, 0, p);
+  VSV_CUDA(ctx, cudaEventRecord(ctx->evk1, ctx->stream));
+  ctx->main_open = true;
+  const unsigned gt = (unsigned)vsv_cdiv(p.n_wt, 128);
+  VSV_LAUNCH(ctx, k_gate<MODE>, gt, 128, 0, p);
+  {  // segmented exclusive scan of the tile aggregates (n_wt + 1 elements, last = identity)
+    TileState init;
+    memset(&init, 0, sizeof(init));
+    size_t tb = 0;
+    VSV_CUDA(ctx, cub::DeviceScan::ExclusiveScan(nullptr, tb, p.wt_agg, d_excl, TileStateOp(), init, p.n_wt + 1, ctx->stream));
+    void* tmp = nullptr;
+    VSV_TRY(vsv_arena_alloc(ctx, tb, &tmp));
+    VSV_CUDA(ctx, cub::DeviceScan::ExclusiveScan(tmp, tb, p.wt_agg, d_excl, TileStateOp(), init, p.n_wt + 1, ctx->stream));
+    ctx->launches += 2;
   }
-  VSV_LAUNCH(ctx, k_scan_tiles<MODE>, (unsigned)grid, SCAN_THREADS, sizeof(ScanSmem), p);
+  VSV_LAUNCH(ctx, k_emit<MODE>, gt, 128, 0, p, d_excl, out_a, cap_a, out_b, cap_b, d_nout);
+  if (rt) VSV_LAUNCH(ctx, k_rec_totals<MODE>, (unsigned)vsv_cdiv(p.n_rec, 256), 256, 0, p, d_excl, rt, qt, xt);
   return VSV_OK;
 }
 
@@ -711,9 +626,9 @@ static int scan_impl(vsv_ctx* ctx, const ScanCall& c) {
     VSV_FAIL(ctx, VSV_E_ARG, std::string(fn) + ": bad argument");
   if (c.min_len_a < 0 || c.min_len_a >= (1 << 27) || c.min_len_b < 0 || c.min_len_b >= (1 << 27))
     VSV_FAIL(ctx, VSV_E_ARG, std::string(fn) + ": min_len out of range");
-  if (c.n_rec >= (int64_t(1) << 31)) VSV_FAIL(ctx, VSV_E_ARG, std::string(fn) + ": more than 2^31-1 records per call");
-  if (c.cap_a >= (int64_t(1) << 30) || c.cap_b >= (int64_t(1) << 30))
-    VSV_FAIL(ctx, VSV_E_ARG, std::string(fn) + ": capacity must be below 2^30 signatures per call");
+  if (c.n_rec >= (int64_t(1) << 31) - 1) VSV_FAIL(ctx, VSV_E_ARG, std::string(fn) + ": more than 2^31-2 records per call");
+  if (c.cap_a >= (int64_t(1) << 31) || c.cap_b >= (int64_t(1) << 31))
+    VSV_FAIL(ctx, VSV_E_ARG, std::string(fn) + ": capacity must be below 2^31 signatures per call");
   const bool want_tot = c.ref_total || c.qry_total || c.aux_total;
   if (want_tot && !(c.ref_total && c.qry_total && c.aux_total))
     VSV_FAIL(ctx, VSV_E_ARG, std::string(fn) + ": pass all three totals or none");
@@ -730,9 +645,9 @@ static int scan_impl(vsv_ctx* ctx, const ScanCall& c) {
     n_ops = c.op_off[c.n_rec];
   }
   if (n_ops < 0) VSV_FAIL(ctx, VSV_E_ARG, std::string(fn) + ": negative op count");
-  const int64_t n_tiles64 = vsv_cdiv(n_ops, SCAN_TILE);
-  if (n_tiles64 >= (int64_t(1) << 31)) VSV_FAIL(ctx, VSV_E_ARG, std::string(fn) + ": too many ops per call");
-  const int32_t n_tiles = (int32_t)n_tiles64;
+  const int64_t n_wt64 = vsv_cdiv(n_ops, WT_OPS);
+  if (n_wt64 >= (int64_t(1) << 31) - 1) VSV_FAIL(ctx, VSV_E_ARG, std::string(fn) + ": too many ops per call");
+  const int32_t n_wt = (int32_t)n_wt64;
 
   ScanParams p;
   memset(&p, 0, sizeof(p));
@@ -757,101 +672,78 @@ static int scan_impl(vsv_ctx* ctx, const ScanCall& c) {
     VSV_TRY(vsv_out(ctx, c.qry_total, (size_t)c.n_rec, &d_qt));
     VSV_TRY(vsv_out(ctx, c.aux_total, (size_t)c.n_rec, &d_xt));
   }
-  const int grid = (int)std::min<int64_t>(n_tiles, (int64_t)ctx->sm_count * SCAN_CTAS_PER_SM);
-  // staging: slots are reserved per tile for the RAW candidate count in chunks, so the exact
-  // need is only known after a run; start from the caller's capacities and retry (rare) with
-  // the measured reservation if a tile found the staging full.
-  const int64_t slack = (int64_t)grid * SCAN_CHUNK + SCAN_CHUNK;
-  int64_t scap_a = (fused ? std::max(c.cap_a, c.cap_b) : c.cap_a) * 5 / 4 + slack;
-  int64_t scap_b = fused ? scap_a : 0;
-  int64_t* d_nout = nullptr;  // [0..1] signature counts, [2..3] staging counters, [4] staging-full flag
+  const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(vsv_cdiv(n_wt, SCAN_WARPS), (int64_t)ctx->sm_count * SCAN_CTAS_PER_SM));
+  // staging holds one entry per RAW candidate (before the record gates), reserved per warp in
+  // chunks, so the exact need is only known after a run: start from the caller's capacities and
+  // retry (rare) with the measured reservation if a warp found the staging full.
+  const int64_t slack = (int64_t)grid * SCAN_WARPS * SCAN_CHUNK + SCAN_CHUNK;
+  int64_t scap = (fused ? std::max(c.cap_a, c.cap_b) : c.cap_a) * 5 / 4 + slack;
+  int64_t* d_nout = nullptr;  // [0..1] signature counts, [2] staging counter, [3] unused, [4] staging-full flag
   uint32_t* d_info = nullptr;
-  int2* d_trec = nullptr;
+  int2* d_starts = nullptr;
   TileState *d_agg = nullptr, *d_excl = nullptr;
-  uint2* d_tstage = nullptr;
+  uint2* d_wstage = nullptr;
+  uint4* d_fstart = nullptr;
   VSV_TRY(vsv_tmp(ctx, 5, &d_nout));
   VSV_TRY(vsv_tmp(ctx, (size_t)c.n_rec, &d_info));
-  VSV_TRY(vsv_tmp(ctx, (size_t)n_tiles, &d_trec));
-  VSV_TRY(vsv_tmp(ctx, (size_t)n_tiles, &d_agg));
-  VSV_TRY(vsv_tmp(ctx, (size_t)n_tiles, &d_excl));
-  VSV_TRY(vsv_tmp(ctx, (size_t)n_tiles, &d_tstage));
+  VSV_TRY(vsv_tmp(ctx, (size_t)n_wt + 1, &d_starts));
+  VSV_TRY(vsv_tmp(ctx, (size_t)n_wt + 1, &d_agg));
+  VSV_TRY(vsv_tmp(ctx, (size_t)n_wt + 1, &d_excl));
+  VSV_TRY(vsv_tmp(ctx, (size_t)n_wt + 1, &d_wstage));
+  VSV_TRY(vsv_tmp(ctx, 2 * ((size_t)c.n_rec + 1), &d_fstart));
 
   p.rec_info = d_info;
-  p.n_rec = c.n_rec; p.n_ops = n_ops; p.n_tiles = n_tiles;
+  p.n_rec = c.n_rec; p.n_ops = n_ops; p.n_wt = n_wt;
   p.min_len_a = c.min_len_a; p.min_len_b = c.min_len_b;
   p.min_w = (uint32_t)(fused ? std::min(c.min_len_a, c.min_len_b) : c.min_len_a) << 4;
-  p.tile_rec = d_trec; p.tile_agg = d_agg; p.tile_stage = d_tstage;
+  p.wt_starts = d_starts; p.wt_agg = d_agg; p.wt_stage = d_wstage; p.fstart = d_fstart;
   p.stage_ctr = reinterpret_cast<unsigned long long*>(d_nout + 2);
-  p.ref_total = (uint32_t*)d_rt; p.qry_total = (uint32_t*)d_qt; p.aux_total = (uint32_t*)d_xt;
 
   int64_t h_n[5] = {0, 0, 0, 0, 0};
   VSV_TRY(vsv_t0(ctx));
-  if (n_tiles > 0) {
+  if (n_wt > 0) {
     VSV_LAUNCH(ctx, k_rec_info, (unsigned)vsv_cdiv(c.n_rec, 256), 256, 0, p.ops, p.op_off, d_mapq, d_ena, d_enb, c.n_rec,
                c.min_mapq_a, c.min_mapq_b, d_info);
-    VSV_LAUNCH(ctx, k_tile_records, (unsigned)vsv_cdiv(n_tiles, 256), 256, 0, p.op_off, c.n_rec, n_ops, n_tiles, d_trec);
+    VSV_LAUNCH(ctx, k_wt_starts, (unsigned)vsv_cdiv(n_wt, 256), 256, 0, p.op_off, c.n_rec, n_ops, n_wt, d_starts);
+    VSV_CUDA(ctx, cudaMemsetAsync(d_agg + n_wt, 0, sizeof(TileState), ctx->stream));  // identity sentinel
   }
   for (int attempt = 0; attempt < 3; ++attempt) {
-    if (scap_a >= (int64_t(1) << 32) - 1 || scap_b >= (int64_t(1) << 32) - 1)
+    if (scap >= (int64_t(1) << 32) - 1)
       VSV_FAIL(ctx, VSV_E_ARG, std::string(fn) + ": too many candidate signatures for one call; split the batch");
-    vsv_sig *d_sa = nullptr, *d_sb = nullptr;
-    VSV_TRY(vsv_tmp(ctx, (size_t)scap_a, &d_sa));
-    if (fused) VSV_TRY(vsv_tmp(ctx, (size_t)scap_b, &d_sb));
-    p.stage_a = d_sa; p.stage_b = d_sb;
-    p.stage_cap_a = (uint32_t)scap_a; p.stage_cap_b = (uint32_t)scap_b;
+    StageEntry* d_stage = nullptr;
+    VSV_TRY(vsv_tmp(ctx, (size_t)scap, &d_stage));
+    p.stage = d_stage;
+    p.stage_cap = (uint32_t)scap;
     VSV_CUDA(ctx, cudaMemsetAsync(d_nout, 0, 5 * sizeof(int64_t), ctx->stream));
-    if (want_tot) {
-      VSV_CUDA(ctx, cudaMemsetAsync(d_rt, 0, sizeof(int32_t) * (size_t)c.n_rec, ctx->stream));
-      VSV_CUDA(ctx, cudaMemsetAsync(d_qt, 0, sizeof(int32_t) * (size_t)c.n_rec, ctx->stream));
-      VSV_CUDA(ctx, cudaMemsetAsync(d_xt, 0, sizeof(int32_t) * (size_t)c.n_rec, ctx->stream));
+    if (n_wt == 0) {
+      if (want_tot) {
+        VSV_CUDA(ctx, cudaMemsetAsync(d_rt, 0, sizeof(int32_t) * (size_t)c.n_rec, ctx->stream));
+        VSV_CUDA(ctx, cudaMemsetAsync(d_qt, 0, sizeof(int32_t) * (size_t)c.n_rec, ctx->stream));
+        VSV_CUDA(ctx, cudaMemsetAsync(d_xt, 0, sizeof(int32_t) * (size_t)c.n_rec, ctx->stream));
+      }
+      break;
     }
-    if (n_tiles == 0) break;
-    VSV_CUDA(ctx, cudaEventRecord(ctx->evk0, ctx->stream));
-    switch (c.mode) {
-      case VSV_MODE_CONTIG: VSV_TRY(launch_scan<VSV_MODE_CONTIG>(ctx, p, grid)); break;
-      case VSV_MODE_READS: VSV_TRY(launch_scan<VSV_MODE_READS>(ctx, p, grid)); break;
-      case VSV_MODE_CUTE: VSV_TRY(launch_scan<VSV_MODE_CUTE>(ctx, p, grid)); break;
-      default: VSV_TRY(launch_scan<VSV_MODE_FUSED>(ctx, p, grid)); break;
-    }
-    VSV_CUDA(ctx, cudaEventRecord(ctx->evk1, ctx->stream));
-    ctx->main_open = true;
-    {  // segmented exclusive scan of the tile aggregates
-      TileState init;
-      memset(&init, 0, sizeof(init));
-      size_t tb = 0;
-      VSV_CUDA(ctx, cub::DeviceScan::ExclusiveScan(nullptr, tb, d_agg, d_excl, TileStateOp(), init, n_tiles, ctx->stream));
-      void* tmp = nullptr;
-      VSV_TRY(vsv_arena_alloc(ctx, tb, &tmp));
-      VSV_CUDA(ctx, cub::DeviceScan::ExclusiveScan(tmp, tb, d_agg, d_excl, TileStateOp(), init, n_tiles, ctx->stream));
-      ctx->launches += 2;
-    }
-    const unsigned gf = (unsigned)vsv_cdiv((int64_t)n_tiles * 32, 256);
+    uint32_t *rt = (uint32_t*)d_rt, *qt = (uint32_t*)d_qt, *xt = (uint32_t*)d_xt;
     switch (c.mode) {
       case VSV_MODE_CONTIG:
-        VSV_LAUNCH(ctx, k_scan_fixup<VSV_MODE_CONTIG>, gf, 256, 0, d_agg, d_excl, d_tstage, n_tiles, d_sa, d_sb, d_out_a,
-                   c.cap_a, d_out_b, c.cap_b, d_nout);
+        VSV_TRY(run_scan_kernels<VSV_MODE_CONTIG>(ctx, p, grid, d_excl, d_out_a, c.cap_a, d_out_b, c.cap_b, d_nout, rt, qt, xt));
         break;
       case VSV_MODE_READS:
-        VSV_LAUNCH(ctx, k_scan_fixup<VSV_MODE_READS>, gf, 256, 0, d_agg, d_excl, d_tstage, n_tiles, d_sa, d_sb, d_out_a,
-                   c.cap_a, d_out_b, c.cap_b, d_nout);
+        VSV_TRY(run_scan_kernels<VSV_MODE_READS>(ctx, p, grid, d_excl, d_out_a, c.cap_a, d_out_b, c.cap_b, d_nout, rt, qt, xt));
         break;
       case VSV_MODE_CUTE:
-        VSV_LAUNCH(ctx, k_scan_fixup<VSV_MODE_CUTE>, gf, 256, 0, d_agg, d_excl, d_tstage, n_tiles, d_sa, d_sb, d_out_a,
-                   c.cap_a, d_out_b, c.cap_b, d_nout);
+        VSV_TRY(run_scan_kernels<VSV_MODE_CUTE>(ctx, p, grid, d_excl, d_out_a, c.cap_a, d_out_b, c.cap_b, d_nout, rt, qt, xt));
         break;
       default:
-        VSV_LAUNCH(ctx, k_scan_fixup<VSV_MODE_FUSED>, gf, 256, 0, d_agg, d_excl, d_tstage, n_tiles, d_sa, d_sb, d_out_a,
-                   c.cap_a, d_out_b, c.cap_b, d_nout);
+        VSV_TRY(run_scan_kernels<VSV_MODE_FUSED>(ctx, p, grid, d_excl, d_out_a, c.cap_a, d_out_b, c.cap_b, d_nout, rt, qt, xt));
         break;
     }
     // the counts are needed on the host to size the copy-out: one small sync
     VSV_CUDA(ctx, cudaMemcpyAsync(h_n, d_nout, 5 * sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
     VSV_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    const bool fits = h_n[0] <= c.cap_a && (!fused || h_n[1] <= c.cap_b);
-    if (h_n[4] == 0 || !fits) break;  // done, or the caller has to grow its buffers anyway
+    if (h_n[4] == 0) break;           // staging held every candidate
     if (attempt == 2) VSV_FAIL(ctx, VSV_E_NOMEM, std::string(fn) + ": staging kept overflowing");
-    scap_a = 2 * h_n[2] + slack;      // reservation of the failed run bounds the raw count
-    if (fused) scap_b = 2 * h_n[3] + slack;
+    scap = 2 * h_n[2] + slack;        // reservation of the failed run bounds the raw count
   }
   VSV_TRY(vsv_t1(ctx));
   *c.n_a = h_n[0];
