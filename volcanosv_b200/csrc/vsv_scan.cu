@@ -278,6 +278,23 @@ __device__ __forceinline__ Sums load_sums(const uint4* src) {
   return Sums{a.x, a.y, a.z, a.w, b.x};
 }
 
+// byte table for PRMT look-ups by op code: byte k (codes base..base+3) = v1 if code in set1,
+// else v2 if code in set2, else 0
+__host__ __device__ constexpr uint32_t tab_word(uint32_t set1, int base, uint32_t v1, uint32_t set2, uint32_t v2) {
+  uint32_t wv = 0;
+  for (int k = 0; k < 4; ++k) {
+    const uint32_t c = (uint32_t)(base + k);
+    const uint32_t b = ((set1 >> c) & 1u) ? v1 : (((set2 >> c) & 1u) ? v2 : 0u);
+    wv |= b << (8 * k);
+  }
+  return wv;
+}
+__device__ __forceinline__ uint32_t prmt(uint32_t lo, uint32_t hi, uint32_t sel) {
+  uint32_t d;
+  asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(lo), "r"(hi), "r"(sel));
+  return d;
+}
+
 // ---- K1: the streaming kernel (every warp is an independent worker) --------------------
 template <int MODE>
 __global__ void __launch_bounds__(SCAN_THREADS, SCAN_CTAS_PER_SM) k_scan_wt(const ScanParams p) {
@@ -335,8 +352,16 @@ __global__ void __launch_bounds__(SCAN_THREADS, SCAN_CTAS_PER_SM) k_scan_wt(cons
     }
 
     // -- fast path: 32 consecutive ops per lane, rotated so LDS.128 is conflict free -------
-    uint32_t r = 0, q = 0, bits = 0, em = 0;
-    {
+    // The integer ALU pipe (LOP3/SHF/SEL/ISETP/PRMT) issues at half rate on sm_100, the FMA
+    // pipe (IMAD) runs beside it, so the per-op work is split across both: three byte-table
+    // look-ups by op code (PRMT: 0xFFFFFFFF = member, 0 = not) feed IMADs that accumulate the
+    // NEGATED reference / query sums; the third table marks I/D (-1) and rare codes
+    // (0x01010101), whose IMAD-summed total tells whether this lane needs the slow path.
+    uint32_t r = 0, q = 0, em = 0;
+    Sums xs = {0, 0, 0, 0, 0};
+    bool lane_rare;
+    if constexpr (MODE == VSV_MODE_CONTIG) {  // contig BAMs are tiny and '=' / 'X' differ from 'M' there: generic path
+      uint32_t bits = 0;
       const int rot = lane & 7;
       const uint4* row = reinterpret_cast<const uint4*>(tl + lane * WT_VPT);
       const uint32_t min_w = p.min_w;
@@ -355,6 +380,52 @@ __global__ void __launch_bounds__(SCAN_THREADS, SCAN_CTAS_PER_SM) k_scan_wt(cons
         }
       }
       em = __funnelshift_l(em, em, 4 * rot);  // loop chunk k is logical chunk (k+rot)&7
+      lane_rare = (bits & RARE) != 0u;
+      if (lane_rare)
+        for (int i = 0; i < WT_VPT; ++i) add_op<MODE>(tl[lane * WT_VPT + i], xs);
+    } else {
+      constexpr uint32_t TR_LO = tab_word(M::REF, 0, 0xFFu, 0, 0), TR_HI = tab_word(M::REF, 4, 0xFFu, 0, 0);
+      constexpr uint32_t TQ_LO = tab_word(M::QRY, 0, 0xFFu, 0, 0), TQ_HI = tab_word(M::QRY, 4, 0xFFu, 0, 0);
+      constexpr uint32_t TC_LO = tab_word(6u, 0, 0xFFu, RARE, 0x01u), TC_HI = tab_word(6u, 4, 0xFFu, RARE, 0x01u);
+      static_assert(((M::REF >> 8) & 1u) == (M::REF & 1u) && ((M::QRY >> 8) & 1u) == (M::QRY & 1u),
+                    "code 8 (X) is looked up as the sign of code 0 (M)");
+      const int rot = lane & 7;
+      const uint4* row = reinterpret_cast<const uint4*>(tl + lane * WT_VPT);
+      const uint32_t min_w = p.min_w;
+      uint32_t nr = 0, nq = 0, mx = 0;
+      int32_t sc = 0;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const uint4 v = row[(k + rot) & 7];
+        const uint32_t ww[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const uint32_t w = ww[i];
+          const uint32_t code = w & 15u, len = w >> 4;
+          const uint32_t sel = code * 0x1111u;
+          const uint32_t tr = prmt(TR_LO, TR_HI, sel), tq = prmt(TQ_LO, TQ_HI, sel);
+          const int32_t tc = (int32_t)prmt(TC_LO, TC_HI, sel);
+          nr = len * tr + nr;  // IMAD: subtracts len when the code is a member
+          nq = len * tq + nq;
+          sc += tc;
+          mx = max(mx, code);
+          em |= (tc < 0 && w >= min_w) ? (1u << (k * 4 + i)) : 0u;
+        }
+      }
+      r = 0u - nr;
+      q = 0u - nq;
+      em = __funnelshift_l(em, em, 4 * rot);  // loop chunk k is logical chunk (k+rot)&7
+      lane_rare = sc > 0 || mx > 8u;           // a rare code (N/H/P...) or a reserved one (9..15)
+      if (lane_rare) {                         // exact recomputation of this lane
+        em = 0;
+        for (int i = 0; i < WT_VPT; ++i) {
+          const uint32_t w = tl[lane * WT_VPT + i];
+          add_op<MODE>(w, xs);
+          em |= (((1u << (w & 15u)) & 6u) && w >= min_w) ? (1u << i) : 0u;
+        }
+        r = xs.r;
+        q = xs.q;
+      }
     }
     const uint32_t c = __popc(em);
 
@@ -369,11 +440,8 @@ __global__ void __launch_bounds__(SCAN_THREADS, SCAN_CTAS_PER_SM) k_scan_wt(cons
     }
     Sums ex = {ir - r, iq - q, 0, 0, 0};  // this lane's exclusive prefix inside the tile
     Sums tot = {__shfl_sync(FULL, ir, 31), __shfl_sync(FULL, iq, 31), 0, 0, 0};
-    const bool anyrare = __any_sync(FULL, (bits & RARE) != 0u);
-    if (anyrare) {  // slow path: this warp saw N / H / P / ...
-      Sums xs = {0, 0, 0, 0, 0};
-      if (bits & RARE)
-        for (int i = 0; i < WT_VPT; ++i) add_op<MODE>(tl[lane * WT_VPT + i], xs);
+    const bool anyrare = __any_sync(FULL, lane_rare);
+    if (anyrare) {  // this warp saw N / H / P / ...: scan the rare sums too
       uint32_t i1 = xs.x1, i2 = xs.x2, i3 = xs.x3;
 #pragma unroll
       for (int d = 1; d < 32; d <<= 1) {
