@@ -125,6 +125,20 @@ int vsv_split_pairs(vsv_ctx* ctx, int variant, int min_mapq, const int32_t* pos,
                     const int32_t* name_id, const uint8_t* select, int64_t n_rec, vsv_sig* out,
                     int64_t cap, int64_t* n_out);
 
+/* analysis_split_read (SE:193-326) on the segment lists organize_split_signal (SE:345-371)
+ * builds (primary first, then the SA entries that pass the mapq filter; SA positions are
+ * kept 1-based, SE:354).  Read r owns segments [seg_off[r], seg_off[r+1]) given as columns
+ * q_s,q_e,r_s,r_e,chrom,strand(0 '+',1 '-'); read_len[r] = query length incl. clips.  Reads
+ * with more than max_parts segments (reference: 7, SE:370) emit nothing; max_parts must be
+ * in [2,16].  Output rows in (read, emission) order: rec = read index, type, pos (already
+ * truncated as '%d' prints the reference's float, SE:562-565), len; for INS q0,q1 = slice of
+ * the query sequence (Python slice semantics) after reversing it `first` times (0/1).  TRA
+ * rows are not produced (SE:637-638 greps them away). */
+int vsv_sa_analysis(vsv_ctx* ctx, int sv_size, int max_size, int max_parts, const int64_t* seg_off,
+                    const int32_t* q_s, const int32_t* q_e, const int32_t* r_s, const int32_t* r_e,
+                    const int32_t* chrom, const uint8_t* strand, const int32_t* read_len,
+                    int64_t n_read, int64_t n_seg, vsv_sig* out, int64_t cap, int64_t* n_out);
+
 /* ---- stage 2: sort / cluster / pair / window joins ---------------------------- */
 /* sort_sig (ECS_H:170-179) with the tie order pinned to stable: order[i] = index of
  * the i-th smallest key. */

@@ -433,13 +433,16 @@ def group_sigs(chrom_id, pos, length):
 
 
 def sig_support(cand_chrom, cand_pos, cand_svlen, sig_chrom, sig_pos, sig_len, sig_cnt,
-                min_size_sim=0.6, max_shift_ratio=2.3):
+                min_size_sim=0.6, max_shift_ratio=2.3, last_in=0, return_last=False):
     """match_varlist_siglist (GTD:92-137) / extract_sig_support (GTI:107-166), literally:
     forward scan and backward scan both start AT last_match_idx (double count), breaks
     are taken only on same-chromosome rows, last_match_idx <- min matched index.
-    Returns (n_support list, match_id list = last_match_idx seen by each candidate).
+    Returns (n_support list, match_id list = last_match_idx seen by each candidate)
+    [+ the final last_match_idx with return_last].  last_in = -1 is the shard-local "the
+    carried index lies in another chromosome's block" (volcanosv_b200/shard.py): the whole
+    window is visited once and nothing can be double counted.
     """
-    last = 0
+    last = last_in
     sup, mids = [], []
     n = len(sig_pos)
     for cc, cp, sv in zip(cand_chrom, cand_pos, cand_svlen):
@@ -451,7 +454,7 @@ def sig_support(cand_chrom, cand_pos, cand_svlen, sig_chrom, sig_pos, sig_len, s
         matched = []
         s = 0
         mids.append(last)
-        for i in range(last, n):
+        for i in range(max(last, 0), n):
             if int(sig_chrom[i]) == cc:
                 if lo <= int(sig_pos[i]) <= hi:
                     matched.append(i)
@@ -459,7 +462,7 @@ def sig_support(cand_chrom, cand_pos, cand_svlen, sig_chrom, sig_pos, sig_len, s
                         s += int(sig_cnt[i])
                 elif int(sig_pos[i]) > hi:
                     break
-        for i in range(min(last, n - 1), -1, -1):
+        for i in (range(min(last, n - 1), -1, -1) if last >= 0 else ()):
             if int(sig_chrom[i]) == cc:
                 if lo <= int(sig_pos[i]) <= hi:
                     matched.append(i)
@@ -470,6 +473,8 @@ def sig_support(cand_chrom, cand_pos, cand_svlen, sig_chrom, sig_pos, sig_len, s
         if matched:
             last = min(matched)
         sup.append(s)
+    if return_last:
+        return sup, mids, last
     return sup, mids
 
 

@@ -200,3 +200,74 @@ def test_depth_stress_properties(ctx):
     dd = ctx.span_depth(rs, re, Sd, Sd + 50)
     for i in range(0, 4096, 257):
         assert dd[i] == O.span_count(rs, re, int(Sd[i]), int(Sd[i]) + 50)
+
+
+def _sa_pack(cases):
+    seg_off, cols, L = [0], [[] for _ in range(6)], []
+    for segs, ln in cases:
+        for s in segs:
+            for k in range(6):
+                cols[k].append(s[k])
+        seg_off.append(seg_off[-1] + len(segs))
+        L.append(ln)
+    return seg_off, cols, L
+
+
+def _sa_check(ctx, cases, max_parts=7):
+    seg_off, cols, L = _sa_pack(cases)
+    got = ctx.sa_analysis(seg_off, *cols, L, max_parts=max_parts)
+    exp = []
+    for r, (segs, ln) in enumerate(cases):
+        for (tp, p, n, q0, q1, rev) in O.sa_split_analysis([tuple(s) for s in segs], ln, max_parts=max_parts):
+            exp.append((r, tp, p, n, q0, q1, rev))
+    g = [tuple(int(x[f]) for f in ("rec", "type", "pos", "len", "q0", "q1", "first")) for x in got]
+    assert g == exp
+    return len(exp)
+
+
+def test_sa_analysis_golden(ctx, golden):
+    """analysis_split_read (SE:193-326): reference-generated rows incl. the INS sequence slice."""
+    g = golden("sa")
+    cases = [([(s[0], s[1], s[2], s[3], 1 if s[4] == "chr1" else 2, 0 if s[5] == "+" else 1) for s in c["segs"]], c["L"])
+             for c in g]
+    seg_off, cols, L = _sa_pack(cases)
+    got = ctx.sa_analysis(seg_off, *cols, L)
+    rows = [[] for _ in g]
+    for x in got:
+        c = g[int(x["rec"])]
+        if int(x["type"]) == V.INS:
+            q = c["query"][::-1] if int(x["first"]) else c["query"]
+            rows[int(x["rec"])].append(["INS", int(x["pos"]), int(x["len"]), q[int(x["q0"]):int(x["q1"])]])
+        else:
+            rows[int(x["rec"])].append(["DEL", int(x["pos"]), int(x["len"])])
+    assert rows == [c["rows"] for c in g]
+    assert sum(len(r) for r in rows) > 50
+
+
+def test_sa_analysis_random_vs_oracle(ctx):
+    rng = np.random.default_rng(99)
+    cases = []
+    for t in range(5000):
+        k = int(rng.choice([0, 1, 2, 2, 2, 3, 3, 4, 5, 7, 8, 9]))
+        ln = int(rng.integers(600, 30000))
+        r = int(rng.integers(10000, 10**8))
+        q = 0
+        st0 = int(rng.integers(0, 2))
+        segs = []
+        for i in range(k):
+            qe = q + int(rng.integers(50, max(60, ln // max(k, 1))))
+            chrom = 1 if rng.random() < 0.85 else 2
+            st = st0 if rng.random() < 0.9 else 1 - st0
+            segs.append((q, qe, r, r + (qe - q) + int(rng.integers(-20, 20)), chrom, st))
+            q = qe + int(rng.choice([0, 0, rng.integers(-60, 60), rng.integers(30, 2000)]))
+            r = segs[-1][3] + int(rng.choice([0, rng.integers(-29, 101), rng.integers(30, 120000), rng.integers(-500, -30)]))
+        if st0:
+            segs = [(ln - s[1], ln - s[0]) + s[2:] for s in segs]
+        order = rng.permutation(len(segs))
+        cases.append(([segs[i] for i in order], ln))
+    assert _sa_check(ctx, cases) > 500
+    assert _sa_check(ctx, cases[:500], max_parts=16) > 50
+    # empty input and the argument check
+    assert len(ctx.sa_analysis([0], [], [], [], [], [], [], [])) == 0
+    with pytest.raises(V.VsvError):
+        ctx.sa_analysis([0, 2], [0, 5], [5, 9], [1, 2], [3, 4], [1, 1], [0, 0], [100], max_parts=40)

@@ -1,0 +1,101 @@
+"""Host-side multi-GPU logic (volcanosv_b200/shard.py): LPT assignment, ordering rules, the
+last_match_idx carry rule against the oracle run genome-wide, and a world_size-2 gloo gather."""
+import os
+import socket
+
+import numpy as np
+
+import oracle as O
+from volcanosv_b200 import shard as S
+
+
+def test_lpt_assignment_is_balanced_and_deterministic():
+    hg19 = [249250621, 243199373, 198022430, 191154276, 180915260, 171115067, 159138663, 146364022, 141213431,
+            135534747, 135006516, 133851895, 115169878, 107349540, 102531392, 90354753, 81195210, 78077248,
+            59128983, 63025520, 48129895, 51304566]                          # LI/header:5-26
+    w = {"chr%d" % (i + 1): float(n) for i, n in enumerate(hg19)}
+    for n in (1, 2, 4, 8):
+        a = S.assign_lpt(w, n)
+        assert sorted(sum(a, [])) == sorted(w)
+        loads = [sum(w[c] for c in r) for r in a]
+        assert max(loads) <= sum(loads) / n * 1.12 + 1
+        assert a == S.assign_lpt(w, n)
+    assert S.assign_lpt({}, 3) == [[], [], []]
+
+
+def test_orders():
+    names = ["chr%d" % i for i in range(1, 23)]
+    assert S.chrom_numeric_order(reversed(names)) == names
+    d = S.chrom_dictionary_order(names)
+    assert d[:3] == ["chr1", "chr10", "chr11"] and d[-1] == "chr9"
+
+
+def test_support_carry_rule_matches_genome_wide_oracle():
+    """Per-chromosome shards with support_carry_in() == match_varlist_siglist run genome-wide."""
+    rng = np.random.default_rng(5)
+    chroms = ["chr1", "chr2", "chr10"]
+    for trial in range(30):
+        sig = {c: None for c in chroms}
+        if trial % 5 == 0:
+            sig.pop("chr1")                                    # first block is then chr10
+        for c in sig:
+            n = int(rng.integers(1, 40))
+            p = np.sort(rng.integers(1000, 20000, n)).astype(np.int32)
+            sig[c] = (p, rng.integers(30, 400, n).astype(np.int32), rng.integers(1, 5, n).astype(np.int32))
+        cand = {}
+        for c in chroms:
+            n = int(rng.integers(0, 12))
+            cand[c] = (np.sort(rng.integers(1000, 20000, n)).astype(np.int32), rng.integers(30, 400, n).astype(np.int32))
+        cid = {c: i for i, c in enumerate(S.chrom_dictionary_order(chroms))}
+        so = S.chrom_dictionary_order(list(sig))
+        g_sc = np.concatenate([np.full(len(sig[c][0]), cid[c], np.int32) for c in so])
+        g_sp, g_sl, g_sn = (np.concatenate([sig[c][k] for c in so]) for k in range(3))
+        co = S.chrom_numeric_order(chroms)
+        g_cc = np.concatenate([np.full(len(cand[c][0]), cid[c], np.int32) for c in co])
+        g_cp, g_cl = (np.concatenate([cand[c][k] for c in co]) for k in range(2))
+        exp, _ = O.sig_support(g_cc, g_cp, g_cl, g_sc, g_sp, g_sl, g_sn)
+        got, matched = [], False
+        for c in co:
+            if c not in sig:
+                got += [0] * len(cand[c][0])
+                continue
+            z = np.zeros(len(cand[c][0]), np.int32)
+            zs = np.zeros(len(sig[c][0]), np.int32)
+            last_in = S.support_carry_in(c, co, list(sig), matched)
+            s, _, last = O.sig_support(z, cand[c][0], cand[c][1], zs, *sig[c], last_in=last_in, return_last=True)
+            got += list(s)
+            matched = matched or (last != last_in)
+        assert list(exp) == got, trial
+
+
+def _worker(rank, world, port, q):
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    w = {"chr%d" % i: float(30 - i) for i in range(1, 9)}
+    mine = S.assign_lpt(w, world)[rank]
+    local = {c: "%s:body-from-rank%d\n" % (c, rank) for c in mine}
+    allr = S.gather_to_root(local)
+    if rank == 0:
+        q.put(S.concat_in_order(allr, S.chrom_numeric_order(list(w))))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_gloo_world2_gather_concat():
+    import torch.multiprocessing as mp
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    ps = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in ps:
+        p.start()
+    out = q.get(timeout=120)
+    for p in ps:
+        p.join(60)
+        assert p.exitcode == 0
+    assert [x.split(":")[0] for x in out] == ["chr%d" % i for i in range(1, 9)]
+    assert {x.strip()[-5:] for x in out} == {"rank0", "rank1"}

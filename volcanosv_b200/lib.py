@@ -53,6 +53,7 @@ SIGNATURES = {
                              _vp, _i64, C.POINTER(_i64), _vp, _vp, _vp],
     "vsv_merge_in_record": [_vp, _int, _vp, _i64, _vp, C.POINTER(_i64), _vp, C.POINTER(_i64)],
     "vsv_split_pairs": [_vp, _int, _int, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _i64, C.POINTER(_i64)],
+    "vsv_sa_analysis": [_vp, _int, _int, _int, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _vp, _i64, C.POINTER(_i64)],
     "vsv_argsort_stable": [_vp, _vp, _i64, _vp],
     "vsv_sort_sigs": [_vp, _vp, _i64, _int, _vp],
     "vsv_sig_columns": [_vp, _vp, _i64, _vp, _vp, _vp],
@@ -232,6 +233,20 @@ class Context:
         return out[: n_out.value]
 
     # ---- stage 2 ---------------------------------------------------------------
+    def sa_analysis(self, seg_off, q_s, q_e, r_s, r_e, chrom, strand, read_len, sv_size=30, max_size=100000,
+                    max_parts=7):
+        """analysis_split_read (SE:193-326): rows (rec=read, type, pos, len, q0, q1, first=rev)."""
+        seg_off = _arr(seg_off, np.int64)
+        n_read, n_seg = len(seg_off) - 1, int(seg_off[-1])
+        cols = [_arr(x, np.int32) for x in (q_s, q_e, r_s, r_e, chrom)]
+        strand, read_len = _arr(strand, np.uint8), _arr(read_len, np.int32)
+        cap = 2 * n_seg + 2
+        out = _aligned_empty(cap, SIG_DTYPE)
+        n = _i64()
+        self._chk(self.lib.vsv_sa_analysis(self.h, sv_size, max_size, max_parts, _p(seg_off), *[_p(c) for c in cols],
+                                           _p(strand), _p(read_len), n_read, n_seg, _p(out), cap, C.byref(n)))
+        return out[: n.value]
+
     def argsort_stable(self, key):
         key = _arr(key, np.int32)
         order = np.empty(len(key), np.int32)

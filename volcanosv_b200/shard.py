@@ -1,0 +1,89 @@
+"""Multi-GPU partitioning of the large-indel stage: chromosome shards, no data-path collective.
+
+The reference fans the per-chromosome chain out over processes (`joblib.Parallel` over 22
+chromosomes, LI/volcanosv-vc-large-indel.py:268) and concatenates the per-chromosome bodies
+in chromosome order (MAIN:271-278).  Here one process owns one GPU; chromosomes are assigned
+to ranks by longest-processing-time-first on their op counts, every rank runs its shards
+independently, and the results meet on the HOST (rank 0) where they are put back in the
+reference's order.  The only values that cross a shard edge are scalars:
+  * the genome-wide coverage median of filter_vcf_by_sig_cov_insdel.py:39,55 (<= 10^4 floats
+    gathered to rank 0), and
+  * `last_match_idx` of match_varlist_siglist (GTD:94): see `support_carry_in`.
+torch.distributed is used for the host-side gather only (gloo for objects; bench.py uses
+NCCL just for its timing barrier).
+"""
+from __future__ import annotations
+
+from typing import Dict, Hashable, List, Sequence
+
+
+def assign_lpt(weights: Dict[Hashable, float], n_ranks: int) -> List[List[Hashable]]:
+    """Longest-processing-time-first: heaviest shard to the least loaded rank.  Deterministic
+    (ties: insertion order of `weights`, then lowest rank)."""
+    if n_ranks < 1:
+        raise ValueError("n_ranks must be >= 1")
+    order = sorted(range(len(weights)), key=lambda i: (-list(weights.values())[i], i))
+    keys = list(weights.keys())
+    load = [0.0] * n_ranks
+    out: List[List[Hashable]] = [[] for _ in range(n_ranks)]
+    for i in order:
+        r = min(range(n_ranks), key=lambda j: (load[j], j))
+        out[r].append(keys[i])
+        load[r] += float(weights[keys[i]])
+    return out
+
+
+def chrom_numeric_order(names: Sequence[str]) -> List[str]:
+    """chr1..chr22 in numeric order: the order MAIN:271-278 concatenates per-chromosome bodies
+    (candidate order of the genotype stage)."""
+    def key(n):
+        s = n[3:] if n.startswith("chr") else n
+        return (0, int(s)) if s.isdigit() else (1, s)
+    return sorted(names, key=key)
+
+
+def chrom_dictionary_order(names: Sequence[str]) -> List[str]:
+    """C-locale string order: `.sigs` files (`sort -k2,2`, SE:637-638) and `vcf-sort`'s
+    `sort -k1,1d` (FGC:177): chr1, chr10, ..., chr19, chr2, chr20, ..."""
+    return sorted(names)
+
+
+def support_carry_in(chrom: str, cand_chroms: Sequence[str], sig_chroms: Sequence[str], matched_before: bool) -> int:
+    """`last_in` of vsv_sig_support for a chromosome shard (GTD:94-133 run genome-wide).
+
+    The reference's last_match_idx starts at 0 and only ever moves to a position-matched
+    signature of the chromosome being processed, so when candidates of `chrom` start it
+    points into `chrom`'s own block of the unique-signature list only if it is still 0 AND
+    that block starts at global index 0 (i.e. `chrom` sorts first among chromosomes that have
+    signatures).  Otherwise it sits in another chromosome's block, can never qualify for the
+    double count, and the shard-local carry is "none" (-1).
+    `matched_before`: some earlier candidate (in candidate order) already moved the index.
+    """
+    if matched_before or not sig_chroms:
+        return -1
+    first_block = chrom_dictionary_order(sig_chroms)[0]
+    return 0 if chrom == first_block else -1
+
+
+def gather_to_root(local: dict, group=None) -> List[dict]:
+    """Host-side gather of per-rank result dicts (keyed by chromosome) to rank 0.  Returns the
+    list of all ranks' dicts on rank 0, [] elsewhere.  No-op without torch.distributed."""
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()):
+        return [local]
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    out = [None] * world if rank == 0 else None
+    dist.gather_object(local, out, dst=0, group=group)
+    return out if rank == 0 else []
+
+
+def concat_in_order(per_rank: List[dict], order: Sequence[str]) -> list:
+    """Merge the ranks' {chrom: value} dicts and list the values in `order` (missing skipped)."""
+    merged = {}
+    for d in per_rank:
+        for k, v in d.items():
+            if k in merged:
+                raise ValueError("chromosome %r produced by two ranks" % (k,))
+            merged[k] = v
+    return [merged[c] for c in order if c in merged]
