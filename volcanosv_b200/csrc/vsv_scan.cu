@@ -150,6 +150,8 @@ struct ScanParams {
   int64_t n_rec, n_ops;
   int32_t n_wt;              // number of warp tiles
   uint32_t min_w;            // min candidate length << 4
+  uint32_t one;              // 1 (opaque multiplier: keeps an accumulate on the FMA pipe)
+  uint32_t tab[6];           // PRMT byte tables by op code: REF lo/hi, QRY lo/hi, candidate/rare lo/hi
   int32_t min_len_a, min_len_b;
   const int2* wt_starts;     // [first,last] record (index in 0..n_rec) whose start lies in the tile
   TileState* wt_agg;         // [n_wt + 1] aggregates (last = identity), counts filled by k_gate
@@ -252,23 +254,6 @@ __device__ __forceinline__ void add_op(uint32_t w, Sums& s) {
   if (M::NX > 2) s.x3 += (bit & M::X3) ? len : 0u;
 }
 
-// sums over row[0, n)  (row = the 32 ops of one lane; shared or global memory)
-template <int MODE>
-__device__ __forceinline__ Sums walk(const uint32_t* row, int n, bool with_rare) {
-  typedef ModeTraits<MODE> M;
-  Sums s = {0, 0, 0, 0, 0};
-  if (with_rare) {
-    for (int i = 0; i < n; ++i) add_op<MODE>(row[i], s);
-  } else {
-    for (int i = 0; i < n; ++i) {
-      const uint32_t w = row[i], bit = 1u << (w & 15u), len = w >> 4;
-      s.r += (bit & M::REF) ? len : 0u;
-      s.q += (bit & M::QRY) ? len : 0u;
-    }
-  }
-  return s;
-}
-
 __device__ __forceinline__ void store_sums(uint4* dst, const Sums& s) {
   dst[0] = make_uint4(s.r, s.q, s.x1, s.x2);
   dst[1] = make_uint4(s.x3, 0u, 0u, 0u);
@@ -352,22 +337,26 @@ __global__ void __launch_bounds__(SCAN_THREADS, SCAN_CTAS_PER_SM) k_scan_wt(cons
     }
 
     // -- fast path: 32 consecutive ops per lane, rotated so LDS.128 is conflict free -------
-    // The integer ALU pipe (LOP3/SHF/SEL/ISETP/PRMT) issues at half rate on sm_100, the FMA
-    // pipe (IMAD) runs beside it, so the per-op work is split across both: three byte-table
-    // look-ups by op code (PRMT: 0xFFFFFFFF = member, 0 = not) feed IMADs that accumulate the
-    // NEGATED reference / query sums; the third table marks I/D (-1) and rare codes
-    // (0x01010101), whose IMAD-summed total tells whether this lane needs the slow path.
-    uint32_t r = 0, q = 0, em = 0;
+    // Per-op budget (v6).  The integer ALU pipe (LOP3/SHF/PRMT/VIMNMX) and the FMA pipe (IMAD)
+    // each issue one warp instruction every two cycles per SM sub-partition, so the per-op work
+    // is balanced across both: three byte-table look-ups by op code (PRMT: 0xFFFFFFFF = member,
+    // 0 = not) feed IMADs that accumulate the NEGATED reference / query sums; the third table
+    // marks I/D (-1) and rare codes (0x01010101) and is summed by an IMAD with an opaque 1.
+    // Candidates (D/I >= min_len: < 1 % of the ops) are NOT located per op: the loop only keeps
+    // max(w & tc), and lanes whose maximum reaches min_w are resolved afterwards by the whole
+    // warp (one LDS + ballot per such lane).  Lanes that saw a rare code (N/H/P, reserved 9..15)
+    // are recomputed exactly, also warp-cooperatively (REDUX).
+    uint32_t r = 0, q = 0;
     Sums xs = {0, 0, 0, 0, 0};
-    bool lane_rare;
-    if constexpr (MODE == VSV_MODE_CONTIG) {  // contig BAMs are tiny and '=' / 'X' differ from 'M' there: generic path
-      uint32_t bits = 0;
+    bool lane_rare, lane_cand;
+    const uint32_t min_w = p.min_w;
+    if constexpr (MODE == VSV_MODE_CONTIG) {  // contig BAMs are tiny: generic per-op path
+      uint32_t bits = 0, mxk = 0;
       const int rot = lane & 7;
       const uint4* row = reinterpret_cast<const uint4*>(tl + lane * WT_VPT);
-      const uint32_t min_w = p.min_w;
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
-        const uint4 v = row[(k + rot) & 7];
+        const uint4 v = row[k ^ rot];
         const uint32_t ww[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
@@ -376,55 +365,74 @@ __global__ void __launch_bounds__(SCAN_THREADS, SCAN_CTAS_PER_SM) k_scan_wt(cons
           bits |= bit;
           r += (bit & M::REF) ? len : 0u;
           q += (bit & M::QRY) ? len : 0u;
-          em |= ((bit & 6u) && w >= min_w) ? (1u << (k * 4 + i)) : 0u;
+          mxk = max(mxk, (bit & 6u) ? w : 0u);
         }
       }
-      em = __funnelshift_l(em, em, 4 * rot);  // loop chunk k is logical chunk (k+rot)&7
       lane_rare = (bits & RARE) != 0u;
-      if (lane_rare)
-        for (int i = 0; i < WT_VPT; ++i) add_op<MODE>(tl[lane * WT_VPT + i], xs);
+      lane_cand = mxk >= min_w;
     } else {
-      constexpr uint32_t TR_LO = tab_word(M::REF, 0, 0xFFu, 0, 0), TR_HI = tab_word(M::REF, 4, 0xFFu, 0, 0);
-      constexpr uint32_t TQ_LO = tab_word(M::QRY, 0, 0xFFu, 0, 0), TQ_HI = tab_word(M::QRY, 4, 0xFFu, 0, 0);
-      constexpr uint32_t TC_LO = tab_word(6u, 0, 0xFFu, RARE, 0x01u), TC_HI = tab_word(6u, 4, 0xFFu, RARE, 0x01u);
+      // the six table words come in through the kernel parameters (filled by the host from
+      // tab_word): as compile-time constants ptxas overwrites and re-materialises them around
+      // every PRMT, which costs an issue slot per look-up
+      uint32_t TR_LO, TR_HI, TQ_LO, TQ_HI, TC_LO, TC_HI;  // pinned in registers (volatile asm: no re-materialisation)
+      asm volatile("mov.u32 %0, %1;" : "=r"(TR_LO) : "r"(p.tab[0]));
+      asm volatile("mov.u32 %0, %1;" : "=r"(TR_HI) : "r"(p.tab[1]));
+      asm volatile("mov.u32 %0, %1;" : "=r"(TQ_LO) : "r"(p.tab[2]));
+      asm volatile("mov.u32 %0, %1;" : "=r"(TQ_HI) : "r"(p.tab[3]));
+      asm volatile("mov.u32 %0, %1;" : "=r"(TC_LO) : "r"(p.tab[4]));
+      asm volatile("mov.u32 %0, %1;" : "=r"(TC_HI) : "r"(p.tab[5]));
       static_assert(((M::REF >> 8) & 1u) == (M::REF & 1u) && ((M::QRY >> 8) & 1u) == (M::QRY & 1u),
                     "code 8 (X) is looked up as the sign of code 0 (M)");
       const int rot = lane & 7;
       const uint4* row = reinterpret_cast<const uint4*>(tl + lane * WT_VPT);
-      const uint32_t min_w = p.min_w;
-      uint32_t nr = 0, nq = 0, mx = 0;
-      int32_t sc = 0;
+      const uint32_t one = p.one;  // == 1, opaque to the compiler: keeps `sc` on the FMA pipe
+      uint32_t nr = 0, nq = 0, mxc = 0, mxk = 0, sc = 0;
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
-        const uint4 v = row[(k + rot) & 7];
+        const uint4 v = row[k ^ rot];
         const uint32_t ww[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
           const uint32_t w = ww[i];
           const uint32_t code = w & 15u, len = w >> 4;
           const uint32_t sel = code * 0x1111u;
-          const uint32_t tr = prmt(TR_LO, TR_HI, sel), tq = prmt(TQ_LO, TQ_HI, sel);
-          const int32_t tc = (int32_t)prmt(TC_LO, TC_HI, sel);
+          const uint32_t tr = prmt(TR_LO, TR_HI, sel), tq = prmt(TQ_LO, TQ_HI, sel), tc = prmt(TC_LO, TC_HI, sel);
           nr = len * tr + nr;  // IMAD: subtracts len when the code is a member
           nq = len * tq + nq;
-          sc += tc;
-          mx = max(mx, code);
-          em |= (tc < 0 && w >= min_w) ? (1u << (k * 4 + i)) : 0u;
+          sc = tc * one + sc;  // I/D: -1 each, rare: +0x01010101 each
+          mxk = max(mxk, w & tc);
+          mxc = max(mxc, code);
         }
       }
       r = 0u - nr;
       q = 0u - nq;
-      em = __funnelshift_l(em, em, 4 * rot);  // loop chunk k is logical chunk (k+rot)&7
-      lane_rare = sc > 0 || mx > 8u;           // a rare code (N/H/P...) or a reserved one (9..15)
-      if (lane_rare) {                         // exact recomputation of this lane
-        em = 0;
-        for (int i = 0; i < WT_VPT; ++i) {
-          const uint32_t w = tl[lane * WT_VPT + i];
-          add_op<MODE>(w, xs);
-          em |= (((1u << (w & 15u)) & 6u) && w >= min_w) ? (1u << i) : 0u;
-        }
-        r = xs.r;
-        q = xs.q;
+      lane_rare = (int32_t)sc > 0 || mxc > 8u;  // a rare code (N/H/P...) or a reserved one (9..15)
+      lane_cand = mxk >= min_w || lane_rare;    // rare lanes: mxk is not trustworthy
+    }
+    // -- rare lanes: exact sums of every class, by the whole warp ---------------------------------
+    uint32_t rare_lanes = __ballot_sync(FULL, lane_rare);
+    const bool anyrare = rare_lanes != 0u;
+    while (rare_lanes) {
+      const int L = __ffs(rare_lanes) - 1;
+      rare_lanes &= rare_lanes - 1;
+      Sums o = {0, 0, 0, 0, 0};
+      add_op<MODE>(tl[L * WT_VPT + lane], o);
+      o.r = __reduce_add_sync(FULL, o.r); o.q = __reduce_add_sync(FULL, o.q);
+      o.x1 = __reduce_add_sync(FULL, o.x1);
+      if (M::NX > 1) o.x2 = __reduce_add_sync(FULL, o.x2);
+      if (M::NX > 2) o.x3 = __reduce_add_sync(FULL, o.x3);
+      if (lane == L) { xs = o; r = o.r; q = o.q; }
+    }
+    // -- candidate lanes: which of the lane's 32 ops are D/I >= min_len ---------------------------
+    uint32_t em = 0;
+    {
+      uint32_t cand_lanes = __ballot_sync(FULL, lane_cand);
+      while (cand_lanes) {
+        const int L = __ffs(cand_lanes) - 1;
+        cand_lanes &= cand_lanes - 1;
+        const uint32_t w = tl[L * WT_VPT + lane];
+        const uint32_t m = __ballot_sync(FULL, ((1u << (w & 15u)) & 6u) && w >= min_w);
+        if (lane == L) em = m;
       }
     }
     const uint32_t c = __popc(em);
@@ -440,7 +448,7 @@ __global__ void __launch_bounds__(SCAN_THREADS, SCAN_CTAS_PER_SM) k_scan_wt(cons
     }
     Sums ex = {ir - r, iq - q, 0, 0, 0};  // this lane's exclusive prefix inside the tile
     Sums tot = {__shfl_sync(FULL, ir, 31), __shfl_sync(FULL, iq, 31), 0, 0, 0};
-    const bool anyrare = __any_sync(FULL, lane_rare);
+    const uint32_t myoff = ic - c, coff = __shfl_sync(FULL, ic, 31);
     if (anyrare) {  // this warp saw N / H / P / ...: scan the rare sums too
       uint32_t i1 = xs.x1, i2 = xs.x2, i3 = xs.x3;
 #pragma unroll
@@ -455,32 +463,29 @@ __global__ void __launch_bounds__(SCAN_THREADS, SCAN_CTAS_PER_SM) k_scan_wt(cons
     }
 
     // -- record starts in this tile: in-tile prefix at each start -> fstart[rec] -------------
+    // start s begins at op x of the tile: prefix = exclusive prefix of lane x>>5 + the first x&31
+    // ops of that lane's row, summed by the whole warp (one LDS + REDUX per class).
     Sums f_last = {0, 0, 0, 0, 0};
-    for (int k0 = 0; k0 < nst; k0 += 32) {
-      const int k = k0 + lane;
-      const bool on = k < nst;
-      int32_t x = sx;
-      if (k0 > 0) x = on ? (int32_t)(__ldg(p.op_off + cur.x + k) - wt_start) : 0;
-      if (!on) x = 0;
+    for (int s = 0; s < nst; ++s) {
+      int32_t x = (s < 32) ? __shfl_sync(FULL, sx, s) : (int32_t)(__ldg(p.op_off + cur.x + s) - wt_start);
       const int t = x >> 5, n = x & 31;
       Sums f;
       f.r = __shfl_sync(FULL, ex.r, t); f.q = __shfl_sync(FULL, ex.q, t);
-      f.x1 = __shfl_sync(FULL, ex.x1, t); f.x2 = __shfl_sync(FULL, ex.x2, t); f.x3 = __shfl_sync(FULL, ex.x3, t);
-      if (on) {
-        const Sums wk = walk<MODE>(tl + t * WT_VPT, n, anyrare);
-        f.r += wk.r; f.q += wk.q; f.x1 += wk.x1; f.x2 += wk.x2; f.x3 += wk.x3;
-        store_sums(p.fstart + 2 * ((int64_t)cur.x + k), f);
+      Sums o = {0, 0, 0, 0, 0};
+      if (lane < n) add_op<MODE>(tl[t * WT_VPT + lane], o);
+      f.r += __reduce_add_sync(FULL, o.r); f.q += __reduce_add_sync(FULL, o.q);
+      f.x1 = 0; f.x2 = 0; f.x3 = 0;
+      if (anyrare) {
+        f.x1 = __shfl_sync(FULL, ex.x1, t) + __reduce_add_sync(FULL, o.x1);
+        if (M::NX > 1) f.x2 = __shfl_sync(FULL, ex.x2, t) + __reduce_add_sync(FULL, o.x2);
+        if (M::NX > 2) f.x3 = __shfl_sync(FULL, ex.x3, t) + __reduce_add_sync(FULL, o.x3);
       }
-      if (k0 + 32 >= nst) {  // last group: the last start's prefix goes to the aggregate
-        const int ll = (nst - 1) & 31;
-        f_last.r = __shfl_sync(FULL, f.r, ll); f_last.q = __shfl_sync(FULL, f.q, ll);
-        f_last.x1 = __shfl_sync(FULL, f.x1, ll); f_last.x2 = __shfl_sync(FULL, f.x2, ll);
-        f_last.x3 = __shfl_sync(FULL, f.x3, ll);
-      }
+      if (lane == (s & 31)) store_sums(p.fstart + 2 * ((int64_t)cur.x + s), f);
+      f_last = f;
     }
 
     // -- raw candidates -> staging entries (op order), chunked slot reservation ---------------
-    const uint32_t ncand = __shfl_sync(FULL, ic, 31);
+    const uint32_t ncand = coff;
     unsigned long long base = ~0ull;
     if (ncand) {
       if (lane == 0) {
@@ -498,7 +503,7 @@ __global__ void __launch_bounds__(SCAN_THREADS, SCAN_CTAS_PER_SM) k_scan_wt(cons
       }
       base = __shfl_sync(FULL, base, 0);
       if (em && base != ~0ull) {
-        uint4* dst = reinterpret_cast<uint4*>(p.stage + base + (ic - c));
+        uint4* dst = reinterpret_cast<uint4*>(p.stage + base + myoff);
         uint32_t m = em;
         while (m) {
           const int s = __ffs(m) - 1;
@@ -553,12 +558,31 @@ __global__ void __launch_bounds__(128) k_gate(const ScanParams p) {
       const uint32_t* row = p.ops + wt_start + (j & ~31);
       const int n = j & 31;
       Sums f = {e0.z, e0.w, e1.x, e1.y, e1.z};
-      {
+      uint32_t w = 0;
+      {  // ops 0..n-1 of the candidate's 128-byte row, read as LDG.128 (the row never crosses n_ops
+         // before op n, but its tail may: only whole uint4 groups that lie inside the array are vector loads)
         Sums wk = {0, 0, 0, 0, 0};
-        for (int u = 0; u < n; ++u) add_op<MODE>(__ldg(row + u), wk);
+        const int64_t left = p.n_ops - (wt_start + (j & ~31));
+        for (int g4 = 0; g4 * 4 <= n; ++g4) {
+          uint4 v;
+          if ((int64_t)(g4 * 4 + 4) <= left) {
+            v = __ldg(reinterpret_cast<const uint4*>(row) + g4);
+          } else {
+            v.x = g4 * 4 < left ? __ldg(row + g4 * 4) : 0u;
+            v.y = g4 * 4 + 1 < left ? __ldg(row + g4 * 4 + 1) : 0u;
+            v.z = g4 * 4 + 2 < left ? __ldg(row + g4 * 4 + 2) : 0u;
+            v.w = 0u;
+          }
+          const uint32_t vv[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const int idx = g4 * 4 + u;
+            if (idx < n) add_op<MODE>(vv[u], wk);
+            if (idx == n) w = vv[u];
+          }
+        }
         f.r += wk.r; f.q += wk.q; f.x1 += wk.x1; f.x2 += wk.x2; f.x3 += wk.x3;
       }
-      const uint32_t w = __ldg(row + n);
       const int32_t rec = rec_of_op(p.op_off, lo, hi, wt_start + j);
       const bool carry = __ldg(p.op_off + rec) < wt_start;
       const Sums part = carry ? f : f - load_sums(p.fstart + 2 * (int64_t)rec);
@@ -663,8 +687,14 @@ struct ScanCall {
 };
 
 template <int MODE>
-static int run_scan_kernels(vsv_ctx* ctx, const ScanParams& p, int grid, TileState* d_excl, vsv_sig* out_a, int64_t cap_a,
+static int run_scan_kernels(vsv_ctx* ctx, const ScanParams& p_in, int grid, TileState* d_excl, vsv_sig* out_a, int64_t cap_a,
                             vsv_sig* out_b, int64_t cap_b, int64_t* d_nout, uint32_t* rt, uint32_t* qt, uint32_t* xt) {
+  typedef ModeTraits<MODE> M;
+  constexpr uint32_t RARE = M::X1 | M::X2 | M::X3;
+  ScanParams p = p_in;
+  p.tab[0] = tab_word(M::REF, 0, 0xFFu, 0, 0); p.tab[1] = tab_word(M::REF, 4, 0xFFu, 0, 0);
+  p.tab[2] = tab_word(M::QRY, 0, 0xFFu, 0, 0); p.tab[3] = tab_word(M::QRY, 4, 0xFFu, 0, 0);
+  p.tab[4] = tab_word(6u, 0, 0xFFu, RARE, 0x01u); p.tab[5] = tab_word(6u, 4, 0xFFu, RARE, 0x01u);
   VSV_CUDA(ctx, cudaEventRecord(ctx->evk0, ctx->stream));
   VSV_LAUNCH(ctx, k_scan_wt<MODE>, (unsigned)grid, SCAN_THREADS, 0, p);
   VSV_CUDA(ctx, cudaEventRecord(ctx->evk1, ctx->stream));
@@ -763,6 +793,7 @@ static int scan_impl(vsv_ctx* ctx, const ScanCall& c) {
   p.rec_info = d_info;
   p.n_rec = c.n_rec; p.n_ops = n_ops; p.n_wt = n_wt;
   p.min_len_a = c.min_len_a; p.min_len_b = c.min_len_b;
+  p.one = 1u;
   p.min_w = (uint32_t)(fused ? std::min(c.min_len_a, c.min_len_b) : c.min_len_a) << 4;
   p.wt_starts = d_starts; p.wt_agg = d_agg; p.wt_stage = d_wstage; p.fstart = d_fstart;
   p.stage_ctr = reinterpret_cast<unsigned long long*>(d_nout + 2);
