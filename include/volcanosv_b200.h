@@ -217,6 +217,15 @@ int vsv_genotype(vsv_ctx* ctx, const int32_t* read_start, const int32_t* read_en
                  const double* thr_del, const double* thr_ins, int32_t* depth2, double* ratio,
                  int32_t* new_gt);
 
+/* ---- redundancy: batched global edit distance ------------------------------------ */
+/* Replaces edlib.align(a, b)["editDistance"] at LI/remove_redundancy.py:75-81 (global /
+ * Needleman-Wunsch, unit costs) for a batch of string pairs: strings are rows of a table
+ * (chars, str_off[n_str+1]); pair p compares strings ia[p] and ib[p].  Exact (Myers/Hyyro
+ * bit-vector).  A string may use at most 16 distinct byte values (DNA alphabets), else
+ * VSV_E_ARG.  Host buffers only. */
+int vsv_edit_distance_batch(vsv_ctx* ctx, const uint8_t* chars, const int64_t* str_off, int64_t n_str,
+                            const int32_t* ia, const int32_t* ib, int64_t n_pair, int32_t* dist);
+
 #ifdef __cplusplus
 }
 #endif

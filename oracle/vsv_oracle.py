@@ -620,3 +620,25 @@ def sa_split_analysis(seg, L, sv_size=30, max_size=100000, max_parts=7):
                 h = int(dis_ref / 2)
                 out.append((INS, min(e2[2], e1[3]), dis_read - dis_ref, e1[1] + h, e2[0] - h, rev))
     return out
+
+
+# --------------------------------------------------------------------------- edit distance
+def edit_distance(a, b):
+    """Global unit-cost edit distance: what remove_redundancy.py takes from
+    edlib.align(a, b)["editDistance"] (RR:75-81; third-party edlib 1.3.9, mode NW).  The value
+    is algorithm-independent; this is the textbook row DP (numpy prefix-min for the in-row
+    dependency)."""
+    import numpy as np
+    n, m = len(a), len(b)
+    if n == 0 or m == 0:
+        return n + m
+    bb = np.frombuffer(b.encode() if isinstance(b, str) else bytes(b), dtype=np.uint8)
+    aa = a.encode() if isinstance(a, str) else bytes(a)
+    prev = np.arange(m + 1, dtype=np.int64)
+    idx = np.arange(m + 1, dtype=np.int64)
+    for i in range(1, n + 1):
+        cur = np.empty(m + 1, dtype=np.int64)
+        cur[0] = i
+        cur[1:] = np.minimum(prev[:-1] + (bb != aa[i - 1]), prev[1:] + 1)
+        prev = np.minimum.accumulate(cur - idx) + idx
+    return int(prev[m])

@@ -271,3 +271,35 @@ def test_sa_analysis_random_vs_oracle(ctx):
     assert len(ctx.sa_analysis([0], [], [], [], [], [], [], [])) == 0
     with pytest.raises(V.VsvError):
         ctx.sa_analysis([0, 2], [0, 5], [5, 9], [1, 2], [3, 4], [1, 1], [0, 0], [100], max_parts=40)
+
+
+def test_edit_distance_batch(ctx):
+    """vsv_edit_distance_batch == edlib NW distance (RR:75-81): known answers, random pairs against
+    the oracle DP, block-edge lengths, long strings, empty strings."""
+    import random
+    rng = random.Random(7)
+    strs = ["kitten", "sitting", "", "ACGT", "ACGTACGTNN", "A" * 64, "A" * 63 + "C", "C" * 65]
+    pairs = [(0, 1), (2, 3), (3, 2), (2, 2), (3, 4), (5, 6), (5, 7), (6, 7), (4, 4)]
+    for m in (1, 31, 63, 64, 65, 127, 128, 129, 500, 2100, 5000):
+        a = "".join(rng.choice("ACGT") for _ in range(m))
+        b = list(a)
+        for _ in range(rng.randint(0, max(1, m // 10))):
+            k = rng.randrange(len(b)) if b else 0
+            u = rng.random()
+            if u < 0.3 and len(b) > 1:
+                b.pop(k)
+            elif u < 0.6:
+                b.insert(k, rng.choice("ACGTN"))
+            elif b:
+                b[k] = rng.choice("ACGT")
+        c = "".join(rng.choice("ACGTN") for _ in range(rng.choice([m, m // 2 + 1, 2 * m + 3])))
+        base = len(strs)
+        strs += [a, "".join(b), c]
+        pairs += [(base, base + 1), (base + 1, base), (base, base + 2), (base + 2, base + 1)]
+    got = ctx.edit_distance_batch(strs, [p[0] for p in pairs], [p[1] for p in pairs])
+    assert int(got[0]) == 3 and int(got[1]) == 4 and int(got[3]) == 0
+    for (i, j), g in zip(pairs, got):
+        assert int(g) == O.edit_distance(strs[i], strs[j]), (len(strs[i]), len(strs[j]))
+    with pytest.raises(V.VsvError):
+        ctx.edit_distance_batch(["ABCDEFGHIJKLMNOPQRS", "ABC"], [0], [1])
+    assert len(ctx.edit_distance_batch(["A"], [], [])) == 0

@@ -68,6 +68,7 @@ SIGNATURES = {
     "vsv_group_sigs": [_vp, _vp, _vp, _vp, _i64, _int, _vp, _vp, _vp, _vp, C.POINTER(_i64)],
     "vsv_sig_support": [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _i64, _i32, _vp, _vp, C.POINTER(_i32)],
     "vsv_span_depth": [_vp, _vp, _vp, _i64, _vp, _vp, _i64, _vp],
+    "vsv_edit_distance_batch": [_vp, _vp, _vp, _i64, _vp, _vp, _i64, _vp],
     "vsv_genotype": [_vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp],
 }
 _RESTYPE = {"vsv_ctx_destroy": None, "vsv_last_error": C.c_char_p, "vsv_version": C.c_char_p}
@@ -326,6 +327,18 @@ class Context:
         self._chk(self.lib.vsv_genotype(self.h, _p(rs), _p(re), len(rs), _p(cp), _p(cl), _p(ct), _p(cg), _p(ns), n,
                                         _p(td), _p(ti), _p(d2), _p(ratio), _p(ng)))
         return d2, ratio, ng
+
+
+    def edit_distance_batch(self, strings, ia, ib):
+        """Global edit distance of strings[ia[p]] vs strings[ib[p]] (edlib NW distance, RR:75-81)."""
+        bs = [x.encode() if isinstance(x, str) else bytes(x) for x in strings]
+        off = np.zeros(len(bs) + 1, np.int64)
+        np.cumsum([len(b) for b in bs], out=off[1:])
+        chars = np.frombuffer(b"".join(bs) + b"\0", dtype=np.uint8)
+        ia, ib = _arr(ia, np.int32), _arr(ib, np.int32)
+        out = np.zeros(len(ia), np.int32)
+        self._chk(self.lib.vsv_edit_distance_batch(self.h, _p(chars), _p(off), len(bs), _p(ia), _p(ib), len(ia), _p(out)))
+        return out
 
 
 def _aligned_empty(n, dtype, align=64):

@@ -587,7 +587,13 @@ def correct_gt(input_path: str, output_path: str, bamfile: str, sigfile: str, dt
             rows.append("%d\t%d\t%d\t%s\t%s\t%d\t%d\t%d\t%s" % (int(chrom[i][3:]), pos[i], svlen[i], gt[i], svid[i], match_id[i],
                                                                sup[i], int(depth2[i]) // 2, _fl(float(ratio[i]))))
     _write_lines(output_path, [hdr + "\n"] + [r + "\n" for r in rows])
-    _write_lines(output_path + ".newgt", [hdr + "\tnew_gt\n"] + [r + "\t" + g + "\n" for r, g in zip(rows, new_gt)])
+    # the reference re-reads its TSV with pandas and writes it back with the new column (GTD:379-382,
+    # GTI:341-344); pandas' default float parser is not round-trip exact, so the n_ratio TEXT of the
+    # .newgt file can differ from the first file in the last digit: do the same round trip
+    import pandas as pd
+    df = pd.read_csv(output_path, sep="\t")
+    df["new_gt"] = new_gt
+    df.to_csv(output_path + ".newgt", sep="\t", index=False)
     by_id = dict(zip(svid, new_gt))
     out = []
     for ln in lines:
@@ -656,3 +662,394 @@ def phase_vcf(infile: str, outfile: str, header_file: str):
             d[-1] = gt
             out.append("\t".join(d) + "\n")
     _write_lines(outfile, out)
+
+
+# --------------------------------------------------------------------------- ECS (contig signatures -> raw VCF)
+_HG19 = [249250621, 243199373, 198022430, 191154276, 180915260, 171115067, 159138663, 146364022, 141213431, 135534747,
+         135006516, 133851895, 115169878, 107349540, 102531392, 90354753, 81195210, 78077248, 59128983, 63025520,
+         48129895, 51304566]
+_INFO_LINES = [
+    '##INFO=<ID=SVTYPE,Number=1,Type=String,Description="Type of SV:DEL=Deletion, CON=Contraction, INS=Insertion, DUP=Duplication, INV=Inversion">\n',
+    '##INFO=<ID=SVLEN,Number=.,Type=Integer,Description="Difference in length between REF and ALT alleles">\n',
+    '##INFO=<ID=TIG_REGION,Number=.,Type=String,Description="Contig region where variant was found (one per alt with h1 before h2 for homozygous calls)">\n',
+    '##INFO=<ID=QUERY_STRAND,Number=.,Type=String,Description="Strand of variant in the contig relative to the reference (order follows TIG_REGION)">\n',
+    '##INFO=<ID=SIG_SOURCE,Number=.,Type=String,Description="Source of the variant call signature (order follows TIG_REGION)">\n',
+    '##INFO=<ID=TIG_MAPQ,Number=.,Type=String,Description="Mapping quality of the contigs (order follows TIG_REGION)">\n',
+    '##INFO=<ID=CollapseId,Number=1,Type=Integer,Description="collapse match ID">\n',
+]
+
+
+def default_header() -> List[str]:
+    """The per-chromosome VCF header the reference ships as LI/header (sample column HG002; RVC:42-43)."""
+    h = ["##fileformat=VCFv4.2\n", '##FILTER=<ID=PASS,Description="All filters passed">\n', "##fileDate=20180605\n",
+         "##reference=GRCh37\n"]
+    h += ["##contig=<ID=chr%d,length=%d>\n" % (i + 1, n) for i, n in enumerate(_HG19)]
+    h += _INFO_LINES
+    h += ['##FORMAT=<ID=GT,Number=1,Type=String,Description="Genotype">\n',
+          "#CHROM\tPOS\tID\tREF\tALT\tQUAL\tFILTER\tINFO\tFORMAT\tHG002\n"]
+    return h
+
+
+def final_header_info(prefix: str) -> List[str]:
+    """LI/header_info with "Sample" -> prefix (MAIN:125-129)."""
+    lines = _INFO_LINES + ['##INFO=<ID=PS,Number=.,Type=Integer,Description="phase block name">\n',
+                           '##FORMAT=<ID=GT,Number=1,Type=String,Description="Genotype">\n',
+                           "#CHROM\tPOS\tID\tREF\tALT\tQUAL\tFILTER\tINFO\tFORMAT\tSample\n"]
+    return [ln.replace("Sample", prefix) for ln in lines]
+
+
+def load_contigs(path: str) -> Dict[str, str]:
+    """load_contigs (ECS_H:605-622): the record name is the whole header line after '>'."""
+    d: Dict[str, List[str]] = {}
+    cur = None
+    op = gzip.open if path.endswith(".gz") else open
+    with op(path, "rt") as f:
+        for line in f:
+            if ">" in line:
+                cur = line[1:-1]
+            else:
+                d.setdefault(cur, []).append(line[:-1])
+    return {k: "".join(v) for k, v in d.items()}
+
+
+_RC = {"N": "N", "A": "T", "T": "A", "G": "C", "C": "G"}
+
+
+def _revcomp(seq: str) -> str:
+    return "".join(_RC[c] for c in seq.upper()[::-1])        # other letters raise, as ECS_H:626-632
+
+
+def _cluster_rows(ctx, rows, is_del):
+    """sort_sig + cluster_del / cluster_ins (ECS_H:170-288) on 10-field signature rows."""
+    if not rows:
+        return []
+    order = ctx.argsort_stable(np.asarray([r[2] for r in rows], dtype=np.int32))
+    rows = [rows[i] for i in order]
+    keep = ctx.cluster(is_del, [r[2] for r in rows], [r[3] for r in rows])
+    return [rows[i] for i in keep]
+
+
+def _sort_rows(ctx, rows):
+    if not rows:
+        return []
+    order = ctx.argsort_stable(np.asarray([r[2] for r in rows], dtype=np.int32))
+    return [rows[i] for i in order]
+
+
+def _contig_one_hap(ctx, R: Records, chrom, hp, dtype, min_cigar_mapq, min_split_mapq, sig_dir):
+    strand = ["-" if x else "+" for x in R.is_rev]
+    has_hp = np.asarray([hp in nm for nm in R.qname], dtype=bool)
+    enable = has_hp.copy()
+    if dtype == "CLR":                                     # ECS_C:53-70,425-427: ins_pct <= 0.13 or mean M run >= 200
+        codes, lens = (R.ops & 15).astype(np.int64), (R.ops >> 4).astype(np.int64)
+        for r in range(R.n):
+            a, b = int(R.op_off[r]), int(R.op_off[r + 1])
+            c, l = codes[a:b], lens[a:b]
+            m_sum, m_cnt, i_sum = int(l[c == 0].sum()), int((c == 0).sum()), int(l[c == 1].sum())
+            ip = i_sum / (m_sum + i_sum)
+            vd = m_sum / m_cnt
+            enable[r] = enable[r] and (ip <= 0.13 or vd >= 200)
+    sigs, rt, qt, xt = ctx.scan_cigar(L.MODE_CONTIG, R.ops, R.op_off, R.pos, R.mapq, enable=enable.astype(np.uint8),
+                                      min_len=30, min_mapq=min_cigar_mapq)
+    d, s = ctx.merge_in_record(L.MODE_CONTIG, sigs)
+
+    def rows_of(a, tp):
+        return [[chrom, tp, int(x["pos"]), int(x["len"]), R.qname[x["rec"]], int(x["q0"]), int(x["q1"]), strand[x["rec"]],
+                 "cigar", int(R.mapq[x["rec"]])] for x in a]
+    del_c, ins_c = _sort_rows(ctx, rows_of(d, "DEL")), _sort_rows(ctx, rows_of(s, "INS"))
+    fmt = lambda rows: ["\t".join(str(x) for x in r) + "\n" for r in rows]
+    if sig_dir:
+        _write_lines("%s/%s_DEL_contig_cigar_%s.txt" % (sig_dir, chrom, hp), fmt(del_c))
+        _write_lines("%s/%s_INS_contig_cigar_%s.txt" % (sig_dir, chrom, hp), fmt(ins_c))
+    del_cc, ins_cc = _cluster_rows(ctx, del_c, True), _cluster_rows(ctx, ins_c, False)
+    # split alignments (ECS_H:421-476): names with >= 2 records passing hp + mapq
+    ok = has_hp & (R.mapq >= min_split_mapq)
+    cnt = Counter(nm for nm, k in zip(R.qname, ok) if k)
+    first_seen: Dict[str, int] = {}
+    for nm, k in zip(R.qname, ok):
+        if k and nm not in first_seen:
+            first_seen[nm] = len(first_seen)
+    select = np.asarray([1 if (k and cnt[nm] > 1) else 0 for nm, k in zip(R.qname, ok)], dtype=np.uint8)
+    name_id = np.asarray([first_seen.get(nm, 0) for nm in R.qname], dtype=np.int32)
+    variant = {"Hifi": L.SPLIT_HIFI, "ONT": L.SPLIT_ONT, "CLR": L.SPLIT_CLR}[dtype]
+    sp = ctx.split_pairs(variant, min_split_mapq, R.pos, (R.pos + rt).astype(np.int32), (qt + xt).astype(np.int32), R.first_op,
+                         R.last_op, R.mapq, R.is_rev, name_id, select) if R.n >= 2 else np.zeros(0, L.SIG_DTYPE)
+
+    def split_rows(tp, code):
+        return [[chrom, tp, int(x["pos"]), int(x["len"]), R.qname[x["rec"]], int(x["q0"]), int(x["q1"]), strand[x["rec"]],
+                 "split-alignment", "%d-%d" % (int(R.mapq[x["rec"]]), int(R.mapq[x["first"]]))] for x in sp if int(x["type"]) == code]
+    del_s, ins_s = _sort_rows(ctx, split_rows("DEL", L.DEL)), _sort_rows(ctx, split_rows("INS", L.INS))
+    if sig_dir:
+        _write_lines("%s/%s_DEL_contig_split_%s.txt" % (sig_dir, chrom, hp), fmt(del_s))
+        _write_lines("%s/%s_INS_contig_split_%s.txt" % (sig_dir, chrom, hp), fmt(ins_s))
+    del_sc, ins_sc = _cluster_rows(ctx, del_s, True), _cluster_rows(ctx, ins_s, False)
+    ins_final = _cluster_rows(ctx, ins_cc + ins_sc, False)                                     # merge_all, ECS_H:478-499
+    del_final = _cluster_rows(ctx, del_cc + del_sc, True)
+    return _sort_rows(ctx, ins_final + del_final)
+
+
+def extract_contig_signature(bam_path: str, contig_path: str, ref_path: str, output_dir: str, chr_number: Optional[int] = None,
+                             dtype: str = "Hifi", header_path: Optional[str] = None, min_cigar_mapq: int = 50,
+                             min_split_mapq: int = 50):
+    """LI/extract_contig_signature_{Hifi,ONT,CLR}.py -bam -contig -header -ref -o -chr: writes
+    <o>/volcano_variant_chrN.vcf (+ the signature/ side files)."""
+    ctx = context()
+    sig_dir = os.path.join(output_dir, "signature")
+    os.makedirs(sig_dir, exist_ok=True)
+    dc_contig = load_contigs(contig_path)
+    dc_ref = load_contigs(ref_path)
+    header = open(header_path).readlines() if header_path else default_header()
+    src = open_alignments(bam_path)
+    for i in ([chr_number] if chr_number is not None else range(1, 23)):
+        chrom = "chr%d" % i
+        ref_seq = dc_ref[chrom]
+        R = src.records(chrom)
+        hp1 = _contig_one_hap(ctx, R, chrom, "hp1", dtype, min_cigar_mapq, min_split_mapq, sig_dir)
+        hp2 = _contig_one_hap(ctx, R, chrom, "hp2", dtype, min_cigar_mapq, min_split_mapq, sig_dir)
+        tcode = lambda rows: [L.DEL if r[1] == "DEL" else L.INS for r in rows]
+        if hp1 and hp2:
+            p1, p2 = ctx.pair_haps([r[2] for r in hp1], [r[3] for r in hp1], tcode(hp1), [r[2] for r in hp2], [r[3] for r in hp2],
+                                   tcode(hp2))
+        else:
+            p1, p2 = [-1] * len(hp1), [-1] * len(hp2)
+        info = lambda r: "%s:%d-%d" % (r[4], r[5], r[6])
+        paired = []
+        for k, s1 in enumerate(hp1):                                                         # ECS_H:571-592
+            if p1[k] < 0:
+                paired.append(s1 + ["0/1", info(s1), s1[7], s1[8], str(s1[9])])
+            else:
+                s2 = hp2[int(p1[k])]
+                extra = ["1/1", info(s1) + "," + info(s2), s1[7] + "," + s2[7], s1[8] + "," + s2[8], str(s1[9]) + "," + str(s2[9])]
+                paired.append((s1 if s1[3] > s2[3] else s2) + extra)
+        for k, s2 in enumerate(hp2):
+            if p2[k] < 0:
+                paired.append(s2 + ["0/1", info(s2), s2[7], s2[8], str(s2[9])])
+        paired = _sort_rows(ctx, paired)
+        out, n_ins, n_del = list(header), 0, 0
+        for sig in paired:                                                                   # add_seq_to_sig + write_vcf
+            if sig[4] not in dc_contig:
+                continue
+            if sig[1] == "INS":
+                sc = dc_contig[sig[4]]
+                seq = _revcomp(sc[-sig[6]:-sig[5]]) if sig[7] == "-" else sc[sig[5]:sig[6]]
+            else:
+                seq = ref_seq[sig[2]:sig[2] + sig[3]]
+            anchor = ref_seq[sig[2] - 1]
+            if sig[1] == "DEL":
+                ref_a, alt_a = anchor + seq, anchor
+                n_del += 1
+                k = n_del
+            else:
+                ref_a, alt_a = anchor, anchor + seq
+                n_ins += 1
+                k = n_ins
+            svinfo = "SVLEN=%d;SVTYPE=%s;TIG_REGION=%s;QUERY_STRAND=%s;SIG_SOURCE=%s;TIG_MAPQ=%s" % (
+                len(alt_a) - len(ref_a), sig[1], sig[11], sig[12], sig[13], sig[14])
+            out.append("%s\t%d\tvolcano.%s.%s.%d\t%s\t%s\t%d\tPASS\t%s\tGT\t%s\n" % (chrom, sig[2], chrom, sig[1], k, ref_a.upper(),
+                                                                                   alt_a.upper(), 20, svinfo, sig[10]))
+        _write_lines(os.path.join(output_dir, "volcano_variant_chr%d.vcf" % i), out)
+
+
+# --------------------------------------------------------------------------- RR (remove_redundancy)
+def _sort_calls(ctx, calls):
+    """sort_sig (RR:26-48): chr1..chr22, stable by POS inside each."""
+    out = []
+    for i in range(1, 23):
+        c = [x for x in calls if x[0] == "chr%d" % i]
+        if c:
+            order = ctx.argsort_stable(np.asarray([x[1] for x in c], dtype=np.int32))
+            out += [c[k] for k in order]
+    return out
+
+
+def _components(links):
+    """Connected components in networkx order (RR:156-160): nodes in edge-insertion order, a
+    component is numbered when its first node is reached."""
+    adj: Dict[str, List[str]] = {}
+    for a, b in links:
+        adj.setdefault(a, []).append(b)
+        adj.setdefault(b, []).append(a)
+    seen, comps = set(), []
+    for n in adj:
+        if n in seen:
+            continue
+        comp, stack = [], [n]
+        seen.add(n)
+        while stack:
+            v = stack.pop()
+            comp.append(v)
+            for w in adj[v]:
+                if w not in seen:
+                    seen.add(w)
+                    stack.append(w)
+        comps.append(comp)
+    return comps
+
+
+def remove_redundancy(input_path: str, output_dir: str, dist_thresh: int = 500, dist_thresh_del: int = 3000,
+                      overlap_thresh: float = 0.0, size_sim_thresh: float = 0.5, size_sim_thresh_del: float = 0.1,
+                      seq_sim_thresh: float = 0.5):
+    """LI/remove_redundancy.py -i <vcf> -o <dir>: writes volcano_variant_no_redundancy.vcf and
+    volcano_variant_redundancy.vcf (RR:51-291).  Insertion pairs are compared by global edit distance
+    on the GPU (vsv_edit_distance_batch replaces edlib, RR:75-81).  Tie pin: among the
+    longest members of a component the one earliest in VCF order is kept."""
+    ctx = context()
+    os.makedirs(output_dir, exist_ok=True)
+    header, dels, inss, dc = [], [], [], {}
+    order_of: Dict[str, int] = {}
+    with open(input_path) as f:
+        for line in f:
+            if line[0] == "#":
+                header.append(line)
+                continue
+            d = line.split()
+            d[1] = int(d[1])
+            d[3], d[4] = d[3].upper(), d[4].upper()
+            order_of.setdefault(d[2], len(order_of))
+            dc[d[2]] = d
+            if "SVTYPE=DEL" in line:
+                dels.append(d)
+            elif "SVTYPE=INS" in line:
+                inss.append(d)
+    header = header[:-2] + ['##INFO=<ID=CollapseId,Number=1,Type=Integer,Description="collapse match ID">\n'] + header[-2:]
+    dels, inss = _sort_calls(ctx, dels), _sort_calls(ctx, inss)
+    svlen = lambda x: abs(len(x[3]) - len(x[4]))
+
+    def windows(calls, thresh):
+        """(i, j) with i != j, same chromosome, |POS_j - POS_i| <= thresh, in the reference's loop order."""
+        for i in range(1, 23):
+            c = [x for x in calls if x[0] == "chr%d" % i]
+            lo = 0
+            for a in range(len(c)):
+                while c[lo][1] < c[a][1] - thresh:
+                    lo += 1
+                b = lo
+                while b < len(c) and c[b][1] <= c[a][1] + thresh:
+                    if b != a:
+                        yield c[a], c[b]
+                    b += 1
+    links_del = []
+    for s1, s2 in windows(dels, dist_thresh_del):
+        l1, l2 = svlen(s1), svlen(s2)
+        if min(l1, l2) / max(l1, l2) >= size_sim_thresh_del:
+            ov = (min(s1[1] + l1, s2[1] + l2) - max(s1[1], s2[1])) / max(l1, l2)
+            if ov >= overlap_thresh:
+                links_del.append((s1[2], s2[2]))
+    cand = []
+    for s1, s2 in windows(inss, dist_thresh):
+        l1, l2 = svlen(s1), svlen(s2)
+        if min(l1, l2) / max(l1, l2) >= size_sim_thresh:
+            cand.append((s1, s2))
+    links_ins = []
+    if cand:
+        ids = {}
+        strs = []
+        for s1, s2 in cand:
+            for s in (s1, s2):
+                if s[2] not in ids:
+                    ids[s[2]] = len(strs)
+                    strs.append(s[4])
+        uniq = {}
+        for s1, s2 in cand:                                  # each unordered pair once
+            k = (min(ids[s1[2]], ids[s2[2]]), max(ids[s1[2]], ids[s2[2]]))
+            uniq.setdefault(k, len(uniq))
+        keys = list(uniq)
+        dist = ctx.edit_distance_batch(strs, [k[0] for k in keys], [k[1] for k in keys])
+        for s1, s2 in cand:
+            k = (min(ids[s1[2]], ids[s2[2]]), max(ids[s1[2]], ids[s2[2]]))
+            tot = len(s1[4]) + len(s2[4])
+            if (tot - int(dist[uniq[k]])) / tot >= seq_sim_thresh:
+                links_ins.append((s1[2], s2[2]))
+
+    def pick(comps):
+        retain, remove = {}, {}
+        for i, comp in enumerate(comps):
+            best = max(comp, key=lambda x: (svlen(dc[x]), -order_of[x]))
+            retain[best] = i
+            for x in comp:
+                if x != best:
+                    remove[x] = i
+        return retain, remove
+    ret_d, rem_d = pick(_components(links_del))
+    ret_i, rem_i = pick(_components(links_ins))
+    keep, drop = [], []
+    for idx, sig in dc.items():
+        if idx in ret_d:
+            sig[7] += ";CollapseId=DEL%d" % ret_d[idx]
+            keep.append(sig)
+        elif idx in ret_i:
+            sig[7] += ";CollapseId=INS%d" % ret_i[idx]
+            keep.append(sig)
+        elif idx in rem_d:
+            sig[7] += ";CollapseId=DEL%d" % rem_d[idx]
+            drop.append(sig)
+        elif idx in rem_i:
+            sig[7] += ";CollapseId=INS%d" % rem_i[idx]
+            drop.append(sig)
+        else:
+            keep.append(sig)
+    fmt = lambda calls: ["\t".join(str(x) for x in c) + "\n" for c in _sort_calls(ctx, calls)]
+    _write_lines(os.path.join(output_dir, "volcano_variant_redundancy.vcf"), header + fmt(drop))
+    _write_lines(os.path.join(output_dir, "volcano_variant_no_redundancy.vcf"), header + fmt(keep))
+
+
+# --------------------------------------------------------------------------- drivers (RVC, MAIN)
+def raw_variant_call(contig_bam: str, contig_path: str, reference_path: str, output_dir: str, dtype: str, chr_num: int,
+                     rbam_file: Optional[str] = None, signature_dir: Optional[str] = None, header_file: Optional[str] = None):
+    """LI/Raw_variant_call.py after its alignment step (RVC:65-105; minimap2/samtools are out of scope:
+    the caller hands over the sorted contig alignments)."""
+    os.makedirs(output_dir, exist_ok=True)
+    extract_contig_signature(contig_bam, contig_path, reference_path, output_dir, chr_num, dtype, header_file)
+    header = open(header_file).readlines() if header_file else default_header()
+    body = []
+    import glob
+    for p in sorted(glob.glob(os.path.join(output_dir, "volcano_variant_chr*vcf"))):
+        body += [ln for ln in open(p) if "#" not in ln]                                     # RVC:77 `grep -v "#"`
+    raw = os.path.join(output_dir, "volcano_raw_variant.vcf")
+    _write_lines(raw, header + body)
+    if signature_dir is None:
+        extract_reads_signature(rbam_file, output_dir, chr_num)
+        signature_dir = os.path.join(output_dir, "reads_signature")
+    filtered = os.path.join(output_dir, "volcano_variant_filtered.vcf")
+    fp_filter(raw, signature_dir, filtered)
+    remove_redundancy(filtered, os.path.join(output_dir, "final_vcf"))
+    return os.path.join(output_dir, "final_vcf", "volcano_variant_no_redundancy.vcf")
+
+
+def large_indel_chr(contig_bam: str, contig_path: str, reference: str, rbam_file: str, output_dir: str, dtype: str,
+                    chr_num: int, prefix: str = "Sample", read_signature_dir: Optional[str] = None,
+                    pre_cutesig: Optional[str] = None):
+    """LI/volcanosv-vc-large-indel.py ... -chr N (MAIN:233-319) with the contig alignments supplied:
+    header, per-chromosome chain, filter + genotype correction, phasing."""
+    out_chr = os.path.join(output_dir, "chr%d" % chr_num)
+    os.makedirs(out_chr, exist_ok=True)
+    ref = load_contigs(reference)
+    vcf_header = ["##fileformat=VCFv4.2\n"] + ["##contig=<ID=%s,length=%d>\n" % (k, len(v)) for k, v in ref.items()
+                                             if k == "chr%d" % chr_num]
+    header_file = os.path.join(out_chr, "VCF_header")
+    _write_lines(header_file, vcf_header + final_header_info(prefix))
+    with open(reference + ".fai", "w") as f:                                               # samtools faidx (MAIN:88-96)
+        off = 0
+        with open(reference, "rb") as fa:
+            data = fa.read().split(b"\n")
+        pos, name, ln, lb, start = 0, None, 0, None, 0
+        for row in data:
+            if row.startswith(b">"):
+                if name is not None:
+                    f.write("%s\t%d\t%d\t%d\t%d\n" % (name, ln, start, lb, lb + 1))
+                name, ln, lb, start = row[1:].split()[0].decode(), 0, None, pos + len(row) + 1
+            elif row:
+                lb = lb or len(row)
+                ln += len(row)
+            pos += len(row) + 1
+        if name is not None:
+            f.write("%s\t%d\t%d\t%d\t%d\n" % (name, ln, start, lb, lb + 1))
+    ref_dir = os.path.join(out_chr, "ref_by_chr")
+    os.makedirs(ref_dir, exist_ok=True)
+    one = os.path.join(ref_dir, "chr%d.fa" % chr_num)
+    _write_lines(one, [">chr%d\n" % chr_num] + [ref["chr%d" % chr_num][i:i + 60] + "\n" for i in range(0, len(ref["chr%d" % chr_num]), 60)])
+    raw = raw_variant_call(contig_bam, contig_path, one, out_chr, dtype, chr_num, rbam_file, read_signature_dir)
+    final = filter_gt_correction(raw, rbam_file, reference, dtype, chr_num, pre_cutesig)
+    outfile = os.path.join(out_chr, "%s_volcanosv_large_indel_chr%d.vcf" % (prefix, chr_num))
+    phase_vcf(final, outfile, header_file)
+    return outfile
