@@ -97,6 +97,14 @@ int vsv_scan_cigar(vsv_ctx* ctx, int mode, int min_len, int min_mapq, const uint
                    const uint8_t* enable, int64_t n_rec, vsv_sig* out, int64_t cap,
                    int64_t* n_out, int32_t* ref_total, int32_t* qry_total, int32_t* aux_total);
 
+/* Compact host->device staging of the packed ops.  ops16[i] = len << 4 | op when len < 4095,
+ * else 0xFFF << 4 | op with the full BAM-native word in the sparse exception list
+ * (exc_idx ascending op indices, exc_val).  Writes the u32 array vsv_scan_* read (ops_out,
+ * 16-byte aligned).  PCIe bytes per op drop from 4 to 2; the scanners are unchanged.  The
+ * host side of the format is volcanosv_b200.lib.pack_ops16. */
+int vsv_expand_ops16(vsv_ctx* ctx, const uint16_t* ops16, int64_t n_ops, const int64_t* exc_idx,
+                     const uint32_t* exc_val, int64_t n_exc, uint32_t* ops_out);
+
 /* The two READ-BAM scanners in ONE pass over the packed ops (the ops are the bulk of the
  * bytes, so this halves HBM traffic of stage 1): stream "reads" == vsv_scan_cigar(
  * VSV_MODE_READS, min_len_reads, min_mapq_reads, enable=NULL) (ERS:47-83,107-145) and
@@ -221,8 +229,8 @@ int vsv_genotype(vsv_ctx* ctx, const int32_t* read_start, const int32_t* read_en
 /* Replaces edlib.align(a, b)["editDistance"] at LI/remove_redundancy.py:75-81 (global /
  * Needleman-Wunsch, unit costs) for a batch of string pairs: strings are rows of a table
  * (chars, str_off[n_str+1]); pair p compares strings ia[p] and ib[p].  Exact (Myers/Hyyro
- * bit-vector).  A string may use at most 16 distinct byte values (DNA alphabets), else
- * VSV_E_ARG.  Host buffers only. */
+ * bit-vector).  The SHORTER string of a pair may use at most 16 distinct byte values (DNA
+ * alphabets), else VSV_E_ARG.  Host buffers only. */
 int vsv_edit_distance_batch(vsv_ctx* ctx, const uint8_t* chars, const int64_t* str_off, int64_t n_str,
                             const int32_t* ia, const int32_t* ib, int64_t n_pair, int32_t* dist);
 

@@ -126,7 +126,24 @@ def make_dataset(seed=20240611, L=140_000):
     rng = random.Random(seed)
     ref = rand_seq(rng, L)
     svs = make_svs(rng, L)
+    # near-duplicate calls for remove_redundancy: the two haplotypes carry similar SVs too far apart
+    # to be paired (> 200 bp) but close enough to be linked (INS: <= 500 bp + edit similarity;
+    # DEL: <= 3000 bp + overlap)
+    def mid(i):
+        a = svs[i]["pos"] + (svs[i]["len"] if svs[i]["type"] == "DEL" else 0)
+        return (a + svs[i + 1]["pos"]) // 2
+    s1 = rand_seq(rng, 300)
+    s2 = "".join(c if rng.random() > 0.08 else rng.choice("ACGT") for c in s1) + rand_seq(rng, 11)
+    m = mid(2)
+    svs.append(dict(pos=m - 160, type="INS", len=len(s1), seq=s1, zyg="h1"))
+    svs.append(dict(pos=m + 160, type="INS", len=len(s2), seq=s2, zyg="h2"))
+    m = mid(6)
+    svs.append(dict(pos=m - 300, type="DEL", len=500, seq="", zyg="h1"))
+    svs.append(dict(pos=m + 50, type="DEL", len=523, seq="", zyg="h2"))
+    svs.sort(key=lambda x: x["pos"])
     haps = {1: hap_svs(svs, 1, rng), 2: hap_svs(svs, 2, rng)}
+    # contig-only artefacts (no read carries them): the read-support filter must drop them
+    ghosts = {1: [(mid(9), "I", 61, rand_seq(rng, 61)), (mid(12), "D", 47, "")], 2: [(mid(15), "I", 120, rand_seq(rng, 120))]}
     # ---------------- contigs: two per haplotype, overlapping by ~8 kb; one on the minus strand,
     # one split (primary + supplementary) at a big deletion
     contig_recs, contig_fa = [], []
@@ -136,6 +153,7 @@ def make_dataset(seed=20240611, L=140_000):
             name = "PS%d_%d_hp%d_%d" % (a + 1, b, hap, k)
             ev = events_for(haps[hap], rng, a, b, 0.00012, False)
             ev = [e for e in ev if e[2] < 30 or any(e[0] == s["pos"] for s in haps[hap])]
+            ev = sorted(ev + [g for g in ghosts[hap] if a + 500 < g[0] < b - 500], key=lambda e: e[0])
             rev = (hap == 2 and k == 0)
             big = [e for e in ev if e[1] == "D" and e[2] >= 600]
             if hap == 1 and k == 1 and big:

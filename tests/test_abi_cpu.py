@@ -45,3 +45,33 @@ def test_no_cpu_fallback():
 def test_sig_struct_layout():
     assert V.SIG_DTYPE.itemsize == 32
     assert V.SIG_DTYPE.names == ("rec", "type", "pos", "len", "q0", "q1", "first", "count")
+
+
+def test_pack_ops16_layout():
+    """Host packer of the compact staging format (vsv_expand_ops16): short ops verbatim, long ops as
+    a marker + exception entry; unpacking on the host restores the BAM-native words."""
+    import numpy as np
+    from volcanosv_b200.lib import pack_ops16
+    rng = np.random.default_rng(3)
+    ln = rng.integers(0, 5000, 10000).astype(np.uint32)
+    ln[::97] = rng.integers(4095, 1 << 27, len(ln[::97]))
+    ops = (ln << 4) | rng.integers(0, 9, 10000).astype(np.uint32)
+    o16, ei, ev = pack_ops16(ops)
+    assert o16.dtype == np.uint16 and o16.ctypes.data % 16 == 0
+    back = o16.astype(np.uint32)
+    assert np.all((back[ei] >> 4) == 0xFFF) and np.all((back[ei] & 15) == (ops[ei] & 15))
+    back[ei] = ev
+    assert np.array_equal(back, ops) and np.all(np.diff(ei) > 0) and len(ei) == int((ln >= 4095).sum())
+
+
+def test_cli_mirrors_every_reference_operator():
+    """One command per LI script on the hot path."""
+    from volcanosv_b200 import cli
+    for name in ("extract_contig_signature_Hifi.py", "extract_contig_signature_ONT.py", "extract_contig_signature_CLR.py",
+                 "extract_reads_signature.py", "FP_filter_v1.py", "remove_redundancy.py", "sig_extract.py",
+                 "calculate_signature_support.py", "filter_vcf_by_sig_cov_insdel.py", "correct_gt_del_real_data.py",
+                 "correct_gt_ins_real_data.py", "filter_GT_correction.py", "volcanosv-vc-large-indel.py"):
+        assert name in cli.COMMANDS
+    import pytest
+    with pytest.raises(SystemExit):
+        cli.main(["no_such_script.py"])

@@ -214,3 +214,16 @@ def test_scan_staging_retry_and_candidate_overflow(ctx):
         es, ert, eqt, ext = O.scan_cigar(ops, off, pos, mapq, mode, 30, 0)
         assert sig_tuples(sigs) == es and len(es) == 11000
         assert np.array_equal(rt, ert) and np.array_equal(qt, eqt)
+
+
+def test_expand_ops16(ctx):
+    """vsv_expand_ops16 restores the BAM-native ops (incl. exceptions and the ragged tail)."""
+    from volcanosv_b200.lib import pack_ops16
+    rng = np.random.default_rng(11)
+    for n in (0, 1, 7, 8, 9, 4099, 100003):
+        ln = rng.integers(0, 6000, n).astype(np.uint32)
+        if n:
+            ln[rng.integers(0, n, max(1, n // 50))] = rng.integers(4095, 1 << 27, max(1, n // 50))
+        ops = (ln << 4) | rng.integers(0, 9, n).astype(np.uint32)
+        o16, ei, ev = pack_ops16(ops)
+        assert np.array_equal(ctx.expand_ops16(o16, ei, ev), ops)

@@ -38,3 +38,25 @@ def test_shard_matches_oracle(profile, dtype, n):
     got2 = sh.download(sh.run_safe())
     for k in got:
         assert np.array_equal(got[k], got2[k], equal_nan=True) if got[k].dtype.kind == "f" else np.array_equal(got[k], got2[k])
+
+
+def test_compact_staging_gives_identical_results():
+    """upload() through the ops16 staging format == upload() of the BAM-native ops."""
+    from volcanosv_b200.lib import pack_ops16
+    L = 3_000_000
+    b = synth.synth_records(41, 3000, "hifi", chrom_len=L, eqx=True)
+    b["ops"][::501] = (np.uint32(70000) << 4) | (b["ops"][::501] & 15)           # long ops -> exception list
+    pos, svlen, typ, gt = synth.synth_candidates(42, 500, chrom_len=L)
+    cands = dict(pos=pos, svlen=svlen, type=typ, gt=gt)
+    sh = ChromShard(0, "Hifi")
+    sh.upload(b, cands)
+    a = sh.download(sh.run_safe())
+    o16, ei, ev = pack_ops16(b["ops"])
+    assert len(ei) > 0
+    b2 = {k: v for k, v in b.items() if k != "ops"}
+    b2.update(ops16=o16, exc_idx=ei, exc_val=ev)
+    sh.upload(b2, cands, n_ops=len(o16))
+    c = sh.download(sh.run_safe())
+    assert sh.h2d_bytes < 0.62 * (4 * len(o16) + 17 * len(b["pos"]) + 16 * 500)
+    for k in a:
+        assert np.array_equal(a[k], c[k], equal_nan=True) if a[k].dtype.kind == "f" else np.array_equal(a[k], c[k]), k

@@ -301,5 +301,6 @@ def test_edit_distance_batch(ctx):
     for (i, j), g in zip(pairs, got):
         assert int(g) == O.edit_distance(strs[i], strs[j]), (len(strs[i]), len(strs[j]))
     with pytest.raises(V.VsvError):
-        ctx.edit_distance_batch(["ABCDEFGHIJKLMNOPQRS", "ABC"], [0], [1])
+        ctx.edit_distance_batch(["ABCDEFGHIJKLMNOPQRS", "ABCDEFGHIJKLMNOPQRSTUV"], [0], [1])
+    assert int(ctx.edit_distance_batch(["ABCDEFGHIJKLMNOPQRS", "ABC"], [0], [1])[0]) == 16   # only the shorter string is limited
     assert len(ctx.edit_distance_batch(["A"], [], [])) == 0

@@ -1,0 +1,173 @@
+"""Command-line twins of the reference's operator scripts: same flags, same files.
+
+    python -m volcanosv_b200.cli <script-name> <the reference script's argv>
+
+e.g. `python -m volcanosv_b200.cli extract_reads_signature.py -i reads.bam -o out -chr 10`
+replaces `python3 LI/extract_reads_signature.py -i reads.bam -o out -chr 10` (RVC:83-88).
+`volcanosv-vc-large-indel.py` takes the reference's flags plus `-cbam` (the sorted contig
+alignments: minimap2/samtools stay outside, RVC:49-58).
+"""
+from __future__ import annotations
+
+import argparse
+import sys
+
+from . import operators as OP
+
+
+def _ers(argv):
+    p = argparse.ArgumentParser(prog="extract_reads_signature.py")
+    p.add_argument("--chr_number", "-chr", type=int)
+    p.add_argument("--input_path", "-i")
+    p.add_argument("--output_dir", "-o")
+    p.add_argument("--min_siglen", type=int, default=30)
+    a, _ = p.parse_known_args(argv)
+    OP.extract_reads_signature(a.input_path, a.output_dir, a.chr_number, a.min_siglen)
+
+
+def _fpf(argv):
+    p = argparse.ArgumentParser(prog="FP_filter_v1.py")
+    p.add_argument("--input_path", "-i")
+    p.add_argument("--signature_dir", "-sigd")
+    p.add_argument("--output_path", "-o")
+    a, _ = p.parse_known_args(argv)
+    OP.fp_filter(a.input_path, a.signature_dir, a.output_path)
+
+
+def _se(argv):
+    p = argparse.ArgumentParser(prog="sig_extract.py")
+    p.add_argument("input")
+    p.add_argument("reference")
+    p.add_argument("work_dir")
+    p.add_argument("-b", "--batches", type=int, default=10_000_000)
+    p.add_argument("-p", "--max_split_parts", type=int, default=7)
+    p.add_argument("-q", "--min_mapq", type=int, default=20)
+    p.add_argument("-r", "--min_read_len", type=int, default=500)
+    p.add_argument("-include_bed", default=None)
+    p.add_argument("-l", "--min_size", type=int, default=30)
+    p.add_argument("-L", "--max_size", type=int, default=100000)
+    p.add_argument("-sl", "--min_siglength", type=int, default=10)
+    a, _ = p.parse_known_args(argv)          # cuteSV clustering flags are accepted and unused, as in the reference
+    OP.sig_extract(a.input, a.reference, a.work_dir, a.include_bed, a.batches, a.min_mapq, a.min_read_len, a.min_siglength,
+                   a.min_size, a.max_size, a.max_split_parts)
+
+
+def _css(argv):
+    p = argparse.ArgumentParser(prog="calculate_signature_support.py")
+    p.add_argument("--vcffile", "-v")
+    p.add_argument("--cutesv_dir", "-ct")
+    p.add_argument("--flanking", "-f", type=int, default=1000)
+    p.add_argument("--min_size", "-s", type=int, default=30)
+    p.add_argument("--chr_num", "-chr", type=int, default=None)
+    a, _ = p.parse_known_args(argv)
+    OP.signature_support(a.vcffile, a.cutesv_dir, a.chr_num, a.flanking, a.min_size)
+
+
+def _cov(argv):
+    p = argparse.ArgumentParser(prog="filter_vcf_by_sig_cov_insdel.py")
+    p.add_argument("--input_path", "-i")
+    p.add_argument("--dtype", "-d")
+    p.add_argument("--asm", "-a")
+    p.add_argument("--vtype", "-v", choices=["INS", "DEL", "INSDEL"], default="INSDEL")
+    a = p.parse_args(argv)
+    OP.filter_by_sig_cov(a.input_path, a.dtype, a.asm, a.vtype)
+
+
+def _gt(argv):
+    p = argparse.ArgumentParser(prog="correct_gt_{del,ins}_real_data.py")
+    p.add_argument("--input_path", "-i")
+    p.add_argument("--output_path", "-o")
+    p.add_argument("--bamfile", "-bam")
+    p.add_argument("--sigfile", "--sig_file", "-sig")
+    p.add_argument("--dtype", "-d", choices=["ONT", "Hifi", "CLR"])
+    p.add_argument("--vtype", "-v", choices=["INS", "DEL"])
+    a, _ = p.parse_known_args(argv)
+    OP.correct_gt(a.input_path, a.output_path, a.bamfile, a.sigfile, a.dtype, a.vtype)
+
+
+def _rr(argv):
+    p = argparse.ArgumentParser(prog="remove_redundancy.py")
+    p.add_argument("--input_path", "-i")
+    p.add_argument("--output_dir", "-o")
+    p.add_argument("--dist_thresh", "-r", type=int, default=500)
+    p.add_argument("--dist_thresh_del", "-rd", type=int, default=3000)
+    p.add_argument("--overlap_thresh", "-O", type=float, default=0)
+    p.add_argument("--size_sim_thresh", "-P", type=float, default=0.5)
+    p.add_argument("--size_sim_thresh_del", "-Pd", type=float, default=0.1)
+    p.add_argument("--seq_sim_thresh", "-p", type=float, default=0.5)
+    a, _ = p.parse_known_args(argv)
+    OP.remove_redundancy(a.input_path, a.output_dir, a.dist_thresh, a.dist_thresh_del, a.overlap_thresh, a.size_sim_thresh,
+                         a.size_sim_thresh_del, a.seq_sim_thresh)
+
+
+def _ecs(dtype):
+    def run(argv):
+        p = argparse.ArgumentParser(prog="extract_contig_signature_%s.py" % dtype)
+        p.add_argument("--chr_number", "-chr", type=int)
+        p.add_argument("--bam_path", "-bam")
+        p.add_argument("--contig_path", "-contig")
+        p.add_argument("--header_path", "-header")
+        p.add_argument("--ref_path", "-ref")
+        p.add_argument("--output_dir", "-o")
+        p.add_argument("--min_cigar_mapq", type=int, default=50)
+        p.add_argument("--min_split_mapq", type=int, default=50)
+        a, _ = p.parse_known_args(argv)
+        # the reference assigns min_split_mapq = args.min_cigar_mapq (ECS_H:41)
+        OP.extract_contig_signature(a.bam_path, a.contig_path, a.ref_path, a.output_dir, a.chr_number, dtype, a.header_path,
+                                    a.min_cigar_mapq, a.min_cigar_mapq)
+    return run
+
+
+def _fgc(argv):
+    p = argparse.ArgumentParser(prog="filter_GT_correction.py")
+    p.add_argument("--vcffile", "-vcf")
+    p.add_argument("--bamfile", "-bam")
+    p.add_argument("--reference", "-ref")
+    p.add_argument("--pre_cutesig", "-presig")
+    p.add_argument("--dtype", "-dtype", choices=["Hifi", "CLR", "ONT"])
+    p.add_argument("--chr_num", "-chr", type=int, default=None)
+    p.add_argument("--n_thread", "-t", type=int, default=22)
+    a = p.parse_args(argv)
+    OP.filter_gt_correction(a.vcffile, a.bamfile, a.reference, a.dtype, a.chr_num, a.pre_cutesig)
+
+
+def _main(argv):
+    p = argparse.ArgumentParser(prog="volcanosv-vc-large-indel.py")
+    p.add_argument("--input_dir", "-i")
+    p.add_argument("--output_dir", "-o")
+    p.add_argument("--data_type", "-dtype")
+    p.add_argument("--bam_file", "-bam")
+    p.add_argument("--reference", "-ref")
+    p.add_argument("--read_signature_dir", "-rdsig")
+    p.add_argument("--pre_cutesig", "-presig")
+    p.add_argument("--chr_num", "-chr", type=int, required=True)
+    p.add_argument("--n_thread", "-t", type=int, default=11)
+    p.add_argument("--n_thread_align", "-ta", type=int, default=10)
+    p.add_argument("--mem_per_thread", "-mempt", default="768M")
+    p.add_argument("--prefix", "-px", default="Sample")
+    p.add_argument("--contig_bam", "-cbam", required=True, help="sorted contig-to-reference alignments (RVC:49-58 output)")
+    a = p.parse_args(argv)
+    contigs = "%s/chr%d/assembly/final_contigs/%s_final_contigs.fa" % (a.input_dir, a.chr_num, a.prefix)
+    print(OP.large_indel_chr(a.contig_bam, contigs, a.reference, a.bam_file, a.output_dir, a.data_type, a.chr_num, a.prefix,
+                             a.read_signature_dir, a.pre_cutesig))
+
+
+COMMANDS = {
+    "extract_reads_signature.py": _ers, "FP_filter_v1.py": _fpf, "sig_extract.py": _se,
+    "calculate_signature_support.py": _css, "filter_vcf_by_sig_cov_insdel.py": _cov,
+    "correct_gt_del_real_data.py": _gt, "correct_gt_ins_real_data.py": _gt, "remove_redundancy.py": _rr,
+    "extract_contig_signature_Hifi.py": _ecs("Hifi"), "extract_contig_signature_ONT.py": _ecs("ONT"),
+    "extract_contig_signature_CLR.py": _ecs("CLR"), "filter_GT_correction.py": _fgc,
+    "volcanosv-vc-large-indel.py": _main,
+}
+
+
+def main(argv=None):
+    argv = list(sys.argv[1:] if argv is None else argv)
+    if not argv or argv[0] not in COMMANDS:
+        sys.exit("usage: python -m volcanosv_b200.cli <%s> [the script's arguments]" % " | ".join(COMMANDS))
+    COMMANDS[argv[0]](argv[1:])
+
+
+if __name__ == "__main__":
+    main()

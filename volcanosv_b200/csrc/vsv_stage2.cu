@@ -686,3 +686,54 @@ extern "C" int vsv_select_i32(vsv_ctx* ctx, const int32_t* key, int32_t val, con
   VSV_TRY(vsv_out_done(ctx, out, dout, (size_t)n));
   return vsv_end(ctx);
 }
+
+// --------------------------------------------------------------------------------
+// compact host->device staging of the packed CIGAR ops ("ops16")
+// --------------------------------------------------------------------------------
+// PCIe, not HBM, bounds the end-to-end path (4 bytes per op over a ~55 GB/s link), so the host
+// packer may stage the ops as 16-bit words: op i = len << 4 | code when len < 4095, else the
+// marker 0xFFF << 4 | code with the full 32-bit word in a sparse exception list.  This kernel
+// widens them back to the BAM-native u32 array every scanner reads (8 ops per thread: one
+// LDG.128 in, two STG.128 out); a second, tiny kernel patches the exceptions.
+__global__ void __launch_bounds__(256) k_expand_ops16(const uint16_t* __restrict__ in, int64_t n, uint32_t* __restrict__ out) {
+  const int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 8;
+  if (i + 8 <= n) {
+    const uint4 v = __ldg(reinterpret_cast<const uint4*>(in + i));
+    uint4 a, b;
+    a.x = v.x & 0xFFFFu; a.y = v.x >> 16; a.z = v.y & 0xFFFFu; a.w = v.y >> 16;
+    b.x = v.z & 0xFFFFu; b.y = v.z >> 16; b.z = v.w & 0xFFFFu; b.w = v.w >> 16;
+    reinterpret_cast<uint4*>(out + i)[0] = a;
+    reinterpret_cast<uint4*>(out + i)[1] = b;
+  } else {
+    for (int64_t k = i; k < n; ++k) out[k] = in[k];
+  }
+}
+__global__ void k_patch_ops(const int64_t* __restrict__ idx, const uint32_t* __restrict__ val, int64_t n_exc, int64_t n,
+                            uint32_t* __restrict__ out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n_exc && idx[i] >= 0 && idx[i] < n) out[idx[i]] = val[i];
+}
+
+extern "C" int vsv_expand_ops16(vsv_ctx* ctx, const uint16_t* ops16, int64_t n_ops, const int64_t* exc_idx,
+                                const uint32_t* exc_val, int64_t n_exc, uint32_t* ops_out) {
+  VSV_TRY(vsv_begin(ctx));
+  if (n_ops < 0 || n_exc < 0 || (n_ops > 0 && (!ops16 || !ops_out)) || (n_exc > 0 && (!exc_idx || !exc_val)))
+    VSV_FAIL(ctx, VSV_E_ARG, "vsv_expand_ops16: bad argument");
+  if (n_ops == 0) return VSV_OK;
+  const uint16_t* din;
+  const int64_t* dix;
+  const uint32_t* dvl;
+  uint32_t* dout;
+  VSV_TRY(vsv_in(ctx, ops16, (size_t)n_ops, &din));
+  VSV_TRY(vsv_in(ctx, exc_idx, (size_t)n_exc, &dix));
+  VSV_TRY(vsv_in(ctx, exc_val, (size_t)n_exc, &dvl));
+  VSV_TRY(vsv_out(ctx, ops_out, (size_t)n_ops, &dout));
+  if ((reinterpret_cast<uintptr_t>(din) & 15u) || (reinterpret_cast<uintptr_t>(dout) & 15u))
+    VSV_FAIL(ctx, VSV_E_ARG, "vsv_expand_ops16: buffers must be 16-byte aligned");
+  VSV_TRY(vsv_t0(ctx));
+  VSV_LAUNCH(ctx, k_expand_ops16, (unsigned)vsv_cdiv(vsv_cdiv(n_ops, 8), 256), 256, 0, din, n_ops, dout);
+  if (n_exc > 0) VSV_LAUNCH(ctx, k_patch_ops, (unsigned)vsv_cdiv(n_exc, 256), 256, 0, dix, dvl, n_exc, n_ops, dout);
+  VSV_TRY(vsv_t1(ctx));
+  VSV_TRY(vsv_out_done(ctx, ops_out, dout, (size_t)n_ops));
+  return vsv_end(ctx);
+}

@@ -49,6 +49,7 @@ SIGNATURES = {
     "vsv_timer_stop": [_vp, C.POINTER(C.c_float)],
     "vsv_get_main_kernel_ms": [_vp, C.POINTER(C.c_float)],
     "vsv_scan_cigar": [_vp, _int, _int, _int, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _i64, C.POINTER(_i64), _vp, _vp, _vp],
+    "vsv_expand_ops16": [_vp, _vp, _i64, _vp, _vp, _i64, _vp],
     "vsv_scan_reads_fused": [_vp, _int, _int, _int, _int, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _i64, C.POINTER(_i64),
                              _vp, _i64, C.POINTER(_i64), _vp, _vp, _vp],
     "vsv_merge_in_record": [_vp, _int, _vp, _i64, _vp, C.POINTER(_i64), _vp, C.POINTER(_i64)],
@@ -185,6 +186,16 @@ class Context:
                 continue
             self._chk(rc)
             return out[: n_out.value], rt, qt, xt
+
+    def expand_ops16(self, ops16, exc_idx, exc_val):
+        """-> the BAM-native u32 ops (host-IO mode: round trip through the device)."""
+        o16 = _arr(ops16, np.uint16)
+        if o16.ctypes.data % 16:
+            o16 = _aligned_copy(o16)
+        ei, ev = _arr(exc_idx, np.int64), _arr(exc_val, np.uint32)
+        out = _aligned_empty(len(o16), np.uint32)
+        self._chk(self.lib.vsv_expand_ops16(self.h, _p(o16), len(o16), _p(ei), _p(ev), len(ei), _p(out)))
+        return out
 
     def scan_reads_fused(self, ops, op_off, pos, mapq, enable_cute=None, min_len_reads=30, min_mapq_reads=50,
                          min_len_cute=10, min_mapq_cute=20, cap=None, totals=True):
@@ -339,6 +350,18 @@ class Context:
         out = np.zeros(len(ia), np.int32)
         self._chk(self.lib.vsv_edit_distance_batch(self.h, _p(chars), _p(off), len(bs), _p(ia), _p(ib), len(ia), _p(out)))
         return out
+
+
+def pack_ops16(ops):
+    """Host packer of the compact staging format of vsv_expand_ops16: (ops16, exc_idx, exc_val)."""
+    ops = np.ascontiguousarray(ops, dtype=np.uint32)
+    big = ops >= np.uint32(0xFFF0)
+    o16 = _aligned_empty(len(ops), np.uint16)
+    np.copyto(o16, ops, casting="unsafe")
+    exc_idx = np.flatnonzero(big).astype(np.int64)
+    exc_val = ops[exc_idx].copy()
+    o16[exc_idx] = (np.uint16(0xFFF0) | (exc_val & np.uint32(15)).astype(np.uint16))
+    return o16, exc_idx, exc_val
 
 
 def _aligned_empty(n, dtype, align=64):

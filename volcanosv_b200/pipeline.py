@@ -91,7 +91,26 @@ class ChromShard:
             self.h2d_bytes += src.numel() * src.element_size()
             return src
 
-        for k in ("ops", "op_off", "pos", "mapq", "qlen"):
+        if "ops16" in batch:
+            # compact staging (include/volcanosv_b200.h: vsv_expand_ops16): 2 bytes per op over PCIe,
+            # widened on the device into the BAM-native u32 array the scanners read
+            n_ops = int(n_ops if n_ops is not None else batch["ops16"].numel() if hasattr(batch["ops16"], "numel") else len(batch["ops16"]))
+            src16 = batch["ops16"]
+            if isinstance(src16, np.ndarray):
+                src16 = torch.from_numpy(np.ascontiguousarray(src16.view(np.int16)))
+            o16 = self._buf("in_ops16", src16.numel(), src16.dtype)
+            o16[: src16.numel()].copy_(src16, non_blocking=True)
+            self.h2d_bytes += src16.numel() * 2
+            ei = put("in_exc_idx", batch["exc_idx"]) if len(batch["exc_idx"]) else None
+            ev = put("in_exc_val", batch["exc_val"]) if len(batch["exc_val"]) else None
+            n_exc = 0 if ei is None else ei.numel()
+            ops = self._buf("in_ops", n_ops, torch.int32)
+            torch.cuda.current_stream().synchronize()
+            self._chk(self.lib.vsv_expand_ops16(self.h, _dp(o16), n_ops, _dp(self.d["in_exc_idx"]) if n_exc else None,
+                                                _dp(self.d["in_exc_val"]) if n_exc else None, n_exc, _dp(ops)))
+        else:
+            put("in_ops", batch["ops"])
+        for k in ("op_off", "pos", "mapq", "qlen"):
             put("in_" + k, batch[k])
         for k in ("pos", "svlen", "type", "gt"):
             put("cand_" + k, cands[k])
@@ -99,6 +118,7 @@ class ChromShard:
         self.n_ops = int(n_ops) if n_ops is not None else int(batch["op_off"][-1])
         self.n_cand = len(cands["pos"])
         torch.cuda.current_stream().synchronize()
+        self.ctx.sync()
 
     def _chk(self, rc):
         if rc != 0:
