@@ -278,8 +278,15 @@ def main():
     alg_bytes = 4.0 * n_ops + 24.0 * n_rec + 32.0 * n_sig_out       # SURVEY.md §8d B1, per launch
     k_ms = float(np.mean(scan_ms)) if scan_ms else float("nan")
     achieved = alg_bytes / (k_ms * 1e-3) / 1e9
-    roof = dict(bound="hbm", kernel="k_scan_tiles<FUSED>", achieved=achieved, peak=peak, unit="GB/s", frac=achieved / peak,
-                traffic=None, peak_source=peak_src, alg_bytes_per_launch=alg_bytes, kernel_ms=k_ms,
+    # dram bytes of that kernel from the committed `ncu --set full` capture (profiles/), per op -> per launch here
+    traffic, traffic_src = None, None
+    tpath = os.path.join(ROOT, "profiles", "scan_traffic.json")
+    if os.path.exists(tpath):
+        tj = json.load(open(tpath))
+        traffic = (tj["dram_bytes_read"] + tj["dram_bytes_write"]) / tj["n_ops"] * n_ops
+        traffic_src = tj["source"]
+    roof = dict(bound="hbm", kernel="k_scan_wt<FUSED>", achieved=achieved, peak=peak, unit="GB/s", frac=achieved / peak,
+                traffic=traffic, traffic_source=traffic_src, peak_source=peak_src, alg_bytes_per_launch=alg_bytes, kernel_ms=k_ms,
                 launches_per_step=1, share_of_step=k_ms / ms_per_step)
     line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=args.steps, warmup=max(args.warmup, 3),
                 ms_per_step=ms_per_step, higher_is_better=True, scaling="weak", vs_baseline=None, dtype="int32",

@@ -5,14 +5,17 @@
 // (LI/sig_extract.py:438-478).  VSV_MODE_FUSED runs the two READ scanners (ERS + SE)
 // in ONE pass over the packed ops and fills two output streams.
 //
-// Design v5 (B200-first; the streaming kernel has NO block-level synchronisation):
+// Design v6 (B200-first; the streaming kernel has NO block-level synchronisation):
 //  * the packed ops of ALL records are one flat u32 array cut into "warp tiles" of 1024
 //    ops (4 KB), independent of record boundaries.  Every WARP is an independent worker: it
 //    pulls its warp tiles round-robin into its own double-buffered shared-memory slot with
 //    1-D TMA bulk copies (cp.async.bulk + mbarrier), folds 32 consecutive ops per lane
-//    (bank-conflict-free rotated LDS.128) into two running sums (reference / query
-//    advance) and a 32-bit candidate mask, and warp-scans them with shuffles.  Rare op
-//    codes (N, P, H, ...) are summed only by warps that saw one.
+//    (bank-conflict-free XOR-swizzled LDS.128) into two running sums (reference / query
+//    advance: PRMT byte-table look-up on the ALU pipe, IMAD accumulate on the FMA pipe)
+//    and the running maximum of (op & table_ID); lanes whose maximum reaches the length
+//    threshold are resolved afterwards by the whole warp (LDS + ballot -> candidate mask).
+//    The sums are warp-scanned with shuffles.  Rare op codes (N, P, H, ...) and record
+//    starts are handled warp-cooperatively (REDUX) only by warps that saw one.
 //  * what the streaming kernel leaves behind per warp tile: a 32-byte aggregate (sums since
 //    the last record start inside the tile), the in-tile prefix at every record start
 //    (`fstart`, one 32-byte row per record), and one 32-byte staging entry per RAW
@@ -28,7 +31,8 @@
 //
 // History: v1 (single-pass chained look-back) was bound by the tile chain at 7 % of HBM
 // (profiles/r01a_scan_v1.md); v2-v4 (CTA tiles, candidates finished by warp 0 behind
-// __syncthreads) were bound by that serial phase at 23-25 % (profiles/r01b_scan_v4.md).
+// __syncthreads) were bound by that serial phase at 23-25 %; v5 (warp-independent, per-op
+// candidate test) reached 52 %; v6 is ALU-issue bound at 66 % (profiles/r01c_scan_v6.md).
 #include <cub/device/device_scan.cuh>
 
 #include "vsv_common.cuh"
