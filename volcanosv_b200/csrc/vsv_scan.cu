@@ -33,16 +33,14 @@
 // (profiles/r01a_scan_v1.md); v2-v4 (CTA tiles, candidates finished by warp 0 behind
 // __syncthreads) were bound by that serial phase at 23-25 %; v5 (warp-independent, per-op
 // candidate test) reached 52 %; v6 is ALU-issue bound at 66 % (profiles/r01c_scan_v6.md).
-#include <cub/device/device_scan.cuh>
-
 #include "vsv_common.cuh"
 
 #define WT_OPS 1024           // ops per warp tile
 #define WT_VPT 32             // ops per lane
-#define SCAN_WARPS 4          // warps (independent workers) per CTA
+#define SCAN_WARPS 14         // warps (independent workers) per CTA: 2 CTAs x 14 warps x 8 KB fill the 227 KB of an SM
 #define SCAN_THREADS (SCAN_WARPS * 32)
 #define SCAN_STAGES 2
-#define SCAN_CTAS_PER_SM 6
+#define SCAN_CTAS_PER_SM 2
 #define SCAN_CHUNK 128        // staging slots reserved per global atomic
 
 #define VSV_MODE_FUSED 3      // internal: READS (stream A) + CUTE (stream B) in one pass
@@ -290,8 +288,10 @@ __global__ void __launch_bounds__(SCAN_THREADS, SCAN_CTAS_PER_SM) k_scan_wt(cons
   typedef ModeTraits<MODE> M;
   constexpr uint32_t RARE = M::X1 | M::X2 | M::X3;
   constexpr uint32_t FULL = 0xffffffffu;
-  __shared__ __align__(128) uint32_t s_ops[SCAN_WARPS][SCAN_STAGES][WT_OPS];
-  __shared__ __align__(8) uint64_t s_bar[SCAN_WARPS][SCAN_STAGES];
+  extern __shared__ __align__(128) unsigned char s_dyn[];
+  uint32_t(*s_ops)[SCAN_STAGES][WT_OPS] = reinterpret_cast<uint32_t(*)[SCAN_STAGES][WT_OPS]>(s_dyn);
+  uint64_t(*s_bar)[SCAN_STAGES] =
+      reinterpret_cast<uint64_t(*)[SCAN_STAGES]>(s_dyn + (size_t)SCAN_WARPS * SCAN_STAGES * WT_OPS * sizeof(uint32_t));
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int64_t TW = (int64_t)gridDim.x * SCAN_WARPS;
   const int64_t gw = (int64_t)blockIdx.x * SCAN_WARPS + warp;
@@ -390,7 +390,8 @@ __global__ void __launch_bounds__(SCAN_THREADS, SCAN_CTAS_PER_SM) k_scan_wt(cons
       const int rot = lane & 7;
       const uint4* row = reinterpret_cast<const uint4*>(tl + lane * WT_VPT);
       const uint32_t one = p.one;  // == 1, opaque to the compiler: keeps `sc` on the FMA pipe
-      uint32_t nr = 0, nq = 0, mxc = 0, mxk = 0, sc = 0;
+      uint32_t nr = 0, nq = 0, mxc = 0, sc = 0;
+      int32_t mnk = 0;
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
         const uint4 v = row[k ^ rot];
@@ -404,14 +405,14 @@ __global__ void __launch_bounds__(SCAN_THREADS, SCAN_CTAS_PER_SM) k_scan_wt(cons
           nr = len * tr + nr;  // IMAD: subtracts len when the code is a member
           nq = len * tq + nq;
           sc = tc * one + sc;  // I/D: -1 each, rare: +0x01010101 each
-          mxk = max(mxk, w & tc);
+          mnk = min(mnk, (int32_t)(len * tc));  // I/D: -len (an IMAD: the ALU pipe is the busier one)
           mxc = max(mxc, code);
         }
       }
       r = 0u - nr;
       q = 0u - nq;
       lane_rare = (int32_t)sc > 0 || mxc > 8u;  // a rare code (N/H/P...) or a reserved one (9..15)
-      lane_cand = mxk >= min_w || lane_rare;    // rare lanes: mxk is not trustworthy
+      lane_cand = mnk <= -(int32_t)(min_w >> 4) || lane_rare;  // rare lanes: mnk is not trustworthy
     }
     // -- rare lanes: exact sums of every class, by the whole warp ---------------------------------
     uint32_t rare_lanes = __ballot_sync(FULL, lane_rare);
@@ -431,12 +432,16 @@ __global__ void __launch_bounds__(SCAN_THREADS, SCAN_CTAS_PER_SM) k_scan_wt(cons
     uint32_t em = 0;
     {
       uint32_t cand_lanes = __ballot_sync(FULL, lane_cand);
-      while (cand_lanes) {
-        const int L = __ffs(cand_lanes) - 1;
+      while (cand_lanes) {  // two candidate lanes per round: the two LDS are in flight together
+        const int L0 = __ffs(cand_lanes) - 1;
         cand_lanes &= cand_lanes - 1;
-        const uint32_t w = tl[L * WT_VPT + lane];
-        const uint32_t m = __ballot_sync(FULL, ((1u << (w & 15u)) & 6u) && w >= min_w);
-        if (lane == L) em = m;
+        const int L1 = cand_lanes ? __ffs(cand_lanes) - 1 : L0;
+        cand_lanes &= cand_lanes - 1;
+        const uint32_t w0 = tl[L0 * WT_VPT + lane], w1 = tl[L1 * WT_VPT + lane];
+        const uint32_t m0 = __ballot_sync(FULL, ((1u << (w0 & 15u)) & 6u) && w0 >= min_w);
+        const uint32_t m1 = __ballot_sync(FULL, ((1u << (w1 & 15u)) & 6u) && w1 >= min_w);
+        if (lane == L0) em = m0;
+        if (lane == L1) em = m1;
       }
     }
     const uint32_t c = __popc(em);
@@ -512,7 +517,7 @@ __global__ void __launch_bounds__(SCAN_THREADS, SCAN_CTAS_PER_SM) k_scan_wt(cons
         while (m) {
           const int s = __ffs(m) - 1;
           m &= m - 1;
-          dst[0] = make_uint4((uint32_t)(lane * WT_VPT + s), 0u, ex.r, ex.q);
+          dst[0] = make_uint4((uint32_t)(lane * WT_VPT + s), (uint32_t)wt, ex.r, ex.q);
           dst[1] = make_uint4(ex.x1, ex.x2, ex.x3, 0u);
           dst += 2;
         }
@@ -541,68 +546,186 @@ __global__ void __launch_bounds__(SCAN_THREADS, SCAN_CTAS_PER_SM) k_scan_wt(cons
   }
 }
 
-// ---- sparse follow-up kernels (lane-dense: one thread per warp tile / per record) --------
-// k_gate: for each raw candidate of a tile: record lookup, gates, exact sums since the record
-// start (or since the tile start when the record began earlier); counts per stream.
-template <int MODE>
-__global__ void __launch_bounds__(128) k_gate(const ScanParams p) {
-  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= p.n_wt) return;
-  const uint2 st = p.wt_stage[t];
-  uint32_t cnt_a = 0, cnt_b = 0;
-  if (st.y != 0u && st.x != 0xFFFFFFFFu) {
-    const int64_t wt_start = t * WT_OPS;
-    const int2 ss = __ldg(p.wt_starts + t);
-    const int32_t lo = max(ss.x - 1, 0);
-    const int32_t hi = max(lo, min(ss.y, (int32_t)p.n_rec - 1));
-    StageEntry* e = p.stage + st.x;
-    for (uint32_t i = 0; i < st.y; ++i) {
-      const uint4 e0 = reinterpret_cast<const uint4*>(e + i)[0], e1 = reinterpret_cast<const uint4*>(e + i)[1];
-      const int j = (int)e0.x;
-      const uint32_t* row = p.ops + wt_start + (j & ~31);
-      const int n = j & 31;
-      Sums f = {e0.z, e0.w, e1.x, e1.y, e1.z};
-      uint32_t w = 0;
-      {  // ops 0..n-1 of the candidate's 128-byte row, read as LDG.128 (the row never crosses n_ops
-         // before op n, but its tail may: only whole uint4 groups that lie inside the array are vector loads)
-        Sums wk = {0, 0, 0, 0, 0};
-        const int64_t left = p.n_ops - (wt_start + (j & ~31));
-        for (int g4 = 0; g4 * 4 <= n; ++g4) {
-          uint4 v;
-          if ((int64_t)(g4 * 4 + 4) <= left) {
-            v = __ldg(reinterpret_cast<const uint4*>(row) + g4);
-          } else {
-            v.x = g4 * 4 < left ? __ldg(row + g4 * 4) : 0u;
-            v.y = g4 * 4 + 1 < left ? __ldg(row + g4 * 4 + 1) : 0u;
-            v.z = g4 * 4 + 2 < left ? __ldg(row + g4 * 4 + 2) : 0u;
-            v.w = 0u;
-          }
-          const uint32_t vv[4] = {v.x, v.y, v.z, v.w};
+// ---- exclusive scan of the tile aggregates (segmented: a tile in which a record starts resets
+// the sums; the signature counts are plain sums).  Three small launches over n_wt + 1 32-byte
+// elements: per-CTA reduce, one-CTA spine, per-CTA scan with carry-in.
+#define TS_THREADS 256
+#define TS_ITEMS 4
+#define TS_BLOCK (TS_THREADS * TS_ITEMS)
+__device__ __forceinline__ TileState ts_identity() {
+  TileState t;
+  t.r = t.q = t.x1 = t.x2 = t.x3 = t.cnt_a = t.cnt_b = t.flag = 0u;
+  return t;
+}
+__device__ __forceinline__ TileState ts_load(const TileState* p) {
+  const uint4 a = reinterpret_cast<const uint4*>(p)[0], b = reinterpret_cast<const uint4*>(p)[1];
+  TileState t;
+  t.r = a.x; t.q = a.y; t.x1 = a.z; t.x2 = a.w; t.x3 = b.x; t.cnt_a = b.y; t.cnt_b = b.z; t.flag = b.w;
+  return t;
+}
+__device__ __forceinline__ void ts_store(TileState* p, const TileState& t) {
+  reinterpret_cast<uint4*>(p)[0] = make_uint4(t.r, t.q, t.x1, t.x2);
+  reinterpret_cast<uint4*>(p)[1] = make_uint4(t.x3, t.cnt_a, t.cnt_b, t.flag);
+}
+__device__ __forceinline__ TileState ts_shfl_up(const TileState& t, int d) {
+  TileState o;
+  o.r = __shfl_up_sync(0xffffffffu, t.r, d); o.q = __shfl_up_sync(0xffffffffu, t.q, d);
+  o.x1 = __shfl_up_sync(0xffffffffu, t.x1, d); o.x2 = __shfl_up_sync(0xffffffffu, t.x2, d);
+  o.x3 = __shfl_up_sync(0xffffffffu, t.x3, d); o.cnt_a = __shfl_up_sync(0xffffffffu, t.cnt_a, d);
+  o.cnt_b = __shfl_up_sync(0xffffffffu, t.cnt_b, d); o.flag = __shfl_up_sync(0xffffffffu, t.flag, d);
+  return o;
+}
+// inclusive scan across the CTA of one value per thread; returns the thread's inclusive value and
+// the CTA total in `total` (s_w: TS_THREADS / 32 slots)
+__device__ __forceinline__ TileState ts_block_scan(TileState v, TileState* s_w, TileState& total) {
+  const TileStateOp op;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
-          for (int u = 0; u < 4; ++u) {
-            const int idx = g4 * 4 + u;
-            if (idx < n) add_op<MODE>(vv[u], wk);
-            if (idx == n) w = vv[u];
-          }
-        }
-        f.r += wk.r; f.q += wk.q; f.x1 += wk.x1; f.x2 += wk.x2; f.x3 += wk.x3;
+  for (int d = 1; d < 32; d <<= 1) {
+    const TileState u = ts_shfl_up(v, d);
+    if (lane >= d) v = op(u, v);
+  }
+  if (lane == 31) s_w[warp] = v;
+  __syncthreads();
+  TileState pre = ts_identity();
+  total = ts_identity();
+  for (int w = 0; w < (int)(blockDim.x >> 5); ++w) {
+    if (w == warp) pre = total;
+    total = op(total, s_w[w]);
+  }
+  __syncthreads();
+  return warp == 0 ? v : op(pre, v);
+}
+__global__ void __launch_bounds__(TS_THREADS) k_ts_reduce(const TileState* __restrict__ in, int64_t n,
+                                                            TileState* __restrict__ block_agg) {
+  __shared__ TileState s_w[TS_THREADS / 32];
+  const TileStateOp op;
+  const int64_t base = (int64_t)blockIdx.x * TS_BLOCK + (int64_t)threadIdx.x * TS_ITEMS;
+  TileState v = ts_identity();
+#pragma unroll
+  for (int k = 0; k < TS_ITEMS; ++k)
+    if (base + k < n) v = op(v, ts_load(in + base + k));
+  TileState total;
+  ts_block_scan(v, s_w, total);
+  if (threadIdx.x == 0) ts_store(block_agg + blockIdx.x, total);
+}
+__global__ void __launch_bounds__(1024) k_ts_spine(TileState* __restrict__ block_agg, int64_t nb) {
+  __shared__ TileState s_w[32];
+  const TileStateOp op;
+  const int64_t per = (nb + blockDim.x - 1) / blockDim.x;
+  const int64_t a = (int64_t)threadIdx.x * per, b = min(a + per, nb);
+  TileState v = ts_identity();
+  for (int64_t i = a; i < b; ++i) v = op(v, ts_load(block_agg + i));
+  TileState total;
+  const TileState inc = ts_block_scan(v, s_w, total);
+  // exclusive prefix of this thread's chunk = inclusive of the previous thread
+  TileState pre = ts_shfl_up(inc, 1);
+  __shared__ TileState s_last[32];
+  if ((threadIdx.x & 31) == 31) s_last[threadIdx.x >> 5] = inc;
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) pre = threadIdx.x == 0 ? ts_identity() : s_last[(threadIdx.x >> 5) - 1];
+  for (int64_t i = a; i < b; ++i) {
+    const TileState cur = ts_load(block_agg + i);
+    ts_store(block_agg + i, pre);
+    pre = op(pre, cur);
+  }
+}
+__global__ void __launch_bounds__(TS_THREADS) k_ts_scan(const TileState* __restrict__ in, int64_t n,
+                                                          const TileState* __restrict__ block_excl,
+                                                          TileState* __restrict__ out) {
+  __shared__ TileState s_w[TS_THREADS / 32];
+  const TileStateOp op;
+  const int64_t base = (int64_t)blockIdx.x * TS_BLOCK + (int64_t)threadIdx.x * TS_ITEMS;
+  TileState it[TS_ITEMS];
+  TileState v = ts_identity();
+#pragma unroll
+  for (int k = 0; k < TS_ITEMS; ++k) {
+    it[k] = ts_identity();
+    if (base + k < n) it[k] = ts_load(in + base + k);
+    v = op(v, it[k]);
+  }
+  TileState total;
+  const TileState inc = ts_block_scan(v, s_w, total);
+  TileState pre = ts_shfl_up(inc, 1);  // inclusive value of the previous thread
+  __shared__ TileState s_last[TS_THREADS / 32];
+  if ((threadIdx.x & 31) == 31) s_last[threadIdx.x >> 5] = inc;
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) pre = threadIdx.x == 0 ? ts_identity() : s_last[(threadIdx.x >> 5) - 1];
+  pre = op(ts_load(block_excl + blockIdx.x), pre);
+#pragma unroll
+  for (int k = 0; k < TS_ITEMS; ++k) {
+    if (base + k < n) ts_store(out + base + k, pre);
+    pre = op(pre, it[k]);
+  }
+}
+
+// ---- sparse follow-up kernels (lane-dense: one thread per candidate / warp tile / record) ----
+// k_gate: one thread per staging slot.  A slot is live when the tile named in it (field b,
+// written by the streaming kernel) reserved a range that contains the slot: chunk tails and
+// entries left over from earlier calls fail that test, so the staging area is never cleared.
+// Per live candidate: record lookup, gates, exact sums since the record start (or since the
+// tile start when the record began earlier); per-tile counts of both streams by atomics.
+template <int MODE>
+__global__ void __launch_bounds__(256) k_gate(const ScanParams p) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const unsigned long long n_res = *reinterpret_cast<const volatile unsigned long long*>(p.stage_ctr);
+  if (i >= n_res || i >= p.stage_cap) return;
+  uint4* slot = reinterpret_cast<uint4*>(p.stage + i);
+  const uint4 e0 = slot[0], e1 = slot[1];
+  const uint32_t t = e0.y;
+  if (t >= (uint32_t)p.n_wt) return;
+  const uint2 st = __ldg(p.wt_stage + t);
+  if (st.x == 0xFFFFFFFFu || i < st.x || i >= (uint64_t)st.x + st.y) return;
+  const int j = (int)e0.x;
+  if ((unsigned)j >= WT_OPS) return;
+  const int64_t wt_start = (int64_t)t * WT_OPS;
+  const int n = j & 31;
+  // ops 0..n of the candidate's 128-byte row: every needed LDG.128 is issued before the first use
+  const uint32_t* row = p.ops + wt_start + (j & ~31);
+  const int64_t left = p.n_ops - (wt_start + (j & ~31));
+  uint4 v[8];
+#pragma unroll
+  for (int g4 = 0; g4 < 8; ++g4) {
+    v[g4] = make_uint4(0u, 0u, 0u, 0u);
+    if (g4 * 4 <= n) {
+      if ((int64_t)(g4 * 4 + 4) <= left) {
+        v[g4] = __ldg(reinterpret_cast<const uint4*>(row) + g4);
+      } else {
+        v[g4].x = g4 * 4 < left ? __ldg(row + g4 * 4) : 0u;
+        v[g4].y = g4 * 4 + 1 < left ? __ldg(row + g4 * 4 + 1) : 0u;
+        v[g4].z = g4 * 4 + 2 < left ? __ldg(row + g4 * 4 + 2) : 0u;
       }
-      const int32_t rec = rec_of_op(p.op_off, lo, hi, wt_start + j);
-      const bool carry = __ldg(p.op_off + rec) < wt_start;
-      const Sums part = carry ? f : f - load_sums(p.fstart + 2 * (int64_t)rec);
-      const uint32_t info = __ldg(p.rec_info + rec);
-      const int32_t len = (int32_t)(w >> 4);
-      const bool ok_a = (info & 1u) && len >= p.min_len_a;
-      const bool ok_b = (MODE == VSV_MODE_FUSED) && (info & 2u) && len >= p.min_len_b;
-      cnt_a += ok_a ? 1u : 0u;
-      cnt_b += ok_b ? 1u : 0u;
-      uint4* o = reinterpret_cast<uint4*>(e + i);
-      o[0] = make_uint4((uint32_t)rec, w, part.r, part.q);
-      o[1] = make_uint4(part.x1, part.x2, part.x3, (ok_a ? 1u : 0u) | (ok_b ? 2u : 0u) | (carry ? 4u : 0u));
     }
   }
-  p.wt_agg[t].cnt_a = cnt_a;
-  p.wt_agg[t].cnt_b = cnt_b;
+  const int2 ss = __ldg(p.wt_starts + t);
+  const int32_t lo = max(ss.x - 1, 0);
+  const int32_t hi = max(lo, min(ss.y, (int32_t)p.n_rec - 1));
+  const int32_t rec = rec_of_op(p.op_off, lo, hi, wt_start + j);
+  const bool carry = __ldg(p.op_off + rec) < wt_start;
+  const uint32_t info = __ldg(p.rec_info + rec);
+  Sums fs = {0, 0, 0, 0, 0};
+  if (!carry) fs = load_sums(p.fstart + 2 * (int64_t)rec);
+  Sums wk = {0, 0, 0, 0, 0};
+  uint32_t w = 0;
+#pragma unroll
+  for (int g4 = 0; g4 < 8; ++g4) {
+    const uint32_t vv[4] = {v[g4].x, v[g4].y, v[g4].z, v[g4].w};
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int idx = g4 * 4 + u;
+      if (idx < n) add_op<MODE>(vv[u], wk);
+      if (idx == n) w = vv[u];
+    }
+  }
+  const Sums f = {e0.z + wk.r, e0.w + wk.q, e1.x + wk.x1, e1.y + wk.x2, e1.z + wk.x3};
+  const Sums part = f - fs;
+  const int32_t len = (int32_t)(w >> 4);
+  const bool ok_a = (info & 1u) && len >= p.min_len_a;
+  const bool ok_b = (MODE == VSV_MODE_FUSED) && (info & 2u) && len >= p.min_len_b;
+  if (ok_a) atomicAdd(&p.wt_agg[t].cnt_a, 1u);
+  if (ok_b) atomicAdd(&p.wt_agg[t].cnt_b, 1u);
+  slot[0] = make_uint4((uint32_t)rec, w, part.r, part.q);
+  slot[1] = make_uint4(part.x1, part.x2, part.x3, (ok_a ? 1u : 0u) | (ok_b ? 2u : 0u) | (carry ? 4u : 0u));
 }
 
 template <int MODE, int STREAM>
@@ -690,6 +813,10 @@ struct ScanCall {
   int32_t *ref_total, *qry_total, *aux_total;
 };
 
+// CTA shape of the streaming kernel: warps are independent workers (no block-level sync), so the
+// shape only sets how many fit an SM - 8 KB of staging per warp, 64 registers per thread -> 28.
+static constexpr size_t SCAN_SMEM = (size_t)SCAN_WARPS * SCAN_STAGES * (WT_OPS * sizeof(uint32_t) + sizeof(uint64_t));
+
 template <int MODE>
 static int run_scan_kernels(vsv_ctx* ctx, const ScanParams& p_in, int grid, TileState* d_excl, vsv_sig* out_a, int64_t cap_a,
                             vsv_sig* out_b, int64_t cap_b, int64_t* d_nout, uint32_t* rt, uint32_t* qt, uint32_t* xt) {
@@ -700,20 +827,19 @@ static int run_scan_kernels(vsv_ctx* ctx, const ScanParams& p_in, int grid, Tile
   p.tab[2] = tab_word(M::QRY, 0, 0xFFu, 0, 0); p.tab[3] = tab_word(M::QRY, 4, 0xFFu, 0, 0);
   p.tab[4] = tab_word(6u, 0, 0xFFu, RARE, 0x01u); p.tab[5] = tab_word(6u, 4, 0xFFu, RARE, 0x01u);
   VSV_CUDA(ctx, cudaEventRecord(ctx->evk0, ctx->stream));
-  VSV_LAUNCH(ctx, k_scan_wt<MODE>, (unsigned)grid, SCAN_THREADS, 0, p);
+  VSV_CUDA(ctx, cudaFuncSetAttribute(k_scan_wt<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCAN_SMEM));
+  VSV_LAUNCH(ctx, k_scan_wt<MODE>, (unsigned)grid, SCAN_THREADS, SCAN_SMEM, p);
   VSV_CUDA(ctx, cudaEventRecord(ctx->evk1, ctx->stream));
   ctx->main_open = true;
   const unsigned gt = (unsigned)vsv_cdiv(p.n_wt, 128);
-  VSV_LAUNCH(ctx, k_gate<MODE>, gt, 128, 0, p);
+  VSV_LAUNCH(ctx, k_gate<MODE>, (unsigned)vsv_cdiv((int64_t)p.stage_cap, 256), 256, 0, p);
   {  // segmented exclusive scan of the tile aggregates (n_wt + 1 elements, last = identity)
-    TileState init;
-    memset(&init, 0, sizeof(init));
-    size_t tb = 0;
-    VSV_CUDA(ctx, cub::DeviceScan::ExclusiveScan(nullptr, tb, p.wt_agg, d_excl, TileStateOp(), init, p.n_wt + 1, ctx->stream));
-    void* tmp = nullptr;
-    VSV_TRY(vsv_arena_alloc(ctx, tb, &tmp));
-    VSV_CUDA(ctx, cub::DeviceScan::ExclusiveScan(tmp, tb, p.wt_agg, d_excl, TileStateOp(), init, p.n_wt + 1, ctx->stream));
-    ctx->launches += 2;
+    const int64_t n_el = (int64_t)p.n_wt + 1, nb = vsv_cdiv(n_el, TS_BLOCK);
+    TileState* d_blk = nullptr;
+    VSV_TRY(vsv_tmp(ctx, (size_t)nb, &d_blk));
+    VSV_LAUNCH(ctx, k_ts_reduce, (unsigned)nb, TS_THREADS, 0, (const TileState*)p.wt_agg, n_el, d_blk);
+    VSV_LAUNCH(ctx, k_ts_spine, 1, 1024, 0, d_blk, nb);
+    VSV_LAUNCH(ctx, k_ts_scan, (unsigned)nb, TS_THREADS, 0, (const TileState*)p.wt_agg, n_el, (const TileState*)d_blk, d_excl);
   }
   VSV_LAUNCH(ctx, k_emit<MODE>, gt, 128, 0, p, d_excl, out_a, cap_a, out_b, cap_b, d_nout);
   if (rt) VSV_LAUNCH(ctx, k_rec_totals<MODE>, (unsigned)vsv_cdiv(p.n_rec, 256), 256, 0, p, d_excl, rt, qt, xt);

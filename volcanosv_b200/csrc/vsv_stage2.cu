@@ -523,17 +523,70 @@ extern "C" int vsv_del_cov(vsv_ctx* ctx, const int32_t* call_start, const int32_
 // tie_mode 1: `.sigs` order (SE:637-638 `sort -k2,2 -k3,3n`, LC_ALL=C): pos numeric, ties by
 //             the rest of the line, whose first field is len as a DECIMAL STRING
 //             ("100" < "95", "10" < "100").
-__global__ void k_len_string_key(const vsv_sig* __restrict__ s, int64_t n, unsigned long long* __restrict__ key,
-                                 int32_t* __restrict__ idx) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  unsigned long long v = (unsigned long long)(uint32_t)max(s[i].len, 0);
+__device__ __forceinline__ unsigned long long len_string_key(int32_t len) {
+  unsigned long long v = (unsigned long long)(uint32_t)max(len, 0);
   int digits = 1;
   for (unsigned long long t = v; t >= 10ull; t /= 10ull) ++digits;
   unsigned long long scaled = v;
   for (int d = digits; d < 10; ++d) scaled *= 10ull;  // left-justify to 10 digits
-  key[i] = (scaled << 4) | (unsigned long long)digits;
-  idx[i] = (int32_t)i;
+  return (scaled << 4) | (unsigned long long)digits;
+}
+// After the stable sort by position, ties are in input order.  The `.sigs` tie order is a property
+// of the runs of equal position only, and those runs are short (a handful of reads at one base),
+// so they are fixed in place instead of paying a second full-width radix sort:
+//   run <= TIE_SMALL : the thread at the run head does a stable insertion sort (registers/local);
+//   longer runs      : queued, one CTA each, stable rank counting in k_tie_long.
+#define TIE_SMALL 32
+__global__ void k_tie_small(const vsv_sig* __restrict__ s, const int32_t* __restrict__ pos_sorted, int64_t n,
+                            int32_t* __restrict__ order, int2* __restrict__ work, unsigned int* __restrict__ n_work) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int32_t p = pos_sorted[i];
+  if (i > 0 && pos_sorted[i - 1] == p) return;  // not a run head
+  int64_t e = i + 1;
+  while (e < n && e - i <= TIE_SMALL && pos_sorted[e] == p) ++e;
+  const int L = (int)(e - i);
+  if (L == 1) return;
+  if (L > TIE_SMALL) {
+    while (e < n && pos_sorted[e] == p) ++e;
+    work[atomicAdd(n_work, 1u)] = make_int2((int32_t)i, (int32_t)(e - i));
+    return;
+  }
+  int32_t id[TIE_SMALL];
+  unsigned long long key[TIE_SMALL];
+  for (int k = 0; k < L; ++k) {
+    const int32_t x = order[i + k];
+    const unsigned long long kx = len_string_key(s[x].len);
+    int m = k;
+    while (m > 0 && key[m - 1] > kx) { key[m] = key[m - 1]; id[m] = id[m - 1]; --m; }
+    key[m] = kx; id[m] = x;
+  }
+  for (int k = 0; k < L; ++k) order[i + k] = id[k];
+}
+__global__ void __launch_bounds__(256) k_tie_long(const vsv_sig* __restrict__ s, int32_t* __restrict__ order,
+                                                   const int2* __restrict__ work, const unsigned int* __restrict__ n_work,
+                                                   unsigned long long* __restrict__ key_tmp, int32_t* __restrict__ ord_tmp) {
+  const unsigned int nw = *n_work;
+  for (unsigned int w = blockIdx.x; w < nw; w += gridDim.x) {
+    const int64_t a = work[w].x;
+    const int L = work[w].y;
+    for (int k = threadIdx.x; k < L; k += blockDim.x) {
+      const int32_t x = order[a + k];
+      ord_tmp[a + k] = x;
+      key_tmp[a + k] = len_string_key(s[x].len);
+    }
+    __syncthreads();
+    for (int k = threadIdx.x; k < L; k += blockDim.x) {
+      const unsigned long long kk = key_tmp[a + k];
+      int rank = 0;
+      for (int m = 0; m < L; ++m) {
+        const unsigned long long km = key_tmp[a + m];
+        rank += (km < kk || (km == kk && m < k)) ? 1 : 0;
+      }
+      order[a + rank] = ord_tmp[a + k];
+    }
+    __syncthreads();
+  }
 }
 __global__ void k_gather_pos(const vsv_sig* __restrict__ s, const int32_t* __restrict__ idx, int64_t n,
                              int32_t* __restrict__ pos) {
@@ -563,34 +616,23 @@ extern "C" int vsv_sort_sigs(vsv_ctx* ctx, const vsv_sig* sigs, int64_t n, int t
   VSV_TRY(vsv_tmp(ctx, (size_t)n, &order));
   const unsigned g = (unsigned)vsv_cdiv(n, 256);
   VSV_TRY(vsv_t0(ctx));
+  VSV_LAUNCH(ctx, k_gather_pos, g, 256, 0, din, (const int32_t*)nullptr, n, pos);
+  int32_t* ks;
+  VSV_TRY(vsv_tmp(ctx, (size_t)n, &ks));
+  VSV_TRY(argsort_dev(ctx, pos, n, order, ks));
   if (tie_mode == 1) {
-    unsigned long long *k0, *k1;
-    VSV_TRY(vsv_tmp(ctx, (size_t)n, &k0));
-    VSV_TRY(vsv_tmp(ctx, (size_t)n, &k1));
-    VSV_TRY(vsv_tmp(ctx, (size_t)n, &idx0));
-    VSV_TRY(vsv_tmp(ctx, (size_t)n, &idx1));
-    VSV_LAUNCH(ctx, k_len_string_key, g, 256, 0, din, n, k0, idx0);
-    size_t tb = 0;
-    VSV_CUDA(ctx, cub::DeviceRadixSort::SortPairs(nullptr, tb, k0, k1, idx0, idx1, (int)n, 0, 40, ctx->stream));
-    void* tmp = nullptr;
-    VSV_TRY(vsv_arena_alloc(ctx, tb, &tmp));
-    VSV_CUDA(ctx, cub::DeviceRadixSort::SortPairs(tmp, tb, k0, k1, idx0, idx1, (int)n, 0, 40, ctx->stream));
-    ctx->launches += 2;
-  }
-  VSV_LAUNCH(ctx, k_gather_pos, g, 256, 0, din, (const int32_t*)idx1, n, pos);
-  {
-    int32_t* ks;
-    VSV_TRY(vsv_tmp(ctx, (size_t)n, &ks));
-    if (!idx1) {
-      VSV_TRY(argsort_dev(ctx, pos, n, order, ks));
-    } else {
-      size_t tb = 0;
-      VSV_CUDA(ctx, cub::DeviceRadixSort::SortPairs(nullptr, tb, pos, ks, idx1, order, (int)n, 0, 32, ctx->stream));
-      void* tmp = nullptr;
-      VSV_TRY(vsv_arena_alloc(ctx, tb, &tmp));
-      VSV_CUDA(ctx, cub::DeviceRadixSort::SortPairs(tmp, tb, pos, ks, idx1, order, (int)n, 0, 32, ctx->stream));
-      ctx->launches += 2;
-    }
+    unsigned long long* key_tmp;
+    int32_t* ord_tmp;
+    int2* work;
+    unsigned int* n_work;
+    VSV_TRY(vsv_tmp(ctx, (size_t)n, &key_tmp));
+    VSV_TRY(vsv_tmp(ctx, (size_t)n, &ord_tmp));
+    VSV_TRY(vsv_tmp(ctx, (size_t)(n / (TIE_SMALL + 1) + 1), &work));
+    VSV_TRY(vsv_tmp(ctx, 1, &n_work));
+    VSV_CUDA(ctx, cudaMemsetAsync(n_work, 0, sizeof(unsigned int), ctx->stream));
+    VSV_LAUNCH(ctx, k_tie_small, g, 256, 0, din, (const int32_t*)ks, n, order, work, n_work);
+    VSV_LAUNCH(ctx, k_tie_long, (unsigned)ctx->sm_count, 256, 0, din, order, (const int2*)work, (const unsigned int*)n_work,
+               key_tmp, ord_tmp);
   }
   VSV_LAUNCH(ctx, k_gather_sigs, g, 256, 0, din, order, n, dout);
   VSV_TRY(vsv_t1(ctx));
