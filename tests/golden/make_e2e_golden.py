@@ -122,33 +122,46 @@ def events_for(hsv, rng, a, b, small_rate, noisy):
     return out
 
 
-def make_dataset(seed=20240611, L=140_000):
+def make_dataset(seed=20240611, L=140_000, chrom="chr1", lite=False, name_prefix="", coverage=32):
+    """`lite` (whole-genome fixture: many small chromosomes) leaves out the hand-placed special cases,
+    keeps read sequences compressible and forces one homozygous INS per chromosome (CSS:87 needs one)."""
     rng = random.Random(seed)
     ref = rand_seq(rng, L)
     svs = make_svs(rng, L)
+    if lite:
+        svs[0].update(type="INS", zyg="hom", seq=rand_seq(rng, svs[0]["len"]))
+        return _finish_dataset(rng, ref, svs, L, chrom, True, name_prefix, coverage)
+    return _finish_dataset(rng, ref, svs, L, chrom, False, name_prefix, coverage)
+
+
+def _finish_dataset(rng, ref, svs, L, chrom, lite, name_prefix, coverage):
     # near-duplicate calls for remove_redundancy: the two haplotypes carry similar SVs too far apart
     # to be paired (> 200 bp) but close enough to be linked (INS: <= 500 bp + edit similarity;
     # DEL: <= 3000 bp + overlap)
     def mid(i):
         a = svs[i]["pos"] + (svs[i]["len"] if svs[i]["type"] == "DEL" else 0)
         return (a + svs[i + 1]["pos"]) // 2
-    s1 = rand_seq(rng, 300)
-    s2 = "".join(c if rng.random() > 0.08 else rng.choice("ACGT") for c in s1) + rand_seq(rng, 11)
-    m = mid(2)
-    svs.append(dict(pos=m - 160, type="INS", len=len(s1), seq=s1, zyg="h1"))
-    svs.append(dict(pos=m + 160, type="INS", len=len(s2), seq=s2, zyg="h2"))
-    m = mid(6)
-    svs.append(dict(pos=m - 300, type="DEL", len=500, seq="", zyg="h1"))
-    svs.append(dict(pos=m + 50, type="DEL", len=523, seq="", zyg="h2"))
+    if not lite:
+        s1 = rand_seq(rng, 300)
+        s2 = "".join(c if rng.random() > 0.08 else rng.choice("ACGT") for c in s1) + rand_seq(rng, 11)
+        m = mid(2)
+        svs.append(dict(pos=m - 160, type="INS", len=len(s1), seq=s1, zyg="h1"))
+        svs.append(dict(pos=m + 160, type="INS", len=len(s2), seq=s2, zyg="h2"))
+        m = mid(6)
+        svs.append(dict(pos=m - 300, type="DEL", len=500, seq="", zyg="h1"))
+        svs.append(dict(pos=m + 50, type="DEL", len=523, seq="", zyg="h2"))
     svs.sort(key=lambda x: x["pos"])
     haps = {1: hap_svs(svs, 1, rng), 2: hap_svs(svs, 2, rng)}
     # contig-only artefacts (no read carries them): the read-support filter must drop them
-    ghosts = {1: [(mid(9), "I", 61, rand_seq(rng, 61)), (mid(12), "D", 47, "")], 2: [(mid(15), "I", 120, rand_seq(rng, 120))]}
+    if lite:
+        ghosts = {1: [(mid(1), "I", 61, rand_seq(rng, 61))] if len(svs) > 2 and rng.random() < 0.4 else [], 2: []}
+    else:
+        ghosts = {1: [(mid(9), "I", 61, rand_seq(rng, 61)), (mid(12), "D", 47, "")], 2: [(mid(15), "I", 120, rand_seq(rng, 120))]}
     # ---------------- contigs: two per haplotype, overlapping by ~8 kb; one on the minus strand,
     # one split (primary + supplementary) at a big deletion
     contig_recs, contig_fa = [], []
     for hap in (1, 2):
-        spans = [(150, 76_000), (68_000, L - 120)]
+        spans = [(150, int(L * 0.56)), (int(L * 0.5), L - 120)] if lite else [(150, 76_000), (68_000, L - 120)]
         for k, (a, b) in enumerate(spans):
             name = "PS%d_%d_hp%d_%d" % (a + 1, b, hap, k)
             ev = events_for(haps[hap], rng, a, b, 0.00012, False)
@@ -172,7 +185,8 @@ def make_dataset(seed=20240611, L=140_000):
     contig_recs.sort(key=lambda r: r[2])
     # ---------------- reads: HiFi-like, 32x
     reads = []
-    n_reads = int(L * 32 / 9000)
+    n_reads = int(L * coverage / 9000)
+    rseq = (lambda n: "A" * n) if lite else (lambda n: rand_seq(rng, n))
     for i in range(n_reads):
         hap = rng.choice((1, 2))
         ln = max(300, int(rng.gauss(9000, 2500))) if rng.random() > 0.03 else rng.randint(200, 480)
@@ -182,7 +196,7 @@ def make_dataset(seed=20240611, L=140_000):
             continue
         rev = rng.random() < 0.5
         mapq = 60 if rng.random() < 0.88 else rng.choice([0, 5, 19, 20, 33, 49, 50, 55])
-        name = "read%05d" % i
+        name = name_prefix + "read%05d" % i
         ev = events_for(haps[hap], rng, a, b, 0.0009, True)
         big = [e for e in ev if e[2] >= 600 and a + 800 < e[0] < b - 800 - (e[2] if e[1] == "D" else 0)]
         if big and rng.random() < 0.6:
@@ -194,10 +208,10 @@ def make_dataset(seed=20240611, L=140_000):
             c2, q2 = build_alignment(ref, [e for e in ev if e[0] > r2s], r2s, b)
             mid = sq if t == "I" else ""
             full = q1 + mid + q2
-            qseq = rand_seq(rng, len(full))
+            qseq = rseq(len(full))
             sa_cig = "%dS%s" % (len(q1) + len(mid), cigar_str(c2))
             st = "-" if rev else "+"
-            sa = "SA:Z:chr1,%d,%s,%s,%d,%d;" % (r2s + 1, st, sa_cig, mapq, rng.randint(0, 30))
+            sa = "SA:Z:%s,%d,%s,%s,%d,%d;" % (chrom, r2s + 1, st, sa_cig, mapq, rng.randint(0, 30))
             reads.append((name, 16 if rev else 0, a, mapq, c1 + [(4, len(mid) + len(q2))], qseq, [sa]))
             reads.append((name, 2064 if rev else 2048, r2s, mapq, [(5, len(q1) + len(mid))] + c2,
                           qseq[len(q1) + len(mid):], []))
@@ -206,7 +220,7 @@ def make_dataset(seed=20240611, L=140_000):
             lead = rng.choice([0, 0, 0, rng.randint(5, 300)])
             tail = rng.choice([0, 0, 0, rng.randint(5, 300)])
             cig = ([(4, lead)] if lead else []) + c + ([(4, tail)] if tail else [])
-            reads.append((name, 16 if rev else 0, a, mapq, cig, rand_seq(rng, lead + len(q) + tail), []))
+            reads.append((name, 16 if rev else 0, a, mapq, cig, rseq(lead + len(q) + tail), []))
     reads.sort(key=lambda r: r[2])
     return ref, svs, contig_recs, contig_fa, reads
 

@@ -140,13 +140,29 @@ def _main(argv):
     p.add_argument("--reference", "-ref")
     p.add_argument("--read_signature_dir", "-rdsig")
     p.add_argument("--pre_cutesig", "-presig")
-    p.add_argument("--chr_num", "-chr", type=int, required=True)
+    p.add_argument("--chr_num", "-chr", type=int, default=None)
     p.add_argument("--n_thread", "-t", type=int, default=11)
     p.add_argument("--n_thread_align", "-ta", type=int, default=10)
     p.add_argument("--mem_per_thread", "-mempt", default="768M")
     p.add_argument("--prefix", "-px", default="Sample")
-    p.add_argument("--contig_bam", "-cbam", required=True, help="sorted contig-to-reference alignments (RVC:49-58 output)")
+    p.add_argument("--contig_bam", "-cbam", required=True,
+                   help="sorted contig-to-reference alignments (RVC:49-58 output); whole-genome mode: a pattern with {chr}")
     a = p.parse_args(argv)
+    if a.chr_num is None:                      # whole-genome mode (MAIN:266-279); one process per GPU under torchrun
+        import os
+        rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+        barrier = None
+        if world > 1:
+            import torch
+            import torch.distributed as dist
+            torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
+            dist.init_process_group("gloo")    # file-level hand-over only: no data-path collective
+            barrier = dist.barrier
+        out = OP.large_indel_wgs(a.contig_bam, a.input_dir, a.reference, a.bam_file, a.output_dir, a.data_type, a.prefix,
+                                 a.read_signature_dir, a.pre_cutesig, rank=rank, world=world, barrier=barrier)
+        if out:
+            print(out)
+        return
     contigs = "%s/chr%d/assembly/final_contigs/%s_final_contigs.fa" % (a.input_dir, a.chr_num, a.prefix)
     print(OP.large_indel_chr(a.contig_bam, contigs, a.reference, a.bam_file, a.output_dir, a.data_type, a.chr_num, a.prefix,
                              a.read_signature_dir, a.pre_cutesig))

@@ -666,10 +666,19 @@ __global__ void __launch_bounds__(TS_THREADS) k_ts_scan(const TileState* __restr
 // Per live candidate: record lookup, gates, exact sums since the record start (or since the
 // tile start when the record began earlier); per-tile counts of both streams by atomics.
 template <int MODE>
+__device__ __forceinline__ void gate_slot(const ScanParams& p, uint64_t i);
+
+// persistent grid-stride launch: the number of reserved slots is only known on the device
+template <int MODE>
 __global__ void __launch_bounds__(256) k_gate(const ScanParams p) {
-  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  const unsigned long long n_res = *reinterpret_cast<const volatile unsigned long long*>(p.stage_ctr);
-  if (i >= n_res || i >= p.stage_cap) return;
+  unsigned long long n_res = *reinterpret_cast<const volatile unsigned long long*>(p.stage_ctr);
+  if (n_res > p.stage_cap) n_res = p.stage_cap;
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_res; i += stride) gate_slot<MODE>(p, i);
+}
+
+template <int MODE>
+__device__ __forceinline__ void gate_slot(const ScanParams& p, uint64_t i) {
   uint4* slot = reinterpret_cast<uint4*>(p.stage + i);
   const uint4 e0 = slot[0], e1 = slot[1];
   const uint32_t t = e0.y;
@@ -832,7 +841,7 @@ static int run_scan_kernels(vsv_ctx* ctx, const ScanParams& p_in, int grid, Tile
   VSV_CUDA(ctx, cudaEventRecord(ctx->evk1, ctx->stream));
   ctx->main_open = true;
   const unsigned gt = (unsigned)vsv_cdiv(p.n_wt, 128);
-  VSV_LAUNCH(ctx, k_gate<MODE>, (unsigned)vsv_cdiv((int64_t)p.stage_cap, 256), 256, 0, p);
+  VSV_LAUNCH(ctx, k_gate<MODE>, (unsigned)std::min<int64_t>(vsv_cdiv((int64_t)p.stage_cap, 256), (int64_t)ctx->sm_count * 8), 256, 0, p);
   {  // segmented exclusive scan of the tile aggregates (n_wt + 1 elements, last = identity)
     const int64_t n_el = (int64_t)p.n_wt + 1, nb = vsv_cdiv(n_el, TS_BLOCK);
     TileState* d_blk = nullptr;

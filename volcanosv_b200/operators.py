@@ -49,10 +49,11 @@ FILTER_PARA = {
 _ctx: Optional[L.Context] = None
 
 
-def context(device: int = 0) -> L.Context:
+def context(device: Optional[int] = None) -> L.Context:
+    """The process-wide library context (one process per GPU: LOCAL_RANK picks the device)."""
     global _ctx
     if _ctx is None:
-        _ctx = L.Context(device)
+        _ctx = L.Context(int(os.environ.get("LOCAL_RANK", "0")) if device is None else device)
     return _ctx
 
 
@@ -1016,6 +1017,87 @@ def raw_variant_call(contig_bam: str, contig_path: str, reference_path: str, out
     return os.path.join(output_dir, "final_vcf", "volcano_variant_no_redundancy.vcf")
 
 
+def _write_fai(reference: str) -> List[tuple]:
+    """`samtools faidx <ref>` (MAIN:78-96): writes <ref>.fai, returns [(name, length)] in file order."""
+    out = []
+    with open(reference, "rb") as fa:
+        data = fa.read().split(b"\n")
+    rows = []
+    pos, name, ln, lb, start = 0, None, 0, None, 0
+    for row in data:
+        if row.startswith(b">"):
+            if name is not None:
+                rows.append((name, ln, start, lb, lb + 1))
+            name, ln, lb, start = row[1:].split()[0].decode(), 0, None, pos + len(row) + 1
+        elif row:
+            lb = lb or len(row)
+            ln += len(row)
+        pos += len(row) + 1
+    if name is not None:
+        rows.append((name, ln, start, lb, lb + 1))
+    with open(reference + ".fai", "w") as f:
+        for r in rows:
+            f.write("%s\t%d\t%d\t%d\t%d\n" % r)
+            out.append((r[0], r[1]))
+    return out
+
+
+def _write_chrom_ref(ref: Dict[str, str], ref_dir: str, chr_num: int) -> str:
+    os.makedirs(ref_dir, exist_ok=True)
+    one = os.path.join(ref_dir, "chr%d.fa" % chr_num)
+    seq = ref["chr%d" % chr_num]
+    _write_lines(one, [">chr%d\n" % chr_num] + [seq[i:i + 60] + "\n" for i in range(0, len(seq), 60)])
+    return one
+
+
+def large_indel_wgs(contig_bam_pattern: str, input_dir: str, reference: str, rbam_file: str, output_dir: str, dtype: str,
+                    prefix: str = "Sample", read_signature_dir: Optional[str] = None, pre_cutesig: Optional[str] = None,
+                    chroms: Sequence[int] = tuple(range(1, 23)), rank: int = 0, world: int = 1, barrier=None):
+    """LI/volcanosv-vc-large-indel.py WITHOUT -chr (MAIN:233-319): chr1..chr22 through the raw-call
+    chain, bodies concatenated in numeric chromosome order into raw_variants_wgs.vcf, ONE
+    genome-wide filter + genotype correction, phasing.
+
+    `contig_bam_pattern` holds `{chr}` (the sorted contig alignments of each chromosome,
+    RVC:49-58 output).  With world > 1 every rank (one per GPU) takes the chromosomes that
+    `shard.assign_lpt` gives it (weight = size of the contig alignments + the chromosome length as a
+    proxy for the reads); files meet in `output_dir`, `barrier()` (e.g. torch.distributed.barrier)
+    separates the per-chromosome phase from the genome-wide one, which rank 0 runs.  Returns the
+    final VCF path on rank 0, None elsewhere."""
+    from . import shard as SH
+    os.makedirs(output_dir, exist_ok=True)
+    ref = load_contigs(reference)
+    header_file = os.path.join(output_dir, "VCF_header")
+    ref_dir = os.path.join(output_dir, "ref_by_chr")
+    if rank == 0:
+        contigs = _write_fai(reference)
+        _write_lines(header_file, ["##fileformat=VCFv4.2\n"] + ["##contig=<ID=%s,length=%d>\n" % c for c in contigs] +
+                     final_header_info(prefix))
+    weights = {}
+    for c in chroms:
+        p = contig_bam_pattern.format(chr=c)
+        weights[c] = float(os.path.getsize(p) if os.path.exists(p) else 0) + float(len(ref.get("chr%d" % c, "")))
+    mine = SH.assign_lpt(weights, world)[rank]
+    for c in sorted(mine):
+        one = _write_chrom_ref(ref, ref_dir, c)
+        contig_path = "%s/chr%d/assembly/final_contigs/%s_final_contigs.fa" % (input_dir, c, prefix)
+        raw_variant_call(contig_bam_pattern.format(chr=c), contig_path, one, os.path.join(output_dir, "chr%d" % c), dtype, c,
+                         rbam_file, read_signature_dir)
+    if barrier is not None:
+        barrier()
+    if rank != 0:
+        return None
+    header, body = [], []
+    for c in chroms:                                                                       # MAIN:271-278
+        header, b = _read_vcf(os.path.join(output_dir, "chr%d" % c, "final_vcf", "volcano_variant_no_redundancy.vcf"))
+        body += b
+    raw = os.path.join(output_dir, "raw_variants_wgs.vcf")
+    _write_lines(raw, header + body)
+    final = filter_gt_correction(raw, rbam_file, reference, dtype, None, pre_cutesig)
+    outfile = os.path.join(output_dir, "%s_volcanosv_large_indel.vcf" % prefix)
+    phase_vcf(final, outfile, header_file)
+    return outfile
+
+
 def large_indel_chr(contig_bam: str, contig_path: str, reference: str, rbam_file: str, output_dir: str, dtype: str,
                     chr_num: int, prefix: str = "Sample", read_signature_dir: Optional[str] = None,
                     pre_cutesig: Optional[str] = None):
@@ -1028,26 +1110,8 @@ def large_indel_chr(contig_bam: str, contig_path: str, reference: str, rbam_file
                                              if k == "chr%d" % chr_num]
     header_file = os.path.join(out_chr, "VCF_header")
     _write_lines(header_file, vcf_header + final_header_info(prefix))
-    with open(reference + ".fai", "w") as f:                                               # samtools faidx (MAIN:88-96)
-        off = 0
-        with open(reference, "rb") as fa:
-            data = fa.read().split(b"\n")
-        pos, name, ln, lb, start = 0, None, 0, None, 0
-        for row in data:
-            if row.startswith(b">"):
-                if name is not None:
-                    f.write("%s\t%d\t%d\t%d\t%d\n" % (name, ln, start, lb, lb + 1))
-                name, ln, lb, start = row[1:].split()[0].decode(), 0, None, pos + len(row) + 1
-            elif row:
-                lb = lb or len(row)
-                ln += len(row)
-            pos += len(row) + 1
-        if name is not None:
-            f.write("%s\t%d\t%d\t%d\t%d\n" % (name, ln, start, lb, lb + 1))
-    ref_dir = os.path.join(out_chr, "ref_by_chr")
-    os.makedirs(ref_dir, exist_ok=True)
-    one = os.path.join(ref_dir, "chr%d.fa" % chr_num)
-    _write_lines(one, [">chr%d\n" % chr_num] + [ref["chr%d" % chr_num][i:i + 60] + "\n" for i in range(0, len(ref["chr%d" % chr_num]), 60)])
+    _write_fai(reference)                                                                  # samtools faidx (MAIN:88-96)
+    one = _write_chrom_ref(ref, os.path.join(out_chr, "ref_by_chr"), chr_num)
     raw = raw_variant_call(contig_bam, contig_path, one, out_chr, dtype, chr_num, rbam_file, read_signature_dir)
     final = filter_gt_correction(raw, rbam_file, reference, dtype, chr_num, pre_cutesig)
     outfile = os.path.join(out_chr, "%s_volcanosv_large_indel_chr%d.vcf" % (prefix, chr_num))

@@ -11,6 +11,7 @@ LI/filter_GT_correction.py:111-172 (SE -> CSS -> GTD/GTI).
 """
 from __future__ import annotations
 
+import contextlib
 import ctypes as C
 from dataclasses import dataclass, field
 from typing import Dict, Optional
@@ -67,6 +68,7 @@ class ChromShard:
         self.sig_cap = 0
         self.h2d_bytes = 0
         self.d2h_bytes = 0
+        self._pending = None
 
     # ---- allocation ------------------------------------------------------------------
     def _buf(self, name, n, dtype):
@@ -76,10 +78,14 @@ class ChromShard:
             self.d[name] = t
         return t
 
-    def upload(self, batch, cands, n_ops: Optional[int] = None):
+    def upload(self, batch, cands, n_ops: Optional[int] = None, stream: Optional["torch.cuda.Stream"] = None):
         """H2D of one shard's inputs (packed records + candidate table).  Values are numpy
-        arrays or (pinned) torch CPU tensors; `ops` may be uint32 numpy or an int32 tensor."""
+        arrays or (pinned) torch CPU tensors; `ops` may be uint32 numpy or an int32 tensor.
+        With `stream` the copies are only enqueued there (pinned sources) and `finish_upload()`
+        must be called before `run()`: that is how `ShardStream` overlaps the upload of the
+        next shard with the kernels of the current one."""
         self.h2d_bytes = 0
+        self._pending = None
 
         def put(name, src):
             if isinstance(src, np.ndarray):
@@ -91,34 +97,48 @@ class ChromShard:
             self.h2d_bytes += src.numel() * src.element_size()
             return src
 
-        if "ops16" in batch:
-            # compact staging (include/volcanosv_b200.h: vsv_expand_ops16): 2 bytes per op over PCIe,
-            # widened on the device into the BAM-native u32 array the scanners read
-            n_ops = int(n_ops if n_ops is not None else batch["ops16"].numel() if hasattr(batch["ops16"], "numel") else len(batch["ops16"]))
-            src16 = batch["ops16"]
-            if isinstance(src16, np.ndarray):
-                src16 = torch.from_numpy(np.ascontiguousarray(src16.view(np.int16)))
-            o16 = self._buf("in_ops16", src16.numel(), src16.dtype)
-            o16[: src16.numel()].copy_(src16, non_blocking=True)
-            self.h2d_bytes += src16.numel() * 2
-            ei = put("in_exc_idx", batch["exc_idx"]) if len(batch["exc_idx"]) else None
-            ev = put("in_exc_val", batch["exc_val"]) if len(batch["exc_val"]) else None
-            n_exc = 0 if ei is None else ei.numel()
-            ops = self._buf("in_ops", n_ops, torch.int32)
-            torch.cuda.current_stream().synchronize()
-            self._chk(self.lib.vsv_expand_ops16(self.h, _dp(o16), n_ops, _dp(self.d["in_exc_idx"]) if n_exc else None,
-                                                _dp(self.d["in_exc_val"]) if n_exc else None, n_exc, _dp(ops)))
-        else:
-            put("in_ops", batch["ops"])
-        for k in ("op_off", "pos", "mapq", "qlen"):
-            put("in_" + k, batch[k])
-        for k in ("pos", "svlen", "type", "gt"):
-            put("cand_" + k, cands[k])
+        with torch.cuda.stream(stream if stream is not None else torch.cuda.current_stream()):
+            expand = None
+            if "ops16" in batch:
+                # compact staging (include/volcanosv_b200.h: vsv_expand_ops16): 2 bytes per op over PCIe,
+                # widened on the device into the BAM-native u32 array the scanners read
+                src16 = batch["ops16"]
+                if isinstance(src16, np.ndarray):
+                    src16 = torch.from_numpy(np.ascontiguousarray(src16.view(np.int16)))
+                n_ops = int(n_ops if n_ops is not None else src16.numel())
+                o16 = self._buf("in_ops16", src16.numel(), src16.dtype)
+                o16[: src16.numel()].copy_(src16, non_blocking=True)
+                self.h2d_bytes += src16.numel() * 2
+                ei = put("in_exc_idx", batch["exc_idx"]) if len(batch["exc_idx"]) else None
+                put("in_exc_val", batch["exc_val"]) if len(batch["exc_val"]) else None
+                expand = (o16, 0 if ei is None else ei.numel(), self._buf("in_ops", n_ops, torch.int32))
+            else:
+                put("in_ops", batch["ops"])
+            for k in ("op_off", "pos", "mapq", "qlen"):
+                put("in_" + k, batch[k])
+            for k in ("pos", "svlen", "type", "gt"):
+                put("cand_" + k, cands[k])
+            done = torch.cuda.Event()
+            done.record()
         self.n_rec = len(batch["pos"])
         self.n_ops = int(n_ops) if n_ops is not None else int(batch["op_off"][-1])
         self.n_cand = len(cands["pos"])
-        torch.cuda.current_stream().synchronize()
-        self.ctx.sync()
+        self._pending = (done, expand)
+        if stream is None:
+            self.finish_upload()
+
+    def finish_upload(self):
+        """Waits for the enqueued copies and widens a compact batch on the device."""
+        if self._pending is None:
+            return
+        done, expand = self._pending
+        self._pending = None
+        done.synchronize()
+        if expand is not None:
+            o16, n_exc, ops = expand
+            self._chk(self.lib.vsv_expand_ops16(self.h, _dp(o16), self.n_ops, _dp(self.d["in_exc_idx"]) if n_exc else None,
+                                                _dp(self.d["in_exc_val"]) if n_exc else None, n_exc, _dp(ops)))
+            self.ctx.sync()
 
     def _chk(self, rc):
         if rc != 0:
@@ -227,11 +247,19 @@ class ChromShard:
         self.ctx.sync()
         torch.cuda.current_stream().synchronize()
 
-    def download(self, res: ShardResult, pinned: Optional[Dict[str, torch.Tensor]] = None) -> Dict[str, np.ndarray]:
+    def download(self, res: ShardResult, pinned: Optional[Dict[str, torch.Tensor]] = None,
+                 stream: Optional["torch.cuda.Stream"] = None) -> Dict[str, np.ndarray]:
         """D2H of the shard's results (per-candidate table + signature arrays)."""
         self.ctx.sync()
         out = {}
         self.d2h_bytes = 0
+        ctxm = torch.cuda.stream(stream) if stream is not None else contextlib.nullcontext()
+        with ctxm:
+            self._download_into(res, pinned, out)
+            torch.cuda.current_stream().synchronize()
+        return {k: v.numpy() for k, v in out.items()}
+
+    def _download_into(self, res, pinned, out):
         for k, t in res.out.items():
             if pinned is not None:
                 dst = pinned.get(k)
@@ -243,9 +271,37 @@ class ChromShard:
             else:
                 out[k] = t.cpu()
             self.d2h_bytes += t.numel() * t.element_size()
-        torch.cuda.current_stream().synchronize()
-        return {k: v.numpy() for k, v in out.items()}
 
 
 class _Regrow(Exception):
     pass
+
+
+class ShardStream:
+    """Two shard slots on one GPU: the H2D copies of shard k+1 (their own stream) run while shard
+    k is expanded, scanned, joined, genotyped and read back.  A chromosome-sharded run is a
+    queue of such shards per GPU (MAIN:268), so this is the steady state of the whole-genome mode."""
+
+    def __init__(self, device: int = 0, dtype: str = "ONT"):
+        self.slots = [ChromShard(device, dtype), ChromShard(device, dtype)]
+        self.up = torch.cuda.Stream(device=self.slots[0].device)
+        self.down = torch.cuda.Stream(device=self.slots[0].device)
+        self.n_in = 0
+        self.n_out = 0
+
+    def submit(self, batch, cands, n_ops: Optional[int] = None):
+        """Enqueues the upload of the next shard (pinned host buffers); returns at once."""
+        if self.n_in - self.n_out >= 2:
+            raise L.VsvError(L.E_ARG, "ShardStream: both slots are busy; collect() first")
+        self.slots[self.n_in % 2].upload(batch, cands, n_ops=n_ops, stream=self.up)
+        self.n_in += 1
+
+    def collect(self, pinned: Optional[Dict[str, torch.Tensor]] = None):
+        """Finishes the oldest submitted shard: hot path + D2H.  Returns (ShardResult, arrays)."""
+        if self.n_out >= self.n_in:
+            raise L.VsvError(L.E_ARG, "ShardStream: nothing submitted")
+        sh = self.slots[self.n_out % 2]
+        self.n_out += 1
+        sh.finish_upload()
+        res = sh.run_safe()
+        return res, sh.download(res, pinned, stream=self.down)
