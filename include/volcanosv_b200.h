@@ -234,6 +234,33 @@ int vsv_genotype(vsv_ctx* ctx, const int32_t* read_start, const int32_t* read_en
 int vsv_edit_distance_batch(vsv_ctx* ctx, const uint8_t* chars, const int64_t* str_off, int64_t n_str,
                             const int32_t* ia, const int32_t* ib, int64_t n_pair, int32_t* dist);
 
+/* ---- host-side BAM feeder (no CUDA; zlib + threads) ------------------------------------- */
+/* Replaces `pysam.AlignmentFile(path).fetch(chr)` and the per-record attribute reads of the
+ * whole-chromosome scans (LI/extract_reads_signature.py:107-145, LI/sig_extract.py:514-560,
+ * LI/extract_contig_signature_Hifi.py:386-419): BGZF inflate (blocks in parallel) + BAM record
+ * -> the packed columns of this header.  The whole file is inflated into memory at open.
+ * Unmapped records (refID < 0) are skipped, CG:B,I long CIGARs are resolved.  Errors:
+ * VSV_E_ARG + vsv_bam_last_error() (thread-local message). */
+typedef struct vsv_bam vsv_bam;
+int vsv_bam_open(const char* path, int n_threads, vsv_bam** out);
+void vsv_bam_close(vsv_bam* b);
+const char* vsv_bam_last_error(void);
+int vsv_bam_n_ref(const vsv_bam* b);
+int vsv_bam_ref(const vsv_bam* b, int i, const char** name, int64_t* len, int64_t* n_rec);
+/* sizes[5] = records, CIGAR ops, qname bytes, SEQ bytes, SA-tag bytes of reference `tid` */
+int vsv_bam_chrom_sizes(vsv_bam* b, int tid, int64_t* sizes);
+/* Columns of reference `tid` in file order; NULL skips a column.  `ops` = BAM-native u32,
+ * `ops16` + (exc_idx, exc_val, exc_cap, n_exc) = the staging format of vsv_expand_ops16
+ * (VSV_E_CAPACITY with *n_exc = needed when the list is too small).  *_off arrays have n_rec + 1
+ * entries; names / seq (ASCII) / sa are concatenated without terminators. */
+int vsv_bam_chrom_fill(vsv_bam* b, int tid, int32_t* pos, uint8_t* mapq, uint16_t* flag, int32_t* qlen,
+                       int64_t* op_off, uint32_t* ops, uint16_t* ops16, int64_t* exc_idx, uint32_t* exc_val,
+                       int64_t exc_cap, int64_t* n_exc, int64_t* name_off, char* names, int64_t* seq_off,
+                       char* seq, int64_t* sa_off, char* sa);
+/* SEQ (ASCII) of record i of reference `tid`: sparse `read.seq` accesses (SE:452, ECS_H:642-700).
+ * VSV_E_CAPACITY with *len = needed when cap is too small. */
+int vsv_bam_record_seq(vsv_bam* b, int tid, int64_t i, char* out, int64_t cap, int64_t* len);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,131 @@
+"""Native BAM feeder (vsv_bam_*, host code: runs without a GPU) against the SAM-text loader on the
+same records.  BAM files are written by tests/bamio.py from the committed SAM fixtures."""
+import gzip
+import os
+import sys
+
+import numpy as np
+import pytest
+
+
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+import bamio  # noqa: E402
+from volcanosv_b200 import lib as L
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+E2E = os.path.join(HERE, "golden", "e2e", "input")
+
+
+def sam_records(path):
+    refs, recs = [], []
+    with gzip.open(path, "rt") as fh:
+        for line in fh:
+            if line[0] == "@":
+                if line.startswith("@SQ"):
+                    d = dict(x.split(":", 1) for x in line.rstrip("\n").split("\t")[1:])
+                    refs.append((d["SN"], int(d["LN"])))
+                continue
+            recs.append(line.rstrip("\n").split("\t"))
+    return refs, recs
+
+
+def check(bam, sam, compact):
+    refs, recs = sam_records(sam)
+    bf = L.BamFile(bam, n_threads=3)
+    assert [(n, ln) for n, ln, _ in bf.refs] == refs
+    for tid, (chrom, _, n_rec) in enumerate(bf.refs):
+        mine = [f for f in recs if f[2] == chrom]
+        assert n_rec == len(mine)
+        d = bf.chrom(chrom, compact=compact)
+        ops = d["ops"] if not compact else None
+        if compact:
+            ops = d["ops16"].astype(np.uint32)
+            assert np.all(np.diff(d["exc_idx"]) > 0)
+            assert np.all((d["ops16"][d["exc_idx"]] >> 4) == 0xFFF)
+            ops[d["exc_idx"]] = d["exc_val"]
+        names = bytes(d["names"])
+        seq = bytes(d["seq"])
+        sa = bytes(d["sa"])
+        for i, f in enumerate(mine):
+            cig = [(int(n) << 4) | bamio._OPC[c] for n, c in bamio.re.findall(r"(\d+)([MIDNSHP=X])", f[5])]
+            assert d["pos"][i] == int(f[3]) - 1 and d["mapq"][i] == int(f[4]) and d["flag"][i] == int(f[1])
+            assert list(ops[d["op_off"][i]: d["op_off"][i + 1]]) == cig
+            assert names[d["name_off"][i]: d["name_off"][i + 1]].decode() == f[0]
+            want_seq = "" if f[9] == "*" else f[9]
+            assert d["qlen"][i] == len(want_seq)
+            assert seq[d["seq_off"][i]: d["seq_off"][i + 1]].decode() == want_seq
+            want_sa = "".join(t[5:] for t in f[11:] if t.startswith("SA:Z:"))
+            assert sa[d["sa_off"][i]: d["sa_off"][i + 1]].decode() == want_sa
+    bf.close()
+
+
+@pytest.mark.parametrize("compact", [False, True])
+def test_reads_and_contigs_round_trip(tmp_path, compact):
+    for name in ("reads", "contigs"):
+        bam = str(tmp_path / (name + ".bam"))
+        bamio.sam_to_bam(os.path.join(E2E, name + ".sam.gz"), bam, block=20000 if name == "reads" else 65000)
+        check(bam, os.path.join(E2E, name + ".sam.gz"), compact)
+
+
+def test_long_cigar_unmapped_and_long_ops(tmp_path):
+    """CG:B,I long CIGAR (> 65535 ops), an unmapped record (skipped), ops of 4095+ bases (exception list)."""
+    rng = np.random.default_rng(5)
+    n = 70000
+    cig = "".join("%d%s" % (int(l), "MID"[i % 3] if i % 3 else "M") for i, l in enumerate(rng.integers(1, 9, n)))
+    cig = re_fix(cig)
+    qlen = sum(int(a) for a, c in bamio.re.findall(r"(\d+)([MIDNSHP=X])", cig) if c in "MIS=X")
+    sam = tmp_path / "x.sam"
+    with open(sam, "w") as f:
+        f.write("@HD\tVN:1.6\n@SQ\tSN:chrA\tLN:900000\n@SQ\tSN:chrB\tLN:5000000\n")
+        f.write("long\t0\tchrA\t11\t60\t%s\t*\t0\t0\t%s\t*\tSA:Z:chrB,5,+,10S20M,60,1;\n" % (cig, "ACGT" * (qlen // 4) + "A" * (qlen % 4)))
+        f.write("nomap\t4\t*\t0\t0\t*\t*\t0\t0\tACGTN\t*\n")
+        f.write("big\t16\tchrB\t101\t7\t5S4095M70000D4094I100000N3M\t*\t0\t0\t*\t*\n")
+    with open(sam, "rb") as fi, gzip.open(str(sam) + ".gz", "wb") as fo:
+        fo.write(fi.read())
+    bam = str(tmp_path / "x.bam")
+    bamio.sam_to_bam(str(sam) + ".gz", bam)
+    check(bam, str(sam) + ".gz", False)
+    check(bam, str(sam) + ".gz", True)
+    d = L.BamFile(bam).chrom("chrB", compact=True)
+    assert len(d["exc_idx"]) == 3 and list(d["exc_val"] >> 4) == [4095, 70000, 100000]
+
+
+def re_fix(cig):
+    """merge adjacent equal ops (a valid CIGAR never repeats an op)"""
+    out = []
+    for n, c in bamio.re.findall(r"(\d+)([MIDNSHP=X])", cig):
+        if out and out[-1][1] == c:
+            out[-1][0] += int(n)
+        else:
+            out.append([int(n), c])
+    return "".join("%d%s" % (n, c) for n, c in out)
+
+
+def test_errors(tmp_path):
+    with pytest.raises(L.VsvError):
+        L.BamFile(str(tmp_path / "missing.bam"))
+    p = tmp_path / "bad.bam"
+    p.write_bytes(b"not a bam file at all, just bytes")
+    with pytest.raises(L.VsvError):
+        L.BamFile(str(p))
+    with gzip.open(str(tmp_path / "plain.gz"), "wb") as f:     # gzip but not BGZF
+        f.write(b"BAM\1")
+    with pytest.raises(L.VsvError):
+        L.BamFile(str(tmp_path / "plain.gz"))
+
+
+def test_alignment_source_bam_equals_sam(tmp_path):
+    """operators.AlignmentSource: a .bam through the native feeder == the same records from SAM text."""
+    from volcanosv_b200 import operators as OP
+    for nm in ("reads", "contigs"):
+        bam = str(tmp_path / (nm + ".bam"))
+        bamio.sam_to_bam(os.path.join(E2E, nm + ".sam.gz"), bam)
+        a = OP.AlignmentSource(os.path.join(E2E, nm + ".sam.gz"))
+        b = OP.AlignmentSource(bam)
+        assert a.references() == b.references()
+        A, B = a.records("chr1"), b.records("chr1")
+        for k in ("ops", "op_off", "pos", "mapq", "flag", "qlen", "is_rev", "first_op", "last_op"):
+            assert np.array_equal(getattr(A, k), getattr(B, k)), k
+        assert A.n == B.n and A.qname == B.qname and A.sa == B.sa
+        assert all(A.seq[i] == B.seq[i] for i in range(0, A.n, 5))
+        assert b.records("chrNone").n == 0

@@ -1,0 +1,414 @@
+// Host-side BAM feeder: BGZF inflate + BAM record -> the packed
+// struct-of-arrays the scanners read, without pysam/htslib.  Replaces, for whole-chromosome
+// scans, `pysam.AlignmentFile(path).fetch(chr)` + the per-record attribute reads at
+// LI/extract_reads_signature.py:107-145, LI/sig_extract.py:514-560 and
+// LI/extract_contig_signature_Hifi.py:386-419 (read.cigar, .pos, .mapq, .flag, .qname,
+// .query_length, .seq, get_tag("SA")).  Pure host code (zlib + std::thread); no CUDA calls.
+//
+// Format notes (SAM/BAM specification v1.6): a BAM file is a series of BGZF blocks (gzip members
+// with a "BC" extra field holding the block size); the inflated stream is "BAM\1", header text,
+// reference list, then records: block_size, refID, pos, l_read_name, mapq, bin, n_cigar_op, flag,
+// l_seq, next_refID, next_pos, tlen, read_name, cigar (u32 = len<<4|op: the layout the kernels
+// use), seq (4 bit), qual, aux.  CIGARs with more than 65535 ops live in a CG:B,I aux array behind
+// a <l_seq>S<ref_len>N placeholder.
+#include <zlib.h>
+
+#include <algorithm>
+#include <atomic>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "../../include/volcanosv_b200.h"
+
+namespace {
+
+struct BamRec {
+  uint64_t off;      // offset of the record body (after block_size) in the inflated stream
+  uint32_t size;     // block_size
+};
+
+struct RefInfo {
+  std::string name;
+  int64_t len;
+  std::vector<uint64_t> recs;  // indices into vsv_bam::recs, file order
+};
+
+inline uint32_t rd32(const uint8_t* p) { uint32_t v; memcpy(&v, p, 4); return v; }
+inline int32_t rd32s(const uint8_t* p) { int32_t v; memcpy(&v, p, 4); return v; }
+inline uint16_t rd16(const uint8_t* p) { uint16_t v; memcpy(&v, p, 2); return v; }
+
+// size of one aux value starting at p (type byte at p[0]); 0 on malformed input
+size_t aux_size(const uint8_t* p, const uint8_t* end) {
+  if (p >= end) return 0;
+  switch (*p) {
+    case 'A': case 'c': case 'C': return 2;
+    case 's': case 'S': return 3;
+    case 'i': case 'I': case 'f': return 5;
+    case 'Z': case 'H': {
+      const uint8_t* q = p + 1;
+      while (q < end && *q) ++q;
+      return q < end ? (size_t)(q - p) + 1 : 0;
+    }
+    case 'B': {
+      if (p + 6 > end) return 0;
+      size_t es = 0;
+      switch (p[1]) {
+        case 'c': case 'C': es = 1; break;
+        case 's': case 'S': es = 2; break;
+        case 'i': case 'I': case 'f': es = 4; break;
+        default: return 0;
+      }
+      return 6 + es * (size_t)rd32(p + 2);
+    }
+    default: return 0;
+  }
+}
+
+struct RecView {
+  const uint8_t* body;
+  int32_t ref_id, pos, l_seq;
+  uint32_t l_name, mapq, n_cigar, flag;
+  const char* name;
+  const uint32_t* cigar;     // may point into the CG tag
+  const uint8_t* seq;
+  const uint8_t* aux;
+  const uint8_t* end;
+};
+
+bool view(const uint8_t* body, uint32_t size, RecView* v) {
+  if (size < 32) return false;
+  v->body = body;
+  v->end = body + size;
+  v->ref_id = rd32s(body);
+  v->pos = rd32s(body + 4);
+  v->l_name = body[8];
+  v->mapq = body[9];
+  v->n_cigar = rd16(body + 12);
+  v->flag = rd16(body + 14);
+  v->l_seq = rd32s(body + 16);
+  if (v->l_seq < 0) return false;
+  const uint8_t* p = body + 32;
+  v->name = reinterpret_cast<const char*>(p);
+  p += v->l_name;
+  v->cigar = reinterpret_cast<const uint32_t*>(p);
+  p += 4 * (size_t)v->n_cigar;
+  v->seq = p;
+  p += ((size_t)v->l_seq + 1) / 2 + (size_t)v->l_seq;
+  if (p > v->end) return false;
+  v->aux = p;
+  // long CIGAR: <l_seq>S<n>N placeholder + CG:B,I
+  if (v->n_cigar == 2) {
+    uint32_t c0, c1;
+    memcpy(&c0, v->cigar, 4);
+    memcpy(&c1, v->cigar + 1, 4);
+    if ((c0 & 15u) == 4u && (int32_t)(c0 >> 4) == v->l_seq && (c1 & 15u) == 3u) {
+      for (const uint8_t* a = v->aux; a + 3 <= v->end;) {
+        const size_t sz = aux_size(a + 2, v->end);
+        if (!sz) break;
+        if (a[0] == 'C' && a[1] == 'G' && a[2] == 'B' && a[3] == 'I') {
+          v->n_cigar = rd32(a + 4);
+          v->cigar = reinterpret_cast<const uint32_t*>(a + 8);
+          break;
+        }
+        a += 2 + sz;
+      }
+    }
+  }
+  return true;
+}
+
+const char* find_sa(const RecView& v, size_t* len) {
+  for (const uint8_t* a = v.aux; a + 3 <= v.end;) {
+    const size_t sz = aux_size(a + 2, v.end);
+    if (!sz) break;
+    if (a[0] == 'S' && a[1] == 'A' && a[2] == 'Z') {
+      *len = sz - 2;  // without type byte and NUL
+      return reinterpret_cast<const char*>(a + 3);
+    }
+    a += 2 + sz;
+  }
+  *len = 0;
+  return nullptr;
+}
+
+template <class F>
+void parallel_for(int64_t n, int n_threads, F f) {
+  n_threads = (int)std::max<int64_t>(1, std::min<int64_t>(n_threads, n));
+  if (n_threads == 1) { f(0, n, 0); return; }
+  std::vector<std::thread> th;
+  const int64_t per = (n + n_threads - 1) / n_threads;
+  for (int t = 0; t < n_threads; ++t) {
+    const int64_t a = t * per, b = std::min(n, a + per);
+    if (a < b) th.emplace_back([=] { f(a, b, t); });
+  }
+  for (auto& x : th) x.join();
+}
+
+}  // namespace
+
+struct vsv_bam {
+  std::vector<uint8_t> data;   // inflated stream
+  std::vector<BamRec> recs;
+  std::vector<RefInfo> refs;
+  std::string header_text;
+  std::string err;
+  int n_threads = 1;
+};
+
+static thread_local std::string g_bam_err;
+
+extern "C" const char* vsv_bam_last_error(void) { return g_bam_err.c_str(); }
+
+#define BAM_FAIL(msg)            \
+  do {                           \
+    g_bam_err = (msg);           \
+    delete b;                    \
+    return VSV_E_ARG;            \
+  } while (0)
+
+extern "C" int vsv_bam_open(const char* path, int n_threads, vsv_bam** out) {
+  if (!path || !out) { g_bam_err = "vsv_bam_open: null argument"; return VSV_E_ARG; }
+  *out = nullptr;
+  vsv_bam* b = new vsv_bam();
+  b->n_threads = n_threads > 0 ? n_threads : (int)std::max(1u, std::thread::hardware_concurrency());
+  FILE* f = fopen(path, "rb");
+  if (!f) BAM_FAIL(std::string("vsv_bam_open: cannot open ") + path);
+  std::vector<uint8_t> raw;
+  {
+    fseek(f, 0, SEEK_END);
+    const long sz = ftell(f);
+    fseek(f, 0, SEEK_SET);
+    raw.resize(sz > 0 ? (size_t)sz : 0);
+    if (sz > 0 && fread(raw.data(), 1, (size_t)sz, f) != (size_t)sz) { fclose(f); BAM_FAIL("vsv_bam_open: short read"); }
+    fclose(f);
+  }
+  // ---- index the BGZF blocks ------------------------------------------------------------
+  struct Blk { size_t in_off, in_len, out_off; uint32_t out_len; };
+  std::vector<Blk> blks;
+  size_t p = 0, total = 0;
+  while (p + 18 <= raw.size()) {
+    const uint8_t* h = raw.data() + p;
+    if (h[0] != 31 || h[1] != 139 || h[2] != 8 || !(h[3] & 4)) BAM_FAIL("vsv_bam_open: not a BGZF file");
+    const uint16_t xlen = rd16(h + 10);
+    int bsize = -1;
+    for (size_t x = 12; x + 4 <= 12 + (size_t)xlen && p + x + 4 <= raw.size();) {
+      const uint16_t slen = rd16(h + x + 2);
+      if (h[x] == 'B' && h[x + 1] == 'C' && slen == 2) bsize = rd16(h + x + 4);
+      x += 4 + slen;
+    }
+    if (bsize < 0 || p + (size_t)bsize + 1 > raw.size()) BAM_FAIL("vsv_bam_open: truncated BGZF block");
+    const size_t blen = (size_t)bsize + 1;
+    const uint32_t isize = rd32(h + blen - 4);
+    blks.push_back({p + 12 + xlen, blen - 12 - xlen - 8, total, isize});
+    total += isize;
+    p += blen;
+  }
+  if (p != raw.size()) BAM_FAIL("vsv_bam_open: trailing bytes after the last BGZF block");
+  b->data.resize(total);
+  std::atomic<int> bad(0);
+  parallel_for((int64_t)blks.size(), b->n_threads, [&](int64_t a, int64_t e, int) {
+    z_stream zs;
+    for (int64_t i = a; i < e; ++i) {
+      if (blks[i].out_len == 0) continue;
+      memset(&zs, 0, sizeof(zs));
+      if (inflateInit2(&zs, -15) != Z_OK) { bad = 1; return; }
+      zs.next_in = raw.data() + blks[i].in_off;
+      zs.avail_in = (uInt)blks[i].in_len;
+      zs.next_out = b->data.data() + blks[i].out_off;
+      zs.avail_out = blks[i].out_len;
+      const int rc = inflate(&zs, Z_FINISH);
+      inflateEnd(&zs);
+      if (rc != Z_STREAM_END || zs.avail_out != 0) { bad = 1; return; }
+    }
+  });
+  if (bad) BAM_FAIL("vsv_bam_open: inflate failed (corrupt BGZF block)");
+  raw.clear();
+  raw.shrink_to_fit();
+  // ---- BAM header -------------------------------------------------------------------------
+  const uint8_t* d = b->data.data();
+  const size_t n = b->data.size();
+  if (n < 12 || memcmp(d, "BAM\1", 4) != 0) BAM_FAIL("vsv_bam_open: not a BAM stream (CRAM/SAM are not read here)");
+  size_t q = 4;
+  const uint32_t l_text = rd32(d + q);
+  q += 4;
+  if (q + l_text + 4 > n) BAM_FAIL("vsv_bam_open: truncated header");
+  b->header_text.assign(reinterpret_cast<const char*>(d + q), l_text);
+  q += l_text;
+  const uint32_t n_ref = rd32(d + q);
+  q += 4;
+  b->refs.resize(n_ref);
+  for (uint32_t i = 0; i < n_ref; ++i) {
+    if (q + 4 > n) BAM_FAIL("vsv_bam_open: truncated reference list");
+    const uint32_t l_name = rd32(d + q);
+    q += 4;
+    if (q + l_name + 4 > n || l_name == 0) BAM_FAIL("vsv_bam_open: truncated reference list");
+    b->refs[i].name.assign(reinterpret_cast<const char*>(d + q), l_name - 1);
+    q += l_name;
+    b->refs[i].len = rd32(d + q);
+    q += 4;
+  }
+  // ---- record index --------------------------------------------------------------------------
+  while (q + 4 <= n) {
+    const uint32_t bs = rd32(d + q);
+    if (bs < 32 || q + 4 + (size_t)bs > n) BAM_FAIL("vsv_bam_open: truncated record");
+    const int32_t rid = rd32s(d + q + 4);
+    if (rid >= 0 && (uint32_t)rid < n_ref) b->refs[rid].recs.push_back(b->recs.size());
+    b->recs.push_back({q + 4, bs});
+    q += 4 + (size_t)bs;
+  }
+  *out = b;
+  return VSV_OK;
+}
+
+extern "C" void vsv_bam_close(vsv_bam* b) { delete b; }
+
+extern "C" int vsv_bam_n_ref(const vsv_bam* b) { return b ? (int)b->refs.size() : 0; }
+
+extern "C" int vsv_bam_ref(const vsv_bam* b, int i, const char** name, int64_t* len, int64_t* n_rec) {
+  if (!b || i < 0 || i >= (int)b->refs.size()) { g_bam_err = "vsv_bam_ref: bad index"; return VSV_E_ARG; }
+  if (name) *name = b->refs[i].name.c_str();
+  if (len) *len = b->refs[i].len;
+  if (n_rec) *n_rec = (int64_t)b->refs[i].recs.size();
+  return VSV_OK;
+}
+
+// sizes[0..4] = n_rec, n_ops, name bytes, SEQ bytes, SA bytes of the records mapped to reference `tid`
+extern "C" int vsv_bam_chrom_sizes(vsv_bam* b, int tid, int64_t* sizes) {
+  if (!b || !sizes || tid < 0 || tid >= (int)b->refs.size()) { g_bam_err = "vsv_bam_chrom_sizes: bad argument"; return VSV_E_ARG; }
+  const std::vector<uint64_t>& rr = b->refs[tid].recs;
+  const int T = b->n_threads;
+  std::vector<int64_t> part(5 * (size_t)std::max(1, T), 0);
+  std::atomic<int> bad(0);
+  parallel_for((int64_t)rr.size(), T, [&](int64_t a, int64_t e, int t) {
+    int64_t* s = part.data() + 5 * t;
+    for (int64_t i = a; i < e; ++i) {
+      RecView v;
+      const BamRec& r = b->recs[rr[i]];
+      if (!view(b->data.data() + r.off, r.size, &v)) { bad = 1; return; }
+      size_t sl;
+      find_sa(v, &sl);
+      s[1] += v.n_cigar;
+      s[2] += v.l_name ? v.l_name - 1 : 0;
+      s[3] += v.l_seq;
+      s[4] += (int64_t)sl;
+    }
+  });
+  if (bad) { g_bam_err = "vsv_bam_chrom_sizes: malformed record"; return VSV_E_ARG; }
+  for (int k = 0; k < 5; ++k) sizes[k] = 0;
+  sizes[0] = (int64_t)rr.size();
+  for (int t = 0; t < std::max(1, T); ++t)
+    for (int k = 1; k < 5; ++k) sizes[k] += part[5 * t + k];
+  return VSV_OK;
+}
+
+// Fills the packed arrays of one chromosome (file order = coordinate order of a sorted BAM).
+// Any output pointer may be NULL to skip that column; `ops` (u32) and `ops16` (+ exception list)
+// are alternative encodings of the same CIGAR ops and may both be requested.
+extern "C" int vsv_bam_chrom_fill(vsv_bam* b, int tid, int32_t* pos, uint8_t* mapq, uint16_t* flag, int32_t* qlen,
+                                  int64_t* op_off, uint32_t* ops, uint16_t* ops16, int64_t* exc_idx, uint32_t* exc_val,
+                                  int64_t exc_cap, int64_t* n_exc, int64_t* name_off, char* names, int64_t* seq_off,
+                                  char* seq, int64_t* sa_off, char* sa) {
+  if (!b || tid < 0 || tid >= (int)b->refs.size()) { g_bam_err = "vsv_bam_chrom_fill: bad argument"; return VSV_E_ARG; }
+  if (ops16 && (!exc_idx || !exc_val || !n_exc)) { g_bam_err = "vsv_bam_chrom_fill: ops16 needs the exception list"; return VSV_E_ARG; }
+  const std::vector<uint64_t>& rr = b->refs[tid].recs;
+  const int64_t n = (int64_t)rr.size();
+  // pass 1 (serial, pointer hops only): offsets of the variable-length columns
+  std::vector<int64_t> o_ops((size_t)n + 1), o_name((size_t)n + 1), o_seq((size_t)n + 1), o_sa((size_t)n + 1);
+  {
+    std::atomic<int> bad(0);
+    parallel_for(n, b->n_threads, [&](int64_t a, int64_t e, int) {
+      for (int64_t i = a; i < e; ++i) {
+        RecView v;
+        const BamRec& r = b->recs[rr[i]];
+        if (!view(b->data.data() + r.off, r.size, &v)) { bad = 1; return; }
+        size_t sl;
+        find_sa(v, &sl);
+        o_ops[i + 1] = v.n_cigar;
+        o_name[i + 1] = v.l_name ? v.l_name - 1 : 0;
+        o_seq[i + 1] = v.l_seq;
+        o_sa[i + 1] = (int64_t)sl;
+      }
+    });
+    if (bad) { g_bam_err = "vsv_bam_chrom_fill: malformed record"; return VSV_E_ARG; }
+    o_ops[0] = o_name[0] = o_seq[0] = o_sa[0] = 0;
+    for (int64_t i = 0; i < n; ++i) {
+      o_ops[i + 1] += o_ops[i]; o_name[i + 1] += o_name[i]; o_seq[i + 1] += o_seq[i]; o_sa[i + 1] += o_sa[i];
+    }
+  }
+  if (op_off) memcpy(op_off, o_ops.data(), sizeof(int64_t) * ((size_t)n + 1));
+  if (name_off) memcpy(name_off, o_name.data(), sizeof(int64_t) * ((size_t)n + 1));
+  if (seq_off) memcpy(seq_off, o_seq.data(), sizeof(int64_t) * ((size_t)n + 1));
+  if (sa_off) memcpy(sa_off, o_sa.data(), sizeof(int64_t) * ((size_t)n + 1));
+  std::atomic<long long> exc_n(0);
+  static const char NT16[] = "=ACMGRSVTWYHKDBN";
+  parallel_for(n, b->n_threads, [&](int64_t a, int64_t e, int) {
+    for (int64_t i = a; i < e; ++i) {
+      RecView v;
+      const BamRec& r = b->recs[rr[i]];
+      view(b->data.data() + r.off, r.size, &v);
+      if (pos) pos[i] = v.pos;
+      if (mapq) mapq[i] = (uint8_t)v.mapq;
+      if (flag) flag[i] = (uint16_t)v.flag;
+      if (qlen) qlen[i] = v.l_seq;
+      const int64_t o = o_ops[i];
+      if (ops) memcpy(ops + o, v.cigar, 4 * (size_t)v.n_cigar);
+      if (ops16) {
+        for (uint32_t k = 0; k < v.n_cigar; ++k) {
+          uint32_t w;
+          memcpy(&w, v.cigar + k, 4);
+          if (w < 0xFFF0u) {
+            ops16[o + k] = (uint16_t)w;
+          } else {  // len >= 4095: marker 0xFFF<<4|op + (index, full word) in the exception list (vsv_expand_ops16)
+            ops16[o + k] = (uint16_t)(0xFFF0u | (w & 15u));
+            const long long s = exc_n.fetch_add(1);
+            if (s < exc_cap) { exc_idx[s] = o + k; exc_val[s] = w; }
+          }
+        }
+      }
+      if (names) memcpy(names + o_name[i], v.name, (size_t)(o_name[i + 1] - o_name[i]));
+      if (seq) {
+        char* dst = seq + o_seq[i];
+        for (int32_t k = 0; k < v.l_seq; ++k) dst[k] = NT16[(v.seq[k >> 1] >> ((~k & 1) << 2)) & 15];
+      }
+      if (sa) {
+        size_t sl;
+        const char* s = find_sa(v, &sl);
+        if (sl) memcpy(sa + o_sa[i], s, sl);
+      }
+    }
+  });
+  if (n_exc) *n_exc = exc_n.load();
+  if (ops16 && exc_n.load() > exc_cap) {
+    g_bam_err = "vsv_bam_chrom_fill: exception list too small";
+    return VSV_E_CAPACITY;
+  }
+  if (ops16 && exc_n.load() > 1) {  // threads appended out of order: vsv_expand_ops16 wants ascending indices
+    const long long m = exc_n.load();
+    std::vector<std::pair<int64_t, uint32_t>> tmp((size_t)m);
+    for (long long k = 0; k < m; ++k) tmp[k] = {exc_idx[k], exc_val[k]};
+    std::sort(tmp.begin(), tmp.end());
+    for (long long k = 0; k < m; ++k) { exc_idx[k] = tmp[k].first; exc_val[k] = tmp[k].second; }
+  }
+  return VSV_OK;
+}
+
+// SEQ of record i (file order) of reference `tid`, decoded to ASCII: the sparse accesses of
+// `read.seq` / `read.query_sequence` (SE:452, ECS_H:642-700) without materialising every read's bases.
+extern "C" int vsv_bam_record_seq(vsv_bam* b, int tid, int64_t i, char* out, int64_t cap, int64_t* len) {
+  if (!b || !len || tid < 0 || tid >= (int)b->refs.size() || i < 0 || i >= (int64_t)b->refs[tid].recs.size()) {
+    g_bam_err = "vsv_bam_record_seq: bad argument";
+    return VSV_E_ARG;
+  }
+  RecView v;
+  const BamRec& r = b->recs[b->refs[tid].recs[i]];
+  if (!view(b->data.data() + r.off, r.size, &v)) { g_bam_err = "vsv_bam_record_seq: malformed record"; return VSV_E_ARG; }
+  *len = v.l_seq;
+  if (!out || cap < v.l_seq) return v.l_seq ? VSV_E_CAPACITY : VSV_OK;
+  static const char NT16[] = "=ACMGRSVTWYHKDBN";
+  for (int32_t k = 0; k < v.l_seq; ++k) out[k] = NT16[(v.seq[k >> 1] >> ((~k & 1) << 2)) & 15];
+  return VSV_OK;
+}

@@ -70,9 +70,19 @@ SIGNATURES = {
     "vsv_sig_support": [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _i64, _i32, _vp, _vp, C.POINTER(_i32)],
     "vsv_span_depth": [_vp, _vp, _vp, _i64, _vp, _vp, _i64, _vp],
     "vsv_edit_distance_batch": [_vp, _vp, _vp, _i64, _vp, _vp, _i64, _vp],
+    "vsv_bam_open": [C.c_char_p, _int, C.POINTER(_vp)],
+    "vsv_bam_close": [_vp],
+    "vsv_bam_last_error": [],
+    "vsv_bam_n_ref": [_vp],
+    "vsv_bam_ref": [_vp, _int, C.POINTER(C.c_char_p), C.POINTER(_i64), C.POINTER(_i64)],
+    "vsv_bam_chrom_sizes": [_vp, _int, _vp],
+    "vsv_bam_record_seq": [_vp, _int, _i64, _vp, _i64, C.POINTER(_i64)],
+    "vsv_bam_chrom_fill": [_vp, _int, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, C.POINTER(_i64), _vp, _vp, _vp, _vp,
+                           _vp, _vp],
     "vsv_genotype": [_vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp],
 }
-_RESTYPE = {"vsv_ctx_destroy": None, "vsv_last_error": C.c_char_p, "vsv_version": C.c_char_p}
+_RESTYPE = {"vsv_ctx_destroy": None, "vsv_last_error": C.c_char_p, "vsv_version": C.c_char_p, "vsv_bam_close": None,
+            "vsv_bam_last_error": C.c_char_p}
 
 
 def load_library(path: Optional[str] = None):
@@ -350,6 +360,79 @@ class Context:
         out = np.zeros(len(ia), np.int32)
         self._chk(self.lib.vsv_edit_distance_batch(self.h, _p(chars), _p(off), len(bs), _p(ia), _p(ib), len(ia), _p(out)))
         return out
+
+
+class BamFile:
+    """Native BAM reader (include/volcanosv_b200.h: vsv_bam_*): the host-side replacement of
+    `pysam.AlignmentFile(path).fetch(chr)` for whole-chromosome scans.  Host code only (no GPU)."""
+
+    def __init__(self, path: str, n_threads: int = 0):
+        self.lib = load_library()
+        self.h = _vp()
+        rc = self.lib.vsv_bam_open(os.fsencode(path), n_threads, C.byref(self.h))
+        if rc != 0:
+            raise VsvError(rc, (self.lib.vsv_bam_last_error() or b"").decode())
+        self.refs = []
+        for i in range(self.lib.vsv_bam_n_ref(self.h)):
+            name, ln, n = C.c_char_p(), _i64(), _i64()
+            self.lib.vsv_bam_ref(self.h, i, C.byref(name), C.byref(ln), C.byref(n))
+            self.refs.append((name.value.decode(), int(ln.value), int(n.value)))
+
+    def close(self):
+        if self.h:
+            self.lib.vsv_bam_close(self.h)
+            self.h = _vp()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:  # noqa: BLE001
+            pass
+
+    def _chk(self, rc):
+        if rc != 0:
+            raise VsvError(rc, (self.lib.vsv_bam_last_error() or b"").decode())
+
+    def chrom(self, name_or_tid, compact: bool = False, want_seq: bool = True):
+        """Columns of one reference: dict(pos, mapq, flag, qlen, op_off, ops | ops16+exc_idx+exc_val,
+        name_off, names, seq_off, seq, sa_off, sa)."""
+        tid = name_or_tid if isinstance(name_or_tid, int) else [r[0] for r in self.refs].index(name_or_tid)
+        sizes = np.zeros(5, np.int64)
+        self._chk(self.lib.vsv_bam_chrom_sizes(self.h, tid, _p(sizes)))
+        n, n_ops, nb, sb, ab = (int(x) for x in sizes)
+        d = dict(pos=np.empty(n, np.int32), mapq=np.empty(n, np.uint8), flag=np.empty(n, np.uint16), qlen=np.empty(n, np.int32),
+                 op_off=np.empty(n + 1, np.int64), name_off=np.empty(n + 1, np.int64), names=np.empty(nb, np.uint8),
+                 seq_off=np.empty(n + 1, np.int64), seq=np.empty(sb if want_seq else 0, np.uint8),
+                 sa_off=np.empty(n + 1, np.int64), sa=np.empty(ab, np.uint8))
+        n_exc = _i64(0)
+        if compact:
+            d["ops16"] = _aligned_empty(n_ops, np.uint16)
+            cap = max(1024, n_ops // 256)
+            while True:
+                d["exc_idx"], d["exc_val"] = np.empty(cap, np.int64), np.empty(cap, np.uint32)
+                rc = self._fill(tid, d, None, d["ops16"], cap, n_exc, want_seq)
+                if rc != E_CAPACITY:
+                    break
+                cap = int(n_exc.value)
+            self._chk(rc)
+            d["exc_idx"], d["exc_val"] = d["exc_idx"][: n_exc.value].copy(), d["exc_val"][: n_exc.value].copy()
+        else:
+            d["ops"] = _aligned_empty(n_ops, np.uint32)
+            self._chk(self._fill(tid, d, d["ops"], None, 0, n_exc, want_seq))
+        return d
+
+    def record_seq(self, tid: int, i: int, length: int) -> str:
+        """SEQ of record i of reference tid (length = its qlen)."""
+        buf = C.create_string_buffer(max(int(length), 1))
+        n = _i64()
+        self._chk(self.lib.vsv_bam_record_seq(self.h, tid, int(i), buf, int(length), C.byref(n)))
+        return buf.raw[: n.value].decode()
+
+    def _fill(self, tid, d, ops, ops16, cap, n_exc, want_seq):
+        return self.lib.vsv_bam_chrom_fill(self.h, tid, _p(d["pos"]), _p(d["mapq"]), _p(d["flag"]), _p(d["qlen"]), _p(d["op_off"]),
+                                           _p(ops), _p(ops16), _p(d.get("exc_idx")), _p(d.get("exc_val")), cap, C.byref(n_exc),
+                                           _p(d["name_off"]), _p(d["names"]), _p(d["seq_off"]),
+                                           _p(d["seq"]) if want_seq else None, _p(d["sa_off"]), _p(d["sa"]))
 
 
 def pack_ops16(ops):

@@ -101,10 +101,24 @@ class Records:
         return self
 
 
+class _LazySeq:
+    """`R.seq[i]` for BAM input: decoded from the record on demand (None for SEQ '*')."""
+
+    def __init__(self, bam, tid, qlen):
+        self.bam, self.tid, self.qlen = bam, tid, qlen
+
+    def __len__(self):
+        return len(self.qlen)
+
+    def __getitem__(self, i):
+        n = int(self.qlen[i])
+        return self.bam.record_seq(self.tid, int(i), n) if n else None
+
+
 class AlignmentSource:
     """`pysam.AlignmentFile`-like view used by the operators: references() and records(chrom).
-    BAM/CRAM go through pysam (htslib stays the decoder, as in the reference); SAM text
-    (plain or .gz) is parsed here so the operators also run where pysam is absent."""
+    BAM goes through the library's own feeder (vsv_bam_*: BGZF inflate + record -> packed columns),
+    SAM text (plain or .gz) is parsed here, anything else (CRAM) through pysam if it is installed."""
 
     def __init__(self, path: str):
         self.path = path
@@ -112,6 +126,8 @@ class AlignmentSource:
         self._by_chrom: Dict[str, Records] = {}
         if path.endswith((".sam", ".sam.gz")):
             self._load_sam(path)
+        elif path.endswith(".bam"):
+            self._load_bam(path)
         else:
             self._load_pysam(path)
 
@@ -137,11 +153,37 @@ class AlignmentSource:
                                                      None if f[9] == "*" else f[9], sa)
         self._by_chrom = {c: r.finish() for c, r in recs.items()}
 
+    def _load_bam(self, path):
+        """BAM through the native feeder (include/volcanosv_b200.h: vsv_bam_*): numeric columns
+        arrive packed; names / SA tags become Python strings, SEQ is decoded per record on demand."""
+        bf = L.BamFile(path)
+        self._bam = bf
+        self._refs = [(n, ln) for n, ln, _ in bf.refs]
+        for tid, (chrom, _, n_rec) in enumerate(bf.refs):
+            if n_rec == 0:
+                continue
+            d = bf.chrom(tid, want_seq=False)
+            R = Records()
+            R.n = n_rec
+            R.ops, R.op_off, R.pos, R.mapq = d["ops"], d["op_off"], d["pos"], d["mapq"]
+            R.flag = d["flag"].astype(np.int32)
+            R.qlen = d["qlen"]
+            R.is_rev = ((R.flag & 16) != 0).astype(np.uint8)
+            has = d["op_off"][1:] > d["op_off"][:-1]
+            R.first_op = np.where(has, R.ops[np.minimum(d["op_off"][:-1], max(len(R.ops) - 1, 0))] if len(R.ops) else 0, 0).astype(np.uint32)
+            R.last_op = np.where(has, R.ops[np.maximum(d["op_off"][1:] - 1, 0)] if len(R.ops) else 0, 0).astype(np.uint32)
+            names, no = bytes(d["names"]), d["name_off"]
+            R.qname = [names[no[i]: no[i + 1]].decode() for i in range(n_rec)]
+            sa, so = bytes(d["sa"]), d["sa_off"]
+            R.sa = [sa[so[i]: so[i + 1]].decode() if so[i + 1] > so[i] else None for i in range(n_rec)]
+            R.seq = _LazySeq(bf, tid, R.qlen)
+            self._by_chrom[chrom] = R
+
     def _load_pysam(self, path):
         try:
             import pysam
         except ImportError as e:  # pragma: no cover - this image has no pysam
-            raise RuntimeError("BAM input needs pysam (htslib); SAM text (.sam/.sam.gz) is read natively") from e
+            raise RuntimeError("CRAM input needs pysam (htslib); BAM and SAM text (.sam/.sam.gz) are read natively") from e
         af = pysam.AlignmentFile(path)
         self._refs = list(zip(af.references, af.lengths))
         recs: Dict[str, Records] = {}
