@@ -292,11 +292,13 @@ __global__ void __launch_bounds__(SCAN_THREADS, SCAN_CTAS_PER_SM) k_scan_wt(cons
   uint32_t(*s_ops)[SCAN_STAGES][WT_OPS] = reinterpret_cast<uint32_t(*)[SCAN_STAGES][WT_OPS]>(s_dyn);
   uint64_t(*s_bar)[SCAN_STAGES] =
       reinterpret_cast<uint64_t(*)[SCAN_STAGES]>(s_dyn + (size_t)SCAN_WARPS * SCAN_STAGES * WT_OPS * sizeof(uint32_t));
+  uint32_t(*s_tab)[8] = reinterpret_cast<uint32_t(*)[8]>(s_dyn + (size_t)SCAN_WARPS * SCAN_STAGES * (WT_OPS * sizeof(uint32_t) + sizeof(uint64_t)));
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int64_t TW = (int64_t)gridDim.x * SCAN_WARPS;
-  const int64_t gw = (int64_t)blockIdx.x * SCAN_WARPS + warp;
-  const int64_t n_wt = p.n_wt;
-  const int64_t n_full = p.n_ops / WT_OPS;  // tiles below n_full are complete
+  // tile indices are 32-bit (n_wt < 2^31 - 1, checked by the host; wt + 2 * TW cannot wrap in u32)
+  const uint32_t TW = gridDim.x * SCAN_WARPS;
+  const uint32_t gw = blockIdx.x * SCAN_WARPS + warp;
+  const uint32_t n_wt = (uint32_t)p.n_wt;
+  const uint32_t n_full = (uint32_t)(p.n_ops / WT_OPS);  // tiles below n_full are complete
 
   if (lane == 0) {
     for (int s = 0; s < SCAN_STAGES; ++s) mbar_init(&s_bar[warp][s], 1);
@@ -306,23 +308,28 @@ __global__ void __launch_bounds__(SCAN_THREADS, SCAN_CTAS_PER_SM) k_scan_wt(cons
   __syncwarp();
   if (lane == 0) {
     for (int s = 0; s < SCAN_STAGES; ++s) {
-      const int64_t t = gw + (int64_t)s * TW;
+      const uint32_t t = gw + (uint32_t)s * TW;
       if (t < n_full) {
         mbar_expect_tx(&s_bar[warp][s], WT_OPS * 4);
-        tma_load_1d(s_ops[warp][s], p.ops + t * WT_OPS, WT_OPS * 4, &s_bar[warp][s]);
+        tma_load_1d(s_ops[warp][s], p.ops + (size_t)t * WT_OPS, WT_OPS * 4, &s_bar[warp][s]);
       }
     }
   }
+  uint32_t tabs[6];
+  if (lane < 6) s_tab[warp][lane] = p.tab[lane];
+  __syncwarp();
+#pragma unroll
+  for (int k = 0; k < 6; ++k) tabs[k] = *reinterpret_cast<volatile uint32_t*>(&s_tab[warp][k]);
   int2 cur = make_int2(0, -1), nxt = make_int2(0, -1);
   if (gw < n_wt) cur = __ldg(p.wt_starts + gw);
   if (gw + TW < n_wt) nxt = __ldg(p.wt_starts + gw + TW);
   unsigned long long ch_next = 0, ch_end = 0;  // this warp's staging chunk (lane 0)
 
   int it = 0;
-  for (int64_t wt = gw; wt < n_wt; wt += TW, ++it) {
+  for (uint32_t wt = gw; wt < n_wt; wt += TW, ++it) {
     const int stage = it % SCAN_STAGES;
     const uint32_t parity = (uint32_t)(it / SCAN_STAGES) & 1u;
-    const int64_t wt_start = wt * WT_OPS;
+    const int64_t wt_start = (int64_t)wt * WT_OPS;
     uint32_t* tl = s_ops[warp][stage];
 
     // record starts inside this tile: issue the offset loads before waiting for the ops
@@ -375,26 +382,22 @@ __global__ void __launch_bounds__(SCAN_THREADS, SCAN_CTAS_PER_SM) k_scan_wt(cons
       lane_rare = (bits & RARE) != 0u;
       lane_cand = mxk >= min_w;
     } else {
-      // the six table words come in through the kernel parameters (filled by the host from
-      // tab_word): as compile-time constants ptxas overwrites and re-materialises them around
-      // every PRMT, which costs an issue slot per look-up
-      uint32_t TR_LO, TR_HI, TQ_LO, TQ_HI, TC_LO, TC_HI;  // pinned in registers (volatile asm: no re-materialisation)
-      asm volatile("mov.u32 %0, %1;" : "=r"(TR_LO) : "r"(p.tab[0]));
-      asm volatile("mov.u32 %0, %1;" : "=r"(TR_HI) : "r"(p.tab[1]));
-      asm volatile("mov.u32 %0, %1;" : "=r"(TQ_LO) : "r"(p.tab[2]));
-      asm volatile("mov.u32 %0, %1;" : "=r"(TQ_HI) : "r"(p.tab[3]));
-      asm volatile("mov.u32 %0, %1;" : "=r"(TC_LO) : "r"(p.tab[4]));
-      asm volatile("mov.u32 %0, %1;" : "=r"(TC_HI) : "r"(p.tab[5]));
+      // the six table words (filled by the host from tab_word) were bounced through shared memory
+      // before the tile loop: as compile-time constants ptxas re-materialises them around every
+      // PRMT, and as kernel parameters it keeps them in UNIFORM registers, which PRMT cannot read
+      // (one IMAD.U32 copy per look-up) - a value loaded from shared memory stays in a plain register
+      const uint32_t TR_LO = tabs[0], TR_HI = tabs[1], TQ_LO = tabs[2], TQ_HI = tabs[3], TC_LO = tabs[4], TC_HI = tabs[5];
       static_assert(((M::REF >> 8) & 1u) == (M::REF & 1u) && ((M::QRY >> 8) & 1u) == (M::QRY & 1u),
                     "code 8 (X) is looked up as the sign of code 0 (M)");
-      const int rot = lane & 7;
-      const uint4* row = reinterpret_cast<const uint4*>(tl + lane * WT_VPT);
+      // 128-byte rows: physical uint4 (k ^ rot) of the row = byte address (row ^ rot*16) ^ k*16
+      const uint32_t row_x = (smem_u32(tl) + (uint32_t)lane * (WT_VPT * 4u)) ^ ((uint32_t)(lane & 7) << 4);
       const uint32_t one = p.one;  // == 1, opaque to the compiler: keeps `sc` on the FMA pipe
       uint32_t nr = 0, nq = 0, mxc = 0, sc = 0;
       int32_t mnk = 0;
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
-        const uint4 v = row[k ^ rot];
+        uint4 v;
+        asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(row_x ^ (uint32_t)(k << 4)));
         const uint32_t ww[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
@@ -534,11 +537,11 @@ __global__ void __launch_bounds__(SCAN_THREADS, SCAN_CTAS_PER_SM) k_scan_wt(cons
     }
     __syncwarp();  // every lane is done with this stage
     if (lane == 0) {
-      const int64_t t2 = wt + (int64_t)SCAN_STAGES * TW;
+      const uint32_t t2 = wt + (uint32_t)SCAN_STAGES * TW;
       if (t2 < n_full) {
         fence_proxy_async();
         mbar_expect_tx(&s_bar[warp][stage], WT_OPS * 4);
-        tma_load_1d(s_ops[warp][stage], p.ops + t2 * WT_OPS, WT_OPS * 4, &s_bar[warp][stage]);
+        tma_load_1d(s_ops[warp][stage], p.ops + (size_t)t2 * WT_OPS, WT_OPS * 4, &s_bar[warp][stage]);
       }
     }
     cur = nxt;
@@ -824,7 +827,7 @@ struct ScanCall {
 
 // CTA shape of the streaming kernel: warps are independent workers (no block-level sync), so the
 // shape only sets how many fit an SM - 8 KB of staging per warp, 64 registers per thread -> 28.
-static constexpr size_t SCAN_SMEM = (size_t)SCAN_WARPS * SCAN_STAGES * (WT_OPS * sizeof(uint32_t) + sizeof(uint64_t));
+static constexpr size_t SCAN_SMEM = (size_t)SCAN_WARPS * (SCAN_STAGES * (WT_OPS * sizeof(uint32_t) + sizeof(uint64_t)) + 8 * sizeof(uint32_t));
 
 template <int MODE>
 static int run_scan_kernels(vsv_ctx* ctx, const ScanParams& p_in, int grid, TileState* d_excl, vsv_sig* out_a, int64_t cap_a,
