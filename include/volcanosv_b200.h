@@ -201,7 +201,8 @@ int vsv_group_sigs(vsv_ctx* ctx, const int32_t* chrom, const int32_t* pos, const
 
 /* match_varlist_siglist (GTD:92-137) / extract_sig_support (GTI:107-166), including
  * the double count at last_match_idx.  last_in/last_out carry last_match_idx across
- * shards (0 for the first).  match_id may be NULL. */
+ * shards (0 for the first).  match_id may be NULL.  last_out may be NULL when both chromosome
+ * arrays are NULL (one chromosome): the call then returns without waiting for the stream. */
 int vsv_sig_support(vsv_ctx* ctx, const int32_t* cand_chrom, const int32_t* cand_pos,
                     const int32_t* cand_svlen, int64_t n_cand, const int32_t* sig_chrom,
                     const int32_t* sig_pos, const int32_t* sig_len, const int32_t* sig_cnt,

@@ -205,25 +205,24 @@ __device__ __forceinline__ int32_t rec_of_op(const int64_t* __restrict__ op_off,
 
 // ---- small pre-kernels ---------------------------------------------------------------
 // per warp tile: the records (indices in 0..n_rec, n_rec = end sentinel) whose START offset
-// lies inside the tile: first = lower_bound(op_off, tile_start), last = upper_bound(op_off,
-// tile_end - 1) - 1; first > last when no record starts here.
-__global__ void k_wt_starts(const int64_t* __restrict__ op_off, int64_t n_rec, int64_t n_ops, int32_t n_wt,
-                            int2* __restrict__ wt_starts) {
+// lies inside the tile: first(t) = lower_bound(op_off, t * WT_OPS), last(t) = first(t + 1) - 1;
+// first > last when no record starts here.  Scatter from the records: record r (op_off[-1] = -1)
+// is first(t) for the tiles t in (op_off[r-1] / WT_OPS, op_off[r] / WT_OPS]; first[n_wt] is
+// n_rec + 1 unless the ops end exactly on a tile edge.
+__global__ void k_wt_first(const int64_t* __restrict__ op_off, int64_t n_rec, int32_t n_wt, int32_t* __restrict__ first) {
+  const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r > n_rec) return;
+  const int64_t cur = __ldg(op_off + r);
+  const int64_t prev = r > 0 ? __ldg(op_off + r - 1) : -1;
+  int64_t t0 = prev < 0 ? 0 : prev / WT_OPS + 1;
+  const int64_t t1 = min(cur / WT_OPS, (int64_t)n_wt);
+  for (; t0 <= t1; ++t0) first[t0] = (int32_t)r;
+  if (r == n_rec && cur % WT_OPS != 0) first[n_wt] = (int32_t)n_rec + 1;  // no offset reaches the edge of the last tile
+}
+__global__ void k_wt_starts(const int32_t* __restrict__ first, int32_t n_wt, int2* __restrict__ wt_starts) {
   const int32_t t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= n_wt) return;
-  const int64_t x0 = (int64_t)t * WT_OPS, x1 = x0 + WT_OPS - 1;
-  int64_t lo = 0, hi = n_rec + 1;  // first index with op_off >= x0
-  while (lo < hi) {
-    const int64_t mid = (lo + hi) >> 1;
-    if (__ldg(op_off + mid) < x0) lo = mid + 1; else hi = mid;
-  }
-  const int32_t first = (int32_t)lo;
-  hi = n_rec + 1;                  // first index with op_off > x1
-  while (lo < hi) {
-    const int64_t mid = (lo + hi) >> 1;
-    if (__ldg(op_off + mid) <= x1) lo = mid + 1; else hi = mid;
-  }
-  wt_starts[t] = make_int2(first, (int32_t)lo - 1);
+  wt_starts[t] = make_int2(first[t], first[t + 1] - 1);
 }
 
 // per record: leading hard clip and the record gates of both streams
@@ -737,7 +736,7 @@ __device__ __forceinline__ void gate_slot(const ScanParams& p, uint64_t i) {
   if (ok_a) atomicAdd(&p.wt_agg[t].cnt_a, 1u);
   if (ok_b) atomicAdd(&p.wt_agg[t].cnt_b, 1u);
   slot[0] = make_uint4((uint32_t)rec, w, part.r, part.q);
-  slot[1] = make_uint4(part.x1, part.x2, part.x3, (ok_a ? 1u : 0u) | (ok_b ? 2u : 0u) | (carry ? 4u : 0u));
+  slot[1] = make_uint4(part.x1, part.x2, part.x3, (t << 3) | (ok_a ? 1u : 0u) | (ok_b ? 2u : 0u) | (carry ? 4u : 0u));
 }
 
 template <int MODE, int STREAM>
@@ -751,36 +750,41 @@ __device__ __forceinline__ void emit_sig(const ScanParams& p, vsv_sig* dst, uint
   o[1] = make_int4(q0, q0 + (type == VSV_INS ? len : 1), 0, 1);
 }
 
-// k_emit: final ordered slots (exclusive scan of the counts) + carry of an open record.
+// k_emit: final ordered slots + carry of an open record.  One thread per staging slot (persistent
+// grid-stride, liveness test as in k_gate with the tile index k_gate left in the flag word).  The
+// output slot of a candidate = exclusive scan of its tile's counts + the gated candidates before
+// it in the tile (a tile holds a handful, in op order).
 template <int MODE>
-__global__ void __launch_bounds__(128) k_emit(const ScanParams p, const TileState* __restrict__ excl,
+__global__ void __launch_bounds__(256) k_emit(const ScanParams p, const TileState* __restrict__ excl,
                                               vsv_sig* __restrict__ out_a, int64_t cap_a, vsv_sig* __restrict__ out_b,
                                               int64_t cap_b, int64_t* __restrict__ n_out) {
-  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t == 0) {  // exclusive scan at the identity sentinel == totals
+  if (blockIdx.x == 0 && threadIdx.x == 0) {  // exclusive scan at the identity sentinel == totals
     n_out[0] = excl[p.n_wt].cnt_a;
     n_out[1] = excl[p.n_wt].cnt_b;
   }
-  if (t >= p.n_wt) return;
-  const uint2 st = p.wt_stage[t];
-  if (st.y == 0u || st.x == 0xFFFFFFFFu) return;
-  const TileState E = excl[t];
-  int64_t ia = E.cnt_a, ib = E.cnt_b;
-  const StageEntry* e = p.stage + st.x;
-  for (uint32_t i = 0; i < st.y; ++i) {
-    const uint4 e1 = reinterpret_cast<const uint4*>(e + i)[1];
+  unsigned long long n_res = *reinterpret_cast<const volatile unsigned long long*>(p.stage_ctr);
+  if (n_res > p.stage_cap) n_res = p.stage_cap;
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_res; i += stride) {
+    const uint4* slot = reinterpret_cast<const uint4*>(p.stage + i);
+    const uint4 e1 = slot[1];
     if ((e1.w & 3u) == 0u) continue;
-    const uint4 e0 = reinterpret_cast<const uint4*>(e + i)[0];
+    const uint32_t t = e1.w >> 3;
+    if (t >= (uint32_t)p.n_wt) continue;
+    const uint2 st = __ldg(p.wt_stage + t);
+    if (st.x == 0xFFFFFFFFu || i < st.x || i >= (uint64_t)st.x + st.y) continue;
+    const uint4 e0 = slot[0];
+    const TileState E = ts_load(excl + t);
+    int64_t ia = E.cnt_a, ib = E.cnt_b;
+    for (uint64_t k = st.x; k < i; ++k) {
+      const uint32_t f = reinterpret_cast<const uint4*>(p.stage + k)[1].w;
+      ia += f & 1u;
+      ib += (f >> 1) & 1u;
+    }
     Sums s = {e0.z, e0.w, e1.x, e1.y, e1.z};
     if (e1.w & 4u) { s.r += E.r; s.q += E.q; s.x1 += E.x1; s.x2 += E.x2; s.x3 += E.x3; }
-    if (e1.w & 1u) {
-      if (ia < cap_a) emit_sig<MODE, 0>(p, out_a + ia, e0.x, e0.y, s);
-      ++ia;
-    }
-    if (MODE == VSV_MODE_FUSED && (e1.w & 2u)) {
-      if (ib < cap_b) emit_sig<MODE, 1>(p, out_b + ib, e0.x, e0.y, s);
-      ++ib;
-    }
+    if ((e1.w & 1u) && ia < cap_a) emit_sig<MODE, 0>(p, out_a + ia, e0.x, e0.y, s);
+    if (MODE == VSV_MODE_FUSED && (e1.w & 2u) && ib < cap_b) emit_sig<MODE, 1>(p, out_b + ib, e0.x, e0.y, s);
   }
 }
 
@@ -843,7 +847,6 @@ static int run_scan_kernels(vsv_ctx* ctx, const ScanParams& p_in, int grid, Tile
   VSV_LAUNCH(ctx, k_scan_wt<MODE>, (unsigned)grid, SCAN_THREADS, SCAN_SMEM, p);
   VSV_CUDA(ctx, cudaEventRecord(ctx->evk1, ctx->stream));
   ctx->main_open = true;
-  const unsigned gt = (unsigned)vsv_cdiv(p.n_wt, 128);
   VSV_LAUNCH(ctx, k_gate<MODE>, (unsigned)std::min<int64_t>(vsv_cdiv((int64_t)p.stage_cap, 256), (int64_t)ctx->sm_count * 8), 256, 0, p);
   {  // segmented exclusive scan of the tile aggregates (n_wt + 1 elements, last = identity)
     const int64_t n_el = (int64_t)p.n_wt + 1, nb = vsv_cdiv(n_el, TS_BLOCK);
@@ -853,7 +856,8 @@ static int run_scan_kernels(vsv_ctx* ctx, const ScanParams& p_in, int grid, Tile
     VSV_LAUNCH(ctx, k_ts_spine, 1, 1024, 0, d_blk, nb);
     VSV_LAUNCH(ctx, k_ts_scan, (unsigned)nb, TS_THREADS, 0, (const TileState*)p.wt_agg, n_el, (const TileState*)d_blk, d_excl);
   }
-  VSV_LAUNCH(ctx, k_emit<MODE>, gt, 128, 0, p, d_excl, out_a, cap_a, out_b, cap_b, d_nout);
+  VSV_LAUNCH(ctx, k_emit<MODE>, (unsigned)std::min<int64_t>(vsv_cdiv((int64_t)p.stage_cap, 256), (int64_t)ctx->sm_count * 8), 256, 0,
+             p, d_excl, out_a, cap_a, out_b, cap_b, d_nout);
   if (rt) VSV_LAUNCH(ctx, k_rec_totals<MODE>, (unsigned)vsv_cdiv(p.n_rec, 256), 256, 0, p, d_excl, rt, qt, xt);
   return VSV_OK;
 }
@@ -886,7 +890,7 @@ static int scan_impl(vsv_ctx* ctx, const ScanCall& c) {
   }
   if (n_ops < 0) VSV_FAIL(ctx, VSV_E_ARG, std::string(fn) + ": negative op count");
   const int64_t n_wt64 = vsv_cdiv(n_ops, WT_OPS);
-  if (n_wt64 >= (int64_t(1) << 31) - 1) VSV_FAIL(ctx, VSV_E_ARG, std::string(fn) + ": too many ops per call");
+  if (n_wt64 >= (int64_t(1) << 29)) VSV_FAIL(ctx, VSV_E_ARG, std::string(fn) + ": too many ops per call");  // tile index shares a word with 3 flag bits
   const int32_t n_wt = (int32_t)n_wt64;
 
   ScanParams p;
@@ -945,7 +949,10 @@ static int scan_impl(vsv_ctx* ctx, const ScanCall& c) {
   if (n_wt > 0) {
     VSV_LAUNCH(ctx, k_rec_info, (unsigned)vsv_cdiv(c.n_rec, 256), 256, 0, p.ops, p.op_off, d_mapq, d_ena, d_enb, c.n_rec,
                c.min_mapq_a, c.min_mapq_b, d_info);
-    VSV_LAUNCH(ctx, k_wt_starts, (unsigned)vsv_cdiv(n_wt, 256), 256, 0, p.op_off, c.n_rec, n_ops, n_wt, d_starts);
+    int32_t* d_first = nullptr;
+    VSV_TRY(vsv_tmp(ctx, (size_t)n_wt + 1, &d_first));
+    VSV_LAUNCH(ctx, k_wt_first, (unsigned)vsv_cdiv(c.n_rec + 1, 256), 256, 0, p.op_off, c.n_rec, n_wt, d_first);
+    VSV_LAUNCH(ctx, k_wt_starts, (unsigned)vsv_cdiv(n_wt, 256), 256, 0, (const int32_t*)d_first, n_wt, d_starts);
     VSV_CUDA(ctx, cudaMemsetAsync(d_agg + n_wt, 0, sizeof(TileState), ctx->stream));  // identity sentinel
   }
   for (int attempt = 0; attempt < 3; ++attempt) {

@@ -147,9 +147,11 @@ extern "C" int vsv_sig_support(vsv_ctx* ctx, const int32_t* cand_chrom, const in
                                int64_t n_sig, int32_t last_in, int32_t* support, int32_t* match_id,
                                int32_t* last_out) {
   VSV_TRY(vsv_begin(ctx));
-  if (n_cand < 0 || n_sig < 0 || n_sig >= (int64_t(1) << 31) || !last_out)
+  // last_out may be NULL for a single-chromosome call (no chromosome arrays): nothing has to come
+  // back to the host then, so the call stays asynchronous (no stream synchronisation)
+  if (n_cand < 0 || n_sig < 0 || n_sig >= (int64_t(1) << 31) || (!last_out && (cand_chrom || sig_chrom)))
     VSV_FAIL(ctx, VSV_E_ARG, "vsv_sig_support: bad argument");
-  *last_out = last_in;
+  if (last_out) *last_out = last_in;
   if (n_cand == 0) return VSV_OK;
   const int32_t *cc, *cp, *cl, *sc, *sp, *sl, *sn;
   VSV_TRY(vsv_in(ctx, cand_chrom, (size_t)n_cand, &cc));
@@ -185,12 +187,14 @@ extern "C" int vsv_sig_support(vsv_ctx* ctx, const int32_t* cand_chrom, const in
   VSV_LAUNCH(ctx, k_support_fixup, (unsigned)vsv_cdiv(n_cand, 256), 256, 0, cc, cl, n_cand, sc, sl, sn, n_sig, lb, ub,
              lscan, last_in, 0.6, d_sup, d_mid, d_last);
   VSV_TRY(vsv_t1(ctx));
-  int32_t h[2] = {0, 0};
-  VSV_CUDA(ctx, cudaMemcpyAsync(h, bad, 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
-  VSV_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-  if (h[0] == 1) VSV_FAIL(ctx, VSV_E_ARG, "vsv_sig_support: chromosome id out of range [0,4096)");
-  if (h[0] == 2) VSV_FAIL(ctx, VSV_E_ARG, "vsv_sig_support: signature table is not grouped by chromosome");
-  *last_out = h[1];
+  if (last_out) {
+    int32_t h[2] = {0, 0};
+    VSV_CUDA(ctx, cudaMemcpyAsync(h, bad, 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    VSV_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (h[0] == 1) VSV_FAIL(ctx, VSV_E_ARG, "vsv_sig_support: chromosome id out of range [0,4096)");
+    if (h[0] == 2) VSV_FAIL(ctx, VSV_E_ARG, "vsv_sig_support: signature table is not grouped by chromosome");
+    *last_out = h[1];
+  }
   VSV_TRY(vsv_out_done(ctx, support, d_sup, (size_t)n_cand));
   VSV_TRY(vsv_out_done(ctx, match_id, d_mid, (size_t)n_cand));
   return vsv_end(ctx);

@@ -212,13 +212,12 @@ class ChromShard:
         p_, l_, n, *_ = uniq["del"]
         self._chk(lib.vsv_del_cov(h, _dp(cpos), _dp(cend), n_cand, _dp(p_), _dp(l_), n, 1000, _dp(cov_d)))      # CSS:138
         sup_d, sup_i = self._buf("sup_del", n_cand, i32), self._buf("sup_ins", n_cand, i32)
-        last = C.c_int32()
         _, _, _, up, ul, un, nu = uniq["del"]
         self._chk(lib.vsv_sig_support(h, None, _dp(cpos), _dp(clen), n_cand, None, _dp(up), _dp(ul), _dp(un), nu, 0,
-                                      _dp(sup_d), None, C.byref(last)))                                         # GTD:92
+                                      _dp(sup_d), None, None))                                                  # GTD:92
         _, _, _, up, ul, un, nu = uniq["ins"]
         self._chk(lib.vsv_sig_support(h, None, _dp(cpos), _dp(clen), n_cand, None, _dp(up), _dp(ul), _dp(un), nu, 0,
-                                      _dp(sup_i), None, C.byref(last)))                                         # GTI:107
+                                      _dp(sup_i), None, None))                                                  # GTI:107
         nsup = self._buf("n_support", n_cand, i32)
         self._chk(lib.vsv_select_i32(h, _dp(ctyp), L.DEL, _dp(sup_d), _dp(sup_i), n_cand, _dp(nsup)))
 
