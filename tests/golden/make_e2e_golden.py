@@ -122,7 +122,7 @@ def events_for(hsv, rng, a, b, small_rate, noisy):
     return out
 
 
-def make_dataset(seed=20240611, L=140_000, chrom="chr1", lite=False, name_prefix="", coverage=32):
+def make_dataset(seed=20240611, L=140_000, chrom="chr1", lite=False, name_prefix="", coverage=32, ps_offset=0):
     """`lite` (whole-genome fixture: many small chromosomes) leaves out the hand-placed special cases,
     keeps read sequences compressible and forces one homozygous INS per chromosome (CSS:87 needs one)."""
     rng = random.Random(seed)
@@ -130,11 +130,11 @@ def make_dataset(seed=20240611, L=140_000, chrom="chr1", lite=False, name_prefix
     svs = make_svs(rng, L)
     if lite:
         svs[0].update(type="INS", zyg="hom", seq=rand_seq(rng, svs[0]["len"]))
-        return _finish_dataset(rng, ref, svs, L, chrom, True, name_prefix, coverage)
-    return _finish_dataset(rng, ref, svs, L, chrom, False, name_prefix, coverage)
+        return _finish_dataset(rng, ref, svs, L, chrom, True, name_prefix, coverage, ps_offset)
+    return _finish_dataset(rng, ref, svs, L, chrom, False, name_prefix, coverage, ps_offset)
 
 
-def _finish_dataset(rng, ref, svs, L, chrom, lite, name_prefix, coverage):
+def _finish_dataset(rng, ref, svs, L, chrom, lite, name_prefix, coverage, ps_offset):
     # near-duplicate calls for remove_redundancy: the two haplotypes carry similar SVs too far apart
     # to be paired (> 200 bp) but close enough to be linked (INS: <= 500 bp + edit similarity;
     # DEL: <= 3000 bp + overlap)
@@ -163,7 +163,7 @@ def _finish_dataset(rng, ref, svs, L, chrom, lite, name_prefix, coverage):
     for hap in (1, 2):
         spans = [(150, int(L * 0.56)), (int(L * 0.5), L - 120)] if lite else [(150, 76_000), (68_000, L - 120)]
         for k, (a, b) in enumerate(spans):
-            name = "PS%d_%d_hp%d_%d" % (a + 1, b, hap, k)
+            name = "PS%d_%d_hp%d_%d" % (a + 1 + ps_offset, b + ps_offset, hap, k)
             ev = events_for(haps[hap], rng, a, b, 0.00012, False)
             ev = [e for e in ev if e[2] < 30 or any(e[0] == s["pos"] for s in haps[hap])]
             ev = sorted(ev + [g for g in ghosts[hap] if a + 500 < g[0] < b - 500], key=lambda e: e[0])

@@ -52,7 +52,8 @@ def main():
             chrom = "chr%d" % c
             L = 30_000 + 700 * ((c * 7) % 11)
             ref, svs, contig_recs, contig_fa, reads = G.make_dataset(seed=7000 + c, L=L, chrom=chrom, lite=True,
-                                                                      name_prefix="c%d" % c, coverage=26)
+                                                                      name_prefix="c%d" % c, coverage=26,
+                                                                      ps_offset=c * 1_000_000)   # contig names unique genome-wide
             sq.append((chrom, L))
             fref.write(">%s\n" % chrom)
             for i in range(0, L, 60):
@@ -98,10 +99,52 @@ def main():
             fo.write(data)
         n += 1
     print("kept %d reference output files under %s" % (n, exp))
+    run_otherasm(work, env)
     for root, _, files in os.walk(inp):
         for fn in files:
             if fn.endswith((".sam", ".fa")):
                 subprocess.check_call(["gzip", "-9", "-n", "-f", os.path.join(root, fn)])
+
+
+def run_otherasm(work, env):
+    """LI/volcanosv-vc-large-indel-otherasm.py on the same data: ONE haplotype-resolved contig FASTA
+    and ONE contig alignment file for the whole genome (the script splits contigs by chromosome)."""
+    allfa = os.path.join(work, "all_contigs.fa")
+    allsam = os.path.join(work, "all_contigs.sam")
+    with open(allfa, "w") as fo:
+        for c in range(1, 23):
+            fo.write(open(os.path.join(work, "asm", "chr%d" % c, "assembly", "final_contigs", "Sample_final_contigs.fa")).read())
+    with open(allsam, "w") as fo:
+        fo.write("@HD\tVN:1.6\tSO:coordinate\n")
+        body = []
+        for c in range(1, 23):
+            for line in open(os.path.join(work, "contigs_chr%d.sam" % c)):
+                if line.startswith("@SQ"):
+                    fo.write(line)
+                elif not line.startswith("@"):
+                    body.append(line)
+        fo.writelines(body)
+    env = dict(env, VSV_CONTIG_SAM=allsam)
+    env.pop("VSV_CONTIG_SAM_DIR", None)
+    out = os.path.join(work, "out_otherasm")
+    cmd = ["python3", G.LI + "volcanosv-vc-large-indel-otherasm.py", "-i", allfa, "-o", out, "-dtype", "Hifi", "-bam",
+           os.path.join(work, "reads.sam"), "-ref", os.path.join(work, "ref.fa"), "-t", "4", "-px", "Sample"]
+    with open(os.path.join(OUT, "reference_run_otherasm.log"), "w") as log:
+        log.write(" ".join(cmd) + "\n")
+        log.flush()
+        rc = subprocess.call(cmd, env=env, stdout=log, stderr=subprocess.STDOUT, cwd=work)
+    print("otherasm reference exit code", rc)
+    exp = os.path.join(OUT, "expected_otherasm")
+    os.makedirs(exp, exist_ok=True)
+    for rel in ("raw_variants_wgs.vcf", "variants_filtered_GT_corrected.vcf", "Sample_volcanosv_large_indel.vcf"):
+        src = os.path.join(out, rel)
+        if not os.path.exists(src):
+            print("missing in the otherasm run:", rel)
+            continue
+        with open(src, "rb") as fi, open(os.path.join(exp, rel), "wb") as fo:
+            fo.write(fi.read().replace(work.encode(), b"$WORK"))
+        same = open(src, "rb").read() == open(os.path.join(work, "out", rel), "rb").read()
+        print(rel, "identical to the per-chromosome-assembly run:", same)
 
 
 if __name__ == "__main__":

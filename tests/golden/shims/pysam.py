@@ -21,6 +21,7 @@ class AlignedSegment:
         self.seq = self.query_sequence = None if f[9] == "*" else f[9]
         self.query_length = 0 if self.seq is None else len(self.seq)
         self.is_reverse = bool(self.flag & 16)
+        self.is_unmapped = bool(self.flag & 4)
         self._tags = []
         for t in f[11:]:
             k, ty, v = t.split(":", 2)
@@ -69,3 +70,29 @@ class AlignmentFile:
 
     def close(self):
         pass
+
+
+class FastaFile:
+    """references + fetch(name) over a plain FASTA (volcanosv-vc-large-indel-otherasm.py:280-282)."""
+
+    def __init__(self, path):
+        self._seq = {}
+        name = None
+        with open(path) as fh:
+            for line in fh:
+                if line.startswith(">"):
+                    name = line[1:].split()[0]
+                    self._seq[name] = []
+                elif name is not None:
+                    self._seq[name].append(line.strip())
+        self._seq = {k: "".join(v) for k, v in self._seq.items()}
+        self.references = tuple(self._seq)
+
+    def fetch(self, name):
+        return self._seq[name]
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        return False

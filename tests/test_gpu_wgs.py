@@ -72,3 +72,30 @@ def test_whole_genome_mode_two_ranks(work):
     for p in procs:
         assert p.wait(timeout=900) == 0
     check(out, work)
+
+
+def test_otherasm_entry_point(work):
+    """LI/volcanosv-vc-large-indel-otherasm.py: one whole-genome contig FASTA + one contig alignment file,
+    contigs split by chromosome on the fly; against the unmodified reference's run of that script."""
+    from volcanosv_b200 import cli
+    allfa, allsam = os.path.join(work, "all_contigs.fa"), os.path.join(work, "all_contigs.sam")
+    with open(allfa, "w") as fo:
+        for c in range(1, 23):
+            fo.write(open(os.path.join(work, "asm", "chr%d" % c, "assembly", "final_contigs", "Sample_final_contigs.fa")).read())
+    with open(allsam, "w") as fo:
+        fo.write("@HD\tVN:1.6\tSO:coordinate\n")
+        body = []
+        for c in range(1, 23):
+            for line in open(os.path.join(work, "contigs_chr%d.sam" % c)):
+                if line.startswith("@SQ"):
+                    fo.write(line)
+                elif not line.startswith("@"):
+                    body.append(line)
+        fo.writelines(body)
+    out = os.path.join(work, "out_otherasm")
+    cli.main(["volcanosv-vc-large-indel-otherasm.py", "-i", allfa, "-o", out, "-dtype", "Hifi", "-bam",
+              os.path.join(work, "reads.sam"), "-ref", os.path.join(work, "ref.fa"), "-t", "4", "-px", "Sample", "-cbam", allsam])
+    exp = os.path.join(WGS, "expected_otherasm")
+    for rel in os.listdir(exp):
+        got = open(os.path.join(out, rel)).read().replace(work, "$WORK")
+        assert got == open(os.path.join(exp, rel)).read(), rel

@@ -149,15 +149,7 @@ def _main(argv):
                    help="sorted contig-to-reference alignments (RVC:49-58 output); whole-genome mode: a pattern with {chr}")
     a = p.parse_args(argv)
     if a.chr_num is None:                      # whole-genome mode (MAIN:266-279); one process per GPU under torchrun
-        import os
-        rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
-        barrier = None
-        if world > 1:
-            import torch
-            import torch.distributed as dist
-            torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
-            dist.init_process_group("gloo")    # file-level hand-over only: no data-path collective
-            barrier = dist.barrier
+        rank, world, barrier = _ranks()
         out = OP.large_indel_wgs(a.contig_bam, a.input_dir, a.reference, a.bam_file, a.output_dir, a.data_type, a.prefix,
                                  a.read_signature_dir, a.pre_cutesig, rank=rank, world=world, barrier=barrier)
         if out:
@@ -168,6 +160,57 @@ def _main(argv):
                              a.read_signature_dir, a.pre_cutesig))
 
 
+def _rvc_otherasm(argv):
+    p = argparse.ArgumentParser(prog="Raw_variant_call-otherasm.py")
+    p.add_argument("--contig_path", "-contig")
+    p.add_argument("--contig_bam", "-cbam")
+    p.add_argument("--reference_path", "-ref")
+    p.add_argument("--rbam_file", "-rbam")
+    p.add_argument("--signature_dir", "-sigd")
+    p.add_argument("--output_dir", "-o")
+    p.add_argument("--data_type", "-dtype")
+    p.add_argument("--n_thread", "-t", type=int, default=10)
+    p.add_argument("--chr_num", "-chr", type=int)
+    p.add_argument("--header_file", "-header", default=None)
+    a, _ = p.parse_known_args(argv)
+    print(OP.raw_variant_call(a.contig_bam, a.contig_path, a.reference_path, a.output_dir, a.data_type, a.chr_num, a.rbam_file,
+                              a.signature_dir, a.header_file))
+
+
+def _ranks():
+    import os
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    barrier = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
+        dist.init_process_group("gloo")    # file-level hand-over only: no data-path collective
+        barrier = dist.barrier
+    return rank, world, barrier
+
+
+def _main_otherasm(argv):
+    p = argparse.ArgumentParser(prog="volcanosv-vc-large-indel-otherasm.py")
+    p.add_argument("--input_path", "-i")
+    p.add_argument("--output_dir", "-o")
+    p.add_argument("--data_type", "-dtype")
+    p.add_argument("--bam_file", "-bam")
+    p.add_argument("--reference", "-ref")
+    p.add_argument("--read_signature_dir", "-rdsig")
+    p.add_argument("--pre_cutesig", "-presig")
+    p.add_argument("--n_thread", "-t", type=int, default=11)
+    p.add_argument("--prefix", "-px", default="Sample")
+    p.add_argument("--contig_bam", "-cbam", required=True,
+                   help="sorted whole-genome contig alignments (otherasm:232-245 output: minimap2 -x asm20 | samtools sort)")
+    a, _ = p.parse_known_args(argv)
+    rank, world, barrier = _ranks()
+    out = OP.large_indel_otherasm(a.input_path, a.contig_bam, a.reference, a.bam_file, a.output_dir, a.data_type, a.prefix,
+                                  a.read_signature_dir, a.pre_cutesig, rank=rank, world=world, barrier=barrier)
+    if out:
+        print(out)
+
+
 COMMANDS = {
     "extract_reads_signature.py": _ers, "FP_filter_v1.py": _fpf, "sig_extract.py": _se,
     "calculate_signature_support.py": _css, "filter_vcf_by_sig_cov_insdel.py": _cov,
@@ -175,6 +218,8 @@ COMMANDS = {
     "extract_contig_signature_Hifi.py": _ecs("Hifi"), "extract_contig_signature_ONT.py": _ecs("ONT"),
     "extract_contig_signature_CLR.py": _ecs("CLR"), "filter_GT_correction.py": _fgc,
     "volcanosv-vc-large-indel.py": _main,
+    "Raw_variant_call-otherasm.py": _rvc_otherasm,
+    "volcanosv-vc-large-indel-otherasm.py": _main_otherasm,
 }
 
 

@@ -1094,7 +1094,8 @@ def _write_chrom_ref(ref: Dict[str, str], ref_dir: str, chr_num: int) -> str:
 
 def large_indel_wgs(contig_bam_pattern: str, input_dir: str, reference: str, rbam_file: str, output_dir: str, dtype: str,
                     prefix: str = "Sample", read_signature_dir: Optional[str] = None, pre_cutesig: Optional[str] = None,
-                    chroms: Sequence[int] = tuple(range(1, 23)), rank: int = 0, world: int = 1, barrier=None):
+                    chroms: Sequence[int] = tuple(range(1, 23)), rank: int = 0, world: int = 1, barrier=None,
+                    contig_fasta_pattern: Optional[str] = None):
     """LI/volcanosv-vc-large-indel.py WITHOUT -chr (MAIN:233-319): chr1..chr22 through the raw-call
     chain, bodies concatenated in numeric chromosome order into raw_variants_wgs.vcf, ONE
     genome-wide filter + genotype correction, phasing.
@@ -1121,7 +1122,8 @@ def large_indel_wgs(contig_bam_pattern: str, input_dir: str, reference: str, rba
     mine = SH.assign_lpt(weights, world)[rank]
     for c in sorted(mine):
         one = _write_chrom_ref(ref, ref_dir, c)
-        contig_path = "%s/chr%d/assembly/final_contigs/%s_final_contigs.fa" % (input_dir, c, prefix)
+        contig_path = contig_fasta_pattern.format(chr=c) if contig_fasta_pattern else \
+            "%s/chr%d/assembly/final_contigs/%s_final_contigs.fa" % (input_dir, c, prefix)
         raw_variant_call(contig_bam_pattern.format(chr=c), contig_path, one, os.path.join(output_dir, "chr%d" % c), dtype, c,
                          rbam_file, read_signature_dir)
     if barrier is not None:
@@ -1138,6 +1140,29 @@ def large_indel_wgs(contig_bam_pattern: str, input_dir: str, reference: str, rba
     outfile = os.path.join(output_dir, "%s_volcanosv_large_indel.vcf" % prefix)
     phase_vcf(final, outfile, header_file)
     return outfile
+
+
+def large_indel_otherasm(input_path: str, contig_bam: str, reference: str, rbam_file: str, output_dir: str, dtype: str,
+                         prefix: str = "Sample", read_signature_dir: Optional[str] = None, pre_cutesig: Optional[str] = None,
+                         rank: int = 0, world: int = 1, barrier=None):
+    """LI/volcanosv-vc-large-indel-otherasm.py (any haplotype-resolved assembly): ONE whole-genome contig
+    FASTA (`input_path`, 'hp1'/'hp2' in the contig names) and ONE sorted contig alignment file
+    (`contig_bam`; the reference makes it with minimap2 -x asm20, otherasm:232-245, out of scope).
+    Contigs are split by the chromosome they align to (otherasm:249-293), then the whole-genome
+    chain of `large_indel_wgs` runs with Raw_variant_call-otherasm.py's contract (-cbam)."""
+    folder = os.path.join(output_dir, "contig_by_chr")
+    if rank == 0:
+        os.makedirs(folder, exist_ok=True)
+        src = open_alignments(contig_bam)
+        seqs = load_contigs(input_path)
+        for c in range(1, 23):
+            names = list(dict.fromkeys(src.records("chr%d" % c).qname))
+            if names:
+                _write_lines(os.path.join(folder, "chr%d.fasta" % c), [">%s\n%s\n" % (n, seqs[n]) for n in names if n in seqs])
+    if barrier is not None:
+        barrier()
+    return large_indel_wgs(contig_bam, "", reference, rbam_file, output_dir, dtype, prefix, read_signature_dir, pre_cutesig,
+                           rank=rank, world=world, barrier=barrier, contig_fasta_pattern=os.path.join(folder, "chr{chr}.fasta"))
 
 
 def large_indel_chr(contig_bam: str, contig_path: str, reference: str, rbam_file: str, output_dir: str, dtype: str,
