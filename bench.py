@@ -223,14 +223,17 @@ def main():
     sampler = ClockSampler(local)
     sampler.start()
     barrier()
-    ms0, l0 = shard.ctx.timing()
+    def launches():
+        return sum(c.timing()[1] for c in [shard.ctx] + shard.side)
+
+    l0 = launches()
     shard.ctx.timer_start()
     scan_ms = []
     for _ in range(args.steps):
         res = shard.run_safe()
         scan_ms += res.scan_ms
     ms = shard.ctx.timer_stop()
-    _, l1 = shard.ctx.timing()
+    l1 = launches()
     barrier()
     sampler.stop_flag = True
     sampler.join()

@@ -227,3 +227,43 @@ def test_expand_ops16(ctx):
         ops = (ln << 4) | rng.integers(0, 9, n).astype(np.uint32)
         o16, ei, ev = pack_ops16(ops)
         assert np.array_equal(ctx.expand_ops16(o16, ei, ev), ops)
+
+
+def test_fused_scan_ont_scale_positions(ctx):
+    """ONT-shaped shard at 1/16 of the BASELINE chr10 size (~5x10^7 ops, far more tiles than resident
+    warps, records spanning several tiles): EVERY signature's position and query offset against numpy
+    prefix sums over the whole op array, for both streams of the fused pass."""
+    n = synth.n_records("ont") // 16
+    b = synth.synth_records(77, n, "ont", eqx=False)
+    ops, off = b["ops"], b["op_off"]
+    n_ops = int(off[-1])
+    code = (ops & 15).astype(np.uint8)
+    ln = (ops >> 4).astype(np.int64)
+    rec_of = np.repeat(np.arange(n, dtype=np.int64), np.diff(off))
+    enable = (b["qlen"] >= 500).astype(np.uint8)
+    ra, rb, rt, qt, xt = ctx.scan_reads_fused(ops, off, b["pos"], b["mapq"], enable_cute=enable)
+
+    def prefix(member):
+        x = np.where(np.isin(code, member), ln, 0)
+        c = np.cumsum(x)
+        excl = c - x                                   # exclusive prefix over the whole array
+        base = np.concatenate([[0], c])[off[:-1]]      # value at each record start
+        return excl - base[rec_of]
+
+    hc = np.where((np.diff(off) > 0) & (code[np.minimum(off[:-1], n_ops - 1)] == 5), ln[np.minimum(off[:-1], n_ops - 1)], 0)
+    isid = np.isin(code, [1, 2])
+    # stream A = extract_reads_signature (ERS:47-83): mapq >= 50, >= 30 bp; ref = M,D,N,=,X; query = M,I,S,=,X (+ leading H)
+    sel = isid & (ln >= 30) & (b["mapq"][rec_of] >= 50)
+    assert len(ra) == int(sel.sum())
+    assert np.array_equal(ra["rec"], rec_of[sel]) and np.array_equal(ra["len"], ln[sel])
+    assert np.array_equal(ra["pos"], (b["pos"][rec_of] + prefix([0, 2, 3, 7, 8]))[sel])
+    assert np.array_equal(ra["q0"], (prefix([0, 1, 4, 7, 8]) + hc[rec_of])[sel])
+    # stream B = parse_read's CIGAR walk (SE:438-478): mapq >= 20, query_length >= 500, >= 10 bp; N moves no reference counter
+    sel = isid & (ln >= 10) & (b["mapq"][rec_of] >= 20) & (enable[rec_of] != 0)
+    assert len(rb) == int(sel.sum())
+    assert np.array_equal(rb["rec"], rec_of[sel]) and np.array_equal(rb["len"], ln[sel])
+    assert np.array_equal(rb["pos"], (b["pos"][rec_of] + prefix([0, 2, 7, 8]))[sel])
+    # per-record totals
+    tot = np.zeros(n, np.int64)
+    np.add.at(tot, rec_of, np.where(np.isin(code, [0, 2, 3, 7, 8]), ln, 0))
+    assert np.array_equal(tot, rt)

@@ -13,6 +13,7 @@ from __future__ import annotations
 
 import contextlib
 import ctypes as C
+from concurrent.futures import ThreadPoolExecutor
 from dataclasses import dataclass, field
 from typing import Dict, Optional
 
@@ -69,6 +70,13 @@ class ChromShard:
         self.h2d_bytes = 0
         self.d2h_bytes = 0
         self._pending = None
+        # independent branches of the call chain (read-signature sort; DEL and INS `.sigs` order +
+        # grouping) run on side contexts = their own streams, driven by two worker threads (the C
+        # calls release the GIL): their kernels and count read-backs overlap instead of queueing
+        self.side = [L.Context(device), L.Context(device)]
+        for c in self.side:
+            c.set_device_io(True)
+        self.pool = ThreadPoolExecutor(max_workers=2)
 
     # ---- allocation ------------------------------------------------------------------
     def _buf(self, name, n, dtype):
@@ -174,30 +182,49 @@ class ChromShard:
         # read intervals for the depth join: [pos, pos + ref_total)  (reference_end)
         rend = self._buf("read_end", n_rec, i32)
         self._chk(lib.vsv_add_i32(h, _dp(pos), _dp(rt), n_rec, _dp(rend)))
+        # every buffer of the branches is taken here, on this thread
         s_reads_sorted = sig("sig_reads_sorted")
-        self._chk(lib.vsv_sort_sigs(h, _dp(s_reads), n_r, 0, _dp(s_reads_sorted)))       # merge_all (ERS:254-258)
         rs_pos, rs_len = self._buf("rs_pos", cap, i32), self._buf("rs_len", cap, i32)
-        self._chk(lib.vsv_sig_columns(h, _dp(s_reads_sorted), n_r, _dp(rs_pos), _dp(rs_len), None))
+        s_del, s_ins = sig("sig_del"), sig("sig_ins")
+        bufs = {}
+        for name in ("del", "ins"):
+            bufs[name] = (sig("sig_%s_sorted" % name), self._buf(name + "_pos", cap, i32), self._buf(name + "_len", cap, i32),
+                          tuple(self._buf("%s_u%s" % (name, k), cap, i32) for k in "cpln"))
+
+        def chk(c, rc):
+            if rc != 0:
+                raise L.VsvError(rc, (lib.vsv_last_error(c.h) or b"").decode())
+
+        def reads_branch(c):                                                              # merge_all (ERS:254-258)
+            chk(c, lib.vsv_sort_sigs(c.h, _dp(s_reads), n_r, 0, _dp(s_reads_sorted)))
+            chk(c, lib.vsv_sig_columns(c.h, _dp(s_reads_sorted), n_r, _dp(rs_pos), _dp(rs_len), None))
+            c.sync()
+
+        def sigs_branch(c, name, src, n, min_len):
+            # `.sigs` order (SE:637-638), unique signatures (GTD:65-86 / GTI:67-101)
+            srt, p_, l_, (uc, up, ul, un) = bufs[name]
+            chk(c, lib.vsv_sort_sigs(c.h, _dp(src), n, 1, _dp(srt)))
+            chk(c, lib.vsv_sig_columns(c.h, _dp(srt), n, _dp(p_), _dp(l_), None))
+            nu = C.c_int64()
+            chk(c, lib.vsv_group_sigs(c.h, None, _dp(p_), _dp(l_), n, min_len, _dp(uc), _dp(up), _dp(ul), _dp(un), C.byref(nu)))
+            c.sync()
+            return (p_, l_, n, up, ul, un, int(nu.value))
+
+        self.ctx.sync()                                        # the scan's outputs are complete for the other streams
+        f_reads = self.pool.submit(reads_branch, self.side[0])
 
         # -- in-read merge of the cuteSV-style signals (SE:373-435) -------------------------
-        s_del, s_ins = sig("sig_del"), sig("sig_ins")
         nd, ni = C.c_int64(), C.c_int64()
         self._chk(lib.vsv_merge_in_record(h, L.MODE_CUTE, _dp(s_cute), n_c, _dp(s_del), C.byref(nd), _dp(s_ins),
                                           C.byref(ni)))
         res.n_del, res.n_ins = int(nd.value), int(ni.value)
+        self.ctx.sync()
 
-        # -- stage 2: `.sigs` order (SE:637-638), unique signatures (GTD:65-86 / GTI:67-101)
-        uniq = {}
-        for name, src, n, min_len in (("del", s_del, res.n_del, 0), ("ins", s_ins, res.n_ins, 30)):
-            srt = sig("sig_%s_sorted" % name)
-            self._chk(lib.vsv_sort_sigs(h, _dp(src), n, 1, _dp(srt)))
-            p_, l_ = self._buf(name + "_pos", cap, i32), self._buf(name + "_len", cap, i32)
-            self._chk(lib.vsv_sig_columns(h, _dp(srt), n, _dp(p_), _dp(l_), None))
-            uc, up, ul, un = (self._buf("%s_u%s" % (name, k), cap, i32) for k in "cpln")
-            nu = C.c_int64()
-            self._chk(lib.vsv_group_sigs(h, None, _dp(p_), _dp(l_), n, min_len, _dp(uc), _dp(up), _dp(ul), _dp(un),
-                                         C.byref(nu)))
-            uniq[name] = (p_, l_, n, up, ul, un, int(nu.value))
+        # -- stage 2: the DEL and INS tables are independent: one on a side stream, one here ---
+        f_reads.result()
+        f_del = self.pool.submit(sigs_branch, self.side[1], "del", s_del, res.n_del, 0)
+        uniq = {"ins": sigs_branch(self.ctx, "ins", s_ins, res.n_ins, 30)}
+        uniq["del"] = f_del.result()
         res.n_udel, res.n_uins = uniq["del"][6], uniq["ins"][6]
 
         # -- candidate-side joins ------------------------------------------------------
