@@ -191,6 +191,13 @@ class ChromShard:
             bufs[name] = (sig("sig_%s_sorted" % name), self._buf(name + "_pos", cap, i32), self._buf(name + "_len", cap, i32),
                           tuple(self._buf("%s_u%s" % (name, k), cap, i32) for k in "cpln"))
 
+        cpos, clen, ctyp, cgt = (d["cand_" + k] for k in ("pos", "svlen", "type", "gt"))
+        fp = self._buf("fp_support", n_cand, i32)
+        cend = self._buf("cand_end", n_cand, i32)
+        self._chk(lib.vsv_add_i32(h, _dp(cpos), _dp(clen), n_cand, _dp(cend)))
+        cov = dict(ins=self._buf("cov_ins", n_cand, i64), **{"del": self._buf("cov_del", n_cand, i64)})
+        sup = dict(ins=self._buf("sup_ins", n_cand, i32), **{"del": self._buf("sup_del", n_cand, i32)})
+
         def chk(c, rc):
             if rc != 0:
                 raise L.VsvError(rc, (lib.vsv_last_error(c.h) or b"").decode())
@@ -198,6 +205,7 @@ class ChromShard:
         def reads_branch(c):                                                              # merge_all (ERS:254-258)
             chk(c, lib.vsv_sort_sigs(c.h, _dp(s_reads), n_r, 0, _dp(s_reads_sorted)))
             chk(c, lib.vsv_sig_columns(c.h, _dp(s_reads_sorted), n_r, _dp(rs_pos), _dp(rs_len), None))
+            chk(c, lib.vsv_fp_support(c.h, _dp(cpos), _dp(clen), n_cand, _dp(rs_pos), _dp(rs_len), n_r, _dp(fp)))  # FPF
             c.sync()
 
         def sigs_branch(c, name, src, n, min_len):
@@ -207,6 +215,13 @@ class ChromShard:
             chk(c, lib.vsv_sig_columns(c.h, _dp(srt), n, _dp(p_), _dp(l_), None))
             nu = C.c_int64()
             chk(c, lib.vsv_group_sigs(c.h, None, _dp(p_), _dp(l_), n, min_len, _dp(uc), _dp(up), _dp(ul), _dp(un), C.byref(nu)))
+            # candidate-side joins of this table: coverage support (CSS:81 / CSS:138), supporting signatures (GTD:92 / GTI:107)
+            if name == "ins":
+                chk(c, lib.vsv_ins_cov(c.h, _dp(cpos), n_cand, _dp(p_), _dp(l_), n, 1000, _dp(cov[name])))
+            else:
+                chk(c, lib.vsv_del_cov(c.h, _dp(cpos), _dp(cend), n_cand, _dp(p_), _dp(l_), n, 1000, _dp(cov[name])))
+            chk(c, lib.vsv_sig_support(c.h, None, _dp(cpos), _dp(clen), n_cand, None, _dp(up), _dp(ul), _dp(un), int(nu.value), 0,
+                                       _dp(sup[name]), None, None))
             c.sync()
             return (p_, l_, n, up, ul, un, int(nu.value))
 
@@ -221,30 +236,14 @@ class ChromShard:
         self.ctx.sync()
 
         # -- stage 2: the DEL and INS tables are independent: one on a side stream, one here ---
-        f_reads.result()
         f_del = self.pool.submit(sigs_branch, self.side[1], "del", s_del, res.n_del, 0)
         uniq = {"ins": sigs_branch(self.ctx, "ins", s_ins, res.n_ins, 30)}
         uniq["del"] = f_del.result()
+        f_reads.result()
         res.n_udel, res.n_uins = uniq["del"][6], uniq["ins"][6]
 
-        # -- candidate-side joins ------------------------------------------------------
-        cpos, clen, ctyp, cgt = (d["cand_" + k] for k in ("pos", "svlen", "type", "gt"))
-        fp = self._buf("fp_support", n_cand, i32)
-        self._chk(lib.vsv_fp_support(h, _dp(cpos), _dp(clen), n_cand, _dp(rs_pos), _dp(rs_len), n_r, _dp(fp)))  # FPF
-        cend = self._buf("cand_end", n_cand, i32)
-        self._chk(lib.vsv_add_i32(h, _dp(cpos), _dp(clen), n_cand, _dp(cend)))
-        cov_i, cov_d = self._buf("cov_ins", n_cand, i64), self._buf("cov_del", n_cand, i64)
-        p_, l_, n, *_ = uniq["ins"]
-        self._chk(lib.vsv_ins_cov(h, _dp(cpos), n_cand, _dp(p_), _dp(l_), n, 1000, _dp(cov_i)))                 # CSS:81
-        p_, l_, n, *_ = uniq["del"]
-        self._chk(lib.vsv_del_cov(h, _dp(cpos), _dp(cend), n_cand, _dp(p_), _dp(l_), n, 1000, _dp(cov_d)))      # CSS:138
-        sup_d, sup_i = self._buf("sup_del", n_cand, i32), self._buf("sup_ins", n_cand, i32)
-        _, _, _, up, ul, un, nu = uniq["del"]
-        self._chk(lib.vsv_sig_support(h, None, _dp(cpos), _dp(clen), n_cand, None, _dp(up), _dp(ul), _dp(un), nu, 0,
-                                      _dp(sup_d), None, None))                                                  # GTD:92
-        _, _, _, up, ul, un, nu = uniq["ins"]
-        self._chk(lib.vsv_sig_support(h, None, _dp(cpos), _dp(clen), n_cand, None, _dp(up), _dp(ul), _dp(un), nu, 0,
-                                      _dp(sup_i), None, None))                                                  # GTI:107
+        # -- the joins ran inside the branches; combine per candidate type -----------------
+        cov_i, cov_d, sup_i, sup_d = cov["ins"], cov["del"], sup["ins"], sup["del"]
         nsup = self._buf("n_support", n_cand, i32)
         self._chk(lib.vsv_select_i32(h, _dp(ctyp), L.DEL, _dp(sup_d), _dp(sup_i), n_cand, _dp(nsup)))
 
