@@ -36,7 +36,8 @@ def make_workload(profile: str, scale: float, rank: int, n_cand: int):
     L = synth.CHR10_LEN
     for c in range(chunks):
         n = n_total // chunks
-        b = synth.synth_records(1000 * rank + 10 + c, n, profile, chrom_len=L // chunks, eqx=True)
+        # CIGAR alphabet as the aligners of each data type write it: minimap2 (ONT, CLR) uses M; pbmm2 (HiFi) =/X
+        b = synth.synth_records(1000 * rank + 10 + c, n, profile, chrom_len=L // chunks, eqx=(profile == "hifi"))
         b["pos"] = (b["pos"].astype(np.int64) + c * (L // chunks)).astype(np.int32)
         parts.append(b)
     batch = {}
@@ -199,10 +200,20 @@ def main():
 
     # host staging format of the end-to-end path: ops as 16-bit words + a sparse exception list
     # (vsv_expand_ops16); produced by the host packer once, like the BAM decode it follows
-    from volcanosv_b200.lib import pack_ops16
-    o16, exc_idx, exc_val = pack_ops16(batch["ops"])
+    from volcanosv_b200.lib import pack_ops16, pack_ops8
+    # densest staging format that fits the data: ops8 (1 B/op; noisy long reads: ~1 % exceptions) when fewer than
+    # 3 % of the ops need the exception list, else ops16 (2 B/op; HiFi / =,X CIGARs).  The native BAM feeder
+    # (vsv_bam_chrom_fill) writes either format straight from the BAM records, so packing is not an extra pass.
+    o8, exc_idx, exc_val = pack_ops8(batch["ops"])
     pinned16 = {k: v for k, v in pinned.items() if k != "ops"}
-    pinned16["ops16"] = torch.from_numpy(o16.view(np.int16)).pin_memory()
+    if len(exc_idx) < 0.03 * n_ops:
+        staging = "ops8"
+        pinned16["ops8"] = torch.from_numpy(o8).pin_memory()
+    else:
+        staging = "ops16"
+        o16, exc_idx, exc_val = pack_ops16(batch["ops"])
+        pinned16["ops16"] = torch.from_numpy(o16.view(np.int16)).pin_memory()
+    del o8
     pinned16["exc_idx"] = torch.from_numpy(exc_idx).pin_memory()
     pinned16["exc_val"] = torch.from_numpy(exc_val.view(np.int32)).pin_memory()
 
@@ -254,8 +265,10 @@ def main():
         stream.n_in = stream.n_out = 0
         stream.submit(host, pinned_c, n_ops=n_ops)
         stream.submit(host, pinned_c, n_ops=n_ops)
-        stream.collect(pin_out)                       # warm both slots and the pinned output buffers
-        barrier()                                     # slot 1's upload is complete here (prologue, untimed)
+        stream.collect(pin_out)                       # warm BOTH slots (buffers, scratch arenas of every context)
+        stream.collect(pin_out)                       # and the pinned output buffers
+        stream.submit(host, pinned_c, n_ops=n_ops)
+        barrier()                                     # one shard's upload is complete here (prologue, untimed)
         t0 = time.perf_counter()
         for _ in range(args.steps):
             stream.submit(host, pinned_c, n_ops=n_ops)
@@ -315,7 +328,7 @@ def main():
                 clocks=sampler.result(), gpu_launches=int(l1 - l0),
                 e2e=dict(value=e2e_value, unit=UNIT, h2d_bytes_per_step=h2d_b,
                          d2h_bytes_per_step=d2h_b, ms_per_step=e2e_per_step * 1e3,
-                         staging="ops16 + %d exceptions (vsv_expand_ops16), pinned host buffers" % len(exc_idx),
+                         staging="%s + %d exceptions (vsv_expand_%s), pinned host buffers" % (staging, len(exc_idx), staging),
                          pipelining="double-buffered shards: H2D of shard k+1 overlaps kernels + D2H of shard k",
                          bam_native_u32=dict(value=world * n_rec / e2e32_per_step, ms_per_step=e2e32_per_step * 1e3,
                                              h2d_bytes_per_step=h2d32_b)),

@@ -104,6 +104,12 @@ int vsv_scan_cigar(vsv_ctx* ctx, int mode, int min_len, int min_mapq, const uint
  * host side of the format is volcanosv_b200.lib.pack_ops16. */
 int vsv_expand_ops16(vsv_ctx* ctx, const uint16_t* ops16, int64_t n_ops, const int64_t* exc_idx,
                      const uint32_t* exc_val, int64_t n_exc, uint32_t* ops_out);
+/* Denser staging for noisy long reads (ONT/CLR: ~99 % of the ops are M/I/D shorter than 63 bases):
+ * ops8[i] = len << 2 | op for op in {M,I,D} and len <= 62, else 0xFF with the full word in the
+ * exception list.  1 byte per op over PCIe (+ 12 bytes per exception).  Host side:
+ * volcanosv_b200.lib.pack_ops8, or vsv_bam_chrom_fill straight from the BAM records. */
+int vsv_expand_ops8(vsv_ctx* ctx, const uint8_t* ops8, int64_t n_ops, const int64_t* exc_idx,
+                    const uint32_t* exc_val, int64_t n_exc, uint32_t* ops_out);
 
 /* The two READ-BAM scanners in ONE pass over the packed ops (the ops are the bulk of the
  * bytes, so this halves HBM traffic of stage 1): stream "reads" == vsv_scan_cigar(
@@ -251,13 +257,13 @@ int vsv_bam_ref(const vsv_bam* b, int i, const char** name, int64_t* len, int64_
 /* sizes[5] = records, CIGAR ops, qname bytes, SEQ bytes, SA-tag bytes of reference `tid` */
 int vsv_bam_chrom_sizes(vsv_bam* b, int tid, int64_t* sizes);
 /* Columns of reference `tid` in file order; NULL skips a column.  `ops` = BAM-native u32,
- * `ops16` + (exc_idx, exc_val, exc_cap, n_exc) = the staging format of vsv_expand_ops16
- * (VSV_E_CAPACITY with *n_exc = needed when the list is too small).  *_off arrays have n_rec + 1
+ * `ops16` or `ops8` (not both) + (exc_idx, exc_val, exc_cap, n_exc) = the staging formats of
+ * vsv_expand_ops16 / vsv_expand_ops8 (VSV_E_CAPACITY with *n_exc = needed when the list is too small).  *_off arrays have n_rec + 1
  * entries; names / seq (ASCII) / sa are concatenated without terminators. */
 int vsv_bam_chrom_fill(vsv_bam* b, int tid, int32_t* pos, uint8_t* mapq, uint16_t* flag, int32_t* qlen,
-                       int64_t* op_off, uint32_t* ops, uint16_t* ops16, int64_t* exc_idx, uint32_t* exc_val,
-                       int64_t exc_cap, int64_t* n_exc, int64_t* name_off, char* names, int64_t* seq_off,
-                       char* seq, int64_t* sa_off, char* sa);
+                       int64_t* op_off, uint32_t* ops, uint16_t* ops16, uint8_t* ops8, int64_t* exc_idx,
+                       uint32_t* exc_val, int64_t exc_cap, int64_t* n_exc, int64_t* name_off, char* names,
+                       int64_t* seq_off, char* seq, int64_t* sa_off, char* sa);
 /* SEQ (ASCII) of record i of reference `tid`: sparse `read.seq` accesses (SE:452, ECS_H:642-700).
  * VSV_E_CAPACITY with *len = needed when cap is too small. */
 int vsv_bam_record_seq(vsv_bam* b, int tid, int64_t i, char* out, int64_t cap, int64_t* len);

@@ -38,7 +38,12 @@ def check(bam, sam, compact):
         assert n_rec == len(mine)
         d = bf.chrom(chrom, compact=compact)
         ops = d["ops"] if not compact else None
-        if compact:
+        if compact == 8:
+            o8 = d["ops8"].astype(np.uint32)
+            ops = ((o8 >> 2) << 4) | (o8 & 3)
+            assert np.all(np.diff(d["exc_idx"]) > 0) and np.all(d["ops8"][d["exc_idx"]] == 0xFF)
+            ops[d["exc_idx"]] = d["exc_val"]
+        elif compact:
             ops = d["ops16"].astype(np.uint32)
             assert np.all(np.diff(d["exc_idx"]) > 0)
             assert np.all((d["ops16"][d["exc_idx"]] >> 4) == 0xFFF)
@@ -59,7 +64,7 @@ def check(bam, sam, compact):
     bf.close()
 
 
-@pytest.mark.parametrize("compact", [False, True])
+@pytest.mark.parametrize("compact", [False, True, 8])
 def test_reads_and_contigs_round_trip(tmp_path, compact):
     for name in ("reads", "contigs"):
         bam = str(tmp_path / (name + ".bam"))
@@ -86,6 +91,7 @@ def test_long_cigar_unmapped_and_long_ops(tmp_path):
     bamio.sam_to_bam(str(sam) + ".gz", bam)
     check(bam, str(sam) + ".gz", False)
     check(bam, str(sam) + ".gz", True)
+    check(bam, str(sam) + ".gz", 8)
     d = L.BamFile(bam).chrom("chrB", compact=True)
     assert len(d["exc_idx"]) == 3 and list(d["exc_val"] >> 4) == [4095, 70000, 100000]
 

@@ -267,3 +267,17 @@ def test_fused_scan_ont_scale_positions(ctx):
     tot = np.zeros(n, np.int64)
     np.add.at(tot, rec_of, np.where(np.isin(code, [0, 2, 3, 7, 8]), ln, 0))
     assert np.array_equal(tot, rt)
+
+
+def test_expand_ops8(ctx):
+    """vsv_expand_ops8 == the BAM-native words, incl. exceptions and a ragged tail."""
+    from volcanosv_b200.lib import pack_ops8
+    rng = np.random.default_rng(21)
+    for n in (0, 1, 15, 16, 17, 100003):
+        code = rng.choice([0, 1, 2, 3, 4, 5, 8, 12], n).astype(np.uint32) if n else np.zeros(0, np.uint32)
+        ln = rng.integers(0, 70, n).astype(np.uint32)
+        if n > 50:
+            ln[rng.integers(0, n, max(1, n // 50))] = rng.integers(4095, 1 << 27, max(1, n // 50))
+        ops = (ln << 4) | code
+        o8, ei, ev = pack_ops8(ops)
+        assert np.array_equal(ctx.expand_ops8(o8, ei, ev), ops)

@@ -60,6 +60,14 @@ def test_compact_staging_gives_identical_results():
     assert sh.h2d_bytes < 0.62 * (4 * len(o16) + 17 * len(b["pos"]) + 16 * 500)
     for k in a:
         assert np.array_equal(a[k], c[k], equal_nan=True) if a[k].dtype.kind == "f" else np.array_equal(a[k], c[k]), k
+    from volcanosv_b200.lib import pack_ops8
+    o8, ei, ev = pack_ops8(b["ops"])
+    b3 = {k: v for k, v in b.items() if k != "ops"}
+    b3.update(ops8=o8, exc_idx=ei, exc_val=ev)
+    sh.upload(b3, cands, n_ops=len(o8))
+    e = sh.download(sh.run_safe())
+    for k in a:
+        assert np.array_equal(a[k], e[k], equal_nan=True) if a[k].dtype.kind == "f" else np.array_equal(a[k], e[k]), k
 
 
 def test_shard_stream_overlapped_uploads_match_single_shard():

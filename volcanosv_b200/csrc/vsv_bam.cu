@@ -309,11 +309,12 @@ extern "C" int vsv_bam_chrom_sizes(vsv_bam* b, int tid, int64_t* sizes) {
 // Any output pointer may be NULL to skip that column; `ops` (u32) and `ops16` (+ exception list)
 // are alternative encodings of the same CIGAR ops and may both be requested.
 extern "C" int vsv_bam_chrom_fill(vsv_bam* b, int tid, int32_t* pos, uint8_t* mapq, uint16_t* flag, int32_t* qlen,
-                                  int64_t* op_off, uint32_t* ops, uint16_t* ops16, int64_t* exc_idx, uint32_t* exc_val,
-                                  int64_t exc_cap, int64_t* n_exc, int64_t* name_off, char* names, int64_t* seq_off,
-                                  char* seq, int64_t* sa_off, char* sa) {
+                                  int64_t* op_off, uint32_t* ops, uint16_t* ops16, uint8_t* ops8, int64_t* exc_idx,
+                                  uint32_t* exc_val, int64_t exc_cap, int64_t* n_exc, int64_t* name_off, char* names,
+                                  int64_t* seq_off, char* seq, int64_t* sa_off, char* sa) {
   if (!b || tid < 0 || tid >= (int)b->refs.size()) { g_bam_err = "vsv_bam_chrom_fill: bad argument"; return VSV_E_ARG; }
-  if (ops16 && (!exc_idx || !exc_val || !n_exc)) { g_bam_err = "vsv_bam_chrom_fill: ops16 needs the exception list"; return VSV_E_ARG; }
+  if ((ops16 || ops8) && (!exc_idx || !exc_val || !n_exc)) { g_bam_err = "vsv_bam_chrom_fill: ops16 / ops8 need the exception list"; return VSV_E_ARG; }
+  if (ops16 && ops8) { g_bam_err = "vsv_bam_chrom_fill: ask for ops16 or ops8, not both"; return VSV_E_ARG; }
   const std::vector<uint64_t>& rr = b->refs[tid].recs;
   const int64_t n = (int64_t)rr.size();
   // pass 1 (serial, pointer hops only): offsets of the variable-length columns
@@ -369,6 +370,19 @@ extern "C" int vsv_bam_chrom_fill(vsv_bam* b, int tid, int32_t* pos, uint8_t* ma
           }
         }
       }
+      if (ops8) {
+        for (uint32_t k = 0; k < v.n_cigar; ++k) {
+          uint32_t w;
+          memcpy(&w, v.cigar + k, 4);
+          if ((w & 15u) <= 2u && (w >> 4) <= 62u) {
+            ops8[o + k] = (uint8_t)(((w >> 4) << 2) | (w & 3u));
+          } else {  // not M/I/D or 63+ bases: marker + (index, full word) in the exception list (vsv_expand_ops8)
+            ops8[o + k] = 0xFFu;
+            const long long s = exc_n.fetch_add(1);
+            if (s < exc_cap) { exc_idx[s] = o + k; exc_val[s] = w; }
+          }
+        }
+      }
       if (names) memcpy(names + o_name[i], v.name, (size_t)(o_name[i + 1] - o_name[i]));
       if (seq) {
         char* dst = seq + o_seq[i];
@@ -382,11 +396,11 @@ extern "C" int vsv_bam_chrom_fill(vsv_bam* b, int tid, int32_t* pos, uint8_t* ma
     }
   });
   if (n_exc) *n_exc = exc_n.load();
-  if (ops16 && exc_n.load() > exc_cap) {
+  if ((ops16 || ops8) && exc_n.load() > exc_cap) {
     g_bam_err = "vsv_bam_chrom_fill: exception list too small";
     return VSV_E_CAPACITY;
   }
-  if (ops16 && exc_n.load() > 1) {  // threads appended out of order: vsv_expand_ops16 wants ascending indices
+  if ((ops16 || ops8) && exc_n.load() > 1) {  // threads appended out of order: vsv_expand_ops16 wants ascending indices
     const long long m = exc_n.load();
     std::vector<std::pair<int64_t, uint32_t>> tmp((size_t)m);
     for (long long k = 0; k < m; ++k) tmp[k] = {exc_idx[k], exc_val[k]};

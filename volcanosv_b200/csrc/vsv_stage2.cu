@@ -756,6 +756,50 @@ __global__ void k_patch_ops(const int64_t* __restrict__ idx, const uint32_t* __r
   if (i < n_exc && idx[i] >= 0 && idx[i] < n) out[idx[i]] = val[i];
 }
 
+// ops8: one byte per op = len << 2 | code for M/I/D (codes 0..2) with len <= 62; 0xFF marks an op
+// whose full word is in the exception list.  16 ops per thread: one LDG.128 in, four STG.128 out.
+__global__ void __launch_bounds__(256) k_expand_ops8(const uint8_t* __restrict__ in, int64_t n, uint32_t* __restrict__ out) {
+  const int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 16;
+  if (i + 16 <= n) {
+    const uint4 v = __ldg(reinterpret_cast<const uint4*>(in + i));
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      uint4 o;
+      const uint32_t b0 = w[k] & 0xFFu, b1 = (w[k] >> 8) & 0xFFu, b2 = (w[k] >> 16) & 0xFFu, b3 = w[k] >> 24;
+      o.x = ((b0 >> 2) << 4) | (b0 & 3u); o.y = ((b1 >> 2) << 4) | (b1 & 3u);
+      o.z = ((b2 >> 2) << 4) | (b2 & 3u); o.w = ((b3 >> 2) << 4) | (b3 & 3u);
+      reinterpret_cast<uint4*>(out + i)[k] = o;
+    }
+  } else {
+    for (int64_t k = i; k < n; ++k) out[k] = (((uint32_t)in[k] >> 2) << 4) | (in[k] & 3u);
+  }
+}
+
+extern "C" int vsv_expand_ops8(vsv_ctx* ctx, const uint8_t* ops8, int64_t n_ops, const int64_t* exc_idx,
+                               const uint32_t* exc_val, int64_t n_exc, uint32_t* ops_out) {
+  VSV_TRY(vsv_begin(ctx));
+  if (n_ops < 0 || n_exc < 0 || (n_ops > 0 && (!ops8 || !ops_out)) || (n_exc > 0 && (!exc_idx || !exc_val)))
+    VSV_FAIL(ctx, VSV_E_ARG, "vsv_expand_ops8: bad argument");
+  if (n_ops == 0) return VSV_OK;
+  const uint8_t* din;
+  const int64_t* dix;
+  const uint32_t* dvl;
+  uint32_t* dout;
+  VSV_TRY(vsv_in(ctx, ops8, (size_t)n_ops, &din));
+  VSV_TRY(vsv_in(ctx, exc_idx, (size_t)n_exc, &dix));
+  VSV_TRY(vsv_in(ctx, exc_val, (size_t)n_exc, &dvl));
+  VSV_TRY(vsv_out(ctx, ops_out, (size_t)n_ops, &dout));
+  if ((reinterpret_cast<uintptr_t>(din) & 15u) || (reinterpret_cast<uintptr_t>(dout) & 15u))
+    VSV_FAIL(ctx, VSV_E_ARG, "vsv_expand_ops8: buffers must be 16-byte aligned");
+  VSV_TRY(vsv_t0(ctx));
+  VSV_LAUNCH(ctx, k_expand_ops8, (unsigned)vsv_cdiv(vsv_cdiv(n_ops, 16), 256), 256, 0, din, n_ops, dout);
+  if (n_exc > 0) VSV_LAUNCH(ctx, k_patch_ops, (unsigned)vsv_cdiv(n_exc, 256), 256, 0, dix, dvl, n_exc, n_ops, dout);
+  VSV_TRY(vsv_t1(ctx));
+  VSV_TRY(vsv_out_done(ctx, ops_out, dout, (size_t)n_ops));
+  return vsv_end(ctx);
+}
+
 extern "C" int vsv_expand_ops16(vsv_ctx* ctx, const uint16_t* ops16, int64_t n_ops, const int64_t* exc_idx,
                                 const uint32_t* exc_val, int64_t n_exc, uint32_t* ops_out) {
   VSV_TRY(vsv_begin(ctx));

@@ -50,6 +50,7 @@ SIGNATURES = {
     "vsv_get_main_kernel_ms": [_vp, C.POINTER(C.c_float)],
     "vsv_scan_cigar": [_vp, _int, _int, _int, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _i64, C.POINTER(_i64), _vp, _vp, _vp],
     "vsv_expand_ops16": [_vp, _vp, _i64, _vp, _vp, _i64, _vp],
+    "vsv_expand_ops8": [_vp, _vp, _i64, _vp, _vp, _i64, _vp],
     "vsv_scan_reads_fused": [_vp, _int, _int, _int, _int, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _i64, C.POINTER(_i64),
                              _vp, _i64, C.POINTER(_i64), _vp, _vp, _vp],
     "vsv_merge_in_record": [_vp, _int, _vp, _i64, _vp, C.POINTER(_i64), _vp, C.POINTER(_i64)],
@@ -77,8 +78,8 @@ SIGNATURES = {
     "vsv_bam_ref": [_vp, _int, C.POINTER(C.c_char_p), C.POINTER(_i64), C.POINTER(_i64)],
     "vsv_bam_chrom_sizes": [_vp, _int, _vp],
     "vsv_bam_record_seq": [_vp, _int, _i64, _vp, _i64, C.POINTER(_i64)],
-    "vsv_bam_chrom_fill": [_vp, _int, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, C.POINTER(_i64), _vp, _vp, _vp, _vp,
-                           _vp, _vp],
+    "vsv_bam_chrom_fill": [_vp, _int, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, C.POINTER(_i64), _vp, _vp, _vp,
+                           _vp, _vp, _vp],
     "vsv_genotype": [_vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp],
 }
 _RESTYPE = {"vsv_ctx_destroy": None, "vsv_last_error": C.c_char_p, "vsv_version": C.c_char_p, "vsv_bam_close": None,
@@ -205,6 +206,15 @@ class Context:
         ei, ev = _arr(exc_idx, np.int64), _arr(exc_val, np.uint32)
         out = _aligned_empty(len(o16), np.uint32)
         self._chk(self.lib.vsv_expand_ops16(self.h, _p(o16), len(o16), _p(ei), _p(ev), len(ei), _p(out)))
+        return out
+
+    def expand_ops8(self, ops8, exc_idx, exc_val):
+        o8 = _arr(ops8, np.uint8)
+        if o8.ctypes.data % 16:
+            o8 = _aligned_copy(o8)
+        ei, ev = _arr(exc_idx, np.int64), _arr(exc_val, np.uint32)
+        out = _aligned_empty(len(o8), np.uint32)
+        self._chk(self.lib.vsv_expand_ops8(self.h, _p(o8), len(o8), _p(ei), _p(ev), len(ei), _p(out)))
         return out
 
     def scan_reads_fused(self, ops, op_off, pos, mapq, enable_cute=None, min_len_reads=30, min_mapq_reads=50,
@@ -393,9 +403,9 @@ class BamFile:
         if rc != 0:
             raise VsvError(rc, (self.lib.vsv_bam_last_error() or b"").decode())
 
-    def chrom(self, name_or_tid, compact: bool = False, want_seq: bool = True):
-        """Columns of one reference: dict(pos, mapq, flag, qlen, op_off, ops | ops16+exc_idx+exc_val,
-        name_off, names, seq_off, seq, sa_off, sa)."""
+    def chrom(self, name_or_tid, compact=False, want_seq: bool = True):
+        """Columns of one reference: dict(pos, mapq, flag, qlen, op_off, ops | ops16 | ops8 (+ exc_idx, exc_val),
+        name_off, names, seq_off, seq, sa_off, sa).  compact: False (u32 ops), True / 16 (ops16), 8 (ops8)."""
         tid = name_or_tid if isinstance(name_or_tid, int) else [r[0] for r in self.refs].index(name_or_tid)
         sizes = np.zeros(5, np.int64)
         self._chk(self.lib.vsv_bam_chrom_sizes(self.h, tid, _p(sizes)))
@@ -406,11 +416,12 @@ class BamFile:
                  sa_off=np.empty(n + 1, np.int64), sa=np.empty(ab, np.uint8))
         n_exc = _i64(0)
         if compact:
-            d["ops16"] = _aligned_empty(n_ops, np.uint16)
-            cap = max(1024, n_ops // 256)
+            key = "ops8" if compact == 8 else "ops16"
+            d[key] = _aligned_empty(n_ops, np.uint8 if compact == 8 else np.uint16)
+            cap = max(1024, n_ops // (32 if compact == 8 else 256))
             while True:
                 d["exc_idx"], d["exc_val"] = np.empty(cap, np.int64), np.empty(cap, np.uint32)
-                rc = self._fill(tid, d, None, d["ops16"], cap, n_exc, want_seq)
+                rc = self._fill(tid, d, None, d[key], cap, n_exc, want_seq)
                 if rc != E_CAPACITY:
                     break
                 cap = int(n_exc.value)
@@ -428,9 +439,11 @@ class BamFile:
         self._chk(self.lib.vsv_bam_record_seq(self.h, tid, int(i), buf, int(length), C.byref(n)))
         return buf.raw[: n.value].decode()
 
-    def _fill(self, tid, d, ops, ops16, cap, n_exc, want_seq):
+    def _fill(self, tid, d, ops, packed, cap, n_exc, want_seq):
+        o16 = packed if packed is not None and packed.dtype == np.uint16 else None
+        o8 = packed if packed is not None and packed.dtype == np.uint8 else None
         return self.lib.vsv_bam_chrom_fill(self.h, tid, _p(d["pos"]), _p(d["mapq"]), _p(d["flag"]), _p(d["qlen"]), _p(d["op_off"]),
-                                           _p(ops), _p(ops16), _p(d.get("exc_idx")), _p(d.get("exc_val")), cap, C.byref(n_exc),
+                                           _p(ops), _p(o16), _p(o8), _p(d.get("exc_idx")), _p(d.get("exc_val")), cap, C.byref(n_exc),
                                            _p(d["name_off"]), _p(d["names"]), _p(d["seq_off"]),
                                            _p(d["seq"]) if want_seq else None, _p(d["sa_off"]), _p(d["sa"]))
 
@@ -445,6 +458,19 @@ def pack_ops16(ops):
     exc_val = ops[exc_idx].copy()
     o16[exc_idx] = (np.uint16(0xFFF0) | (exc_val & np.uint32(15)).astype(np.uint16))
     return o16, exc_idx, exc_val
+
+
+def pack_ops8(ops):
+    """Host packer of vsv_expand_ops8: (ops8, exc_idx, exc_val).  One byte per M/I/D op of <= 62 bases."""
+    ops = np.ascontiguousarray(ops, dtype=np.uint32)
+    code, ln = ops & np.uint32(15), ops >> np.uint32(4)
+    big = (code > 2) | (ln > 62)
+    o8 = _aligned_empty(len(ops), np.uint8)
+    np.copyto(o8, (ln << np.uint32(2)) | code, casting="unsafe")
+    exc_idx = np.flatnonzero(big).astype(np.int64)
+    exc_val = ops[exc_idx].copy()
+    o8[exc_idx] = 0xFF
+    return o8, exc_idx, exc_val
 
 
 def _aligned_empty(n, dtype, align=64):

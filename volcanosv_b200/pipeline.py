@@ -107,19 +107,20 @@ class ChromShard:
 
         with torch.cuda.stream(stream if stream is not None else torch.cuda.current_stream()):
             expand = None
-            if "ops16" in batch:
-                # compact staging (include/volcanosv_b200.h: vsv_expand_ops16): 2 bytes per op over PCIe,
-                # widened on the device into the BAM-native u32 array the scanners read
-                src16 = batch["ops16"]
+            if "ops16" in batch or "ops8" in batch:
+                # compact staging (include/volcanosv_b200.h: vsv_expand_ops16 / vsv_expand_ops8): 2 bytes or
+                # 1 byte per op over PCIe, widened on the device into the BAM-native u32 array the scanners read
+                wide = "ops16" in batch
+                src16 = batch["ops16" if wide else "ops8"]
                 if isinstance(src16, np.ndarray):
-                    src16 = torch.from_numpy(np.ascontiguousarray(src16.view(np.int16)))
+                    src16 = torch.from_numpy(np.ascontiguousarray(src16.view(np.int16 if wide else np.uint8)))
                 n_ops = int(n_ops if n_ops is not None else src16.numel())
-                o16 = self._buf("in_ops16", src16.numel(), src16.dtype)
+                o16 = self._buf("in_ops16" if wide else "in_ops8", src16.numel(), src16.dtype)
                 o16[: src16.numel()].copy_(src16, non_blocking=True)
-                self.h2d_bytes += src16.numel() * 2
+                self.h2d_bytes += src16.numel() * src16.element_size()
                 ei = put("in_exc_idx", batch["exc_idx"]) if len(batch["exc_idx"]) else None
                 put("in_exc_val", batch["exc_val"]) if len(batch["exc_val"]) else None
-                expand = (o16, 0 if ei is None else ei.numel(), self._buf("in_ops", n_ops, torch.int32))
+                expand = (o16, 0 if ei is None else ei.numel(), self._buf("in_ops", n_ops, torch.int32), wide)
             else:
                 put("in_ops", batch["ops"])
             for k in ("op_off", "pos", "mapq", "qlen"):
@@ -143,9 +144,10 @@ class ChromShard:
         self._pending = None
         done.synchronize()
         if expand is not None:
-            o16, n_exc, ops = expand
-            self._chk(self.lib.vsv_expand_ops16(self.h, _dp(o16), self.n_ops, _dp(self.d["in_exc_idx"]) if n_exc else None,
-                                                _dp(self.d["in_exc_val"]) if n_exc else None, n_exc, _dp(ops)))
+            o16, n_exc, ops, wide = expand
+            fn = self.lib.vsv_expand_ops16 if wide else self.lib.vsv_expand_ops8
+            self._chk(fn(self.h, _dp(o16), self.n_ops, _dp(self.d["in_exc_idx"]) if n_exc else None,
+                    _dp(self.d["in_exc_val"]) if n_exc else None, n_exc, _dp(ops)))
             self.ctx.sync()
 
     def _chk(self, rc):
