@@ -104,10 +104,14 @@ int vsv_scan_cigar(vsv_ctx* ctx, int mode, int min_len, int min_mapq, const uint
  * host side of the format is volcanosv_b200.lib.pack_ops16. */
 int vsv_expand_ops16(vsv_ctx* ctx, const uint16_t* ops16, int64_t n_ops, const int64_t* exc_idx,
                      const uint32_t* exc_val, int64_t n_exc, uint32_t* ops_out);
-/* Denser staging for noisy long reads (ONT/CLR: ~99 % of the ops are M/I/D shorter than 63 bases):
- * ops8[i] = len << 2 | op for op in {M,I,D} and len <= 62, else 0xFF with the full word in the
- * exception list.  1 byte per op over PCIe (+ 12 bytes per exception).  Host side:
+/* Denser staging for noisy long reads (ONT/CLR: ~99.9 % of the ops are short M/I/D runs):
+ * one byte per op, the 254 codes split by op type: 0..159 = M of 1..160 bases, 160..206 = I of
+ * 1..47, 207..253 = D of 1..47; 0xFF = the full word is in the exception list (S/H/N/P/=/X,
+ * longer or empty ops).  1 byte per op over PCIe (+ 12 bytes per exception).  Host side:
  * volcanosv_b200.lib.pack_ops8, or vsv_bam_chrom_fill straight from the BAM records. */
+#define VSV_OPS8_M 160
+#define VSV_OPS8_I 47
+#define VSV_OPS8_D 47
 int vsv_expand_ops8(vsv_ctx* ctx, const uint8_t* ops8, int64_t n_ops, const int64_t* exc_idx,
                     const uint32_t* exc_val, int64_t n_exc, uint32_t* ops_out);
 

@@ -79,20 +79,21 @@ def test_cli_mirrors_every_reference_operator():
 
 
 def test_pack_ops8_layout():
-    """ops8: len << 2 | op for M/I/D up to 62 bases, 0xFF + exception otherwise; inverse on the host."""
+    """ops8: one byte per short M/I/D run, 0xFF + exception otherwise; inverse on the host."""
     import numpy as np
-    from volcanosv_b200.lib import pack_ops8
+    from volcanosv_b200.lib import pack_ops8, unpack_ops8
     rng = np.random.default_rng(9)
     n = 5000
     code = rng.choice([0, 1, 2, 4, 5, 7, 8], n, p=[.5, .2, .2, .04, .02, .02, .02]).astype(np.uint32)
-    ln = rng.integers(0, 80, n).astype(np.uint32)
+    ln = rng.integers(0, 200, n).astype(np.uint32)
     ln[::97] = rng.integers(4095, 1 << 27, len(ln[::97]))
     ops = (ln << 4) | code
     o8, ei, ev = pack_ops8(ops)
     assert o8.dtype == np.uint8 and o8.ctypes.data % 16 == 0
-    big = (code > 2) | (ln > 62)
+    cap = np.array([160, 47, 47] + [0] * 13)[code]
+    big = (ln < 1) | (ln > cap)
     assert np.array_equal(ei, np.flatnonzero(big)) and np.array_equal(ev, ops[big])
     assert np.all(o8[big] == 0xFF) and not np.any(o8[~big] == 0xFF)
-    back = ((o8.astype(np.uint32) >> 2) << 4) | (o8 & 3)
-    back[ei] = ev
-    assert np.array_equal(back, ops)
+    assert o8[(code == 0) & (ln == 1)].tolist() == [0] * int(((code == 0) & (ln == 1)).sum())
+    assert np.all(o8[(code == 2) & (ln == 47)] == 253)
+    assert np.array_equal(unpack_ops8(o8, ei, ev), ops)

@@ -39,10 +39,8 @@ def check(bam, sam, compact):
         d = bf.chrom(chrom, compact=compact)
         ops = d["ops"] if not compact else None
         if compact == 8:
-            o8 = d["ops8"].astype(np.uint32)
-            ops = ((o8 >> 2) << 4) | (o8 & 3)
             assert np.all(np.diff(d["exc_idx"]) > 0) and np.all(d["ops8"][d["exc_idx"]] == 0xFF)
-            ops[d["exc_idx"]] = d["exc_val"]
+            ops = L.unpack_ops8(d["ops8"], d["exc_idx"], d["exc_val"])
         elif compact:
             ops = d["ops16"].astype(np.uint32)
             assert np.all(np.diff(d["exc_idx"]) > 0)

@@ -275,7 +275,7 @@ def test_expand_ops8(ctx):
     rng = np.random.default_rng(21)
     for n in (0, 1, 15, 16, 17, 100003):
         code = rng.choice([0, 1, 2, 3, 4, 5, 8, 12], n).astype(np.uint32) if n else np.zeros(0, np.uint32)
-        ln = rng.integers(0, 70, n).astype(np.uint32)
+        ln = rng.integers(0, 200, n).astype(np.uint32)
         if n > 50:
             ln[rng.integers(0, n, max(1, n // 50))] = rng.integers(4095, 1 << 27, max(1, n // 50))
         ops = (ln << 4) | code

@@ -374,9 +374,12 @@ extern "C" int vsv_bam_chrom_fill(vsv_bam* b, int tid, int32_t* pos, uint8_t* ma
         for (uint32_t k = 0; k < v.n_cigar; ++k) {
           uint32_t w;
           memcpy(&w, v.cigar + k, 4);
-          if ((w & 15u) <= 2u && (w >> 4) <= 62u) {
-            ops8[o + k] = (uint8_t)(((w >> 4) << 2) | (w & 3u));
-          } else {  // not M/I/D or 63+ bases: marker + (index, full word) in the exception list (vsv_expand_ops8)
+          const uint32_t code = w & 15u, len = w >> 4;
+          static const uint32_t cnt[3] = {VSV_OPS8_M, VSV_OPS8_I, VSV_OPS8_D};
+          static const uint32_t base[3] = {0, VSV_OPS8_M, VSV_OPS8_M + VSV_OPS8_I};
+          if (code <= 2u && len >= 1u && len <= cnt[code]) {
+            ops8[o + k] = (uint8_t)(base[code] + len - 1u);
+          } else {  // not a short M/I/D run: marker + (index, full word) in the exception list (vsv_expand_ops8)
             ops8[o + k] = 0xFFu;
             const long long s = exc_n.fetch_add(1);
             if (s < exc_cap) { exc_idx[s] = o + k; exc_val[s] = w; }

@@ -756,8 +756,15 @@ __global__ void k_patch_ops(const int64_t* __restrict__ idx, const uint32_t* __r
   if (i < n_exc && idx[i] >= 0 && idx[i] < n) out[idx[i]] = val[i];
 }
 
-// ops8: one byte per op = len << 2 | code for M/I/D (codes 0..2) with len <= 62; 0xFF marks an op
-// whose full word is in the exception list.  16 ops per thread: one LDG.128 in, four STG.128 out.
+// ops8: one byte per op.  The 254 codes are split by how long each op type runs in noisy long reads:
+// 0..159 = M of 1..160 bases, 160..206 = I of 1..47, 207..253 = D of 1..47; 0xFF marks an op whose full
+// word is in the exception list (anything else: S/H/N/P/=/X, longer or empty ops).  16 ops per thread:
+// one LDG.128 in, four STG.128 out.
+__device__ __forceinline__ uint32_t ops8_word(uint32_t b) {
+  const uint32_t code = (b >= VSV_OPS8_M ? 1u : 0u) + (b >= VSV_OPS8_M + VSV_OPS8_I ? 1u : 0u);
+  const uint32_t base = code == 0u ? 0u : (code == 1u ? (uint32_t)VSV_OPS8_M : (uint32_t)(VSV_OPS8_M + VSV_OPS8_I));
+  return ((b - base + 1u) << 4) | code;
+}
 __global__ void __launch_bounds__(256) k_expand_ops8(const uint8_t* __restrict__ in, int64_t n, uint32_t* __restrict__ out) {
   const int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 16;
   if (i + 16 <= n) {
@@ -766,13 +773,12 @@ __global__ void __launch_bounds__(256) k_expand_ops8(const uint8_t* __restrict__
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
       uint4 o;
-      const uint32_t b0 = w[k] & 0xFFu, b1 = (w[k] >> 8) & 0xFFu, b2 = (w[k] >> 16) & 0xFFu, b3 = w[k] >> 24;
-      o.x = ((b0 >> 2) << 4) | (b0 & 3u); o.y = ((b1 >> 2) << 4) | (b1 & 3u);
-      o.z = ((b2 >> 2) << 4) | (b2 & 3u); o.w = ((b3 >> 2) << 4) | (b3 & 3u);
+      o.x = ops8_word(w[k] & 0xFFu); o.y = ops8_word((w[k] >> 8) & 0xFFu);
+      o.z = ops8_word((w[k] >> 16) & 0xFFu); o.w = ops8_word(w[k] >> 24);
       reinterpret_cast<uint4*>(out + i)[k] = o;
     }
   } else {
-    for (int64_t k = i; k < n; ++k) out[k] = (((uint32_t)in[k] >> 2) << 4) | (in[k] & 3u);
+    for (int64_t k = i; k < n; ++k) out[k] = ops8_word(in[k]);
   }
 }
 

@@ -460,17 +460,33 @@ def pack_ops16(ops):
     return o16, exc_idx, exc_val
 
 
+OPS8_M, OPS8_I, OPS8_D = 160, 47, 47      # include/volcanosv_b200.h: VSV_OPS8_*
+
+
 def pack_ops8(ops):
-    """Host packer of vsv_expand_ops8: (ops8, exc_idx, exc_val).  One byte per M/I/D op of <= 62 bases."""
+    """Host packer of vsv_expand_ops8: (ops8, exc_idx, exc_val).  One byte per short M/I/D run
+    (M 1..160 -> 0..159, I 1..47 -> 160..206, D 1..47 -> 207..253), 0xFF + exception otherwise."""
     ops = np.ascontiguousarray(ops, dtype=np.uint32)
     code, ln = ops & np.uint32(15), ops >> np.uint32(4)
-    big = (code > 2) | (ln > 62)
+    cnt = np.array([OPS8_M, OPS8_I, OPS8_D] + [0] * 13, np.uint32)
+    base = np.array([0, OPS8_M, OPS8_M + OPS8_I] + [0] * 13, np.uint32)
+    big = (ln < 1) | (ln > cnt[code])
     o8 = _aligned_empty(len(ops), np.uint8)
-    np.copyto(o8, (ln << np.uint32(2)) | code, casting="unsafe")
+    np.copyto(o8, base[code] + ln - np.uint32(1), casting="unsafe")
     exc_idx = np.flatnonzero(big).astype(np.int64)
     exc_val = ops[exc_idx].copy()
     o8[exc_idx] = 0xFF
     return o8, exc_idx, exc_val
+
+
+def unpack_ops8(o8, exc_idx, exc_val):
+    """Inverse of pack_ops8 on the host (tests, debugging)."""
+    b = np.asarray(o8).astype(np.uint32)
+    code = (b >= OPS8_M).astype(np.uint32) + (b >= OPS8_M + OPS8_I).astype(np.uint32)
+    base = np.array([0, OPS8_M, OPS8_M + OPS8_I], np.uint32)
+    out = ((b - base[code] + 1) << 4) | code
+    out[exc_idx] = exc_val
+    return out
 
 
 def _aligned_empty(n, dtype, align=64):
