@@ -99,3 +99,20 @@ def test_otherasm_entry_point(work):
     for rel in os.listdir(exp):
         got = open(os.path.join(out, rel)).read().replace(work, "$WORK")
         assert got == open(os.path.join(exp, rel)).read(), rel
+
+
+def test_whole_genome_mode_from_bam(work):
+    """Same run with BAM inputs (22 references in one reads BAM, per-chromosome contig BAMs) through the
+    native feeder: same bytes as from SAM text."""
+    sys.path.insert(0, HERE)
+    import bamio
+    from volcanosv_b200 import cli
+    bamio.sam_to_bam(os.path.join(work, "reads.sam"), os.path.join(work, "reads.bam"), block=40000)
+    for c in range(1, 23):
+        bamio.sam_to_bam(os.path.join(work, "contigs_chr%d.sam" % c), os.path.join(work, "contigs_chr%d.bam" % c))
+    out = os.path.join(work, "out_bam")
+    a = argv(work, out)
+    a[a.index("-bam") + 1] = os.path.join(work, "reads.bam")
+    a[a.index("-cbam") + 1] = os.path.join(work, "contigs_chr{chr}.bam")
+    cli.main(a)
+    check(out, work)
