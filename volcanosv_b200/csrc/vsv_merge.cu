@@ -4,96 +4,125 @@
 // ================================================================================
 // K2: per-record merge.  cluster_ins_one_read / cluster_del_one_read (ECS_H:87-164),
 // generate_combine_sigs (SE:373-435).  Signatures are sparse (<= a few per record), so
-// this is one thread per record run walking its (already ordered) signatures; two
-// passes (count, exclusive scan, write) keep the output order deterministic.
+// this is one thread per record run walking its (already ordered) signatures, both types in
+// one walk with a state per type; two passes (count, exclusive scan, write) keep the output
+// order deterministic.
 // ================================================================================
-__global__ void k_type_flags(const vsv_sig* __restrict__ s, int64_t n, int32_t* __restrict__ is_del) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) is_del[i] = s[i].type == VSV_DEL ? 1 : 0;
-}
+#include <cub/device/device_scan.cuh>
 
-__global__ void k_type_split(const vsv_sig* __restrict__ s, int64_t n, const int64_t* __restrict__ del_excl,
-                             vsv_sig* __restrict__ dels, vsv_sig* __restrict__ inss) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  vsv_sig v = s[i];
-  int64_t d = del_excl[i];
-  if (v.type == VSV_DEL) dels[d] = v; else inss[i - d] = v;
-}
+// State of one type's merge inside a record (the reference keeps one list per type, so DEL merging
+// never sees the INS signatures in between and vice versa).
+struct MState {
+  vsv_sig cur;
+  int32_t mark;  // cute: last INS pos / DEL end
+  bool open;
+};
 
-// Walk one record's run [i0,i1) of same-type signatures; calls f(merged) per output.
+// Feeds the next same-type signature `n` (index `idx` in the type's own list); calls f(merged)
+// whenever a merged signature is complete.
 template <typename F>
-__device__ __forceinline__ void merge_walk(const vsv_sig* __restrict__ s, int64_t i0, int64_t i1, int mode,
-                                           int type, F f) {
-  vsv_sig cur = s[i0];
-  cur.first = (int32_t)i0;
-  cur.count = 1;
-  if (mode == VSV_MODE_READS) {
-    f(cur);
-    for (int64_t k = i0 + 1; k < i1; ++k) {
-      cur = s[k]; cur.first = (int32_t)k; cur.count = 1;
-      f(cur);
-    }
+__device__ __forceinline__ void mstate_push(MState& st, const vsv_sig& n, int32_t idx, int mode, int type, F f) {
+  vsv_sig& cur = st.cur;
+  if (!st.open) {
+    cur = n; cur.first = idx; cur.count = 1;
+    st.mark = (type == VSV_INS) ? n.pos : n.pos + n.len;
+    st.open = true;
     return;
   }
-  int32_t mark = (type == VSV_INS) ? cur.pos : cur.pos + cur.len;  // cute: last INS pos / DEL end
-  for (int64_t k = i0 + 1; k < i1; ++k) {
-    const vsv_sig n = s[k];
-    bool hit;
-    if (mode == VSV_MODE_CONTIG) {
-      int32_t d = abs(n.pos - cur.pos);
-      if (type == VSV_INS) {
-        hit = (cur.len > 250 && n.len > 250 && d < 250) || (cur.len > 320 && n.len > 320 && d < 380) ||
-              (cur.len > 100 && n.len > 100 && d < 250);           // ECS_H:112-135
-        if (hit) { cur.q1 = n.q1; cur.len = cur.q1 - cur.q0; }     // ECS_H:91-97
-      } else {
-        hit = cur.len > 150 && n.len > 150 && d < 150;             // ECS_H:148-150
-        if (hit) { cur.len = n.pos + n.len - cur.pos; cur.q1 = cur.q0 + 1; }  // ECS_H:99-106
-      }
-    } else {  // VSV_MODE_CUTE
-      if (type == VSV_INS) {
-        hit = n.pos - mark <= 100;                                 // SE:396-399
-        if (hit) { cur.len += n.len; mark = n.pos; }
-      } else {
-        hit = n.pos - mark <= 0;                                   // SE:420
-        if (hit) { cur.len += n.len; mark = n.pos + n.len; }
-      }
-    }
-    if (hit) {
-      cur.count++;
+  bool hit = false;
+  if (mode == VSV_MODE_CONTIG) {
+    const int32_t d = abs(n.pos - cur.pos);
+    if (type == VSV_INS) {
+      hit = (cur.len > 250 && n.len > 250 && d < 250) || (cur.len > 320 && n.len > 320 && d < 380) ||
+            (cur.len > 100 && n.len > 100 && d < 250);           // ECS_H:112-135
+      if (hit) { cur.q1 = n.q1; cur.len = cur.q1 - cur.q0; }     // ECS_H:91-97
     } else {
-      f(cur);
-      cur = n; cur.first = (int32_t)k; cur.count = 1;
-      mark = n.pos;                                                // SE:412-413 / SE:429-430 (end := start quirk)
+      hit = cur.len > 150 && n.len > 150 && d < 150;             // ECS_H:148-150
+      if (hit) { cur.len = n.pos + n.len - cur.pos; cur.q1 = cur.q0 + 1; }  // ECS_H:99-106
     }
+  } else if (mode == VSV_MODE_CUTE) {
+    if (type == VSV_INS) {
+      hit = n.pos - st.mark <= 100;                              // SE:396-399
+      if (hit) { cur.len += n.len; st.mark = n.pos; }
+    } else {
+      hit = n.pos - st.mark <= 0;                                // SE:420
+      if (hit) { cur.len += n.len; st.mark = n.pos + n.len; }
+    }
+  }                                                              // VSV_MODE_READS: never merged
+  if (hit) {
+    cur.count++;
+  } else {
+    f(cur);
+    cur = n; cur.first = idx; cur.count = 1;
+    st.mark = n.pos;                                             // SE:412-413 / SE:429-430 (end := start quirk)
   }
-  f(cur);
 }
 
-__global__ void k_merge_count(const vsv_sig* __restrict__ s, int64_t n, int mode, int type,
-                              int32_t* __restrict__ cnt) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+// Walks one record's run [i0,i1) of signatures (op order, both types interleaved) with one state per
+// type.  in_del / in_ins: how many DEL / INS signatures precede the run (the `first` indices count
+// inside each type's own list).  fd / fi receive the merged DEL / INS signatures in order.
+template <typename FD, typename FI>
+__device__ __forceinline__ void merge_walk2(const vsv_sig* __restrict__ s, int64_t i0, int64_t i1, int mode, int32_t in_del,
+                                            int32_t in_ins, FD fd, FI fi) {
+  MState sd, si;
+  sd.open = si.open = false;
+  for (int64_t k = i0; k < i1; ++k) {
+    const int4 a = reinterpret_cast<const int4*>(s + k)[0], b = reinterpret_cast<const int4*>(s + k)[1];
+    vsv_sig n;
+    n.rec = a.x; n.type = a.y; n.pos = a.z; n.len = a.w; n.q0 = b.x; n.q1 = b.y; n.first = b.z; n.count = b.w;
+    if (n.type == VSV_DEL) mstate_push(sd, n, in_del++, mode, VSV_DEL, fd);
+    else mstate_push(si, n, in_ins++, mode, VSV_INS, fi);
+  }
+  if (sd.open) fd(sd.cur);
+  if (si.open) fi(si.cur);
+}
+
+struct SumU4 {
+  __host__ __device__ uint4 operator()(const uint4& a, const uint4& b) const {
+    return make_uint4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
+  }
+};
+
+// per record-run head: (DEL in, INS in, DEL out, INS out); zeros elsewhere
+__global__ void k_merge2_count(const vsv_sig* __restrict__ s, int64_t n, int mode, uint4* __restrict__ cnt) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  int32_t c = 0;
-  if (i == 0 || s[i - 1].rec != s[i].rec) {
+  uint4 c = make_uint4(0u, 0u, 0u, 0u);
+  const int32_t r = s[i].rec;
+  if (i == 0 || s[i - 1].rec != r) {
     int64_t e = i + 1;
-    const int32_t r = s[i].rec;
     while (e < n && s[e].rec == r) ++e;
-    merge_walk(s, i, e, mode, type, [&](const vsv_sig&) { ++c; });
+    for (int64_t k = i; k < e; ++k) {
+      if (s[k].type == VSV_DEL) ++c.x; else ++c.y;
+    }
+    merge_walk2(s, i, e, mode, 0, 0, [&](const vsv_sig&) { ++c.z; }, [&](const vsv_sig&) { ++c.w; });
   }
   cnt[i] = c;
 }
 
-__global__ void k_merge_write(const vsv_sig* __restrict__ s, int64_t n, int mode, int type,
-                              const int64_t* __restrict__ excl, vsv_sig* __restrict__ out) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+__global__ void k_merge2_write(const vsv_sig* __restrict__ s, int64_t n, int mode, const uint4* __restrict__ excl,
+                               vsv_sig* __restrict__ out_del, vsv_sig* __restrict__ out_ins) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  if (i == 0 || s[i - 1].rec != s[i].rec) {
+  const int32_t r = s[i].rec;
+  if (i == 0 || s[i - 1].rec != r) {
     int64_t e = i + 1;
-    const int32_t r = s[i].rec;
     while (e < n && s[e].rec == r) ++e;
-    int64_t o = excl[i];
-    merge_walk(s, i, e, mode, type, [&](const vsv_sig& v) { out[o++] = v; });
+    const uint4 b = excl[i];
+    int64_t od = b.z, oi = b.w;
+    auto put = [](vsv_sig* dst, const vsv_sig& v) {
+      reinterpret_cast<int4*>(dst)[0] = make_int4(v.rec, v.type, v.pos, v.len);
+      reinterpret_cast<int4*>(dst)[1] = make_int4(v.q0, v.q1, v.first, v.count);
+    };
+    merge_walk2(s, i, e, mode, (int32_t)b.x, (int32_t)b.y, [&](const vsv_sig& v) { put(out_del + od++, v); },
+                [&](const vsv_sig& v) { put(out_ins + oi++, v); });
+  }
+}
+
+__global__ void k_merge2_total(const uint4* __restrict__ cnt, const uint4* __restrict__ excl, int64_t n, int64_t* __restrict__ tot) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) {
+    tot[0] = (int64_t)excl[n - 1].z + cnt[n - 1].z;
+    tot[1] = (int64_t)excl[n - 1].w + cnt[n - 1].w;
   }
 }
 
@@ -106,40 +135,34 @@ extern "C" int vsv_merge_in_record(vsv_ctx* ctx, int mode, const vsv_sig* sigs, 
   if (n == 0) return VSV_OK;
   const vsv_sig* d_in = nullptr;
   VSV_TRY(vsv_in(ctx, sigs, (size_t)n, &d_in));
-  vsv_sig *d_od = nullptr, *d_oi = nullptr, *t_del = nullptr, *t_ins = nullptr;
+  vsv_sig *d_od = nullptr, *d_oi = nullptr;
   VSV_TRY(vsv_out(ctx, out_del, (size_t)n, &d_od));
   VSV_TRY(vsv_out(ctx, out_ins, (size_t)n, &d_oi));
-  VSV_TRY(vsv_tmp(ctx, (size_t)n, &t_del));
-  VSV_TRY(vsv_tmp(ctx, (size_t)n, &t_ins));
-  int32_t* flags = nullptr;
-  int64_t *excl = nullptr, *tot = nullptr;
-  VSV_TRY(vsv_tmp(ctx, (size_t)n, &flags));
+  uint4 *cnt = nullptr, *excl = nullptr;
+  int64_t* tot = nullptr;
+  VSV_TRY(vsv_tmp(ctx, (size_t)n, &cnt));
   VSV_TRY(vsv_tmp(ctx, (size_t)n, &excl));
-  VSV_TRY(vsv_tmp(ctx, 3, &tot));
-  const unsigned g = (unsigned)vsv_cdiv(n, 256);
+  VSV_TRY(vsv_tmp(ctx, 2, &tot));
+  const unsigned g = (unsigned)vsv_cdiv(n, 128);
   VSV_TRY(vsv_t0(ctx));
-  VSV_LAUNCH(ctx, k_type_flags, g, 256, 0, d_in, n, flags);
-  VSV_TRY(vsv_exclusive_scan_i32(ctx, flags, n, excl, tot));
-  VSV_LAUNCH(ctx, k_type_split, g, 256, 0, d_in, n, excl, t_del, t_ins);
-  int64_t h_tot[3] = {0, 0, 0};
-  VSV_CUDA(ctx, cudaMemcpyAsync(h_tot, tot, sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
-  VSV_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-  const int64_t nd = h_tot[0], ni = n - h_tot[0];
-  for (int type = 0; type < 2; ++type) {
-    const int64_t m = type == VSV_DEL ? nd : ni;
-    if (m == 0) continue;
-    const vsv_sig* src = type == VSV_DEL ? t_del : t_ins;
-    vsv_sig* dst = type == VSV_DEL ? d_od : d_oi;
-    const unsigned gm = (unsigned)vsv_cdiv(m, 128);
-    VSV_LAUNCH(ctx, k_merge_count, gm, 128, 0, src, m, mode, type, flags);
-    VSV_TRY(vsv_exclusive_scan_i32(ctx, flags, m, excl, tot + 1 + type));
-    VSV_LAUNCH(ctx, k_merge_write, gm, 128, 0, src, m, mode, type, excl, dst);
+  // one pass per record run with a state per type: count, one 4-lane exclusive scan, write
+  VSV_LAUNCH(ctx, k_merge2_count, g, 128, 0, d_in, n, mode, cnt);
+  {
+    size_t tb = 0;
+    VSV_CUDA(ctx, cub::DeviceScan::ExclusiveScan(nullptr, tb, cnt, excl, SumU4(), make_uint4(0u, 0u, 0u, 0u), n, ctx->stream));
+    void* tmp = nullptr;
+    VSV_TRY(vsv_arena_alloc(ctx, tb, &tmp));
+    VSV_CUDA(ctx, cub::DeviceScan::ExclusiveScan(tmp, tb, cnt, excl, SumU4(), make_uint4(0u, 0u, 0u, 0u), n, ctx->stream));
+    ctx->launches += 2;
   }
+  VSV_LAUNCH(ctx, k_merge2_write, g, 128, 0, d_in, n, mode, (const uint4*)excl, d_od, d_oi);
+  VSV_LAUNCH(ctx, k_merge2_total, 1, 32, 0, (const uint4*)cnt, (const uint4*)excl, n, tot);
   VSV_TRY(vsv_t1(ctx));
-  VSV_CUDA(ctx, cudaMemcpyAsync(h_tot + 1, tot + 1, 2 * sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
+  int64_t h_tot[2] = {0, 0};
+  VSV_CUDA(ctx, cudaMemcpyAsync(h_tot, tot, 2 * sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
   VSV_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-  *n_del = nd ? h_tot[1] : 0;
-  *n_ins = ni ? h_tot[2] : 0;
+  *n_del = h_tot[0];
+  *n_ins = h_tot[1];
   VSV_TRY(vsv_out_done(ctx, out_del, d_od, (size_t)*n_del));
   VSV_TRY(vsv_out_done(ctx, out_ins, d_oi, (size_t)*n_ins));
   return vsv_end(ctx);
