@@ -249,11 +249,15 @@ int vsv_edit_distance_batch(vsv_ctx* ctx, const uint8_t* chars, const int64_t* s
 /* Replaces `pysam.AlignmentFile(path).fetch(chr)` and the per-record attribute reads of the
  * whole-chromosome scans (LI/extract_reads_signature.py:107-145, LI/sig_extract.py:514-560,
  * LI/extract_contig_signature_Hifi.py:386-419): BGZF inflate (blocks in parallel) + BAM record
- * -> the packed columns of this header.  The whole file is inflated into memory at open.
- * Unmapped records (refID < 0) are skipped, CG:B,I long CIGARs are resolved.  Errors:
- * VSV_E_ARG + vsv_bam_last_error() (thread-local message). */
+ * -> the packed columns of this header.  The file is streamed in 32 MB windows (blocks of a
+ * window inflate in parallel); what stays in memory are the kept records without their qualities.
+ * vsv_bam_open keeps every mapped record; vsv_bam_open_ref keeps one reference ("" = header only),
+ * seeks to it through <path>.bai / <path minus .bam>.bai when present and stops after it in a
+ * coordinate-sorted file.  Unmapped records (refID < 0) are skipped, CG:B,I long CIGARs are
+ * resolved.  Errors: VSV_E_ARG + vsv_bam_last_error() (thread-local message). */
 typedef struct vsv_bam vsv_bam;
 int vsv_bam_open(const char* path, int n_threads, vsv_bam** out);
+int vsv_bam_open_ref(const char* path, const char* ref_name, int n_threads, vsv_bam** out);
 void vsv_bam_close(vsv_bam* b);
 const char* vsv_bam_last_error(void);
 int vsv_bam_n_ref(const vsv_bam* b);

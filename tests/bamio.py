@@ -42,9 +42,11 @@ def _aux(tag: str) -> bytes:
     return k.encode() + b"Z" + v.encode() + b"\0"
 
 
-def sam_to_bam(sam_path: str, bam_path: str, block: int = 60000, extra_tags=("NM:i:3", "ms:B:s,1,-2,3")):
+def sam_to_bam(sam_path: str, bam_path: str, block: int = 60000, extra_tags=("NM:i:3", "ms:B:s,1,-2,3"), bai: bool = False):
     """Every mapped/unmapped record of the SAM file, in file order; `extra_tags` are added in front of
-    the record's own tags so the reader has to walk past other aux types."""
+    the record's own tags so the reader has to walk past other aux types.  bai=True also writes
+    <bam_path>.bai (per reference: its records as one chunk in bin 0 plus the metadata pseudo-bin; no
+    linear index entries) - enough for readers that seek to the start of a reference."""
     op = gzip.open if sam_path.endswith(".gz") else open
     refs, text, recs = [], [], []
     with op(sam_path, "rt") as fh:
@@ -62,8 +64,10 @@ def sam_to_bam(sam_path: str, bam_path: str, block: int = 60000, extra_tags=("NM
     out += struct.pack("<I", len(t)) + t + struct.pack("<I", len(refs))
     for n, ln in refs:
         out += struct.pack("<I", len(n) + 1) + n.encode() + b"\0" + struct.pack("<I", ln)
+    rec_off = []                                   # (refID, offset of the record in the uncompressed stream)
     for f in recs:
         name, flag, rname, pos, mapq, cig, seq = f[0], int(f[1]), f[2], int(f[3]) - 1, int(f[4]), f[5], f[9]
+        rec_off.append((rid.get(rname, -1), len(out)))
         cigar = [(int(n) << 4) | _OPC[c] for n, c in re.findall(r"(\d+)([MIDNSHP=X])", cig)] if cig != "*" else []
         ref_len = sum(w >> 4 for w in cigar if (w & 15) in (0, 2, 3, 7, 8))
         l_seq = 0 if seq == "*" else len(seq)
@@ -78,7 +82,27 @@ def sam_to_bam(sam_path: str, bam_path: str, block: int = 60000, extra_tags=("NM
                            len(cigar), flag, l_seq, -1, -1, 0)
         body += name.encode() + b"\0" + struct.pack("<%dI" % len(cigar), *cigar) + bytes(sq) + b"\xff" * l_seq + aux
         out += struct.pack("<I", len(body)) + body
+    coff = []                                      # compressed offset of every block
     with open(bam_path, "wb") as fo:
         for i in range(0, len(out), block):
+            coff.append(fo.tell())
             fo.write(_bgzf_block(bytes(out[i:i + block])))
+        coff.append(fo.tell())
         fo.write(_bgzf_block(b""))
+    if bai:
+        def voff(u):
+            return (coff[u // block] << 16) | (u % block)
+        with open(bam_path + ".bai", "wb") as fo:
+            fo.write(b"BAI\1" + struct.pack("<i", len(refs)))
+            for r in range(len(refs)):
+                mine = [u for t, u in rec_off if t == r]
+                if not mine:
+                    fo.write(struct.pack("<ii", 0, 0))
+                    continue
+                nxt = [u for t, u in rec_off if u > mine[-1]]
+                end = voff(nxt[0]) if nxt else voff(len(out) - 1) + 1
+                fo.write(struct.pack("<i", 2))
+                fo.write(struct.pack("<IiQQ", 0, 1, voff(mine[0]), end))
+                fo.write(struct.pack("<IiQQQQ", 37450, 2, 1, 2, len(mine), 0))   # pseudo-bin: offsets there are not chunk starts
+                fo.write(struct.pack("<i", 0))
+            fo.write(struct.pack("<Q", sum(1 for t, _ in rec_off if t < 0)))

@@ -133,3 +133,34 @@ def test_alignment_source_bam_equals_sam(tmp_path):
         assert A.n == B.n and A.qname == B.qname and A.sa == B.sa
         assert all(A.seq[i] == B.seq[i] for i in range(0, A.n, 5))
         assert b.records("chrNone").n == 0
+
+
+def _columns(bf, chrom):
+    d = bf.chrom(chrom)
+    return {k: (bytes(v) if v.dtype == np.uint8 and k in ("names", "seq", "sa") else v.tolist()) for k, v in d.items()}
+
+
+@pytest.mark.parametrize("window", [None, "700", "70000"])
+def test_open_one_reference_streaming(tmp_path, monkeypatch, window):
+    """vsv_bam_open_ref: one reference of a 22-reference BAM == the same reference of the full load; with the
+    .bai (seek), without it (scan + stop after the reference), and with read windows far smaller than a
+    BGZF block / a record (VSV_BAM_WINDOW), so records and blocks straddle window edges."""
+    if window:
+        monkeypatch.setenv("VSV_BAM_WINDOW", window)
+    wgs = os.path.join(HERE, "golden", "e2e_wgs", "input")
+    bam = str(tmp_path / "reads.bam")
+    bamio.sam_to_bam(os.path.join(wgs, "reads.sam.gz"), bam, block=30000, bai=True)
+    full = L.BamFile(bam, n_threads=2)
+    assert len(full.refs) == 22
+    for chrom in ("chr1", "chr10", "chr22"):
+        one = L.BamFile(bam, n_threads=2, ref=chrom)
+        assert [(n, ln) for n, ln, _ in one.refs] == [(n, ln) for n, ln, _ in full.refs]
+        assert [n for _, _, n in one.refs if n] == [dict((a, c) for a, _, c in full.refs)[chrom]]
+        assert _columns(one, chrom) == _columns(full, chrom)
+    os.remove(bam + ".bai")
+    one = L.BamFile(bam, ref="chr7")
+    assert _columns(one, "chr7") == _columns(full, "chr7")
+    hdr = L.BamFile(bam, ref="")
+    assert len(hdr.refs) == 22 and all(n == 0 for _, _, n in hdr.refs)
+    with pytest.raises(L.VsvError):
+        L.BamFile(bam, ref="chrUn")

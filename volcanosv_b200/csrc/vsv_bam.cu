@@ -11,12 +11,14 @@
 // l_seq, next_refID, next_pos, tlen, read_name, cigar (u32 = len<<4|op: the layout the kernels
 // use), seq (4 bit), qual, aux.  CIGARs with more than 65535 ops live in a CG:B,I aux array behind
 // a <l_seq>S<ref_len>N placeholder.
+#include <sys/types.h>
 #include <zlib.h>
 
 #include <algorithm>
 #include <atomic>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <thread>
@@ -79,7 +81,8 @@ struct RecView {
   const uint8_t* end;
 };
 
-bool view(const uint8_t* body, uint32_t size, RecView* v) {
+// `has_qual`: records as they are in the file; the kept copies (vsv_bam::data) drop the qualities
+bool view(const uint8_t* body, uint32_t size, RecView* v, bool has_qual = false) {
   if (size < 32) return false;
   v->body = body;
   v->end = body + size;
@@ -97,7 +100,7 @@ bool view(const uint8_t* body, uint32_t size, RecView* v) {
   v->cigar = reinterpret_cast<const uint32_t*>(p);
   p += 4 * (size_t)v->n_cigar;
   v->seq = p;
-  p += ((size_t)v->l_seq + 1) / 2 + (size_t)v->l_seq;
+  p += ((size_t)v->l_seq + 1) / 2 + (has_qual ? (size_t)v->l_seq : 0);
   if (p > v->end) return false;
   v->aux = p;
   // long CIGAR: <l_seq>S<n>N placeholder + CG:B,I
@@ -151,7 +154,7 @@ void parallel_for(int64_t n, int n_threads, F f) {
 }  // namespace
 
 struct vsv_bam {
-  std::vector<uint8_t> data;   // inflated stream
+  std::vector<uint8_t> data;   // kept record bodies (qualities dropped), back to back
   std::vector<BamRec> recs;
   std::vector<RefInfo> refs;
   std::string header_text;
@@ -163,105 +166,265 @@ static thread_local std::string g_bam_err;
 
 extern "C" const char* vsv_bam_last_error(void) { return g_bam_err.c_str(); }
 
-#define BAM_FAIL(msg)            \
-  do {                           \
-    g_bam_err = (msg);           \
-    delete b;                    \
-    return VSV_E_ARG;            \
-  } while (0)
+namespace {
 
-extern "C" int vsv_bam_open(const char* path, int n_threads, vsv_bam** out) {
-  if (!path || !out) { g_bam_err = "vsv_bam_open: null argument"; return VSV_E_ARG; }
-  *out = nullptr;
-  vsv_bam* b = new vsv_bam();
-  b->n_threads = n_threads > 0 ? n_threads : (int)std::max(1u, std::thread::hardware_concurrency());
-  FILE* f = fopen(path, "rb");
-  if (!f) BAM_FAIL(std::string("vsv_bam_open: cannot open ") + path);
-  std::vector<uint8_t> raw;
-  {
+// Streaming BGZF reader: fill() reads the next stretch of compressed bytes, inflates the complete
+// blocks in it in parallel and appends the result; memory is bounded by the window, not the file.
+class BgzfReader {
+ public:
+  BgzfReader(FILE* f, int n_threads) : f_(f), nt_(n_threads) {}
+  void seek(uint64_t coffset) {
+    fseeko(f_, (off_t)coffset, SEEK_SET);
+    raw_.clear();
+    eof_ = false;
+  }
+  // 1 = appended something, 0 = end of file, -1 = error (err set)
+  int fill(std::vector<uint8_t>& out, size_t want, std::string& err) {
+    for (;;) {
+      if (eof_ && raw_.empty()) return 0;
+      const size_t have = raw_.size();
+      if (!eof_) {
+        raw_.resize(have + want);
+        const size_t got = fread(raw_.data() + have, 1, want, f_);
+        raw_.resize(have + got);
+        if (got < want) eof_ = true;
+      }
+      struct Blk { size_t in_off, in_len, out_off; uint32_t out_len; };
+      std::vector<Blk> blks;
+      size_t p = 0, total = 0;
+      while (p + 18 <= raw_.size()) {
+        const uint8_t* h = raw_.data() + p;
+        if (h[0] != 31 || h[1] != 139 || h[2] != 8 || !(h[3] & 4)) { err = "not a BGZF file"; return -1; }
+        const uint16_t xlen = rd16(h + 10);
+        if (p + 12 + (size_t)xlen > raw_.size()) break;
+        int bsize = -1;
+        for (size_t x = 12; x + 4 <= 12 + (size_t)xlen;) {
+          const uint16_t slen = rd16(h + x + 2);
+          if (h[x] == 'B' && h[x + 1] == 'C' && slen == 2 && x + 6 <= 12 + (size_t)xlen) bsize = rd16(h + x + 4);
+          x += 4 + slen;
+        }
+        if (bsize < 0 || (size_t)bsize + 1 < 12 + (size_t)xlen + 8) { err = "malformed BGZF block header"; return -1; }
+        const size_t blen = (size_t)bsize + 1;
+        if (p + blen > raw_.size()) break;
+        const uint32_t isize = rd32(h + blen - 4);
+        blks.push_back({p + 12 + xlen, blen - 12 - xlen - 8, total, isize});
+        total += isize;
+        p += blen;
+      }
+      if (blks.empty()) {
+        if (eof_) {
+          if (!raw_.empty()) { err = "truncated BGZF block"; return -1; }
+          return 0;
+        }
+        continue;  // a block larger than what was read so far: read more
+      }
+      const size_t base = out.size();
+      out.resize(base + total);
+      std::atomic<int> bad(0);
+      uint8_t* dst = out.data() + base;
+      const uint8_t* src = raw_.data();
+      parallel_for((int64_t)blks.size(), nt_, [&](int64_t a, int64_t e, int) {
+        z_stream zs;
+        for (int64_t i = a; i < e; ++i) {
+          if (blks[i].out_len == 0) continue;
+          memset(&zs, 0, sizeof(zs));
+          if (inflateInit2(&zs, -15) != Z_OK) { bad = 1; return; }
+          zs.next_in = const_cast<uint8_t*>(src) + blks[i].in_off;
+          zs.avail_in = (uInt)blks[i].in_len;
+          zs.next_out = dst + blks[i].out_off;
+          zs.avail_out = blks[i].out_len;
+          const int rc = inflate(&zs, Z_FINISH);
+          inflateEnd(&zs);
+          if (rc != Z_STREAM_END || zs.avail_out != 0) { bad = 1; return; }
+        }
+      });
+      if (bad) { err = "inflate failed (corrupt BGZF block)"; return -1; }
+      raw_.erase(raw_.begin(), raw_.begin() + (ptrdiff_t)p);
+      if (total == 0) continue;  // only empty blocks (the EOF marker): look further
+      return 1;
+    }
+  }
+
+ private:
+  FILE* f_;
+  int nt_;
+  std::vector<uint8_t> raw_;
+  bool eof_ = false;
+};
+
+// smallest chunk start (virtual offset) of reference `tid` in a BAI index; false if the file is
+// absent / unreadable; *has = false when the reference has no records
+bool bai_ref_start(const std::string& bam_path, int tid, uint64_t* voff, bool* has) {
+  std::vector<std::string> cand = {bam_path + ".bai"};
+  if (bam_path.size() > 4 && bam_path.compare(bam_path.size() - 4, 4, ".bam") == 0)
+    cand.push_back(bam_path.substr(0, bam_path.size() - 4) + ".bai");
+  for (const std::string& p : cand) {
+    FILE* f = fopen(p.c_str(), "rb");
+    if (!f) continue;
+    std::vector<uint8_t> d;
     fseek(f, 0, SEEK_END);
     const long sz = ftell(f);
     fseek(f, 0, SEEK_SET);
-    raw.resize(sz > 0 ? (size_t)sz : 0);
-    if (sz > 0 && fread(raw.data(), 1, (size_t)sz, f) != (size_t)sz) { fclose(f); BAM_FAIL("vsv_bam_open: short read"); }
+    d.resize(sz > 0 ? (size_t)sz : 0);
+    const bool ok = sz > 0 && fread(d.data(), 1, (size_t)sz, f) == (size_t)sz;
     fclose(f);
-  }
-  // ---- index the BGZF blocks ------------------------------------------------------------
-  struct Blk { size_t in_off, in_len, out_off; uint32_t out_len; };
-  std::vector<Blk> blks;
-  size_t p = 0, total = 0;
-  while (p + 18 <= raw.size()) {
-    const uint8_t* h = raw.data() + p;
-    if (h[0] != 31 || h[1] != 139 || h[2] != 8 || !(h[3] & 4)) BAM_FAIL("vsv_bam_open: not a BGZF file");
-    const uint16_t xlen = rd16(h + 10);
-    int bsize = -1;
-    for (size_t x = 12; x + 4 <= 12 + (size_t)xlen && p + x + 4 <= raw.size();) {
-      const uint16_t slen = rd16(h + x + 2);
-      if (h[x] == 'B' && h[x + 1] == 'C' && slen == 2) bsize = rd16(h + x + 4);
-      x += 4 + slen;
+    if (!ok || d.size() < 8 || memcmp(d.data(), "BAI\1", 4) != 0) continue;
+    size_t q = 4;
+    const int32_t n_ref = rd32s(d.data() + q);
+    q += 4;
+    bool bad = false;
+    for (int32_t r = 0; r < n_ref && !bad; ++r) {
+      if (q + 4 > d.size()) { bad = true; break; }
+      const int32_t n_bin = rd32s(d.data() + q);
+      q += 4;
+      uint64_t best = ~0ull;
+      for (int32_t k = 0; k < n_bin; ++k) {
+        if (q + 8 > d.size()) { bad = true; break; }
+        const uint32_t bin = rd32(d.data() + q);
+        const int32_t n_chunk = rd32s(d.data() + q + 4);
+        q += 8;
+        if (n_chunk < 0 || q + 16 * (size_t)n_chunk > d.size()) { bad = true; break; }
+        for (int32_t c = 0; c < n_chunk; ++c) {
+          uint64_t beg;
+          memcpy(&beg, d.data() + q + 16 * (size_t)c, 8);
+          if (bin != 37450u && beg < best) best = beg;  // 37450 = the metadata pseudo-bin
+        }
+        q += 16 * (size_t)n_chunk;
+      }
+      if (bad || q + 4 > d.size()) { bad = true; break; }
+      const int32_t n_intv = rd32s(d.data() + q);
+      q += 4;
+      if (n_intv < 0 || q + 8 * (size_t)n_intv > d.size()) { bad = true; break; }
+      q += 8 * (size_t)n_intv;
+      if (r == tid) {
+        *has = best != ~0ull;
+        *voff = best;
+        return true;
+      }
     }
-    if (bsize < 0 || p + (size_t)bsize + 1 > raw.size()) BAM_FAIL("vsv_bam_open: truncated BGZF block");
-    const size_t blen = (size_t)bsize + 1;
-    const uint32_t isize = rd32(h + blen - 4);
-    blks.push_back({p + 12 + xlen, blen - 12 - xlen - 8, total, isize});
-    total += isize;
-    p += blen;
   }
-  if (p != raw.size()) BAM_FAIL("vsv_bam_open: trailing bytes after the last BGZF block");
-  b->data.resize(total);
-  std::atomic<int> bad(0);
-  parallel_for((int64_t)blks.size(), b->n_threads, [&](int64_t a, int64_t e, int) {
-    z_stream zs;
-    for (int64_t i = a; i < e; ++i) {
-      if (blks[i].out_len == 0) continue;
-      memset(&zs, 0, sizeof(zs));
-      if (inflateInit2(&zs, -15) != Z_OK) { bad = 1; return; }
-      zs.next_in = raw.data() + blks[i].in_off;
-      zs.avail_in = (uInt)blks[i].in_len;
-      zs.next_out = b->data.data() + blks[i].out_off;
-      zs.avail_out = blks[i].out_len;
-      const int rc = inflate(&zs, Z_FINISH);
-      inflateEnd(&zs);
-      if (rc != Z_STREAM_END || zs.avail_out != 0) { bad = 1; return; }
+  return false;
+}
+
+int bam_load(const char* path, int n_threads, const char* ref_name, vsv_bam** out) {
+  const char* fn = ref_name ? "vsv_bam_open_ref" : "vsv_bam_open";
+  if (!path || !out) { g_bam_err = std::string(fn) + ": null argument"; return VSV_E_ARG; }
+  *out = nullptr;
+  FILE* f = fopen(path, "rb");
+  if (!f) { g_bam_err = std::string(fn) + ": cannot open " + path; return VSV_E_ARG; }
+  vsv_bam* b = new vsv_bam();
+  b->n_threads = n_threads > 0 ? n_threads : (int)std::max(1u, std::thread::hardware_concurrency());
+  BgzfReader rd(f, b->n_threads);
+  std::vector<uint8_t> buf;
+  size_t pos = 0;
+  std::string err;
+  size_t WINDOW = size_t(32) << 20;                       // compressed bytes per read; VSV_BAM_WINDOW overrides (tests)
+  if (const char* e = getenv("VSV_BAM_WINDOW")) { const long long w = atoll(e); if (w >= 64) WINDOW = (size_t)w; }
+  int rc_fill = 1;
+  auto fail = [&](const std::string& m) {
+    g_bam_err = std::string(fn) + ": " + m;
+    fclose(f);
+    delete b;
+    return VSV_E_ARG;
+  };
+  // makes `n` bytes available at buf[pos..]; false at end of file (or error: err set)
+  auto need = [&](size_t n) -> bool {
+    while (buf.size() - pos < n) {
+      if (pos > (size_t(1) << 20)) { buf.erase(buf.begin(), buf.begin() + (ptrdiff_t)pos); pos = 0; }
+      rc_fill = rd.fill(buf, WINDOW, err);
+      if (rc_fill <= 0) return false;
     }
-  });
-  if (bad) BAM_FAIL("vsv_bam_open: inflate failed (corrupt BGZF block)");
-  raw.clear();
-  raw.shrink_to_fit();
+    return true;
+  };
   // ---- BAM header -------------------------------------------------------------------------
-  const uint8_t* d = b->data.data();
-  const size_t n = b->data.size();
-  if (n < 12 || memcmp(d, "BAM\1", 4) != 0) BAM_FAIL("vsv_bam_open: not a BAM stream (CRAM/SAM are not read here)");
-  size_t q = 4;
-  const uint32_t l_text = rd32(d + q);
-  q += 4;
-  if (q + l_text + 4 > n) BAM_FAIL("vsv_bam_open: truncated header");
-  b->header_text.assign(reinterpret_cast<const char*>(d + q), l_text);
-  q += l_text;
-  const uint32_t n_ref = rd32(d + q);
-  q += 4;
+  if (!need(12)) return fail(err.empty() ? "not a BAM stream (CRAM/SAM are not read here)" : err);
+  if (memcmp(buf.data() + pos, "BAM\1", 4) != 0) return fail("not a BAM stream (CRAM/SAM are not read here)");
+  const uint32_t l_text = rd32(buf.data() + pos + 4);
+  pos += 8;
+  if (!need((size_t)l_text + 4)) return fail("truncated header");
+  b->header_text.assign(reinterpret_cast<const char*>(buf.data() + pos), l_text);
+  pos += l_text;
+  const uint32_t n_ref = rd32(buf.data() + pos);
+  pos += 4;
   b->refs.resize(n_ref);
   for (uint32_t i = 0; i < n_ref; ++i) {
-    if (q + 4 > n) BAM_FAIL("vsv_bam_open: truncated reference list");
-    const uint32_t l_name = rd32(d + q);
-    q += 4;
-    if (q + l_name + 4 > n || l_name == 0) BAM_FAIL("vsv_bam_open: truncated reference list");
-    b->refs[i].name.assign(reinterpret_cast<const char*>(d + q), l_name - 1);
-    q += l_name;
-    b->refs[i].len = rd32(d + q);
-    q += 4;
+    if (!need(4)) return fail("truncated reference list");
+    const uint32_t l_name = rd32(buf.data() + pos);
+    pos += 4;
+    if (l_name == 0 || !need((size_t)l_name + 4)) return fail("truncated reference list");
+    b->refs[i].name.assign(reinterpret_cast<const char*>(buf.data() + pos), l_name - 1);
+    pos += l_name;
+    b->refs[i].len = rd32(buf.data() + pos);
+    pos += 4;
   }
-  // ---- record index --------------------------------------------------------------------------
-  while (q + 4 <= n) {
-    const uint32_t bs = rd32(d + q);
-    if (bs < 32 || q + 4 + (size_t)bs > n) BAM_FAIL("vsv_bam_open: truncated record");
-    const int32_t rid = rd32s(d + q + 4);
-    if (rid >= 0 && (uint32_t)rid < n_ref) b->refs[rid].recs.push_back(b->recs.size());
-    b->recs.push_back({q + 4, bs});
-    q += 4 + (size_t)bs;
+  // ---- which records to keep ------------------------------------------------------------------
+  int tid = -1;
+  bool stop_after = false;  // coordinate-sorted: nothing of `tid` follows a later reference
+  if (ref_name && !*ref_name) {  // "" = header only
+    fclose(f);
+    *out = b;
+    return VSV_OK;
   }
+  if (ref_name) {
+    for (uint32_t i = 0; i < n_ref; ++i)
+      if (b->refs[i].name == ref_name) tid = (int)i;
+    if (tid < 0) return fail(std::string("reference ") + ref_name + " is not in the BAM header");
+    stop_after = b->header_text.find("SO:coordinate") != std::string::npos;
+    uint64_t voff = 0;
+    bool has = false;
+    if (bai_ref_start(path, tid, &voff, &has)) {
+      stop_after = true;
+      if (!has) {  // indexed and empty
+        fclose(f);
+        *out = b;
+        return VSV_OK;
+      }
+      rd.seek(voff >> 16);
+      buf.clear();
+      pos = 0;
+      if (!need((size_t)(voff & 0xFFFFu) + 4)) return fail(err.empty() ? "index points past the end of the file" : err);
+      pos = (size_t)(voff & 0xFFFFu);
+    }
+  }
+  // ---- records ----------------------------------------------------------------------------------
+  for (;;) {
+    if (!need(4)) {
+      if (rc_fill < 0) return fail(err);
+      if (buf.size() != pos) return fail("truncated record");
+      break;
+    }
+    const uint32_t bs = rd32(buf.data() + pos);
+    if (bs < 32) return fail("truncated record");
+    if (!need(4 + (size_t)bs)) return fail(rc_fill < 0 ? err : "truncated record");
+    const uint8_t* body = buf.data() + pos + 4;
+    const int32_t rid = rd32s(body);
+    if (tid >= 0 && stop_after && (rid > tid || rid < 0)) break;  // sorted: later references, then the unmapped tail
+    if (rid >= 0 && (uint32_t)rid < n_ref && (tid < 0 || rid == tid)) {
+      RecView v;
+      if (!view(body, bs, &v, true)) return fail("malformed record");
+      const size_t head = (size_t)(v.aux - body) - (size_t)v.l_seq;   // fixed part, name, cigar, 4-bit seq
+      const size_t aux = (size_t)(v.end - v.aux);
+      const size_t o = b->data.size();
+      b->data.resize(o + head + aux);
+      memcpy(b->data.data() + o, body, head);
+      memcpy(b->data.data() + o + head, v.aux, aux);
+      b->refs[rid].recs.push_back(b->recs.size());
+      b->recs.push_back({o, (uint32_t)(head + aux)});
+    }
+    pos += 4 + (size_t)bs;
+  }
+  fclose(f);
   *out = b;
   return VSV_OK;
+}
+
+}  // namespace
+
+extern "C" int vsv_bam_open(const char* path, int n_threads, vsv_bam** out) { return bam_load(path, n_threads, nullptr, out); }
+
+extern "C" int vsv_bam_open_ref(const char* path, const char* ref_name, int n_threads, vsv_bam** out) {
+  if (!ref_name) { g_bam_err = "vsv_bam_open_ref: null argument"; return VSV_E_ARG; }
+  return bam_load(path, n_threads, ref_name, out);
 }
 
 extern "C" void vsv_bam_close(vsv_bam* b) { delete b; }

@@ -72,6 +72,7 @@ SIGNATURES = {
     "vsv_span_depth": [_vp, _vp, _vp, _i64, _vp, _vp, _i64, _vp],
     "vsv_edit_distance_batch": [_vp, _vp, _vp, _i64, _vp, _vp, _i64, _vp],
     "vsv_bam_open": [C.c_char_p, _int, C.POINTER(_vp)],
+    "vsv_bam_open_ref": [C.c_char_p, C.c_char_p, _int, C.POINTER(_vp)],
     "vsv_bam_close": [_vp],
     "vsv_bam_last_error": [],
     "vsv_bam_n_ref": [_vp],
@@ -376,10 +377,15 @@ class BamFile:
     """Native BAM reader (include/volcanosv_b200.h: vsv_bam_*): the host-side replacement of
     `pysam.AlignmentFile(path).fetch(chr)` for whole-chromosome scans.  Host code only (no GPU)."""
 
-    def __init__(self, path: str, n_threads: int = 0):
+    def __init__(self, path: str, n_threads: int = 0, ref: Optional[str] = None):
+        """ref=None: every mapped record; ref="chr10": that reference only (seeks through the .bai when there
+        is one); ref="": header only."""
         self.lib = load_library()
         self.h = _vp()
-        rc = self.lib.vsv_bam_open(os.fsencode(path), n_threads, C.byref(self.h))
+        if ref is None:
+            rc = self.lib.vsv_bam_open(os.fsencode(path), n_threads, C.byref(self.h))
+        else:
+            rc = self.lib.vsv_bam_open_ref(os.fsencode(path), ref.encode(), n_threads, C.byref(self.h))
         if rc != 0:
             raise VsvError(rc, (self.lib.vsv_bam_last_error() or b"").decode())
         self.refs = []

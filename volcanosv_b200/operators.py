@@ -154,30 +154,37 @@ class AlignmentSource:
         self._by_chrom = {c: r.finish() for c, r in recs.items()}
 
     def _load_bam(self, path):
-        """BAM through the native feeder (include/volcanosv_b200.h: vsv_bam_*): numeric columns
-        arrive packed; names / SA tags become Python strings, SEQ is decoded per record on demand."""
-        bf = L.BamFile(path)
-        self._bam = bf
-        self._refs = [(n, ln) for n, ln, _ in bf.refs]
-        for tid, (chrom, _, n_rec) in enumerate(bf.refs):
-            if n_rec == 0:
-                continue
-            d = bf.chrom(tid, want_seq=False)
-            R = Records()
-            R.n = n_rec
-            R.ops, R.op_off, R.pos, R.mapq = d["ops"], d["op_off"], d["pos"], d["mapq"]
-            R.flag = d["flag"].astype(np.int32)
-            R.qlen = d["qlen"]
-            R.is_rev = ((R.flag & 16) != 0).astype(np.uint8)
-            has = d["op_off"][1:] > d["op_off"][:-1]
-            R.first_op = np.where(has, R.ops[np.minimum(d["op_off"][:-1], max(len(R.ops) - 1, 0))] if len(R.ops) else 0, 0).astype(np.uint32)
-            R.last_op = np.where(has, R.ops[np.maximum(d["op_off"][1:] - 1, 0)] if len(R.ops) else 0, 0).astype(np.uint32)
-            names, no = bytes(d["names"]), d["name_off"]
-            R.qname = [names[no[i]: no[i + 1]].decode() for i in range(n_rec)]
-            sa, so = bytes(d["sa"]), d["sa_off"]
-            R.sa = [sa[so[i]: so[i + 1]].decode() if so[i + 1] > so[i] else None for i in range(n_rec)]
-            R.seq = _LazySeq(bf, tid, R.qlen)
-            self._by_chrom[chrom] = R
+        """BAM through the native feeder (include/volcanosv_b200.h: vsv_bam_*): only the header here; a
+        chromosome's records are read when an operator asks for them (records()), so memory is bounded
+        by one chromosome, as with `samfile.fetch(chr)`."""
+        self._bam_path = path
+        self._refs = [(n, ln) for n, ln, _ in L.BamFile(path, ref="").refs]
+
+    def _bam_records(self, chrom):
+        if chrom not in dict(self._refs):
+            return Records().finish()
+        bf = L.BamFile(self._bam_path, ref=chrom)
+        tid = [r[0] for r in bf.refs].index(chrom)
+        n_rec = bf.refs[tid][2]
+        if n_rec == 0:
+            return Records().finish()
+        d = bf.chrom(tid, want_seq=False)
+        R = Records()
+        R.n = n_rec
+        R.ops, R.op_off, R.pos, R.mapq = d["ops"], d["op_off"], d["pos"], d["mapq"]
+        R.flag = d["flag"].astype(np.int32)
+        R.qlen = d["qlen"]
+        R.is_rev = ((R.flag & 16) != 0).astype(np.uint8)
+        has = d["op_off"][1:] > d["op_off"][:-1]
+        last = max(len(R.ops) - 1, 0)
+        R.first_op = np.where(has, R.ops[np.minimum(d["op_off"][:-1], last)] if len(R.ops) else 0, 0).astype(np.uint32)
+        R.last_op = np.where(has, R.ops[np.maximum(d["op_off"][1:] - 1, 0)] if len(R.ops) else 0, 0).astype(np.uint32)
+        names, no = bytes(d["names"]), d["name_off"]
+        R.qname = [names[no[i]: no[i + 1]].decode() for i in range(n_rec)]
+        sa, so = bytes(d["sa"]), d["sa_off"]
+        R.sa = [sa[so[i]: so[i + 1]].decode() if so[i + 1] > so[i] else None for i in range(n_rec)]
+        R.seq = _LazySeq(bf, tid, R.qlen)
+        return R
 
     def _load_pysam(self, path):
         try:
@@ -197,6 +204,8 @@ class AlignmentSource:
         return list(self._refs)
 
     def records(self, chrom: str) -> Records:
+        if getattr(self, "_bam_path", None) is not None and chrom not in self._by_chrom:
+            self._by_chrom = {chrom: self._bam_records(chrom)}      # one chromosome resident at a time
         return self._by_chrom.get(chrom) or Records().finish()
 
 
