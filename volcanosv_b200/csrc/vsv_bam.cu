@@ -16,6 +16,7 @@
 
 #include <algorithm>
 #include <atomic>
+#include <chrono>
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
@@ -220,6 +221,7 @@ class BgzfReader {
       }
       const size_t base = out.size();
       out.resize(base + total);
+      const auto t_inf0 = std::chrono::steady_clock::now();
       std::atomic<int> bad(0);
       uint8_t* dst = out.data() + base;
       const uint8_t* src = raw_.data();
@@ -238,6 +240,7 @@ class BgzfReader {
           if (rc != Z_STREAM_END || zs.avail_out != 0) { bad = 1; return; }
         }
       });
+      inflate_s += std::chrono::duration<double>(std::chrono::steady_clock::now() - t_inf0).count();
       if (bad) { err = "inflate failed (corrupt BGZF block)"; return -1; }
       raw_.erase(raw_.begin(), raw_.begin() + (ptrdiff_t)p);
       if (total == 0) continue;  // only empty blocks (the EOF marker): look further
@@ -250,6 +253,9 @@ class BgzfReader {
   int nt_;
   std::vector<uint8_t> raw_;
   bool eof_ = false;
+
+ public:
+  double inflate_s = 0;
 };
 
 // smallest chunk start (virtual offset) of reference `tid` in a BAI index; false if the file is
@@ -414,6 +420,7 @@ int bam_load(const char* path, int n_threads, const char* ref_name, vsv_bam** ou
     pos += 4 + (size_t)bs;
   }
   fclose(f);
+  if (getenv("VSV_BAM_DEBUG")) fprintf(stderr, "vsv_bam: inflate %.3f s (threads %d), kept %zu bytes\n", rd.inflate_s, b->n_threads, b->data.size());
   *out = b;
   return VSV_OK;
 }
