@@ -369,7 +369,7 @@ def main():
                          bam_native_u32=dict(value=world * n_rec / e2e32_per_step, ms_per_step=e2e32_per_step * 1e3,
                                              h2d_bytes_per_step=h2d32_b)),
                 roofline=roof, candidates_per_s=geno, resident_two_shards_in_flight=inflight2)
-    if not args.no_cpu_baseline:
+    if not args.no_cpu_baseline and world == 1:              # reported at N=1 only (the host cores are shared by the ranks)
         base, _, _ = cpu_baseline(batch, cands, thr)
         line["cpu_baseline"] = base
     print(json.dumps(line))

@@ -454,34 +454,44 @@ class BamFile:
                                            _p(d["seq"]) if want_seq else None, _p(d["sa_off"]), _p(d["sa"]))
 
 
-def pack_ops16(ops):
+def pack_ops16(ops, chunk: int = 1 << 24):
     """Host packer of the compact staging format of vsv_expand_ops16: (ops16, exc_idx, exc_val)."""
     ops = np.ascontiguousarray(ops, dtype=np.uint32)
-    big = ops >= np.uint32(0xFFF0)
     o16 = _aligned_empty(len(ops), np.uint16)
-    np.copyto(o16, ops, casting="unsafe")
-    exc_idx = np.flatnonzero(big).astype(np.int64)
+    idx = []
+    for a in range(0, len(ops), chunk):
+        w = ops[a: a + chunk]
+        np.copyto(o16[a: a + chunk], w, casting="unsafe")
+        e = np.flatnonzero(w >= np.uint32(0xFFF0)).astype(np.int64)
+        o16[a + e] = (np.uint16(0xFFF0) | (w[e] & np.uint32(15)).astype(np.uint16))
+        idx.append(e + a)
+    exc_idx = np.concatenate(idx) if idx else np.zeros(0, np.int64)
     exc_val = ops[exc_idx].copy()
-    o16[exc_idx] = (np.uint16(0xFFF0) | (exc_val & np.uint32(15)).astype(np.uint16))
     return o16, exc_idx, exc_val
 
 
 OPS8_M, OPS8_I, OPS8_D = 160, 47, 47      # include/volcanosv_b200.h: VSV_OPS8_*
 
 
-def pack_ops8(ops):
+def pack_ops8(ops, chunk: int = 1 << 24):
     """Host packer of vsv_expand_ops8: (ops8, exc_idx, exc_val).  One byte per short M/I/D run
-    (M 1..160 -> 0..159, I 1..47 -> 160..206, D 1..47 -> 207..253), 0xFF + exception otherwise."""
+    (M 1..160 -> 0..159, I 1..47 -> 160..206, D 1..47 -> 207..253), 0xFF + exception otherwise.
+    Works through the array in chunks so the temporaries stay small next to the input."""
     ops = np.ascontiguousarray(ops, dtype=np.uint32)
-    code, ln = ops & np.uint32(15), ops >> np.uint32(4)
     cnt = np.array([OPS8_M, OPS8_I, OPS8_D] + [0] * 13, np.uint32)
     base = np.array([0, OPS8_M, OPS8_M + OPS8_I] + [0] * 13, np.uint32)
-    big = (ln < 1) | (ln > cnt[code])
     o8 = _aligned_empty(len(ops), np.uint8)
-    np.copyto(o8, base[code] + ln - np.uint32(1), casting="unsafe")
-    exc_idx = np.flatnonzero(big).astype(np.int64)
+    idx = []
+    for a in range(0, len(ops), chunk):
+        w = ops[a: a + chunk]
+        code, ln = w & np.uint32(15), w >> np.uint32(4)
+        big = (ln < 1) | (ln > cnt[code])
+        np.copyto(o8[a: a + chunk], base[code] + ln - np.uint32(1), casting="unsafe")
+        e = np.flatnonzero(big).astype(np.int64)
+        o8[a + e] = 0xFF
+        idx.append(e + a)
+    exc_idx = np.concatenate(idx) if idx else np.zeros(0, np.int64)
     exc_val = ops[exc_idx].copy()
-    o8[exc_idx] = 0xFF
     return o8, exc_idx, exc_val
 
 
