@@ -281,3 +281,22 @@ def test_expand_ops8(ctx):
         ops = (ln << 4) | code
         o8, ei, ev = pack_ops8(ops)
         assert np.array_equal(ctx.expand_ops8(o8, ei, ev), ops)
+
+
+def test_record_range_parts_concatenate_to_the_whole(ctx):
+    """Level-2 sharding (shard.split_records): scanning contiguous record ranges separately and
+    concatenating in part order == scanning the chromosome batch at once (both fused streams)."""
+    from volcanosv_b200 import shard as SH
+    b = synth.synth_records(91, 4000, "ont", eqx=True)
+    enable = (b["qlen"] >= 500).astype(np.uint8)
+    ra, rb, rt, qt, xt = ctx.scan_reads_fused(b["ops"], b["op_off"], b["pos"], b["mapq"], enable_cute=enable)
+    pa, pb, prt = [], [], []
+    for lo, hi in SH.split_records(b["op_off"], 5):
+        t = SH.take_records(b, lo, hi)
+        a_, b_, rt_, _, _ = ctx.scan_reads_fused(t["ops"], t["op_off"], t["pos"], t["mapq"], enable_cute=enable[lo:hi])
+        for s_ in (a_, b_):
+            s_["rec"] += lo
+        pa.append(a_); pb.append(b_); prt.append(rt_)
+    assert np.array_equal(np.concatenate(pa).view(np.uint8), ra.view(np.uint8))
+    assert np.array_equal(np.concatenate(pb).view(np.uint8), rb.view(np.uint8))
+    assert np.array_equal(np.concatenate(prt), rt)

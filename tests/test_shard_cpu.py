@@ -99,3 +99,24 @@ def test_gloo_world2_gather_concat():
         assert p.exitcode == 0
     assert [x.split(":")[0] for x in out] == ["chr%d" % i for i in range(1, 9)]
     assert {x.strip()[-5:] for x in out} == {"rank0", "rank1"}
+
+
+def test_split_records_balanced_and_complete():
+    import numpy as np
+    from volcanosv_b200 import shard as SH
+    rng = np.random.default_rng(3)
+    n_ops = rng.integers(0, 5000, 1000)
+    n_ops[::50] = 0                                            # records without ops
+    off = np.concatenate([[0], np.cumsum(n_ops)])
+    for parts in (1, 2, 3, 8, 2000):
+        r = SH.split_records(off, parts)
+        assert len(r) == parts and r[0][0] == 0 and r[-1][1] == 1000
+        assert all(a[1] == b[0] for a, b in zip(r, r[1:])) and all(lo <= hi for lo, hi in r)
+        if parts <= 8:
+            load = [off[hi] - off[lo] for lo, hi in r]
+            assert max(load) - min(load) <= 2 * 5000
+    b = dict(ops=np.arange(off[-1], dtype=np.uint32), op_off=off, pos=np.arange(1000, dtype=np.int32))
+    lo, hi = SH.split_records(off, 3)[1]
+    t = SH.take_records(b, lo, hi)
+    assert t["op_off"][0] == 0 and len(t["ops"]) == t["op_off"][-1] and t["ops"][0] == off[lo]
+    assert np.array_equal(t["pos"], b["pos"][lo:hi])

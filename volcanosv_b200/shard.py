@@ -87,3 +87,32 @@ def concat_in_order(per_rank: List[dict], order: Sequence[str]) -> list:
                 raise ValueError("chromosome %r produced by two ranks" % (k,))
             merged[k] = v
     return [merged[c] for c in order if c in merged]
+
+
+def split_records(op_off: Sequence[int], n_parts: int) -> List[tuple]:
+    """Level-2 sharding of ONE chromosome (the reference cuts a chromosome into 10 Mb
+    batches with read-start ownership, SE:603-612,535): contiguous record ranges [lo, hi) of a
+    coordinate-sorted batch, balanced by CIGAR-op count.  The scans are per record, so the
+    signatures of the parts, concatenated in part order, are exactly the signatures of the whole
+    batch; sorting, grouping and the joins then run on the gathered table."""
+    import numpy as np
+    off = np.asarray(op_off, dtype=np.int64)
+    n = len(off) - 1
+    if n_parts < 1:
+        raise ValueError("n_parts must be >= 1")
+    cuts = [0]
+    for k in range(1, n_parts):
+        target = off[0] + (off[-1] - off[0]) * k // n_parts
+        cuts.append(max(cuts[-1], min(n, int(np.searchsorted(off, target, side="left")))))
+    cuts.append(n)
+    return [(cuts[i], cuts[i + 1]) for i in range(n_parts)]
+
+
+def take_records(batch: dict, lo: int, hi: int) -> dict:
+    """The packed columns of records [lo, hi) with op offsets rebased to 0."""
+    import numpy as np
+    a, b = int(batch["op_off"][lo]), int(batch["op_off"][hi])
+    out = {k: v[lo:hi] for k, v in batch.items() if k not in ("ops", "op_off")}
+    out["ops"] = np.ascontiguousarray(batch["ops"][a:b])
+    out["op_off"] = np.asarray(batch["op_off"][lo: hi + 1], dtype=np.int64) - a
+    return out
