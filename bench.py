@@ -246,8 +246,6 @@ def main():
     ms = shard.ctx.timer_stop()
     l1 = launches()
     barrier()
-    sampler.stop_flag = True
-    sampler.join()
     t = torch.tensor([ms], dtype=torch.float64, device="cuda")
     if dist is not None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -286,6 +284,8 @@ def main():
     e2e_per_step, (h2d_b, d2h_b) = e2e_run(pinned16)
     e2e_value = world * n_rec / e2e_per_step
     e2e32_per_step, (h2d32_b, _) = e2e_run(pinned)   # BAM-native u32 ops, no compact staging
+    sampler.stop_flag = True                          # clocks sampled through the resident AND the end-to-end timed regions
+    sampler.join()
 
     # ---- resident throughput with two shards in flight (a GPU holds many chromosome shards in its
     # 180 GB; while one shard's scan owns the SMs the other's small join kernels fill the gaps).
