@@ -29,6 +29,19 @@
 
 namespace {
 
+// std::vector that does not zero-fill on resize (the bytes are overwritten right away by fread /
+// inflate / memcpy; the zero fill was a serial first touch of every page)
+template <class T>
+struct NoInit : std::allocator<T> {
+  template <class U> struct rebind { using other = NoInit<U>; };
+  template <class U, class... A>
+  void construct(U* p, A&&... a) {
+    if constexpr (sizeof...(A) == 0) ::new ((void*)p) U;
+    else ::new ((void*)p) U(std::forward<A>(a)...);
+  }
+};
+typedef std::vector<uint8_t, NoInit<uint8_t>> Bytes;
+
 struct BamRec {
   uint64_t off;      // offset of the record body (after block_size) in the inflated stream
   uint32_t size;     // block_size
@@ -155,7 +168,7 @@ void parallel_for(int64_t n, int n_threads, F f) {
 }  // namespace
 
 struct vsv_bam {
-  std::vector<uint8_t> data;   // kept record bodies (qualities dropped), back to back
+  Bytes data;                  // kept record bodies (qualities dropped), back to back
   std::vector<BamRec> recs;
   std::vector<RefInfo> refs;
   std::string header_text;
@@ -180,7 +193,7 @@ class BgzfReader {
     eof_ = false;
   }
   // 1 = appended something, 0 = end of file, -1 = error (err set)
-  int fill(std::vector<uint8_t>& out, size_t want, std::string& err) {
+  int fill(Bytes& out, size_t want, std::string& err) {
     for (;;) {
       if (eof_ && raw_.empty()) return 0;
       const size_t have = raw_.size();
@@ -251,7 +264,7 @@ class BgzfReader {
  private:
   FILE* f_;
   int nt_;
-  std::vector<uint8_t> raw_;
+  Bytes raw_;
   bool eof_ = false;
 
  public:
@@ -321,7 +334,7 @@ int bam_load(const char* path, int n_threads, const char* ref_name, vsv_bam** ou
   vsv_bam* b = new vsv_bam();
   b->n_threads = n_threads > 0 ? n_threads : (int)std::max(1u, std::thread::hardware_concurrency());
   BgzfReader rd(f, b->n_threads);
-  std::vector<uint8_t> buf;
+  Bytes buf;
   size_t pos = 0;
   std::string err;
   size_t WINDOW = size_t(32) << 20;                       // compressed bytes per read; VSV_BAM_WINDOW overrides (tests)
@@ -392,32 +405,59 @@ int bam_load(const char* path, int n_threads, const char* ref_name, vsv_bam** ou
       pos = (size_t)(voff & 0xFFFFu);
     }
   }
-  // ---- records ----------------------------------------------------------------------------------
-  for (;;) {
+  // ---- records: per window, a serial walk of the block_size chain, then sizes and copies in parallel ----
+  struct Keep { size_t off; uint32_t bs, head, aux; int32_t rid; };
+  std::vector<Keep> keep;
+  bool stop = false;
+  while (!stop) {
     if (!need(4)) {
       if (rc_fill < 0) return fail(err);
       if (buf.size() != pos) return fail("truncated record");
       break;
     }
-    const uint32_t bs = rd32(buf.data() + pos);
-    if (bs < 32) return fail("truncated record");
-    if (!need(4 + (size_t)bs)) return fail(rc_fill < 0 ? err : "truncated record");
-    const uint8_t* body = buf.data() + pos + 4;
-    const int32_t rid = rd32s(body);
-    if (tid >= 0 && stop_after && (rid > tid || rid < 0)) break;  // sorted: later references, then the unmapped tail
-    if (rid >= 0 && (uint32_t)rid < n_ref && (tid < 0 || rid == tid)) {
-      RecView v;
-      if (!view(body, bs, &v, true)) return fail("malformed record");
-      const size_t head = (size_t)(v.aux - body) - (size_t)v.l_seq;   // fixed part, name, cigar, 4-bit seq
-      const size_t aux = (size_t)(v.end - v.aux);
-      const size_t o = b->data.size();
-      b->data.resize(o + head + aux);
-      memcpy(b->data.data() + o, body, head);
-      memcpy(b->data.data() + o + head, v.aux, aux);
-      b->refs[rid].recs.push_back(b->recs.size());
-      b->recs.push_back({o, (uint32_t)(head + aux)});
+    {
+      const uint32_t bs0 = rd32(buf.data() + pos);
+      if (bs0 < 32) return fail("truncated record");
+      if (!need(4 + (size_t)bs0)) return fail(rc_fill < 0 ? err : "truncated record");
     }
-    pos += 4 + (size_t)bs;
+    keep.clear();
+    size_t p = pos;
+    while (p + 4 <= buf.size()) {
+      const uint32_t bs = rd32(buf.data() + p);
+      if (bs < 32) return fail("truncated record");
+      if (p + 4 + (size_t)bs > buf.size()) break;
+      const int32_t rid = rd32s(buf.data() + p + 4);
+      if (tid >= 0 && stop_after && (rid > tid || rid < 0)) { stop = true; break; }  // sorted: later references, then the unmapped tail
+      if (rid >= 0 && (uint32_t)rid < n_ref && (tid < 0 || rid == tid)) keep.push_back({p + 4, bs, 0u, 0u, rid});
+      p += 4 + (size_t)bs;
+    }
+    std::atomic<int> bad(0);
+    parallel_for((int64_t)keep.size(), b->n_threads, [&](int64_t a0, int64_t e0, int) {
+      for (int64_t i = a0; i < e0; ++i) {
+        RecView v;
+        const uint8_t* body = buf.data() + keep[i].off;
+        if (!view(body, keep[i].bs, &v, true)) { bad = 1; return; }
+        keep[i].head = (uint32_t)((size_t)(v.aux - body) - (size_t)v.l_seq);   // fixed part, name, cigar, 4-bit seq
+        keep[i].aux = (uint32_t)(v.end - v.aux);
+      }
+    });
+    if (bad) return fail("malformed record");
+    std::vector<size_t> dst(keep.size() + 1);
+    dst[0] = b->data.size();
+    for (size_t i = 0; i < keep.size(); ++i) dst[i + 1] = dst[i] + keep[i].head + keep[i].aux;
+    b->data.resize(dst[keep.size()]);
+    parallel_for((int64_t)keep.size(), b->n_threads, [&](int64_t a0, int64_t e0, int) {
+      for (int64_t i = a0; i < e0; ++i) {
+        const uint8_t* body = buf.data() + keep[i].off;
+        memcpy(b->data.data() + dst[i], body, keep[i].head);
+        memcpy(b->data.data() + dst[i] + keep[i].head, body + keep[i].bs - keep[i].aux, keep[i].aux);
+      }
+    });
+    for (size_t i = 0; i < keep.size(); ++i) {
+      b->refs[keep[i].rid].recs.push_back(b->recs.size());
+      b->recs.push_back({dst[i], keep[i].head + keep[i].aux});
+    }
+    pos = p;
   }
   fclose(f);
   if (getenv("VSV_BAM_DEBUG")) fprintf(stderr, "vsv_bam: inflate %.3f s (threads %d), kept %zu bytes\n", rd.inflate_s, b->n_threads, b->data.size());
