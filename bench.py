@@ -185,8 +185,12 @@ def main():
         raise SystemExit("bench.py: no CUDA device (volcanosv_b200 has no CPU path)")
     torch.cuda.set_device(local)
     dist = None
+    host_binding = None
     if world > 1:
         import torch.distributed as dist
+        from volcanosv_b200.shard import bind_host_to_gpu
+        if os.environ.get("VSV_NO_BIND") != "1":
+            host_binding = bind_host_to_gpu(local)   # pinned staging buffers on the GPU's own socket
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     from volcanosv_b200.pipeline import ShardStream
 
@@ -369,6 +373,8 @@ def main():
                          bam_native_u32=dict(value=world * n_rec / e2e32_per_step, ms_per_step=e2e32_per_step * 1e3,
                                              h2d_bytes_per_step=h2d32_b)),
                 roofline=roof, candidates_per_s=geno, resident_two_shards_in_flight=inflight2)
+    if host_binding is not None:
+        line["config"]["host_binding"] = host_binding         # rank 0's; every rank binds to its own GPU's CPUs
     if not args.no_cpu_baseline and world == 1:              # reported at N=1 only (the host cores are shared by the ranks)
         base, _, _ = cpu_baseline(batch, cands, thr)
         line["cpu_baseline"] = base

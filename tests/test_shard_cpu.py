@@ -120,3 +120,17 @@ def test_split_records_balanced_and_complete():
     t = SH.take_records(b, lo, hi)
     assert t["op_off"][0] == 0 and len(t["ops"]) == t["op_off"][-1] and t["ops"][0] == off[lo]
     assert np.array_equal(t["pos"], b["pos"][lo:hi])
+
+
+def test_bind_host_to_gpu_is_best_effort():
+    """No driver here: the helper reports why it did nothing and leaves the affinity mask alone."""
+    import os
+    from volcanosv_b200 import shard as SH
+    before = os.sched_getaffinity(0)
+    info = SH.bind_host_to_gpu(0)
+    assert isinstance(info, dict) and "bound" in info
+    if not info["bound"]:
+        assert os.sched_getaffinity(0) == before
+    else:
+        assert os.sched_getaffinity(0) <= before
+        os.sched_setaffinity(0, before)

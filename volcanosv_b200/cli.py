@@ -184,7 +184,10 @@ def _ranks():
     if world > 1:
         import torch
         import torch.distributed as dist
-        torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
+        local = int(os.environ.get("LOCAL_RANK", "0"))
+        torch.cuda.set_device(local)
+        from .shard import bind_host_to_gpu
+        bind_host_to_gpu(local)            # staging buffers and feeder threads on the GPU's own socket
         dist.init_process_group("gloo")    # file-level hand-over only: no data-path collective
         barrier = dist.barrier
     return rank, world, barrier

@@ -116,3 +116,38 @@ def take_records(batch: dict, lo: int, hi: int) -> dict:
     out["ops"] = np.ascontiguousarray(batch["ops"][a:b])
     out["op_off"] = np.asarray(batch["op_off"][lo: hi + 1], dtype=np.int64) - a
     return out
+
+
+def bind_host_to_gpu(device: int) -> dict:
+    """Keep this rank's host threads (and so its first-touch pinned staging buffers) on the CPUs
+    the driver reports as local to `device`.  With several ranks per node the shard uploads are
+    the end-to-end bound; a staging buffer on the far socket sends every byte
+    over the inter-socket link first.  Call before allocating pinned memory and before starting
+    worker threads (they inherit the mask).  Best effort: returns what was done, never raises.
+    """
+    import os
+    info = {"bound": False}
+    try:
+        import pynvml
+        import torch
+        pynvml.nvmlInit()
+        pr = torch.cuda.get_device_properties(device)
+        bus = "%08x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+        hd = pynvml.nvmlDeviceGetHandleByPciBusId(bus.encode())
+        n_cpu = os.cpu_count() or 1
+        words = pynvml.nvmlDeviceGetCpuAffinity(hd, (n_cpu + 63) // 64)
+        local = {64 * w + b for w, m in enumerate(words) for b in range(64) if (int(m) >> b) & 1}
+        allowed = os.sched_getaffinity(0)
+        info.update(gpu_local_cpus=len(local), allowed_cpus=len(allowed))
+        try:
+            info["numa_node"] = int(pynvml.nvmlDeviceGetNumaNodeId(hd))
+        except Exception:
+            pass
+        both = local & allowed
+        if len(both) >= 4 and both != allowed:
+            os.sched_setaffinity(0, both)
+            info["bound"] = True
+        info["cpus"] = len(both) if both else len(allowed)
+    except Exception as e:   # no NVML, restricted cpuset, old driver: run unbound
+        info["error"] = "%s: %s" % (type(e).__name__, e)
+    return info
