@@ -71,7 +71,8 @@ def test_cli_mirrors_every_reference_operator():
                  "extract_reads_signature.py", "FP_filter_v1.py", "remove_redundancy.py", "sig_extract.py",
                  "calculate_signature_support.py", "filter_vcf_by_sig_cov_insdel.py", "correct_gt_del_real_data.py",
                  "correct_gt_ins_real_data.py", "filter_GT_correction.py", "volcanosv-vc-large-indel.py",
-                 "Raw_variant_call-otherasm.py", "volcanosv-vc-large-indel-otherasm.py"):
+                 "Raw_variant_call-otherasm.py", "volcanosv-vc-large-indel-otherasm.py",
+                 "volcanosv-vc-large-indel-otherasm-2hap.py"):
         assert name in cli.COMMANDS
     import pytest
     with pytest.raises(SystemExit):

@@ -74,10 +74,8 @@ def test_whole_genome_mode_two_ranks(work):
     check(out, work)
 
 
-def test_otherasm_entry_point(work):
-    """LI/volcanosv-vc-large-indel-otherasm.py: one whole-genome contig FASTA + one contig alignment file,
-    contigs split by chromosome on the fly; against the unmodified reference's run of that script."""
-    from volcanosv_b200 import cli
+def _whole_genome_contigs(work):
+    """One contig FASTA and one coordinate-sorted contig alignment file for the whole genome."""
     allfa, allsam = os.path.join(work, "all_contigs.fa"), os.path.join(work, "all_contigs.sam")
     with open(allfa, "w") as fo:
         for c in range(1, 23):
@@ -92,10 +90,44 @@ def test_otherasm_entry_point(work):
                 elif not line.startswith("@"):
                     body.append(line)
         fo.writelines(body)
+    return allfa, allsam
+
+
+def test_otherasm_entry_point(work):
+    """LI/volcanosv-vc-large-indel-otherasm.py: one whole-genome contig FASTA + one contig alignment file,
+    contigs split by chromosome on the fly; against the unmodified reference's run of that script."""
+    from volcanosv_b200 import cli
+    allfa, allsam = _whole_genome_contigs(work)
     out = os.path.join(work, "out_otherasm")
     cli.main(["volcanosv-vc-large-indel-otherasm.py", "-i", allfa, "-o", out, "-dtype", "Hifi", "-bam",
               os.path.join(work, "reads.sam"), "-ref", os.path.join(work, "ref.fa"), "-t", "4", "-px", "Sample", "-cbam", allsam])
     exp = os.path.join(WGS, "expected_otherasm")
+    for rel in os.listdir(exp):
+        got = open(os.path.join(out, rel)).read().replace(work, "$WORK")
+        assert got == open(os.path.join(exp, rel)).read(), rel
+
+
+def test_otherasm_2hap_entry_point(work):
+    """LI/volcanosv-vc-large-indel-otherasm-2hap.py: one FASTA per haplotype, the merged sorted contig
+    alignments (2hap:250-258) supplied; against the unmodified reference's run of that script
+    (tests/golden/make_e2e_2hap_golden.py)."""
+    from volcanosv_b200 import cli
+    allfa, allsam = _whole_genome_contigs(work)
+    hp = {k: open(os.path.join(work, "%s.fa" % k), "w") for k in ("hp1", "hp2")}
+    cur = None
+    for line in open(allfa):
+        if line.startswith(">"):
+            cur = hp["hp1" if "hp1" in line else "hp2"]
+        cur.write(line)
+    for f in hp.values():
+        f.close()
+    out = os.path.join(work, "out_2hap")
+    cli.main(["volcanosv-vc-large-indel-otherasm-2hap.py", "-hp1", os.path.join(work, "hp1.fa"), "-hp2",
+              os.path.join(work, "hp2.fa"), "-o", out, "-dtype", "Hifi", "-bam", os.path.join(work, "reads.sam"),
+              "-ref", os.path.join(work, "ref.fa"), "-t", "4", "-px", "Sample", "-cbam", allsam])
+    assert open(os.path.join(out, "contig_by_chr", "merged.fa")).read() == \
+        open(os.path.join(work, "hp1.fa")).read() + open(os.path.join(work, "hp2.fa")).read()
+    exp = os.path.join(WGS, "expected_otherasm_2hap")
     for rel in os.listdir(exp):
         got = open(os.path.join(out, rel)).read().replace(work, "$WORK")
         assert got == open(os.path.join(exp, rel)).read(), rel

@@ -214,6 +214,28 @@ def _main_otherasm(argv):
         print(out)
 
 
+def _main_otherasm_2hap(argv):
+    p = argparse.ArgumentParser(prog="volcanosv-vc-large-indel-otherasm-2hap.py")
+    p.add_argument("--hp1_fa", "-hp1")
+    p.add_argument("--hp2_fa", "-hp2")
+    p.add_argument("--output_dir", "-o")
+    p.add_argument("--data_type", "-dtype")
+    p.add_argument("--bam_file", "-bam")
+    p.add_argument("--reference", "-ref")
+    p.add_argument("--read_signature_dir", "-rdsig")
+    p.add_argument("--pre_cutesig", "-presig")
+    p.add_argument("--n_thread", "-t", type=int, default=11)
+    p.add_argument("--prefix", "-px", default="Sample")
+    p.add_argument("--contig_bam", "-cbam", required=True,
+                   help="sorted merge of both haplotypes' contig alignments (2hap:250-258 output)")
+    a, _ = p.parse_known_args(argv)
+    rank, world, barrier = _ranks()
+    out = OP.large_indel_otherasm_2hap(a.hp1_fa, a.hp2_fa, a.contig_bam, a.reference, a.bam_file, a.output_dir, a.data_type,
+                                       a.prefix, a.read_signature_dir, a.pre_cutesig, rank=rank, world=world, barrier=barrier)
+    if out:
+        print(out)
+
+
 COMMANDS = {
     "extract_reads_signature.py": _ers, "FP_filter_v1.py": _fpf, "sig_extract.py": _se,
     "calculate_signature_support.py": _css, "filter_vcf_by_sig_cov_insdel.py": _cov,
@@ -223,6 +245,7 @@ COMMANDS = {
     "volcanosv-vc-large-indel.py": _main,
     "Raw_variant_call-otherasm.py": _rvc_otherasm,
     "volcanosv-vc-large-indel-otherasm.py": _main_otherasm,
+    "volcanosv-vc-large-indel-otherasm-2hap.py": _main_otherasm_2hap,
 }
 
 

@@ -21,6 +21,7 @@ from __future__ import annotations
 import gzip
 import math
 import os
+import shutil
 import re
 from collections import Counter
 from typing import Dict, List, Optional, Sequence
@@ -1172,6 +1173,27 @@ def large_indel_otherasm(input_path: str, contig_bam: str, reference: str, rbam_
         barrier()
     return large_indel_wgs(contig_bam, "", reference, rbam_file, output_dir, dtype, prefix, read_signature_dir, pre_cutesig,
                            rank=rank, world=world, barrier=barrier, contig_fasta_pattern=os.path.join(folder, "chr{chr}.fasta"))
+
+
+def large_indel_otherasm_2hap(hp1_fa: str, hp2_fa: str, contig_bam: str, reference: str, rbam_file: str, output_dir: str,
+                              dtype: str, prefix: str = "Sample", read_signature_dir: Optional[str] = None,
+                              pre_cutesig: Optional[str] = None, rank: int = 0, world: int = 1, barrier=None):
+    """LI/volcanosv-vc-large-indel-otherasm-2hap.py: the two haplotypes arrive as two FASTA files.  The
+    reference aligns each, merges the two BAMs into one sorted file (2hap:250-258, minimap2 / samtools: out
+    of scope, `contig_bam` is that file) and concatenates the FASTAs to `contig_by_chr/merged.fa`
+    (2hap:274-279) before the same per-chromosome split as the one-file entry (2hap:281-311)."""
+    folder = os.path.join(output_dir, "contig_by_chr")
+    merged = os.path.join(folder, "merged.fa")
+    if rank == 0:
+        os.makedirs(folder, exist_ok=True)
+        with open(merged, "wb") as fo:                                                     # cat hp1 hp2 > merged.fa
+            for src in (hp1_fa, hp2_fa):
+                with open(src, "rb") as fi:
+                    shutil.copyfileobj(fi, fo)
+    if barrier is not None:
+        barrier()
+    return large_indel_otherasm(merged, contig_bam, reference, rbam_file, output_dir, dtype, prefix, read_signature_dir,
+                                pre_cutesig, rank=rank, world=world, barrier=barrier)
 
 
 def large_indel_chr(contig_bam: str, contig_path: str, reference: str, rbam_file: str, output_dir: str, dtype: str,
