@@ -137,6 +137,8 @@ def main():
     ap.add_argument("--scale", type=float, default=1.0, help="fraction of the chr10 shard (tests use < 1)")
     ap.add_argument("--cands", type=int, default=3000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--staging", default="auto", choices=["auto", "ops12", "ops8"],
+                    help="host staging format of the end-to-end leg (auto = the densest that fits the data)")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -204,20 +206,32 @@ def main():
 
     # host staging format of the end-to-end path: ops as 16-bit words + a sparse exception list
     # (vsv_expand_ops16); produced by the host packer once, like the BAM decode it follows
-    from volcanosv_b200.lib import pack_ops16, pack_ops8
+    from volcanosv_b200.lib import pack_ops16, pack_ops8, pack_ops12
     # densest staging format that fits the data: ops8 (1 B/op; noisy long reads: ~1 % exceptions) when fewer than
     # 3 % of the ops need the exception list, else ops16 (2 B/op; HiFi / =,X CIGARs).  The native BAM feeder
     # (vsv_bam_chrom_fill) writes either format straight from the BAM records, so packing is not an extra pass.
+    # ops12 (12 bits per M + short-indel PAIR, vsv_expand_ops12) is denser still when the CIGARs alternate as minimap2's
+    # long-read CIGARs do: taken when its total (tokens + 16 bytes per odd pair) is below ops8's.
     o8, exc_idx, exc_val = pack_ops8(batch["ops"])
     pinned16 = {k: v for k, v in pinned.items() if k != "ops"}
-    if len(exc_idx) < 0.03 * n_ops:
+    bytes8 = o8.nbytes + 12 * len(exc_idx)
+    o12 = None
+    if args.staging in ("auto", "ops12") and len(exc_idx) < 0.03 * n_ops:
+        o12, exc_pair, exc_val12 = pack_ops12(batch["ops"])
+        if args.staging == "auto" and o12.nbytes + 16 * len(exc_pair) >= bytes8:
+            o12 = None
+    if o12 is not None:
+        staging = "ops12"
+        pinned16["ops12"] = torch.from_numpy(o12).pin_memory()
+        exc_idx, exc_val = exc_pair, exc_val12
+    elif len(exc_idx) < 0.03 * n_ops:
         staging = "ops8"
         pinned16["ops8"] = torch.from_numpy(o8).pin_memory()
     else:
         staging = "ops16"
         o16, exc_idx, exc_val = pack_ops16(batch["ops"])
         pinned16["ops16"] = torch.from_numpy(o16.view(np.int16)).pin_memory()
-    del o8
+    del o8, o12
     pinned16["exc_idx"] = torch.from_numpy(exc_idx).pin_memory()
     pinned16["exc_val"] = torch.from_numpy(exc_val.view(np.int32)).pin_memory()
 

@@ -114,6 +114,18 @@ int vsv_expand_ops16(vsv_ctx* ctx, const uint16_t* ops16, int64_t n_ops, const i
 #define VSV_OPS8_D 47
 int vsv_expand_ops8(vsv_ctx* ctx, const uint8_t* ops8, int64_t n_ops, const int64_t* exc_idx,
                     const uint32_t* exc_val, int64_t n_exc, uint32_t* ops_out);
+/* Densest staging for noisy long reads: 12 bits per PAIR of ops (0.75 byte per op).  The CIGARs minimap2
+ * writes for ONT/CLR reads alternate a match run with a short indel, so (ops[2k], ops[2k+1]) is nearly
+ * always {M of 1..128, I or D of 1..8} in either order: token = (mlen-1) | (xlen-1) << 7 | is_D << 10 |
+ * indel_first << 11; token k occupies bits [12k, 12k+12) of the little-endian byte stream `ops12`, which is
+ * padded to a whole group of 8 tokens: vsv_ops12_bytes(n_ops) bytes, 4-byte aligned.  Every other pair has
+ * both full words in the exception list (exc_pair[i] = k ascending, exc_val[2i], exc_val[2i+1]).  Pairing
+ * is positional over the whole array (it ignores record boundaries).  Host side: volcanosv_b200.lib.pack_ops12. */
+#define VSV_OPS12_M 128
+#define VSV_OPS12_X 8
+int64_t vsv_ops12_bytes(int64_t n_ops);
+int vsv_expand_ops12(vsv_ctx* ctx, const uint8_t* ops12, int64_t n_ops, const int64_t* exc_pair,
+                     const uint32_t* exc_val, int64_t n_exc, uint32_t* ops_out);
 
 /* The two READ-BAM scanners in ONE pass over the packed ops (the ops are the bulk of the
  * bytes, so this halves HBM traffic of stage 1): stream "reads" == vsv_scan_cigar(

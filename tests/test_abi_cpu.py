@@ -98,3 +98,32 @@ def test_pack_ops8_layout():
     assert o8[(code == 0) & (ln == 1)].tolist() == [0] * int(((code == 0) & (ln == 1)).sum())
     assert np.all(o8[(code == 2) & (ln == 47)] == 253)
     assert np.array_equal(unpack_ops8(o8, ei, ev), ops)
+
+
+def test_pack_ops12_layout():
+    """ops12: 12 bits per {M 1..128, I/D 1..8} pair in either order, odd pairs in the exception list with both
+    words; token k at bits [12k, 12k+12) of the byte stream; inverse on the host."""
+    import numpy as np
+    from volcanosv_b200.lib import pack_ops12, unpack_ops12, ops12_bytes, load_library
+    ops = np.array([(5 << 4) | 0, (3 << 4) | 2,          # M5 D3  -> token 4 | 2<<7 | 1<<10
+                    (8 << 4) | 1, (128 << 4) | 0,        # I8 M128 -> 127 | 7<<7 | 1<<11
+                    (129 << 4) | 0, (1 << 4) | 1,        # M too long -> exception
+                    (4 << 4) | 4], np.uint32)            # lone soft clip at an odd tail -> exception
+    o12, ep, ev = pack_ops12(ops)
+    assert len(o12) == 12 == ops12_bytes(len(ops)) and list(ep) == [2, 3]
+    assert list(ev) == [(129 << 4) | 0, (1 << 4) | 1, (4 << 4) | 4, 0]
+    t0, t1 = 4 | (2 << 7) | (1 << 10), 127 | (7 << 7) | (1 << 11)
+    assert list(o12[:3]) == [t0 & 0xFF, (t0 >> 8) | ((t1 & 15) << 4), t1 >> 4]
+    assert np.array_equal(unpack_ops12(o12, len(ops), ep, ev), ops)
+    rng = np.random.default_rng(5)
+    for n in (0, 1, 16, 17, 4097):
+        m = rng.integers(1, 200, n).astype(np.uint32) << 4
+        x = (rng.integers(1, 12, n).astype(np.uint32) << 4) | rng.integers(1, 3, n).astype(np.uint32)
+        w = np.where((np.arange(n) + (np.arange(n) > n // 3)) % 2 == 0, m, x).astype(np.uint32)
+        for chunk in (8, 1 << 24):
+            o12, ep, ev = pack_ops12(w, chunk=chunk)
+            assert len(o12) == ops12_bytes(n) and np.all(np.diff(ep) > 0)
+            assert np.array_equal(unpack_ops12(o12, n, ep, ev), w)
+    lib = load_library()
+    for n in (0, 1, 2, 16, 17, 12345):
+        assert lib.vsv_ops12_bytes(n) == ops12_bytes(n)

@@ -283,6 +283,29 @@ def test_expand_ops8(ctx):
         assert np.array_equal(ctx.expand_ops8(o8, ei, ev), ops)
 
 
+def test_expand_ops12(ctx):
+    """vsv_expand_ops12 == the BAM-native words: alternating M / short-indel pairs in both phases, odd pairs
+    through the exception list, ragged tails and odd lengths."""
+    from volcanosv_b200.lib import pack_ops12, unpack_ops12
+    rng = np.random.default_rng(22)
+    for n in (0, 1, 2, 15, 16, 17, 31, 32, 33, 100003, 1 << 20):
+        code = rng.choice([0, 1, 2, 3, 4, 5, 8, 12], n).astype(np.uint32) if n else np.zeros(0, np.uint32)
+        ln = rng.integers(0, 200, n).astype(np.uint32)
+        ops = (ln << 4) | code
+        if n > 50:      # mostly minimap2-like: M, indel, M, indel ... with a phase flip in the middle
+            m = (rng.integers(1, 140, n).astype(np.uint32) << 4)
+            x = (rng.integers(1, 11, n).astype(np.uint32) << 4) | rng.integers(1, 3, n).astype(np.uint32)
+            alt = np.where(np.arange(n) % 2 == 0, m, x)
+            alt[n // 2:] = np.where(np.arange(n - n // 2) % 2 == (n // 2 + 1) % 2, m[n // 2:], x[n // 2:])
+            keep = rng.random(n) < 0.97
+            ops = np.where(keep, alt, ops)
+        o12, ep, ev = pack_ops12(ops)
+        if n > 50:
+            assert 0 < len(ep) < 0.35 * n
+        assert np.array_equal(unpack_ops12(o12, n, ep, ev), ops)
+        assert np.array_equal(ctx.expand_ops12(o12, n, ep, ev), ops)
+
+
 def test_record_range_parts_concatenate_to_the_whole(ctx):
     """Level-2 sharding (shard.split_records): scanning contiguous record ranges separately and
     concatenating in part order == scanning the chromosome batch at once (both fused streams)."""

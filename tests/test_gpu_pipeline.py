@@ -68,6 +68,14 @@ def test_compact_staging_gives_identical_results():
     e = sh.download(sh.run_safe())
     for k in a:
         assert np.array_equal(a[k], e[k], equal_nan=True) if a[k].dtype.kind == "f" else np.array_equal(a[k], e[k]), k
+    from volcanosv_b200.lib import pack_ops12
+    o12, ep, ev = pack_ops12(b["ops"])
+    b4 = {k: v for k, v in b.items() if k != "ops"}
+    b4.update(ops12=o12, exc_idx=ep, exc_val=ev)
+    sh.upload(b4, cands, n_ops=len(b["ops"]))
+    f = sh.download(sh.run_safe())
+    for k in a:
+        assert np.array_equal(a[k], f[k], equal_nan=True) if a[k].dtype.kind == "f" else np.array_equal(a[k], f[k]), k
 
 
 def test_shard_stream_overlapped_uploads_match_single_shard():

@@ -806,6 +806,80 @@ extern "C" int vsv_expand_ops8(vsv_ctx* ctx, const uint8_t* ops8, int64_t n_ops,
   return vsv_end(ctx);
 }
 
+// ops12: 12 bits per PAIR of ops (0.75 byte per op).  minimap2's long-read CIGARs alternate a match run with
+// a short indel, so the pair (ops[2k], ops[2k+1]) is almost always {M of 1..128, I/D of 1..8} in one of the two
+// orders: token = mlen-1 | (xlen-1) << 7 | (D ? 1 : 0) << 10 | (indel first ? 1 : 0) << 11, tokens packed
+// little-endian into the byte stream (token k = bits [12k, 12k+12)), the stream padded to a whole group of
+// 8 tokens (12 bytes).  Any other pair has both full words in the exception list.  One thread per group:
+// three LDG.32 in, four STG.128 out.  Pairing is positional over the whole ops array, so no prefix scan.
+__device__ __forceinline__ uint2 ops12_pair(uint32_t t) {
+  const uint32_t m = ((t & 127u) + 1u) << 4;
+  const uint32_t x = ((((t >> 7) & 7u) + 1u) << 4) | (1u + ((t >> 10) & 1u));
+  return (t & 0x800u) ? make_uint2(x, m) : make_uint2(m, x);
+}
+__global__ void __launch_bounds__(256) k_expand_ops12(const uint32_t* __restrict__ in, int64_t n_grp, int64_t n,
+                                                      uint32_t* __restrict__ out) {
+  const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= n_grp) return;
+  const uint32_t w0 = __ldg(in + 3 * g), w1 = __ldg(in + 3 * g + 1), w2 = __ldg(in + 3 * g + 2);
+  const uint32_t t[8] = {w0 & 0xFFFu, (w0 >> 12) & 0xFFFu, (w0 >> 24) | ((w1 & 0xFu) << 8), (w1 >> 4) & 0xFFFu,
+                         (w1 >> 16) & 0xFFFu, (w1 >> 28) | ((w2 & 0xFFu) << 4), (w2 >> 8) & 0xFFFu, w2 >> 20};
+  const int64_t i = g * 16;
+  if (i + 16 <= n) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const uint2 a = ops12_pair(t[2 * k]), b = ops12_pair(t[2 * k + 1]);
+      reinterpret_cast<uint4*>(out + i)[k] = make_uint4(a.x, a.y, b.x, b.y);
+    }
+  } else {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const uint2 a = ops12_pair(t[k]);
+      if (i + 2 * k < n) out[i + 2 * k] = a.x;
+      if (i + 2 * k + 1 < n) out[i + 2 * k + 1] = a.y;
+    }
+  }
+}
+__global__ void k_patch_pairs(const int64_t* __restrict__ pair, const uint32_t* __restrict__ val, int64_t n_exc, int64_t n,
+                              uint32_t* __restrict__ out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_exc) return;
+  const int64_t o = 2 * pair[i];
+  if (o < 0) return;
+  if (o < n) out[o] = val[2 * i];
+  if (o + 1 < n) out[o + 1] = val[2 * i + 1];
+}
+
+extern "C" int64_t vsv_ops12_bytes(int64_t n_ops) {
+  return n_ops <= 0 ? 0 : vsv_cdiv(vsv_cdiv(n_ops, 2), 8) * 12;
+}
+
+extern "C" int vsv_expand_ops12(vsv_ctx* ctx, const uint8_t* ops12, int64_t n_ops, const int64_t* exc_pair,
+                                const uint32_t* exc_val, int64_t n_exc, uint32_t* ops_out) {
+  VSV_TRY(vsv_begin(ctx));
+  if (n_ops < 0 || n_exc < 0 || (n_ops > 0 && (!ops12 || !ops_out)) || (n_exc > 0 && (!exc_pair || !exc_val)))
+    VSV_FAIL(ctx, VSV_E_ARG, "vsv_expand_ops12: bad argument");
+  if (n_ops == 0) return VSV_OK;
+  const int64_t n_bytes = vsv_ops12_bytes(n_ops), n_grp = n_bytes / 12;
+  const uint8_t* din;
+  const int64_t* dix;
+  const uint32_t* dvl;
+  uint32_t* dout;
+  VSV_TRY(vsv_in(ctx, ops12, (size_t)n_bytes, &din));
+  VSV_TRY(vsv_in(ctx, exc_pair, (size_t)n_exc, &dix));
+  VSV_TRY(vsv_in(ctx, exc_val, (size_t)(2 * n_exc), &dvl));
+  VSV_TRY(vsv_out(ctx, ops_out, (size_t)n_ops, &dout));
+  if ((reinterpret_cast<uintptr_t>(din) & 3u) || (reinterpret_cast<uintptr_t>(dout) & 15u))
+    VSV_FAIL(ctx, VSV_E_ARG, "vsv_expand_ops12: ops12 must be 4-byte aligned, ops_out 16-byte aligned");
+  VSV_TRY(vsv_t0(ctx));
+  VSV_LAUNCH(ctx, k_expand_ops12, (unsigned)vsv_cdiv(n_grp, 256), 256, 0, reinterpret_cast<const uint32_t*>(din), n_grp,
+             n_ops, dout);
+  if (n_exc > 0) VSV_LAUNCH(ctx, k_patch_pairs, (unsigned)vsv_cdiv(n_exc, 256), 256, 0, dix, dvl, n_exc, n_ops, dout);
+  VSV_TRY(vsv_t1(ctx));
+  VSV_TRY(vsv_out_done(ctx, ops_out, dout, (size_t)n_ops));
+  return vsv_end(ctx);
+}
+
 extern "C" int vsv_expand_ops16(vsv_ctx* ctx, const uint16_t* ops16, int64_t n_ops, const int64_t* exc_idx,
                                 const uint32_t* exc_val, int64_t n_exc, uint32_t* ops_out) {
   VSV_TRY(vsv_begin(ctx));

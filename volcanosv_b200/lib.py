@@ -51,6 +51,8 @@ SIGNATURES = {
     "vsv_scan_cigar": [_vp, _int, _int, _int, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _i64, C.POINTER(_i64), _vp, _vp, _vp],
     "vsv_expand_ops16": [_vp, _vp, _i64, _vp, _vp, _i64, _vp],
     "vsv_expand_ops8": [_vp, _vp, _i64, _vp, _vp, _i64, _vp],
+    "vsv_expand_ops12": [_vp, _vp, _i64, _vp, _vp, _i64, _vp],
+    "vsv_ops12_bytes": [_i64],
     "vsv_scan_reads_fused": [_vp, _int, _int, _int, _int, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _i64, C.POINTER(_i64),
                              _vp, _i64, C.POINTER(_i64), _vp, _vp, _vp],
     "vsv_merge_in_record": [_vp, _int, _vp, _i64, _vp, C.POINTER(_i64), _vp, C.POINTER(_i64)],
@@ -84,7 +86,7 @@ SIGNATURES = {
     "vsv_genotype": [_vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp],
 }
 _RESTYPE = {"vsv_ctx_destroy": None, "vsv_last_error": C.c_char_p, "vsv_version": C.c_char_p, "vsv_bam_close": None,
-            "vsv_bam_last_error": C.c_char_p}
+            "vsv_bam_last_error": C.c_char_p, "vsv_ops12_bytes": _i64}
 
 
 def load_library(path: Optional[str] = None):
@@ -216,6 +218,17 @@ class Context:
         ei, ev = _arr(exc_idx, np.int64), _arr(exc_val, np.uint32)
         out = _aligned_empty(len(o8), np.uint32)
         self._chk(self.lib.vsv_expand_ops8(self.h, _p(o8), len(o8), _p(ei), _p(ev), len(ei), _p(out)))
+        return out
+
+    def expand_ops12(self, ops12, n_ops, exc_pair, exc_val):
+        o12 = _arr(ops12, np.uint8)
+        if len(o12) != ops12_bytes(n_ops):
+            raise ValueError("expand_ops12: %d bytes for %d ops, expected %d" % (len(o12), n_ops, ops12_bytes(n_ops)))
+        if o12.ctypes.data % 16:
+            o12 = _aligned_copy(o12)
+        ei, ev = _arr(exc_pair, np.int64), _arr(exc_val, np.uint32)
+        out = _aligned_empty(int(n_ops), np.uint32)
+        self._chk(self.lib.vsv_expand_ops12(self.h, _p(o12), int(n_ops), _p(ei), _p(ev), len(ei), _p(out)))
         return out
 
     def scan_reads_fused(self, ops, op_off, pos, mapq, enable_cute=None, min_len_reads=30, min_mapq_reads=50,
@@ -493,6 +506,78 @@ def pack_ops8(ops, chunk: int = 1 << 24):
     exc_idx = np.concatenate(idx) if idx else np.zeros(0, np.int64)
     exc_val = ops[exc_idx].copy()
     return o8, exc_idx, exc_val
+
+
+OPS12_M, OPS12_X = 128, 8                 # include/volcanosv_b200.h: VSV_OPS12_*
+
+
+def ops12_bytes(n_ops: int) -> int:
+    """vsv_ops12_bytes: 12 bits per pair of ops, padded to a whole group of 8 tokens (12 bytes)."""
+    n_ops = int(n_ops)
+    return 0 if n_ops <= 0 else -(-(-(-n_ops // 2)) // 8) * 12
+
+
+def pack_ops12(ops, chunk: int = 1 << 24):
+    """Host packer of vsv_expand_ops12: (ops12, exc_pair, exc_val).  Token k of the pair (ops[2k], ops[2k+1]) =
+    {M of 1..128, I/D of 1..8} in either order: (mlen-1) | (xlen-1) << 7 | is_D << 10 | indel_first << 11, two
+    tokens per three bytes, little-endian; any other pair (and the lone last op of an odd array) goes to the
+    exception list with both full words.  `chunk` (even) pairs at a time keep the temporaries small."""
+    ops = np.ascontiguousarray(ops, dtype=np.uint32)
+    n = len(ops)
+    n_pair = (n + 1) // 2
+    o12 = _aligned_empty(ops12_bytes(n), np.uint8)
+    o12[:] = 0
+    chunk = max(8, chunk - chunk % 8)
+    idx = []
+    for a in range(0, n_pair, chunk):
+        b = min(n_pair, a + chunk)
+        first = ops[2 * a: 2 * b: 2]
+        second = np.zeros(b - a, np.uint32)
+        tail = ops[2 * a + 1: 2 * b: 2]
+        second[: len(tail)] = tail
+        c1, l1, c2, l2 = first & np.uint32(15), first >> np.uint32(4), second & np.uint32(15), second >> np.uint32(4)
+        indel_first = c1 != 0
+        cm, lm = np.where(indel_first, c2, c1), np.where(indel_first, l2, l1)
+        cx, lx = np.where(indel_first, c1, c2), np.where(indel_first, l1, l2)
+        ok = (cm == 0) & (lm >= 1) & (lm <= OPS12_M) & ((cx == 1) | (cx == 2)) & (lx >= 1) & (lx <= OPS12_X)
+        tok = ((lm - np.uint32(1)) | ((lx - np.uint32(1)) << np.uint32(7)) | ((cx == 2).astype(np.uint32) << np.uint32(10))
+               | (indel_first.astype(np.uint32) << np.uint32(11)))
+        tok = np.where(ok, tok, np.uint32(0))
+        if len(tok) % 2:
+            tok = np.append(tok, np.uint32(0))
+        t0, t1 = tok[0::2], tok[1::2]
+        out = o12[3 * (a // 2): 3 * (a // 2) + 3 * len(t0)].reshape(-1, 3)
+        np.copyto(out[:, 0], t0 & np.uint32(0xFF), casting="unsafe")
+        np.copyto(out[:, 1], (t0 >> np.uint32(8)) | ((t1 & np.uint32(15)) << np.uint32(4)), casting="unsafe")
+        np.copyto(out[:, 2], t1 >> np.uint32(4), casting="unsafe")
+        idx.append(np.flatnonzero(~ok).astype(np.int64) + a)
+    exc_pair = np.concatenate(idx) if idx else np.zeros(0, np.int64)
+    exc_val = np.zeros(2 * len(exc_pair), np.uint32)
+    exc_val[0::2] = ops[2 * exc_pair]
+    odd = 2 * exc_pair + 1
+    inside = odd < n
+    exc_val[1::2][inside] = ops[odd[inside]]
+    return o12, exc_pair, exc_val
+
+
+def unpack_ops12(o12, n_ops, exc_pair, exc_val):
+    """Inverse of pack_ops12 on the host (tests, debugging)."""
+    n_ops = int(n_ops)
+    b = np.asarray(o12, dtype=np.uint8).astype(np.uint32).reshape(-1, 3)
+    tok = np.empty(2 * len(b), np.uint32)
+    tok[0::2] = b[:, 0] | ((b[:, 1] & 15) << 8)
+    tok[1::2] = (b[:, 1] >> 4) | (b[:, 2] << 4)
+    m = ((tok & 127) + 1) << 4
+    x = ((((tok >> 7) & 7) + 1) << 4) | (1 + ((tok >> 10) & 1))
+    swap = (tok >> 11) == 1
+    out = np.empty(2 * len(tok), np.uint32)
+    out[0::2] = np.where(swap, x, m)
+    out[1::2] = np.where(swap, m, x)
+    ep = np.asarray(exc_pair, dtype=np.int64)
+    ev = np.asarray(exc_val, dtype=np.uint32)
+    out[2 * ep] = ev[0::2]
+    out[2 * ep + 1] = ev[1::2]
+    return out[:n_ops].copy()
 
 
 def unpack_ops8(o8, exc_idx, exc_val):

@@ -107,7 +107,21 @@ class ChromShard:
 
         with torch.cuda.stream(stream if stream is not None else torch.cuda.current_stream()):
             expand = None
-            if "ops16" in batch or "ops8" in batch:
+            if "ops12" in batch:
+                # densest staging (vsv_expand_ops12): 12 bits per pair of ops + both words of the odd pairs
+                src12 = batch["ops12"]
+                if isinstance(src12, np.ndarray):
+                    src12 = torch.from_numpy(np.ascontiguousarray(src12.view(np.uint8)))
+                n_ops = int(n_ops if n_ops is not None else batch["op_off"][-1])
+                if src12.numel() != L.ops12_bytes(n_ops):
+                    raise ValueError("ops12: %d bytes for %d ops" % (src12.numel(), n_ops))
+                o12 = self._buf("in_ops12", src12.numel(), src12.dtype)
+                o12[: src12.numel()].copy_(src12, non_blocking=True)
+                self.h2d_bytes += src12.numel() * src12.element_size()
+                ei = put("in_exc_idx", batch["exc_idx"]) if len(batch["exc_idx"]) else None
+                put("in_exc_val", batch["exc_val"]) if len(batch["exc_val"]) else None
+                expand = (o12, 0 if ei is None else ei.numel(), self._buf("in_ops", n_ops, torch.int32), 12)
+            elif "ops16" in batch or "ops8" in batch:
                 # compact staging (include/volcanosv_b200.h: vsv_expand_ops16 / vsv_expand_ops8): 2 bytes or
                 # 1 byte per op over PCIe, widened on the device into the BAM-native u32 array the scanners read
                 wide = "ops16" in batch
@@ -145,7 +159,7 @@ class ChromShard:
         done.synchronize()
         if expand is not None:
             o16, n_exc, ops, wide = expand
-            fn = self.lib.vsv_expand_ops16 if wide else self.lib.vsv_expand_ops8
+            fn = self.lib.vsv_expand_ops12 if wide == 12 else (self.lib.vsv_expand_ops16 if wide else self.lib.vsv_expand_ops8)
             self._chk(fn(self.h, _dp(o16), self.n_ops, _dp(self.d["in_exc_idx"]) if n_exc else None,
                     _dp(self.d["in_exc_val"]) if n_exc else None, n_exc, _dp(ops)))
             self.ctx.sync()
