@@ -206,7 +206,7 @@ def main():
 
     # host staging format of the end-to-end path: ops as 16-bit words + a sparse exception list
     # (vsv_expand_ops16); produced by the host packer once, like the BAM decode it follows
-    from volcanosv_b200.lib import pack_ops16, pack_ops8, pack_ops12
+    from volcanosv_b200.lib import pack_ops16, pack_ops8, pack_ops12_native
     # densest staging format that fits the data: ops8 (1 B/op; noisy long reads: ~1 % exceptions) when fewer than
     # 3 % of the ops need the exception list, else ops16 (2 B/op; HiFi / =,X CIGARs).  The native BAM feeder
     # (vsv_bam_chrom_fill) writes either format straight from the BAM records, so packing is not an extra pass.
@@ -217,7 +217,7 @@ def main():
     bytes8 = o8.nbytes + 12 * len(exc_idx)
     o12 = None
     if args.staging in ("auto", "ops12") and len(exc_idx) < 0.03 * n_ops:
-        o12, exc_pair, exc_val12 = pack_ops12(batch["ops"])
+        o12, exc_pair, exc_val12 = pack_ops12_native(batch["ops"])   # vsv_pack_ops12 on the host threads
         if args.staging == "auto" and o12.nbytes + 16 * len(exc_pair) >= bytes8:
             o12 = None
     if o12 is not None:

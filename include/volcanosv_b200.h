@@ -126,6 +126,12 @@ int vsv_expand_ops8(vsv_ctx* ctx, const uint8_t* ops8, int64_t n_ops, const int6
 int64_t vsv_ops12_bytes(int64_t n_ops);
 int vsv_expand_ops12(vsv_ctx* ctx, const uint8_t* ops12, int64_t n_ops, const int64_t* exc_pair,
                      const uint32_t* exc_val, int64_t n_exc, uint32_t* ops_out);
+/* Host packer of that format (no CUDA; threads over groups of 8 tokens, n_threads <= 0 = all cores): fills
+ * ops12 (vsv_ops12_bytes(n_ops) bytes) and the ascending exception list; *n_exc = pairs listed.  VSV_E_CAPACITY
+ * with *n_exc = the capacity needed when exc_cap is too small (ops12 is complete then).  Errors:
+ * vsv_bam_last_error().  Same bytes as volcanosv_b200.lib.pack_ops12 (the numpy statement of the format). */
+int vsv_pack_ops12(const uint32_t* ops, int64_t n_ops, int n_threads, uint8_t* ops12, int64_t* exc_pair,
+                   uint32_t* exc_val, int64_t exc_cap, int64_t* n_exc);
 
 /* The two READ-BAM scanners in ONE pass over the packed ops (the ops are the bulk of the
  * bytes, so this halves HBM traffic of stage 1): stream "reads" == vsv_scan_cigar(

@@ -127,3 +127,32 @@ def test_pack_ops12_layout():
     lib = load_library()
     for n in (0, 1, 2, 16, 17, 12345):
         assert lib.vsv_ops12_bytes(n) == ops12_bytes(n)
+
+
+def test_native_ops12_packer_matches_the_numpy_statement():
+    """vsv_pack_ops12 (host threads, no GPU) writes the same bytes and the same exception list as lib.pack_ops12,
+    whatever the thread count; capacity query pattern."""
+    import ctypes as C
+    import numpy as np
+    from volcanosv_b200 import lib as L
+    from volcanosv_b200 import synth
+    rng = np.random.default_rng(12)
+    cases = [np.zeros(0, np.uint32), np.array([(7 << 4) | 4], np.uint32),
+             synth.synth_records(77, 300, "ont")["ops"], synth.synth_records(78, 300, "hifi", eqx=True)["ops"][:100001]]
+    n = 70001
+    m = rng.integers(1, 140, n).astype(np.uint32) << 4
+    x = (rng.integers(1, 11, n).astype(np.uint32) << 4) | rng.integers(1, 3, n).astype(np.uint32)
+    cases.append(np.where((np.arange(n) + (np.arange(n) > n // 2)) % 2 == 0, m, x).astype(np.uint32))
+    for ops in cases:
+        want = L.pack_ops12(ops)
+        for threads in (1, 3, 0):
+            got = L.pack_ops12_native(ops, threads=threads)
+            for a, b in zip(got, want):
+                assert a.dtype == b.dtype and np.array_equal(a, b)
+    lib = L.load_library()
+    ops = cases[-1]
+    o12 = np.empty(L.ops12_bytes(len(ops)), np.uint8)
+    n_exc = C.c_int64(0)
+    rc = lib.vsv_pack_ops12(L._p(ops), len(ops), 2, L._p(o12), None, None, 0, C.byref(n_exc))
+    assert rc == L.E_CAPACITY and n_exc.value == len(L.pack_ops12(ops)[1]) and np.array_equal(o12, L.pack_ops12(ops)[0])
+    assert lib.vsv_pack_ops12(None, 5, 1, None, None, None, 0, C.byref(n_exc)) == L.E_ARG

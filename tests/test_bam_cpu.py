@@ -41,6 +41,9 @@ def check(bam, sam, compact):
         if compact == 8:
             assert np.all(np.diff(d["exc_idx"]) > 0) and np.all(d["ops8"][d["exc_idx"]] == 0xFF)
             ops = L.unpack_ops8(d["ops8"], d["exc_idx"], d["exc_val"])
+        elif compact == 12:
+            assert np.all(np.diff(d["exc_idx"]) > 0) and len(d["ops12"]) == L.ops12_bytes(d["n_ops"])
+            ops = L.unpack_ops12(d["ops12"], d["n_ops"], d["exc_idx"], d["exc_val"])
         elif compact:
             ops = d["ops16"].astype(np.uint32)
             assert np.all(np.diff(d["exc_idx"]) > 0)
@@ -62,7 +65,7 @@ def check(bam, sam, compact):
     bf.close()
 
 
-@pytest.mark.parametrize("compact", [False, True, 8])
+@pytest.mark.parametrize("compact", [False, True, 8, 12])
 def test_reads_and_contigs_round_trip(tmp_path, compact):
     for name in ("reads", "contigs"):
         bam = str(tmp_path / (name + ".bam"))

@@ -623,6 +623,70 @@ extern "C" int vsv_bam_chrom_fill(vsv_bam* b, int tid, int32_t* pos, uint8_t* ma
   return VSV_OK;
 }
 
+// Host packer of the ops12 staging format (vsv_expand_ops12): 12 bits per {M 1..128, I/D 1..8} pair in either
+// order, both words of every other pair in the exception list.  Threads take contiguous ranges of 8-token
+// groups (12 output bytes each, so no two threads share a byte), collect their exceptions locally and copy
+// them out in range order: the list is ascending and the result does not depend on the thread count.
+extern "C" int vsv_pack_ops12(const uint32_t* ops, int64_t n_ops, int n_threads, uint8_t* ops12, int64_t* exc_pair,
+                              uint32_t* exc_val, int64_t exc_cap, int64_t* n_exc) {
+  if (n_ops < 0 || exc_cap < 0 || !n_exc || (n_ops > 0 && (!ops || !ops12)) || (exc_cap > 0 && (!exc_pair || !exc_val))) {
+    g_bam_err = "vsv_pack_ops12: bad argument";
+    return VSV_E_ARG;
+  }
+  *n_exc = 0;
+  if (n_ops == 0) return VSV_OK;
+  const int64_t n_pair = (n_ops + 1) / 2, n_grp = (n_pair + 7) / 8;
+  const int T = (int)std::max<int64_t>(1, std::min<int64_t>(n_threads > 0 ? n_threads : (int)std::max(1u, std::thread::hardware_concurrency()),
+                                                            (n_grp + 4095) / 4096));
+  std::vector<std::vector<int64_t>> found((size_t)T);
+  parallel_for(n_grp, T, [&](int64_t a, int64_t e, int t) {
+    std::vector<int64_t>& mine = found[(size_t)t];
+    for (int64_t g = a; g < e; ++g) {
+      uint32_t tok[8];
+      for (int k = 0; k < 8; ++k) {
+        const int64_t p = g * 8 + k;
+        tok[k] = 0;
+        if (p >= n_pair) continue;
+        const uint32_t w0 = ops[2 * p], w1 = 2 * p + 1 < n_ops ? ops[2 * p + 1] : 0u;
+        const bool indel_first = (w0 & 15u) != 0u;
+        const uint32_t m = indel_first ? w1 : w0, x = indel_first ? w0 : w1;
+        const uint32_t lm = m >> 4, lx = x >> 4, cx = x & 15u;
+        if ((m & 15u) == 0u && lm >= 1u && lm <= (uint32_t)VSV_OPS12_M && (cx == 1u || cx == 2u) && lx >= 1u &&
+            lx <= (uint32_t)VSV_OPS12_X)
+          tok[k] = (lm - 1u) | ((lx - 1u) << 7) | ((cx == 2u ? 1u : 0u) << 10) | ((indel_first ? 1u : 0u) << 11);
+        else
+          mine.push_back(p);
+      }
+      uint8_t* o = ops12 + g * 12;
+      for (int k = 0; k < 4; ++k) {
+        const uint32_t t0 = tok[2 * k], t1 = tok[2 * k + 1];
+        o[3 * k] = (uint8_t)(t0 & 0xFFu);
+        o[3 * k + 1] = (uint8_t)((t0 >> 8) | ((t1 & 15u) << 4));
+        o[3 * k + 2] = (uint8_t)(t1 >> 4);
+      }
+    }
+  });
+  std::vector<int64_t> start((size_t)T + 1, 0);
+  for (int t = 0; t < T; ++t) start[(size_t)t + 1] = start[(size_t)t] + (int64_t)found[(size_t)t].size();
+  *n_exc = start[(size_t)T];
+  if (*n_exc > exc_cap) {
+    g_bam_err = "vsv_pack_ops12: exception list too small";
+    return VSV_E_CAPACITY;
+  }
+  parallel_for(T, T, [&](int64_t a, int64_t e, int) {
+    for (int64_t t = a; t < e; ++t) {
+      int64_t o = start[(size_t)t];
+      for (int64_t p : found[(size_t)t]) {
+        exc_pair[o] = p;
+        exc_val[2 * o] = ops[2 * p];
+        exc_val[2 * o + 1] = 2 * p + 1 < n_ops ? ops[2 * p + 1] : 0u;
+        ++o;
+      }
+    }
+  });
+  return VSV_OK;
+}
+
 // SEQ of record i (file order) of reference `tid`, decoded to ASCII: the sparse accesses of
 // `read.seq` / `read.query_sequence` (SE:452, ECS_H:642-700) without materialising every read's bases.
 extern "C" int vsv_bam_record_seq(vsv_bam* b, int tid, int64_t i, char* out, int64_t cap, int64_t* len) {

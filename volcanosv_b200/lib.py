@@ -53,6 +53,7 @@ SIGNATURES = {
     "vsv_expand_ops8": [_vp, _vp, _i64, _vp, _vp, _i64, _vp],
     "vsv_expand_ops12": [_vp, _vp, _i64, _vp, _vp, _i64, _vp],
     "vsv_ops12_bytes": [_i64],
+    "vsv_pack_ops12": [_vp, _i64, _int, _vp, _vp, _vp, _i64, C.POINTER(_i64)],
     "vsv_scan_reads_fused": [_vp, _int, _int, _int, _int, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _i64, C.POINTER(_i64),
                              _vp, _i64, C.POINTER(_i64), _vp, _vp, _vp],
     "vsv_merge_in_record": [_vp, _int, _vp, _i64, _vp, C.POINTER(_i64), _vp, C.POINTER(_i64)],
@@ -424,7 +425,8 @@ class BamFile:
 
     def chrom(self, name_or_tid, compact=False, want_seq: bool = True):
         """Columns of one reference: dict(pos, mapq, flag, qlen, op_off, ops | ops16 | ops8 (+ exc_idx, exc_val),
-        name_off, names, seq_off, seq, sa_off, sa).  compact: False (u32 ops), True / 16 (ops16), 8 (ops8)."""
+        name_off, names, seq_off, seq, sa_off, sa).  compact: False (u32 ops), True / 16 (ops16), 8 (ops8),
+        12 (ops12: the u32 words of the feeder packed by vsv_pack_ops12; exc_idx holds PAIR indices, n_ops the op count)."""
         tid = name_or_tid if isinstance(name_or_tid, int) else [r[0] for r in self.refs].index(name_or_tid)
         sizes = np.zeros(5, np.int64)
         self._chk(self.lib.vsv_bam_chrom_sizes(self.h, tid, _p(sizes)))
@@ -434,7 +436,12 @@ class BamFile:
                  seq_off=np.empty(n + 1, np.int64), seq=np.empty(sb if want_seq else 0, np.uint8),
                  sa_off=np.empty(n + 1, np.int64), sa=np.empty(ab, np.uint8))
         n_exc = _i64(0)
-        if compact:
+        if compact == 12:
+            ops = _aligned_empty(n_ops, np.uint32)
+            self._chk(self._fill(tid, d, ops, None, 0, n_exc, want_seq))
+            d["ops12"], d["exc_idx"], d["exc_val"] = pack_ops12_native(ops)
+            d["n_ops"] = n_ops
+        elif compact:
             key = "ops8" if compact == 8 else "ops16"
             d[key] = _aligned_empty(n_ops, np.uint8 if compact == 8 else np.uint16)
             cap = max(1024, n_ops // (32 if compact == 8 else 256))
@@ -558,6 +565,26 @@ def pack_ops12(ops, chunk: int = 1 << 24):
     inside = odd < n
     exc_val[1::2][inside] = ops[odd[inside]]
     return o12, exc_pair, exc_val
+
+
+def pack_ops12_native(ops, threads: int = 0):
+    """vsv_pack_ops12: the same (ops12, exc_pair, exc_val) as pack_ops12, packed by the library's host threads
+    (no GPU involved): seconds -> tenths of a second for a chromosome of long reads."""
+    lib = load_library()
+    ops = np.ascontiguousarray(ops, dtype=np.uint32)
+    n = len(ops)
+    o12 = _aligned_empty(ops12_bytes(n), np.uint8)
+    cap = max(1024, n // 64)
+    while True:
+        ep, ev, n_exc = np.empty(cap, np.int64), np.empty(2 * cap, np.uint32), _i64(0)
+        rc = lib.vsv_pack_ops12(_p(ops), n, int(threads), _p(o12), _p(ep), _p(ev), cap, C.byref(n_exc))
+        if rc == E_CAPACITY:
+            cap = int(n_exc.value)
+            continue
+        if rc != 0:
+            raise VsvError(rc, (lib.vsv_bam_last_error() or b"").decode())
+        k = int(n_exc.value)
+        return o12, ep[:k].copy(), ev[: 2 * k].copy()
 
 
 def unpack_ops12(o12, n_ops, exc_pair, exc_val):
