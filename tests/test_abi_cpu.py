@@ -156,3 +156,26 @@ def test_native_ops12_packer_matches_the_numpy_statement():
     rc = lib.vsv_pack_ops12(L._p(ops), len(ops), 2, L._p(o12), None, None, 0, C.byref(n_exc))
     assert rc == L.E_CAPACITY and n_exc.value == len(L.pack_ops12(ops)[1]) and np.array_equal(o12, L.pack_ops12(ops)[0])
     assert lib.vsv_pack_ops12(None, 5, 1, None, None, None, 0, C.byref(n_exc)) == L.E_ARG
+
+
+def test_ops12_round_trip_property():
+    """Any u32 ops array survives pack -> unpack in both packers (hypothesis: arbitrary words, skewed to the
+    M / short-indel alphabet so that tokens, both orders and exceptions all occur)."""
+    import numpy as np
+    from hypothesis import given, settings, strategies as st
+    from volcanosv_b200 import lib as L
+    word = st.one_of(
+        st.builds(lambda ln: (ln << 4), st.integers(0, 140)),
+        st.builds(lambda ln, c: (ln << 4) | c, st.integers(0, 10), st.sampled_from([1, 2])),
+        st.integers(0, 2 ** 32 - 1))
+
+    @settings(max_examples=150, deadline=None)
+    @given(st.lists(word, max_size=70))
+    def run(words):
+        ops = np.array(words, dtype=np.uint32)
+        a = L.pack_ops12(ops, chunk=8)
+        b = L.pack_ops12_native(ops, threads=2)
+        assert all(np.array_equal(x, y) for x, y in zip(a, b))
+        assert np.array_equal(L.unpack_ops12(a[0], len(ops), a[1], a[2]), ops)
+
+    run()
