@@ -1,13 +1,18 @@
 #!/usr/bin/env python
 """Benchmark of the large-indel hot path (BASELINE.json metric: alignment records/s, with
-genotyped candidates/s beside it) on synthetic chr10 ONT-shaped alignments.
+genotyped candidates/s beside it) on synthetic alignments of the shapes BASELINE.json names.
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+                    [--workload chr10-ont|chr10-hifi|chr10-clr|wgs-hifi|wgs-ont|sweep]
 
-One "step" = one pass of the whole hot path (ERS scan -> cuteSV-style scan + merge ->
-.sigs order/grouping -> FP-filter / coverage / support joins -> spanning depth ->
-genotype) over one chromosome-sized shard.  N>1 (torchrun): every rank owns one shard on
-its own GPU (independent shards, no collective on the data path) -> weak scaling.
+chr10-*  one "step" = one pass of the whole read-side hot path over one chromosome shard: both read scanners
+         in one pass over the CIGAR ops, split pairs, SA analysis, in-read merge, one sort of all tables,
+         sort -u, unique signatures, then FP support / coverage / supporting signatures / spanning depth /
+         genotype for the candidate table (vsv_shard_scan + vsv_shard_candidates; ONE host sync per step, at
+         its end).  N > 1: every rank owns one shard (weak scaling, no collective on the data path).
+wgs-*    one step = the 22 autosomes, split over the N ranks by LPT on the op counts (strong scaling).
+sweep    genotyping stress grid (BASELINE config 5): candidates/s for 10^4..10^7 candidates x 10^6..10^8 reads,
+         candidates split over the ranks by position.
 Prints ONE JSON line on rank 0.
 """
 from __future__ import annotations
@@ -26,19 +31,27 @@ sys.path.insert(0, ROOT)
 
 METRIC = "alignment records/s"
 UNIT = "records/s"
+HG19 = [249250621, 243199373, 198022430, 191154276, 180915260, 171115067, 159138663, 146364022, 141213431, 135534747,
+        135006516, 133851895, 115169878, 107349540, 102531392, 90354753, 81195210, 78077248, 59128983, 63025520,
+        48129895, 51304566]          # LI/header:5-26
+COV = {"ont": 50, "hifi": 30, "clr": 89}
+DTYPE = {"ont": "ONT", "hifi": "Hifi", "clr": "CLR"}
 
 
-def make_workload(profile: str, scale: float, rank: int, n_cand: int):
-    """chr10-shaped shard: records in 8 genomic windows (bounded generator memory)."""
+# --------------------------------------------------------------------------------------------- workloads
+def make_chrom(profile: str, chrom_len: int, n_total: int, seed: int, chunks: int = 8):
+    """One chromosome-shaped batch: records generated in `chunks` genomic windows (bounded generator memory),
+    read names interned, next-same-name links (ERS:227-237) and SA tags for 8 % of the primary reads."""
     from volcanosv_b200 import synth
-    n_total = max(64, int(synth.n_records(profile) * scale))
-    parts, chunks = [], 8
-    L = synth.CHR10_LEN
+    from volcanosv_b200.lib import next_same_name
+    parts = []
+    n_total = max(64, n_total)
     for c in range(chunks):
         n = n_total // chunks
         # CIGAR alphabet as the aligners of each data type write it: minimap2 (ONT, CLR) uses M; pbmm2 (HiFi) =/X
-        b = synth.synth_records(1000 * rank + 10 + c, n, profile, chrom_len=L // chunks, eqx=(profile == "hifi"))
-        b["pos"] = (b["pos"].astype(np.int64) + c * (L // chunks)).astype(np.int32)
+        b = synth.synth_records(seed + c, n, profile, chrom_len=chrom_len // chunks, eqx=(profile == "hifi"))
+        b["pos"] = (b["pos"].astype(np.int64) + c * (chrom_len // chunks)).astype(np.int32)
+        b["name_id"] = (b["name_id"].astype(np.int64) + c * n).astype(np.int32)       # names are local to a window
         parts.append(b)
     batch = {}
     off, tot = [np.zeros(1, np.int64)], 0
@@ -48,9 +61,33 @@ def make_workload(profile: str, scale: float, rank: int, n_cand: int):
     batch["op_off"] = np.concatenate(off)
     for k in ("ops", "pos", "mapq", "qlen", "flag", "name_id"):
         batch[k] = np.concatenate([b[k] for b in parts])
-    pos, svlen, typ, gt = synth.synth_candidates(77 + rank, n_cand)
-    cands = dict(pos=pos, svlen=svlen, type=typ, gt=gt)
-    return batch, cands
+    batch["next_same_name"] = next_same_name(batch["name_id"])
+    synth.add_sa(batch, np.random.default_rng(seed + 99), frac=0.08)
+    return batch
+
+
+def make_cands(seed, n, chrom_len):
+    from volcanosv_b200 import synth
+    pos, svlen, typ, gt = synth.synth_candidates(seed, n, chrom_len=chrom_len)
+    return dict(pos=pos, svlen=svlen, type=typ, gt=gt)
+
+
+def prefix(batch, m):
+    """The first m records of a batch as views (no copy of the ops): a smaller chromosome of the same shape."""
+    e = int(batch["op_off"][m])
+    out = dict(ops=batch["ops"][:e], op_off=batch["op_off"][: m + 1])
+    for k in ("pos", "mapq", "qlen", "flag", "name_id"):
+        out[k] = batch[k][:m]
+    nx = batch["next_same_name"][:m].copy()
+    nx[nx >= m] = -1
+    out["next_same_name"] = nx
+    k = int(np.searchsorted(batch["sa_rec"], m))
+    out["sa_rec"], out["sa_off"] = batch["sa_rec"][:k], batch["sa_off"][: k + 1]
+    ee = int(batch["sa_off"][k])
+    for c in ("chrom", "pos", "strand", "first_s", "last_s", "bias", "mapq"):
+        out["sa_" + c] = batch["sa_" + c][:ee]
+    out["sa_self_chrom"] = batch.get("sa_self_chrom", 0)
+    return out
 
 
 class ClockSampler(threading.Thread):
@@ -94,89 +131,137 @@ class ClockSampler(threading.Thread):
                     samples=len(s))
 
 
+# --------------------------------------------------------------------------------------------- CPU arm
+def cpu_step(batch, cands, thr, threads):
+    """The same stage list on the host: oracle C port (scan, merge, joins, depth, genotype on `threads` threads),
+    numpy for sort / group / split pairs, Python for the SA rule set."""
+    from oracle import c_oracle as CO
+    return CO.shard_step2(batch, cands, thr[0], thr[1], threads=threads)
+
+
 def cpu_baseline(batch, cands, thr, target_s=12.0, threads=None):
-    """Oracle C port (oracle/vsv_oracle_c.c) timed on a bounded prefix of the workload."""
+    """Oracle port timed on a bounded prefix of the workload (all host threads for the threaded parts)."""
     from oracle import c_oracle as CO
     threads = threads or CO.num_threads()
     n = len(batch["pos"])
 
-    def prefix(m):
-        e = int(batch["op_off"][m])
-        b = dict(ops=batch["ops"][:e], op_off=batch["op_off"][: m + 1], pos=batch["pos"][:m], mapq=batch["mapq"][:m],
-                 qlen=batch["qlen"][:m])
-        hi = int(batch["pos"][m - 1])
-        keep = cands["pos"] <= hi
-        c = {k: np.ascontiguousarray(v[keep]) for k, v in cands.items()}
-        return b, c
+    def sample(m):
+        b = prefix(batch, m)
+        keep = cands["pos"] <= int(batch["pos"][m - 1])
+        return b, {k: np.ascontiguousarray(v[keep]) for k, v in cands.items()}
 
     m = max(64, n // 64)
-    b, c = prefix(m)
+    b, c = sample(m)
     t0 = time.perf_counter()
-    CO.shard_step(b, c, thr[0], thr[1], threads=threads)
+    cpu_step(b, c, thr, threads)
     dt = time.perf_counter() - t0
     frac = min(1.0, (m / n) * target_s / max(dt, 1e-4))
     m2 = int(min(n, max(m, n * frac)))
     if m2 > m * 1.5:
-        b, c = prefix(m2)
+        b, c = sample(m2)
         t0 = time.perf_counter()
-        CO.shard_step(b, c, thr[0], thr[1], threads=threads)
+        cpu_step(b, c, thr, threads)
         dt = time.perf_counter() - t0
         m = m2
     return dict(value=m / dt, unit=UNIT, cores=threads, kind="port",
-                sample="first %d of %d records (%.1f%% of the shard, %d candidates), oracle C port, %.2f s" %
-                       (m, n, 100.0 * m / n, len(c["pos"]), dt)), m, dt
+                sample="first %d of %d records (%.1f%% of the shard, %d candidates), oracle port (C: scan/merge/joins/depth/"
+                       "genotype on %d threads; numpy: sort/group/split pairs on 1; Python: SA rules), %.2f s" %
+                       (m, n, 100.0 * m / n, len(c["pos"]), threads, dt)), m, (b, c)
 
 
+def sweep_grid(scale):
+    reads = [10 ** 6, 10 ** 7, 10 ** 8]
+    cands = [10 ** 4, 10 ** 5, 10 ** 6, 10 ** 7]
+    if scale < 1:
+        reads = [max(1000, int(r * scale)) for r in reads]
+        cands = [max(100, int(c * scale)) for c in cands]
+    return reads, cands
+
+
+# --------------------------------------------------------------------------------------------- main
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--profile", default="ont", choices=["ont", "hifi", "clr"])
-    ap.add_argument("--scale", type=float, default=1.0, help="fraction of the chr10 shard (tests use < 1)")
+    ap.add_argument("--workload", default=None, choices=["chr10-ont", "chr10-hifi", "chr10-clr", "wgs-hifi", "wgs-ont", "sweep"])
+    ap.add_argument("--profile", default=None, choices=["ont", "hifi", "clr"], help="alias of --workload chr10-<profile>")
+    ap.add_argument("--scale", type=float, default=1.0, help="fraction of the named workload (tests use < 1)")
     ap.add_argument("--cands", type=int, default=3000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--staging", default="auto", choices=["auto", "ops12", "ops8"],
-                    help="host staging format of the end-to-end leg (auto = the densest that fits the data)")
     args = ap.parse_args()
-
+    if args.workload is None:
+        args.workload = "chr10-%s" % (args.profile or "ont")
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
-    dtype = {"ont": "ONT", "hifi": "Hifi", "clr": "CLR"}[args.profile]
+    if args.workload == "sweep":
+        return run_sweep(args, rank, world, local)
+    kind, profile = args.workload.split("-")
+    dtype = DTYPE[profile]
     from volcanosv_b200.pipeline import GT_THRESHOLDS
     thr = (GT_THRESHOLDS[dtype]["DEL"], GT_THRESHOLDS[dtype]["INS"])
-    workload = "chr10 %s %dx single-chromosome large-indel detection, synthetic (scale %.3g)" % (
-        dtype, {"ont": 50, "hifi": 30, "clr": 89}[args.profile], args.scale)
+    from volcanosv_b200 import synth
+    wgs = kind == "wgs"
+    if wgs:
+        workload = "WGS %s %dx, 22 autosomes (hg19 lengths), large-indel hot path sharded by chromosome, synthetic (scale %.3g)" % (
+            dtype, COV[profile], args.scale)
+    else:
+        workload = "chr10 %s %dx single-chromosome large-indel detection, synthetic (scale %.3g)" % (dtype, COV[profile], args.scale)
+
+    # ---- the shards of this process ------------------------------------------------------------------
+    # chr10-*: one chr10 shard per rank.  wgs-*: a chr1-sized master batch; chromosome c is its first n_c records
+    # (n_c proportional to the chromosome length, so the prefix spans ~ the chromosome), i.e. 22 shards of the named
+    # shape whose CIGAR content overlaps -- what a throughput measurement needs, generated in minutes.
+    if wgs:
+        master_len = HG19[0]
+        n_master = max(64, int(synth.n_records(profile, master_len) * args.scale))
+        master = make_chrom(profile, master_len, n_master, 4242)
+        n_master = len(master["pos"])
+        chrom_n = [min(n_master, max(32, int(n_master * L / master_len))) for L in HG19]
+        chrom_ops = [int(master["op_off"][m]) for m in chrom_n]
+        from volcanosv_b200.shard import assign_lpt
+        plan = assign_lpt({c: float(chrom_ops[c]) for c in range(22)}, world)
+        mine = sorted(plan[rank])
+        loads = [sum(chrom_ops[c] for c in p) for p in plan]
+        lpt = dict(max_over_mean=max(loads) / (sum(loads) / world), chroms_per_rank=[len(p) for p in plan])
+        shards = [(prefix(master, chrom_n[c]), make_cands(500 + c, max(16, int(args.cands * HG19[c] / HG19[9])), int(master["pos"][chrom_n[c] - 1])))
+                  for c in mine]
+        total_rec, total_ops = sum(chrom_n), sum(chrom_ops)
+    else:
+        n_total = max(64, int(synth.n_records(profile) * args.scale))
+        b = make_chrom(profile, synth.CHR10_LEN, n_total, 1000 * (rank if args.impl == "ours" else 0) + 10)
+        shards = [(b, make_cands(77 + (rank if args.impl == "ours" else 0), args.cands, synth.CHR10_LEN))]
+        total_rec, total_ops = world * len(b["pos"]), world * int(b["op_off"][-1])
+        lpt = None
 
     # ------------------------------------------------------------------ reference arm
     if args.impl == "reference":
         if rank != 0:
             return
-        batch, cands = make_workload(args.profile, args.scale, 0, args.cands)
-        from oracle import c_oracle as CO
-        base, m, _ = cpu_baseline(batch, cands, thr, target_s=8.0)
+        if wgs:
+            # the arm runs the shards of ONE process at a time; sample the largest chromosome this arm can bound
+            ref_b, ref_c = prefix(master, chrom_n[20]), make_cands(520, max(16, int(args.cands * HG19[20] / HG19[9])), int(master["pos"][chrom_n[20] - 1]))
+        else:
+            ref_b, ref_c = shards[0]
+        base, m, (sb, sc) = cpu_baseline(ref_b, ref_c, thr, target_s=8.0)
         times = []
-        e = int(batch["op_off"][m])
-        b = dict(ops=batch["ops"][:e], op_off=batch["op_off"][: m + 1], pos=batch["pos"][:m], mapq=batch["mapq"][:m],
-                 qlen=batch["qlen"][:m])
-        keep = cands["pos"] <= int(batch["pos"][m - 1])
-        c = {k: np.ascontiguousarray(v[keep]) for k, v in cands.items()}
         for i in range(args.warmup + args.steps):
             t0 = time.perf_counter()
-            CO.shard_step(b, c, thr[0], thr[1], threads=base["cores"])
+            cpu_step(sb, sc, thr, base["cores"])
             if i >= args.warmup:
                 times.append(time.perf_counter() - t0)
         dt = sum(times) / max(1, len(times))
         v = m / dt
         base["value"] = v
         print(json.dumps(dict(impl="reference", metric=METRIC, value=v, unit=UNIT, n_gpus=args.gpus, steps=args.steps,
-                              warmup=args.warmup, ms_per_step=dt * 1e3, higher_is_better=True, scaling="weak",
+                              warmup=args.warmup, ms_per_step=dt * 1e3, higher_is_better=True, scaling="strong" if wgs else "weak",
                               vs_baseline=None, dtype="int32", data="synthetic",
-                              config=dict(workload=workload, records_per_step=m, ops_per_step=e,
-                                          note="reference is pure Python and cannot travel; timed: its C port "
-                                               "(oracle/vsv_oracle_c.c) on all host threads, bounded sample per step"),
+                              config=dict(workload=workload, records_per_step=m, ops_per_step=int(sb["op_off"][-1]),
+                                          note="the reference is pure Python and cannot travel; timed: its port (oracle/) on all host "
+                                               "threads over a bounded sample of the same workload, same stage list as the GPU arm; one box "
+                                               "whatever N is (box-vs-box ratio)"),
                               cpu_baseline=base,
                               e2e=dict(value=v, unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0))))
         return
@@ -187,222 +272,237 @@ def main():
         raise SystemExit("bench.py: no CUDA device (volcanosv_b200 has no CPU path)")
     torch.cuda.set_device(local)
     dist = None
-    host_binding = None
     if world > 1:
         import torch.distributed as dist
-        from volcanosv_b200.shard import bind_host_to_gpu
-        if os.environ.get("VSV_NO_BIND") != "1":
-            host_binding = bind_host_to_gpu(local)   # pinned staging buffers on the GPU's own socket
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     from volcanosv_b200.pipeline import ShardStream
-
-    batch, cands = make_workload(args.profile, args.scale, rank, args.cands)
-    n_rec, n_ops = len(batch["pos"]), int(batch["op_off"][-1])
-    pinned = {k: torch.from_numpy(np.ascontiguousarray(v.view(np.int32) if k == "ops" else v)).pin_memory()
-              for k, v in batch.items() if k in ("ops", "op_off", "pos", "mapq", "qlen")}
-    pinned_c = {k: torch.from_numpy(v).pin_memory() for k, v in cands.items()}
     stream = ShardStream(local, dtype)   # two shard slots: upload of shard k+1 overlaps the work on shard k
     shard = stream.slots[0]
 
-    # host staging format of the end-to-end path: ops as 16-bit words + a sparse exception list
-    # (vsv_expand_ops16); produced by the host packer once, like the BAM decode it follows
-    from volcanosv_b200.lib import pack_ops16, pack_ops8, pack_ops12_native
-    # densest staging format that fits the data: ops8 (1 B/op; noisy long reads: ~1 % exceptions) when fewer than
-    # 3 % of the ops need the exception list, else ops16 (2 B/op; HiFi / =,X CIGARs).  The native BAM feeder
-    # (vsv_bam_chrom_fill) writes either format straight from the BAM records, so packing is not an extra pass.
-    # ops12 (12 bits per M + short-indel PAIR, vsv_expand_ops12) is denser still when the CIGARs alternate as minimap2's
-    # long-read CIGARs do: taken when its total (tokens + 16 bytes per odd pair) is below ops8's.
-    o8, exc_idx, exc_val = pack_ops8(batch["ops"])
-    pinned16 = {k: v for k, v in pinned.items() if k != "ops"}
-    bytes8 = o8.nbytes + 12 * len(exc_idx)
-    o12 = None
-    if args.staging in ("auto", "ops12") and len(exc_idx) < 0.03 * n_ops:
-        o12, exc_pair, exc_val12 = pack_ops12_native(batch["ops"])   # vsv_pack_ops12 on the host threads
-        if args.staging == "auto" and o12.nbytes + 16 * len(exc_pair) >= bytes8:
-            o12 = None
-    if o12 is not None:
-        staging = "ops12"
-        pinned16["ops12"] = torch.from_numpy(o12).pin_memory()
-        exc_idx, exc_val = exc_pair, exc_val12
-    elif len(exc_idx) < 0.03 * n_ops:
-        staging = "ops8"
-        pinned16["ops8"] = torch.from_numpy(o8).pin_memory()
-    else:
-        staging = "ops16"
-        o16, exc_idx, exc_val = pack_ops16(batch["ops"])
-        pinned16["ops16"] = torch.from_numpy(o16.view(np.int16)).pin_memory()
-    del o8, o12
-    pinned16["exc_idx"] = torch.from_numpy(exc_idx).pin_memory()
-    pinned16["exc_val"] = torch.from_numpy(exc_val.view(np.int32)).pin_memory()
-
-    def upload(compact=False):
-        shard.upload(pinned16 if compact else pinned, pinned_c, n_ops=n_ops)
+    def pin(b):
+        keys = ("ops", "op_off", "pos", "mapq", "qlen", "flag", "name_id", "next_same_name", "sa_rec", "sa_off", "sa_chrom", "sa_pos",
+                "sa_strand", "sa_first_s", "sa_last_s", "sa_bias", "sa_mapq")
+        out = {}
+        for k in keys:
+            v = b[k]
+            v = v.view(np.int32) if v.dtype == np.uint32 else (v.view(np.int16) if v.dtype == np.uint16 else v)
+            out[k] = torch.from_numpy(np.ascontiguousarray(v)).pin_memory()
+        out["sa_self_chrom"] = b.get("sa_self_chrom", 0)
+        return out
 
     def barrier():
-        shard.sync()
+        for sl in stream.slots:
+            sl.sync()
         torch.cuda.synchronize()
         if dist is not None:
             dist.barrier()
 
-    upload()
+    def reduce_max(x):
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        if dist is not None:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    host = [(pin(b), {k: torch.from_numpy(v).pin_memory() for k, v in c.items()}, int(b["op_off"][-1])) for b, c in shards]
+    if wgs:
+        del master
+    warm = max(args.warmup, 3)
+
+    # ---- resident timing: every shard of this rank on the device, CUDA events on the library's stream ----
+    res_shards = []
+    if wgs:
+        from volcanosv_b200.pipeline import ChromShard
+        # all chromosomes of this rank stay resident (180 GB of HBM): one engine per chromosome
+        for hb, hc, n_ops in host:
+            cs = ChromShard(local, dtype)
+            cs.upload(hb, hc, n_ops=n_ops)
+            res_shards.append(cs)
+    else:
+        shard.upload(host[0][0], host[0][1], n_ops=host[0][2])
+        res_shards = [shard]
     res = None
-    for _ in range(max(args.warmup, 3)):
-        res = shard.run_safe()
-    # ---- resident timing: CUDA events on the library's stream ------------------------
+    for _ in range(warm):
+        for cs in res_shards:
+            res = cs.run_safe()
     sampler = ClockSampler(local)
     sampler.start()
     barrier()
-    def launches():
-        return sum(c.timing()[1] for c in [shard.ctx] + shard.side)
-
+    launches = lambda: sum(cs.ctx.timing()[1] for cs in res_shards)
     l0 = launches()
-    shard.ctx.timer_start()
-    scan_ms = []
-    for _ in range(args.steps):
-        res = shard.run_safe()
-        scan_ms += res.scan_ms
-    ms = shard.ctx.timer_stop()
+    scan_ms, per_shard = [], []
+    t_ev0, t_ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if len(res_shards) == 1:
+        shard.ctx.timer_start()
+        for _ in range(args.steps):
+            res = shard.run_safe()
+            scan_ms += res.scan_ms
+        ms = shard.ctx.timer_stop()
+        last_res = [res]
+    else:
+        t_ev0.record()
+        last_res = []
+        for _ in range(args.steps):
+            last_res = []
+            for cs in res_shards:
+                r = cs.run_safe()          # ends with the one host read of the counts: every shard's work is complete here
+                scan_ms += r.scan_ms
+                last_res.append(r)
+        t_ev1.record()
+        t_ev1.synchronize()
+        ms = t_ev0.elapsed_time(t_ev1)
     l1 = launches()
     barrier()
-    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
-    if dist is not None:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_max = float(t.item())
-    ms_per_step = ms_max / args.steps
-    value = world * n_rec / (ms_per_step * 1e-3)
+    ms_per_step = reduce_max(ms) / args.steps
+    value = total_rec / (ms_per_step * 1e-3)
 
-    # ---- end to end: pinned host buffers -> H2D -> hot path -> D2H of the results ------
-    # A GPU works through a queue of shards (chromosomes, MAIN:268), so the steady state is timed:
-    # every timed step enqueues one shard's H2D copies, runs the hot path of the previously
-    # uploaded shard and reads its results back (K uploads + K runs + K downloads in K steps).
+    # ---- end to end: pinned host buffers (BAM-native u32 words, the boundary format of SURVEY.md 8b) -> H2D -> hot
+    # path -> D2H of the per-candidate results.  A GPU works through a queue of shards (chromosomes, MAIN:268), so the
+    # steady state is timed: every timed step enqueues the next shard's H2D copies, runs the hot path of the previously
+    # uploaded shard and reads its results back.
     pin_out = {}
 
-    def e2e_run(host):
+    def e2e_run(queue, steps):
         stream.n_in = stream.n_out = 0
-        stream.submit(host, pinned_c, n_ops=n_ops)
-        stream.submit(host, pinned_c, n_ops=n_ops)
-        stream.collect(pin_out)                       # warm BOTH slots (buffers, scratch arenas of every context)
-        stream.collect(pin_out)                       # and the pinned output buffers
-        stream.submit(host, pinned_c, n_ops=n_ops)
+        q = [queue[i % len(queue)] for i in range(steps * len(queue) + 3)]
+        stream.submit(*q[0][:2], n_ops=q[0][2])
+        stream.submit(*q[1][:2], n_ops=q[1][2])
+        stream.collect(pin_out)                       # warm BOTH slots (buffers, capacities, scratch)
+        stream.collect(pin_out)
+        stream.submit(*q[2][:2], n_ops=q[2][2])
         barrier()                                     # one shard's upload is complete here (prologue, untimed)
         t0 = time.perf_counter()
-        for _ in range(args.steps):
-            stream.submit(host, pinned_c, n_ops=n_ops)
+        h2d = d2h = 0
+        for i in range(steps * len(queue)):
+            nxt = q[3 + i] if 3 + i < len(q) else q[i % len(queue)]
+            stream.submit(*nxt[:2], n_ops=nxt[2])
             stream.collect(pin_out)
+            sl = stream.slots[(stream.n_out - 1) % 2]
+            h2d += int(sl.h2d_bytes)
+            d2h += int(sl.d2h_bytes)
         torch.cuda.synchronize()
         dt = time.perf_counter() - t0
-        sh = stream.slots[0]
-        bytes_io = (int(sh.h2d_bytes), int(sh.d2h_bytes))
         stream.collect(pin_out)                       # drain
-        t = torch.tensor([dt], dtype=torch.float64, device="cuda")
-        if dist is not None:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item()) / args.steps, bytes_io
+        return reduce_max(dt) / steps, (h2d // steps, d2h // steps)
 
-    e2e_per_step, (h2d_b, d2h_b) = e2e_run(pinned16)
-    e2e_value = world * n_rec / e2e_per_step
-    e2e32_per_step, (h2d32_b, _) = e2e_run(pinned)   # BAM-native u32 ops, no compact staging
+    rot = host[2 % len(host):] + host[: 2 % len(host)] if len(host) > 1 else host
+    e2e_per_step, (h2d_b, d2h_b) = e2e_run(rot, args.steps if not wgs else max(1, args.steps // 2))
+    e2e_value = total_rec / e2e_per_step
+
+    # compact staging written by the BAM feeder in its own pass (vsv_bam_chrom_fill -> ops8 / ops16) or packed from
+    # the u32 words (ops12): reported BESIDE the headline with the host pack time, which is outside that timed region
+    staged = None
+    if not wgs:
+        from volcanosv_b200.lib import pack_ops8, pack_ops12_native, pack_ops16
+        ops = shards[0][0]["ops"]
+        n_ops = len(ops)
+        t0 = time.perf_counter()
+        o12, exc_pair, exc_val12 = pack_ops12_native(ops)
+        pack12_s = time.perf_counter() - t0
+        o8, exc8, excv8 = pack_ops8(ops[: max(1, n_ops // 16)])
+        frac8 = len(exc8) / max(1, len(o8))
+        hb = {k: v for k, v in host[0][0].items() if k != "ops"}
+        if frac8 < 0.03 and o12.nbytes + 16 * len(exc_pair) < 1.05 * n_ops:
+            name = "ops12"
+            hb.update(ops12=torch.from_numpy(o12).pin_memory(), exc_idx=torch.from_numpy(exc_pair).pin_memory(),
+                      exc_val=torch.from_numpy(exc_val12.view(np.int32)).pin_memory())
+            pack_s, n_exc = pack12_s, len(exc_pair)
+        else:
+            name = "ops16"
+            t0 = time.perf_counter()
+            o16, ei, ev = pack_ops16(ops)
+            pack_s, n_exc = time.perf_counter() - t0, len(ei)
+            hb.update(ops16=torch.from_numpy(o16.view(np.int16)).pin_memory(), exc_idx=torch.from_numpy(ei).pin_memory(),
+                      exc_val=torch.from_numpy(ev.view(np.int32)).pin_memory())
+        st_per_step, (st_h2d, _) = e2e_run([(hb, host[0][1], n_ops)], args.steps)
+        staged = dict(format="%s + %d exceptions" % (name, n_exc), value=total_rec / st_per_step, ms_per_step=st_per_step * 1e3,
+                      h2d_bytes_per_step=st_h2d, host_pack_ms=pack_s * 1e3, host_pack_threads=os.cpu_count(),
+                      ms_per_step_incl_pack=(st_per_step + pack_s) * 1e3,
+                      note="pack time is NOT in ms_per_step; ms_per_step_incl_pack adds it serially (no overlap)")
+        del o12, o8
     sampler.stop_flag = True                          # clocks sampled through the resident AND the end-to-end timed regions
     sampler.join()
 
-    # ---- resident throughput with two shards in flight (a GPU holds many chromosome shards in its
-    # 180 GB; while one shard's scan owns the SMs the other's small join kernels fill the gaps).
-    # Reported beside `value`, which stays the one-shard-at-a-time figure the roofline refers to.
-    inflight2 = None
-    try:
-        import threading
-        pair = stream.slots                            # both already hold the shard after the e2e runs
-        for sh in pair:
-            sh.finish_upload()
-            sh.run_safe()
-            sh.sync()
-        k_each = max(1, args.steps // 2)
-        barrier()
-        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        ev0.record()
-
-        def work(sh):
-            for _ in range(k_each):
-                sh.run_safe()
-            sh.sync()
-        th = [threading.Thread(target=work, args=(sh,)) for sh in pair]
-        for t_ in th:
-            t_.start()
-        for t_ in th:
-            t_.join()
-        torch.cuda.synchronize()
-        ev1.record()
-        ev1.synchronize()
-        t = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device="cuda")
-        if dist is not None:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms2 = float(t.item()) / (2 * k_each)
-        inflight2 = dict(value=world * n_rec / (ms2 * 1e-3), unit=UNIT, ms_per_step=ms2, steps=2 * k_each)
-    except Exception as ex:  # noqa: BLE001
-        inflight2 = dict(error=str(ex))
-
     # ---- genotyping stress point (candidates/s), resident ------------------------------
     geno = None
-    try:
-        geno = genotype_point(shard, local)
-    except Exception as ex:  # noqa: BLE001
-        geno = dict(error=str(ex))
+    if not wgs:
+        try:
+            geno = genotype_point(shard, local, cpu=(world == 1 and not args.no_cpu_baseline), thr=thr)
+        except Exception as ex:  # noqa: BLE001
+            geno = dict(error=str(ex))
 
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
         return
-    # ---- roofline of the dominant kernel (k_scan_cigar) ---------------------------------
+    # ---- roofline of the dominant kernel (k_scan_wt<FUSED>) and of the whole step --------------------
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(peaks_path):
         peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
     else:
         peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
-    n_sig_out = res.n_read_sigs + res.n_cute_sigs            # both streams of the fused pass
-    alg_bytes = 4.0 * n_ops + 24.0 * n_rec + 32.0 * n_sig_out       # SURVEY.md §8d B1, per launch
-    k_ms = float(np.mean(scan_ms)) if scan_ms else float("nan")
-    achieved = alg_bytes / (k_ms * 1e-3) / 1e9
-    # dram bytes of that kernel from the committed `ncu --set full` capture (profiles/), per op -> per launch here
+    r0 = last_res[0]
+    my_rec = sum(r.n_rec for r in last_res)
+    my_ops = sum(r.n_ops for r in last_res)
+    n_sig_out = sum(r.n_read_sigs + r.n_cute_sigs for r in last_res)
+    n_rows = sum(r.counts["n_reads_cigar"] + r.counts["n_reads_split"] + r.counts["n_del"] + r.counts["n_ins"] for r in last_res)
+    n_usig = sum(r.n_udel + r.n_uins for r in last_res)
+    n_cand = sum(r.n_cand for r in last_res)
+    b1 = 4.0 * my_ops + 24.0 * my_rec + 32.0 * n_sig_out
+    b2 = 3.0 * 32.0 * n_rows + 32.0 * n_cand                                   # B2
+    b3 = 8.0 * my_rec + 16.0 * n_usig + 24.0 * n_cand                          # B3
+    per_launch_ms = float(np.mean(scan_ms)) if scan_ms else float("nan")
+    scans_per_step = len(last_res)
+    alg_launch = b1 / scans_per_step
+    achieved = alg_launch / (per_launch_ms * 1e-3) / 1e9
     traffic, traffic_src = None, None
     tpath = os.path.join(ROOT, "profiles", "scan_traffic.json")
     if os.path.exists(tpath):
         tj = json.load(open(tpath))
-        traffic = (tj["dram_bytes_read"] + tj["dram_bytes_write"]) / tj["n_ops"] * n_ops
+        traffic = (tj["dram_bytes_read"] + tj["dram_bytes_write"]) / tj["n_ops"] * (my_ops / scans_per_step)
         traffic_src = tj["source"]
     roof = dict(bound="hbm", kernel="k_scan_wt<FUSED>", achieved=achieved, peak=peak, unit="GB/s", frac=achieved / peak,
-                traffic=traffic, traffic_source=traffic_src, peak_source=peak_src, alg_bytes_per_launch=alg_bytes, kernel_ms=k_ms,
-                launches_per_step=1, share_of_step=k_ms / ms_per_step)
-    line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=args.steps, warmup=max(args.warmup, 3),
-                ms_per_step=ms_per_step, higher_is_better=True, scaling="weak", vs_baseline=None, dtype="int32",
-                data="synthetic",
-                config=dict(workload=workload, records_per_gpu=n_rec, ops_per_gpu=n_ops, candidates_per_gpu=len(cands["pos"]),
-                            read_sigs=res.n_read_sigs, cute_sigs=res.n_cute_sigs, unique_del=res.n_udel,
-                            unique_ins=res.n_uins, parallelism="shard-per-gpu x%d, no collective" % world,
-                            l2="inputs (%.2f GB/step) exceed the 126 MB L2; no flush needed" % (4.0 * n_ops / 1e9)),
-                clocks=sampler.result(), gpu_launches=int(l1 - l0),
-                e2e=dict(value=e2e_value, unit=UNIT, h2d_bytes_per_step=h2d_b,
-                         d2h_bytes_per_step=d2h_b, ms_per_step=e2e_per_step * 1e3,
-                         staging="%s + %d exceptions (vsv_expand_%s), pinned host buffers" % (staging, len(exc_idx), staging),
-                         pipelining="double-buffered shards: H2D of shard k+1 overlaps kernels + D2H of shard k",
-                         bam_native_u32=dict(value=world * n_rec / e2e32_per_step, ms_per_step=e2e32_per_step * 1e3,
-                                             h2d_bytes_per_step=h2d32_b)),
-                roofline=roof, candidates_per_s=geno, resident_two_shards_in_flight=inflight2)
-    if host_binding is not None:
-        line["config"]["host_binding"] = host_binding         # rank 0's; every rank binds to its own GPU's CPUs
+                traffic=traffic, traffic_source=traffic_src, peak_source=peak_src, alg_bytes_per_launch=alg_launch,
+                kernel_ms=per_launch_ms, launches_per_step=scans_per_step, share_of_step=per_launch_ms * scans_per_step / ms_per_step,
+                step_alg_bytes=b1 + b2 + b3, step_frac=(b1 + b2 + b3) / (ms_per_step * 1e-3) / 1e9 / peak,
+                step_note="step_frac = (B1 + B2 + B3 of SURVEY.md 8d for this rank's shards) / ms_per_step / peak")
+    cfg = dict(workload=workload, records=total_rec, ops=total_ops, records_this_rank=my_rec, candidates_this_rank=n_cand,
+               read_sigs=sum(r.n_read_sigs for r in last_res), cute_sigs=sum(r.n_cute_sigs for r in last_res),
+               sigs_rows_del=sum(r.counts["n_del"] for r in last_res), sigs_rows_ins=sum(r.counts["n_ins"] for r in last_res),
+               sa_rows=sum(r.counts["n_sa_rows"] for r in last_res), split_sigs=sum(r.counts["n_reads_split"] for r in last_res),
+               unique_del=sum(r.n_udel for r in last_res), unique_ins=sum(r.n_uins for r in last_res),
+               candidates="synthetic table (pos sorted, Pareto lengths)", host_syncs_per_shard=1,
+               parallelism=("22 chromosome shards over %d ranks by LPT, no collective" % world) if wgs else
+               ("shard-per-gpu x%d, no collective" % world),
+               l2="inputs (%.2f GB/step on this rank) exceed the 126 MB L2; no flush needed" % (4.0 * my_ops / 1e9)
+               if 4.0 * my_ops / scans_per_step > 2.5e8 else
+               "per-shard inputs (%.0f MB) are of the order of the 126 MB L2: consecutive shards evict each other only in the "
+               "wgs workloads; chr10-hifi re-runs one 164 MB shard (larger than L2)" % (4.0 * my_ops / scans_per_step / 1e6))
+    if lpt:
+        cfg["lpt"] = lpt
+    line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=args.steps, warmup=warm,
+                ms_per_step=ms_per_step, higher_is_better=True, scaling="strong" if wgs else "weak", vs_baseline=None, dtype="int32",
+                data="synthetic", config=cfg, clocks=sampler.result(), gpu_launches=int(l1 - l0),
+                e2e=dict(value=e2e_value, unit=UNIT, h2d_bytes_per_step=h2d_b, d2h_bytes_per_step=d2h_b,
+                         ms_per_step=e2e_per_step * 1e3,
+                         staging="BAM-native u32 CIGAR words + per-record columns in pinned host buffers (no host-side packing)",
+                         pipelining="two shard slots: H2D of shard k+1 overlaps kernels + D2H of shard k",
+                         feeder_staging=staged),
+                roofline=roof, candidates_per_s=geno)
     if not args.no_cpu_baseline and world == 1:              # reported at N=1 only (the host cores are shared by the ranks)
-        base, _, _ = cpu_baseline(batch, cands, thr)
+        ref_b, ref_c = shards[-1] if wgs else shards[0]
+        base, _, _ = cpu_baseline(ref_b, ref_c, thr)
         line["cpu_baseline"] = base
     print(json.dumps(line))
     if dist is not None:
         dist.destroy_process_group()
 
 
-def genotype_point(shard, local, n_reads=10_000_000, n_cand=1_000_000):
-    """BASELINE config 5 grid point: 10^6 candidates x 10^7 reads, resident, 3 timed runs."""
-    import ctypes as C
+def genotype_point(shard, local, n_reads=10_000_000, n_cand=1_000_000, cpu=False, thr=None):
+    """BASELINE config 5 grid point: 10^6 candidates x 10^7 reads, resident (the sort of the read ends is inside)."""
     import torch
     from volcanosv_b200 import synth
     from volcanosv_b200.pipeline import _dp
+    import ctypes as C
     rs, re = synth.synth_intervals(5, n_reads)
     pos, svlen, typ, gt = synth.synth_candidates(6, n_cand)
     dev = torch.device("cuda", local)
@@ -413,19 +513,163 @@ def genotype_point(shard, local, n_reads=10_000_000, n_cand=1_000_000):
     ratio = torch.empty(n_cand, dtype=torch.float64, device=dev)
     torch.cuda.synchronize()
     lib, h = shard.lib, shard.h
+    p = shard.ctx.get_params()
     times = []
     for i in range(5):
         shard.ctx.timer_start()
         rc = lib.vsv_genotype(h, _dp(t["rs"]), _dp(t["re"]), n_reads, _dp(t["pos"]), _dp(t["svlen"]), _dp(t["typ"]),
-                              _dp(t["gt"]), _dp(nsup), n_cand, shard.thr_del, shard.thr_ins, _dp(d2), _dp(ratio), _dp(ng))
+                              _dp(t["gt"]), _dp(nsup), n_cand, p.thr_del, p.thr_ins, _dp(d2), _dp(ratio), _dp(ng))
         shard._chk(rc)
         ms = shard.ctx.timer_stop()
         if i >= 2:
             times.append(ms)
     ms = float(np.mean(times))
-    alg = 8.0 * n_reads + 24.0 * n_cand        # SURVEY.md §8d B3 without the signature table
-    return dict(value=n_cand / (ms * 1e-3), unit="candidates/s", reads=n_reads, candidates=n_cand, ms=ms,
-                alg_GBps=alg / (ms * 1e-3) / 1e9)
+    alg = 8.0 * n_reads + 24.0 * n_cand        # SURVEY.md 8d B3 without the signature table
+    out = dict(value=n_cand / (ms * 1e-3), unit="candidates/s", reads=n_reads, candidates=n_cand, ms=ms,
+               alg_GBps=alg / (ms * 1e-3) / 1e9, kernel="radix sort of the read ends + k_genotype (closed-form depth)")
+    if cpu:
+        from oracle import c_oracle as CO
+        m = 20000
+        t0 = time.perf_counter()
+        CO.genotype(rs, re, pos[:m], svlen[:m], typ[:m], gt[:m], np.zeros(m, np.int32), thr[0], thr[1], threads=CO.num_threads())
+        dt = time.perf_counter() - t0
+        out["cpu_baseline"] = dict(value=m / dt, unit="candidates/s", cores=CO.num_threads(), kind="port",
+                                   sample="first %d candidates against all %d reads, %.2f s" % (m, n_reads, dt))
+    return out
+
+
+def run_sweep(args, rank, world, local):
+    """BASELINE config 5: candidates/s over the grid; candidates split over the ranks by position (every rank holds all
+    the reads: 8 n_reads bytes), device-timed, max over ranks."""
+    from volcanosv_b200 import synth
+    from volcanosv_b200.pipeline import GT_THRESHOLDS
+    thr = (GT_THRESHOLDS["ONT"]["DEL"], GT_THRESHOLDS["ONT"]["INS"])
+    reads_grid, cand_grid = sweep_grid(args.scale)
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        from oracle import c_oracle as CO
+        pts = []
+        tot_c, tot_t = 0, 0.0
+        for nr in reads_grid:
+            rs, re = synth.synth_intervals(5, nr)
+            pos, svlen, typ, gt = synth.synth_candidates(6, 20000)
+            t0 = time.perf_counter()
+            CO.genotype(rs, re, pos, svlen, typ, gt, np.zeros(len(pos), np.int32), thr[0], thr[1], threads=CO.num_threads())
+            dt = time.perf_counter() - t0
+            pts.append(dict(reads=nr, candidates_sampled=len(pos), candidates_per_s=len(pos) / dt))
+            tot_c += len(pos)
+            tot_t += dt
+        v = tot_c / tot_t
+        print(json.dumps(dict(impl="reference", metric="genotyped candidates/s", value=v, unit="candidates/s", n_gpus=args.gpus,
+                              steps=args.steps, warmup=args.warmup, ms_per_step=tot_t * 1e3, higher_is_better=True, scaling="strong",
+                              vs_baseline=None, dtype="int32", data="synthetic",
+                              config=dict(workload="genotyping stress sweep (scale %.3g)" % args.scale, points=pts,
+                                          note="oracle C port on all host threads; 20000 candidates per read count: the per-candidate "
+                                               "cost does not depend on the number of candidates"),
+                              cpu_baseline=dict(value=v, unit="candidates/s", cores=CO.num_threads(), kind="port",
+                                                sample="20000 candidates per read count"),
+                              e2e=dict(value=v, unit="candidates/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0))))
+        return
+    import torch
+    import ctypes as C
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    import volcanosv_b200 as V
+    from volcanosv_b200 import lib as L
+    from volcanosv_b200.pipeline import _dp
+    ctx = V.Context(local)
+    ctx.set_params(L.default_params("ONT"))
+    ctx.set_device_io(True)
+    dev = torch.device("cuda", local)
+    p = ctx.get_params()
+    sampler = ClockSampler(local)
+    sampler.start()
+    pts = []
+    tot_c, tot_ms, launches0 = 0, 0.0, ctx.timing()[1]
+    e2e_c, e2e_s, h2d, d2h = 0, 0.0, 0, 0
+    for nr in reads_grid:
+        rs, re = synth.synth_intervals(5, nr)
+        rs_p, re_p = torch.from_numpy(rs).pin_memory(), torch.from_numpy(re).pin_memory()
+        d_rs, d_re = rs_p.to(dev), re_p.to(dev)
+        for nc in cand_grid:
+            pos, svlen, typ, gt = synth.synth_candidates(6, nc)
+            a, b = rank * nc // world, (rank + 1) * nc // world
+            hc = {k: torch.from_numpy(np.ascontiguousarray(v[a:b])).pin_memory() for k, v in dict(pos=pos, svlen=svlen, typ=typ, gt=gt).items()}
+            dc = {k: v.to(dev) for k, v in hc.items()}
+            m = b - a
+            nsup = torch.zeros(m, dtype=torch.int32, device=dev)
+            d2, ng = torch.empty(m, dtype=torch.int32, device=dev), torch.empty(m, dtype=torch.int32, device=dev)
+            ratio = torch.empty(m, dtype=torch.float64, device=dev)
+            out_p = torch.empty(m, dtype=torch.int32).pin_memory()
+
+            def step():
+                rc = ctx.lib.vsv_genotype(ctx.h, _dp(d_rs), _dp(d_re), nr, _dp(dc["pos"]), _dp(dc["svlen"]), _dp(dc["typ"]), _dp(dc["gt"]),
+                                          _dp(nsup), m, p.thr_del, p.thr_ins, _dp(d2), _dp(ratio), _dp(ng))
+                ctx._chk(rc)
+            for _ in range(max(args.warmup, 3)):
+                step()
+            torch.cuda.synchronize()
+            if dist is not None:
+                dist.barrier()
+            ctx.timer_start()
+            for _ in range(args.steps):
+                step()
+            ms = ctx.timer_stop() / args.steps
+            t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+            if dist is not None:
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+            # end to end: reads + candidates from pinned host memory, new genotypes back
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            d_rs.copy_(rs_p, non_blocking=True); d_re.copy_(re_p, non_blocking=True)
+            for k in dc:
+                dc[k].copy_(hc[k], non_blocking=True)
+            torch.cuda.synchronize()
+            step()
+            ctx.sync()
+            out_p.copy_(ng, non_blocking=True)
+            torch.cuda.synchronize()
+            dt = time.perf_counter() - t0
+            t = torch.tensor([dt], dtype=torch.float64, device="cuda")
+            if dist is not None:
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dt = float(t.item())
+            alg = 8.0 * nr + 24.0 * m
+            pts.append(dict(reads=nr, candidates=nc, ms=ms, candidates_per_s=nc / (ms * 1e-3), alg_GBps_this_rank=alg / (ms * 1e-3) / 1e9,
+                            e2e_ms=dt * 1e3, e2e_candidates_per_s=nc / dt))
+            tot_c += nc
+            tot_ms += ms
+            e2e_c += nc
+            e2e_s += dt
+            h2d += 8 * nr + 16 * m
+            d2h += 4 * m
+        del d_rs, d_re
+    sampler.stop_flag = True
+    sampler.join()
+    if rank == 0:
+        peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+        peak = float(json.load(open(peaks_path))["hbm_gbs"]) if os.path.exists(peaks_path) else 6650.0
+        big = max(pts, key=lambda x: x["reads"] * 1e3 + x["candidates"])
+        line = dict(metric="genotyped candidates/s", value=tot_c / (tot_ms * 1e-3), unit="candidates/s", n_gpus=world, steps=args.steps,
+                    warmup=max(args.warmup, 3), ms_per_step=tot_ms, higher_is_better=True, scaling="strong", vs_baseline=None, dtype="int32",
+                    data="synthetic",
+                    config=dict(workload="genotyping stress sweep: %s reads x %s candidates (scale %.3g)" % (reads_grid, cand_grid, args.scale),
+                                points=pts, parallelism="candidates split by position over %d ranks, reads replicated, no collective" % world,
+                                l2="read arrays of 8 n_reads bytes: 8 MB / 80 MB / 800 MB; the two smaller ones fit the 126 MB L2 (a resident "
+                                   "index is the point of the closed form), candidates stream"),
+                    clocks=sampler.result(), gpu_launches=int(ctx.timing()[1] - launches0),
+                    e2e=dict(value=e2e_c / e2e_s, unit="candidates/s", h2d_bytes_per_step=h2d, d2h_bytes_per_step=d2h),
+                    roofline=dict(bound="hbm", kernel="radix sort of read ends + k_genotype", achieved=big["alg_GBps_this_rank"], peak=peak,
+                                  unit="GB/s", frac=big["alg_GBps_this_rank"] / peak, traffic=None,
+                                  note="largest grid point; algorithmic bytes = 8 n_reads + 24 n_cand (SURVEY.md 8d B3)"))
+        print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
 
 
 if __name__ == "__main__":

@@ -263,6 +263,183 @@ int vsv_genotype(vsv_ctx* ctx, const int32_t* read_start, const int32_t* read_en
 int vsv_edit_distance_batch(vsv_ctx* ctx, const uint8_t* chars, const int64_t* str_off, int64_t n_str,
                             const int32_t* ia, const int32_t* ib, int64_t n_pair, int32_t* dist);
 
+/* ---- parameters: every constant of the reference's operators --------- */
+/* Defaults = the reference's (argparse defaults, literals in the scripts, LI/para/*.txt, LI/filter_para.csv).
+ * A ctx starts with vsv_params_default(dtype Hifi); vsv_ctx_set_params replaces them.  dtype: 0 Hifi, 1 ONT,
+ * 2 CLR (the -dtype flag of volcanosv-vc-large-indel.py, MAIN:13). */
+#define VSV_DTYPE_HIFI 0
+#define VSV_DTYPE_ONT 1
+#define VSV_DTYPE_CLR 2
+typedef struct vsv_params {
+  int32_t dtype;
+  /* read scanners */
+  int32_t reads_min_len;      /* 30   ERS --min_siglen (ERS:40)                         */
+  int32_t reads_min_mapq;     /* 50   ERS:120                                           */
+  int32_t cute_min_len;       /* 10   SE -sl / --min_siglength                          */
+  int32_t cute_min_mapq;      /* 20   SE -q                                             */
+  int32_t cute_min_read_len;  /* 500  SE -r  (SE:439)                                   */
+  int32_t sa_sv_size;         /* 30   SE -l  (min_size)                                 */
+  int32_t sa_max_size;        /* 100000 SE -L                                           */
+  int32_t sa_max_parts;       /* 7    SE -p  (SE:370)                                   */
+  int32_t batch_size;         /* 10000000 SE -b: read-start ownership of a task (SE:603-612,535) */
+  /* contig side */
+  int32_t contig_min_len;     /* 30   ECS min_siglen                                    */
+  int32_t contig_min_mapq;    /* 50   ECS_H:392-394                                     */
+  int32_t cluster_max_shift;  /* 100  ECS_H:196-288                                     */
+  int32_t pair_max_shift;     /* 200  ECS_H:548-569                                     */
+  double clr_max_ins_pct;     /* 0.13 ECS_C:425-427                                     */
+  double clr_min_var_dist;    /* 200                                                    */
+  /* FP filter */
+  int32_t fp_max_comp;        /* 250  FPF:110                                           */
+  int32_t fp_max_shift;       /* 500  FPF:99                                            */
+  /* coverage support / band filter */
+  int32_t cov_flanking;       /* 1000 CSS:28                                            */
+  int32_t cov_min_size;       /* 30   CSS:29                                            */
+  double cov_lb_ins, cov_rb_ins, cov_lb_del, cov_rb_del; /* LI/filter_para.csv row (volcano, dtype) */
+  /* genotype */
+  int32_t gt_ins_min_len;     /* 30   GTI:81                                            */
+  double gt_min_size_sim;     /* 0.6  GTD:103-104                                       */
+  double gt_max_shift_ratio;  /* 2.3  GTD:105                                           */
+  double gt_min_shift;        /* 500                                                    */
+  int32_t gt_ins_flank;       /* 100  GTI:327                                           */
+  int32_t gt_del_large;       /* 1000 GTD:150                                           */
+  int32_t gt_del_off;         /* 150  GTD:157-168                                       */
+  int32_t gt_del_win;         /* 100                                                    */
+  double thr_del[4];          /* LI/para/GT_correction_para_<dtype>_DEL.txt: large_11, small_11, large_01, small_01 */
+  double thr_ins[4];          /* ..._INS.txt (NaN = leave the genotype)                  */
+} vsv_params;
+int vsv_params_default(vsv_params* p, int dtype);
+int vsv_ctx_set_params(vsv_ctx* ctx, const vsv_params* p);
+int vsv_ctx_get_params(vsv_ctx* ctx, vsv_params* p);
+
+/* ECS_C:53-70: per contig record, sum of I lengths, sum of M lengths and number of M ops (the CLR gate
+ * ins_pct = I / (M + I) <= 0.13 or var_dist = M / #M >= 200 is then two fp64 divisions on the host). */
+int vsv_cigar_class_sums(vsv_ctx* ctx, const uint32_t* ops, const int64_t* op_off, int64_t n_rec,
+                         int64_t* ins_sum, int64_t* match_sum, int64_t* match_cnt);
+
+/* ---- resident shard engine: the whole read-side hot path of one chromosome in one enqueue --------- */
+/* A vsv_shard owns the device copy of one chromosome's packed records and every table derived from them.
+ * vsv_shard_scan enqueues, WITHOUT any host synchronisation in between:
+ *   both read scanners in one pass over the ops (ERS:47-145 + SE:438-478), reference_end / read length per
+ *   record, the read split pairs (ERS:147-248), the SA-tag analysis (SE:193-371), the in-read merge
+ *   (SE:373-435), ONE radix sort that orders the read-signature table (sort_sig), the DEL and INS `.sigs`
+ *   tables (SE:637-638) and the read ends (for the spanning-depth join), `sort -u` de-duplication, unique
+ *   signatures (GTD:65-86, GTI:67-101).
+ * Counts stay on the device; vsv_shard_counts reads them once.  vsv_shard_candidates runs the per-call joins
+ * (FPF:106-123, CSS:81-253, GTD:92-170, GTI:107-196) and the genotype decision against the resident tables.
+ * Reference call chain replaced: RVC:83-96 and FGC:111-172 for one chromosome. */
+typedef struct vsv_shard vsv_shard;
+
+typedef struct vsv_records {
+  int64_t n_rec, n_ops;
+  int32_t ops_format;            /* 32: BAM-native u32 words; 16 / 12 / 8: the staging formats above          */
+  const void* ops;               /* 16-byte aligned                                                          */
+  const int64_t* exc_idx;        /* exception list of the staging format (NULL for 32)                        */
+  const uint32_t* exc_val;
+  int64_t n_exc;
+  const int64_t* op_off;         /* [n_rec + 1]                                                               */
+  const int32_t* pos;            /* 0-based leftmost, non-decreasing (coordinate-sorted BAM)                  */
+  const uint8_t* mapq;
+  const uint16_t* flag;          /* may be NULL: every record is treated as primary forward (no SA analysis)  */
+  const int32_t* qlen;           /* query_length: SEQ length, 0 for '*' (SE:439)                              */
+  const int32_t* name_id;        /* interned qname; NULL: no `sort -u` de-duplication                         */
+  const int32_t* next_same_name; /* next record in BAM order with the same qname, -1 = none (ERS:227-237);
+                                    NULL: no split pairs                                                      */
+  /* SA tags of the records that carry one (SE:495-511), parsed by the host as acquire_clip_pos does
+   * (SE:328-358): entry e of read i in [sa_off[i], sa_off[i+1]) */
+  int64_t n_sa_read, n_sa_ent;
+  const int32_t* sa_rec;         /* record index of read i (ascending)                                        */
+  const int64_t* sa_off;         /* [n_sa_read + 1]                                                           */
+  const int32_t* sa_chrom;       /* interned chromosome of the entry; sa_self_chrom = id of this chromosome   */
+  const int32_t* sa_pos;         /* POS field as written (1-based, kept: SE:354)                              */
+  const uint8_t* sa_strand;      /* 0 '+', 1 '-'                                                              */
+  const int32_t* sa_first_s;     /* leading / trailing soft clip (S only), sum of M,D,=,X                     */
+  const int32_t* sa_last_s;
+  const int32_t* sa_bias;
+  const uint8_t* sa_mapq;
+  int32_t sa_self_chrom;
+} vsv_records;
+
+typedef struct vsv_shard_counts {
+  int64_t n_reads_cigar;  /* ERS CIGAR signatures                                     */
+  int64_t n_reads_split;  /* ERS split-pair signatures (stored after the CIGAR ones)  */
+  int64_t n_cute;         /* cuteSV-style signatures before the in-read merge         */
+  int64_t n_del, n_ins;   /* `.sigs` rows (merged CIGAR rows + SA rows), before sort -u */
+  int64_t n_sa_rows;      /* of which from the SA analysis                            */
+  int64_t n_del_dup;      /* DEL rows removed by sort -u                              */
+  int64_t n_ins_maybe_dup;/* INS rows equal in (pos,len,read) to an earlier one: the host compares sequences */
+  int64_t n_udel, n_uins; /* unique signatures                                        */
+  int64_t overflow;       /* bit mask of VSV_OVF_*: a capacity was too small, counts hold the need */
+  int64_t n_stage;        /* staging slots reserved by the scan (sizing)              */
+} vsv_shard_counts;
+#define VSV_OVF_READS 1
+#define VSV_OVF_CUTE 2
+#define VSV_OVF_DEL 4
+#define VSV_OVF_INS 8
+#define VSV_OVF_STAGE 16
+#define VSV_OVF_POS 32   /* a position >= 2^28: the chromosome is too long for the combined sort key */
+#define VSV_OVF_DUPLIST 64
+
+int vsv_shard_create(vsv_ctx* ctx, vsv_shard** out);
+void vsv_shard_destroy(vsv_shard* s);
+/* Capacities (rows) of the read-signature, raw cute, DEL and INS tables; 0 keeps the current one. */
+int vsv_shard_reserve(vsv_shard* s, int64_t cap_reads, int64_t cap_cute, int64_t cap_del, int64_t cap_ins);
+/* Copies (host-IO ctx) or adopts (device-IO ctx: the pointers must stay valid) one chromosome's records and
+ * widens a staging format.  Asynchronous on the ctx stream with pinned host memory. */
+int vsv_shard_load(vsv_shard* s, const vsv_records* r);
+/* -include_bed regions of this chromosome, already widened by 1000 bp as load_bed does (SE:58-80), and the
+ * chromosome length; n = -1: no BED (every record is in).  Host pointers. */
+int vsv_shard_set_bed(vsv_shard* s, const int32_t* b0, const int32_t* b1, int64_t n, int64_t chrom_len);
+int vsv_shard_scan(vsv_shard* s);
+/* Waits for the stream and returns the counts of the last vsv_shard_scan. */
+int vsv_shard_counts_get(vsv_shard* s, vsv_shard_counts* c);
+/* INS rows the host found to be exact duplicates (same sequence too): their uids (field `first` of the
+ * row), ascending.  Re-runs the grouping.  Host pointer. */
+int vsv_shard_drop_ins(vsv_shard* s, const int32_t* uid, int64_t n);
+
+/* tables a host formatter can fetch (host pointers, capacity in rows; returns rows in *n) */
+#define VSV_TAB_READS 0      /* vsv_sig: CIGAR signatures in (record, op) order, then the split-pair ones */
+#define VSV_TAB_CUTE 1       /* vsv_sig: raw cuteSV-style signatures in (record, op) order               */
+#define VSV_TAB_DEL_ROWS 2   /* vsv_sig: `.sigs` rows in no particular order: rec, type (| 256 for a reversed
+                                query in an SA row), pos, len, q0, q1 (SA rows: slice of the query), first = uid
+                                (merged rows: index of the first folded raw signature in VSV_TAB_CUTE; SA rows:
+                                negative), count (merged rows: raw signatures folded; SA rows: 0)           */
+#define VSV_TAB_INS_ROWS 3
+#define VSV_TAB_REF_END 4    /* int32 per record: reference_end                                            */
+#define VSV_TAB_READ_LEN 5   /* int32 per record: read length incl. hard clips (ERS:151)                   */
+#define VSV_TAB_IN_BED 6     /* uint8 per record                                                           */
+#define VSV_TAB_INS_DUPS 7   /* int32 pairs (uid of the later row, uid of the earlier row)                 */
+#define VSV_TAB_UDEL 8       /* int32 triples (pos, len, count) of the unique DEL signatures, file order   */
+#define VSV_TAB_UINS 9
+int vsv_shard_fetch(vsv_shard* s, int table, void* out, int64_t cap_rows, int64_t* n);
+
+/* Per-call joins against the resident tables.  Candidates in VCF order on this chromosome: pos, svlen (DEL:
+ * |SVLEN|, INS: SVLEN), type (VSV_DEL / VSV_INS), call_gt (0 '0/1', 1 '1/1', other = pass through).  `what`
+ * selects the stages; outputs of unselected stages may be NULL:
+ *   VSV_JOIN_FP       fp_support  eval_sig (FPF:106-123) against the read-signature table
+ *   VSV_JOIN_COV      cov         calc_ins_call_cov / calc_del_call_cov (CSS:81-253), flanking cov_flanking
+ *   VSV_JOIN_SUPPORT  n_support, match_id  match_varlist_siglist / extract_sig_support incl. the double count
+ *                     at last_match_idx; DEL and INS candidates carry separate indices (the reference runs
+ *                     GTD and GTI separately): last_in[2] / last_out[2] = {DEL, INS} (-1 = none; NULL = {0,0})
+ *   VSV_JOIN_GENOTYPE depth2, ratio, new_gt  (GTD:140-170,206-217,291-318; GTI:188-196,228,258-283); needs
+ *                     n_support from VSV_JOIN_SUPPORT in the same call or as input in `n_support`
+ * Host-IO ctx: synchronous.  Device-IO ctx: asynchronous, last_out must be NULL. */
+#define VSV_JOIN_FP 1
+#define VSV_JOIN_COV 2
+#define VSV_JOIN_SUPPORT 4
+#define VSV_JOIN_GENOTYPE 8
+int vsv_shard_candidates(vsv_shard* s, int what, const int32_t* cand_pos, const int32_t* cand_svlen,
+                         const int32_t* cand_type, const int32_t* call_gt, int64_t n_cand, const int32_t* last_in,
+                         int32_t* fp_support, int64_t* cov, int32_t* n_support, int32_t* match_id, int32_t* depth2,
+                         double* ratio, int32_t* new_gt, int32_t* last_out);
+/* CUDA-event time (ms) of the streaming scan kernel of the last vsv_shard_scan. */
+int vsv_shard_scan_kernel_ms(vsv_shard* s, float* ms);
+
+/* Closed-form spanning depth (GTD:140-146): reads sorted by start; `sorted_end` = the read ends sorted
+ * ascending.  depth = #{start < S} - #{end <= E} + #{S <= start <= E and end <= E}. */
+int vsv_span_depth_sorted(vsv_ctx* ctx, const int32_t* read_start, const int32_t* read_end, const int32_t* sorted_end,
+                          int64_t n_reads, const int32_t* S, const int32_t* E, int64_t n_win, int32_t* depth);
+
 /* ---- host-side BAM feeder (no CUDA; zlib + threads) ------------------------------------- */
 /* Replaces `pysam.AlignmentFile(path).fetch(chr)` and the per-record attribute reads of the
  * whole-chromosome scans (LI/extract_reads_signature.py:107-145, LI/sig_extract.py:514-560,

@@ -153,3 +153,150 @@ def shard_step(batch, cands, thr_del, thr_ins, threads=1):
     d2, ratio, ng = genotype(pos, rend, cpos, clen, ctyp, cgt, nsup, thr_del, thr_ins, threads=threads)
     return dict(fp_support=fp, cov_ins=cov_i, cov_del=cov_d, n_support=nsup, depth2=d2, ratio=ratio, new_gt=ng,
                 sig_reads=s_reads, sig_del=dels, sig_ins=inss)
+
+
+# --------------------------------------------------------------------------- resident step, round 2
+def split_reads(pos, ref_end, readlen, first_op, last_op, is_rev, nxt):
+    """extract_sig_from_split for READ records (ERS:147-197, min_mapq 0) on the consecutive same-name pairs
+    (r, nxt[r]) (ERS:227-237), vectorised.  Returns SIG_DTYPE rows: rec = first record, first = second."""
+    pos, ref_end, readlen = (np.asarray(x, np.int64) for x in (pos, ref_end, readlen))
+    first_op, last_op = np.asarray(first_op, np.int64), np.asarray(last_op, np.int64)
+    r = np.flatnonzero(np.asarray(nxt) >= 0)
+    b = np.asarray(nxt)[r].astype(np.int64)
+    clip = lambda w: ((w & 15) == 4) | ((w & 15) == 5)
+    ok = (np.asarray(is_rev)[r] == np.asarray(is_rev)[b]) & clip(last_op[r]) & clip(first_op[b])      # ERS:160-166
+    Ref1e, Ref2s = ref_end[r], pos[b]
+    Read1e, Read2s = readlen[r] - (last_op[r] >> 4), first_op[b] >> 4
+    D = (Ref2s - Ref1e) - (Read2s - Read1e)
+    O = Ref1e - Ref2s
+    ok &= np.abs(D) <= 50000
+    is_del = ok & (O < 30) & (D >= 30)                                                                   # ERS:191-193
+    is_ins = ok & (O < 30) & (D <= -30)                                                                  # ERS:194-196
+    out = np.zeros(int(is_del.sum() + is_ins.sum()), SIG_DTYPE)
+    k = np.flatnonzero(is_del | is_ins)
+    out["rec"], out["first"], out["count"] = r[k], b[k], 1
+    out["type"] = np.where(is_del[k], 0, 1)
+    mid = np.trunc((Ref1e[k] + Ref2s[k]) / 2.0).astype(np.int64)                                         # int((a+b)/2)
+    out["pos"] = np.where(is_del[k], Ref1e[k], mid)
+    out["len"] = np.abs(D[k])
+    out["q0"], out["q1"] = Read1e[k], Read2s[k]
+    return out
+
+
+def sa_rows(batch, ref_end, in_bed, min_mapq=20, min_read_len=500, sv_size=30, max_size=100000, max_parts=7):
+    """SA-tag analysis rows (SE:345-371,193-326) from the pre-parsed SA columns of a batch (tests: small)."""
+    from . import vsv_oracle as O
+    dels, inss = [], []
+    if "sa_rec" not in batch:
+        return dels, inss
+    ops, off = batch["ops"], batch["op_off"]
+    for i, r in enumerate(batch["sa_rec"]):
+        r = int(r)
+        fl, qlen = int(batch["flag"][r]), int(batch["qlen"][r])
+        if fl not in (0, 16) or qlen < min_read_len or not in_bed[r]:
+            continue
+        primary = None
+        if int(batch["mapq"][r]) >= min_mapq:
+            a, b = int(off[r]), int(off[r + 1])
+            f, l = (int(ops[a]), int(ops[b - 1])) if b > a else (0, 0)
+            left = (f >> 4) if (f & 15) in (4, 5) else 0
+            right = (l >> 4) if (l & 15) in (4, 5) else 0
+            primary = (left, qlen - right, int(batch["pos"][r]), int(ref_end[r]), int(batch.get("sa_self_chrom", 0)), 0) if fl == 0 else \
+                (right, qlen - left, int(batch["pos"][r]), int(ref_end[r]), int(batch.get("sa_self_chrom", 0)), 1)
+        ent = [(int(batch["sa_chrom"][e]), int(batch["sa_pos"][e]), int(batch["sa_strand"][e]), int(batch["sa_first_s"][e]),
+                int(batch["sa_last_s"][e]), int(batch["sa_bias"][e]), int(batch["sa_mapq"][e]))
+               for e in range(int(batch["sa_off"][i]), int(batch["sa_off"][i + 1]))]
+        seg = O.sa_segments(primary, ent, qlen, min_mapq)
+        if len(seg) < 2:
+            continue
+        for (tp, p, ln, q0, q1, rev) in O.sa_split_analysis(seg, qlen, sv_size, max_size, max_parts):
+            (dels if tp == 0 else inss).append((r, p, ln, q0, q1, rev))
+    return dels, inss
+
+
+def shard_step2(batch, cands, thr_del, thr_ins, threads=1, bed=None, chrom_len=None, batch_size=10_000_000, drop_ins=()):
+    """CPU restatement of the resident step of csrc/vsv_shard.cu (vsv_shard_scan + vsv_shard_candidates) with the
+    reference's product semantics: RVC:83-96 (ERS cigar + split -> FPF) and FGC:111-172 (SE cigar + merge + SA,
+    sort -u, .sigs order -> CSS; GTD on the DEL calls and GTI on the INS calls, each with its own last_match_idx)."""
+    ops, off, pos, mapq, qlen = batch["ops"], batch["op_off"], batch["pos"], batch["mapq"], batch["qlen"]
+    n = len(pos)
+    s_reads, rt, qt, xt = scan_cigar(ops, off, pos, mapq, 1, 30, 50, threads=threads)
+    rend = (pos + rt).astype(np.int32)
+    readlen = (qt + xt).astype(np.int32)
+    in_bed = np.ones(n, bool)
+    if bed is not None:                                               # SE:58-80 + SE:524-535
+        in_bed[:] = False
+        t0 = (pos.astype(np.int64) // batch_size) * batch_size if chrom_len >= batch_size else np.zeros(n, np.int64)
+        t1 = np.minimum(t0 + batch_size, chrom_len) if chrom_len >= batch_size else np.full(n, chrom_len, np.int64)
+        for (r0, r1) in bed:
+            att = ((t0 <= r0) & (t1 > r0)) | ((r0 <= t0) & (t0 < r1))
+            in_bed |= att & ~((rend <= r0) | (pos >= r1))
+    res = dict(ref_end=rend, readlen=readlen, in_bed=in_bed.astype(np.uint8), sig_reads_cigar=s_reads)
+    split = np.zeros(0, SIG_DTYPE)
+    if batch.get("next_same_name") is not None:
+        has = off[1:] > off[:-1]
+        last = max(len(ops) - 1, 0)
+        f_op = np.where(has, ops[np.minimum(off[:-1], last)], 0)
+        l_op = np.where(has, ops[np.maximum(off[1:] - 1, 0)], 0)
+        is_rev = (batch["flag"] >> 4) & 1 if batch.get("flag") is not None else np.zeros(n, np.int64)
+        split = split_reads(pos, rend, readlen, f_op, l_op, is_rev, batch["next_same_name"])
+    res["sig_reads_split"] = split
+    reads_all = np.concatenate([s_reads, split])
+    reads_sorted = reads_all[np.argsort(reads_all["pos"], kind="stable")]
+    enable = (qlen >= 500).astype(np.uint8)
+    s_cute, *_ = scan_cigar(ops, off, pos, mapq, 2, 10, 20, enable=enable, threads=threads, totals=False)
+    res["sig_cute"] = s_cute
+    s_cute_in = s_cute[in_bed[s_cute["rec"]]] if bed is not None else s_cute
+    dels, inss = merge_cute(s_cute_in)
+    sd, si = sa_rows(batch, rend, in_bed)
+    def with_sa(rows, sa, tp):
+        if not sa:
+            return rows
+        extra = np.zeros(len(sa), SIG_DTYPE)
+        for k, (r, p, ln, q0, q1, rev) in enumerate(sa):
+            extra[k] = (r, tp | (256 if rev else 0), p, ln, q0, q1, -1, 0)
+        return np.concatenate([rows, extra])
+    dels, inss = with_sa(dels, sd, 0), with_sa(inss, si, 1)
+    res["n_sa_rows"] = len(sd) + len(si)
+    res["rows_del"], res["rows_ins"] = dels, inss
+    name = batch.get("name_id")
+
+    def dedup(rows, is_del):
+        """sort -u: `.sigs` order, then rows equal to an earlier one in (pos, len, read) -> DEL dropped, INS reported"""
+        rows = sigs_order(rows)
+        keep = np.ones(len(rows), bool)
+        maybe = 0
+        if name is not None and len(rows):
+            key = np.stack([rows["pos"].astype(np.int64), rows["len"].astype(np.int64), np.asarray(name)[rows["rec"]].astype(np.int64)], 1)
+            _, first_idx, inv = np.unique(key, axis=0, return_index=True, return_inverse=True)
+            later = first_idx[inv.reshape(-1)] != np.arange(len(rows))
+            # np.unique returns the FIRST occurrence in array order, which is the `.sigs` order here
+            if is_del:
+                keep = ~later
+            else:
+                maybe = int(later.sum())
+        return rows, keep, maybe
+    dels_s, keep_d, _ = dedup(dels, True)
+    inss_s, keep_i, maybe_i = dedup(inss, False)
+    if len(drop_ins):
+        raise NotImplementedError("confirmed INS duplicates are a host decision; tests drop them through the engine only")
+    res["n_del_dup"], res["n_ins_maybe_dup"] = int((~keep_d).sum()), maybe_i
+    ud = group(dels_s["pos"][keep_d], dels_s["len"][keep_d], 0)
+    # GTI:81 keeps INS signatures >= 30 bp; a dropped duplicate never heads a group
+    ui = group(inss_s["pos"][keep_i], inss_s["len"][keep_i], 30)
+    res["udel"], res["uins"] = ud, ui
+    if cands is None:
+        return res
+    cpos, clen, ctyp, cgt = cands["pos"], cands["svlen"], cands["type"], cands["gt"]
+    res["fp_support"] = fp_support(cpos, clen, reads_sorted["pos"], reads_sorted["len"])
+    cov_i = cov(False, cpos, cpos, inss_s["pos"][keep_i], inss_s["len"][keep_i])
+    cov_d = cov(True, cpos, (cpos + clen).astype(np.int32), dels_s["pos"][keep_d], dels_s["len"][keep_d])
+    res["cov"] = np.where(ctyp == 0, cov_d, cov_i)
+    nsup = np.zeros(len(cpos), np.int32)
+    for tp, u in ((0, ud), (1, ui)):
+        m = ctyp == tp
+        nsup[m] = sig_support(cpos[m], clen[m], *u)
+    res["n_support"] = nsup
+    d2, ratio, ng = genotype(pos, rend, cpos, clen, ctyp, cgt, nsup, thr_del, thr_ins, threads=threads)
+    res.update(depth2=d2, ratio=ratio, new_gt=ng)
+    return res

@@ -9,7 +9,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libvolcano_b200.so")
-SOURCES = ["vsv_ctx.cu", "vsv_scan.cu", "vsv_merge.cu", "vsv_sa.cu", "vsv_stage2.cu", "vsv_stage3.cu", "vsv_depth.cu", "vsv_edit.cu", "vsv_bam.cu"]
+SOURCES = ["vsv_ctx.cu", "vsv_scan.cu", "vsv_merge.cu", "vsv_sa.cu", "vsv_stage2.cu", "vsv_stage3.cu", "vsv_depth.cu", "vsv_edit.cu", "vsv_bam.cu", "vsv_shard.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "--extended-lambda", "-fmad=false", "-Xcompiler", "-fPIC", "-Xcompiler", "-O2"]
 

@@ -31,6 +31,8 @@ struct vsv_ctx {
   char* arena = nullptr;
   size_t arena_cap = 0, arena_used = 0;
   std::vector<void*> overflow;  // allocations that did not fit the arena (freed at reset)
+  vsv_params params;            // reference constants (vsv_params_default; replaced by vsv_ctx_set_params)
+  bool scan_attr_set = false;   // cudaFuncSetAttribute of the streaming kernels done
 };
 
 #define VSV_CUDA(ctx, call)                                                            \

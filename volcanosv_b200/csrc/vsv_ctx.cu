@@ -8,6 +8,45 @@ static const size_t kAlign = 256;
 
 extern "C" const char* vsv_version(void) { return "volcanosv_b200 0.1 (sm_100a)"; }
 
+// Reference defaults: argparse defaults and literals of the LI scripts, LI/para/
+// GT_correction_para_<dtype>_<type>.txt, LI/filter_para.csv rows asm=volcano.
+extern "C" int vsv_params_default(vsv_params* p, int dtype) {
+  if (!p || dtype < 0 || dtype > 2) return VSV_E_ARG;
+  memset(p, 0, sizeof(*p));
+  p->dtype = dtype;
+  p->reads_min_len = 30; p->reads_min_mapq = 50;
+  p->cute_min_len = 10; p->cute_min_mapq = 20; p->cute_min_read_len = 500;
+  p->sa_sv_size = 30; p->sa_max_size = 100000; p->sa_max_parts = 7; p->batch_size = 10000000;
+  p->contig_min_len = 30; p->contig_min_mapq = 50; p->cluster_max_shift = 100; p->pair_max_shift = 200;
+  p->clr_max_ins_pct = 0.13; p->clr_min_var_dist = 200.0;
+  p->fp_max_comp = 250; p->fp_max_shift = 500;
+  p->cov_flanking = 1000; p->cov_min_size = 30;
+  static const double cov[3][4] = {{0.097, 2.754, 0.2, 2.605}, {0.206, 2.79, 0.242, 2.77}, {0.075, 2.383, 0.186, 3.018}};
+  p->cov_lb_ins = cov[dtype][0]; p->cov_rb_ins = cov[dtype][1]; p->cov_lb_del = cov[dtype][2]; p->cov_rb_del = cov[dtype][3];
+  p->gt_ins_min_len = 30; p->gt_min_size_sim = 0.6; p->gt_max_shift_ratio = 2.3; p->gt_min_shift = 500.0;
+  p->gt_ins_flank = 100; p->gt_del_large = 1000; p->gt_del_off = 150; p->gt_del_win = 100;
+  const double nan = __builtin_nan("");
+  static const double td[3][4] = {{0.6, 0.69, 0.71, 0.91}, {0.61, 0.61, 0.68, 0.79}, {0.55, 0.59, 0.65, 0.75}};
+  const double ti[3][4] = {{nan, 0.59, 0.63, 0.79}, {nan, nan, 0.67, 0.72}, {nan, nan, 0.64, 0.75}};
+  for (int k = 0; k < 4; ++k) { p->thr_del[k] = td[dtype][k]; p->thr_ins[k] = ti[dtype][k]; }
+  return VSV_OK;
+}
+extern "C" int vsv_ctx_set_params(vsv_ctx* c, const vsv_params* p) {
+  if (!c || !p) return VSV_E_ARG;
+  if (p->sa_max_parts < 2 || p->sa_max_parts > 16 || p->batch_size <= 0 || p->cov_flanking < 0 || p->reads_min_len < 0 ||
+      p->cute_min_len < 0 || p->reads_min_len >= (1 << 27) || p->cute_min_len >= (1 << 27)) {
+    c->err = "vsv_ctx_set_params: parameter out of range";
+    return VSV_E_ARG;
+  }
+  c->params = *p;
+  return VSV_OK;
+}
+extern "C" int vsv_ctx_get_params(vsv_ctx* c, vsv_params* p) {
+  if (!c || !p) return VSV_E_ARG;
+  *p = c->params;
+  return VSV_OK;
+}
+
 extern "C" int vsv_ctx_create(int device, vsv_ctx** out) {
   if (!out) return VSV_E_ARG;
   *out = nullptr;
@@ -33,6 +72,7 @@ extern "C" int vsv_ctx_create(int device, vsv_ctx** out) {
     return VSV_E_NOMEM;
   }
   c->arena_cap = kArenaInitial;
+  vsv_params_default(&c->params, VSV_DTYPE_HIFI);
   *out = c;
   return VSV_OK;
 }

@@ -1,5 +1,5 @@
 // K2: per-record merge (split out of vsv_scan.cu).
-#include "vsv_common.cuh"
+#include "vsv_rules.cuh"
 
 // ================================================================================
 // K2: per-record merge.  cluster_ins_one_read / cluster_del_one_read (ECS_H:87-164),
@@ -9,73 +9,6 @@
 // order deterministic.
 // ================================================================================
 #include <cub/device/device_scan.cuh>
-
-// State of one type's merge inside a record (the reference keeps one list per type, so DEL merging
-// never sees the INS signatures in between and vice versa).
-struct MState {
-  vsv_sig cur;
-  int32_t mark;  // cute: last INS pos / DEL end
-  bool open;
-};
-
-// Feeds the next same-type signature `n` (index `idx` in the type's own list); calls f(merged)
-// whenever a merged signature is complete.
-template <typename F>
-__device__ __forceinline__ void mstate_push(MState& st, const vsv_sig& n, int32_t idx, int mode, int type, F f) {
-  vsv_sig& cur = st.cur;
-  if (!st.open) {
-    cur = n; cur.first = idx; cur.count = 1;
-    st.mark = (type == VSV_INS) ? n.pos : n.pos + n.len;
-    st.open = true;
-    return;
-  }
-  bool hit = false;
-  if (mode == VSV_MODE_CONTIG) {
-    const int32_t d = abs(n.pos - cur.pos);
-    if (type == VSV_INS) {
-      hit = (cur.len > 250 && n.len > 250 && d < 250) || (cur.len > 320 && n.len > 320 && d < 380) ||
-            (cur.len > 100 && n.len > 100 && d < 250);           // ECS_H:112-135
-      if (hit) { cur.q1 = n.q1; cur.len = cur.q1 - cur.q0; }     // ECS_H:91-97
-    } else {
-      hit = cur.len > 150 && n.len > 150 && d < 150;             // ECS_H:148-150
-      if (hit) { cur.len = n.pos + n.len - cur.pos; cur.q1 = cur.q0 + 1; }  // ECS_H:99-106
-    }
-  } else if (mode == VSV_MODE_CUTE) {
-    if (type == VSV_INS) {
-      hit = n.pos - st.mark <= 100;                              // SE:396-399
-      if (hit) { cur.len += n.len; st.mark = n.pos; }
-    } else {
-      hit = n.pos - st.mark <= 0;                                // SE:420
-      if (hit) { cur.len += n.len; st.mark = n.pos + n.len; }
-    }
-  }                                                              // VSV_MODE_READS: never merged
-  if (hit) {
-    cur.count++;
-  } else {
-    f(cur);
-    cur = n; cur.first = idx; cur.count = 1;
-    st.mark = n.pos;                                             // SE:412-413 / SE:429-430 (end := start quirk)
-  }
-}
-
-// Walks one record's run [i0,i1) of signatures (op order, both types interleaved) with one state per
-// type.  in_del / in_ins: how many DEL / INS signatures precede the run (the `first` indices count
-// inside each type's own list).  fd / fi receive the merged DEL / INS signatures in order.
-template <typename FD, typename FI>
-__device__ __forceinline__ void merge_walk2(const vsv_sig* __restrict__ s, int64_t i0, int64_t i1, int mode, int32_t in_del,
-                                            int32_t in_ins, FD fd, FI fi) {
-  MState sd, si;
-  sd.open = si.open = false;
-  for (int64_t k = i0; k < i1; ++k) {
-    const int4 a = reinterpret_cast<const int4*>(s + k)[0], b = reinterpret_cast<const int4*>(s + k)[1];
-    vsv_sig n;
-    n.rec = a.x; n.type = a.y; n.pos = a.z; n.len = a.w; n.q0 = b.x; n.q1 = b.y; n.first = b.z; n.count = b.w;
-    if (n.type == VSV_DEL) mstate_push(sd, n, in_del++, mode, VSV_DEL, fd);
-    else mstate_push(si, n, in_ins++, mode, VSV_INS, fi);
-  }
-  if (sd.open) fd(sd.cur);
-  if (si.open) fi(si.cur);
-}
 
 struct SumU4 {
   __host__ __device__ uint4 operator()(const uint4& a, const uint4& b) const {

@@ -7,52 +7,7 @@
 // most 2(k-1)+1 rows) and are compacted in (read, emission) order: count -> exclusive scan
 // -> copy.  TRA rows are not produced (SE:637-638 drops them with `grep -w`), but the
 // different-chromosome trigger of the rescue rule is kept.
-#include "vsv_common.cuh"
-
-#define SA_MAXSEG 16
-
-struct SaSeg {
-  int64_t qs, qe, rs, re;
-  int32_t chr, st;
-};
-
-struct SaIn {
-  const int64_t* seg_off;
-  const int32_t *q_s, *q_e, *r_s, *r_e, *chrom, *read_len;
-  const uint8_t* strand;
-};
-
-__device__ __forceinline__ SaSeg sa_mirror(const SaSeg& e, int64_t L) {  // SE: '-' strand -> query mirrored
-  SaSeg o = e;
-  o.qs = L - e.qe;
-  o.qe = L - e.qs;
-  return o;
-}
-
-struct SaEmit {
-  vsv_sig* dst;
-  int32_t rec, n, rev;
-  int64_t sv_size, max_size;
-  __device__ __forceinline__ void put(int type, int64_t pos, int64_t len, int64_t q0, int64_t q1) {
-    vsv_sig o;
-    o.rec = rec; o.type = type; o.pos = (int32_t)pos; o.len = (int32_t)len;
-    o.q0 = (int32_t)q0; o.q1 = (int32_t)q1; o.first = rev; o.count = 1;
-    dst[n++] = o;
-  }
-  // SE:217-232 (pair) / SE:255-293 (triple): INS then DEL test of one ordered pair
-  __device__ __forceinline__ void ins_del(const SaSeg& e1, const SaSeg& e2, bool guard) {
-    if (e1.re - e2.rs < sv_size) {
-      const int64_t il = e2.qs + e1.re - e2.rs - e1.qe;
-      if (il >= sv_size && e2.rs - e1.re <= 100 && (il <= max_size || max_size == -1) && guard) {
-        const int64_t h = (e2.rs - e1.re) / 2;  // int(x/2): truncation toward zero == C
-        put(VSV_INS, (e2.rs + e1.re) / 2, il, e1.qe + h, e2.qs - h);
-      }
-      const int64_t dl = e2.rs - e2.qs + e1.qe - e1.re;
-      if (dl >= sv_size && e2.qs - e1.qe <= 100 && (dl <= max_size || max_size == -1) && guard)
-        put(VSV_DEL, e1.re, dl, 0, 0);
-    }
-  }
-};
+#include "vsv_rules.cuh"
 
 __global__ void __launch_bounds__(128) k_sa_analysis(SaIn in, int64_t n_read, int sv_size, int max_size, int max_parts,
                                                      vsv_sig* __restrict__ tmp, int32_t* __restrict__ cnt) {
@@ -64,52 +19,13 @@ __global__ void __launch_bounds__(128) k_sa_analysis(SaIn in, int64_t n_read, in
   em.dst = tmp + 2 * a; em.rec = (int32_t)r; em.n = 0; em.rev = 0; em.sv_size = sv_size; em.max_size = max_size;
   if (k >= 2 && k <= max_parts) {
     SaSeg sp[SA_MAXSEG];
-    for (int i = 0; i < k; ++i) {  // stable insertion sort by query start
+    for (int i = 0; i < k; ++i) {
       SaSeg s;
       s.qs = in.q_s[a + i]; s.qe = in.q_e[a + i]; s.rs = in.r_s[a + i]; s.re = in.r_e[a + i];
       s.chr = in.chrom[a + i]; s.st = in.strand[a + i] ? 1 : 0;
-      int j = i;
-      while (j > 0 && sp[j - 1].qs > s.qs) { sp[j] = sp[j - 1]; --j; }
-      sp[j] = s;
+      sa_insert(sp, i, s);
     }
-    const int64_t L = in.read_len[r];
-    bool trig = false;
-    if (k == 2) {
-      if (sp[0].chr == sp[1].chr) {
-        if (sp[0].st == sp[1].st) {
-          SaSeg e1 = sp[0], e2 = sp[1];
-          if (e1.st == 1) { e1 = sa_mirror(sp[1], L); e2 = sa_mirror(sp[0], L); em.rev ^= 1; }
-          em.ins_del(e1, e2, true);
-        }
-      } else {
-        trig = true;
-      }
-    } else {
-      for (int i = 0; i + 2 < k; ++i) {
-        if (sp[i].chr == sp[i + 1].chr) {
-          if (sp[i + 1].chr == sp[i + 2].chr && sp[i].st == sp[i + 2].st && sp[i].st == sp[i + 1].st) {
-            SaSeg e1 = sp[i], e2 = sp[i + 1], e3 = sp[i + 2];
-            if (e1.st == 1) {
-              e1 = sa_mirror(sp[i + 2], L); e2 = sa_mirror(sp[i + 1], L); e3 = sa_mirror(sp[i], L);
-              em.rev ^= 1;
-            }
-            em.ins_del(e1, e2, e3.rs >= e2.re);
-            if (k - 3 == i) em.ins_del(e2, e3, true);
-          }
-        } else {
-          trig = true;
-        }
-      }
-    }
-    if (k >= 3 && trig && sp[0].chr == sp[k - 1].chr && sp[0].st == sp[k - 1].st) {  // SE:303-326
-      SaSeg e1 = sp[0], e2 = sp[k - 1];
-      if (sp[0].st == 1) { e1 = sa_mirror(sp[k - 1], L); e2 = sa_mirror(sp[0], L); em.rev ^= 1; }
-      const int64_t dis_ref = e2.rs - e1.re, dis_read = e2.qs - e1.qe, d = dis_read - dis_ref;
-      if (dis_ref < 100 && d >= sv_size && (d <= max_size || max_size == -1)) {
-        const int64_t h = dis_ref / 2;
-        em.put(VSV_INS, min(e2.rs, e1.re), d, e1.qe + h, e2.qs - h);
-      }
-    }
+    sa_analyze(sp, k, in.read_len[r], em);
   }
   cnt[r] = em.n;
 }

@@ -7,6 +7,7 @@
 // across a gap larger than the rule's max shift) and walking each segment in order.
 #include <cub/device/device_radix_sort.cuh>
 
+#include "vsv_rules.cuh"
 #include "vsv_search.cuh"
 
 // --------------------------------------------------------------------------------
@@ -50,75 +51,6 @@ extern "C" int vsv_argsort_stable(vsv_ctx* ctx, const int32_t* key, int64_t n, i
 // --------------------------------------------------------------------------------
 // split pairs
 // --------------------------------------------------------------------------------
-__device__ __forceinline__ bool is_clip(uint32_t op) { return (op & 15u) == 4u || (op & 15u) == 5u; }
-
-// One consecutive same-name record pair -> at most one signature.
-// ECS_H:307-371 / ECS_O:307-382 / ECS_C:328-402 / ERS:147-197.
-__device__ bool split_rule(int variant, int min_mapq, int32_t end1, int32_t rl1, uint32_t last1, int mq1, int rv1,
-                           int32_t pos2, uint32_t first2, int mq2, int rv2, vsv_sig& o) {
-  if (rv1 != rv2 || mq1 < min_mapq || mq2 < min_mapq) return false;
-  if (!is_clip(last1) || !is_clip(first2)) return false;
-  const int64_t Ref1e = end1, Ref2s = pos2;
-  const int64_t Read1e = (int64_t)rl1 - (int64_t)(last1 >> 4);
-  const int64_t Read2s = (int64_t)(first2 >> 4);
-  const int64_t D = (Ref2s - Ref1e) - (Read2s - Read1e);
-  if (llabs(D) > 50000) return false;
-  if (variant == VSV_SPLIT_READS) {
-    const int64_t O = Ref1e - Ref2s;
-    if (O < 30 && D >= 30) {
-      o.type = VSV_DEL; o.pos = (int32_t)Ref1e; o.len = (int32_t)D; o.q0 = (int32_t)Read1e; o.q1 = (int32_t)Read2s;
-      return true;
-    }
-    if (O < 30 && D <= -30) {
-      o.type = VSV_INS; o.pos = (int32_t)((Ref1e + Ref2s) / 2); o.len = (int32_t)llabs(D);
-      o.q0 = (int32_t)Read1e; o.q1 = (int32_t)Read2s;
-      return true;
-    }
-    return false;
-  }
-  if (variant == VSV_SPLIT_HIFI) {
-    if (D >= 30) {
-      const int64_t O = Read1e - Read2s;
-      if (llabs(O) <= 3000) {
-        const int64_t h = O / 2;  // int(O/2): truncation toward zero, as C
-        o.type = VSV_DEL; o.pos = (int32_t)(Ref1e - h); o.len = (int32_t)D;
-        o.q0 = (int32_t)(Read1e - h); o.q1 = o.q0 + 1;
-        return true;
-      }
-      return false;
-    }
-    if (D <= -30) {
-      const int64_t O = Ref1e - Ref2s;
-      if (O < 3000) {
-        o.type = VSV_INS; o.len = (int32_t)llabs(Read2s - Read1e + O);
-        o.pos = (int32_t)(llabs(O) > 400 ? (Ref1e + Ref2s) / 2 : Ref2s);
-        o.q0 = (int32_t)(Read1e - O); o.q1 = (int32_t)Read2s;
-        return true;
-      }
-    }
-    return false;
-  }
-  const double r = variant == VSV_SPLIT_ONT ? 0.5 : 0.3;
-  const double lo = variant == VSV_SPLIT_ONT ? 0.8 : r;
-  if (D >= 30) {
-    const int64_t O = Read1e - Read2s;
-    const double dr = (double)D * r;
-    if (-dr <= (double)O && (double)O <= dr) {
-      o.type = VSV_DEL; o.pos = (int32_t)Ref1e; o.len = (int32_t)D; o.q0 = (int32_t)Read1e; o.q1 = (int32_t)Read2s;
-      return true;
-    }
-    return false;
-  }
-  const int64_t O = Ref1e - Ref2s;
-  if ((double)D * lo <= (double)O && (double)O <= (double)llabs(D) * r && D <= -30) {
-    o.type = VSV_INS; o.len = (int32_t)llabs(Read2s - Read1e + O);
-    o.pos = (int32_t)(llabs(O) > 400 ? (Ref1e + Ref2s) / 2 : Ref2s);
-    o.q0 = (int32_t)(Read1e - O); o.q1 = (int32_t)Read2s;
-    return true;
-  }
-  return false;
-}
-
 __global__ void k_select_flags(const uint8_t* __restrict__ sel, int64_t n, int32_t* __restrict__ f) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) f[i] = sel[i] ? 1 : 0;
@@ -523,14 +455,6 @@ extern "C" int vsv_del_cov(vsv_ctx* ctx, const int32_t* call_start, const int32_
 // tie_mode 1: `.sigs` order (SE:637-638 `sort -k2,2 -k3,3n`, LC_ALL=C): pos numeric, ties by
 //             the rest of the line, whose first field is len as a DECIMAL STRING
 //             ("100" < "95", "10" < "100").
-__device__ __forceinline__ unsigned long long len_string_key(int32_t len) {
-  unsigned long long v = (unsigned long long)(uint32_t)max(len, 0);
-  int digits = 1;
-  for (unsigned long long t = v; t >= 10ull; t /= 10ull) ++digits;
-  unsigned long long scaled = v;
-  for (int d = digits; d < 10; ++d) scaled *= 10ull;  // left-justify to 10 digits
-  return (scaled << 4) | (unsigned long long)digits;
-}
 // After the stable sort by position, ties are in input order.  The `.sigs` tie order is a property
 // of the runs of equal position only, and those runs are short (a handful of reads at one base),
 // so they are fixed in place instead of paying a second full-width radix sort:

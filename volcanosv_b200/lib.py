@@ -25,6 +25,69 @@ SIG_DTYPE = np.dtype([("rec", "<i4"), ("type", "<i4"), ("pos", "<i4"), ("len", "
 assert SIG_DTYPE.itemsize == 32
 
 
+DTYPE_CODE = {"Hifi": 0, "ONT": 1, "CLR": 2}
+OVF_READS, OVF_CUTE, OVF_DEL, OVF_INS, OVF_STAGE, OVF_POS, OVF_DUPLIST = 1, 2, 4, 8, 16, 32, 64
+TAB_READS, TAB_CUTE, TAB_DEL_ROWS, TAB_INS_ROWS, TAB_REF_END, TAB_READ_LEN, TAB_IN_BED, TAB_INS_DUPS, TAB_UDEL, TAB_UINS = range(10)
+JOIN_FP, JOIN_COV, JOIN_SUPPORT, JOIN_GENOTYPE = 1, 2, 4, 8
+ROW_SA_REV = 256
+
+
+class Params(C.Structure):
+    """struct vsv_params (include/volcanosv_b200.h): every constant of the reference's operators."""
+    _fields_ = [("dtype", C.c_int32), ("reads_min_len", C.c_int32), ("reads_min_mapq", C.c_int32), ("cute_min_len", C.c_int32),
+                ("cute_min_mapq", C.c_int32), ("cute_min_read_len", C.c_int32), ("sa_sv_size", C.c_int32),
+                ("sa_max_size", C.c_int32), ("sa_max_parts", C.c_int32), ("batch_size", C.c_int32),
+                ("contig_min_len", C.c_int32), ("contig_min_mapq", C.c_int32), ("cluster_max_shift", C.c_int32),
+                ("pair_max_shift", C.c_int32), ("clr_max_ins_pct", C.c_double), ("clr_min_var_dist", C.c_double),
+                ("fp_max_comp", C.c_int32), ("fp_max_shift", C.c_int32), ("cov_flanking", C.c_int32), ("cov_min_size", C.c_int32),
+                ("cov_lb_ins", C.c_double), ("cov_rb_ins", C.c_double), ("cov_lb_del", C.c_double), ("cov_rb_del", C.c_double),
+                ("gt_ins_min_len", C.c_int32), ("gt_min_size_sim", C.c_double), ("gt_max_shift_ratio", C.c_double),
+                ("gt_min_shift", C.c_double), ("gt_ins_flank", C.c_int32), ("gt_del_large", C.c_int32), ("gt_del_off", C.c_int32),
+                ("gt_del_win", C.c_int32), ("thr_del", C.c_double * 4), ("thr_ins", C.c_double * 4)]
+
+
+class RecordsStruct(C.Structure):
+    """struct vsv_records."""
+    _fields_ = [("n_rec", C.c_int64), ("n_ops", C.c_int64), ("ops_format", C.c_int32), ("ops", C.c_void_p),
+                ("exc_idx", C.c_void_p), ("exc_val", C.c_void_p), ("n_exc", C.c_int64), ("op_off", C.c_void_p),
+                ("pos", C.c_void_p), ("mapq", C.c_void_p), ("flag", C.c_void_p), ("qlen", C.c_void_p), ("name_id", C.c_void_p),
+                ("next_same_name", C.c_void_p), ("n_sa_read", C.c_int64), ("n_sa_ent", C.c_int64), ("sa_rec", C.c_void_p),
+                ("sa_off", C.c_void_p), ("sa_chrom", C.c_void_p), ("sa_pos", C.c_void_p), ("sa_strand", C.c_void_p),
+                ("sa_first_s", C.c_void_p), ("sa_last_s", C.c_void_p), ("sa_bias", C.c_void_p), ("sa_mapq", C.c_void_p),
+                ("sa_self_chrom", C.c_int32)]
+
+
+class ShardCounts(C.Structure):
+    """struct vsv_shard_counts."""
+    _fields_ = [(k, C.c_int64) for k in ("n_reads_cigar", "n_reads_split", "n_cute", "n_del", "n_ins", "n_sa_rows", "n_del_dup",
+                                         "n_ins_maybe_dup", "n_udel", "n_uins", "overflow", "n_stage")]
+
+    def as_dict(self):
+        return {k: int(getattr(self, k)) for k, _ in self._fields_}
+
+
+def default_params(dtype: str = "Hifi") -> Params:
+    p = Params()
+    rc = load_library().vsv_params_default(C.byref(p), DTYPE_CODE[dtype])
+    if rc != 0:
+        raise VsvError(rc, "vsv_params_default")
+    return p
+
+
+def next_same_name(name_id) -> np.ndarray:
+    """next_same_name column of vsv_records: for every record the next record in BAM order with the same
+    interned qname, -1 if there is none (the consecutive pairs extract_sig_from_split_reads walks, ERS:227-237)."""
+    name_id = np.asarray(name_id)
+    n = len(name_id)
+    out = np.full(n, -1, np.int32)
+    if n < 2:
+        return out
+    o = np.argsort(name_id, kind="stable")
+    same = name_id[o[1:]] == name_id[o[:-1]]
+    out[o[:-1][same]] = o[1:][same]
+    return out
+
+
 class VsvError(RuntimeError):
     def __init__(self, code, msg):
         super().__init__("volcanosv_b200 error %d: %s" % (code, msg))
@@ -85,8 +148,24 @@ SIGNATURES = {
     "vsv_bam_chrom_fill": [_vp, _int, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, C.POINTER(_i64), _vp, _vp, _vp,
                            _vp, _vp, _vp],
     "vsv_genotype": [_vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp],
+    "vsv_span_depth_sorted": [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _i64, _vp],
+    "vsv_params_default": [_vp, _int],
+    "vsv_ctx_set_params": [_vp, _vp],
+    "vsv_ctx_get_params": [_vp, _vp],
+    "vsv_cigar_class_sums": [_vp, _vp, _vp, _i64, _vp, _vp, _vp],
+    "vsv_shard_create": [_vp, C.POINTER(_vp)],
+    "vsv_shard_destroy": [_vp],
+    "vsv_shard_reserve": [_vp, _i64, _i64, _i64, _i64],
+    "vsv_shard_load": [_vp, _vp],
+    "vsv_shard_set_bed": [_vp, _vp, _vp, _i64, _i64],
+    "vsv_shard_scan": [_vp],
+    "vsv_shard_counts_get": [_vp, _vp],
+    "vsv_shard_drop_ins": [_vp, _vp, _i64],
+    "vsv_shard_fetch": [_vp, _int, _vp, _i64, C.POINTER(_i64)],
+    "vsv_shard_candidates": [_vp, _int, _vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
+    "vsv_shard_scan_kernel_ms": [_vp, C.POINTER(C.c_float)],
 }
-_RESTYPE = {"vsv_ctx_destroy": None, "vsv_last_error": C.c_char_p, "vsv_version": C.c_char_p, "vsv_bam_close": None,
+_RESTYPE = {"vsv_ctx_destroy": None, "vsv_shard_destroy": None, "vsv_last_error": C.c_char_p, "vsv_version": C.c_char_p, "vsv_bam_close": None,
             "vsv_bam_last_error": C.c_char_p, "vsv_ops12_bytes": _i64}
 
 
@@ -149,6 +228,22 @@ class Context:
     def _chk(self, rc):
         if rc != 0:
             raise VsvError(rc, (self.lib.vsv_last_error(self.h) or b"").decode())
+
+    def set_params(self, params: "Params"):
+        self._chk(self.lib.vsv_ctx_set_params(self.h, C.byref(params)))
+
+    def get_params(self) -> "Params":
+        p = Params()
+        self._chk(self.lib.vsv_ctx_get_params(self.h, C.byref(p)))
+        return p
+
+    def cigar_class_sums(self, ops, op_off):
+        """(sum of I lengths, sum of M lengths, number of M ops) per record (ECS_C:53-70)."""
+        ops, op_off = _arr(ops, np.uint32), _arr(op_off, np.int64)
+        n = len(op_off) - 1
+        out = [np.zeros(n, np.int64) for _ in range(3)]
+        self._chk(self.lib.vsv_cigar_class_sums(self.h, _p(ops), _p(op_off), n, _p(out[0]), _p(out[1]), _p(out[2])))
+        return tuple(out)
 
     def set_device_io(self, on: bool):
         self._chk(self.lib.vsv_ctx_set_device_io(self.h, 1 if on else 0))
@@ -385,6 +480,135 @@ class Context:
         out = np.zeros(len(ia), np.int32)
         self._chk(self.lib.vsv_edit_distance_batch(self.h, _p(chars), _p(off), len(bs), _p(ia), _p(ib), len(ia), _p(out)))
         return out
+
+
+class Shard:
+    """One vsv_shard on a HOST-IO context: numpy in, numpy out (the operators' path).  The device-resident
+    driver for benchmarks / queues of shards is volcanosv_b200.pipeline.ChromShard."""
+
+    def __init__(self, ctx: Context):
+        self.ctx, self.lib = ctx, ctx.lib
+        self.h = _vp()
+        ctx._chk(self.lib.vsv_shard_create(ctx.h, C.byref(self.h)))
+        self._keep = []
+        self.counts = None
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.vsv_shard_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:  # noqa: BLE001
+            pass
+
+    def reserve(self, cap_reads=0, cap_cute=0, cap_del=0, cap_ins=0):
+        self.ctx._chk(self.lib.vsv_shard_reserve(self.h, int(cap_reads), int(cap_cute), int(cap_del), int(cap_ins)))
+
+    def load(self, ops, op_off, pos, mapq, qlen, flag=None, name_id=None, next_name=None, sa=None, self_chrom=0):
+        """sa: dict(rec, off, chrom, pos, strand, first_s, last_s, bias, mapq) or None."""
+        ops = _arr(ops, np.uint32)
+        if len(ops) and ops.ctypes.data % 16:
+            ops = _aligned_copy(ops)
+        cols = dict(ops=ops, op_off=_arr(op_off, np.int64), pos=_arr(pos, np.int32), mapq=_arr(mapq, np.uint8),
+                    qlen=_arr(qlen, np.int32), flag=_arr(flag, np.uint16), name=_arr(name_id, np.int32),
+                    nxt=_arr(next_name, np.int32))
+        r = RecordsStruct()
+        r.n_rec, r.n_ops, r.ops_format = len(cols["pos"]), len(ops), 32
+        ptr = lambda a: None if a is None else a.ctypes.data
+        r.ops, r.op_off, r.pos, r.mapq, r.flag, r.qlen = (ptr(cols[k]) for k in ("ops", "op_off", "pos", "mapq", "flag", "qlen"))
+        r.name_id, r.next_same_name = ptr(cols["name"]), ptr(cols["nxt"])
+        if sa is not None and len(sa["rec"]):
+            sc = dict(rec=_arr(sa["rec"], np.int32), off=_arr(sa["off"], np.int64), chrom=_arr(sa["chrom"], np.int32),
+                      pos=_arr(sa["pos"], np.int32), strand=_arr(sa["strand"], np.uint8), first_s=_arr(sa["first_s"], np.int32),
+                      last_s=_arr(sa["last_s"], np.int32), bias=_arr(sa["bias"], np.int32), mapq=_arr(sa["mapq"], np.uint8))
+            cols.update({"sa_" + k: v for k, v in sc.items()})
+            r.n_sa_read, r.n_sa_ent = len(sc["rec"]), len(sc["pos"])
+            r.sa_rec, r.sa_off, r.sa_chrom, r.sa_pos, r.sa_strand = (ptr(sc[k]) for k in ("rec", "off", "chrom", "pos", "strand"))
+            r.sa_first_s, r.sa_last_s, r.sa_bias, r.sa_mapq = (ptr(sc[k]) for k in ("first_s", "last_s", "bias", "mapq"))
+        r.sa_self_chrom = int(self_chrom)
+        self._keep = [cols]
+        self.n_rec = int(r.n_rec)
+        self.ctx._chk(self.lib.vsv_shard_load(self.h, C.byref(r)))
+
+    def set_bed(self, regions, chrom_len):
+        """regions: list of (start - 1000, end + 1000) as load_bed widens them (SE:69), or None."""
+        if regions is None:
+            self.ctx._chk(self.lib.vsv_shard_set_bed(self.h, None, None, -1, int(chrom_len)))
+            return
+        b0 = np.asarray([x[0] for x in regions], np.int32)
+        b1 = np.asarray([x[1] for x in regions], np.int32)
+        self.ctx._chk(self.lib.vsv_shard_set_bed(self.h, _p(b0) if len(b0) else None, _p(b1) if len(b1) else None, len(b0), int(chrom_len)))
+
+    def scan(self, max_tries: int = 4):
+        """Runs the step; grows a table that overflowed and retries.  Returns the counts dict."""
+        for _ in range(max_tries):
+            self.ctx._chk(self.lib.vsv_shard_scan(self.h))
+            c = ShardCounts()
+            self.ctx._chk(self.lib.vsv_shard_counts_get(self.h, C.byref(c)))
+            d = c.as_dict()
+            ov = d["overflow"]
+            if ov & OVF_POS:
+                raise VsvError(E_ARG, "a position is negative or >= 2^28: the chromosome is too long for one shard")
+            if ov & OVF_DUPLIST:
+                raise VsvError(E_CAPACITY, "more than 65536 potential duplicate INS rows")
+            if ov == 0:
+                self.counts = d
+                return d
+            grow = lambda n: int(n * 1.25) + 1024
+            self.reserve(grow(d["n_reads_cigar"] + d["n_reads_split"]) if ov & OVF_READS else 0, grow(d["n_cute"]) if ov & OVF_CUTE else 0,
+                         grow(d["n_del"]) if ov & OVF_DEL else 0, grow(d["n_ins"]) if ov & OVF_INS else 0)
+        raise VsvError(E_CAPACITY, "vsv_shard_scan kept overflowing")
+
+    def drop_ins(self, uids):
+        u = np.sort(np.asarray(uids, np.int32))
+        self.ctx._chk(self.lib.vsv_shard_drop_ins(self.h, _p(u) if len(u) else None, len(u)))
+        c = ShardCounts()
+        self.ctx._chk(self.lib.vsv_shard_counts_get(self.h, C.byref(c)))
+        self.counts = c.as_dict()
+        return self.counts
+
+    def fetch(self, table):
+        c = self.counts
+        if table in (TAB_READS, TAB_CUTE, TAB_DEL_ROWS, TAB_INS_ROWS):
+            n = {TAB_READS: c["n_reads_cigar"] + c["n_reads_split"], TAB_CUTE: c["n_cute"], TAB_DEL_ROWS: c["n_del"],
+                 TAB_INS_ROWS: c["n_ins"]}[table]
+            out = np.empty(n, SIG_DTYPE)
+        elif table in (TAB_REF_END, TAB_READ_LEN):
+            n, out = self.n_rec, np.empty(self.n_rec, np.int32)
+        elif table == TAB_IN_BED:
+            n, out = self.n_rec, np.empty(self.n_rec, np.uint8)
+        elif table == TAB_INS_DUPS:
+            n = min(c["n_ins_maybe_dup"], 65536)
+            out = np.empty((n, 2), np.int32)
+        else:
+            n = c["n_udel"] if table == TAB_UDEL else c["n_uins"]
+            out = np.empty((3, max(n, 1)), np.int32)
+            got = _i64()
+            self.ctx._chk(self.lib.vsv_shard_fetch(self.h, table, _p(out), max(n, 1), C.byref(got)))
+            return out[0, :got.value].copy(), out[1, :got.value].copy(), out[2, :got.value].copy()
+        got = _i64()
+        self.ctx._chk(self.lib.vsv_shard_fetch(self.h, table, _p(out) if n else None, n, C.byref(got)))
+        return out[: got.value]
+
+    def candidates(self, what, pos, svlen, typ, gt=None, last_in=(0, 0), n_support=None):
+        """-> dict with the outputs of the selected stages (+ last_out for JOIN_SUPPORT)."""
+        cp, cl, ct = (_arr(x, np.int32) for x in (pos, svlen, typ))
+        cg = _arr(gt, np.int32)
+        n = len(cp)
+        li, lo = np.asarray(last_in, np.int32), np.zeros(2, np.int32)
+        o = dict(fp_support=np.zeros(n, np.int32) if what & JOIN_FP else None, cov=np.zeros(n, np.int64) if what & JOIN_COV else None,
+                 n_support=(np.zeros(n, np.int32) if what & JOIN_SUPPORT else _arr(n_support, np.int32)) if what & (JOIN_SUPPORT | JOIN_GENOTYPE) else None,
+                 match_id=np.zeros(n, np.int32) if what & JOIN_SUPPORT else None,
+                 depth2=np.zeros(n, np.int32) if what & JOIN_GENOTYPE else None, ratio=np.zeros(n, np.float64) if what & JOIN_GENOTYPE else None,
+                 new_gt=np.zeros(n, np.int32) if what & JOIN_GENOTYPE else None)
+        self.ctx._chk(self.lib.vsv_shard_candidates(self.h, what, _p(cp), _p(cl), _p(ct), _p(cg), n, _p(li), _p(o["fp_support"]), _p(o["cov"]),
+                                                   _p(o["n_support"]), _p(o["match_id"]), _p(o["depth2"]), _p(o["ratio"]), _p(o["new_gt"]),
+                                                   _p(lo) if what & JOIN_SUPPORT else None))
+        o["last_out"] = (int(lo[0]), int(lo[1]))
+        return o
 
 
 class BamFile:

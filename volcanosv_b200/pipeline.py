@@ -1,19 +1,17 @@
 """Device-resident large-indel hot path for one chromosome shard.
 
-`ChromShard.run()` chains the C-ABI calls of include/volcanosv_b200.h with every
-intermediate staying in HBM (the ctx is in device-IO mode): read scan (ERS), cuteSV-style
-scan + in-read merge (SE), `.sigs` ordering and grouping, FP-filter support, coverage
-support, supporting-signature count, spanning depth and the genotype decision.
+`ChromShard` drives ONE `vsv_shard` (include/volcanosv_b200.h, csrc/vsv_shard.cu) on a device-IO
+context: the packed records are uploaded once, `run()` enqueues the whole read-side chain of the
+reference (RVC:83-96 ERS -> FPF; FGC:111-172 SE -> CSS -> GTD/GTI) on one stream without a single
+host synchronisation, and the counts / per-candidate results are read once at the end.  The
+operators (volcanosv_b200.operators) format the reference's files from the same engine, so the
+benchmarked path and the byte-exact path are one call chain.
 torch is used only for device / pinned allocations and the H2D / D2H copies.
-
-Reference call chain reproduced: LI/Raw_variant_call.py:83-96 (ERS -> FPF) and
-LI/filter_GT_correction.py:111-172 (SE -> CSS -> GTD/GTI).
 """
 from __future__ import annotations
 
 import contextlib
 import ctypes as C
-from concurrent.futures import ThreadPoolExecutor
 from dataclasses import dataclass, field
 from typing import Dict, Optional
 
@@ -23,60 +21,103 @@ import torch
 from . import lib as L
 
 NAN = float("nan")
-# LI/para/GT_correction_para_<dtype>_<type>.txt : t_large_11, t_small_11, t_large_01, t_small_01
+# LI/para/GT_correction_para_<dtype>_<type>.txt (the library holds the same numbers: vsv_params_default)
 GT_THRESHOLDS = {
     "Hifi": dict(DEL=[0.6, 0.69, 0.71, 0.91], INS=[NAN, 0.59, 0.63, 0.79]),
     "ONT": dict(DEL=[0.61, 0.61, 0.68, 0.79], INS=[NAN, NAN, 0.67, 0.72]),
     "CLR": dict(DEL=[0.55, 0.59, 0.65, 0.75], INS=[NAN, NAN, 0.64, 0.75]),
 }
+_REC_COLS = ("op_off", "pos", "mapq", "qlen", "flag", "name_id", "next_same_name")
+_SA_COLS = ("sa_rec", "sa_off", "sa_chrom", "sa_pos", "sa_strand", "sa_first_s", "sa_last_s", "sa_bias", "sa_mapq")
+_COL_DTYPE = dict(op_off=np.int64, pos=np.int32, mapq=np.uint8, qlen=np.int32, flag=np.uint16, name_id=np.int32,
+                  next_same_name=np.int32, sa_rec=np.int32, sa_off=np.int64, sa_chrom=np.int32, sa_pos=np.int32,
+                  sa_strand=np.uint8, sa_first_s=np.int32, sa_last_s=np.int32, sa_bias=np.int32, sa_mapq=np.uint8)
 
 
 def _dp(t: Optional[torch.Tensor]):
     return None if t is None else C.c_void_p(t.data_ptr())
 
 
+def _as_tensor(src, name=None):
+    if isinstance(src, np.ndarray):
+        if name in _COL_DTYPE and src.dtype != _COL_DTYPE[name]:
+            src = src.astype(_COL_DTYPE[name])
+        if src.dtype == np.uint32:
+            src = src.view(np.int32)
+        elif src.dtype == np.uint16:
+            src = src.view(np.int16)
+        src = torch.from_numpy(np.ascontiguousarray(src))
+    elif src.dtype == torch.uint16:
+        src = src.view(torch.int16)
+    elif src.dtype == torch.uint32:
+        src = src.view(torch.int32)
+    return src
+
+
 @dataclass
 class ShardResult:
     n_rec: int = 0
     n_ops: int = 0
-    n_read_sigs: int = 0
-    n_cute_sigs: int = 0
-    n_del: int = 0
-    n_ins: int = 0
-    n_udel: int = 0
-    n_uins: int = 0
     n_cand: int = 0
+    counts: Dict[str, int] = field(default_factory=dict)
     scan_ms: list = field(default_factory=list)      # dominant kernel, per scan call
     out: Dict[str, torch.Tensor] = field(default_factory=dict)
+
+    # names the round-1 callers used
+    @property
+    def n_read_sigs(self):
+        return self.counts.get("n_reads_cigar", 0) + self.counts.get("n_reads_split", 0)
+
+    @property
+    def n_cute_sigs(self):
+        return self.counts.get("n_cute", 0)
+
+    @property
+    def n_udel(self):
+        return self.counts.get("n_udel", 0)
+
+    @property
+    def n_uins(self):
+        return self.counts.get("n_uins", 0)
 
 
 class ChromShard:
     """Buffers and call chain for one (chromosome, GPU) shard."""
 
-    def __init__(self, device: int = 0, dtype: str = "ONT"):
+    def __init__(self, device: int = 0, dtype: str = "ONT", params: Optional[L.Params] = None):
         if not torch.cuda.is_available():
             raise L.VsvError(L.E_CUDA, "no CUDA device: volcanosv_b200 has no CPU path")
         self.device = torch.device("cuda", device)
         torch.cuda.set_device(self.device)
         self.ctx = L.Context(device)
+        self.ctx.set_params(params if params is not None else L.default_params(dtype))
         self.ctx.set_device_io(True)
         self.lib = self.ctx.lib
         self.h = self.ctx.h
         self.dtype = dtype
-        self.thr_del = (C.c_double * 4)(*GT_THRESHOLDS[dtype]["DEL"])
-        self.thr_ins = (C.c_double * 4)(*GT_THRESHOLDS[dtype]["INS"])
+        self.sh = C.c_void_p()
+        self._chk(self.lib.vsv_shard_create(self.h, C.byref(self.sh)))
         self.d: Dict[str, torch.Tensor] = {}
-        self.sig_cap = 0
         self.h2d_bytes = 0
         self.d2h_bytes = 0
         self._pending = None
-        # independent branches of the call chain (read-signature sort; DEL and INS `.sigs` order +
-        # grouping) run on side contexts = their own streams, driven by two worker threads (the C
-        # calls release the GIL): their kernels and count read-backs overlap instead of queueing
-        self.side = [L.Context(device), L.Context(device)]
-        for c in self.side:
-            c.set_device_io(True)
-        self.pool = ThreadPoolExecutor(max_workers=2)
+        self.n_rec = self.n_ops = self.n_cand = 0
+        self.caps = None            # (reads, cute, del, ins) once a run has measured the need
+
+    def close(self):
+        if getattr(self, "sh", None):
+            self.lib.vsv_shard_destroy(self.sh)
+            self.sh = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:  # noqa: BLE001
+            pass
+
+    def _chk(self, rc):
+        if rc != 0:
+            raise L.VsvError(rc, (self.lib.vsv_last_error(self.h) or b"").decode())
 
     # ---- allocation ------------------------------------------------------------------
     def _buf(self, name, n, dtype):
@@ -86,236 +127,159 @@ class ChromShard:
             self.d[name] = t
         return t
 
-    def upload(self, batch, cands, n_ops: Optional[int] = None, stream: Optional["torch.cuda.Stream"] = None):
-        """H2D of one shard's inputs (packed records + candidate table).  Values are numpy
-        arrays or (pinned) torch CPU tensors; `ops` may be uint32 numpy or an int32 tensor.
-        With `stream` the copies are only enqueued there (pinned sources) and `finish_upload()`
-        must be called before `run()`: that is how `ShardStream` overlaps the upload of the
-        next shard with the kernels of the current one."""
+    def upload(self, batch, cands=None, n_ops: Optional[int] = None, stream: Optional["torch.cuda.Stream"] = None):
+        """H2D of one shard's inputs (packed records + optional candidate table).  Values are numpy arrays or
+        (pinned) torch CPU tensors.  `ops` (BAM-native u32) or one of the staging formats `ops16` / `ops12` /
+        `ops8` with `exc_idx` / `exc_val`.  With `stream` the copies are only enqueued there (pinned sources)
+        and `finish_upload()` must be called before `run()`: that is how `ShardStream` overlaps the upload of
+        the next shard with the kernels of the current one."""
         self.h2d_bytes = 0
         self._pending = None
+        rec = L.RecordsStruct()
 
         def put(name, src):
-            if isinstance(src, np.ndarray):
-                if src.dtype == np.uint32:
-                    src = src.view(np.int32)
-                src = torch.from_numpy(np.ascontiguousarray(src))
-            dst = self._buf(name, src.numel(), src.dtype)
+            src = _as_tensor(src, name)
+            dst = self._buf("in_" + name, src.numel(), src.dtype)
             dst[: src.numel()].copy_(src, non_blocking=True)
             self.h2d_bytes += src.numel() * src.element_size()
-            return src
+            return dst
 
         with torch.cuda.stream(stream if stream is not None else torch.cuda.current_stream()):
-            expand = None
-            if "ops12" in batch:
-                # densest staging (vsv_expand_ops12): 12 bits per pair of ops + both words of the odd pairs
-                src12 = batch["ops12"]
-                if isinstance(src12, np.ndarray):
-                    src12 = torch.from_numpy(np.ascontiguousarray(src12.view(np.uint8)))
-                n_ops = int(n_ops if n_ops is not None else batch["op_off"][-1])
-                if src12.numel() != L.ops12_bytes(n_ops):
-                    raise ValueError("ops12: %d bytes for %d ops" % (src12.numel(), n_ops))
-                o12 = self._buf("in_ops12", src12.numel(), src12.dtype)
-                o12[: src12.numel()].copy_(src12, non_blocking=True)
-                self.h2d_bytes += src12.numel() * src12.element_size()
-                ei = put("in_exc_idx", batch["exc_idx"]) if len(batch["exc_idx"]) else None
-                put("in_exc_val", batch["exc_val"]) if len(batch["exc_val"]) else None
-                expand = (o12, 0 if ei is None else ei.numel(), self._buf("in_ops", n_ops, torch.int32), 12)
-            elif "ops16" in batch or "ops8" in batch:
-                # compact staging (include/volcanosv_b200.h: vsv_expand_ops16 / vsv_expand_ops8): 2 bytes or
-                # 1 byte per op over PCIe, widened on the device into the BAM-native u32 array the scanners read
-                wide = "ops16" in batch
-                src16 = batch["ops16" if wide else "ops8"]
-                if isinstance(src16, np.ndarray):
-                    src16 = torch.from_numpy(np.ascontiguousarray(src16.view(np.int16 if wide else np.uint8)))
-                n_ops = int(n_ops if n_ops is not None else src16.numel())
-                o16 = self._buf("in_ops16" if wide else "in_ops8", src16.numel(), src16.dtype)
-                o16[: src16.numel()].copy_(src16, non_blocking=True)
-                self.h2d_bytes += src16.numel() * src16.element_size()
-                ei = put("in_exc_idx", batch["exc_idx"]) if len(batch["exc_idx"]) else None
-                put("in_exc_val", batch["exc_val"]) if len(batch["exc_val"]) else None
-                expand = (o16, 0 if ei is None else ei.numel(), self._buf("in_ops", n_ops, torch.int32), wide)
-            else:
-                put("in_ops", batch["ops"])
-            for k in ("op_off", "pos", "mapq", "qlen"):
-                put("in_" + k, batch[k])
-            for k in ("pos", "svlen", "type", "gt"):
-                put("cand_" + k, cands[k])
+            fmt = next((f for f in (12, 16, 8) if "ops%d" % f in batch), 32)
+            key = "ops" if fmt == 32 else "ops%d" % fmt
+            src = batch[key]
+            if isinstance(src, np.ndarray) and fmt == 12:
+                src = src.view(np.uint8)
+            t_ops = put(key, src)
+            if n_ops is None:
+                n_ops = int(batch["op_off"][-1])
+            if fmt == 12 and _as_tensor(src).numel() != L.ops12_bytes(n_ops):
+                raise ValueError("ops12: %d bytes for %d ops" % (_as_tensor(src).numel(), n_ops))
+            rec.ops, rec.ops_format, rec.n_ops = t_ops.data_ptr(), fmt, int(n_ops)
+            if fmt != 32 and len(batch["exc_idx"]):
+                rec.exc_idx, rec.exc_val = put("exc_idx", batch["exc_idx"]).data_ptr(), put("exc_val", batch["exc_val"]).data_ptr()
+                rec.n_exc = len(batch["exc_idx"])
+            for k in _REC_COLS:
+                if k in batch and batch[k] is not None:
+                    setattr(rec, k, put(k, batch[k]).data_ptr())
+            n_rec = len(batch["pos"])
+            rec.n_rec = n_rec
+            if "sa_rec" in batch and len(batch["sa_rec"]):
+                for k in _SA_COLS:
+                    setattr(rec, k, put(k, batch[k]).data_ptr())
+                rec.n_sa_read, rec.n_sa_ent = len(batch["sa_rec"]), len(batch["sa_pos"])
+                rec.sa_self_chrom = int(batch.get("sa_self_chrom", 0))
+            if cands is not None:
+                for k in ("pos", "svlen", "type", "gt"):
+                    put("cand_" + k, cands[k])
+                self.n_cand = len(cands["pos"])
             done = torch.cuda.Event()
             done.record()
-        self.n_rec = len(batch["pos"])
-        self.n_ops = int(n_ops) if n_ops is not None else int(batch["op_off"][-1])
-        self.n_cand = len(cands["pos"])
-        self._pending = (done, expand)
+        self.n_rec, self.n_ops = n_rec, int(n_ops)
+        self._pending = (done, rec)
         if stream is None:
             self.finish_upload()
 
+    def set_candidates(self, cands):
+        """Replaces the resident candidate table (pos, svlen, type, gt)."""
+        for k in ("pos", "svlen", "type", "gt"):
+            src = _as_tensor(cands[k])
+            self._buf("in_cand_" + k, src.numel(), src.dtype)[: src.numel()].copy_(src, non_blocking=True)
+        self.n_cand = len(cands["pos"])
+        torch.cuda.current_stream().synchronize()
+
     def finish_upload(self):
-        """Waits for the enqueued copies and widens a compact batch on the device."""
+        """Waits for the enqueued copies and hands the device columns to the engine (widening a staging format)."""
         if self._pending is None:
             return
-        done, expand = self._pending
+        done, rec = self._pending
         self._pending = None
         done.synchronize()
-        if expand is not None:
-            o16, n_exc, ops, wide = expand
-            fn = self.lib.vsv_expand_ops12 if wide == 12 else (self.lib.vsv_expand_ops16 if wide else self.lib.vsv_expand_ops8)
-            self._chk(fn(self.h, _dp(o16), self.n_ops, _dp(self.d["in_exc_idx"]) if n_exc else None,
-                    _dp(self.d["in_exc_val"]) if n_exc else None, n_exc, _dp(ops)))
-            self.ctx.sync()
-
-    def _chk(self, rc):
-        if rc != 0:
-            raise L.VsvError(rc, (self.lib.vsv_last_error(self.h) or b"").decode())
+        self._chk(self.lib.vsv_shard_load(self.sh, C.byref(rec)))
 
     # ---- the hot path ----------------------------------------------------------------
-    def run(self) -> ShardResult:
-        lib, h, d = self.lib, self.h, self.d
-        n_rec, n_ops, n_cand = self.n_rec, self.n_ops, self.n_cand
-        res = ShardResult(n_rec=n_rec, n_ops=n_ops, n_cand=n_cand)
-        i32, u8, i64, f64 = torch.int32, torch.uint8, torch.int64, torch.float64
-        ops, op_off, pos, mapq, qlen = (d["in_" + k] for k in ("ops", "op_off", "pos", "mapq", "qlen"))
-        cap = max(self.sig_cap, 1 << 16, n_ops // 64)
-        sig = lambda name: self._buf(name, cap * 8, i32)  # vsv_sig = 8 x int32
-        rt, qt, xt = (self._buf(k, n_rec, i32) for k in ("ref_total", "qry_total", "aux_total"))
-        # -- stage 1: BOTH read scanners in one pass over the ops -------------------------
-        #    stream "reads": ERS:107-145 (mapq>=50, >=30 bp); stream "cute": SE:438-478
-        #    (query_length>=500, mapq>=20, >=10 bp)
-        enable = self._buf("enable", n_rec, u8)
-        self._chk(lib.vsv_ge_u8(h, _dp(qlen), 500, n_rec, _dp(enable)))                 # SE:439
-        s_reads, s_cute = sig("sig_reads"), sig("sig_cute")
-        n_r_, n_c_ = C.c_int64(), C.c_int64()
-        rc = lib.vsv_scan_reads_fused(h, 30, 50, 10, 20, _dp(ops), _dp(op_off), _dp(pos), _dp(mapq), _dp(enable), n_rec,
-                                      _dp(s_reads), cap, C.byref(n_r_), _dp(s_cute), cap, C.byref(n_c_), _dp(rt), _dp(qt),
-                                      _dp(xt))
-        if rc == L.E_CAPACITY:
-            self.sig_cap = int(max(n_r_.value, n_c_.value) * 1.25) + 1024
-            raise _Regrow()
-        self._chk(rc)
-        res.scan_ms.append(self.ctx.main_kernel_ms())
-        n_r, n_c = int(n_r_.value), int(n_c_.value)
-        res.n_read_sigs, res.n_cute_sigs = n_r, n_c
-        # read intervals for the depth join: [pos, pos + ref_total)  (reference_end)
-        rend = self._buf("read_end", n_rec, i32)
-        self._chk(lib.vsv_add_i32(h, _dp(pos), _dp(rt), n_rec, _dp(rend)))
-        # every buffer of the branches is taken here, on this thread
-        s_reads_sorted = sig("sig_reads_sorted")
-        rs_pos, rs_len = self._buf("rs_pos", cap, i32), self._buf("rs_len", cap, i32)
-        s_del, s_ins = sig("sig_del"), sig("sig_ins")
-        bufs = {}
-        for name in ("del", "ins"):
-            bufs[name] = (sig("sig_%s_sorted" % name), self._buf(name + "_pos", cap, i32), self._buf(name + "_len", cap, i32),
-                          tuple(self._buf("%s_u%s" % (name, k), cap, i32) for k in "cpln"))
-
-        cpos, clen, ctyp, cgt = (d["cand_" + k] for k in ("pos", "svlen", "type", "gt"))
-        fp = self._buf("fp_support", n_cand, i32)
-        cend = self._buf("cand_end", n_cand, i32)
-        self._chk(lib.vsv_add_i32(h, _dp(cpos), _dp(clen), n_cand, _dp(cend)))
-        cov = dict(ins=self._buf("cov_ins", n_cand, i64), **{"del": self._buf("cov_del", n_cand, i64)})
-        sup = dict(ins=self._buf("sup_ins", n_cand, i32), **{"del": self._buf("sup_del", n_cand, i32)})
-
-        def chk(c, rc):
-            if rc != 0:
-                raise L.VsvError(rc, (lib.vsv_last_error(c.h) or b"").decode())
-
-        def reads_branch(c):                                                              # merge_all (ERS:254-258)
-            chk(c, lib.vsv_sort_sigs(c.h, _dp(s_reads), n_r, 0, _dp(s_reads_sorted)))
-            chk(c, lib.vsv_sig_columns(c.h, _dp(s_reads_sorted), n_r, _dp(rs_pos), _dp(rs_len), None))
-            chk(c, lib.vsv_fp_support(c.h, _dp(cpos), _dp(clen), n_cand, _dp(rs_pos), _dp(rs_len), n_r, _dp(fp)))  # FPF
-            c.sync()
-
-        def sigs_branch(c, name, src, n, min_len):
-            # `.sigs` order (SE:637-638), unique signatures (GTD:65-86 / GTI:67-101)
-            srt, p_, l_, (uc, up, ul, un) = bufs[name]
-            chk(c, lib.vsv_sort_sigs(c.h, _dp(src), n, 1, _dp(srt)))
-            chk(c, lib.vsv_sig_columns(c.h, _dp(srt), n, _dp(p_), _dp(l_), None))
-            nu = C.c_int64()
-            chk(c, lib.vsv_group_sigs(c.h, None, _dp(p_), _dp(l_), n, min_len, _dp(uc), _dp(up), _dp(ul), _dp(un), C.byref(nu)))
-            # candidate-side joins of this table: coverage support (CSS:81 / CSS:138), supporting signatures (GTD:92 / GTI:107)
-            if name == "ins":
-                chk(c, lib.vsv_ins_cov(c.h, _dp(cpos), n_cand, _dp(p_), _dp(l_), n, 1000, _dp(cov[name])))
-            else:
-                chk(c, lib.vsv_del_cov(c.h, _dp(cpos), _dp(cend), n_cand, _dp(p_), _dp(l_), n, 1000, _dp(cov[name])))
-            chk(c, lib.vsv_sig_support(c.h, None, _dp(cpos), _dp(clen), n_cand, None, _dp(up), _dp(ul), _dp(un), int(nu.value), 0,
-                                       _dp(sup[name]), None, None))
-            c.sync()
-            return (p_, l_, n, up, ul, un, int(nu.value))
-
-        self.ctx.sync()                                        # the scan's outputs are complete for the other streams
-        f_reads = self.pool.submit(reads_branch, self.side[0])
-
-        # -- in-read merge of the cuteSV-style signals (SE:373-435) -------------------------
-        nd, ni = C.c_int64(), C.c_int64()
-        self._chk(lib.vsv_merge_in_record(h, L.MODE_CUTE, _dp(s_cute), n_c, _dp(s_del), C.byref(nd), _dp(s_ins),
-                                          C.byref(ni)))
-        res.n_del, res.n_ins = int(nd.value), int(ni.value)
-        self.ctx.sync()
-
-        # -- stage 2: the DEL and INS tables are independent: one on a side stream, one here ---
-        f_del = self.pool.submit(sigs_branch, self.side[1], "del", s_del, res.n_del, 0)
-        uniq = {"ins": sigs_branch(self.ctx, "ins", s_ins, res.n_ins, 30)}
-        uniq["del"] = f_del.result()
-        f_reads.result()
-        res.n_udel, res.n_uins = uniq["del"][6], uniq["ins"][6]
-
-        # -- the joins ran inside the branches; combine per candidate type -----------------
-        cov_i, cov_d, sup_i, sup_d = cov["ins"], cov["del"], sup["ins"], sup["del"]
-        nsup = self._buf("n_support", n_cand, i32)
-        self._chk(lib.vsv_select_i32(h, _dp(ctyp), L.DEL, _dp(sup_d), _dp(sup_i), n_cand, _dp(nsup)))
-
-        # -- stage 3: spanning depth + genotype (GTD:140-170,291-318; GTI:188-196,258-283)
-        d2, ratio, ngt = self._buf("depth2", n_cand, i32), self._buf("ratio", n_cand, f64), self._buf("new_gt", n_cand, i32)
-        self._chk(lib.vsv_genotype(h, _dp(pos), _dp(rend), n_rec, _dp(cpos), _dp(clen), _dp(ctyp), _dp(cgt),
-                                   _dp(nsup), n_cand, self.thr_del, self.thr_ins, _dp(d2), _dp(ratio), _dp(ngt)))
-        res.out = dict(fp_support=fp[:n_cand], cov_ins=cov_i[:n_cand], cov_del=cov_d[:n_cand], n_support=nsup[:n_cand],
-                       depth2=d2[:n_cand], ratio=ratio[:n_cand], new_gt=ngt[:n_cand],
-                       sig_reads=s_reads_sorted[: n_r * 8], sig_del=self.d["sig_del_sorted"][: res.n_del * 8],
-                       sig_ins=self.d["sig_ins_sorted"][: res.n_ins * 8])
+    def run(self, what: int = L.JOIN_FP | L.JOIN_COV | L.JOIN_SUPPORT | L.JOIN_GENOTYPE) -> ShardResult:
+        """Enqueues scan + tables + (if a candidate table is resident) the per-candidate joins; nothing is
+        waited for.  `counts()` / `download()` synchronise."""
+        res = ShardResult(n_rec=self.n_rec, n_ops=self.n_ops, n_cand=self.n_cand)
+        self._chk(self.lib.vsv_shard_scan(self.sh))
+        n = self.n_cand
+        if n and what:
+            i32, i64, f64 = torch.int32, torch.int64, torch.float64
+            o = dict(fp_support=self._buf("fp_support", n, i32), cov=self._buf("cov", n, i64), n_support=self._buf("n_support", n, i32),
+                     match_id=self._buf("match_id", n, i32), depth2=self._buf("depth2", n, i32), ratio=self._buf("ratio", n, f64),
+                     new_gt=self._buf("new_gt", n, i32))
+            d = self.d
+            self._chk(self.lib.vsv_shard_candidates(self.sh, what, _dp(d["in_cand_pos"]), _dp(d["in_cand_svlen"]), _dp(d["in_cand_type"]),
+                                                    _dp(d["in_cand_gt"]), n, None, _dp(o["fp_support"]), _dp(o["cov"]), _dp(o["n_support"]),
+                                                    _dp(o["match_id"]), _dp(o["depth2"]), _dp(o["ratio"]), _dp(o["new_gt"]), None))
+            res.out = {k: v[:n] for k, v in o.items()}
         return res
 
-    def run_safe(self) -> ShardResult:
-        """run() with one retry if a signature buffer had to grow."""
-        for _ in range(4):
-            try:
-                return self.run()
-            except _Regrow:
-                for k in list(self.d):
-                    if k.startswith(("sig_", "rs_", "del_", "ins_")):
-                        del self.d[k]
-        raise L.VsvError(L.E_CAPACITY, "signature buffers kept growing")
+    def counts(self) -> Dict[str, int]:
+        c = L.ShardCounts()
+        self._chk(self.lib.vsv_shard_counts_get(self.sh, C.byref(c)))
+        return c.as_dict()
+
+    def run_safe(self, what: int = 15) -> ShardResult:
+        """run() + counts; a table that overflowed is grown and the step repeated; capacities far above the
+        measured need are tightened for the next run (the sort works on capacity-sized arrays)."""
+        for _ in range(5):
+            res = self.run(what)
+            c = self.counts()
+            res.counts = c
+            res.scan_ms.append(self.ctx.main_kernel_ms())
+            ov = c["overflow"]
+            need = (c["n_reads_cigar"] + c["n_reads_split"], c["n_cute"], c["n_del"], c["n_ins"])
+            if ov & L.OVF_POS:
+                raise L.VsvError(L.E_ARG, "a position is negative or >= 2^28: the chromosome is too long for one shard")
+            if ov & L.OVF_DUPLIST:
+                raise L.VsvError(L.E_CAPACITY, "more than 65536 potential duplicate INS rows")
+            tight = tuple(int(x * 1.25) + 4096 for x in need)
+            if ov == 0:
+                if self.caps is None or any(a > 2 * b for a, b in zip(self.caps, tight)):
+                    self.caps = tight
+                    self._chk(self.lib.vsv_shard_reserve(self.sh, *tight))
+                return res
+            self.caps = tight
+            self._chk(self.lib.vsv_shard_reserve(self.sh, *tight))
+        raise L.VsvError(L.E_CAPACITY, "signature tables kept overflowing")
 
     def sync(self):
         self.ctx.sync()
         torch.cuda.current_stream().synchronize()
 
+    def fetch(self, table):
+        """A table of the engine as numpy (synchronises).  See lib.TAB_*."""
+        self.ctx.sync()
+        sh = L.Shard.__new__(L.Shard)          # borrow the fetch logic of the host-IO wrapper (fetch always copies to the host)
+        sh.ctx, sh.lib, sh.h, sh.counts, sh.n_rec = self.ctx, self.lib, self.sh, self.counts(), self.n_rec
+        try:
+            return L.Shard.fetch(sh, table)
+        finally:
+            sh.h = None
+
     def download(self, res: ShardResult, pinned: Optional[Dict[str, torch.Tensor]] = None,
                  stream: Optional["torch.cuda.Stream"] = None) -> Dict[str, np.ndarray]:
-        """D2H of the shard's results (per-candidate table + signature arrays)."""
+        """D2H of the per-candidate results (what the VCF / TSV writers print)."""
         self.ctx.sync()
         out = {}
         self.d2h_bytes = 0
         ctxm = torch.cuda.stream(stream) if stream is not None else contextlib.nullcontext()
         with ctxm:
-            self._download_into(res, pinned, out)
+            for k, t in res.out.items():
+                if pinned is not None:
+                    dst = pinned.get(k)
+                    if dst is None or dst.numel() < t.numel() or dst.dtype != t.dtype:
+                        dst = torch.empty(max(t.numel(), 1), dtype=t.dtype, pin_memory=True)
+                        pinned[k] = dst
+                    dst[: t.numel()].copy_(t, non_blocking=True)
+                    out[k] = dst[: t.numel()]
+                else:
+                    out[k] = t.cpu()
+                self.d2h_bytes += t.numel() * t.element_size()
             torch.cuda.current_stream().synchronize()
         return {k: v.numpy() for k, v in out.items()}
-
-    def _download_into(self, res, pinned, out):
-        for k, t in res.out.items():
-            if pinned is not None:
-                dst = pinned.get(k)
-                if dst is None or dst.numel() < t.numel():
-                    dst = torch.empty(max(t.numel(), 1), dtype=t.dtype, pin_memory=True)
-                    pinned[k] = dst
-                dst[: t.numel()].copy_(t, non_blocking=True)
-                out[k] = dst[: t.numel()]
-            else:
-                out[k] = t.cpu()
-            self.d2h_bytes += t.numel() * t.element_size()
-
-
-class _Regrow(Exception):
-    pass
 
 
 class ShardStream:

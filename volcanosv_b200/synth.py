@@ -130,3 +130,65 @@ def synth_sig_table(seed: int, cand_pos, cand_len, per_cand: int = 10):
     cnt = rng.integers(1, 12, n).astype(np.int32)
     o = np.argsort(pos, kind="stable")
     return np.maximum(0, pos[o]).astype(np.int32), ln[o], cnt[o]
+
+
+def add_sa(b, rng, frac=0.08, self_chrom=0):
+    """8 % of the reads are split with SA tags.  Plausible SA tags for a share of the primary records: a second segment behind the primary one with a
+    reference gap (deletion), a query gap (insertion), a third segment, another chromosome, low mapq ..."""
+    n = len(b["pos"])
+    off, ops = b["op_off"], b["ops"]
+    codes, lens = ops & 15, (ops >> 4).astype(np.int64)
+    ref_adv = np.isin(codes, [0, 2, 3, 7, 8])
+    csum = np.concatenate([[0], np.cumsum(np.where(ref_adv, lens, 0))])
+    ref_end = b["pos"] + (csum[off[1:]] - csum[off[:-1]])
+    pick = np.flatnonzero((rng.random(n) < frac) & np.isin(b["flag"], [0, 16]))
+    cols = {k: [] for k in ("chrom", "pos", "strand", "first_s", "last_s", "bias", "mapq")}
+    sa_off = [0]
+    for r in pick:
+        a, e = int(off[r]), int(off[r + 1])
+        l = int(ops[e - 1])
+        right = (l >> 4) if (l & 15) in (4, 5) else 0
+        qlen = int(b["qlen"][r])
+        q_end = qlen - right
+        st = 1 if b["flag"][r] == 16 else 0
+        k = int(rng.integers(1, 4)) if rng.random() < 0.9 else int(rng.integers(7, 10))
+        p = int(ref_end[r])
+        for j in range(k):
+            kind = rng.random()
+            gap_ref = int(rng.integers(30, 4000)) if kind < 0.45 else int(rng.integers(-20, 60))
+            gap_q = int(rng.integers(30, 3000)) if 0.45 <= kind < 0.8 else int(rng.integers(0, 80))
+            bias = int(rng.integers(500, 5000))
+            fs = min(max(q_end + gap_q, 0), max(qlen - 1, 0))
+            cols["chrom"].append(self_chrom if rng.random() < 0.9 else self_chrom + 1)
+            cols["pos"].append(max(1, p + gap_ref + 1))
+            cols["strand"].append(st if rng.random() < 0.9 else 1 - st)
+            if st == 0:
+                cols["first_s"].append(fs); cols["last_s"].append(max(0, qlen - fs - bias))
+            else:   # '-' entries swap the roles of the clips (SE:356-357)
+                cols["last_s"].append(fs); cols["first_s"].append(max(0, qlen - fs - bias))
+            cols["bias"].append(bias)
+            cols["mapq"].append(int(rng.choice([60, 60, 60, 30, 10, 0])))
+            p += gap_ref + bias
+            q_end = fs + bias
+        sa_off.append(len(cols["pos"]))
+    b["sa_rec"] = pick.astype(np.int32)
+    b["sa_off"] = np.asarray(sa_off, np.int64)
+    for k, v in cols.items():
+        b["sa_" + k] = np.asarray(v, np.uint8 if k in ("strand", "mapq") else np.int32)
+    b["sa_self_chrom"] = self_chrom
+    return b
+
+
+def add_duplicates(b, rng, n_dup=40):
+    """Copies of records under the same read name right behind the original: every `.sigs` row of the copy is
+    a `sort -u` duplicate (DEL) or a potential one (INS)."""
+    n = len(b["pos"])
+    src = np.sort(rng.choice(n, n_dup, replace=False))
+    order = np.sort(np.concatenate([np.arange(n), src]), kind="stable")
+    nops = np.diff(b["op_off"])
+    out = {k: (v[order] if isinstance(v, np.ndarray) and len(v) == n else v) for k, v in b.items() if k not in ("ops", "op_off")}
+    new_nops = nops[order]
+    out["op_off"] = np.concatenate([[0], np.cumsum(new_nops)]).astype(np.int64)
+    idx = np.concatenate([np.arange(b["op_off"][r], b["op_off"][r + 1]) for r in order]) if len(order) else np.zeros(0, np.int64)
+    out["ops"] = np.ascontiguousarray(b["ops"][idx])
+    return out
