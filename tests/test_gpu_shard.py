@@ -86,7 +86,8 @@ def test_resident_step_matches_oracle(profile, dtype, n):
     assert res.counts["overflow"] == 0
     check_tables(sh.fetch, res.counts, exp)
     check_cands(got, exp)
-    assert exp["n_sa_rows"] > 0 and exp["n_del_dup"] > 0 and exp["n_ins_maybe_dup"] > 0 and len(exp["sig_reads_split"]) > 0
+    assert exp["n_sa_rows"] > 0 and exp["n_del_dup"] > 0 and exp["n_ins_maybe_dup"] > 0
+    assert profile != "hifi" or len(exp["sig_reads_split"]) > 0
     assert (exp["n_support"] > 0).sum() > 50 and (exp["depth2"] > 0).sum() > 100 and (exp["fp_support"] > 0).sum() > 50
     # idempotent: a second run on the same resident inputs gives the same results
     res2 = sh.run_safe()

@@ -4,8 +4,9 @@
 
 e.g. `python -m volcanosv_b200.cli extract_reads_signature.py -i reads.bam -o out -chr 10`
 replaces `python3 LI/extract_reads_signature.py -i reads.bam -o out -chr 10` (RVC:83-88).
-`volcanosv-vc-large-indel.py` takes the reference's flags plus `-cbam` (the sorted contig
-alignments: minimap2/samtools stay outside, RVC:49-58).
+`volcanosv-vc-large-indel.py` takes exactly the reference's flags (MAIN:10-36); `-cbam` is an optional
+extension that hands over contig alignments made elsewhere instead of running RVC:49-58's command.
+The executables under bin/VolcanoSV-vc/Large_INDEL/ carry the reference's script names and forward here.
 """
 from __future__ import annotations
 
@@ -145,19 +146,38 @@ def _main(argv):
     p.add_argument("--n_thread_align", "-ta", type=int, default=10)
     p.add_argument("--mem_per_thread", "-mempt", default="768M")
     p.add_argument("--prefix", "-px", default="Sample")
-    p.add_argument("--contig_bam", "-cbam", required=True,
-                   help="sorted contig-to-reference alignments (RVC:49-58 output); whole-genome mode: a pattern with {chr}")
+    p.add_argument("--contig_bam", "-cbam", default=None,
+                   help="OPTIONAL extension: sorted contig-to-reference alignments made elsewhere (whole-genome mode: a pattern with "
+                        "{chr}).  Without it the contigs are aligned exactly as Raw_variant_call.py:49-58 does (minimap2 | samtools sort)")
     a = p.parse_args(argv)
     if a.chr_num is None:                      # whole-genome mode (MAIN:266-279); one process per GPU under torchrun
         rank, world, barrier = _ranks()
         out = OP.large_indel_wgs(a.contig_bam, a.input_dir, a.reference, a.bam_file, a.output_dir, a.data_type, a.prefix,
-                                 a.read_signature_dir, a.pre_cutesig, rank=rank, world=world, barrier=barrier)
+                                 a.read_signature_dir, a.pre_cutesig, rank=rank, world=world, barrier=barrier,
+                                 n_thread_align=a.n_thread_align)
         if out:
             print(out)
         return
     contigs = "%s/chr%d/assembly/final_contigs/%s_final_contigs.fa" % (a.input_dir, a.chr_num, a.prefix)
     print(OP.large_indel_chr(a.contig_bam, contigs, a.reference, a.bam_file, a.output_dir, a.data_type, a.chr_num, a.prefix,
-                             a.read_signature_dir, a.pre_cutesig))
+                             a.read_signature_dir, a.pre_cutesig, n_thread_align=a.n_thread_align))
+
+
+def _rvc(argv):
+    p = argparse.ArgumentParser(prog="Raw_variant_call.py")
+    p.add_argument("--contig_path", "-contig")
+    p.add_argument("--reference_path", "-ref")
+    p.add_argument("--signature_dir", "-sigd")
+    p.add_argument("--rbam_file", "-rbam")
+    p.add_argument("--output_dir", "-o")
+    p.add_argument("--data_type", "-dtype")
+    p.add_argument("--chr_num", "-chr", type=int)
+    p.add_argument("--header_file", "-header", default=None)
+    p.add_argument("--n_thread", "-t", type=int, default=10)
+    p.add_argument("--mem_per_thread", "-mempt", default="1G")
+    a, _ = p.parse_known_args(argv)
+    print(OP.raw_variant_call(None, a.contig_path, a.reference_path, a.output_dir, a.data_type, a.chr_num, a.rbam_file,
+                              a.signature_dir, a.header_file, n_thread=a.n_thread, mem_per_thread=a.mem_per_thread))
 
 
 def _rvc_otherasm(argv):
@@ -204,12 +224,16 @@ def _main_otherasm(argv):
     p.add_argument("--pre_cutesig", "-presig")
     p.add_argument("--n_thread", "-t", type=int, default=11)
     p.add_argument("--prefix", "-px", default="Sample")
-    p.add_argument("--contig_bam", "-cbam", required=True,
-                   help="sorted whole-genome contig alignments (otherasm:232-245 output: minimap2 -x asm20 | samtools sort)")
+    p.add_argument("--n_thread_align", "-ta", type=int, default=10)
+    p.add_argument("--mem_per_thread", "-mempt", default="768M")
+    p.add_argument("--contig_bam", "-cbam", default=None,
+                   help="OPTIONAL extension: sorted whole-genome contig alignments made elsewhere; without it otherasm:232-245's "
+                        "command runs (minimap2 -x asm20 | samtools sort)")
     a, _ = p.parse_known_args(argv)
     rank, world, barrier = _ranks()
     out = OP.large_indel_otherasm(a.input_path, a.contig_bam, a.reference, a.bam_file, a.output_dir, a.data_type, a.prefix,
-                                  a.read_signature_dir, a.pre_cutesig, rank=rank, world=world, barrier=barrier)
+                                  a.read_signature_dir, a.pre_cutesig, rank=rank, world=world, barrier=barrier,
+                                  n_thread=a.n_thread, mem_per_thread=a.mem_per_thread)
     if out:
         print(out)
 
@@ -226,12 +250,16 @@ def _main_otherasm_2hap(argv):
     p.add_argument("--pre_cutesig", "-presig")
     p.add_argument("--n_thread", "-t", type=int, default=11)
     p.add_argument("--prefix", "-px", default="Sample")
-    p.add_argument("--contig_bam", "-cbam", required=True,
-                   help="sorted merge of both haplotypes' contig alignments (2hap:250-258 output)")
+    p.add_argument("--n_thread_align", "-ta", type=int, default=10)
+    p.add_argument("--mem_per_thread", "-mempt", default="768M")
+    p.add_argument("--contig_bam", "-cbam", default=None,
+                   help="OPTIONAL extension: sorted merge of both haplotypes' contig alignments made elsewhere; without it 2hap:250-258's "
+                        "commands run")
     a, _ = p.parse_known_args(argv)
     rank, world, barrier = _ranks()
     out = OP.large_indel_otherasm_2hap(a.hp1_fa, a.hp2_fa, a.contig_bam, a.reference, a.bam_file, a.output_dir, a.data_type,
-                                       a.prefix, a.read_signature_dir, a.pre_cutesig, rank=rank, world=world, barrier=barrier)
+                                       a.prefix, a.read_signature_dir, a.pre_cutesig, rank=rank, world=world, barrier=barrier,
+                                       n_thread=a.n_thread, mem_per_thread=a.mem_per_thread)
     if out:
         print(out)
 
@@ -243,6 +271,7 @@ COMMANDS = {
     "extract_contig_signature_Hifi.py": _ecs("Hifi"), "extract_contig_signature_ONT.py": _ecs("ONT"),
     "extract_contig_signature_CLR.py": _ecs("CLR"), "filter_GT_correction.py": _fgc,
     "volcanosv-vc-large-indel.py": _main,
+    "Raw_variant_call.py": _rvc,
     "Raw_variant_call-otherasm.py": _rvc_otherasm,
     "volcanosv-vc-large-indel-otherasm.py": _main_otherasm,
     "volcanosv-vc-large-indel-otherasm-2hap.py": _main_otherasm_2hap,

@@ -74,6 +74,7 @@ class Records:
         self.sa: List[Optional[str]] = []
         self.first_op: List[int] = []
         self.last_op: List[int] = []
+        self.name_key = None          # optional fixed-width byte-string array of the names (vectorised interning)
 
     def add(self, qname, flag, pos, mapq, cigar, seq, sa):
         packed = [(ln << 4) | op for op, ln in cigar]
@@ -102,6 +103,35 @@ class Records:
         return self
 
 
+class _LazyNames:
+    """`R.qname` for BAM input: names decoded on demand from the concatenated name bytes."""
+
+    def __init__(self, buf: bytes, off):
+        self.buf, self.off = buf, off
+
+    def __len__(self):
+        return len(self.off) - 1
+
+    def __getitem__(self, i):
+        return self.buf[self.off[i]: self.off[i + 1]].decode()
+
+    def __iter__(self):
+        return (self[i] for i in range(len(self)))
+
+
+def _name_key(names: np.ndarray, off: np.ndarray) -> np.ndarray:
+    """Fixed-width byte-string array of the read names (vectorised interning key: np.unique on it)."""
+    n = len(off) - 1
+    lens = (off[1:] - off[:-1]).astype(np.int64)
+    width = int(lens.max()) if n else 1
+    pad = np.zeros((n, max(width, 1)), np.uint8)
+    if len(names):
+        row = np.repeat(np.arange(n, dtype=np.int64), lens)
+        col = np.arange(len(names), dtype=np.int64) - np.repeat(off[:-1].astype(np.int64), lens)
+        pad[row, col] = names
+    return pad.view("S%d" % max(width, 1)).reshape(n)
+
+
 class _LazySeq:
     """`R.seq[i]` for BAM input: decoded from the record on demand (None for SEQ '*')."""
 
@@ -125,15 +155,33 @@ class AlignmentSource:
         self.path = path
         self._refs: List[tuple] = []
         self._by_chrom: Dict[str, Records] = {}
-        if path.endswith((".sam", ".sam.gz")):
+        kind = self._sniff(path)
+        if kind == "sam":
             self._load_sam(path)
-        elif path.endswith(".bam"):
+        elif kind == "bam":
             self._load_bam(path)
         else:
             self._load_pysam(path)
 
+    @staticmethod
+    def _sniff(path):
+        """The container format from the first bytes, not the file name (a `samtools sort` stand-in may leave SAM text
+        in a `.bam`): BGZF whose first block starts with BAM\1 -> bam; gzip or plain text starting with '@' / a
+        record line -> sam; anything else (CRAM) -> pysam."""
+        with open(path, "rb") as f:
+            head = f.read(4)
+        if head[:2] == b"\x1f\x8b":
+            with gzip.open(path, "rb") as g:
+                inner = g.read(4)
+            return "bam" if inner == b"BAM\x01" else "sam"
+        if head[:4] == b"CRAM":
+            return "cram"
+        return "sam"
+
     def _load_sam(self, path):
-        op = gzip.open if path.endswith(".gz") else open
+        with open(path, "rb") as f:
+            zipped = f.read(2) == b"\x1f\x8b"
+        op = gzip.open if zipped else open
         recs: Dict[str, Records] = {}
         with op(path, "rt") as fh:
             for line in fh:
@@ -180,10 +228,12 @@ class AlignmentSource:
         last = max(len(R.ops) - 1, 0)
         R.first_op = np.where(has, R.ops[np.minimum(d["op_off"][:-1], last)] if len(R.ops) else 0, 0).astype(np.uint32)
         R.last_op = np.where(has, R.ops[np.maximum(d["op_off"][1:] - 1, 0)] if len(R.ops) else 0, 0).astype(np.uint32)
-        names, no = bytes(d["names"]), d["name_off"]
-        R.qname = [names[no[i]: no[i + 1]].decode() for i in range(n_rec)]
+        R.qname = _LazyNames(bytes(d["names"]), d["name_off"])
+        R.name_key = _name_key(d["names"], d["name_off"])
         sa, so = bytes(d["sa"]), d["sa_off"]
-        R.sa = [sa[so[i]: so[i + 1]].decode() if so[i + 1] > so[i] else None for i in range(n_rec)]
+        R.sa = [None] * n_rec
+        for i in np.flatnonzero(so[1:] > so[:-1]):
+            R.sa[i] = sa[so[i]: so[i + 1]].decode()
         R.seq = _LazySeq(bf, tid, R.qlen)
         return R
 
@@ -243,53 +293,74 @@ def _stable_by_pos(ctx, sigs):
 
 
 # --------------------------------------------------------------------------- ERS
+def _chrom_len(src, chrom):
+    return dict(src.references()).get(chrom, 0)
+
+
+def _read_shard(input_path: str, chrom: str):
+    """The resident shard of one chromosome of a read alignment file (packed, uploaded and scanned once per process)."""
+    from . import resident as RS
+    src = open_alignments(input_path)
+    return RS.get(context(), src, input_path, chrom, _chrom_len(src, chrom))
+
+
+def _np_stable_by_pos(sigs):
+    return sigs[np.argsort(sigs["pos"], kind="stable")] if len(sigs) else sigs
+
+
 def extract_reads_signature(input_path: str, output_dir: str, chr_number: int, min_siglen: int = 30):
     """LI/extract_reads_signature.py -i <bam> -o <dir> -chr N: writes
-    <dir>/reads_signature/chrN_{DEL_reads_cigar,INS_reads_ciga,DEL_reads_split,INS_reads_split,reads_sig}.txt"""
+    <dir>/reads_signature/chrN_{DEL_reads_cigar,INS_reads_ciga,DEL_reads_split,INS_reads_split,reads_sig}.txt
+    from the resident shard's read-signature table (one scan serves ERS, SE, CSS, GTD and GTI)."""
+    from . import resident as RS
     ctx = context()
+    if min_siglen != ctx.get_params().reads_min_len:
+        p = ctx.get_params()
+        p.reads_min_len = min_siglen
+        ctx.set_params(p)
+        RS.clear()
     chrom = "chr%d" % chr_number
     out = os.path.join(output_dir, "reads_signature")
     os.makedirs(out, exist_ok=True)
-    R = open_alignments(input_path).records(chrom)
-    strand = ["-" if x else "+" for x in R.is_rev]
-    # CIGAR signatures (ERS:47-83,107-145): mapq >= 50, >= 30 bp, no per-read merge
-    sigs, rt, qt, xt = ctx.scan_cigar(L.MODE_READS, R.ops, R.op_off, R.pos, R.mapq, min_len=30, min_mapq=50)
-    dels = _stable_by_pos(ctx, sigs[sigs["type"] == L.DEL])
-    inss = _stable_by_pos(ctx, sigs[sigs["type"] == L.INS])
+    sh = _read_shard(input_path, chrom)
+    R = sh.R
+    counts = sh.scan(None if sh.bed == "unset" else (list(sh.bed) if sh.bed is not None else None))
+    reads = sh.fetch(L.TAB_READS)
+    nc = counts["n_reads_cigar"]
+    sigs, sp = reads[:nc], reads[nc:]
+    strand = np.where(R.is_rev != 0, "-", "+") if R.n else np.zeros(0, "U1")
+    # CIGAR signatures (ERS:47-83,107-145): mapq >= 50, >= 30 bp, no per-read merge; (record, op) order, then sort_sig
+    dels = _np_stable_by_pos(sigs[sigs["type"] == L.DEL])
+    inss = _np_stable_by_pos(sigs[sigs["type"] == L.INS])
 
     def cig_rows(a, tp):
-        return [[chrom, tp, int(s["pos"]), int(s["len"]), R.qname[s["rec"]], int(s["q0"]), strand[s["rec"]], "cigar"] for s in a]
+        return [[chrom, tp, int(p_), int(l_), R.qname[r_], int(q_), strand[r_], "cigar"]
+                for p_, l_, r_, q_ in zip(a["pos"], a["len"], a["rec"], a["q0"])]
     del_c, ins_c = cig_rows(dels, "DEL"), cig_rows(inss, "INS")
     fmt = lambda rows: ["\t".join(str(x) for x in r) + "\n" for r in rows]
     _write_lines("%s/%s_DEL_reads_cigar.txt" % (out, chrom), fmt(del_c))
     _write_lines("%s/%s_INS_reads_ciga.txt" % (out, chrom), fmt(ins_c))     # file name typo is the reference's
-    # split-alignment signatures (ERS:147-248): every name seen more than once, no mapq filter
-    cnt = Counter(R.qname)
-    first_seen: Dict[str, int] = {}
-    for nm in R.qname:
-        if nm not in first_seen:
-            first_seen[nm] = len(first_seen)
-    name_id = np.asarray([first_seen[nm] for nm in R.qname], dtype=np.int32)
-    select = np.asarray([1 if cnt[nm] > 1 else 0 for nm in R.qname], dtype=np.uint8)
-    ref_end = (R.pos + rt).astype(np.int32)
-    readlen = (qt + xt).astype(np.int32)                                     # ops {M,=,X,I,S} + H (ERS:151)
-    sp = ctx.split_pairs(L.SPLIT_READS, 0, R.pos, ref_end, readlen, R.first_op, R.last_op, R.mapq, R.is_rev, name_id,
-                         select) if R.n >= 2 else np.zeros(0, L.SIG_DTYPE)
-    sdel = _stable_by_pos(ctx, sp[sp["type"] == L.DEL])
-    sins = _stable_by_pos(ctx, sp[sp["type"] == L.INS])
+    # split-alignment signatures (ERS:147-248): names in first-appearance order, consecutive records of a name (the engine
+    # appends them unordered: restore the reference's order), then sort_sig
+    if len(sp):
+        sp = sp[np.lexsort((sp["rec"], sh.name_first[sh.name_id[sp["rec"]]]))]
+    sdel = _np_stable_by_pos(sp[sp["type"] == L.DEL])
+    sins = _np_stable_by_pos(sp[sp["type"] == L.INS])
 
     def split_rows(a, tp, label):
-        return [[chrom, tp, int(s["pos"]), int(s["len"]), R.qname[s["rec"]], int(s["q0"]), int(s["q1"]), strand[s["rec"]],
-                 label] for s in a]
+        return [[chrom, tp, int(p_), int(l_), R.qname[r_], int(q0), int(q1), strand[r_], label]
+                for p_, l_, r_, q0, q1 in zip(a["pos"], a["len"], a["rec"], a["q0"], a["q1"])]
     del_s = split_rows(sdel, "DEL", "split-alignemnt")                       # typos are the reference's (ERS:192,195)
     ins_s = split_rows(sins, "INS", "split_alignment")
     _write_lines("%s/%s_DEL_reads_split.txt" % (out, chrom), fmt(del_s))
     _write_lines("%s/%s_INS_reads_split.txt" % (out, chrom), fmt(ins_s))
     allrows = del_c + ins_c + del_s + ins_s                                  # ERS:279-282, then sort_sig
     if allrows:
-        order = ctx.argsort_stable(np.asarray([r[2] for r in allrows], dtype=np.int32))
+        order = np.argsort(np.asarray([r[2] for r in allrows], dtype=np.int64), kind="stable")
         allrows = [allrows[i] for i in order]
-    _write_lines("%s/%s_reads_sig.txt" % (out, chrom), fmt(allrows))
+    sig_file = "%s/%s_reads_sig.txt" % (out, chrom)
+    _write_lines(sig_file, fmt(allrows))
+    RS.register_file(sig_file, chrom, sh)
     return allrows
 
 
@@ -304,6 +375,7 @@ def _read_vcf(path):
 
 def fp_filter(input_path: str, signature_dir: str, output_path: str):
     """LI/FP_filter_v1.py -i <raw.vcf> -sigd <reads_signature dir> -o <filtered.vcf> (FPF:87-202)."""
+    from . import resident as RS
     ctx = context()
     header, body = _read_vcf(input_path)
     by_chr: Dict[str, List[str]] = {}
@@ -317,133 +389,97 @@ def fp_filter(input_path: str, signature_dir: str, output_path: str):
         lines = by_chr[chrom]
         cpos = np.asarray([int(x.split()[1]) for x in lines], dtype=np.int32)
         clen = np.asarray([abs(len(x.split()[4]) - len(x.split()[3])) for x in lines], dtype=np.int32)
-        spos, slen = [], []
-        with open("%s/%s_reads_sig.txt" % (signature_dir, chrom)) as f:
-            for line in f:
-                d = line.split()
-                spos.append(int(d[2]))
-                slen.append(int(d[3]))
-        sup = ctx.fp_support(cpos, clen, np.asarray(spos, dtype=np.int32), np.asarray(slen, dtype=np.int32))
+        sig_file = "%s/%s_reads_sig.txt" % (signature_dir, chrom)
+        owner = RS.owner_of(sig_file)
+        if owner is not None and chrom in owner:          # written from a resident shard in this process: join on the device table
+            sup = owner[chrom].candidates(L.JOIN_FP, cpos, clen, np.zeros(len(cpos), np.int32))["fp_support"]
+        else:                                             # a pre-extracted signature directory (-rdsig): columns 3-4 of the file
+            spos, slen = [], []
+            with open(sig_file) as f:
+                for line in f:
+                    d = line.split()
+                    spos.append(int(d[2]))
+                    slen.append(int(d[3]))
+            sup = ctx.fp_support(cpos, clen, np.asarray(spos, dtype=np.int32), np.asarray(slen, dtype=np.int32))
         out += [ln for ln, s in zip(lines, sup) if s > 0]
     _write_lines(output_path, out)
 
 
 # --------------------------------------------------------------------------- SE
-def _parse_sa(entry):
-    """acquire_clip_pos + the SA fields organize_split_signal uses (SE:328-358)."""
-    chrom, pos, strand, cg, mq, _nm = entry.split(",")
-    items = [(int(n), ch) for n, ch in _CIG.findall(cg)]
-    fs = items[0][0] if items[0][1] == "S" else 0
-    ls = items[-1][0] if items[-1][1] == "S" else 0
-    bias = sum(n for n, ch in items if ch in "MD=X")
-    return chrom, int(pos), 0 if strand == "+" else 1, fs, ls, bias, int(mq)
+def _sigs_chrom(sh, chrom, clen, batches, min_mapq, bed_regions):
+    """The `.sigs` / `.reads` lines of ONE chromosome from its resident shard (SE:514-572): (DEL line set, INS line set,
+    {`_chrom_lo_hi.reads` file name: lines})."""
+    R = sh.R
+    # batches own the records that START inside them (SE:522,535); the regions of the BED file are attached to the
+    # tasks they overlap and a record is tested against its own task's regions only (SE:58-80) - both on the device
+    sh.scan(bed_regions)
+    in_bed = sh.fetch(L.TAB_IN_BED).astype(bool)
+    ref_end = sh.fetch(L.TAB_REF_END)
+    batch_of = (R.pos // batches) if clen >= batches else np.zeros(R.n, np.int64)
+    has_rows = np.zeros(int(batch_of.max()) + 1 if R.n else 1, bool)
+    d_rows, i_rows = sh.fetch(L.TAB_DEL_ROWS), sh.fetch(L.TAB_INS_ROWS)
+    pieces = sh._ins_piece_index() if len(i_rows) else None
+    del_lines, ins_lines = set(), set()
+    for m in i_rows:                                                                     # INS rows: SE:394-415 / SE:220-232
+        r = int(m["rec"])
+        ins_lines.add("INS\t%s\t%d\t%d\t%s\t%s\n" % (chrom, int(m["pos"]), int(m["len"]), R.qname[r], sh.ins_sequence(m, pieces)))
+    for pos_, len_, r in zip(d_rows["pos"], d_rows["len"], d_rows["rec"]):
+        del_lines.add("DEL\t%s\t%d\t%d\t%s\n" % (chrom, int(pos_), int(len_), R.qname[r]))
+    has_rows[batch_of[d_rows["rec"]]] = True
+    has_rows[batch_of[i_rows["rec"]]] = True
+    # reads.sigs: per batch (file-name order of `cat signatures/*.reads`), records with mapq >= min (SE:536-541); a
+    # batch without a candidate row writes no files (SE:548-550)
+    keep = has_rows[batch_of] & in_bed & (R.mapq >= min_mapq)
+    prim = np.isin(R.flag, (0, 16)).astype(np.int64)
+    names = {}
+    for bt in np.unique(batch_of[keep]):
+        lo = int(bt) * batches if clen >= batches else 0
+        hi = min(clen, lo + batches) if clen >= batches else clen
+        idx = np.flatnonzero(keep & (batch_of == bt))
+        names["_%s_%d_%d.reads" % (chrom, lo, hi)] = ["%s\t%d\t%d\t%d\t%s\n" % (chrom, int(R.pos[r]), int(ref_end[r]), int(prim[r]), R.qname[r])
+                                                     for r in idx]
+    return del_lines, ins_lines, names
+
+
+_sigs_key = lambda ln: (ln.split("\t")[1], int(ln.split("\t")[2]), ln)          # sort -k2,2 -k3,3n, C locale (SE:637-638)
 
 
 def sig_extract(input_path: str, reference: str, work_dir: str, include_bed: Optional[str] = None, batches: int = 10_000_000,
                 min_mapq: int = 20, min_read_len: int = 500, min_siglength: int = 10, min_size: int = 30,
                 max_size: int = 100000, max_split_parts: int = 7):
     """LI/sig_extract.py <bam> <ref> <work_dir> [-include_bed bed]: writes DEL.sigs, INS.sigs,
-    reads.sigs (SE:514-644).  merge thresholds are the script defaults (DEL 0, INS 100)."""
+    reads.sigs (SE:514-644).  merge thresholds are the script defaults (DEL 0, INS 100).  The rows come from the
+    resident shard of each chromosome (CIGAR scan + in-read merge + SA analysis on the device); the sequence column
+    of the INS rows is cut from the reads here."""
+    from . import resident as RS
     ctx = context()
     if not os.path.isfile(reference):
         raise FileNotFoundError("[Errno 2] No such file: '%s'" % reference)
     os.makedirs(os.path.join(work_dir, "signatures"), exist_ok=True)
+    p = ctx.get_params()
+    want = (min_siglength, min_mapq, min_read_len, min_size, max_size, max_split_parts, batches)
+    if want != (p.cute_min_len, p.cute_min_mapq, p.cute_min_read_len, p.sa_sv_size, p.sa_max_size, p.sa_max_parts, p.batch_size):
+        (p.cute_min_len, p.cute_min_mapq, p.cute_min_read_len, p.sa_sv_size, p.sa_max_size, p.sa_max_parts, p.batch_size) = want
+        ctx.set_params(p)
+        RS.clear()
     src = open_alignments(input_path)
     bed: Optional[Dict[str, list]] = None
     if include_bed is not None:
         bed = {}
         with open(include_bed) as f:
             for line in f:
-                s = line.strip().split("\t")
-                bed.setdefault(s[0], []).append((int(s[1]) - 1000, int(s[2]) + 1000))          # SE:69
+                x = line.strip().split("\t")
+                bed.setdefault(x[0], []).append((int(x[1]) - 1000, int(x[2]) + 1000))          # SE:69
     del_lines, ins_lines, read_lines = set(), set(), []
-    chrom_ids: Dict[str, int] = {}
+    owners = {}
     for chrom, clen in src.references():
-        R = src.records(chrom)
-        if R.n == 0:
+        sh = RS.get(ctx, src, input_path, chrom, clen)
+        if sh.R.n == 0:
             continue
-        # batches own the records that START inside them (SE:522,535); a batch with no candidate
-        # writes no files (SE:548-550), which only matters for reads.sigs
-        edges = list(range(0, clen, batches)) if clen >= batches else [0]
-        rt0 = None
-        enable = (R.qlen >= min_read_len).astype(np.uint8)                                    # SE:439
-        sigs, rt, qt, xt = ctx.scan_cigar(L.MODE_CUTE, R.ops, R.op_off, R.pos, R.mapq, enable=enable, min_len=min_siglength,
-                                          min_mapq=min_mapq)
-        ref_end = R.pos + rt + xt                                                            # CUTE totals: aux = N
-        in_bed = np.ones(R.n, dtype=bool)
-        if bed is not None:
-            in_bed[:] = False
-            for (b0, b1) in bed.get(chrom, []):
-                in_bed |= ~((ref_end <= b0) | (R.pos >= b1))                                   # SE:528-533
-        d, s = ctx.merge_in_record(L.MODE_CUTE, sigs)
-        rows_by_batch: Dict[int, int] = {}
-        inss = sigs[sigs["type"] == L.INS]
-        for m in s:                                                                          # INS rows: SE:394-415
-            r = int(m["rec"])
-            if not in_bed[r]:
-                continue
-            seq = R.seq[r]
-            piece = "".join(seq[int(inss[k]["q0"]):int(inss[k]["q1"])] for k in range(int(m["first"]), int(m["first"]) + int(m["count"])))
-            ins_lines.add("INS\t%s\t%d\t%d\t%s\t%s\n" % (chrom, int(m["pos"]), int(m["len"]), R.qname[r], piece))
-            rows_by_batch[int(R.pos[r]) // batches if clen >= batches else 0] = 1
-        for m in d:
-            r = int(m["rec"])
-            if not in_bed[r]:
-                continue
-            del_lines.add("DEL\t%s\t%d\t%d\t%s\n" % (chrom, int(m["pos"]), int(m["len"]), R.qname[r]))
-            rows_by_batch[int(R.pos[r]) // batches if clen >= batches else 0] = 1
-        # SA-tag split analysis (SE:495-511,345-371): primary records (flag 0 / 16) carrying an SA tag
-        seg_off, cols, rlen, owners = [0], [[] for _ in range(6)], [], []
-        for r in range(R.n):
-            if R.sa[r] is None or int(R.flag[r]) not in (0, 16) or not enable[r] or not in_bed[r]:
-                continue
-            segs = []
-            mq_min = min_mapq
-            qlen = int(R.qlen[r])
-            if int(R.mapq[r]) >= min_mapq:
-                f, l = int(R.first_op[r]), int(R.last_op[r])
-                left = (f >> 4) if (f & 15) in (4, 5) else 0
-                right = (l >> 4) if (l & 15) in (4, 5) else 0
-                if int(R.flag[r]) == 0:
-                    segs.append((left, qlen - right, int(R.pos[r]), int(ref_end[r]), chrom, 0))
-                else:
-                    segs.append((right, qlen - left, int(R.pos[r]), int(ref_end[r]), chrom, 1))
-                mq_min = 0                                                                  # SE:348-350
-            for e in R.sa[r].split(";")[:-1]:
-                c, p, st, fs, ls, bias, mq = _parse_sa(e)
-                if mq >= mq_min:
-                    segs.append((fs, qlen - ls, p, p + bias, c, 0) if st == 0 else (ls, qlen - fs, p, p + bias, c, 1))
-            for sg in segs:
-                for k in range(4):
-                    cols[k].append(sg[k])
-                cols[4].append(chrom_ids.setdefault(sg[4], len(chrom_ids)))
-                cols[5].append(sg[5])
-            seg_off.append(seg_off[-1] + len(segs))
-            rlen.append(qlen)
-            owners.append(r)
-        if owners:
-            sa_rows = ctx.sa_analysis(seg_off, *cols, rlen, sv_size=min_size, max_size=max_size, max_parts=max_split_parts)
-            for x in sa_rows:
-                r = owners[int(x["rec"])]
-                if int(x["type"]) == L.INS:
-                    q = R.seq[r][::-1] if int(x["first"]) else R.seq[r]
-                    ins_lines.add("INS\t%s\t%d\t%d\t%s\t%s\n" % (chrom, int(x["pos"]), int(x["len"]), R.qname[r],
-                                                                q[int(x["q0"]):int(x["q1"])]))
-                else:
-                    del_lines.add("DEL\t%s\t%d\t%d\t%s\n" % (chrom, int(x["pos"]), int(x["len"]), R.qname[r]))
-                rows_by_batch[int(R.pos[r]) // batches if clen >= batches else 0] = 1
-        # reads.sigs: per batch (file-name order of `cat signatures/*.reads`), records with mapq >= min (SE:536-541)
-        per_batch: Dict[int, List[str]] = {}
-        for r in range(R.n):
-            b = int(R.pos[r]) // batches if clen >= batches else 0
-            if b in rows_by_batch and in_bed[r] and int(R.mapq[r]) >= min_mapq:
-                per_batch.setdefault(b, []).append("%s\t%d\t%d\t%d\t%s\n" % (chrom, int(R.pos[r]), int(ref_end[r]),
-                                                                            1 if int(R.flag[r]) in (0, 16) else 0, R.qname[r]))
-        names = {}
-        for b in per_batch:
-            lo = b * batches if clen >= batches else 0
-            hi = min(clen, lo + batches) if clen >= batches else clen
-            names["_%s_%d_%d.reads" % (chrom, lo, hi)] = per_batch[b]
+        owners[chrom] = sh
+        d, i, names = _sigs_chrom(sh, chrom, clen, batches, min_mapq, None if bed is None else sorted(bed.get(chrom, [])))
+        del_lines |= d
+        ins_lines |= i
         for nm in sorted(names):
             read_lines.append((nm, names[nm]))
     key = lambda ln: (ln.split("\t")[1], int(ln.split("\t")[2]), ln)          # sort -k2,2 -k3,3n, C locale (SE:637-638)
@@ -453,6 +489,9 @@ def sig_extract(input_path: str, reference: str, work_dir: str, include_bed: Opt
     for nm, lines in sorted(read_lines, key=lambda x: x[0]):
         out += lines
     _write_lines(os.path.join(work_dir, "reads.sigs"), out)
+    for fn in ("DEL.sigs", "INS.sigs"):
+        for chrom, sh in owners.items():
+            RS.register_file(os.path.join(work_dir, fn), chrom, sh)
 
 
 # --------------------------------------------------------------------------- CSS + coverage filter
@@ -480,9 +519,44 @@ def _fl(x: float) -> str:
 def signature_support(vcffile: str, cutesv_dir: str, chr_num: Optional[int] = None, flanking: int = 1000, min_size: int = 30):
     """LI/calculate_signature_support.py -v <vcf> -ct <cute_sig dir> [-chr N]: writes
     <vcf-basename>_cutesv_sig_support_mins30_fl1000.csv (CSS:32-366)."""
+    from . import resident as RS
     ctx = context()
-    sig_ins = _load_sigs(os.path.join(cutesv_dir, "INS.sigs"))
-    sig_del = _load_sigs(os.path.join(cutesv_dir, "DEL.sigs"))
+    own_i, own_d = RS.owner_of(os.path.join(cutesv_dir, "INS.sigs")), RS.owner_of(os.path.join(cutesv_dir, "DEL.sigs"))
+    resident = own_i is not None and own_d is not None and (flanking, min_size) == (ctx.get_params().cov_flanking, 30)
+    # -presig (a pre-extracted cute_sig directory): the tables are read from the files; otherwise they are on the device already
+    sig_ins = {} if resident else _load_sigs(os.path.join(cutesv_dir, "INS.sigs"))
+    sig_del = {} if resident else _load_sigs(os.path.join(cutesv_dir, "DEL.sigs"))
+    calls = _css_calls(vcffile, min_size)
+    chroms = ["chr%d" % chr_num] if chr_num is not None else ["chr%d" % i for i in range(1, 23)]
+    rows, any_float = [], False
+    for chrom in chroms:
+        cl = calls["INS"].get(chrom)
+        if cl:
+            starts = np.asarray([c[0] for c in cl], dtype=np.int32)
+            if resident:
+                cov = own_i[chrom].candidates(L.JOIN_COV, starts, np.asarray([c[2] for c in cl], np.int32), np.full(len(cl), L.INS, np.int32))["cov"] \
+                    if chrom in own_i else np.zeros(len(cl), np.int64)
+            else:
+                sp, sl = sig_ins.get(chrom, (np.zeros(0, np.int32), np.zeros(0, np.int32)))
+                cov = ctx.ins_cov(starts, sp, sl, flanking)
+            any_float = True
+            rows += [list(c) + [float(v)] for c, v in zip(cl, cov)]
+    for chrom in chroms:
+        cl = calls["DEL"].get(chrom)
+        if cl and resident:
+            cov = own_d[chrom].candidates(L.JOIN_COV, np.asarray([c[0] for c in cl], np.int32), np.asarray([-c[2] for c in cl], np.int32),
+                                          np.full(len(cl), L.DEL, np.int32))["cov"] if chrom in own_d else np.zeros(len(cl), np.int64)
+            rows += [list(c) + [int(v)] for c, v in zip(cl, cov)]
+        elif cl:
+            sp, sl = sig_del.get(chrom, (np.zeros(0, np.int32), np.zeros(0, np.int32)))
+            cov = ctx.del_cov(np.asarray([c[0] for c in cl], dtype=np.int32), np.asarray([c[1] for c in cl], dtype=np.int32),
+                              sp, sl, flanking)
+            rows += [list(c) + [int(v)] for c, v in zip(cl, cov)]
+    return _css_write(vcffile, rows, any_float, min_size, flanking)
+
+
+def _css_calls(vcffile, min_size=30):
+    """load_vcf (CSS:32-53): {type: {chrom: [(start, end, svlen, id, gt, type)]}} in file order, |SVLEN| >= min_size."""
     calls = {"INS": {}, "DEL": {}}
     _, body = _read_vcf(vcffile)
     for line in body:
@@ -494,22 +568,11 @@ def signature_support(vcffile: str, cutesv_dir: str, chr_num: Optional[int] = No
                     start = int(d[1])
                     end = start + 1 if tp == "INS" else start - svlen
                     calls[tp].setdefault(d[0], []).append((start, end, svlen, d[2], d[-1].split(":")[0], tp))
-    chroms = ["chr%d" % chr_num] if chr_num is not None else ["chr%d" % i for i in range(1, 23)]
-    rows, any_float = [], False
-    for chrom in chroms:
-        cl = calls["INS"].get(chrom)
-        if cl:
-            sp, sl = sig_ins.get(chrom, (np.zeros(0, np.int32), np.zeros(0, np.int32)))
-            cov = ctx.ins_cov(np.asarray([c[0] for c in cl], dtype=np.int32), sp, sl, flanking)
-            any_float = True
-            rows += [list(c) + [float(v)] for c, v in zip(cl, cov)]
-    for chrom in chroms:
-        cl = calls["DEL"].get(chrom)
-        if cl:
-            sp, sl = sig_del.get(chrom, (np.zeros(0, np.int32), np.zeros(0, np.int32)))
-            cov = ctx.del_cov(np.asarray([c[0] for c in cl], dtype=np.int32), np.asarray([c[1] for c in cl], dtype=np.int32),
-                              sp, sl, flanking)
-            rows += [list(c) + [int(v)] for c, v in zip(cl, cov)]
+    return calls
+
+
+def _css_write(vcffile, rows, any_float, min_size=30, flanking=1000):
+    """The CSV of CSS:361-366: the INS coverages are floats, so the shared column prints DEL sums as floats too."""
     base = os.path.basename(vcffile).split(".")[0]
     csv = os.path.join(os.path.dirname(vcffile), "%s_cutesv_sig_support_mins%d_fl%d.csv" % (base, min_size, flanking))
     out = ["start,end,svlen,svid,gt,svtype,cov,rel_cov\n"]
@@ -562,21 +625,8 @@ def _chrom_id(name: str, table: Dict[str, int]) -> int:
     return table.setdefault(name, len(table))
 
 
-def correct_gt(input_path: str, output_path: str, bamfile: str, sigfile: str, dtype: str, vtype: str):
-    """LI/correct_gt_del_real_data.py / correct_gt_ins_real_data.py -i <vcf> -o <tsv> -bam <bam>
-    -sig <DEL.sigs|INS.sigs> -d <dtype> -v DEL|INS: writes <tsv>, <tsv>.newgt and <vcf>.newgt.<vtype>
-    (INS also <sigfile>.gte30auto)."""
-    ctx = context()
-    is_del = vtype == "DEL"
-    _, body = _read_vcf(input_path)
-    lines = [ln for ln in body if "SVTYPE=%s" % vtype in ln]
-    chrom = [ln.split()[0] for ln in lines]
-    pos = np.asarray([int(ln.split()[1]) for ln in lines], dtype=np.int32)
-    svid = [ln.split()[2] for ln in lines]
-    gt = [ln.split()[-1].split(":")[0] for ln in lines]
-    sv_signed = [int(ln.split("SVLEN=")[1].split(";")[0]) for ln in lines]
-    svlen = np.asarray([abs(x) for x in sv_signed] if is_del else sv_signed, dtype=np.int32)
-    # unique signatures in file order (GTD:65-86 / GTI:67-101: INS keeps len >= 30 on integer chrN)
+def _correct_gt_from_file(ctx, bamfile, sigfile, is_del, dtype, chrom, pos, svlen, gcode):
+    """-presig: the unique signatures come from a `.sigs` FILE (GTD:65-86 / GTI:67-101: INS keeps len >= 30 on integer chrN)."""
     ctab: Dict[str, int] = {}
     s_chrom, s_pos, s_len = [], [], []
     with open(sigfile) as f:
@@ -588,42 +638,125 @@ def correct_gt(input_path: str, output_path: str, bamfile: str, sigfile: str, dt
             s_chrom.append(_chrom_id(d[1], ctab))
             s_pos.append(int(d[2]))
             s_len.append(int(d[3]))
-    n_sig = len(s_pos)
-    if n_sig:
+    if s_pos:
         uc, up, ul, un = ctx.group_sigs(np.asarray(s_chrom, np.int32), np.asarray(s_pos, np.int32), np.asarray(s_len, np.int32))
     else:
         uc = up = ul = un = np.zeros(0, np.int32)
     inv = {v: k for k, v in ctab.items()}
     if not is_del:
-        _write_lines(sigfile + ".gte30auto", ["%d\t%d\t%d\t%d\n" % (int(inv[int(c)][3:]), p, l, n) for c, p, l, n in zip(uc, up, ul, un)])
+        _write_lines(sigfile + ".gte30auto", ["%d\t%d\t%d\t%d\n" % (int(inv[int(c)][3:]), p, l, k) for c, p, l, k in zip(uc, up, ul, un)])
     cc = np.asarray([_chrom_id(c, ctab) for c in chrom], dtype=np.int32)
-    n = len(lines)
-    if n:
-        if len(up):
-            sup, match_id, _ = ctx.sig_support(cc, pos, svlen, uc, up, ul, un, last_in=0)
-        else:
-            sup, match_id = np.zeros(n, np.int32), np.zeros(n, np.int32)
-        for i in range(n):                       # the reference's pysam.fetch raises on a negative start (GTI:190, GTD:160)
-            lo = pos[i] - 100 if not is_del else (pos[i] - 150 if svlen[i] > 1000 else pos[i])
-            if lo < 0:
-                raise L.VsvError(L.E_ARG, "candidate %s is closer than %d bp to the chromosome start: the reference's "
-                                          "fetch() fails here" % (svid[i], pos[i] - lo))
-        depth2 = np.zeros(n, np.int32)
-        ratio = np.zeros(n, np.float64)
-        newgt = np.zeros(n, np.int32)
-        src = open_alignments(bamfile)
-        gcode = np.asarray([0 if g == "0/1" else 1 if g == "1/1" else 2 for g in gt], dtype=np.int32)
-        thr_d, thr_i = GT_THRESHOLDS[dtype]["DEL"], GT_THRESHOLDS[dtype]["INS"]
-        for c in dict.fromkeys(chrom):            # depth per chromosome (reads of that chromosome, BAM order)
-            idx = np.asarray([i for i in range(n) if chrom[i] == c], dtype=np.int64)
-            R = src.records(c)
-            rend = _ref_end(ctx, R)
-            d2, rr, ng = ctx.genotype(R.pos, rend, pos[idx], svlen[idx], np.full(len(idx), L.DEL if is_del else L.INS, np.int32),
-                                      gcode[idx], sup[idx], thr_d, thr_i)
-            depth2[idx], ratio[idx], newgt[idx] = d2, rr, ng
+    n = len(pos)
+    if n == 0:
+        z = np.zeros(0, np.int32)
+        return z, z, z, np.zeros(0, np.float64), z
+    if len(up):
+        sup, match_id, _ = ctx.sig_support(cc, pos, svlen, uc, up, ul, un, last_in=0)
     else:
-        sup = match_id = depth2 = newgt = np.zeros(0, np.int32)
-        ratio = np.zeros(0, np.float64)
+        sup, match_id = np.zeros(n, np.int32), np.zeros(n, np.int32)
+    depth2, ratio, newgt = np.zeros(n, np.int32), np.zeros(n, np.float64), np.zeros(n, np.int32)
+    src = open_alignments(bamfile)
+    thr_d, thr_i = GT_THRESHOLDS[dtype]["DEL"], GT_THRESHOLDS[dtype]["INS"]
+    carr = np.asarray(chrom)
+    for c in dict.fromkeys(chrom):            # depth per chromosome (reads of that chromosome, BAM order)
+        idx = np.flatnonzero(carr == c)
+        R = src.records(c)
+        rend = _ref_end(ctx, R)
+        d2, rr, ng = ctx.genotype(R.pos, rend, pos[idx], svlen[idx], np.full(len(idx), L.DEL if is_del else L.INS, np.int32),
+                                  gcode[idx], sup[idx], thr_d, thr_i)
+        depth2[idx], ratio[idx], newgt[idx] = d2, rr, ng
+    return sup, match_id, depth2, ratio, newgt
+
+
+def _correct_gt_resident(owner, bamfile, sigfile, is_del, chrom, pos, svlen, gcode):
+    """The `.sigs` file was written from resident shards in this process: supporting signatures, spanning depth and the
+    genotype decision run against the device tables, one call per run of same-chromosome candidates.  The reference's
+    last_match_idx (GTD:94-133) indexes the GENOME-WIDE unique list (chromosomes in `.sigs` order = C-locale string order):
+    it is carried from call to call as a global index and handed to a shard only while it points into that shard's block."""
+    tb = 0 if is_del else 1
+    key = "n_udel" if is_del else "n_uins"
+    chroms = sorted(c for c, sh in owner.items() if sh.counts and sh.counts[key] > 0 and (is_del or c[3:].isdigit()))
+    block, off = {}, 0
+    for c in chroms:
+        block[c] = (off, owner[c].counts[key])
+        off += owner[c].counts[key]
+    if not is_del:
+        out = []
+        for c in chroms:
+            up, ul, un = owner[c].fetch(L.TAB_UINS)
+            out += ["%d\t%d\t%d\t%d\n" % (int(c[3:]), p_, l_, k_) for p_, l_, k_ in zip(up, ul, un)]
+        _write_lines(sigfile + ".gte30auto", out)
+    n = len(pos)
+    sup, match_id, depth2, newgt = (np.zeros(n, np.int32) for _ in range(4))
+    ratio = np.zeros(n, np.float64)
+    if n == 0:
+        return sup, match_id, depth2, ratio, newgt
+    typ = np.full(n, L.DEL if is_del else L.INS, np.int32)
+    src = open_alignments(bamfile)
+    global_last = 0
+    carr = np.asarray(chrom)
+    cut = np.flatnonzero(np.concatenate([[True], carr[1:] != carr[:-1]]))
+    for a, b in zip(cut, list(cut[1:]) + [n]):
+        c = chrom[a]
+        sh = owner.get(c)
+        if sh is None:                                     # a chromosome without a single read signature: still needs its reads
+            sh = _read_shard(bamfile, c)
+            sh.scan(None if sh.bed == "unset" else (list(sh.bed) if sh.bed is not None else None))
+        b0, nu = block.get(c, (0, 0))
+        li = global_last - b0 if (nu > 0 and b0 <= global_last < b0 + nu) else -1
+        last_in = (li, -1) if is_del else (-1, li)
+        o = sh.candidates(L.JOIN_SUPPORT | L.JOIN_GENOTYPE, pos[a:b], svlen[a:b], typ[a:b], gcode[a:b], last_in=last_in)
+        sup[a:b], depth2[a:b], ratio[a:b] = o["n_support"], o["depth2"], o["ratio"]
+        newgt[a:b] = o["new_gt"] if o["new_gt"] is not None else gcode[a:b]
+        mid = np.asarray(o["match_id"])
+        match_id[a:b] = np.where(mid >= 0, b0 + mid, global_last) if off > 0 else 0
+        lo = o["last_out"][tb]
+        if lo >= 0:
+            global_last = b0 + lo
+    return sup, match_id, depth2, ratio, newgt
+
+
+def correct_gt(input_path: str, output_path: str, bamfile: str, sigfile: str, dtype: str, vtype: str):
+    """LI/correct_gt_del_real_data.py / correct_gt_ins_real_data.py -i <vcf> -o <tsv> -bam <bam>
+    -sig <DEL.sigs|INS.sigs> -d <dtype> -v DEL|INS: writes <tsv>, <tsv>.newgt and <vcf>.newgt.<vtype>
+    (INS also <sigfile>.gte30auto)."""
+    ctx = context()
+    is_del = vtype == "DEL"
+    lines, chrom, pos, svid, gt, svlen = _gt_calls(input_path, vtype)
+    from . import resident as RS
+    n = len(lines)
+    gcode = np.asarray([0 if g == "0/1" else 1 if g == "1/1" else 2 for g in gt], dtype=np.int32)
+    for i in range(n):                           # the reference's pysam.fetch raises on a negative start (GTI:190, GTD:160)
+        lo = pos[i] - 100 if not is_del else (pos[i] - 150 if svlen[i] > 1000 else pos[i])
+        if lo < 0:
+            raise L.VsvError(L.E_ARG, "candidate %s is closer than %d bp to the chromosome start: the reference's "
+                                      "fetch() fails here" % (svid[i], pos[i] - lo))
+    ctx.set_params(L.default_params(dtype))
+    owner = RS.owner_of(sigfile)
+    if owner is not None:
+        sup, match_id, depth2, ratio, newgt = _correct_gt_resident(owner, bamfile, sigfile, is_del, chrom, pos, svlen, gcode)
+    else:
+        sup, match_id, depth2, ratio, newgt = _correct_gt_from_file(ctx, bamfile, sigfile, is_del, dtype, chrom, pos, svlen, gcode)
+    _gt_write(input_path, output_path, vtype, lines, chrom, pos, svid, gt, svlen, sup, match_id, depth2, ratio, newgt)
+
+
+def _gt_calls(input_path, vtype):
+    """The candidate lines of one type (GTD:250-289 / GTI:303-322): lines, chrom, pos, id, gt, svlen (DEL: |SVLEN|)."""
+    _, body = _read_vcf(input_path)
+    lines = [ln for ln in body if "SVTYPE=%s" % vtype in ln]
+    chrom = [ln.split()[0] for ln in lines]
+    pos = np.asarray([int(ln.split()[1]) for ln in lines], dtype=np.int32)
+    svid = [ln.split()[2] for ln in lines]
+    gt = [ln.split()[-1].split(":")[0] for ln in lines]
+    sv_signed = [int(ln.split("SVLEN=")[1].split(";")[0]) for ln in lines]
+    svlen = np.asarray([abs(x) for x in sv_signed] if vtype == "DEL" else sv_signed, dtype=np.int32)
+    return lines, chrom, pos, svid, gt, svlen
+
+
+def _gt_write(input_path, output_path, vtype, lines, chrom, pos, svid, gt, svlen, sup, match_id, depth2, ratio, newgt):
+    """<tsv>, <tsv>.newgt and <vcf>.newgt.<vtype> (GTD:219-234,320-340,379-382; GTI:222-229,285-301,341-344)."""
+    is_del = vtype == "DEL"
+    n = len(lines)
     new_gt = [g if k == 2 else ("1/1" if k == 1 else "0/1") for g, k in zip(gt, newgt)]
     rows = []
     if is_del:
@@ -656,6 +789,7 @@ def correct_gt(input_path: str, output_path: str, bamfile: str, sigfile: str, dt
     _write_lines(input_path + ".newgt.%s" % vtype, out)
 
 
+
 # --------------------------------------------------------------------------- FGC driver + final steps
 def vcf_sort(lines: Sequence[str]) -> List[str]:
     """vcftools `vcf-sort` default: header, then body by `sort -k1,1d -k2,2n` (FGC:177; SURVEY §8c pin 4).
@@ -668,8 +802,15 @@ def vcf_sort(lines: Sequence[str]) -> List[str]:
 
 
 def filter_gt_correction(vcffile: str, bamfile: Optional[str], reference: Optional[str], dtype: str,
-                         chr_num: Optional[int] = None, pre_cutesig: Optional[str] = None):
-    """LI/filter_GT_correction.py -vcf <vcf> -bam <bam> -ref <ref> -dtype <Hifi|CLR|ONT> [-chr N] [-presig dir]."""
+                         chr_num: Optional[int] = None, pre_cutesig: Optional[str] = None, rank: int = 0, world: int = 1,
+                         barrier=None, mine: Optional[Sequence[int]] = None):
+    """LI/filter_GT_correction.py -vcf <vcf> -bam <bam> -ref <ref> -dtype <Hifi|CLR|ONT> [-chr N] [-presig dir].
+    With world > 1 (whole-genome mode, one process per GPU) every rank runs the BAM-scale half for the chromosomes in
+    `mine` (`_fgc_sharded`); rank 0 only concatenates, takes the genome-wide median and writes the files."""
+    if world > 1 and chr_num is None and pre_cutesig is None:
+        return _fgc_sharded(vcffile, bamfile, reference, dtype, list(mine or []), rank, world, barrier)
+    if rank != 0:
+        return None
     wd = os.path.dirname(vcffile)
     if pre_cutesig is None:
         sigdir = os.path.join(wd, "cute_sig")
@@ -692,6 +833,159 @@ def filter_gt_correction(vcffile: str, bamfile: Optional[str], reference: Option
     os.makedirs(gtdir, exist_ok=True)
     correct_gt(filtered, os.path.join(gtdir, "bnd_del_real.tsv"), bamfile, os.path.join(sigdir, "DEL.sigs"), dtype, "DEL")
     correct_gt(filtered, os.path.join(gtdir, "bnd_ins_real.tsv"), bamfile, os.path.join(sigdir, "INS.sigs"), dtype, "INS")
+    header, _ = _read_vcf(filtered)
+    _write_lines(os.path.join(wd, "header"), header)
+    merged = header + open(filtered + ".newgt.DEL").readlines() + open(filtered + ".newgt.INS").readlines()
+    final = os.path.join(wd, "variants_filtered_GT_corrected.vcf")
+    _write_lines(final, vcf_sort(merged))
+    return final
+
+
+def _fgc_sharded(vcffile, bamfile, reference, dtype, mine, rank, world, barrier):
+    """filter_GT_correction.py for the whole genome, sharded like the reference shards it (sig_extract over 10 Mb tasks,
+    SE:600-632; the depth join per candidate, GTD:201-204), here by chromosome over the ranks.  Every rank: `.sigs` rows,
+    coverage support, supporting signatures, depth and genotype of ITS chromosomes from the shards it already holds.
+    Rank 0: concatenation in the reference's orders, the genome-wide coverage median (filter_vcf_by_sig_cov_insdel.py:39,55)
+    and the files.  Two values cross chromosome edges through the host: that median and last_match_idx (GTD:94)."""
+    from . import resident as RS
+    ctx = context()
+    wd = os.path.dirname(vcffile)
+    sigdir = os.path.join(wd, "cute_sig")
+    parts = os.path.join(sigdir, "signatures")
+    if rank == 0:
+        if os.path.exists(sigdir):
+            shutil.rmtree(sigdir)                                                            # FGC:64-66
+        os.makedirs(parts)
+    barrier()
+    ctx.set_params(L.default_params(dtype))
+    P = ctx.get_params()
+    src = open_alignments(bamfile)
+    refs = dict(src.references())
+    autos = {"chr%d" % c for c in range(1, 23)}
+    my = ["chr%d" % c for c in mine if "chr%d" % c in refs]
+    if rank == 0:
+        my += [c for c in refs if c not in autos]          # other references of the BAM: `.sigs` rows only
+    calls = _css_calls(vcffile)
+    shards = {}
+    for chrom in my:
+        sh = RS.get(ctx, src, bamfile, chrom, refs[chrom])
+        if sh.R.n == 0:
+            continue
+        shards[chrom] = sh
+        d, i, names = _sigs_chrom(sh, chrom, refs[chrom], P.batch_size, P.cute_min_mapq, None)
+        _write_lines(os.path.join(parts, "_%s.DEL.part" % chrom), sorted(d, key=_sigs_key))
+        _write_lines(os.path.join(parts, "_%s.INS.part" % chrom), sorted(i, key=_sigs_key))
+        for nm, lines in names.items():
+            _write_lines(os.path.join(parts, nm), lines)
+        up, ul, un = sh.fetch(L.TAB_UINS)
+        ci, cd = calls["INS"].get(chrom, []), calls["DEL"].get(chrom, [])
+        cov_i = sh.candidates(L.JOIN_COV, np.asarray([c[0] for c in ci], np.int32), np.asarray([c[2] for c in ci], np.int32),
+                              np.full(len(ci), L.INS, np.int32))["cov"]
+        cov_d = sh.candidates(L.JOIN_COV, np.asarray([c[0] for c in cd], np.int32), np.asarray([-c[2] for c in cd], np.int32),
+                              np.full(len(cd), L.DEL, np.int32))["cov"]
+        np.savez(os.path.join(parts, "_%s.tables.npz" % chrom), n_udel=sh.counts["n_udel"], n_uins=sh.counts["n_uins"], uins=np.stack([up, ul, un]),
+                 cov_ins=cov_i, cov_del=cov_d)
+    barrier()
+    chrom_files = sorted(fn[1:-len(".tables.npz")] for fn in os.listdir(parts) if fn.endswith(".tables.npz"))     # C-locale order
+    tables = {c: np.load(os.path.join(parts, "_%s.tables.npz" % c)) for c in chrom_files}
+    filtered = vcffile.replace(".vcf", "_filter_DEL.vcf")
+    if rank == 0:
+        for tp in ("DEL", "INS"):
+            with open(os.path.join(sigdir, tp + ".sigs"), "w") as fo:
+                for c in chrom_files:                      # lines sort by (chromosome, position, line): per-chromosome sorted parts in string order
+                    with open(os.path.join(parts, "_%s.%s.part" % (c, tp))) as fi:
+                        shutil.copyfileobj(fi, fo)
+        with open(os.path.join(sigdir, "reads.sigs"), "w") as fo:
+            for fn in sorted(f for f in os.listdir(parts) if f.endswith(".reads")):
+                with open(os.path.join(parts, fn)) as fi:
+                    shutil.copyfileobj(fi, fo)
+        rows, any_float = [], False
+        for tp, key in (("INS", "cov_ins"), ("DEL", "cov_del")):
+            for c in ["chr%d" % k for k in range(1, 23)]:
+                cl = calls[tp].get(c)
+                if cl:
+                    cov = tables[c][key] if c in tables else np.zeros(len(cl), np.int64)
+                    any_float |= tp == "INS"
+                    rows += [list(x) + [float(v) if tp == "INS" else int(v)] for x, v in zip(cl, cov)]
+        _css_write(vcffile, rows, any_float)
+        filter_by_sig_cov(vcffile, dtype.lower(), "volcano", "DEL")                           # FGC:27,141-145
+    barrier()
+    # ---- genotype correction of this rank's chromosomes ---------------------------------------------------------------
+    gtdir = os.path.join(wd, "GT_Correction")
+    res_path = lambda c, tp: os.path.join(parts, "_%s.gt.%s.npz" % (c, tp))
+    per_type = {}
+    for tp in ("DEL", "INS"):
+        is_del = tp == "DEL"
+        lines, chrom, pos, svid, gt, svlen = _gt_calls(filtered, tp)
+        per_type[tp] = (lines, chrom, pos, svid, gt, svlen)
+        n = len(lines)
+        for i in range(n):
+            lo = pos[i] - 100 if not is_del else (pos[i] - 150 if svlen[i] > 1000 else pos[i])
+            if lo < 0:
+                raise L.VsvError(L.E_ARG, "candidate %s is closer than %d bp to the chromosome start: the reference's "
+                                          "fetch() fails here" % (svid[i], pos[i] - lo))
+        gcode = np.asarray([0 if g == "0/1" else 1 if g == "1/1" else 2 for g in gt], dtype=np.int32)
+        carr = np.asarray(chrom)
+        key = "n_udel" if is_del else "n_uins"
+        with_sigs = [c for c in chrom_files if int(tables[c][key]) > 0 and (is_del or c[3:].isdigit())]
+        first_block = with_sigs[0] if with_sigs else None
+        for c in my:
+            idx = np.flatnonzero(carr == c)
+            if len(idx) == 0:
+                continue
+            if len(idx) != idx[-1] - idx[0] + 1:
+                raise L.VsvError(L.E_ARG, "candidates of %s are not contiguous in %s" % (c, filtered))
+            sh = shards.get(c) or RS.get(ctx, src, bamfile, c, refs[c])
+            sh.scan(None)
+            typ = np.full(len(idx), L.DEL if is_del else L.INS, np.int32)
+            out = {}
+            for li in ((-1, 0) if c == first_block else (-1,)):   # the block at global index 0 may be entered with last_match_idx == 0
+                o = sh.candidates(L.JOIN_SUPPORT | L.JOIN_GENOTYPE, pos[idx], svlen[idx], typ, gcode[idx],
+                                  last_in=(li, -1) if is_del else (-1, li))
+                tag = "a" if li < 0 else "b"
+                out.update({"sup_" + tag: o["n_support"], "mid_" + tag: o["match_id"], "gt_" + tag: o["new_gt"] if o["new_gt"] is not None else gcode[idx],
+                            "ratio_" + tag: o["ratio"], "last_" + tag: np.int64(o["last_out"][0 if is_del else 1]), "d2": o["depth2"]})
+            np.savez(res_path(c, tp), **out)
+    barrier()
+    if rank != 0:
+        return None
+    os.makedirs(gtdir, exist_ok=True)
+    for tp in ("DEL", "INS"):
+        is_del = tp == "DEL"
+        lines, chrom, pos, svid, gt, svlen = per_type[tp]
+        n = len(lines)
+        sup, match_id, depth2, newgt = (np.zeros(n, np.int32) for _ in range(4))
+        ratio = np.zeros(n, np.float64)
+        key = "n_udel" if is_del else "n_uins"
+        with_sigs = [c for c in chrom_files if int(tables[c][key]) > 0 and (is_del or c[3:].isdigit())]
+        block, off = {}, 0
+        for c in with_sigs:
+            block[c] = (off, int(tables[c][key]))
+            off += int(tables[c][key])
+        if not is_del:
+            out = []
+            for c in with_sigs:
+                up, ul, un = tables[c]["uins"]
+                out += ["%d\t%d\t%d\t%d\n" % (int(c[3:]), p_, l_, k_) for p_, l_, k_ in zip(up, ul, un)]
+            _write_lines(os.path.join(sigdir, "INS.sigs.gte30auto"), out)
+        carr = np.asarray(chrom)
+        global_last = 0
+        for c in dict.fromkeys(chrom):                 # chromosomes in VCF order (each one contiguous: checked by its rank)
+            idx = np.flatnonzero(carr == c)
+            r = np.load(res_path(c, tp))
+            b0, nu = block.get(c, (0, 0))
+            li = global_last - b0 if (nu > 0 and b0 <= global_last < b0 + nu) else -1
+            if li > 0 or (li == 0 and "sup_b" not in r.files):
+                raise L.VsvError(L.E_ARG, "last_match_idx points inside the block of %s before its first candidate" % c)
+            tag = "b" if li == 0 else "a"
+            sup[idx], depth2[idx], ratio[idx], newgt[idx] = r["sup_" + tag], r["d2"], r["ratio_" + tag], r["gt_" + tag]
+            mid = r["mid_" + tag]
+            match_id[idx] = np.where(mid >= 0, b0 + mid, global_last) if off > 0 else 0
+            lo = int(r["last_" + tag])
+            if lo >= 0:
+                global_last = b0 + lo
+        _gt_write(filtered, os.path.join(gtdir, "bnd_%s_real.tsv" % tp.lower()), tp, lines, chrom, pos, svid, gt, svlen, sup, match_id,
+                  depth2, ratio, newgt)
     header, _ = _read_vcf(filtered)
     _write_lines(os.path.join(wd, "header"), header)
     merged = header + open(filtered + ".newgt.DEL").readlines() + open(filtered + ".newgt.INS").readlines()
@@ -1047,11 +1341,36 @@ def remove_redundancy(input_path: str, output_dir: str, dist_thresh: int = 500, 
 
 
 # --------------------------------------------------------------------------- drivers (RVC, MAIN)
-def raw_variant_call(contig_bam: str, contig_path: str, reference_path: str, output_dir: str, dtype: str, chr_num: int,
-                     rbam_file: Optional[str] = None, signature_dir: Optional[str] = None, header_file: Optional[str] = None):
-    """LI/Raw_variant_call.py after its alignment step (RVC:65-105; minimap2/samtools are out of scope:
-    the caller hands over the sorted contig alignments)."""
+def align_contigs(contig_path: str, reference_path: str, output_dir: str, n_thread: int = 10, mem_per_thread: str = "1G",
+                  preset: str = "asm5", bam_path: Optional[str] = None) -> str:
+    """The alignment step of LI/Raw_variant_call.py (RVC:45-58; otherasm:232-245 with preset asm20), verbatim: the contig BAM is
+    made by the external tools the reference uses.  Alignment itself is out of scope: without minimap2 and
+    samtools on PATH this raises and names -cbam, which hands over alignments made elsewhere."""
+    import subprocess
+    missing = [t for t in ("minimap2", "samtools") if shutil.which(t) is None]
+    if missing:
+        raise RuntimeError("%s not found on PATH: volcanosv-vc-large-indel.py aligns the contigs with `minimap2 -a -x %s --cs -r2k | "
+                           "samtools sort` (Raw_variant_call.py:49-58).  Install them, or pass the sorted contig alignments with -cbam."
+                           % (" and ".join(missing), preset))
     os.makedirs(output_dir, exist_ok=True)
+    if bam_path is None:
+        bam_path = output_dir + "/" + contig_path.split("/")[-1].split(".")[0] + ".sorted.bam"
+    cmd = "minimap2 -a -x %s --cs -r2k -t %d %s %s | samtools sort -@ %d -m %s > %s" % (preset, n_thread, reference_path, contig_path,
+                                                                                       n_thread, mem_per_thread, bam_path)
+    if subprocess.Popen(cmd, shell=True).wait() != 0 or not os.path.exists(bam_path) or os.path.getsize(bam_path) == 0:
+        raise RuntimeError("contig alignment failed: %s" % cmd)
+    subprocess.Popen("samtools index " + bam_path, shell=True).wait()
+    return bam_path
+
+
+def raw_variant_call(contig_bam: Optional[str], contig_path: str, reference_path: str, output_dir: str, dtype: str, chr_num: int,
+                     rbam_file: Optional[str] = None, signature_dir: Optional[str] = None, header_file: Optional[str] = None,
+                     n_thread: int = 10, mem_per_thread: str = "1G"):
+    """LI/Raw_variant_call.py (RVC:45-105).  contig_bam=None runs the reference's own alignment command (`align_contigs`);
+    a path skips it (-cbam: the sorted contig alignments made elsewhere)."""
+    os.makedirs(output_dir, exist_ok=True)
+    if contig_bam is None:
+        contig_bam = align_contigs(contig_path, reference_path, output_dir, n_thread, mem_per_thread)
     extract_contig_signature(contig_bam, contig_path, reference_path, output_dir, chr_num, dtype, header_file)
     header = open(header_file).readlines() if header_file else default_header()
     body = []
@@ -1102,10 +1421,10 @@ def _write_chrom_ref(ref: Dict[str, str], ref_dir: str, chr_num: int) -> str:
     return one
 
 
-def large_indel_wgs(contig_bam_pattern: str, input_dir: str, reference: str, rbam_file: str, output_dir: str, dtype: str,
+def large_indel_wgs(contig_bam_pattern: Optional[str], input_dir: str, reference: str, rbam_file: str, output_dir: str, dtype: str,
                     prefix: str = "Sample", read_signature_dir: Optional[str] = None, pre_cutesig: Optional[str] = None,
                     chroms: Sequence[int] = tuple(range(1, 23)), rank: int = 0, world: int = 1, barrier=None,
-                    contig_fasta_pattern: Optional[str] = None):
+                    contig_fasta_pattern: Optional[str] = None, n_thread_align: int = 10):
     """LI/volcanosv-vc-large-indel.py WITHOUT -chr (MAIN:233-319): chr1..chr22 through the raw-call
     chain, bodies concatenated in numeric chromosome order into raw_variants_wgs.vcf, ONE
     genome-wide filter + genotype correction, phasing.
@@ -1126,41 +1445,51 @@ def large_indel_wgs(contig_bam_pattern: str, input_dir: str, reference: str, rba
         _write_lines(header_file, ["##fileformat=VCFv4.2\n"] + ["##contig=<ID=%s,length=%d>\n" % c for c in contigs] +
                      final_header_info(prefix))
     weights = {}
+    fasta_of = lambda c: contig_fasta_pattern.format(chr=c) if contig_fasta_pattern else \
+        "%s/chr%d/assembly/final_contigs/%s_final_contigs.fa" % (input_dir, c, prefix)
     for c in chroms:
-        p = contig_bam_pattern.format(chr=c)
+        p = contig_bam_pattern.format(chr=c) if contig_bam_pattern else fasta_of(c)
         weights[c] = float(os.path.getsize(p) if os.path.exists(p) else 0) + float(len(ref.get("chr%d" % c, "")))
     mine = SH.assign_lpt(weights, world)[rank]
     for c in sorted(mine):
         one = _write_chrom_ref(ref, ref_dir, c)
-        contig_path = contig_fasta_pattern.format(chr=c) if contig_fasta_pattern else \
-            "%s/chr%d/assembly/final_contigs/%s_final_contigs.fa" % (input_dir, c, prefix)
-        raw_variant_call(contig_bam_pattern.format(chr=c), contig_path, one, os.path.join(output_dir, "chr%d" % c), dtype, c,
-                         rbam_file, read_signature_dir)
+        raw_variant_call(contig_bam_pattern.format(chr=c) if contig_bam_pattern else None, fasta_of(c), one,
+                         os.path.join(output_dir, "chr%d" % c), dtype, c, rbam_file, read_signature_dir, n_thread=n_thread_align)
     if barrier is not None:
         barrier()
+    raw = os.path.join(output_dir, "raw_variants_wgs.vcf")
+    if rank == 0:
+        header, body = [], []
+        for c in chroms:                                                                   # MAIN:271-278
+            header, b = _read_vcf(os.path.join(output_dir, "chr%d" % c, "final_vcf", "volcano_variant_no_redundancy.vcf"))
+            body += b
+        _write_lines(raw, header + body)
+    if barrier is not None:
+        barrier()
+    # the genome-wide half (FGC:111-178): every rank works on the chromosomes whose shards it holds
+    final = filter_gt_correction(raw, rbam_file, reference, dtype, None, pre_cutesig, rank=rank, world=world, barrier=barrier, mine=sorted(mine))
     if rank != 0:
         return None
-    header, body = [], []
-    for c in chroms:                                                                       # MAIN:271-278
-        header, b = _read_vcf(os.path.join(output_dir, "chr%d" % c, "final_vcf", "volcano_variant_no_redundancy.vcf"))
-        body += b
-    raw = os.path.join(output_dir, "raw_variants_wgs.vcf")
-    _write_lines(raw, header + body)
-    final = filter_gt_correction(raw, rbam_file, reference, dtype, None, pre_cutesig)
     outfile = os.path.join(output_dir, "%s_volcanosv_large_indel.vcf" % prefix)
     phase_vcf(final, outfile, header_file)
     return outfile
 
 
-def large_indel_otherasm(input_path: str, contig_bam: str, reference: str, rbam_file: str, output_dir: str, dtype: str,
+def large_indel_otherasm(input_path: str, contig_bam: Optional[str], reference: str, rbam_file: str, output_dir: str, dtype: str,
                          prefix: str = "Sample", read_signature_dir: Optional[str] = None, pre_cutesig: Optional[str] = None,
-                         rank: int = 0, world: int = 1, barrier=None):
+                         rank: int = 0, world: int = 1, barrier=None, n_thread: int = 11, mem_per_thread: str = "768M"):
     """LI/volcanosv-vc-large-indel-otherasm.py (any haplotype-resolved assembly): ONE whole-genome contig
     FASTA (`input_path`, 'hp1'/'hp2' in the contig names) and ONE sorted contig alignment file
     (`contig_bam`; the reference makes it with minimap2 -x asm20, otherasm:232-245, out of scope).
     Contigs are split by the chromosome they align to (otherasm:249-293), then the whole-genome
     chain of `large_indel_wgs` runs with Raw_variant_call-otherasm.py's contract (-cbam)."""
     folder = os.path.join(output_dir, "contig_by_chr")
+    if contig_bam is None:                                 # otherasm:305,328: <o>/<prefix>.sorted.bam with preset asm20
+        contig_bam = output_dir + "/" + prefix + ".sorted.bam"
+        if rank == 0:
+            align_contigs(input_path, reference, output_dir, n_thread, mem_per_thread, "asm20", contig_bam)
+        if barrier is not None:
+            barrier()
     if rank == 0:
         os.makedirs(folder, exist_ok=True)
         src = open_alignments(contig_bam)
@@ -1175,15 +1504,28 @@ def large_indel_otherasm(input_path: str, contig_bam: str, reference: str, rbam_
                            rank=rank, world=world, barrier=barrier, contig_fasta_pattern=os.path.join(folder, "chr{chr}.fasta"))
 
 
-def large_indel_otherasm_2hap(hp1_fa: str, hp2_fa: str, contig_bam: str, reference: str, rbam_file: str, output_dir: str,
+def large_indel_otherasm_2hap(hp1_fa: str, hp2_fa: str, contig_bam: Optional[str], reference: str, rbam_file: str, output_dir: str,
                               dtype: str, prefix: str = "Sample", read_signature_dir: Optional[str] = None,
-                              pre_cutesig: Optional[str] = None, rank: int = 0, world: int = 1, barrier=None):
+                              pre_cutesig: Optional[str] = None, rank: int = 0, world: int = 1, barrier=None, n_thread: int = 11,
+                              mem_per_thread: str = "768M"):
     """LI/volcanosv-vc-large-indel-otherasm-2hap.py: the two haplotypes arrive as two FASTA files.  The
     reference aligns each, merges the two BAMs into one sorted file (2hap:250-258, minimap2 / samtools: out
     of scope, `contig_bam` is that file) and concatenates the FASTAs to `contig_by_chr/merged.fa`
     (2hap:274-279) before the same per-chromosome split as the one-file entry (2hap:281-311)."""
     folder = os.path.join(output_dir, "contig_by_chr")
     merged = os.path.join(folder, "merged.fa")
+    if contig_bam is None:                                 # 2hap:250-258: one alignment per haplotype, merged and sorted
+        import subprocess
+        contig_bam = output_dir + "/" + prefix + ".sorted.bam"
+        if rank == 0:
+            hp = [align_contigs(fa, reference, output_dir, n_thread, mem_per_thread, "asm20", output_dir + "/hp%d.bam" % (k + 1))
+                  for k, fa in enumerate((hp1_fa, hp2_fa))]
+            cmd = "samtools merge -u - %s %s | samtools sort -o %s;samtools index %s" % (hp[0], hp[1], contig_bam, contig_bam)
+            subprocess.Popen(cmd, shell=True).wait()
+            if not os.path.exists(contig_bam):
+                raise RuntimeError("merging the haplotype alignments failed: %s" % cmd)
+        if barrier is not None:
+            barrier()
     if rank == 0:
         os.makedirs(folder, exist_ok=True)
         with open(merged, "wb") as fo:                                                     # cat hp1 hp2 > merged.fa
@@ -1196,9 +1538,9 @@ def large_indel_otherasm_2hap(hp1_fa: str, hp2_fa: str, contig_bam: str, referen
                                 pre_cutesig, rank=rank, world=world, barrier=barrier)
 
 
-def large_indel_chr(contig_bam: str, contig_path: str, reference: str, rbam_file: str, output_dir: str, dtype: str,
+def large_indel_chr(contig_bam: Optional[str], contig_path: str, reference: str, rbam_file: str, output_dir: str, dtype: str,
                     chr_num: int, prefix: str = "Sample", read_signature_dir: Optional[str] = None,
-                    pre_cutesig: Optional[str] = None):
+                    pre_cutesig: Optional[str] = None, n_thread_align: int = 10):
     """LI/volcanosv-vc-large-indel.py ... -chr N (MAIN:233-319) with the contig alignments supplied:
     header, per-chromosome chain, filter + genotype correction, phasing."""
     out_chr = os.path.join(output_dir, "chr%d" % chr_num)
@@ -1210,7 +1552,7 @@ def large_indel_chr(contig_bam: str, contig_path: str, reference: str, rbam_file
     _write_lines(header_file, vcf_header + final_header_info(prefix))
     _write_fai(reference)                                                                  # samtools faidx (MAIN:88-96)
     one = _write_chrom_ref(ref, os.path.join(out_chr, "ref_by_chr"), chr_num)
-    raw = raw_variant_call(contig_bam, contig_path, one, out_chr, dtype, chr_num, rbam_file, read_signature_dir)
+    raw = raw_variant_call(contig_bam, contig_path, one, out_chr, dtype, chr_num, rbam_file, read_signature_dir, n_thread=n_thread_align)
     final = filter_gt_correction(raw, rbam_file, reference, dtype, chr_num, pre_cutesig)
     outfile = os.path.join(out_chr, "%s_volcanosv_large_indel_chr%d.vcf" % (prefix, chr_num))
     phase_vcf(final, outfile, header_file)
