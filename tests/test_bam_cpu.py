@@ -133,7 +133,7 @@ def test_alignment_source_bam_equals_sam(tmp_path):
         A, B = a.records("chr1"), b.records("chr1")
         for k in ("ops", "op_off", "pos", "mapq", "flag", "qlen", "is_rev", "first_op", "last_op"):
             assert np.array_equal(getattr(A, k), getattr(B, k)), k
-        assert A.n == B.n and A.qname == B.qname and A.sa == B.sa
+        assert A.n == B.n and list(A.qname) == list(B.qname) and A.sa == B.sa
         assert all(A.seq[i] == B.seq[i] for i in range(0, A.n, 5))
         assert b.records("chrNone").n == 0
 
@@ -167,3 +167,81 @@ def test_open_one_reference_streaming(tmp_path, monkeypatch, window):
     assert len(hdr.refs) == 22 and all(n == 0 for _, _, n in hdr.refs)
     with pytest.raises(L.VsvError):
         L.BamFile(bam, ref="chrUn")
+
+
+def _raw_bam(records, refs=(("chrA", 100000),), l_text_override=None, n_ref_override=None):
+    """A one-block BAM from hand-made record bodies (malformed on purpose)."""
+    import struct
+    out = bytearray(b"BAM\1")
+    out += struct.pack("<I", 0 if l_text_override is None else l_text_override)
+    out += struct.pack("<I", len(refs) if n_ref_override is None else n_ref_override)
+    for n, ln in refs:
+        out += struct.pack("<I", len(n) + 1) + n.encode() + b"\0" + struct.pack("<I", ln)
+    for body in records:
+        out += struct.pack("<I", len(body)) + body
+    return bamio._bgzf_block(bytes(out)) + bamio._bgzf_block(b"")
+
+
+def _cg_record(n_claimed, n_present, l_seq=8):
+    """<l_seq>S<n>N placeholder CIGAR + a CG:B,I tag that CLAIMS n_claimed ops but carries n_present."""
+    import struct
+    name = b"r\0"
+    cigar = [(l_seq << 4) | 4, (50 << 4) | 3]
+    body = struct.pack("<iiBBHHHIiii", 0, 10, len(name), 60, 4681, len(cigar), 0, l_seq, -1, -1, 0)
+    body += name + struct.pack("<2I", *cigar) + bytes((l_seq + 1) // 2) + b"\xff" * l_seq
+    body += b"CGBI" + struct.pack("<I", n_claimed) + struct.pack("<%dI" % n_present, *([(5 << 4) | 0] * n_present))
+    return body
+
+
+def test_malformed_records_are_rejected_not_overread(tmp_path):
+    """a CG:B,I count that runs past the record, a scalar tag cut short, implausible header sizes -> an
+    error (or a clean load), never a read past the record."""
+    good = tmp_path / "good.bam"
+    good.write_bytes(_raw_bam([_cg_record(3, 3)]))
+    bf = L.BamFile(str(good))
+    d = bf.chrom("chrA")
+    assert d["op_off"].tolist() == [0, 3] and d["ops"].tolist() == [(5 << 4)] * 3
+    for name, blob in (("cg_count_past_record", _raw_bam([_cg_record(1 << 20, 3)])),
+                       ("cg_count_huge", _raw_bam([_cg_record(0xFFFFFFF0, 1)])),
+                       ("scalar_tag_cut", _raw_bam([_cg_record(3, 3)[:-10] + b"XYi\x01"])),
+                       ("l_text_huge", _raw_bam([_cg_record(3, 3)], l_text_override=0x7FFFFFF0)),
+                       ("n_ref_huge", _raw_bam([_cg_record(3, 3)], n_ref_override=0x7FFFFFF0))):
+        p = tmp_path / (name + ".bam")
+        p.write_bytes(blob)
+        with pytest.raises(L.VsvError):
+            f = L.BamFile(str(p))
+            f.chrom("chrA")
+
+
+def test_stale_index_falls_back_to_the_linear_scan(tmp_path):
+    """A .bai of another file (different reference count) or one whose offsets point at records of another reference
+    must not make the feeder return part of a chromosome."""
+    wgs = os.path.join(HERE, "golden", "e2e_wgs", "input")
+    bam = str(tmp_path / "reads.bam")
+    bamio.sam_to_bam(os.path.join(wgs, "reads.sam.gz"), bam, block=30000, bai=True)
+    full = L.BamFile(bam, n_threads=2)
+    want = _columns(full, "chr7")
+    good = open(bam + ".bai", "rb").read()
+    # (a) index with another reference count
+    import struct
+    open(bam + ".bai", "wb").write(b"BAI\1" + struct.pack("<i", 3) + good[8:])
+    assert _columns(L.BamFile(bam, ref="chr7"), "chr7") == want
+    # (b) same count, but chr7's chunk start replaced by chr2's: the record there is not chr7's
+    other = str(tmp_path / "other.bam")
+    bamio.sam_to_bam(os.path.join(wgs, "reads.sam.gz"), other, block=30000, bai=True)
+    idx = bytearray(open(other + ".bai", "rb").read())
+    # per reference: n_bin(4) [bin(4) n_chunk(4) chunks(16 each)]* n_intv(4); the writer emits 2 bins: (0, 1 chunk) and the pseudo-bin (2 chunks)
+    q, starts = 8, []
+    for r in range(22):
+        n_bin = struct.unpack_from("<i", idx, q)[0]
+        q += 4
+        for _ in range(n_bin):
+            b_, n_chunk = struct.unpack_from("<Ii", idx, q)
+            q += 8
+            if b_ != 37450:
+                starts.append(q)
+            q += 16 * n_chunk
+        q += 4 + 8 * struct.unpack_from("<i", idx, q)[0]
+    idx[starts[6]: starts[6] + 8] = idx[starts[1]: starts[1] + 8]
+    open(bam + ".bai", "wb").write(bytes(idx))
+    assert _columns(L.BamFile(bam, ref="chr7"), "chr7") == want

@@ -60,10 +60,11 @@ inline uint16_t rd16(const uint8_t* p) { uint16_t v; memcpy(&v, p, 2); return v;
 // size of one aux value starting at p (type byte at p[0]); 0 on malformed input
 size_t aux_size(const uint8_t* p, const uint8_t* end) {
   if (p >= end) return 0;
+  const size_t room = (size_t)(end - p);
   switch (*p) {
-    case 'A': case 'c': case 'C': return 2;
-    case 's': case 'S': return 3;
-    case 'i': case 'I': case 'f': return 5;
+    case 'A': case 'c': case 'C': return room >= 2 ? 2 : 0;
+    case 's': case 'S': return room >= 3 ? 3 : 0;
+    case 'i': case 'I': case 'f': return room >= 5 ? 5 : 0;
     case 'Z': case 'H': {
       const uint8_t* q = p + 1;
       while (q < end && *q) ++q;
@@ -78,7 +79,8 @@ size_t aux_size(const uint8_t* p, const uint8_t* end) {
         case 'i': case 'I': case 'f': es = 4; break;
         default: return 0;
       }
-      return 6 + es * (size_t)rd32(p + 2);
+      const size_t sz = 6 + es * (size_t)rd32(p + 2);
+      return sz <= room ? sz : 0;   // a count that runs past the record is malformed, not a size
     }
     default: return 0;
   }
@@ -112,10 +114,11 @@ bool view(const uint8_t* body, uint32_t size, RecView* v, bool has_qual = false)
   v->name = reinterpret_cast<const char*>(p);
   p += v->l_name;
   v->cigar = reinterpret_cast<const uint32_t*>(p);
+  if ((size_t)(v->end - body) < 32 + (size_t)v->l_name + 4 * (size_t)v->n_cigar) return false;
   p += 4 * (size_t)v->n_cigar;
   v->seq = p;
+  if ((size_t)(v->end - p) < ((size_t)v->l_seq + 1) / 2 + (has_qual ? (size_t)v->l_seq : 0)) return false;
   p += ((size_t)v->l_seq + 1) / 2 + (has_qual ? (size_t)v->l_seq : 0);
-  if (p > v->end) return false;
   v->aux = p;
   // long CIGAR: <l_seq>S<n>N placeholder + CG:B,I
   if (v->n_cigar == 2) {
@@ -123,10 +126,11 @@ bool view(const uint8_t* body, uint32_t size, RecView* v, bool has_qual = false)
     memcpy(&c0, v->cigar, 4);
     memcpy(&c1, v->cigar + 1, 4);
     if ((c0 & 15u) == 4u && (int32_t)(c0 >> 4) == v->l_seq && (c1 & 15u) == 3u) {
-      for (const uint8_t* a = v->aux; a + 3 <= v->end;) {
+      for (const uint8_t* a = v->aux; a + 4 <= v->end;) {
         const size_t sz = aux_size(a + 2, v->end);
-        if (!sz) break;
+        if (!sz) return false;   // a malformed tag in a record that needs its CG tag: reject the record
         if (a[0] == 'C' && a[1] == 'G' && a[2] == 'B' && a[3] == 'I') {
+          // aux_size has checked that the whole B array (8 + 4 * count bytes from `a`) lies inside the record
           v->n_cigar = rd32(a + 4);
           v->cigar = reinterpret_cast<const uint32_t*>(a + 8);
           break;
@@ -273,7 +277,7 @@ class BgzfReader {
 
 // smallest chunk start (virtual offset) of reference `tid` in a BAI index; false if the file is
 // absent / unreadable; *has = false when the reference has no records
-bool bai_ref_start(const std::string& bam_path, int tid, uint64_t* voff, bool* has) {
+bool bai_ref_start(const std::string& bam_path, int tid, int n_ref_bam, uint64_t* voff, bool* has) {
   std::vector<std::string> cand = {bam_path + ".bai"};
   if (bam_path.size() > 4 && bam_path.compare(bam_path.size() - 4, 4, ".bam") == 0)
     cand.push_back(bam_path.substr(0, bam_path.size() - 4) + ".bai");
@@ -291,6 +295,7 @@ bool bai_ref_start(const std::string& bam_path, int tid, uint64_t* voff, bool* h
     size_t q = 4;
     const int32_t n_ref = rd32s(d.data() + q);
     q += 4;
+    if (n_ref != n_ref_bam) continue;   // an index of another file
     bool bad = false;
     for (int32_t r = 0; r < n_ref && !bad; ++r) {
       if (q + 4 > d.size()) { bad = true; break; }
@@ -360,17 +365,19 @@ int bam_load(const char* path, int n_threads, const char* ref_name, vsv_bam** ou
   if (memcmp(buf.data() + pos, "BAM\1", 4) != 0) return fail("not a BAM stream (CRAM/SAM are not read here)");
   const uint32_t l_text = rd32(buf.data() + pos + 4);
   pos += 8;
+  if (l_text > (1u << 30)) return fail("implausible header text length");
   if (!need((size_t)l_text + 4)) return fail("truncated header");
   b->header_text.assign(reinterpret_cast<const char*>(buf.data() + pos), l_text);
   pos += l_text;
   const uint32_t n_ref = rd32(buf.data() + pos);
   pos += 4;
+  if (n_ref > (1u << 24)) return fail("implausible reference count");   // each reference needs >= 9 bytes of stream anyway
   b->refs.resize(n_ref);
   for (uint32_t i = 0; i < n_ref; ++i) {
     if (!need(4)) return fail("truncated reference list");
     const uint32_t l_name = rd32(buf.data() + pos);
     pos += 4;
-    if (l_name == 0 || !need((size_t)l_name + 4)) return fail("truncated reference list");
+    if (l_name == 0 || l_name > (1u << 20) || !need((size_t)l_name + 4)) return fail("truncated reference list");
     b->refs[i].name.assign(reinterpret_cast<const char*>(buf.data() + pos), l_name - 1);
     pos += l_name;
     b->refs[i].len = rd32(buf.data() + pos);
@@ -391,18 +398,45 @@ int bam_load(const char* path, int n_threads, const char* ref_name, vsv_bam** ou
     stop_after = b->header_text.find("SO:coordinate") != std::string::npos;
     uint64_t voff = 0;
     bool has = false;
-    if (bai_ref_start(path, tid, &voff, &has)) {
-      stop_after = true;
+    if (bai_ref_start(path, tid, (int)n_ref, &voff, &has)) {
       if (!has) {  // indexed and empty
         fclose(f);
         *out = b;
         return VSV_OK;
       }
-      rd.seek(voff >> 16);
-      buf.clear();
-      pos = 0;
-      if (!need((size_t)(voff & 0xFFFFu) + 4)) return fail(err.empty() ? "index points past the end of the file" : err);
-      pos = (size_t)(voff & 0xFFFFu);
+      // trust the index only if the record it points at belongs to `tid` (a stale or foreign .bai would make the
+      // feeder seek mid-stream and return part of a chromosome); otherwise read the file from its start
+      fseek(f, 0, SEEK_END);
+      const long fsz = ftell(f);
+      bool ok = fsz > 0 && (voff >> 16) < (uint64_t)fsz;
+      if (ok) {
+        rd.seek(voff >> 16);
+        buf.clear();
+        pos = 0;
+        ok = need((size_t)(voff & 0xFFFFu) + 40);
+        if (ok) {
+          const uint8_t* r = buf.data() + (voff & 0xFFFFu);
+          ok = rd32(r) >= 32 && rd32s(r + 4) == tid;
+        }
+        if (ok) {
+          pos = (size_t)(voff & 0xFFFFu);
+          stop_after = true;
+        } else {   // back to the linear scan after the header
+          err.clear();
+          rd.seek(0);
+          buf.clear();
+          pos = 0;
+          // re-read the header bytes to reposition behind them
+          size_t skip = 12 + (size_t)l_text;
+          if (!need(skip)) return fail("truncated header");
+          for (uint32_t i = 0; i < n_ref; ++i) {
+            if (!need(skip + 4)) return fail("truncated reference list");
+            skip += 8 + (size_t)rd32(buf.data() + skip);
+          }
+          if (!need(skip)) return fail("truncated reference list");
+          pos = skip;
+        }
+      }
     }
   }
   // ---- records: per window, a serial walk of the block_size chain, then sizes and copies in parallel ----
@@ -467,11 +501,26 @@ int bam_load(const char* path, int n_threads, const char* ref_name, vsv_bam** ou
 
 }  // namespace
 
-extern "C" int vsv_bam_open(const char* path, int n_threads, vsv_bam** out) { return bam_load(path, n_threads, nullptr, out); }
+// bad_alloc / length_error from a crafted size field must not cross the C ABI
+static int bam_load_guarded(const char* path, int n_threads, const char* ref_name, vsv_bam** out) {
+  try {
+    return bam_load(path, n_threads, ref_name, out);
+  } catch (const std::bad_alloc&) {
+    g_bam_err = "vsv_bam_open: out of memory (or a corrupt size field)";
+    if (out) *out = nullptr;
+    return VSV_E_NOMEM;
+  } catch (const std::exception& e) {
+    g_bam_err = std::string("vsv_bam_open: ") + e.what();
+    if (out) *out = nullptr;
+    return VSV_E_ARG;
+  }
+}
+
+extern "C" int vsv_bam_open(const char* path, int n_threads, vsv_bam** out) { return bam_load_guarded(path, n_threads, nullptr, out); }
 
 extern "C" int vsv_bam_open_ref(const char* path, const char* ref_name, int n_threads, vsv_bam** out) {
   if (!ref_name) { g_bam_err = "vsv_bam_open_ref: null argument"; return VSV_E_ARG; }
-  return bam_load(path, n_threads, ref_name, out);
+  return bam_load_guarded(path, n_threads, ref_name, out);
 }
 
 extern "C" void vsv_bam_close(vsv_bam* b) { delete b; }

@@ -28,7 +28,9 @@
 #define TAG_INS 2u
 #define TAG_END 3u
 #define DUPLIST_CAP 65536
-#define GROUP_THREADS 512
+#define GROUP_THREADS 256
+#define GROUP_ITEMS 8
+#define GROUP_TILE (GROUP_THREADS * GROUP_ITEMS)
 #define CHAIN_THREADS 1024
 #define ROW_SA_REV 256
 
@@ -100,6 +102,51 @@ __device__ __forceinline__ int2 lookback_exclusive(LbDesc* desc, unsigned int ti
   desc[tile].inc = op(excl, agg);
   __threadfence();
   st_release_u32(&desc[tile].flag, 2u);
+  return excl;
+}
+
+// Same, called by all 32 lanes of ONE warp with identical arguments: 32 predecessor descriptors are polled at once
+// (the serial walk above costs one global round trip per tile and was 16 % of the ONT step).  Returns the exclusive
+// prefix to every lane.
+template <typename Op>
+__device__ __forceinline__ int2 lookback_exclusive_warp(LbDesc* desc, unsigned int tile, int2 agg, int2 identity, Op op) {
+  const int lane = threadIdx.x & 31;
+  if (tile == 0) {
+    if (lane == 0) {
+      desc[0].inc = agg;
+      __threadfence();
+      st_release_u32(&desc[0].flag, 2u);
+    }
+    return identity;
+  }
+  if (lane == 0) {
+    desc[tile].agg = agg;
+    __threadfence();
+    st_release_u32(&desc[tile].flag, 1u);
+  }
+  int2 excl = identity;
+  for (int64_t base = (int64_t)tile - 1;; base -= 32) {
+    const int64_t j = base - lane;   // lane 0 looks at the nearest predecessor
+    unsigned int f = 2u;
+    int2 val = identity;
+    if (j >= 0) {
+      do { f = ld_acquire_u32(&desc[j].flag); } while (f == 0u);
+      val = ld_volatile_i2(f == 2u ? &desc[j].inc : &desc[j].agg);
+    }
+    const unsigned int m2 = __ballot_sync(0xffffffffu, f == 2u);
+    const int last = m2 ? __ffs(m2) - 1 : 31;
+    for (int k = 0; k <= last; ++k) {
+      int2 v;
+      v.x = __shfl_sync(0xffffffffu, val.x, k); v.y = __shfl_sync(0xffffffffu, val.y, k);
+      excl = op(v, excl);
+    }
+    if (m2) break;
+  }
+  if (lane == 0) {
+    desc[tile].inc = op(excl, agg);
+    __threadfence();
+    st_release_u32(&desc[tile].flag, 2u);
+  }
   return excl;
 }
 
@@ -298,12 +345,25 @@ k_shard_sa(RecCols R, SaCols A, const int32_t* __restrict__ ref_end, const uint8
 // ---- P11: in-read merge of the raw cute signatures (SE:373-435) -> `.sigs` rows ----------------------
 // One thread per record run (head = first signature of a record); count, block-aggregated slot
 // reservation (two atomics per CTA), write.  `first` of a row = index of its first raw signature.
-template <typename FD, typename FI>
-__device__ __forceinline__ void merge_walk_rows(const vsv_sig* __restrict__ s, int64_t i0, int64_t i1, FD fd, FI fi) {
+#define MERGE_THREADS 256
+#define MERGE_HALO 96
+// the first half (rec, type, pos, len) of raw signature k: from the CTA's shared-memory window when it is inside
+struct SigWindow {
+  const int4* s_a;       // rows [lo, hi) staged (first halves)
+  int64_t lo, hi;
+  const vsv_sig* g;
+  __device__ __forceinline__ int4 a(int64_t k) const {
+    return (k >= lo && k < hi) ? s_a[k - lo] : __ldg(reinterpret_cast<const int4*>(g + k));
+  }
+};
+template <bool FULL, typename FD, typename FI>
+__device__ __forceinline__ void merge_walk_rows(const SigWindow& W, int64_t i0, int64_t i1, FD fd, FI fi) {
   MState sd, si;
   sd.open = si.open = false;
   for (int64_t k = i0; k < i1; ++k) {
-    const int4 a = reinterpret_cast<const int4*>(s + k)[0], b = reinterpret_cast<const int4*>(s + k)[1];
+    const int4 a = W.a(k);
+    int4 b = make_int4(0, 0, 0, 0);
+    if (FULL) b = __ldg(reinterpret_cast<const int4*>(W.g + k) + 1);
     vsv_sig n;
     n.rec = a.x; n.type = a.y; n.pos = a.z; n.len = a.w; n.q0 = b.x; n.q1 = b.y; n.first = b.z; n.count = b.w;
     if (n.type == VSV_DEL) mstate_push(sd, n, (int32_t)k, VSV_MODE_CUTE, VSV_DEL, fd);
@@ -312,26 +372,57 @@ __device__ __forceinline__ void merge_walk_rows(const vsv_sig* __restrict__ s, i
   if (sd.open) fd(sd.cur);
   if (si.open) fi(si.cur);
 }
-static __global__ void __launch_bounds__(256)
+// The CTA stages the decision fields of its 256 signatures (+ a halo: a run is a handful long) in shared memory with
+// coalesced loads and COMPACTS the record heads (first signature of a record: ~1 in 8) into a dense list, so the threads
+// that walk a run are the first n_heads threads of the CTA - full warps instead of ~4 active lanes per warp (the
+// thread-per-signature version spent 200 us of issue slots on idle lanes).  Heads walk their run twice in shared
+// memory: count, then write after a block-aggregated slot reservation (two atomics per CTA).
+static __global__ void __launch_bounds__(MERGE_THREADS)
 k_shard_merge(const vsv_sig* __restrict__ s, ShardState* st, Caps cap, const uint8_t* __restrict__ in_bed,
               vsv_sig* __restrict__ rows_del, vsv_sig* __restrict__ rows_ins) {
-  __shared__ unsigned int s_wd[8], s_wi[8];
+  __shared__ int4 s_a[MERGE_THREADS + MERGE_HALO + 1];
+  __shared__ int32_t s_head[MERGE_THREADS];
+  __shared__ unsigned int s_wd[MERGE_THREADS / 32], s_wi[MERGE_THREADS / 32], s_wh[MERGE_THREADS / 32];
   __shared__ unsigned long long s_base[2];
+  __shared__ unsigned int s_nhead;
   const int64_t n = min((int64_t)st->nout[1], cap.c);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  for (int64_t base = (int64_t)blockIdx.x * blockDim.x; base < n; base += (int64_t)gridDim.x * blockDim.x) {
+  for (int64_t base = (int64_t)blockIdx.x * MERGE_THREADS; base < n; base += (int64_t)gridDim.x * MERGE_THREADS) {
+    SigWindow W;
+    W.s_a = s_a; W.g = s;
+    W.lo = max(base - 1, (int64_t)0);
+    W.hi = min(base + MERGE_THREADS + MERGE_HALO, n);
+    for (int64_t k = W.lo + threadIdx.x; k < W.hi; k += MERGE_THREADS) s_a[k - W.lo] = __ldg(reinterpret_cast<const int4*>(s + k));
+    __syncthreads();
+    // ---- compact the heads of this tile -----------------------------------------------------------------
     const int64_t i = base + threadIdx.x;
-    unsigned int cd = 0, ci = 0;
-    int64_t e = i;
+    bool head = false;
     if (i < n) {
-      const int32_t r = s[i].rec;
-      if ((i == 0 || s[i - 1].rec != r) && in_bed[r]) {
-        e = i + 1;
-        while (e < n && s[e].rec == r) ++e;
-        merge_walk_rows(s, i, e, [&](const vsv_sig&) { ++cd; }, [&](const vsv_sig&) { ++ci; });
-      }
+      const int32_t r = W.a(i).x;
+      head = (i == 0 || W.a(i - 1).x != r) && in_bed[r];
     }
-    // block exclusive scan of (cd, ci)
+    const unsigned int hm = __ballot_sync(0xffffffffu, head);
+    if (lane == 0) s_wh[warp] = __popc(hm);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      unsigned int t = 0;
+      for (int w = 0; w < MERGE_THREADS / 32; ++w) { const unsigned int c = s_wh[w]; s_wh[w] = t; t += c; }
+      s_nhead = t;
+    }
+    __syncthreads();
+    if (head) s_head[s_wh[warp] + __popc(hm & ((1u << lane) - 1u))] = (int32_t)threadIdx.x;
+    __syncthreads();
+    const unsigned int nh = s_nhead;
+    // ---- dense walk: thread t owns head number t ------------------------------------------------------------
+    unsigned int cd = 0, ci = 0;
+    int64_t h = 0, e = 0;
+    if (threadIdx.x < nh) {
+      h = base + s_head[threadIdx.x];
+      const int32_t r = W.a(h).x;
+      e = h + 1;
+      while (e < n && W.a(e).x == r) ++e;
+      merge_walk_rows<false>(W, h, e, [&](const vsv_sig&) { ++cd; }, [&](const vsv_sig&) { ++ci; });
+    }
     unsigned int xd = cd, xi = ci;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
@@ -342,7 +433,7 @@ k_shard_merge(const vsv_sig* __restrict__ s, ShardState* st, Caps cap, const uin
     __syncthreads();
     if (threadIdx.x == 0) {
       unsigned int td = 0, ti = 0;
-      for (int w = 0; w < 8; ++w) { const unsigned int a = s_wd[w], b = s_wi[w]; s_wd[w] = td; s_wi[w] = ti; td += a; ti += b; }
+      for (int w = 0; w < MERGE_THREADS / 32; ++w) { const unsigned int a = s_wd[w], b = s_wi[w]; s_wd[w] = td; s_wi[w] = ti; td += a; ti += b; }
       s_base[0] = td ? atomicAdd(&st->n_del, (unsigned long long)td) : 0ull;
       s_base[1] = ti ? atomicAdd(&st->n_ins, (unsigned long long)ti) : 0ull;
     }
@@ -350,9 +441,9 @@ k_shard_merge(const vsv_sig* __restrict__ s, ShardState* st, Caps cap, const uin
     if (cd | ci) {
       int64_t od = (int64_t)s_base[0] + s_wd[warp] + (xd - cd), oi = (int64_t)s_base[1] + s_wi[warp] + (xi - ci);
       bool ovd = false, ovi = false;
-      merge_walk_rows(s, i, e,
-                      [&](const vsv_sig& v) { if (od < cap.d) put_sig(rows_del + od, v); else ovd = true; ++od; },
-                      [&](const vsv_sig& v) { if (oi < cap.i) put_sig(rows_ins + oi, v); else ovi = true; ++oi; });
+      merge_walk_rows<true>(W, h, e,
+                            [&](const vsv_sig& v) { if (od < cap.d) put_sig(rows_del + od, v); else ovd = true; ++od; },
+                            [&](const vsv_sig& v) { if (oi < cap.i) put_sig(rows_ins + oi, v); else ovi = true; ++oi; });
       if (ovd) atomicOr(&st->overflow, (unsigned)VSV_OVF_DEL);
       if (ovi) atomicOr(&st->overflow, (unsigned)VSV_OVF_INS);
     }
@@ -574,44 +665,69 @@ k_shard_group(ShardState* st, Caps cap, Sorted S, GroupIn G, const uint8_t* __re
   if (threadIdx.x == 0) s_tile = atomicAdd(&st->ticket[tb], 1u);
   __syncthreads();
   const unsigned int tile = s_tile;
-  const int64_t i = (int64_t)tile * GROUP_THREADS + threadIdx.x;
+  const int64_t i0 = (int64_t)tile * GROUP_TILE + (int64_t)threadIdx.x * GROUP_ITEMS;   // GROUP_ITEMS consecutive rows per thread
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  int32_t p = 0, l = 0;
-  bool head = false;
-  int2 v = make_int2(0, INT32_MIN);
-  if (i < n) {
-    p = pos[i]; l = len[i];
-    head = (i == 0 || pos[i - 1] != p || len[i - 1] != l) && l >= G.min_len[tb];
-    v.x = head ? 1 : 0;
-    v.y = (int32_t)min((int64_t)p + l, (int64_t)INT32_MAX);
-  }
   const SumMax op;
-  int2 inc = v;
+  const int2 ident = make_int2(0, INT32_MIN);
+  int32_t p[GROUP_ITEMS], l[GROUP_ITEMS];
+  int2 v[GROUP_ITEMS];
+  int32_t pp = 0, pl = 0;
+  bool have_prev = false;
+  if (i0 > 0 && i0 < n) { pp = pos[i0 - 1]; pl = len[i0 - 1]; have_prev = true; }
+  int2 agg = ident;
+#pragma unroll
+  for (int k = 0; k < GROUP_ITEMS; ++k) {
+    const int64_t i = i0 + k;
+    v[k] = ident;
+    p[k] = 0; l[k] = 0;
+    if (i < n) {
+      p[k] = pos[i]; l[k] = len[i];
+      const bool head = (!have_prev || pp != p[k] || pl != l[k]) && l[k] >= G.min_len[tb];
+      v[k] = make_int2(head ? 1 : 0, (int32_t)min((int64_t)p[k] + l[k], (int64_t)INT32_MAX));
+      pp = p[k]; pl = l[k]; have_prev = true;
+    }
+    agg = op(agg, v[k]);
+  }
+  int2 inc = agg;
 #pragma unroll
   for (int d = 1; d < 32; d <<= 1) {
     int2 u;
     u.x = __shfl_up_sync(0xffffffffu, inc.x, d); u.y = __shfl_up_sync(0xffffffffu, inc.y, d);
     if (lane >= d) inc = op(u, inc);
   }
+  int2 prevl;   // inclusive value of the previous lane == this lane's exclusive prefix inside the warp
+  prevl.x = __shfl_up_sync(0xffffffffu, inc.x, 1); prevl.y = __shfl_up_sync(0xffffffffu, inc.y, 1);
   if (lane == 31) s_w[warp] = inc;
   __syncthreads();
-  if (threadIdx.x == 0) {
-    int2 run = make_int2(0, INT32_MIN);
-    for (int w = 0; w < GROUP_THREADS / 32; ++w) { const int2 a = s_w[w]; s_w[w] = run; run = op(run, a); }
-    s_excl = lookback_exclusive(desc, tile, run, make_int2(0, INT32_MIN), op);
-    // the last tile that holds rows publishes the unique count
-    if (n > 0 && (int64_t)tile == (n - 1) / GROUP_THREADS) st->n_u[tb] = (unsigned long long)(s_excl.x + run.x);
+  if (warp == 0) {
+    int2 run = ident;
+    if (lane == 0) {
+      for (int w = 0; w < GROUP_THREADS / 32; ++w) { const int2 a = s_w[w]; s_w[w] = run; run = op(run, a); }
+    }
+    run.x = __shfl_sync(0xffffffffu, run.x, 0); run.y = __shfl_sync(0xffffffffu, run.y, 0);
+    const int2 ex = lookback_exclusive_warp(desc, tile, run, ident, op);
+    if (lane == 0) {
+      s_excl = ex;
+      // the last tile that holds rows publishes the unique count
+      if (n > 0 && (int64_t)tile == (n - 1) / GROUP_TILE) st->n_u[tb] = (unsigned long long)(ex.x + run.x);
+    }
   }
   __syncthreads();
-  if (i >= n) return;
-  const int2 pre = op(s_excl, s_w[warp]);
-  inc = op(pre, inc);
-  if (tb == 0) pmax_del[i] = inc.y;
-  if (head) {
-    int32_t c = 0;
-    for (int64_t e = i; e < n && pos[e] == p && len[e] == l; ++e) c += keep[e];
-    const int64_t u = (int64_t)inc.x - 1;
-    U.pos[tb][u] = p; U.len[tb][u] = l; U.cnt[tb][u] = c;
+  if (i0 >= n) return;
+  int2 run = op(s_excl, s_w[warp]);   // tiles before + warps before + lanes before
+  if (lane > 0) run = op(run, prevl);
+#pragma unroll
+  for (int k = 0; k < GROUP_ITEMS; ++k) {
+    const int64_t i = i0 + k;
+    if (i >= n) break;
+    run = op(run, v[k]);
+    if (tb == 0) pmax_del[i] = run.y;
+    if (v[k].x) {
+      int32_t c = 0;
+      for (int64_t e = i; e < n && pos[e] == p[k] && len[e] == l[k]; ++e) c += keep[e];
+      const int64_t u = (int64_t)run.x - 1;
+      U.pos[tb][u] = p[k]; U.len[tb][u] = l[k]; U.cnt[tb][u] = c;
+    }
   }
 }
 
@@ -627,71 +743,77 @@ struct CandOut {
   int64_t* cov;
   int32_t *sup, *lb, *ub;
 };
+// One WARP per candidate.  A candidate needs six binary searches (two window bounds in each of three tables); they run
+// on six lanes at the same time and are broadcast, then all 32 lanes stride over the windows.  (One 8-lane group doing
+// the searches one after the other was latency bound: 130 us for 3000 candidates.)
 static __global__ void __launch_bounds__(256)
 k_cand_joins(const ShardState* st, Caps cap, Sorted S, Unique U, const uint8_t* __restrict__ keep_del,
              const uint8_t* __restrict__ keep_ins, const int32_t* __restrict__ pmax_del, const int32_t* __restrict__ cpos,
              const int32_t* __restrict__ clen, const int32_t* __restrict__ ctype, int64_t n_cand, JoinParams jp,
              CandOut O) {
-  const int64_t k = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / JOIN_GROUP;
-  const int g = threadIdx.x % JOIN_GROUP;
-  const unsigned gmask = 0xFFu << ((threadIdx.x & 31) / JOIN_GROUP * JOIN_GROUP);
-  if (k >= n_cand) return;
+  const int64_t k = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (k >= n_cand) return;   // whole warps exit together
   const Tables T = tables_of(st, cap);
   const int64_t p = cpos[k];
   const int32_t cl = clen[k];
   const int tb = ctype[k] == VSV_INS ? 1 : 0;
+  const int64_t nu = min((int64_t)st->n_u[tb], tb == 0 ? cap.d : cap.i);
+  const double sv = (double)cl;
+  const double shift = fmax(sv * jp.max_shift_ratio, jp.min_shift);
+  const int64_t cov_lb = p - jp.cov_flank, cov_rb = (tb == 1 ? p : p + (int64_t)cl) + jp.cov_flank;
+  const int32_t lo32 = (int32_t)max(cov_lb, (int64_t)INT32_MIN), hi32 = (int32_t)min(cov_rb, (int64_t)INT32_MAX);
+  int64_t r = 0;
+  switch (lane) {
+    case 0: if (jp.what & VSV_JOIN_FP) r = lower_bound_i32(S.r_pos, 0, T.n_r, (int32_t)max(p - jp.fp_max_shift, (int64_t)INT32_MIN)); break;
+    case 1: if (jp.what & VSV_JOIN_FP) r = upper_bound_i32(S.r_pos, 0, T.n_r, (int32_t)min(p + jp.fp_max_shift, (int64_t)INT32_MAX)); break;
+    case 2: if (jp.what & VSV_JOIN_COV) r = tb == 1 ? lower_bound_i32(S.t_pos[1], 0, T.n_i, lo32) : lower_bound_i32(pmax_del, 0, T.n_d, lo32); break;
+    case 3: if (jp.what & VSV_JOIN_COV) r = tb == 1 ? upper_bound_i32(S.t_pos[1], 0, T.n_i, hi32) : upper_bound_i32(S.t_pos[0], 0, T.n_d, hi32); break;
+    case 4: if (jp.what & VSV_JOIN_SUPPORT) r = lower_bound_f64(U.pos[tb], 0, nu, (double)p - shift); break;
+    case 5: if (jp.what & VSV_JOIN_SUPPORT) r = upper_bound_f64(U.pos[tb], 0, nu, (double)p + shift); break;
+    default: break;
+  }
+  const int64_t fa = __shfl_sync(0xffffffffu, r, 0), fb = __shfl_sync(0xffffffffu, r, 1);
+  const int64_t ca = __shfl_sync(0xffffffffu, r, 2), cb = __shfl_sync(0xffffffffu, r, 3);
+  const int64_t sa = __shfl_sync(0xffffffffu, r, 4), sb = __shfl_sync(0xffffffffu, r, 5);
   if (jp.what & VSV_JOIN_FP) {      // eval_sig (FPF:106-123): any signature type counts
     int32_t s = 0;
     if (cl > jp.fp_max_comp) {
-      s = (g == 0) ? 60 : 0;
+      s = (lane == 0) ? 60 : 0;
     } else {
-      const int64_t a = lower_bound_i32(S.r_pos, 0, T.n_r, (int32_t)max(p - jp.fp_max_shift, (int64_t)INT32_MIN));
-      const int64_t b = upper_bound_i32(S.r_pos, a, T.n_r, (int32_t)min(p + jp.fp_max_shift, (int64_t)INT32_MAX));
-      for (int64_t i = a + g; i < b; i += JOIN_GROUP) {
+      for (int64_t i = fa + lane; i < fb; i += 32) {
         const int32_t sl = __ldg(S.r_len + i);
         const int32_t mx = max(cl, sl);
         if (mx != 0 && 2 * (int64_t)min(cl, sl) >= mx) ++s;
       }
     }
-#pragma unroll
-    for (int d = JOIN_GROUP / 2; d >= 1; d >>= 1) s += __shfl_xor_sync(gmask, s, d);
-    if (g == 0) O.fp[k] = s;
+    s = __reduce_add_sync(0xffffffffu, s);
+    if (lane == 0) O.fp[k] = s;
   }
   if (jp.what & VSV_JOIN_COV) {
     long long s = 0;
     if (tb == 1) {                  // calc_ins_call_cov (CSS:81-125)
-      const int64_t a = lower_bound_i32(S.t_pos[1], 0, T.n_i, (int32_t)max(p - jp.cov_flank, (int64_t)INT32_MIN));
-      const int64_t b = upper_bound_i32(S.t_pos[1], a, T.n_i, (int32_t)min(p + jp.cov_flank, (int64_t)INT32_MAX));
-      for (int64_t i = a + g; i < b; i += JOIN_GROUP)
+      for (int64_t i = ca + lane; i < cb; i += 32)
         if (keep_ins[i]) s += __ldg(S.t_len[1] + i);
-    } else {                        // calc_del_call_cov (CSS:138-253): closed-interval overlap with the flanked call
-      const int64_t lb = p - jp.cov_flank, rb = p + (int64_t)cl + jp.cov_flank;
-      const int64_t hi = upper_bound_i32(S.t_pos[0], 0, T.n_d, (int32_t)min(rb, (int64_t)INT32_MAX));
-      const int64_t lo = lower_bound_i32(pmax_del, 0, hi, (int32_t)max(lb, (int64_t)INT32_MIN));
-      for (int64_t i = lo + g; i < hi; i += JOIN_GROUP) {
+    } else {                        // calc_del_call_cov (CSS:138-253): closed-interval overlap with the flanked call; rows before
+      for (int64_t i = ca + lane; i < cb; i += 32) {   // `ca` (running max of the ends < lb) cannot reach the window
         const int32_t sl = __ldg(S.t_len[0] + i);
-        if (keep_del[i] && (int64_t)__ldg(S.t_pos[0] + i) + sl >= lb) s -= sl;
+        if (keep_del[i] && (int64_t)__ldg(S.t_pos[0] + i) + sl >= cov_lb) s -= sl;
       }
     }
 #pragma unroll
-    for (int d = JOIN_GROUP / 2; d >= 1; d >>= 1) s += __shfl_xor_sync(gmask, s, d);
-    if (g == 0) O.cov[k] = s;
+    for (int d = 16; d >= 1; d >>= 1) s += __shfl_xor_sync(0xffffffffu, s, d);
+    if (lane == 0) O.cov[k] = s;
   }
   if (jp.what & VSV_JOIN_SUPPORT) {  // match_varlist_siglist window sum (GTD:92-137)
-    const int64_t nu = min((int64_t)st->n_u[tb], tb == 0 ? cap.d : cap.i);
-    const double sv = (double)cl;
     const double max_size = sv / jp.min_size_sim, min_size = sv * jp.min_size_sim;
-    const double shift = fmax(sv * jp.max_shift_ratio, jp.min_shift);
-    const int64_t a = lower_bound_f64(U.pos[tb], 0, nu, (double)p - shift);
-    const int64_t b = upper_bound_f64(U.pos[tb], a, nu, (double)p + shift);
     int32_t s = 0;
-    for (int64_t i = a + g; i < b; i += JOIN_GROUP) {
+    for (int64_t i = sa + lane; i < sb; i += 32) {
       const double L = (double)__ldg(U.len[tb] + i);
       if (min_size <= L && L <= max_size) s += __ldg(U.cnt[tb] + i);
     }
-#pragma unroll
-    for (int d = JOIN_GROUP / 2; d >= 1; d >>= 1) s += __shfl_xor_sync(gmask, s, d);
-    if (g == 0) { O.sup[k] = s; O.lb[k] = (int32_t)a; O.ub[k] = (int32_t)b; }
+    s = __reduce_add_sync(0xffffffffu, s);
+    if (lane == 0) { O.sup[k] = s; O.lb[k] = (int32_t)sa; O.ub[k] = (int32_t)max(sb, sa); }
   }
 }
 
@@ -732,19 +854,22 @@ k_cand_chain(const ShardState* st, Caps cap, Unique U, const int32_t* __restrict
   }
   if (lane == 31) s_w[warp] = inc;
   __syncthreads();
-  if (threadIdx.x == 0) {
+  // exclusive prefix of this candidate inside the warp = inclusive of the previous lane
+  int2 prev;
+  prev.x = __shfl_up_sync(0xffffffffu, inc.x, 1); prev.y = __shfl_up_sync(0xffffffffu, inc.y, 1);
+  if (warp == 0) {
     int2 run = make_int2(-1, -1);
-    for (int w = 0; w < CHAIN_THREADS / 32; ++w) { const int2 a = s_w[w]; s_w[w] = run; run = op(run, a); }
-    s_excl = lookback_exclusive(desc, tile, run, make_int2(-1, -1), op);
-    if (n_cand > 0 && (int64_t)tile == (n_cand - 1) / CHAIN_THREADS && last_out) {
-      const int2 fin = op(last_in, op(s_excl, run));
-      *last_out = fin;
+    if (lane == 0) {
+      for (int w = 0; w < CHAIN_THREADS / 32; ++w) { const int2 a = s_w[w]; s_w[w] = run; run = op(run, a); }
+    }
+    run.x = __shfl_sync(0xffffffffu, run.x, 0); run.y = __shfl_sync(0xffffffffu, run.y, 0);
+    const int2 ex = lookback_exclusive_warp(desc, tile, run, make_int2(-1, -1), op);
+    if (lane == 0) {
+      s_excl = ex;
+      if (n_cand > 0 && (int64_t)tile == (n_cand - 1) / CHAIN_THREADS && last_out) *last_out = op(last_in, op(ex, run));
     }
   }
   __syncthreads();
-  // exclusive prefix of this candidate = inclusive of the previous one
-  int2 prev;
-  prev.x = __shfl_up_sync(0xffffffffu, inc.x, 1); prev.y = __shfl_up_sync(0xffffffffu, inc.y, 1);
   if (k >= n_cand) return;
   int2 pre = op(s_excl, s_w[warp]);
   if (lane > 0) pre = op(pre, prev);
@@ -759,18 +884,66 @@ k_cand_chain(const ShardState* st, Caps cap, Unique U, const int32_t* __restrict
   }
 }
 
+// 8 lanes per candidate: the three binary searches of each of the (up to two) windows run on six lanes at once, the
+// short scan of the reads that start inside a window is strided over the group (closed form: vsv_depth.cuh).
 static __global__ void __launch_bounds__(256)
 k_cand_genotype(const int32_t* __restrict__ rstart, const int32_t* __restrict__ rend, const int32_t* __restrict__ send,
                 int64_t n_reads, const int32_t* __restrict__ pos, const int32_t* __restrict__ svlen,
                 const int32_t* __restrict__ type, const int32_t* __restrict__ call_gt, const int32_t* __restrict__ nsup,
                 int64_t n, GtParams gp, int32_t* __restrict__ depth2, double* __restrict__ ratio,
                 int32_t* __restrict__ new_gt) {
-  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  int32_t d2, out;
-  double r;
-  genotype_one(rstart, rend, send, n_reads, pos[i], svlen[i], type[i], call_gt ? call_gt[i] : 2, nsup[i], gp, d2, r, out);
-  depth2[i] = d2; ratio[i] = r; new_gt[i] = out;
+  const int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 3;
+  const int g = threadIdx.x & 7;
+  const int gbase = (threadIdx.x & 31) & ~7;
+  const unsigned gmask = 0xFFu << gbase;
+  if (i >= n) return;   // whole groups exit together
+  const int32_t p = pos[i], L = svlen[i], tp = type[i];
+  int32_t S[2], E[2];
+  int nw = 1;
+  if (tp == VSV_INS) { S[0] = p - gp.ins_flank; E[0] = p + gp.ins_flank; S[1] = 0; E[1] = 0; }
+  else if (L <= gp.del_large) { S[0] = p; E[0] = p + L; S[1] = 0; E[1] = 0; }
+  else { S[0] = p - gp.del_off; E[0] = S[0] + gp.del_win; S[1] = p + L + gp.del_off; E[1] = S[1] + gp.del_win; nw = 2; }
+  // lane g: window g / 3, search g % 3 (0: #start < S, 1: #end <= E, 2: first start > E)
+  int64_t r = 0;
+  {
+    const int w = g / 3, q = g % 3;
+    if (w < nw && g < 6) {
+      if (q == 0) r = lower_bound_i32(rstart, 0, n_reads, S[w]);
+      else if (q == 1) r = upper_bound_i32(send, 0, n_reads, E[w]);
+      else r = upper_bound_i32(rstart, 0, n_reads, E[w]);
+    }
+  }
+  int32_t d[2] = {0, 0};
+  for (int w = 0; w < 2; ++w) {
+    const int64_t a = __shfl_sync(gmask, r, gbase + 3 * w), ue = __shfl_sync(gmask, r, gbase + 3 * w + 1),
+                  b = __shfl_sync(gmask, r, gbase + 3 * w + 2);
+    int32_t c = 0;
+    if (w < nw) {
+      for (int64_t j = a + g; j < b; j += 8) c += (__ldg(rend + j) <= E[w]) ? 1 : 0;   // empty when E < S (b <= a)
+    }
+#pragma unroll
+    for (int s = 4; s >= 1; s >>= 1) c += __shfl_xor_sync(gmask, c, s);
+    d[w] = w < nw ? (int32_t)(a - ue + c) : 0;
+  }
+  if (g != 0) return;
+  const int32_t d2 = nw == 2 ? d[0] + d[1] : 2 * d[0];
+  const int32_t ns = nsup[i];
+  const double depth = (double)d2 / 2.0;  // GTD:168
+  double rt;
+  if (tp == VSV_DEL) rt = (d2 == 0) ? 1.0 : (double)ns / depth;                                     // GTD:213-217
+  else rt = (d2 == 0) ? (ns == 0 ? CUDART_NAN : CUDART_INF) : (double)ns / depth;                   // GTI:228
+  const int32_t gt = call_gt ? call_gt[i] : 2;
+  int32_t out = gt;
+  if (gt == 0 || gt == 1) {
+    const double* t4 = tp == VSV_DEL ? gp.thr_del : gp.thr_ins;
+    const bool large = L > gp.del_large;
+    const double t = gt == 1 ? (large ? t4[0] : t4[1]) : (large ? t4[2] : t4[3]);
+    if (!isnan(t)) {  // GTD:302-318
+      if (rt > t) out = 1;
+      else if (rt <= t) out = 0;
+    }
+  }
+  depth2[i] = d2; ratio[i] = rt; new_gt[i] = out;
 }
 
 // ==================================================================================================
@@ -1025,7 +1198,7 @@ static int enqueue_group(vsv_shard* s) {
   VSV_CUDA(ctx, cudaMemsetAsync(s->desc.p, 0, desc_bytes, ctx->stream));
   const unsigned gk = (unsigned)std::max<int64_t>(1, std::min<int64_t>(vsv_cdiv(cap_max, 256), (int64_t)ctx->sm_count * 8));
   VSV_LAUNCH(ctx, k_shard_keep, dim3(gk, 2), 256, 0, st, s->cap, S, G, (uint8_t*)s->keep[0].p, (uint8_t*)s->keep[1].p, (int2*)s->dup_list.p);
-  const unsigned gt = (unsigned)std::max<int64_t>(1, vsv_cdiv(cap_max, GROUP_THREADS));
+  const unsigned gt = (unsigned)std::max<int64_t>(1, vsv_cdiv(cap_max, GROUP_TILE));
   VSV_LAUNCH(ctx, k_shard_group, dim3(gt, 2), GROUP_THREADS, 0, st, s->cap, S, G, (const uint8_t*)s->keep[0].p, (const uint8_t*)s->keep[1].p,
              (LbDesc*)s->desc.p, (LbDesc*)s->desc.p + s->desc_tiles[0], unique_of(s), (int32_t*)s->pmax.p);
   VSV_CUDA(ctx, cudaMemcpyAsync(s->h_state, st, sizeof(ShardState), cudaMemcpyDeviceToHost, ctx->stream));
@@ -1089,7 +1262,7 @@ extern "C" int vsv_shard_scan(vsv_shard* s) {
     VSV_TRY(dbuf_ensure(ctx, s->u_pos[t], (size_t)capt[t] * 4));
     VSV_TRY(dbuf_ensure(ctx, s->u_len[t], (size_t)capt[t] * 4));
     VSV_TRY(dbuf_ensure(ctx, s->u_cnt[t], (size_t)capt[t] * 4));
-    s->desc_tiles[t] = vsv_cdiv(std::max(cap.d, cap.i), GROUP_THREADS) + 1;
+    s->desc_tiles[t] = vsv_cdiv(std::max(cap.d, cap.i), GROUP_TILE) + 1;
   }
   VSV_TRY(dbuf_ensure(ctx, s->pmax, (size_t)cap.d * 4));
   VSV_TRY(dbuf_ensure(ctx, s->send, (size_t)n_rec * 4));
@@ -1166,7 +1339,7 @@ extern "C" int vsv_shard_scan(vsv_shard* s) {
                  (const uint8_t*)s->in_bed.p, P.cute_min_mapq, P.cute_min_read_len, P.sa_sv_size, P.sa_max_size, P.sa_max_parts, st,
                  (vsv_sig*)s->rows_del.p, cap.d, (vsv_sig*)s->rows_ins.p, cap.i);
     const unsigned gm = (unsigned)std::max<int64_t>(1, std::min<int64_t>(vsv_cdiv(cap.c, 256), (int64_t)ctx->sm_count * 8));
-    VSV_LAUNCH(ctx, k_shard_merge, gm, 256, 0, (const vsv_sig*)s->sig_cute.p, st, cap, (const uint8_t*)s->in_bed.p, (vsv_sig*)s->rows_del.p,
+    VSV_LAUNCH(ctx, k_shard_merge, gm, MERGE_THREADS, 0, (const vsv_sig*)s->sig_cute.p, st, cap, (const uint8_t*)s->in_bed.p, (vsv_sig*)s->rows_del.p,
                (vsv_sig*)s->rows_ins.p);
   }
   const unsigned gk = (unsigned)std::max<int64_t>(1, std::min<int64_t>(vsv_cdiv(cap_total, 256), (int64_t)ctx->sm_count * 16));
@@ -1347,7 +1520,7 @@ extern "C" int vsv_shard_candidates(vsv_shard* s, int what, const int32_t* cand_
     jp.min_size_sim = P.gt_min_size_sim; jp.max_shift_ratio = P.gt_max_shift_ratio; jp.min_shift = P.gt_min_shift;
     CandOut O;
     O.fp = d_fp; O.cov = d_cov; O.sup = d_sup; O.lb = d_lb; O.ub = d_ub;
-    VSV_LAUNCH(ctx, k_cand_joins, (unsigned)vsv_cdiv(n_cand * JOIN_GROUP, 256), 256, 0, (const ShardState*)st, s->cap, S, U,
+    VSV_LAUNCH(ctx, k_cand_joins, (unsigned)vsv_cdiv(n_cand * 32, 256), 256, 0, (const ShardState*)st, s->cap, S, U,
                (const uint8_t*)s->keep[0].p, (const uint8_t*)s->keep[1].p, (const int32_t*)s->pmax.p, cp, cl, ct, n_cand, jp, O);
   }
   int2* d_last = nullptr;
@@ -1365,7 +1538,7 @@ extern "C" int vsv_shard_candidates(vsv_shard* s, int what, const int32_t* cand_
   }
   if (what & VSV_JOIN_GENOTYPE) {
     const GtParams gp = gt_params_of(P);
-    VSV_LAUNCH(ctx, k_cand_genotype, (unsigned)vsv_cdiv(n_cand, 256), 256, 0, s->R.pos, (const int32_t*)s->ref_end.p, (const int32_t*)s->send.p,
+    VSV_LAUNCH(ctx, k_cand_genotype, (unsigned)vsv_cdiv(n_cand * 8, 256), 256, 0, s->R.pos, (const int32_t*)s->ref_end.p, (const int32_t*)s->send.p,
                s->R.n_rec, cp, cl, ct, cg, (const int32_t*)d_sup, n_cand, gp, d_d2, d_ratio, d_gt);
   }
   VSV_TRY(vsv_t1(ctx));
