@@ -363,11 +363,34 @@ def gold_sa():
     return cases
 
 
+def gold_clr_gate():
+    """ECS_C:53-70,425-427: ins_pct / var_dist of the reference on contig CIGARs around both thresholds (0.13, 200), incl. exact
+    ties (13/100, 200.0) and contigs the gate rejects."""
+    ns = H.load_defs("extract_contig_signature_CLR.py")
+    rng = random.Random(99)
+    cases = []
+    fixed = [[(0, 87), (1, 13)], [(0, 870), (1, 130), (0, 1)], [(0, 200)], [(0, 100), (2, 5), (0, 300)], [(0, 199), (1, 40), (0, 200)],
+             [(5, 10), (0, 50), (1, 30), (0, 50), (4, 7)], [(0, 1), (1, 1)], [(0, 400), (1, 200)]]
+    for cg in fixed + [None] * 60:
+        if cg is None:
+            k = rng.randint(1, 40)
+            mrun = rng.choice([20, 60, 150, 200, 260, 900])
+            cg = []
+            for _ in range(k):
+                cg.append((0, max(1, int(rng.gauss(mrun, mrun / 4)))))
+                u = rng.random()
+                cg.append((1, rng.randint(1, mrun // 2 + 2)) if u < 0.75 else (2, rng.randint(1, 60)))
+            cg.append((0, rng.randint(1, 400)))
+        ip, vd = ns["ins_pct"](cg), ns["var_dist"](cg)
+        cases.append(dict(cigar=[list(x) for x in cg], ins_pct=ip, var_dist=vd, gate=bool((ip <= 0.13) or (vd >= 200))))
+    return cases
+
+
 def main():
     assert H.available(), "reference not mounted; goldens can only be regenerated in the build container"
     jobs = dict(contig_scan=gold_contig_scan, reads_scan=gold_reads_scan, parse_read=gold_parse_read,
                 split_pair=gold_split_pair, cluster_pair=gold_cluster_pair, window=gold_window,
-                genotype=gold_genotype, sa=gold_sa)
+                genotype=gold_genotype, sa=gold_sa, clr_gate=gold_clr_gate)
     only = sys.argv[1:]
     for k, fn in jobs.items():
         if only and k not in only:

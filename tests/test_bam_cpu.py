@@ -245,3 +245,35 @@ def test_stale_index_falls_back_to_the_linear_scan(tmp_path):
     idx[starts[6]: starts[6] + 8] = idx[starts[1]: starts[1] + 8]
     open(bam + ".bai", "wb").write(bytes(idx))
     assert _columns(L.BamFile(bam, ref="chr7"), "chr7") == want
+
+
+def test_htsbox_written_bam(tmp_path):
+    """BAM + BAI written by the reference's vendored htsbox (htslib lite-r346), not by tests/bamio.py: the native feeder
+    must give the same columns as the SAM-text loader - whole file, and one reference at a time through htslib's own index
+    (real bins, chunks and linear index; multi-member BGZF as htslib cuts it)."""
+    from volcanosv_b200 import operators as OP
+    hb = os.path.join(HERE, "golden", "htsbox")
+    wgs_sam = os.path.join(HERE, "golden", "e2e_wgs", "input", "reads.sam.gz")
+    a = OP.AlignmentSource(wgs_sam)
+    b = OP.AlignmentSource(os.path.join(hb, "reads_wgs.bam"))
+    assert a.references() == b.references() and len(a.references()) == 22
+    for chrom, _ in a.references():                       # b.records() opens one reference through the .bai each time
+        A, B = a.records(chrom), b.records(chrom)
+        assert A.n == B.n and A.n > 0
+        for k in ("ops", "op_off", "pos", "mapq", "flag", "qlen", "is_rev", "first_op", "last_op"):
+            assert np.array_equal(getattr(A, k), getattr(B, k)), (chrom, k)
+        assert list(A.qname) == list(B.qname) and A.sa == B.sa
+        assert all(A.seq[i] == B.seq[i] for i in range(0, A.n, 7))
+    full = L.BamFile(os.path.join(hb, "reads_wgs.bam"), n_threads=2)
+    one = L.BamFile(os.path.join(hb, "reads_wgs.bam"), n_threads=2, ref="chr13")
+    assert _columns(one, "chr13") == _columns(full, "chr13")
+    # without the index: linear scan, stops after the reference
+    shutil_bam = str(tmp_path / "noidx.bam")
+    import shutil
+    shutil.copy(os.path.join(hb, "reads_wgs.bam"), shutil_bam)
+    assert _columns(L.BamFile(shutil_bam, ref="chr13"), "chr13") == _columns(full, "chr13")
+    # contigs with real sequences (4-bit SEQ decode incl. odd lengths)
+    ca = OP.AlignmentSource(os.path.join(E2E, "contigs.sam.gz")).records("chr1")
+    cb = OP.AlignmentSource(os.path.join(hb, "contigs_chr1.bam")).records("chr1")
+    assert ca.n == cb.n and np.array_equal(ca.ops, cb.ops) and list(ca.qname) == list(cb.qname)
+    assert all(ca.seq[i] == cb.seq[i] for i in range(ca.n))

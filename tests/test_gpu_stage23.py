@@ -1,6 +1,7 @@
 """CUDA stage 2 (split pairs, sort, cluster, pair, window joins) and stage 3 (group,
 support, depth, genotype) against the reference-generated goldens and the oracle."""
 import math
+import os
 
 import numpy as np
 import pytest
@@ -300,7 +301,31 @@ def test_edit_distance_batch(ctx):
     assert int(got[0]) == 3 and int(got[1]) == 4 and int(got[3]) == 0
     for (i, j), g in zip(pairs, got):
         assert int(g) == O.edit_distance(strs[i], strs[j]), (len(strs[i]), len(strs[j]))
+    from oracle import edlib_ref as E
+    if E.available():        # the reference's own vendored edlib, built into oracle/_ref by oracle/Makefile (travels with the snapshot)
+        for (i, j), g in zip(pairs, got):
+            assert int(g) == E.distance(strs[i], strs[j])
     with pytest.raises(V.VsvError):
         ctx.edit_distance_batch(["ABCDEFGHIJKLMNOPQRS", "ABCDEFGHIJKLMNOPQRSTUV"], [0], [1])
     assert int(ctx.edit_distance_batch(["ABCDEFGHIJKLMNOPQRS", "ABC"], [0], [1])[0]) == 16   # only the shorter string is limited
     assert len(ctx.edit_distance_batch(["A"], [], [])) == 0
+
+
+def test_clr_contig_gate_golden(ctx):
+    """a2: the CLR gate (ECS_C:53-70,425-427) from the device class sums against the reference's own ins_pct / var_dist
+    (tests/golden/clr_gate.json, generated by executing the reference functions), incl. the exact ties 13/100 and 200.0 and
+    contigs the gate REJECTS."""
+    import json
+    from volcanosv_b200 import operators as OP
+    cases = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "clr_gate.json")))
+    ops, off = [], [0]
+    for c in cases:
+        ops += [(ln << 4) | op for op, ln in c["cigar"]]
+        off.append(len(ops))
+    ops, off = np.asarray(ops, np.uint32), np.asarray(off, np.int64)
+    i_sum, m_sum, m_cnt = ctx.cigar_class_sums(ops, off)
+    for k, c in enumerate(cases):
+        assert i_sum[k] / (m_sum[k] + i_sum[k]) == c["ins_pct"] and m_sum[k] / m_cnt[k] == c["var_dist"], k
+    gate = OP.clr_gate(ctx, ops, off)
+    assert gate.tolist() == [c["gate"] for c in cases]
+    assert 10 <= sum(1 for c in cases if not c["gate"]) <= len(cases) - 10

@@ -91,7 +91,7 @@ struct RecView {
   int32_t ref_id, pos, l_seq;
   uint32_t l_name, mapq, n_cigar, flag;
   const char* name;
-  const uint32_t* cigar;     // may point into the CG tag
+  const uint8_t* cigar;      // n_cigar little-endian u32 words, NOT 4-byte aligned (may point into the CG tag): read with memcpy
   const uint8_t* seq;
   const uint8_t* aux;
   const uint8_t* end;
@@ -113,7 +113,7 @@ bool view(const uint8_t* body, uint32_t size, RecView* v, bool has_qual = false)
   const uint8_t* p = body + 32;
   v->name = reinterpret_cast<const char*>(p);
   p += v->l_name;
-  v->cigar = reinterpret_cast<const uint32_t*>(p);
+  v->cigar = p;
   if ((size_t)(v->end - body) < 32 + (size_t)v->l_name + 4 * (size_t)v->n_cigar) return false;
   p += 4 * (size_t)v->n_cigar;
   v->seq = p;
@@ -124,7 +124,7 @@ bool view(const uint8_t* body, uint32_t size, RecView* v, bool has_qual = false)
   if (v->n_cigar == 2) {
     uint32_t c0, c1;
     memcpy(&c0, v->cigar, 4);
-    memcpy(&c1, v->cigar + 1, 4);
+    memcpy(&c1, v->cigar + 4, 4);
     if ((c0 & 15u) == 4u && (int32_t)(c0 >> 4) == v->l_seq && (c1 & 15u) == 3u) {
       for (const uint8_t* a = v->aux; a + 4 <= v->end;) {
         const size_t sz = aux_size(a + 2, v->end);
@@ -132,7 +132,7 @@ bool view(const uint8_t* body, uint32_t size, RecView* v, bool has_qual = false)
         if (a[0] == 'C' && a[1] == 'G' && a[2] == 'B' && a[3] == 'I') {
           // aux_size has checked that the whole B array (8 + 4 * count bytes from `a`) lies inside the record
           v->n_cigar = rd32(a + 4);
-          v->cigar = reinterpret_cast<const uint32_t*>(a + 8);
+          v->cigar = a + 8;
           break;
         }
         a += 2 + sz;
@@ -619,7 +619,7 @@ extern "C" int vsv_bam_chrom_fill(vsv_bam* b, int tid, int32_t* pos, uint8_t* ma
       if (ops16) {
         for (uint32_t k = 0; k < v.n_cigar; ++k) {
           uint32_t w;
-          memcpy(&w, v.cigar + k, 4);
+          memcpy(&w, v.cigar + 4 * (size_t)k, 4);
           if (w < 0xFFF0u) {
             ops16[o + k] = (uint16_t)w;
           } else {  // len >= 4095: marker 0xFFF<<4|op + (index, full word) in the exception list (vsv_expand_ops16)
@@ -632,7 +632,7 @@ extern "C" int vsv_bam_chrom_fill(vsv_bam* b, int tid, int32_t* pos, uint8_t* ma
       if (ops8) {
         for (uint32_t k = 0; k < v.n_cigar; ++k) {
           uint32_t w;
-          memcpy(&w, v.cigar + k, 4);
+          memcpy(&w, v.cigar + 4 * (size_t)k, 4);
           const uint32_t code = w & 15u, len = w >> 4;
           static const uint32_t cnt[3] = {VSV_OPS8_M, VSV_OPS8_I, VSV_OPS8_D};
           static const uint32_t base[3] = {0, VSV_OPS8_M, VSV_OPS8_M + VSV_OPS8_I};

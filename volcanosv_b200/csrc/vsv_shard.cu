@@ -349,11 +349,14 @@ k_shard_sa(RecCols R, SaCols A, const int32_t* __restrict__ ref_end, const uint8
 #define MERGE_HALO 96
 // the first half (rec, type, pos, len) of raw signature k: from the CTA's shared-memory window when it is inside
 struct SigWindow {
-  const int4* s_a;       // rows [lo, hi) staged (first halves)
+  const int4 *s_a, *s_b;  // rows [lo, hi) staged: (rec, type, pos, len) and (q0, q1, first, count)
   int64_t lo, hi;
   const vsv_sig* g;
   __device__ __forceinline__ int4 a(int64_t k) const {
     return (k >= lo && k < hi) ? s_a[k - lo] : __ldg(reinterpret_cast<const int4*>(g + k));
+  }
+  __device__ __forceinline__ int4 b(int64_t k) const {
+    return (k >= lo && k < hi) ? s_b[k - lo] : __ldg(reinterpret_cast<const int4*>(g + k) + 1);
   }
 };
 template <bool FULL, typename FD, typename FI>
@@ -363,7 +366,7 @@ __device__ __forceinline__ void merge_walk_rows(const SigWindow& W, int64_t i0, 
   for (int64_t k = i0; k < i1; ++k) {
     const int4 a = W.a(k);
     int4 b = make_int4(0, 0, 0, 0);
-    if (FULL) b = __ldg(reinterpret_cast<const int4*>(W.g + k) + 1);
+    if (FULL) b = W.b(k);
     vsv_sig n;
     n.rec = a.x; n.type = a.y; n.pos = a.z; n.len = a.w; n.q0 = b.x; n.q1 = b.y; n.first = b.z; n.count = b.w;
     if (n.type == VSV_DEL) mstate_push(sd, n, (int32_t)k, VSV_MODE_CUTE, VSV_DEL, fd);
@@ -380,7 +383,7 @@ __device__ __forceinline__ void merge_walk_rows(const SigWindow& W, int64_t i0, 
 static __global__ void __launch_bounds__(MERGE_THREADS)
 k_shard_merge(const vsv_sig* __restrict__ s, ShardState* st, Caps cap, const uint8_t* __restrict__ in_bed,
               vsv_sig* __restrict__ rows_del, vsv_sig* __restrict__ rows_ins) {
-  __shared__ int4 s_a[MERGE_THREADS + MERGE_HALO + 1];
+  __shared__ int4 s_a[MERGE_THREADS + MERGE_HALO + 1], s_b[MERGE_THREADS + MERGE_HALO + 1];
   __shared__ int32_t s_head[MERGE_THREADS];
   __shared__ unsigned int s_wd[MERGE_THREADS / 32], s_wi[MERGE_THREADS / 32], s_wh[MERGE_THREADS / 32];
   __shared__ unsigned long long s_base[2];
@@ -389,10 +392,13 @@ k_shard_merge(const vsv_sig* __restrict__ s, ShardState* st, Caps cap, const uin
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   for (int64_t base = (int64_t)blockIdx.x * MERGE_THREADS; base < n; base += (int64_t)gridDim.x * MERGE_THREADS) {
     SigWindow W;
-    W.s_a = s_a; W.g = s;
+    W.s_a = s_a; W.s_b = s_b; W.g = s;
     W.lo = max(base - 1, (int64_t)0);
     W.hi = min(base + MERGE_THREADS + MERGE_HALO, n);
-    for (int64_t k = W.lo + threadIdx.x; k < W.hi; k += MERGE_THREADS) s_a[k - W.lo] = __ldg(reinterpret_cast<const int4*>(s + k));
+    for (int64_t k = W.lo + threadIdx.x; k < W.hi; k += MERGE_THREADS) {
+      s_a[k - W.lo] = __ldg(reinterpret_cast<const int4*>(s + k));
+      s_b[k - W.lo] = __ldg(reinterpret_cast<const int4*>(s + k) + 1);
+    }
     __syncthreads();
     // ---- compact the heads of this tile -----------------------------------------------------------------
     const int64_t i = base + threadIdx.x;
@@ -434,8 +440,11 @@ k_shard_merge(const vsv_sig* __restrict__ s, ShardState* st, Caps cap, const uin
     if (threadIdx.x == 0) {
       unsigned int td = 0, ti = 0;
       for (int w = 0; w < MERGE_THREADS / 32; ++w) { const unsigned int a = s_wd[w], b = s_wi[w]; s_wd[w] = td; s_wi[w] = ti; td += a; ti += b; }
-      s_base[0] = td ? atomicAdd(&st->n_del, (unsigned long long)td) : 0ull;
-      s_base[1] = ti ? atomicAdd(&st->n_ins, (unsigned long long)ti) : 0ull;
+      // both reservations in flight together (the results are consumed after the second is issued)
+      const unsigned long long bd = td ? atomicAdd(&st->n_del, (unsigned long long)td) : 0ull;
+      const unsigned long long bi = ti ? atomicAdd(&st->n_ins, (unsigned long long)ti) : 0ull;
+      s_base[0] = bd;
+      s_base[1] = bi;
     }
     __syncthreads();
     if (cd | ci) {

@@ -8,6 +8,7 @@ from __future__ import annotations
 
 import ctypes as C
 import os
+import sys
 from typing import Optional
 
 import numpy as np
@@ -220,8 +221,10 @@ class Context:
             self.h = None
 
     def __del__(self):
+        # at interpreter shutdown the CUDA runtime may already be unloading: leave the handle to the OS
         try:
-            self.close()
+            if not sys.is_finalizing():
+                self.close()
         except Exception:
             pass
 
@@ -500,7 +503,8 @@ class Shard:
 
     def __del__(self):
         try:
-            self.close()
+            if not sys.is_finalizing():
+                self.close()
         except Exception:  # noqa: BLE001
             pass
 

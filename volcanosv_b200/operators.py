@@ -48,6 +48,12 @@ FILTER_PARA = {
 }
 
 _ctx: Optional[L.Context] = None
+# The reference's intermediate files that are ROW DUMPS of the read-side tables (reads_signature/*.txt, cute_sig/*.sigs,
+# INS.sigs.gte30auto: 10^5 - 10^7 text rows per chromosome).  Off: the tables stay on the device, a one-line stub marks
+# the file, and everything downstream (which joins against the resident tables anyway) is unchanged.  The per-call
+# files (VCFs, CSV, TSVs) are always written.
+WRITE_ROW_DUMPS = True
+_STUB = "# volcanosv_b200: table kept on the device (row dumps off)\n"
 
 
 def context(device: Optional[int] = None) -> L.Context:
@@ -55,7 +61,23 @@ def context(device: Optional[int] = None) -> L.Context:
     global _ctx
     if _ctx is None:
         _ctx = L.Context(int(os.environ.get("LOCAL_RANK", "0")) if device is None else device)
+        import atexit
+        from . import resident as RS
+        atexit.register(_close_context)      # registered after resident's hook, so it runs first ... and closes the shards itself
+        RS  # noqa: B018
     return _ctx
+
+
+def _close_context():
+    global _ctx
+    from . import resident as RS
+    RS._at_exit()
+    if _ctx is not None:
+        try:
+            _ctx.close()
+        except Exception:  # noqa: BLE001
+            pass
+        _ctx = None
 
 
 # --------------------------------------------------------------------------- alignment input
@@ -89,6 +111,31 @@ class Records:
         self.first_op.append(packed[0] if packed else 0)
         self.last_op.append(packed[-1] if packed else 0)
 
+    @classmethod
+    def from_arrays(cls, batch: dict, names=None, seqs=None):
+        """Packed columns (ops u32, op_off i64, pos, mapq, flag, qlen [, name_id, next_same_name, sa_* columns]) -> Records.
+        names / seqs: optional sequences indexed by record (default: 'r<name_id>' / no SEQ)."""
+        R = cls()
+        R.n = len(batch["pos"])
+        R.ops, R.op_off, R.pos, R.mapq = batch["ops"], batch["op_off"], batch["pos"], batch["mapq"]
+        R.flag = np.asarray(batch["flag"]).astype(np.int32)
+        R.qlen = batch["qlen"]
+        R.is_rev = ((R.flag & 16) != 0).astype(np.uint8)
+        off = R.op_off
+        has = off[1:] > off[:-1]
+        last = max(len(R.ops) - 1, 0)
+        R.first_op = np.where(has, R.ops[np.minimum(off[:-1], last)] if len(R.ops) else 0, 0).astype(np.uint32)
+        R.last_op = np.where(has, R.ops[np.maximum(off[1:] - 1, 0)] if len(R.ops) else 0, 0).astype(np.uint32)
+        nid = batch.get("name_id")
+        R.name_key = None if nid is None else np.asarray(nid)
+        R.qname = names if names is not None else _IdNames(nid if nid is not None else np.arange(R.n))
+        R.seq = seqs if seqs is not None else _NoSeq(R.n)
+        R.sa = _NoSeq(R.n)
+        R.next_same_name = batch.get("next_same_name")
+        if "sa_rec" in batch:
+            R.sa_packed = {k[3:]: batch[k] for k in batch if k.startswith("sa_") and k != "sa_self_chrom"}
+        return R
+
     def finish(self):
         self.n = len(self.pos)
         self.ops = np.asarray(self.ops, dtype=np.uint32)
@@ -101,6 +148,33 @@ class Records:
         self.is_rev = ((self.flag & 16) != 0).astype(np.uint8)
         self.qlen = np.asarray([0 if s is None else len(s) for s in self.seq], dtype=np.int32)
         return self
+
+
+class _IdNames:
+    """Read names of a packed batch that carries only interned ids: 'r<id>'."""
+
+    def __init__(self, ids):
+        self.ids = ids
+
+    def __len__(self):
+        return len(self.ids)
+
+    def __getitem__(self, i):
+        return "r%d" % int(self.ids[i])
+
+    def __iter__(self):
+        return (self[i] for i in range(len(self)))
+
+
+class _NoSeq:
+    def __init__(self, n):
+        self.n = n
+
+    def __len__(self):
+        return self.n
+
+    def __getitem__(self, i):
+        return None
 
 
 class _LazyNames:
@@ -260,7 +334,28 @@ class AlignmentSource:
         return self._by_chrom.get(chrom) or Records().finish()
 
 
+class ArraySource:
+    """An alignment source that is ALREADY packed (include/volcanosv_b200.h layout): what a BAM decode hands over.
+    `records_by_chrom` maps a reference name to a `Records` (see `Records.from_arrays`)."""
+
+    def __init__(self, refs, records_by_chrom):
+        self._refs = list(refs)
+        self._by_chrom = dict(records_by_chrom)
+
+    def references(self):
+        return list(self._refs)
+
+    def records(self, chrom: str) -> "Records":
+        return self._by_chrom.get(chrom) or Records().finish()
+
+
 _sources: Dict[str, AlignmentSource] = {}
+
+
+def register_source(name: str, source) -> str:
+    """Makes an in-memory source reachable under a pseudo path (the operators take paths, as the reference's scripts do)."""
+    _sources[name] = source
+    return name
 
 
 def open_alignments(path: str) -> AlignmentSource:
@@ -325,6 +420,11 @@ def extract_reads_signature(input_path: str, output_dir: str, chr_number: int, m
     sh = _read_shard(input_path, chrom)
     R = sh.R
     counts = sh.scan(None if sh.bed == "unset" else (list(sh.bed) if sh.bed is not None else None))
+    sig_file = "%s/%s_reads_sig.txt" % (out, chrom)
+    if not WRITE_ROW_DUMPS:
+        _write_lines(sig_file, [_STUB])
+        RS.register_file(sig_file, chrom, sh)
+        return None
     reads = sh.fetch(L.TAB_READS)
     nc = counts["n_reads_cigar"]
     sigs, sp = reads[:nc], reads[nc:]
@@ -358,7 +458,6 @@ def extract_reads_signature(input_path: str, output_dir: str, chr_number: int, m
     if allrows:
         order = np.argsort(np.asarray([r[2] for r in allrows], dtype=np.int64), kind="stable")
         allrows = [allrows[i] for i in order]
-    sig_file = "%s/%s_reads_sig.txt" % (out, chrom)
     _write_lines(sig_file, fmt(allrows))
     RS.register_file(sig_file, chrom, sh)
     return allrows
@@ -453,7 +552,7 @@ def sig_extract(input_path: str, reference: str, work_dir: str, include_bed: Opt
     of the INS rows is cut from the reads here."""
     from . import resident as RS
     ctx = context()
-    if not os.path.isfile(reference):
+    if isinstance(reference, str) and not os.path.isfile(reference):
         raise FileNotFoundError("[Errno 2] No such file: '%s'" % reference)
     os.makedirs(os.path.join(work_dir, "signatures"), exist_ok=True)
     p = ctx.get_params()
@@ -477,18 +576,24 @@ def sig_extract(input_path: str, reference: str, work_dir: str, include_bed: Opt
         if sh.R.n == 0:
             continue
         owners[chrom] = sh
+        if not WRITE_ROW_DUMPS:
+            sh.scan(None if bed is None else sorted(bed.get(chrom, [])))
+            continue
         d, i, names = _sigs_chrom(sh, chrom, clen, batches, min_mapq, None if bed is None else sorted(bed.get(chrom, [])))
         del_lines |= d
         ins_lines |= i
         for nm in sorted(names):
             read_lines.append((nm, names[nm]))
-    key = lambda ln: (ln.split("\t")[1], int(ln.split("\t")[2]), ln)          # sort -k2,2 -k3,3n, C locale (SE:637-638)
-    _write_lines(os.path.join(work_dir, "DEL.sigs"), sorted(del_lines, key=key))
-    _write_lines(os.path.join(work_dir, "INS.sigs"), sorted(ins_lines, key=key))
-    out = []
-    for nm, lines in sorted(read_lines, key=lambda x: x[0]):
-        out += lines
-    _write_lines(os.path.join(work_dir, "reads.sigs"), out)
+    if WRITE_ROW_DUMPS:
+        _write_lines(os.path.join(work_dir, "DEL.sigs"), sorted(del_lines, key=_sigs_key))
+        _write_lines(os.path.join(work_dir, "INS.sigs"), sorted(ins_lines, key=_sigs_key))
+        out = []
+        for nm, lines in sorted(read_lines, key=lambda x: x[0]):
+            out += lines
+        _write_lines(os.path.join(work_dir, "reads.sigs"), out)
+    else:
+        for fn in ("DEL.sigs", "INS.sigs", "reads.sigs"):
+            _write_lines(os.path.join(work_dir, fn), [_STUB])
     for fn in ("DEL.sigs", "INS.sigs"):
         for chrom, sh in owners.items():
             RS.register_file(os.path.join(work_dir, fn), chrom, sh)
@@ -680,7 +785,7 @@ def _correct_gt_resident(owner, bamfile, sigfile, is_del, chrom, pos, svlen, gco
     for c in chroms:
         block[c] = (off, owner[c].counts[key])
         off += owner[c].counts[key]
-    if not is_del:
+    if not is_del and WRITE_ROW_DUMPS:
         out = []
         for c in chroms:
             up, ul, un = owner[c].fetch(L.TAB_UINS)
@@ -820,8 +925,11 @@ def filter_gt_correction(vcffile: str, bamfile: Optional[str], reference: Option
         os.makedirs(sigdir)
         bed = None
         if chr_num is not None:
-            with open(reference + ".fai") as f:
-                chr_len = int(f.readlines()[chr_num - 1].split()[1])
+            if isinstance(reference, str):
+                with open(reference + ".fai") as f:
+                    chr_len = int(f.readlines()[chr_num - 1].split()[1])
+            else:
+                chr_len = len(reference["chr%d" % chr_num])
             bed = os.path.join(sigdir, "sample.bed")
             _write_lines(bed, ["chr%d\t1\t%d\n" % (chr_num, chr_len)])
         sig_extract(bamfile, reference, sigdir, include_bed=bed)
@@ -1047,6 +1155,8 @@ def final_header_info(prefix: str) -> List[str]:
 
 def load_contigs(path: str) -> Dict[str, str]:
     """load_contigs (ECS_H:605-622): the record name is the whole header line after '>'."""
+    if not isinstance(path, str):          # already in memory: {name: sequence-like}
+        return path
     d: Dict[str, List[str]] = {}
     cur = None
     op = gzip.open if path.endswith(".gz") else open
@@ -1083,19 +1193,24 @@ def _sort_rows(ctx, rows):
     return [rows[i] for i in order]
 
 
+def clr_gate(ctx, ops, op_off):
+    """The CLR contig gate (ECS_C:53-70,425-427): ins_pct = I / (M + I) <= 0.13 or var_dist = M / #M >= 200, from the
+    per-record class sums of the device (vsv_cigar_class_sums); the two ratios are fp64 divisions as in the reference.  A
+    contig without a single M or I op makes the reference divide by zero: such a record is simply not enabled here."""
+    p = ctx.get_params()
+    i_sum, m_sum, m_cnt = ctx.cigar_class_sums(ops, op_off)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        ip = i_sum.astype(np.float64) / (m_sum + i_sum).astype(np.float64)
+        vd = m_sum.astype(np.float64) / m_cnt.astype(np.float64)
+    return (ip <= p.clr_max_ins_pct) | (vd >= p.clr_min_var_dist)
+
+
 def _contig_one_hap(ctx, R: Records, chrom, hp, dtype, min_cigar_mapq, min_split_mapq, sig_dir):
     strand = ["-" if x else "+" for x in R.is_rev]
     has_hp = np.asarray([hp in nm for nm in R.qname], dtype=bool)
     enable = has_hp.copy()
-    if dtype == "CLR":                                     # ECS_C:53-70,425-427: ins_pct <= 0.13 or mean M run >= 200
-        codes, lens = (R.ops & 15).astype(np.int64), (R.ops >> 4).astype(np.int64)
-        for r in range(R.n):
-            a, b = int(R.op_off[r]), int(R.op_off[r + 1])
-            c, l = codes[a:b], lens[a:b]
-            m_sum, m_cnt, i_sum = int(l[c == 0].sum()), int((c == 0).sum()), int(l[c == 1].sum())
-            ip = i_sum / (m_sum + i_sum)
-            vd = m_sum / m_cnt
-            enable[r] = enable[r] and (ip <= 0.13 or vd >= 200)
+    if dtype == "CLR" and R.n:                             # ECS_C:53-70,425-427: ins_pct <= 0.13 or mean M run >= 200
+        enable &= clr_gate(ctx, R.ops, R.op_off)
     sigs, rt, qt, xt = ctx.scan_cigar(L.MODE_CONTIG, R.ops, R.op_off, R.pos, R.mapq, enable=enable.astype(np.uint8),
                                       min_len=30, min_mapq=min_cigar_mapq)
     d, s = ctx.merge_in_record(L.MODE_CONTIG, sigs)
@@ -1540,9 +1655,24 @@ def large_indel_otherasm_2hap(hp1_fa: str, hp2_fa: str, contig_bam: Optional[str
 
 def large_indel_chr(contig_bam: Optional[str], contig_path: str, reference: str, rbam_file: str, output_dir: str, dtype: str,
                     chr_num: int, prefix: str = "Sample", read_signature_dir: Optional[str] = None,
-                    pre_cutesig: Optional[str] = None, n_thread_align: int = 10):
+                    pre_cutesig: Optional[str] = None, n_thread_align: int = 10, row_dumps: bool = True):
     """LI/volcanosv-vc-large-indel.py ... -chr N (MAIN:233-319) with the contig alignments supplied:
-    header, per-chromosome chain, filter + genotype correction, phasing."""
+    header, per-chromosome chain, filter + genotype correction, phasing.
+    `contig_path` / `reference` may be in-memory {name: sequence} mappings and the alignment "paths" names registered with
+    `register_source` (packed records straight from a decoder); row_dumps=False keeps the read-side tables on the device
+    (see WRITE_ROW_DUMPS): same final VCF, none of the 10^5-10^7-row text files in between."""
+    global WRITE_ROW_DUMPS
+    was = WRITE_ROW_DUMPS
+    WRITE_ROW_DUMPS = bool(row_dumps)
+    try:
+        return _large_indel_chr(contig_bam, contig_path, reference, rbam_file, output_dir, dtype, chr_num, prefix, read_signature_dir,
+                                pre_cutesig, n_thread_align)
+    finally:
+        WRITE_ROW_DUMPS = was
+
+
+def _large_indel_chr(contig_bam, contig_path, reference, rbam_file, output_dir, dtype, chr_num, prefix, read_signature_dir, pre_cutesig,
+                     n_thread_align):
     out_chr = os.path.join(output_dir, "chr%d" % chr_num)
     os.makedirs(out_chr, exist_ok=True)
     ref = load_contigs(reference)
@@ -1550,8 +1680,11 @@ def large_indel_chr(contig_bam: Optional[str], contig_path: str, reference: str,
                                              if k == "chr%d" % chr_num]
     header_file = os.path.join(out_chr, "VCF_header")
     _write_lines(header_file, vcf_header + final_header_info(prefix))
-    _write_fai(reference)                                                                  # samtools faidx (MAIN:88-96)
-    one = _write_chrom_ref(ref, os.path.join(out_chr, "ref_by_chr"), chr_num)
+    if isinstance(reference, str):
+        _write_fai(reference)                                                              # samtools faidx (MAIN:88-96)
+        one = _write_chrom_ref(ref, os.path.join(out_chr, "ref_by_chr"), chr_num)
+    else:
+        one = ref                                                                          # in memory: nothing to split or index
     raw = raw_variant_call(contig_bam, contig_path, one, out_chr, dtype, chr_num, rbam_file, read_signature_dir, n_thread=n_thread_align)
     final = filter_gt_correction(raw, rbam_file, reference, dtype, chr_num, pre_cutesig)
     outfile = os.path.join(out_chr, "%s_volcanosv_large_indel_chr%d.vcf" % (prefix, chr_num))

@@ -111,7 +111,9 @@ class ChromShard:
 
     def __del__(self):
         try:
-            self.close()
+            import sys
+            if not sys.is_finalizing():
+                self.close()
         except Exception:  # noqa: BLE001
             pass
 

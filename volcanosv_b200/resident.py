@@ -71,8 +71,12 @@ class ReadShard:
         self.name_id, self.name_first = intern_names(getattr(R, "name_key", None) if getattr(R, "name_key", None) is not None else R.qname)
         self.shard = L.Shard(ctx)
         if R.n:
+            # a packed batch may bring the links and the parsed SA columns with it (they are part of the host packing)
+            nxt = getattr(R, "next_same_name", None)
+            sa = getattr(R, "sa_packed", None)
             self.shard.load(R.ops, R.op_off, R.pos, R.mapq, R.qlen, R.flag.astype(np.uint16), self.name_id,
-                            L.next_same_name(self.name_id), sa=pack_sa(R, chrom), self_chrom=0)
+                            nxt if nxt is not None else L.next_same_name(self.name_id),
+                            sa=sa if sa is not None else pack_sa(R, chrom), self_chrom=0)
         self.bed = "unset"
         self.counts: Optional[dict] = None
         self._cache: Dict[int, np.ndarray] = {}
@@ -212,3 +216,16 @@ def clear():
         s.close()
     _shards.clear()
     _file_owner.clear()
+
+
+def _at_exit():
+    """Destroy the engines while the CUDA runtime is still up (Python's atexit runs before the C-level handlers)."""
+    try:
+        clear()
+    except Exception:  # noqa: BLE001
+        pass
+
+
+import atexit  # noqa: E402
+
+atexit.register(_at_exit)

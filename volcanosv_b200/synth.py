@@ -192,3 +192,61 @@ def add_duplicates(b, rng, n_dup=40):
     idx = np.concatenate([np.arange(b["op_off"][r], b["op_off"][r + 1]) for r in order]) if len(order) else np.zeros(0, np.int64)
     out["ops"] = np.ascontiguousarray(b["ops"][idx])
     return out
+
+
+class SynthSeq:
+    """A deterministic pseudo-random DNA sequence of a given length that is never materialised: a slice is generated on
+    demand from a counter-based generator keyed by (seed, block), so a 135 Mb reference or 300 kb contigs cost nothing to
+    hold.  Supports len(), integer and slice indexing (Python semantics) and returns str."""
+    _BASES = np.frombuffer(b"ACGT", dtype=np.uint8)
+    BLOCK = 4096
+
+    def __init__(self, length: int, seed: int):
+        self.n, self.seed = int(length), int(seed)
+
+    def __len__(self):
+        return self.n
+
+    def _block(self, b):
+        rng = np.random.Generator(np.random.Philox(key=self.seed, counter=[b, 0, 0, 0]))
+        return self._BASES[rng.integers(0, 4, self.BLOCK)]
+
+    def __getitem__(self, k):
+        if isinstance(k, slice):
+            a, b, step = k.indices(self.n)
+            if step != 1:
+                raise IndexError("SynthSeq: step slices are not supported")
+            if b <= a:
+                return ""
+            parts = [self._block(blk) for blk in range(a // self.BLOCK, (b - 1) // self.BLOCK + 1)]
+            buf = np.concatenate(parts)
+            o = a - (a // self.BLOCK) * self.BLOCK
+            return buf[o: o + (b - a)].tobytes().decode()
+        k = int(k)
+        if k < 0:
+            k += self.n
+        if not 0 <= k < self.n:
+            raise IndexError("SynthSeq index out of range")
+        return chr(self._block(k // self.BLOCK)[k % self.BLOCK])
+
+
+def synth_contigs(seed: int, chrom_len: int = CHR10_LEN, contig_len: int = 300_000, chrom: str = "chr10"):
+    """Contig-to-reference alignments of two haplotypes tiling one chromosome: packed records with the
+    M/I/D/S/H alphabet the contig scanner accepts, names `PS<s>_<e>_hp<h>_<k>` (the hp tag selects the haplotype,
+    ECS_H:392), and the contig sequences as `SynthSeq` (length = read length incl. hard clips).  Returns (batch, names,
+    {name: SynthSeq})."""
+    n = max(4, int(2 * chrom_len / contig_len))
+    b = synth_records(seed, n, "contig", chrom_len=chrom_len, eqx=False, clip_rate=0.05)
+    codes, lens = b["ops"] & 15, (b["ops"] >> 4).astype(np.int64)
+    off = b["op_off"]
+    csum = np.concatenate([[0], np.cumsum(np.where(np.isin(codes, [0, 1, 4, 5]), lens, 0))])
+    readlen = csum[off[1:]] - csum[off[:-1]]
+    names, seqs = [], {}
+    for k in range(n):
+        s = int(b["pos"][k])
+        nm = "PS%d_%d_hp%d_%d" % (s + 1, s + contig_len, int(b["hp"][k]), k)
+        names.append(nm)
+        seqs[nm] = SynthSeq(int(readlen[k]), seed * 1_000_003 + k)
+    b["flag"] = (b["flag"] & 16).astype(np.uint16)            # primary alignments only: one record per contig name
+    b["name_id"] = np.arange(n, dtype=np.int32)
+    return b, names, seqs
