@@ -251,9 +251,11 @@ __device__ __forceinline__ void add_op(uint32_t w, Sums& s) {
   const uint32_t bit = 1u << (w & 15u), len = w >> 4;
   s.r += (bit & M::REF) ? len : 0u;
   s.q += (bit & M::QRY) ? len : 0u;
-  s.x1 += (bit & M::X1) ? len : 0u;
-  if (M::NX > 1) s.x2 += (bit & M::X2) ? len : 0u;
-  if (M::NX > 2) s.x3 += (bit & M::X3) ? len : 0u;
+  if (bit & (M::X1 | M::X2 | M::X3)) {   // N / H / P / reserved codes: a branch that is almost never taken (k_gate spends its
+    s.x1 += (bit & M::X1) ? len : 0u;    // issue slots in 32 of these per candidate)
+    if (M::NX > 1) s.x2 += (bit & M::X2) ? len : 0u;
+    if (M::NX > 2) s.x3 += (bit & M::X3) ? len : 0u;
+  }
 }
 
 __device__ __forceinline__ void store_sums(uint4* dst, const Sums& s) {

@@ -85,6 +85,10 @@ class ReadShard:
     def scan(self, bed: Optional[List[Tuple[int, int]]] = None):
         """Runs the fused step (again only if the -include_bed regions changed).  bed: regions of THIS chromosome
         already widened by 1000 bp (SE:69), or None."""
+        if bed is not None and any(r0 <= 0 and r1 >= self.chrom_len for r0, r1 in bed):
+            # a region that covers the whole chromosome (the driver's sample.bed, FGC:71-75) is attached to every task and
+            # overlaps every record: same result as no BED, and the scan that already ran without one is reused
+            bed = None
         key = None if bed is None else tuple(bed)
         if self.counts is not None and key == self.bed:
             return self.counts
