@@ -134,3 +134,22 @@ def test_bind_host_to_gpu_is_best_effort():
     else:
         assert os.sched_getaffinity(0) <= before
         os.sched_setaffinity(0, before)
+
+
+def test_write_fai_variants(tmp_path):
+    """the samtools-faidx stand-in on FASTA variants the real tool accepts (empty record, CRLF, short last line)
+    and the one it refuses (ragged lines)."""
+    import pytest
+    from volcanosv_b200 import operators as OP
+    p = tmp_path / "a.fa"
+    p.write_bytes(b">chr1 desc\nACGTAC\nACGTAC\nAC\n>empty\n>chr2\nAAAA\n")
+    assert OP._write_fai(str(p)) == [("chr1", 14), ("empty", 0), ("chr2", 4)]
+    assert open(str(p) + ".fai").read() == "chr1\t14\t11\t6\t7\nempty\t0\t35\t0\t0\nchr2\t4\t41\t4\t5\n"
+    q = tmp_path / "crlf.fa"
+    q.write_bytes(b">chr1\r\nACGT\r\nAC\r\n")
+    assert OP._write_fai(str(q)) == [("chr1", 6)]
+    assert open(str(q) + ".fai").read() == "chr1\t6\t7\t4\t6\n"
+    r = tmp_path / "ragged.fa"
+    r.write_bytes(b">chr1\nACGT\nAC\nACGT\n")
+    with pytest.raises(ValueError):
+        OP._write_fai(str(r))

@@ -1504,23 +1504,32 @@ def raw_variant_call(contig_bam: Optional[str], contig_path: str, reference_path
 
 
 def _write_fai(reference: str) -> List[tuple]:
-    """`samtools faidx <ref>` (MAIN:78-96): writes <ref>.fai, returns [(name, length)] in file order."""
+    """`samtools faidx <ref>` (MAIN:78-96): writes <ref>.fai, returns [(name, length)] in file order.  As faidx: LF or CRLF
+    line ends, a record without sequence lines has length 0, and a sequence line longer than the first one of its record
+    (or a short line that is not the last) is an error."""
     out = []
     with open(reference, "rb") as fa:
         data = fa.read().split(b"\n")
     rows = []
-    pos, name, ln, lb, start = 0, None, 0, None, 0
+    pos, name, ln, lb, lw, start, short_seen = 0, None, 0, 0, 0, 0, False
     for row in data:
-        if row.startswith(b">"):
+        raw = len(row) + 1                     # bytes of the line incl. its LF
+        body = row[:-1] if row.endswith(b"\r") else row
+        if body.startswith(b">"):
             if name is not None:
-                rows.append((name, ln, start, lb, lb + 1))
-            name, ln, lb, start = row[1:].split()[0].decode(), 0, None, pos + len(row) + 1
-        elif row:
-            lb = lb or len(row)
-            ln += len(row)
-        pos += len(row) + 1
+                rows.append((name, ln, start, lb, lw))
+            name, ln, lb, lw, start, short_seen = body[1:].split()[0].decode(), 0, 0, 0, pos + raw, False
+        elif body and name is not None:
+            if lb == 0:
+                lb, lw = len(body), raw
+            elif len(body) > lb or short_seen:
+                raise ValueError("%s: different line length in sequence '%s' (samtools faidx refuses such a FASTA)" % (reference, name))
+            if len(body) < lb:
+                short_seen = True
+            ln += len(body)
+        pos += raw
     if name is not None:
-        rows.append((name, ln, start, lb, lb + 1))
+        rows.append((name, ln, start, lb, lw))
     with open(reference + ".fai", "w") as f:
         for r in rows:
             f.write("%s\t%d\t%d\t%d\t%d\n" % r)
