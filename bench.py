@@ -90,6 +90,27 @@ def prefix(batch, m):
     return out
 
 
+def prefix_t(tm, batch, m, pin_small=True):
+    """prefix() over torch tensors `tm` of the same batch (pinned host or device): views, no copy of the ops; the links
+    past the cut are rewritten in a small per-chromosome copy."""
+    import torch
+    e = int(batch["op_off"][m])
+    out = dict(ops=tm["ops"][:e], op_off=tm["op_off"][: m + 1])
+    for k in ("pos", "mapq", "qlen", "flag", "name_id"):
+        out[k] = tm[k][:m]
+    nx = batch["next_same_name"][:m].copy()
+    nx[nx >= m] = -1
+    nx = torch.from_numpy(nx)
+    out["next_same_name"] = nx.to(tm["ops"].device) if tm["ops"].is_cuda else (nx.pin_memory() if pin_small else nx)
+    k = int(np.searchsorted(batch["sa_rec"], m))
+    out["sa_rec"], out["sa_off"] = tm["sa_rec"][:k], tm["sa_off"][: k + 1]
+    ee = int(batch["sa_off"][k])
+    for c in ("chrom", "pos", "strand", "first_s", "last_s", "bias", "mapq"):
+        out["sa_" + c] = tm["sa_" + c][:ee]
+    out["sa_self_chrom"] = batch.get("sa_self_chrom", 0)
+    return out
+
+
 class ClockSampler(threading.Thread):
     """nvidia-smi style clock / throttle-reason samples during the timed region."""
 
@@ -226,8 +247,8 @@ def main():
         mine = sorted(plan[rank])
         loads = [sum(chrom_ops[c] for c in p) for p in plan]
         lpt = dict(max_over_mean=max(loads) / (sum(loads) / world), chroms_per_rank=[len(p) for p in plan])
-        shards = [(prefix(master, chrom_n[c]), make_cands(500 + c, max(16, int(args.cands * HG19[c] / HG19[9])), int(master["pos"][chrom_n[c] - 1])))
-                  for c in mine]
+        shard_cands = [make_cands(500 + c, max(16, int(args.cands * HG19[c] / HG19[9])), int(master["pos"][chrom_n[c] - 1])) for c in mine]
+        shards = None          # chromosome = prefix VIEW of the master (host: pinned once; device: uploaded once)
         total_rec, total_ops = sum(chrom_n), sum(chrom_ops)
     else:
         n_total = max(64, int(synth.n_records(profile) * args.scale))
@@ -303,19 +324,24 @@ def main():
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    host = [(pin(b), {k: torch.from_numpy(v).pin_memory() for k, v in c.items()}, int(b["op_off"][-1])) for b, c in shards]
+    pin_c = lambda c: {k: torch.from_numpy(v).pin_memory() for k, v in c.items()}
     if wgs:
-        del master
+        pm = pin(master)                                   # ONE pinned copy of the master; every chromosome is a view of it
+        host = [(prefix_t(pm, master, chrom_n[c]), pin_c(cc), chrom_ops[c]) for c, cc in zip(mine, shard_cands)]
+    else:
+        host = [(pin(b), pin_c(c), int(b["op_off"][-1])) for b, c in shards]
     warm = max(args.warmup, 3)
 
     # ---- resident timing: every shard of this rank on the device, CUDA events on the library's stream ----
     res_shards = []
     if wgs:
         from volcanosv_b200.pipeline import ChromShard
-        # all chromosomes of this rank stay resident (180 GB of HBM): one engine per chromosome
-        for hb, hc, n_ops in host:
+        # all chromosomes of this rank stay resident: the master is uploaded once, one engine per chromosome adopts its prefix
+        dm = {k: (v.to("cuda", non_blocking=True) if hasattr(v, "to") else v) for k, v in pm.items()}
+        torch.cuda.synchronize()
+        for c, (hb, hc, n_ops) in zip(mine, host):
             cs = ChromShard(local, dtype)
-            cs.upload(hb, hc, n_ops=n_ops)
+            cs.adopt(prefix_t(dm, master, chrom_n[c]), hc, n_ops=n_ops)
             res_shards.append(cs)
     else:
         shard.upload(host[0][0], host[0][1], n_ops=host[0][2])
@@ -341,12 +367,15 @@ def main():
     else:
         t_ev0.record()
         last_res = []
+        from volcanosv_b200.pipeline import run_many
         for _ in range(args.steps):
-            last_res = []
-            for cs in res_shards:
-                r = cs.run_safe()          # ends with the one host read of the counts: every shard's work is complete here
+            # all shards of this rank in flight (one stream each); the counts of every shard are read once, after the enqueues:
+            # every shard's work is complete when the last count has been read
+            last_res = run_many(res_shards)
+            for r in last_res:
                 scan_ms += r.scan_ms
-                last_res.append(r)
+        for cs in res_shards:
+            cs.sync()
         t_ev1.record()
         t_ev1.synchronize()
         ms = t_ev0.elapsed_time(t_ev1)
@@ -480,6 +509,7 @@ def main():
                sa_rows=sum(r.counts["n_sa_rows"] for r in last_res), split_sigs=sum(r.counts["n_reads_split"] for r in last_res),
                unique_del=sum(r.n_udel for r in last_res), unique_ins=sum(r.n_uins for r in last_res),
                candidates="synthetic table (pos sorted, Pareto lengths)", host_syncs_per_shard=1,
+               shards_in_flight=len(res_shards),
                parallelism=("22 chromosome shards over %d ranks by LPT, no collective" % world) if wgs else
                ("shard-per-gpu x%d, no collective" % world),
                l2="inputs (%.2f GB/step on this rank) exceed the 126 MB L2; no flush needed" % (4.0 * my_ops / 1e9)
@@ -498,7 +528,7 @@ def main():
                          feeder_staging=staged, to_final_vcf=to_vcf),
                 roofline=roof, candidates_per_s=geno)
     if not args.no_cpu_baseline and world == 1:              # reported at N=1 only (the host cores are shared by the ranks)
-        ref_b, ref_c = shards[-1] if wgs else shards[0]
+        ref_b, ref_c = (prefix(master, chrom_n[mine[-1]]), shard_cands[-1]) if wgs else shards[0]
         base, _, _ = cpu_baseline(ref_b, ref_c, thr)
         line["cpu_baseline"] = base
     print(json.dumps(line))

@@ -182,6 +182,34 @@ class ChromShard:
         if stream is None:
             self.finish_upload()
 
+    def adopt(self, dev_batch, cands=None, n_ops: Optional[int] = None):
+        """Uses record columns that are ALREADY on this GPU (torch tensors, e.g. slices of a larger resident batch) without
+        copying them: the engine adopts the device pointers (device-IO ctx).  BAM-native u32 ops only."""
+        rec = L.RecordsStruct()
+        self._pending = None
+        self._adopted = dict(dev_batch)          # keeps the tensors alive
+        t_ops = _as_tensor(dev_batch["ops"])
+        n_rec = int(dev_batch["pos"].numel())
+        n_ops = int(n_ops if n_ops is not None else t_ops.numel())
+        rec.ops, rec.ops_format, rec.n_ops, rec.n_rec = t_ops.data_ptr(), 32, n_ops, n_rec
+        for k in _REC_COLS:
+            if dev_batch.get(k) is not None:
+                setattr(rec, k, _as_tensor(dev_batch[k]).data_ptr())
+        if dev_batch.get("sa_rec") is not None and dev_batch["sa_rec"].numel():
+            for k in _SA_COLS:
+                setattr(rec, k, _as_tensor(dev_batch[k]).data_ptr())
+            rec.n_sa_read, rec.n_sa_ent = int(dev_batch["sa_rec"].numel()), int(dev_batch["sa_pos"].numel())
+            rec.sa_self_chrom = int(dev_batch.get("sa_self_chrom", 0))
+        if cands is not None:
+            for k in ("pos", "svlen", "type", "gt"):
+                src = _as_tensor(cands[k])
+                self._buf("in_cand_" + k, src.numel(), src.dtype)[: src.numel()].copy_(src, non_blocking=True)
+            self.n_cand = len(cands["pos"])
+        torch.cuda.current_stream().synchronize()
+        self.n_rec, self.n_ops = n_rec, n_ops
+        self.h2d_bytes = 0
+        self._chk(self.lib.vsv_shard_load(self.sh, C.byref(rec)))
+
     def set_candidates(self, cands):
         """Replaces the resident candidate table (pos, svlen, type, gt)."""
         for k in ("pos", "svlen", "type", "gt"):
@@ -282,6 +310,20 @@ class ChromShard:
                 self.d2h_bytes += t.numel() * t.element_size()
             torch.cuda.current_stream().synchronize()
         return {k: v.numpy() for k, v in out.items()}
+
+
+def run_many(shards, what: int = 15):
+    """Several resident shards in flight on one GPU: every shard's step is enqueued on its own stream (each engine has its
+    own context) before any count is read, so the small latency-bound kernels of one chromosome fill the gaps of another -
+    the steady state of the whole-genome mode, where a GPU owns 3 - 22 chromosomes.  A shard whose tables overflowed is
+    repeated on its own (`run_safe`).  Returns the ShardResults in order."""
+    results = [sh.run(what) for sh in shards]
+    for i, (sh, res) in enumerate(zip(shards, results)):
+        res.counts = sh.counts()
+        res.scan_ms.append(sh.ctx.main_kernel_ms())
+        if res.counts["overflow"]:
+            results[i] = sh.run_safe(what)
+    return results
 
 
 class ShardStream:

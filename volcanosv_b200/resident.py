@@ -68,7 +68,12 @@ class ReadShard:
 
     def __init__(self, ctx: L.Context, R, chrom: str, chrom_len: int):
         self.ctx, self.R, self.chrom, self.chrom_len = ctx, R, chrom, int(chrom_len)
-        self.name_id, self.name_first = intern_names(getattr(R, "name_key", None) if getattr(R, "name_key", None) is not None else R.qname)
+        key = getattr(R, "name_key", None)
+        if key is not None and isinstance(key, np.ndarray) and key.dtype.kind in "iu":
+            # a packed batch whose names are interned already (ids from the decoder): nothing to hash
+            self.name_id, self._name_first = np.ascontiguousarray(key, dtype=np.int32), None
+        else:
+            self.name_id, self._name_first = intern_names(key if key is not None else R.qname)
         self.shard = L.Shard(ctx)
         if R.n:
             # a packed batch may bring the links and the parsed SA columns with it (they are part of the host packing)
@@ -80,6 +85,16 @@ class ReadShard:
         self.bed = "unset"
         self.counts: Optional[dict] = None
         self._cache: Dict[int, np.ndarray] = {}
+
+    @property
+    def name_first(self):
+        """First record index of every name id (the first-appearance order of ERS:227-237), built when a formatter asks."""
+        if self._name_first is None:
+            n = len(self.name_id)
+            first = np.full(int(self.name_id.max()) + 1 if n else 0, n, np.int64)
+            np.minimum.at(first, self.name_id, np.arange(n, dtype=np.int64))
+            self._name_first = first
+        return self._name_first
 
     # ---- the one scan ----------------------------------------------------------------------------------
     def scan(self, bed: Optional[List[Tuple[int, int]]] = None):
