@@ -153,3 +153,54 @@ def test_write_fai_variants(tmp_path):
     r.write_bytes(b">chr1\nACGT\nAC\nACGT\n")
     with pytest.raises(ValueError):
         OP._write_fai(str(r))
+
+
+def test_assemble_support_chain_matches_genome_wide_oracle():
+    """Rank 0's assembly of the sharded supporting-signature count (operators._fgc_sharded): every shard computes its
+    candidates with the local carry-in -1 (and 0 for the block at global index 0), `assemble_support_chain` picks the variant
+    and rebuilds the GLOBAL match_id column == match_varlist_siglist run over the whole genome (GTD:92-137)."""
+    rng = np.random.default_rng(11)
+    chroms = ["chr1", "chr2", "chr3", "chr10", "chr11"]
+    for trial in range(40):
+        sig = {}
+        for c in chroms:
+            if (trial % 4 == 0 and c == "chr1") or rng.random() < 0.15:
+                continue                                       # a chromosome without signatures (first block moves to chr10)
+            n = int(rng.integers(1, 30))
+            sig[c] = (np.sort(rng.integers(1000, 20000, n)).astype(np.int32), rng.integers(30, 400, n).astype(np.int32),
+                      rng.integers(1, 5, n).astype(np.int32))
+        cand = {c: (np.sort(rng.integers(1000, 20000, int(rng.integers(0, 10)))).astype(np.int32),) for c in chroms}
+        cand = {c: (p[0], rng.integers(30, 400, len(p[0])).astype(np.int32)) for c, p in cand.items()}
+        cid = {c: i for i, c in enumerate(S.chrom_dictionary_order(chroms))}
+        so = S.chrom_dictionary_order(list(sig))
+        co = [c for c in S.chrom_numeric_order(chroms) if len(cand[c][0])]
+        if not so or not co:
+            continue
+        g_sc = np.concatenate([np.full(len(sig[c][0]), cid[c], np.int32) for c in so])
+        g_sp, g_sl, g_sn = (np.concatenate([sig[c][k] for c in so]) for k in range(3))
+        g_cc = np.concatenate([np.full(len(cand[c][0]), cid[c], np.int32) for c in co])
+        g_cp, g_cl = (np.concatenate([cand[c][k] for c in co]) for k in range(2))
+        exp_sup, exp_mid = O.sig_support(g_cc, g_cp, g_cl, g_sc, g_sp, g_sl, g_sn)
+        blocks, off = {}, 0
+        for c in so:
+            blocks[c] = (off, len(sig[c][0]))
+            off += len(sig[c][0])
+        runs = []
+        for c in co:                                           # what each rank computes for its chromosome
+            n = len(cand[c][0])
+            z = np.zeros(n, np.int32)
+            run = dict(chrom=c)
+            for tag, li in (("a", -1), ("b", 0)):
+                if tag == "b" and blocks.get(c, (1, 0))[0] != 0:
+                    continue
+                if c in sig:
+                    s, m, last = O.sig_support(z, cand[c][0], cand[c][1], np.zeros(len(sig[c][0]), np.int32), *sig[c], last_in=li, return_last=True)
+                else:
+                    s, m, last = [0] * n, [li] * n, li
+                run[tag] = (np.asarray(s), np.asarray(m), last)
+            runs.append(run)
+        chosen, _ = S.assemble_support_chain(runs, blocks)
+        got_sup = np.concatenate([x[1] for x in chosen])
+        got_mid = np.concatenate([x[2] for x in chosen])
+        assert list(got_sup) == list(exp_sup), trial
+        assert list(got_mid) == list(exp_mid), trial

@@ -956,6 +956,7 @@ def _fgc_sharded(vcffile, bamfile, reference, dtype, mine, rank, world, barrier)
     Rank 0: concatenation in the reference's orders, the genome-wide coverage median (filter_vcf_by_sig_cov_insdel.py:39,55)
     and the files.  Two values cross chromosome edges through the host: that median and last_match_idx (GTD:94)."""
     from . import resident as RS
+    from . import shard as SH
     ctx = context()
     wd = os.path.dirname(vcffile)
     sigdir = os.path.join(wd, "cute_sig")
@@ -1077,21 +1078,19 @@ def _fgc_sharded(vcffile, bamfile, reference, dtype, mine, rank, world, barrier)
                 out += ["%d\t%d\t%d\t%d\n" % (int(c[3:]), p_, l_, k_) for p_, l_, k_ in zip(up, ul, un)]
             _write_lines(os.path.join(sigdir, "INS.sigs.gte30auto"), out)
         carr = np.asarray(chrom)
-        global_last = 0
+        runs, idxs = [], []
         for c in dict.fromkeys(chrom):                 # chromosomes in VCF order (each one contiguous: checked by its rank)
             idx = np.flatnonzero(carr == c)
             r = np.load(res_path(c, tp))
-            b0, nu = block.get(c, (0, 0))
-            li = global_last - b0 if (nu > 0 and b0 <= global_last < b0 + nu) else -1
-            if li > 0 or (li == 0 and "sup_b" not in r.files):
-                raise L.VsvError(L.E_ARG, "last_match_idx points inside the block of %s before its first candidate" % c)
-            tag = "b" if li == 0 else "a"
-            sup[idx], depth2[idx], ratio[idx], newgt[idx] = r["sup_" + tag], r["d2"], r["ratio_" + tag], r["gt_" + tag]
-            mid = r["mid_" + tag]
-            match_id[idx] = np.where(mid >= 0, b0 + mid, global_last) if off > 0 else 0
-            lo = int(r["last_" + tag])
-            if lo >= 0:
-                global_last = b0 + lo
+            run = dict(chrom=c, a=(r["sup_a"], r["mid_a"], int(r["last_a"])))
+            if "sup_b" in r.files:
+                run["b"] = (r["sup_b"], r["mid_b"], int(r["last_b"]))
+            runs.append(run)
+            idxs.append((idx, r))
+        chosen, _ = SH.assemble_support_chain(runs, block)
+        for (idx, r), (tag, s_, m_) in zip(idxs, chosen):
+            sup[idx], match_id[idx] = s_, m_
+            depth2[idx], ratio[idx], newgt[idx] = r["d2"], r["ratio_" + tag], r["gt_" + tag]
         _gt_write(filtered, os.path.join(gtdir, "bnd_%s_real.tsv" % tp.lower()), tp, lines, chrom, pos, svid, gt, svlen, sup, match_id,
                   depth2, ratio, newgt)
     header, _ = _read_vcf(filtered)

@@ -65,6 +65,34 @@ def support_carry_in(chrom: str, cand_chroms: Sequence[str], sig_chroms: Sequenc
     return 0 if chrom == first_block else -1
 
 
+def assemble_support_chain(runs, blocks):
+    """Rank 0's side of the sharded supporting-signature count (GTD:92-137 run genome-wide).
+
+    The reference's last_match_idx indexes the GENOME-WIDE unique-signature list (chromosome blocks in `.sigs` order).  Every
+    shard computed its candidates with a LOCAL carry-in: variant "a" = -1 (the index points into another chromosome's block
+    and can never be double counted) and, for the chromosome whose block starts at global index 0, also variant "b" = 0.
+    `runs`: the chromosome runs in VCF order, each dict(chrom=..., a=(support, local_match_id, local_last_out)[, b=...]);
+    `blocks`: {chrom: (first global index of its block, unique signatures in it)}.
+    Returns ([(variant, support, global_match_id) per run], final global last_match_idx): walks the runs in order, keeps the global
+    index, picks the variant that matches it and lifts the local indices into the global list."""
+    import numpy as np
+    out, global_last = [], 0
+    total = sum(n for _, n in blocks.values())
+    for run in runs:
+        b0, nu = blocks.get(run["chrom"], (0, 0))
+        li = global_last - b0 if (nu > 0 and b0 <= global_last < b0 + nu) else -1
+        if li > 0 or (li == 0 and "b" not in run):
+            raise ValueError("last_match_idx points inside the block of %s before its first candidate" % run["chrom"])
+        tag = "b" if li == 0 else "a"
+        sup, mid, last_out = run[tag]
+        mid = np.asarray(mid)
+        gmid = np.where(mid >= 0, b0 + mid, global_last) if total > 0 else np.zeros(len(mid), np.int64)
+        out.append((tag, np.asarray(sup), gmid))
+        if int(last_out) >= 0:
+            global_last = b0 + int(last_out)
+    return out, global_last
+
+
 def gather_to_root(local: dict, group=None) -> List[dict]:
     """Host-side gather of per-rank result dicts (keyed by chromosome) to rank 0.  Returns the
     list of all ranks' dicts on rank 0, [] elsewhere.  No-op without torch.distributed."""
