@@ -468,6 +468,13 @@ def main():
         except Exception as ex:  # noqa: BLE001
             geno = dict(error=str(ex))
 
+    edit = None
+    if not wgs and rank == 0:
+        try:
+            edit = edit_distance_point(local, cpu=(world == 1 and not args.no_cpu_baseline))
+        except Exception as ex:  # noqa: BLE001
+            edit = dict(error="%s: %s" % (type(ex).__name__, ex))
+
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
@@ -526,7 +533,7 @@ def main():
                          staging="BAM-native u32 CIGAR words + per-record columns in pinned host buffers (no host-side packing)",
                          pipelining="two shard slots: H2D of shard k+1 overlaps kernels + D2H of shard k",
                          feeder_staging=staged, to_final_vcf=to_vcf),
-                roofline=roof, candidates_per_s=geno)
+                roofline=roof, candidates_per_s=geno, edit_distance=edit)
     if not args.no_cpu_baseline and world == 1:              # reported at N=1 only (the host cores are shared by the ranks)
         ref_b, ref_c = (prefix(master, chrom_n[mine[-1]]), shard_cands[-1]) if wgs else shards[0]
         base, _, _ = cpu_baseline(ref_b, ref_c, thr)
@@ -614,6 +621,68 @@ def genotype_point(shard, local, n_reads=10_000_000, n_cand=1_000_000, cpu=False
         dt = time.perf_counter() - t0
         out["cpu_baseline"] = dict(value=m / dt, unit="candidates/s", cores=CO.num_threads(), kind="port",
                                    sample="first %d candidates against all %d reads, %.2f s" % (m, n_reads, dt))
+    return out
+
+
+def edit_pairs(seed, n_pair, lo=100, hi=100_000, frac_same=0.6):
+    """Insertion-sequence pairs shaped like the redundancy stage's input (RR:92-102 keeps pairs within 500 bp whose sizes are
+    within 2x): Pareto lengths in [lo, hi]; `frac_same` of the pairs are one event seen on two haplotypes (1 % divergence:
+    substitutions and short indels), the rest unrelated sequences of similar size."""
+    rng = np.random.default_rng(seed)
+    acgt = np.frombuffer(b"ACGT", np.uint8)
+    strs, ia, ib = [], [], []
+    for _ in range(n_pair):
+        la = int(min(hi, lo * (1.0 - rng.random()) ** (-1.0 / 1.1)))
+        a = acgt[rng.integers(0, 4, la)]
+        if rng.random() < frac_same:
+            b = a.copy()
+            k = max(1, la // 100)
+            b[rng.integers(0, la, k)] = acgt[rng.integers(0, 4, k)]
+            for _ in range(max(1, la // 2000)):                # short indels
+                c, ln = int(rng.integers(0, len(b))), int(rng.integers(1, 6))
+                b = np.concatenate([b[:c], acgt[rng.integers(0, 4, ln)], b[c:]]) if rng.random() < 0.5 else np.concatenate([b[:c], b[c + ln:]])
+        else:
+            b = acgt[rng.integers(0, 4, max(1, int(la * rng.uniform(0.5, 1.0))))]
+        ia.append(len(strs))
+        ib.append(len(strs) + 1)
+        strs += [a.tobytes(), b.tobytes()]
+    return strs, ia, ib
+
+
+def edit_distance_point(local, cpu=False, n_pair=1000):
+    """SURVEY.md 8f-1 / RR:75-102: one redundancy-stage batch (10^3 insertion pairs of 10^2..10^5 bp) through
+    vsv_edit_distance_batch with HOST buffers; the reference's own vendored edlib (oracle/_ref) beside it."""
+    from volcanosv_b200 import lib as L
+    ctx = L.Context(local)
+    strs, ia, ib = edit_pairs(21, n_pair)
+    cells = float(sum(len(strs[i]) * len(strs[j]) for i, j in zip(ia, ib)))
+    ctx.edit_distance_batch(strs[:8], ia[:4], ib[:4])              # module load
+    wall, kern = [], []
+    for _ in range(3):
+        t0 = time.perf_counter()
+        d = ctx.edit_distance_batch(strs, ia, ib)
+        wall.append(time.perf_counter() - t0)
+        kern.append(ctx.timing()[0])
+    w, k = float(np.median(wall)), float(np.median(kern))
+    tot = np.array([len(strs[i]) + len(strs[j]) for i, j in zip(ia, ib)])
+    out = dict(value=n_pair / w, unit="pairs/s", pairs=n_pair, ms=w * 1e3, kernel_ms=k, lengths="Pareto(1.1) in [100, 100000] bp",
+               max_len=int(max(len(x) for x in strs)), similar_pairs=int(np.sum((tot - d) / tot >= 0.5)),
+               full_matrix_cells=cells, cell_updates_per_s=cells / (k * 1e-3),
+               note="cell_updates_per_s = full-matrix cells (len1 x len2 summed) / kernel time: the band skips most of them for the "
+                    "near-identical pairs, so it is an equivalent rate, comparable with the CPU figure computed the same way",
+               kernel="k_edit_banded (Myers/Hyyro 64-row blocks, Ukkonen band x8 per round, state in shared memory)")
+    ctx.close()
+    if cpu:
+        from oracle import edlib_ref as E
+        if E.available():
+            m = n_pair
+            t0 = time.perf_counter()
+            ref = [E.distance(strs[i].decode(), strs[j].decode()) for i, j in zip(ia[:m], ib[:m])]
+            dt = time.perf_counter() - t0
+            c = float(sum(len(strs[i]) * len(strs[j]) for i, j in zip(ia[:m], ib[:m])))
+            out["cpu_baseline"] = dict(value=m / dt, unit="pairs/s", cores=1, kind="reference", cell_updates_per_s=c / dt,
+                                       sample="first %d pairs, the reference's vendored edlib (oracle/_ref/libedlib_ref.so, "
+                                              "EDLIB_MODE_NW, k = -1), %.2f s" % (m, dt), parity=bool(ref == d[:m].tolist()))
     return out
 
 

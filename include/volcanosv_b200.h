@@ -258,8 +258,9 @@ int vsv_genotype(vsv_ctx* ctx, const int32_t* read_start, const int32_t* read_en
 /* Replaces edlib.align(a, b)["editDistance"] at LI/remove_redundancy.py:75-81 (global /
  * Needleman-Wunsch, unit costs) for a batch of string pairs: strings are rows of a table
  * (chars, str_off[n_str+1]); pair p compares strings ia[p] and ib[p].  Exact (Myers/Hyyro
- * bit-vector).  The SHORTER string of a pair may use at most 16 distinct byte values (DNA
- * alphabets), else VSV_E_ARG.  Host buffers only. */
+ * bit-vector blocks inside an Ukkonen band that widens until the result is proven, as edlib's
+ * NW mode does).  The string table may use at most 32 distinct byte values (DNA alphabets) and
+ * strings shorter than 2^28, else VSV_E_ARG.  Host buffers only. */
 int vsv_edit_distance_batch(vsv_ctx* ctx, const uint8_t* chars, const int64_t* str_off, int64_t n_str,
                             const int32_t* ia, const int32_t* ib, int64_t n_pair, int32_t* dist);
 

@@ -305,10 +305,74 @@ def test_edit_distance_batch(ctx):
     if E.available():        # the reference's own vendored edlib, built into oracle/_ref by oracle/Makefile (travels with the snapshot)
         for (i, j), g in zip(pairs, got):
             assert int(g) == E.distance(strs[i], strs[j])
+    # one symbol table per call: up to 32 distinct byte values anywhere in the table
+    assert int(ctx.edit_distance_batch(["ABCDEFGHIJKLMNOPQRS", "ABCDEFGHIJKLMNOPQRSTUV"], [0], [1])[0]) == 3
+    assert int(ctx.edit_distance_batch(["ABCDEFGHIJKLMNOPQRS", "ABC"], [0], [1])[0]) == 16
     with pytest.raises(V.VsvError):
-        ctx.edit_distance_batch(["ABCDEFGHIJKLMNOPQRS", "ABCDEFGHIJKLMNOPQRSTUV"], [0], [1])
-    assert int(ctx.edit_distance_batch(["ABCDEFGHIJKLMNOPQRS", "ABC"], [0], [1])[0]) == 16   # only the shorter string is limited
+        ctx.edit_distance_batch(["".join(chr(48 + i) for i in range(33)), "0"], [0], [1])
+    with pytest.raises(V.VsvError):
+        ctx.edit_distance_batch(["A", "C"], [0], [2])
     assert len(ctx.edit_distance_batch(["A"], [], [])) == 0
+
+
+def test_edit_distance_banded_long(ctx):
+    """The banded sweep of k_edit_banded: long pairs (one CTA per pair), pairs that finish in the first narrow round, pairs
+    that need the band widened to the full matrix, very unequal lengths, a pair whose state does not fit shared memory
+    (global scratch through the same pointers) -- all against the oracle DP and the reference's vendored edlib."""
+    import random
+    from oracle import edlib_ref as E
+    rng = random.Random(19)
+
+    def rand(n, alpha="ACGT"):
+        return "".join(rng.choice(alpha) for _ in range(n))
+
+    def mutate(a, frac):
+        b = list(a)
+        for _ in range(int(len(a) * frac)):
+            k = rng.randrange(len(b))
+            u = rng.random()
+            if u < 0.33 and len(b) > 1:
+                b.pop(k)
+            elif u < 0.66:
+                b.insert(k, rng.choice("ACGT"))
+            else:
+                b[k] = rng.choice("ACGT")
+        return "".join(b)
+    strs, pairs = [], []
+
+    def add(a, b):
+        strs.extend([a, b])
+        pairs.append((len(strs) - 2, len(strs) - 1))
+    a = rand(8193)
+    add(a, a)                                        # first long size, identical
+    add(a, mutate(a, 0.01))
+    add(a, mutate(a, 0.2))                           # second round
+    add(a, rand(8193))                               # unrelated: full matrix
+    add(rand(9000), rand(17999))
+    a = rand(20011)
+    add(a, mutate(a, 0.004))
+    add(a[:12000], a)                                # delta = 8011: the stripe is shifted
+    add(rand(64), rand(30000))                       # one block against a long text
+    add(rand(8192), rand(8192))                      # largest short pair
+    a = rand(8200)
+    add(a[:4100] + rand(300) + a[4100:], a)          # one long insertion
+    got = ctx.edit_distance_batch(strs, [p[0] for p in pairs], [p[1] for p in pairs])
+    wide = "ABCDEFGHIJKLMNOPQRSTUVWXYZ012345"
+    a = rand(60000, wide)                            # 32 symbols x 938 blocks: 37 words per block > 200 KB -> global scratch
+    w_strs = [a, mutate(a, 0.002), rand(500, wide), rand(700, wide)]
+    w_got = ctx.edit_distance_batch(w_strs, [0, 2, 3], [1, 3, 0])
+    for (i, j), g in zip([(0, 1), (2, 3), (3, 0)], w_got):
+        exp = E.distance(w_strs[i], w_strs[j]) if E.available() else O.edit_distance(w_strs[i], w_strs[j])
+        assert int(g) == exp, (len(w_strs[i]), len(w_strs[j]))
+    for (i, j), g in zip(pairs, got):
+        exp = E.distance(strs[i], strs[j]) if E.available() else O.edit_distance(strs[i], strs[j])
+        assert int(g) == exp, (len(strs[i]), len(strs[j]))
+    for i, j in pairs[:5]:                           # and the two checkers against each other where the DP is quick
+        if E.available():
+            assert E.distance(strs[i], strs[j]) == O.edit_distance(strs[i], strs[j])
+    # the order of a pair does not matter
+    rev = ctx.edit_distance_batch(strs, [p[1] for p in pairs], [p[0] for p in pairs])
+    assert rev.tolist() == got.tolist()
 
 
 def test_clr_contig_gate_golden(ctx):
