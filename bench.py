@@ -468,6 +468,12 @@ def main():
         except Exception as ex:  # noqa: BLE001
             geno = dict(error=str(ex))
 
+    probe = None
+    if world > 1 and not wgs:
+        try:
+            probe = h2d_probe(local, rank, world, dist)
+        except Exception as ex:  # noqa: BLE001
+            probe = dict(error="%s: %s" % (type(ex).__name__, ex))
     edit = None
     if not wgs and rank == 0:
         try:
@@ -534,6 +540,8 @@ def main():
                          pipelining="two shard slots: H2D of shard k+1 overlaps kernels + D2H of shard k",
                          feeder_staging=staged, to_final_vcf=to_vcf),
                 roofline=roof, candidates_per_s=geno, edit_distance=edit)
+    if probe is not None:
+        line["e2e"]["h2d_probe"] = probe
     if not args.no_cpu_baseline and world == 1:              # reported at N=1 only (the host cores are shared by the ranks)
         ref_b, ref_c = (prefix(master, chrom_n[mine[-1]]), shard_cands[-1]) if wgs else shards[0]
         base, _, _ = cpu_baseline(ref_b, ref_c, thr)
@@ -684,6 +692,43 @@ def edit_distance_point(local, cpu=False, n_pair=1000):
                                        sample="first %d pairs, the reference's vendored edlib (oracle/_ref/libedlib_ref.so, "
                                               "EDLIB_MODE_NW, k = -1), %.2f s" % (m, dt), parity=bool(ref == d[:m].tolist()))
     return out
+
+
+def h2d_probe(local, rank, world, dist, nbytes=1 << 30, reps=4):
+    """Pinned-host -> device bandwidth of this box under three schedules (N > 1 only): every rank alone, all ranks at once, and
+    the ranks in two halves one after the other.  What bounds the end-to-end curve is the 'all' aggregate; if 'halves' does not
+    beat it, queueing the uploads cannot help (VERDICT r1 #5)."""
+    import torch
+    hostbuf = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
+    devbuf = torch.empty(nbytes, dtype=torch.uint8, device=torch.device("cuda", local))
+    devbuf.copy_(hostbuf, non_blocking=True)
+    torch.cuda.synchronize()
+
+    def timed(active):
+        dist.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        if active:
+            for _ in range(reps):
+                devbuf.copy_(hostbuf, non_blocking=True)
+            torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        dist.barrier()
+        return dt
+
+    def gmax(x):
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+    gb = nbytes * reps / 1e9
+    alone = [gmax(timed(rank == r)) for r in range(world)]
+    t_all = gmax(timed(True))
+    half = (world + 1) // 2
+    t_half = gmax(timed(rank < half)) + gmax(timed(rank >= half))
+    return dict(bytes_per_rank=nbytes * reps, alone_GBps_per_rank=[gb / t for t in alone], all_at_once_GBps_aggregate=world * gb / t_all,
+                two_halves_GBps_aggregate=world * gb / t_half,
+                note="aggregate pinned-host -> device bandwidth with all ranks copying at once vs in two halves; "
+                     "e2e efficiency at N = (all_at_once aggregate) / (N x alone) because the end-to-end step is upload-bound")
 
 
 def run_sweep(args, rank, world, local):

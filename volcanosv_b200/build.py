@@ -8,7 +8,9 @@ import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-LIB = os.path.join(HERE, "libvolcano_b200.so")
+# profiling variants (tools/scan_ablation.sh): VSV_BUILD_TAG=_x VSV_NVCC_EXTRA="-DVSV_ABLATE_DETECT" build a separate library
+TAG = os.environ.get("VSV_BUILD_TAG", "")
+LIB = os.path.join(HERE, "libvolcano_b200%s.so" % TAG)
 SOURCES = ["vsv_ctx.cu", "vsv_scan.cu", "vsv_merge.cu", "vsv_sa.cu", "vsv_stage2.cu", "vsv_stage3.cu", "vsv_depth.cu", "vsv_edit.cu", "vsv_bam.cu", "vsv_shard.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "--extended-lambda", "-fmad=false", "-Xcompiler", "-fPIC", "-Xcompiler", "-O2"]
@@ -27,13 +29,15 @@ def build(force: bool = False, verbose: bool = False) -> str:
     hdrs.append(os.path.join(HERE, "..", "include", "volcanosv_b200.h"))
     objs = []
     procs = []
-    os.makedirs(os.path.join(HERE, "build"), exist_ok=True)
+    bdir = os.path.join(HERE, "build" + TAG)
+    os.makedirs(bdir, exist_ok=True)
+    extra = os.environ.get("VSV_NVCC_EXTRA", "").split()
     for s in SOURCES:
         src = os.path.join(CSRC, s)
-        obj = os.path.join(HERE, "build", s.replace(".cu", ".o"))
+        obj = os.path.join(bdir, s.replace(".cu", ".o"))
         objs.append(obj)
         if force or _stale(obj, [src] + hdrs):
-            cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", src, "-o", obj]
+            cmd = [nvcc] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-c", src, "-o", obj]
             procs.append((s, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
     failed = False
     for s, p in procs:

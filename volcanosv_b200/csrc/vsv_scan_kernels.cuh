@@ -406,12 +406,20 @@ static __global__ void __launch_bounds__(SCAN_THREADS, SCAN_CTAS_PER_SM) k_scan_
           const uint32_t w = ww[i];
           const uint32_t code = w & 15u, len = w >> 4;
           const uint32_t sel = code * 0x1111u;
-          const uint32_t tr = prmt(TR_LO, TR_HI, sel), tq = prmt(TQ_LO, TQ_HI, sel), tc = prmt(TC_LO, TC_HI, sel);
+#if defined(VSV_ABLATE_LOOP)   // profiling builds only (profiles/r02s_scan.md): stream + scans, no per-op work
+          nr += w;
+          (void)code; (void)len; (void)sel; (void)one;
+#else
+          const uint32_t tr = prmt(TR_LO, TR_HI, sel), tq = prmt(TQ_LO, TQ_HI, sel);
           nr = len * tr + nr;  // IMAD: subtracts len when the code is a member
           nq = len * tq + nq;
+#if !defined(VSV_ABLATE_DETECT)  // profiling builds only: the two sums without candidate / rare-code detection
+          const uint32_t tc = prmt(TC_LO, TC_HI, sel);
           sc = tc * one + sc;  // I/D: -1 each, rare: +0x01010101 each
           mnk = min(mnk, (int32_t)(len * tc));  // I/D: -len (an IMAD: the ALU pipe is the busier one)
           mxc = max(mxc, code);
+#endif
+#endif
         }
       }
       r = 0u - nr;

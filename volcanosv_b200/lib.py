@@ -14,7 +14,7 @@ from typing import Optional
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libvolcano_b200.so")
+LIB_PATH = os.environ.get("VSV_B200_LIB") or os.path.join(_HERE, "libvolcano_b200.so")   # override: profiling builds of the same sources
 
 MODE_CONTIG, MODE_READS, MODE_CUTE = 0, 1, 2
 DEL, INS = 0, 1
