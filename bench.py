@@ -575,19 +575,22 @@ def to_vcf_leg(profile, dtype, host_batch, steps, warm=1):
     for i in range(warm + steps):
         out = tempfile.mkdtemp(prefix="vsv_bench_", dir=base)
         RS.clear()                                 # the shard is rebuilt: H2D of the packed records is inside the timed region
+        OP.STAGE_TIMES.clear()
         t0 = time.perf_counter()
         vcf = OP.large_indel_chr("mem://contigs", cseqs, ref, "mem://reads", out, dtype, 10, "Sample", row_dumps=False)
         data = open(vcf, "rb").read()
         dt = time.perf_counter() - t0
         if i >= warm:
             times.append(dt)
+            for k, v in OP.STAGE_TIMES.items():
+                phases[k] = phases.get(k, 0.0) + v * 1e3 / steps
         n_calls = sum(1 for ln in data.split(b"\n") if ln and not ln.startswith(b"#"))
         n_bytes = len(data)
         shutil.rmtree(out, ignore_errors=True)
     RS.clear()
     dt = float(np.mean(times))
     return dict(value=len(host_batch["pos"]) / dt, unit=UNIT, ms_per_step=dt * 1e3, final_vcf_calls=n_calls, final_vcf_bytes=n_bytes,
-                contig_records=len(cnames), note="product driver large_indel_chr(row_dumps=False): packed host records -> bytes of the "
+                contig_records=len(cnames), stage_ms={k: round(v, 2) for k, v in phases.items()}, note="product driver large_indel_chr(row_dumps=False): packed host records -> bytes of the "
                 "phased VCF; includes the Python text handling of ~10^3 calls through 8 VCF/TSV/CSV files as the reference chains them")
 
 

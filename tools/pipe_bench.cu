@@ -38,6 +38,36 @@ __global__ void __launch_bounds__(256) k(uint32_t* out, uint32_t a, uint32_t b, 
       if (OP == 11) asm volatile("shf.r.wrap.b32 %0, %0, %0, 4;" : "+r"(x[i]));
       if (OP == 12) asm volatile("add.u32 %0, %0, %1;" : "+r"(x[i]) : "r"(a));
       if (OP == 13) asm volatile("dp4a.u32.u32 %0, %0, %1, %2;" : "+r"(x[i]) : "r"(a), "r"(b));
+      if (OP == 14) {  // mix: 1 prmt + 1 dp4a
+        asm volatile("prmt.b32 %0, %0, %1, %2;" : "+r"(x[i]) : "r"(a), "r"(b));
+        asm volatile("dp4a.u32.s32 %0, %1, %2, %0;" : "+r"(x[(i + 1) % NACC]) : "r"(a), "r"(b));
+      }
+      if (OP == 15) {  // the scan kernel's per-op work today: and, shr, mad(sel), 3 prmt, 3 mad, mad + min, max  (12)
+        uint32_t w = x[i], code, len, sel, tr, tq, tc, t;
+        asm volatile("and.b32 %0, %1, 15;" : "=r"(code) : "r"(w));
+        asm volatile("shr.u32 %0, %1, 4;" : "=r"(len) : "r"(w));
+        asm volatile("mul.lo.u32 %0, %1, 0x1111;" : "=r"(sel) : "r"(code));
+        asm volatile("prmt.b32 %0, %1, %2, %3;" : "=r"(tr) : "r"(a), "r"(b), "r"(sel));
+        asm volatile("prmt.b32 %0, %1, %2, %3;" : "=r"(tq) : "r"(b), "r"(a), "r"(sel));
+        asm volatile("prmt.b32 %0, %1, %2, %3;" : "=r"(tc) : "r"(a), "r"(a), "r"(sel));
+        asm volatile("mad.lo.u32 %0, %1, %2, %0;" : "+r"(x[(i + 1) % NACC]) : "r"(len), "r"(tr));
+        asm volatile("mad.lo.u32 %0, %1, %2, %0;" : "+r"(x[(i + 2) % NACC]) : "r"(len), "r"(tq));
+        asm volatile("mad.lo.u32 %0, %1, %2, %0;" : "+r"(x[(i + 3) % NACC]) : "r"(tc), "r"(a));
+        asm volatile("mul.lo.u32 %0, %1, %2;" : "=r"(t) : "r"(len), "r"(tc));
+        asm volatile("min.s32 %0, %0, %1;" : "+r"(x[(i + 4) % NACC]) : "r"(t));
+        asm volatile("max.u32 %0, %0, %1;" : "+r"(x[(i + 5) % NACC]) : "r"(code));
+      }
+      if (OP == 16) {  // candidate per-op work: shr, 3 prmt (selector = the word), 3 dp4a, min  (8)
+        uint32_t w = x[i], len, tr, tq, tc, t;
+        asm volatile("shr.u32 %0, %1, 4;" : "=r"(len) : "r"(w));
+        asm volatile("prmt.b32 %0, %1, %2, %3;" : "=r"(tr) : "r"(a), "r"(b), "r"(w));
+        asm volatile("prmt.b32 %0, %1, %2, %3;" : "=r"(tq) : "r"(b), "r"(a), "r"(w));
+        asm volatile("prmt.b32 %0, %1, %2, %3;" : "=r"(tc) : "r"(a), "r"(a), "r"(w));
+        asm volatile("dp4a.u32.s32 %0, %1, %2, %0;" : "+r"(x[(i + 1) % NACC]) : "r"(len), "r"(tr));
+        asm volatile("dp4a.u32.s32 %0, %1, %2, %0;" : "+r"(x[(i + 2) % NACC]) : "r"(len), "r"(tq));
+        asm volatile("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(t) : "r"(len), "r"(tc), "r"(0));
+        asm volatile("min.s32 %0, %0, %1;" : "+r"(x[(i + 4) % NACC]) : "r"(t));
+      }
     }
   }
   long long t1 = clock64();
@@ -79,6 +109,9 @@ int main() {
   run<11>("shf.r.wrap", 1);
   run<12>("add", 1);
   run<13>("dp4a", 1);
+  run<14>("prmt+dp4a pair", 2);
+  run<15>("scan per-op, today (x12)", 1);
+  run<16>("scan per-op, dp4a (x8)", 1);
   cudaError_t e = cudaGetLastError();
   printf("status: %s\n", cudaGetErrorString(e));
   return e != cudaSuccess;

@@ -56,6 +56,25 @@ WRITE_ROW_DUMPS = True
 _STUB = "# volcanosv_b200: table kept on the device (row dumps off)\n"
 
 
+STAGE_TIMES: Dict[str, float] = {}          # seconds per stage of the last driver run (bench.py reports them; cleared by the caller)
+
+
+class _stage:
+    """with _stage("name"): ...  accumulates wall time into STAGE_TIMES (a stopwatch, no behaviour)."""
+
+    def __init__(self, name):
+        self.name = name
+
+    def __enter__(self):
+        import time
+        self.t0 = time.perf_counter()
+
+    def __exit__(self, *exc):
+        import time
+        STAGE_TIMES[self.name] = STAGE_TIMES.get(self.name, 0.0) + time.perf_counter() - self.t0
+        return False
+
+
 def context(device: Optional[int] = None) -> L.Context:
     """The process-wide library context (one process per GPU: LOCAL_RANK picks the device)."""
     global _ctx
@@ -932,15 +951,19 @@ def filter_gt_correction(vcffile: str, bamfile: Optional[str], reference: Option
                 chr_len = len(reference["chr%d" % chr_num])
             bed = os.path.join(sigdir, "sample.bed")
             _write_lines(bed, ["chr%d\t1\t%d\n" % (chr_num, chr_len)])
-        sig_extract(bamfile, reference, sigdir, include_bed=bed)
+        with _stage("fgc.sig_extract"):
+            sig_extract(bamfile, reference, sigdir, include_bed=bed)
     else:
         sigdir = pre_cutesig
-    signature_support(vcffile, sigdir, chr_num)
-    filtered = filter_by_sig_cov(vcffile, dtype.lower(), "volcano", "DEL")                     # FGC:27,141-145
+    with _stage("fgc.signature_support"):
+        signature_support(vcffile, sigdir, chr_num)
+    with _stage("fgc.filter_by_sig_cov"):
+        filtered = filter_by_sig_cov(vcffile, dtype.lower(), "volcano", "DEL")                 # FGC:27,141-145
     gtdir = os.path.join(wd, "GT_Correction")
     os.makedirs(gtdir, exist_ok=True)
-    correct_gt(filtered, os.path.join(gtdir, "bnd_del_real.tsv"), bamfile, os.path.join(sigdir, "DEL.sigs"), dtype, "DEL")
-    correct_gt(filtered, os.path.join(gtdir, "bnd_ins_real.tsv"), bamfile, os.path.join(sigdir, "INS.sigs"), dtype, "INS")
+    with _stage("fgc.correct_gt"):
+        correct_gt(filtered, os.path.join(gtdir, "bnd_del_real.tsv"), bamfile, os.path.join(sigdir, "DEL.sigs"), dtype, "DEL")
+        correct_gt(filtered, os.path.join(gtdir, "bnd_ins_real.tsv"), bamfile, os.path.join(sigdir, "INS.sigs"), dtype, "INS")
     header, _ = _read_vcf(filtered)
     _write_lines(os.path.join(wd, "header"), header)
     merged = header + open(filtered + ".newgt.DEL").readlines() + open(filtered + ".newgt.INS").readlines()
@@ -1485,7 +1508,8 @@ def raw_variant_call(contig_bam: Optional[str], contig_path: str, reference_path
     os.makedirs(output_dir, exist_ok=True)
     if contig_bam is None:
         contig_bam = align_contigs(contig_path, reference_path, output_dir, n_thread, mem_per_thread)
-    extract_contig_signature(contig_bam, contig_path, reference_path, output_dir, chr_num, dtype, header_file)
+    with _stage("contig_signature"):
+        extract_contig_signature(contig_bam, contig_path, reference_path, output_dir, chr_num, dtype, header_file)
     header = open(header_file).readlines() if header_file else default_header()
     body = []
     import glob
@@ -1494,11 +1518,14 @@ def raw_variant_call(contig_bam: Optional[str], contig_path: str, reference_path
     raw = os.path.join(output_dir, "volcano_raw_variant.vcf")
     _write_lines(raw, header + body)
     if signature_dir is None:
-        extract_reads_signature(rbam_file, output_dir, chr_num)
+        with _stage("reads_signature"):
+            extract_reads_signature(rbam_file, output_dir, chr_num)
         signature_dir = os.path.join(output_dir, "reads_signature")
     filtered = os.path.join(output_dir, "volcano_variant_filtered.vcf")
-    fp_filter(raw, signature_dir, filtered)
-    remove_redundancy(filtered, os.path.join(output_dir, "final_vcf"))
+    with _stage("fp_filter"):
+        fp_filter(raw, signature_dir, filtered)
+    with _stage("remove_redundancy"):
+        remove_redundancy(filtered, os.path.join(output_dir, "final_vcf"))
     return os.path.join(output_dir, "final_vcf", "volcano_variant_no_redundancy.vcf")
 
 
@@ -1694,7 +1721,9 @@ def _large_indel_chr(contig_bam, contig_path, reference, rbam_file, output_dir, 
     else:
         one = ref                                                                          # in memory: nothing to split or index
     raw = raw_variant_call(contig_bam, contig_path, one, out_chr, dtype, chr_num, rbam_file, read_signature_dir, n_thread=n_thread_align)
-    final = filter_gt_correction(raw, rbam_file, reference, dtype, chr_num, pre_cutesig)
+    with _stage("filter_gt_correction"):
+        final = filter_gt_correction(raw, rbam_file, reference, dtype, chr_num, pre_cutesig)
     outfile = os.path.join(out_chr, "%s_volcanosv_large_indel_chr%d.vcf" % (prefix, chr_num))
-    phase_vcf(final, outfile, header_file)
+    with _stage("phase_vcf"):
+        phase_vcf(final, outfile, header_file)
     return outfile
