@@ -323,3 +323,58 @@ def test_record_range_parts_concatenate_to_the_whole(ctx):
     assert np.array_equal(np.concatenate(pa).view(np.uint8), ra.view(np.uint8))
     assert np.array_equal(np.concatenate(pb).view(np.uint8), rb.view(np.uint8))
     assert np.array_equal(np.concatenate(prt), rt)
+
+
+def _segmented_alphabet_batch(seed):
+    """Consecutive stretches of different op alphabets, each tens of tiles long: what a warp of the streaming kernel meets when
+    it walks many tiles (byte path -> v6 loop for 32 tiles -> byte path again)."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    segs = [("m", 300_000), ("eqx", 150_000), ("m", 700_000), ("clips", 120_000), ("rare", 90_000), ("m", 600_000),
+            ("reserved", 40_000), ("long_id", 150_000), ("m", 250_000)]
+    parts = []
+    for kind, n in segs:
+        code = rng.choice(np.array([0, 0, 0, 1, 2], np.uint32), n)
+        ln = rng.integers(0, 40, n).astype(np.uint32)
+        if kind == "eqx":
+            code = rng.choice(np.array([7, 7, 8, 1, 2], np.uint32), n)
+        elif kind == "clips":                       # lengths >= 256 on M / S in ~1 op of 200 (a few lanes per tile)
+            big = rng.random(n) < 0.005
+            ln[big] = rng.integers(256, 70000, int(big.sum()))
+            code[big] = rng.choice(np.array([0, 4], np.uint32), int(big.sum()))
+        elif kind == "rare":                        # N / H / P everywhere: more than six exact lanes per tile
+            code = rng.choice(np.array([0, 1, 2, 3, 5, 6], np.uint32), n)
+        elif kind == "reserved":
+            code = rng.choice(np.arange(16, dtype=np.uint32), n)
+        elif kind == "long_id":                     # I / D of 128..255 bases (the byte path's -128 threshold) and of >= 256
+            big = rng.random(n) < 0.003
+            ln[big] = rng.choice(np.array([127, 128, 129, 255, 256, 257, 4000], np.uint32), int(big.sum()))
+            code[big] = rng.choice(np.array([1, 2], np.uint32), int(big.sum()))
+        parts.append((ln << 4) | code)
+    ops = np.concatenate(parts).astype(np.uint32)
+    n_rec = 700
+    cuts = np.sort(rng.choice(np.arange(1, len(ops)), n_rec - 1, replace=False))
+    off = np.concatenate([[0], cuts, [len(ops)]]).astype(np.int64)
+    pos = np.sort(rng.integers(0, 100_000_000, n_rec)).astype(np.int32)
+    mapq = rng.integers(0, 61, n_rec).astype(np.uint8)
+    return ops, off, pos, mapq
+
+
+@pytest.mark.parametrize("grid", ["1", "3", ""])
+def test_scan_byte_path_switching(ctx, grid, monkeypatch):
+    """The streaming kernel's byte path (dp4a sums, valid for codes <= 7 and lengths < 256) and its per-warp fall-back to the
+    general loop, on an input whose alphabet changes every few dozen tiles; VSV_SCAN_GRID = 1 / 3 makes every warp walk
+    hundreds of consecutive tiles.  Signatures and per-record totals against the oracle, every mode."""
+    ops, off, pos, mapq = _segmented_alphabet_batch(17)
+    if grid:
+        monkeypatch.setenv("VSV_SCAN_GRID", grid)
+    en = (np.arange(len(pos)) % 7 != 3).astype(np.uint8)
+    r, c, rt, qt, xt = ctx.scan_reads_fused(ops, off, pos, mapq, enable_cute=en)
+    er, ert, eqt, ext = O.scan_cigar(ops, off, pos, mapq, V.MODE_READS, 30, 50)
+    ec, *_ = O.scan_cigar(ops, off, pos, mapq, V.MODE_CUTE, 10, 20, enable=en)
+    assert sig_tuples(r) == er and sig_tuples(c) == ec and len(er) > 1000 and len(ec) > 1000
+    assert np.array_equal(rt, ert) and np.array_equal(qt, eqt) and np.array_equal(xt, ext)
+    for mode, minlen, minmq in ((V.MODE_READS, 30, 50), (V.MODE_CUTE, 10, 20)):
+        sigs, rt, qt, xt = ctx.scan_cigar(mode, ops, off, pos, mapq, enable=en, min_len=minlen, min_mapq=minmq)
+        es, ert, eqt, ext = O.scan_cigar(ops, off, pos, mapq, mode, minlen, minmq, enable=en)
+        assert sig_tuples(sigs) == es
+        assert np.array_equal(rt, ert) and np.array_equal(qt, eqt) and np.array_equal(xt, ext)

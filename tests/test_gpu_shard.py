@@ -18,7 +18,8 @@ SIG_FIELDS = ("rec", "type", "pos", "len", "q0", "q1")
 
 def make(profile, n, seed, L_chrom=4_000_000, sa=True, dups=True, n_cand=4000):
     rng = np.random.default_rng(seed)
-    b = synth.synth_records(seed, n, profile, chrom_len=L_chrom, eqx=True)
+    # both alphabets the aligners write: 'M' (the streaming kernel's byte path) for three of the seeds, '='/'X' for the rest
+    b = synth.synth_records(seed, n, profile, chrom_len=L_chrom, eqx=seed not in (31, 9, 13))
     if dups:
         b = synth.add_duplicates(b, rng)
     b["next_same_name"] = L.next_same_name(b["name_id"])

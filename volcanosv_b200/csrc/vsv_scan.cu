@@ -26,6 +26,7 @@ static int run_scan_kernels(vsv_ctx* ctx, const ScanParams& p_in, int grid, Tile
   p.tab[0] = tab_word(M::REF, 0, 0xFFu, 0, 0); p.tab[1] = tab_word(M::REF, 4, 0xFFu, 0, 0);
   p.tab[2] = tab_word(M::QRY, 0, 0xFFu, 0, 0); p.tab[3] = tab_word(M::QRY, 4, 0xFFu, 0, 0);
   p.tab[4] = tab_word(6u, 0, 0xFFu, RARE, 0x01u); p.tab[5] = tab_word(6u, 4, 0xFFu, RARE, 0x01u);
+  p.tab[6] = tab_word(6u, 0, 0xFFu, RARE, 0x80u); p.tab[7] = tab_word(6u, 4, 0xFFu, RARE, 0x80u);
   VSV_CUDA(ctx, cudaEventRecord(ctx->evk0, ctx->stream));
   VSV_CUDA(ctx, cudaFuncSetAttribute(k_scan_wt<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SCAN_SMEM));
   VSV_LAUNCH(ctx, k_scan_wt<MODE>, (unsigned)grid, SCAN_THREADS, SCAN_SMEM, p);
@@ -100,7 +101,7 @@ static int scan_impl(vsv_ctx* ctx, const ScanCall& c) {
     VSV_TRY(vsv_out(ctx, c.qry_total, (size_t)c.n_rec, &d_qt));
     VSV_TRY(vsv_out(ctx, c.aux_total, (size_t)c.n_rec, &d_xt));
   }
-  const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(vsv_cdiv(n_wt, SCAN_WARPS), (int64_t)ctx->sm_count * SCAN_CTAS_PER_SM));
+  const int grid = vsv_scan_grid(ctx, n_wt);
   // staging holds one entry per RAW candidate (before the record gates), reserved per warp in
   // chunks, so the exact need is only known after a run: start from the caller's capacities and
   // retry (rare) with the measured reservation if a warp found the staging full.

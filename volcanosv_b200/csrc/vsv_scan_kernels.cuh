@@ -34,6 +34,9 @@
 // __syncthreads) were bound by that serial phase at 23-25 %; v5 (warp-independent, per-op
 // candidate test) reached 52 %; v6 is ALU-issue bound at 66 % (profiles/r01c_scan_v6.md).
 #pragma once
+#include <stdlib.h>
+
+#include <algorithm>
 #include "vsv_common.cuh"
 
 #define WT_OPS 1024           // ops per warp tile
@@ -154,7 +157,7 @@ struct ScanParams {
   int32_t n_wt;              // number of warp tiles
   uint32_t min_w;            // min candidate length << 4
   uint32_t one;              // 1 (opaque multiplier: keeps an accumulate on the FMA pipe)
-  uint32_t tab[6];           // PRMT byte tables by op code: REF lo/hi, QRY lo/hi, candidate/rare lo/hi
+  uint32_t tab[8];           // PRMT byte tables by op code: REF lo/hi, QRY lo/hi, candidate/rare lo/hi (v6), I/D -1 | rare -128 lo/hi (v8)
   int32_t min_len_a, min_len_b;
   const int2* wt_starts;     // [first,last] record (index in 0..n_rec) whose start lies in the tile
   TileState* wt_agg;         // [n_wt + 1] aggregates (last = identity), counts filled by k_gate
@@ -284,6 +287,24 @@ __device__ __forceinline__ uint32_t prmt(uint32_t lo, uint32_t hi, uint32_t sel)
   return d;
 }
 
+// CTAs of the streaming kernel: one per resident slot.  VSV_SCAN_GRID caps it (tests: many tiles per warp from a small input,
+// which is what exercises the byte-path / v6 switching of a warp over consecutive tiles).
+static inline int vsv_scan_grid(const vsv_ctx* ctx, int64_t n_wt) {
+  int64_t g = std::max<int64_t>(1, std::min<int64_t>(vsv_cdiv(n_wt, SCAN_WARPS), (int64_t)ctx->sm_count * SCAN_CTAS_PER_SM));
+  if (const char* e = getenv("VSV_SCAN_GRID")) {
+    const long v = strtol(e, nullptr, 10);
+    if (v > 0) g = std::min<int64_t>(g, v);
+  }
+  return (int)g;
+}
+
+// d = c + sum of (unsigned byte i of a) * (signed byte i of b)
+__device__ __forceinline__ uint32_t dp4a_us(uint32_t a, uint32_t b, uint32_t c) {
+  uint32_t d;
+  asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+  return d;
+}
+
 // ---- K1: the streaming kernel (every warp is an independent worker) --------------------
 template <int MODE>
 static __global__ void __launch_bounds__(SCAN_THREADS, SCAN_CTAS_PER_SM) k_scan_wt(const ScanParams p) {
@@ -317,11 +338,12 @@ static __global__ void __launch_bounds__(SCAN_THREADS, SCAN_CTAS_PER_SM) k_scan_
       }
     }
   }
-  uint32_t tabs[6];
-  if (lane < 6) s_tab[warp][lane] = p.tab[lane];
+  uint32_t tabs[8];
+  if (lane < 8) s_tab[warp][lane] = p.tab[lane];
   __syncwarp();
 #pragma unroll
-  for (int k = 0; k < 6; ++k) tabs[k] = *reinterpret_cast<volatile uint32_t*>(&s_tab[warp][k]);
+  for (int k = 0; k < 8; ++k) tabs[k] = *reinterpret_cast<volatile uint32_t*>(&s_tab[warp][k]);
+  int classic_left = 0;  // > 0: this warp runs the v6 loop for that many more tiles before probing the byte path again
   int2 cur = make_int2(0, -1), nxt = make_int2(0, -1);
   if (gw < n_wt) cur = __ldg(p.wt_starts + gw);
   if (gw + TW < n_wt) nxt = __ldg(p.wt_starts + gw + TW);
@@ -394,37 +416,83 @@ static __global__ void __launch_bounds__(SCAN_THREADS, SCAN_CTAS_PER_SM) k_scan_
       // 128-byte rows: physical uint4 (k ^ rot) of the row = byte address (row ^ rot*16) ^ k*16
       const uint32_t row_x = (smem_u32(tl) + (uint32_t)lane * (WT_VPT * 4u)) ^ ((uint32_t)(lane & 7) << 4);
       const uint32_t one = p.one;  // == 1, opaque to the compiler: keeps `sc` on the FMA pipe
-      uint32_t nr = 0, nq = 0, mxc = 0, sc = 0;
+      uint32_t nr = 0, nq = 0;
       int32_t mnk = 0;
+      // -- v8 byte path.  When every op of the tile has a code <= 7 and a length < 256 (M-alphabet long reads: all but a
+      // few ops) the op word itself is the PRMT selector (its low nibble is the code; the other result bytes are garbage)
+      // and dp4a(len, table bytes) multiplies the length, whose upper three bytes are zero, by the signed table byte of
+      // the code: no `code`, no selector, no mask widening -- shr + 3 prmt + 3 dp4a + min per op instead of 12
+      // instructions (tools/pipe_bench.cu: 5.8 vs 14.4 cycles per op slot).  The third table holds -1 for I/D and -128
+      // for N/H/P, so one running minimum finds both the lanes with a candidate (<= -min_len) and the lanes that need the
+      // exact recomputation (<= -128: a rare code, or an I/D of 128+ bases).  The OR of the lane's words tells whether
+      // the assumptions held: a length >= 256 sends the lane to the exact path; a code >= 8 (X of an =/X alphabet, or
+      // a reserved code), or more than six such lanes, sends the whole tile through the v6 loop below, and the warp
+      // stays on v6 for the next 31 tiles before it probes again (=/X or HiFi-like files cost one probe in 32).
+      bool classic = classic_left > 0;
+#if !defined(VSV_ABLATE_LOOP) && !defined(VSV_ABLATE_DETECT) && !defined(VSV_NO_BYTE_PATH)
+      if (!classic) {
+        const uint32_t TF_LO = tabs[6], TF_HI = tabs[7];
+        uint32_t orw = 0;
 #pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        uint4 v;
-        asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(row_x ^ (uint32_t)(k << 4)));
-        const uint32_t ww[4] = {v.x, v.y, v.z, v.w};
+        for (int k = 0; k < 8; ++k) {
+          uint4 v;
+          asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(row_x ^ (uint32_t)(k << 4)));
+          const uint32_t ww[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const uint32_t w = ww[i];
-          const uint32_t code = w & 15u, len = w >> 4;
-          const uint32_t sel = code * 0x1111u;
-#if defined(VSV_ABLATE_LOOP)   // profiling builds only (profiles/r02s_scan.md): stream + scans, no per-op work
-          nr += w;
-          (void)code; (void)len; (void)sel; (void)one;
-#else
-          const uint32_t tr = prmt(TR_LO, TR_HI, sel), tq = prmt(TQ_LO, TQ_HI, sel);
-          nr = len * tr + nr;  // IMAD: subtracts len when the code is a member
-          nq = len * tq + nq;
-#if !defined(VSV_ABLATE_DETECT)  // profiling builds only: the two sums without candidate / rare-code detection
-          const uint32_t tc = prmt(TC_LO, TC_HI, sel);
-          sc = tc * one + sc;  // I/D: -1 each, rare: +0x01010101 each
-          mnk = min(mnk, (int32_t)(len * tc));  // I/D: -len (an IMAD: the ALU pipe is the busier one)
-          mxc = max(mxc, code);
-#endif
-#endif
+          for (int i = 0; i < 4; ++i) {
+            const uint32_t w = ww[i];
+            const uint32_t len = w >> 4;
+            const uint32_t tr = prmt(TR_LO, TR_HI, w), tq = prmt(TQ_LO, TQ_HI, w), tf = prmt(TF_LO, TF_HI, w);
+            nr = dp4a_us(len, tr, nr);
+            nq = dp4a_us(len, tq, nq);
+            mnk = min(mnk, (int32_t)dp4a_us(len, tf, 0u));
+          }
+          orw |= (v.x | v.y) | (v.z | v.w);
         }
+        lane_rare = orw >= 4096u || mnk <= -128;
+        const uint32_t xb = __ballot_sync(FULL, (orw & 8u) != 0u), rb = __ballot_sync(FULL, lane_rare);
+        if (xb != 0u || __popc(rb) > 6) {
+          classic = true;
+          classic_left = 32;
+          nr = 0; nq = 0; mnk = 0;
+        }
+      }
+#else
+      classic = true;
+#endif
+      if (classic) {
+        --classic_left;
+        uint32_t mxc = 0, sc = 0;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          uint4 v;
+          asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(row_x ^ (uint32_t)(k << 4)));
+          const uint32_t ww[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const uint32_t w = ww[i];
+            const uint32_t code = w & 15u, len = w >> 4;
+            const uint32_t sel = code * 0x1111u;
+#if defined(VSV_ABLATE_LOOP)   // profiling builds only (profiles/r02s_scan.md): stream + scans, no per-op work
+            nr += w;
+            (void)code; (void)len; (void)sel; (void)one;
+#else
+            const uint32_t tr = prmt(TR_LO, TR_HI, sel), tq = prmt(TQ_LO, TQ_HI, sel);
+            nr = len * tr + nr;  // IMAD: subtracts len when the code is a member
+            nq = len * tq + nq;
+#if !defined(VSV_ABLATE_DETECT)  // profiling builds only: the two sums without candidate / rare-code detection
+            const uint32_t tc = prmt(TC_LO, TC_HI, sel);
+            sc = tc * one + sc;  // I/D: -1 each, rare: +0x01010101 each
+            mnk = min(mnk, (int32_t)(len * tc));  // I/D: -len (an IMAD: the ALU pipe is the busier one)
+            mxc = max(mxc, code);
+#endif
+#endif
+          }
+        }
+        lane_rare = (int32_t)sc > 0 || mxc > 8u;  // a rare code (N/H/P...) or a reserved one (9..15)
       }
       r = 0u - nr;
       q = 0u - nq;
-      lane_rare = (int32_t)sc > 0 || mxc > 8u;  // a rare code (N/H/P...) or a reserved one (9..15)
       lane_cand = mnk <= -(int32_t)(min_w >> 4) || lane_rare;  // rare lanes: mnk is not trustworthy
     }
     // -- rare lanes: exact sums of every class, by the whole warp ---------------------------------

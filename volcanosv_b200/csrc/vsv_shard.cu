@@ -1232,7 +1232,7 @@ extern "C" int vsv_shard_scan(vsv_shard* s) {
   const Caps cap = s->cap;
   const int64_t cap_total = cap.r + cap.d + cap.i + n_rec;
   if (cap_total >= (int64_t(1) << 31)) VSV_FAIL(ctx, VSV_E_ARG, "vsv_shard_scan: table capacities exceed 2^31 rows");
-  const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(vsv_cdiv(n_wt, SCAN_WARPS), (int64_t)ctx->sm_count * SCAN_CTAS_PER_SM));
+  const int grid = vsv_scan_grid(ctx, n_wt);
   const int64_t slack = (int64_t)grid * SCAN_WARPS * SCAN_CHUNK + SCAN_CHUNK;
   const int64_t scap = std::max(s->stage_cap, std::max(cap.r, cap.c) * 5 / 4 + slack);
   if (scap >= (int64_t(1) << 32) - 1) VSV_FAIL(ctx, VSV_E_ARG, "vsv_shard_scan: staging capacity out of range");
@@ -1303,6 +1303,7 @@ extern "C" int vsv_shard_scan(vsv_shard* s) {
   p.tab[0] = tab_word(M::REF, 0, 0xFFu, 0, 0); p.tab[1] = tab_word(M::REF, 4, 0xFFu, 0, 0);
   p.tab[2] = tab_word(M::QRY, 0, 0xFFu, 0, 0); p.tab[3] = tab_word(M::QRY, 4, 0xFFu, 0, 0);
   p.tab[4] = tab_word(6u, 0, 0xFFu, RARE, 0x01u); p.tab[5] = tab_word(6u, 4, 0xFFu, RARE, 0x01u);
+  p.tab[6] = tab_word(6u, 0, 0xFFu, RARE, 0x80u); p.tab[7] = tab_word(6u, 4, 0xFFu, RARE, 0x80u);
   p.wt_starts = (const int2*)s->starts.p; p.wt_agg = (TileState*)s->agg.p; p.wt_stage = (uint2*)s->wstage.p;
   p.fstart = (uint4*)s->fstart.p;
   p.stage = (StageEntry*)s->stage.p; p.stage_cap = (uint32_t)scap;
