@@ -441,6 +441,18 @@ int vsv_shard_scan_kernel_ms(vsv_shard* s, float* ms);
 int vsv_span_depth_sorted(vsv_ctx* ctx, const int32_t* read_start, const int32_t* read_end, const int32_t* sorted_end,
                           int64_t n_reads, const int32_t* S, const int32_t* E, int64_t n_win, int32_t* depth);
 
+/* vsv_span_depth for callers that cannot allocate.  NO COUNTERPART IN THE REFERENCE: added
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  Same result as
+ * vsv_span_depth; its temporaries (the ascending copy of the read ends and the sort's work space) live in one fixed
+ * file-scope device array (17 MiB, held by every GPU that loads the library until exit), so the call performs no
+ * cudaMalloc / cudaFree and touches no arena.  Requirements: a device-IO context (every pointer is a DEVICE pointer;
+ * else VSV_E_ARG); n_reads <= VSV_NOALLOC_MAX_READS (else VSV_E_CAPACITY); the first call on a device resolves the
+ * array's address and should be made outside a graph capture.  The array is shared by all calls on a device and keeps
+ * the last call's contents: calls that overlap on the GPU race on it -- serialise them.  Asynchronous on the ctx's stream. */
+#define VSV_NOALLOC_MAX_READS (1 << 21)
+int vsv_span_depth_noalloc(vsv_ctx* ctx, const int32_t* read_start, const int32_t* read_end, int64_t n_reads,
+                           const int32_t* S, const int32_t* E, int64_t n_win, int32_t* depth);
+
 /* ---- host-side BAM feeder (no CUDA; zlib + threads) ------------------------------------- */
 /* Replaces `pysam.AlignmentFile(path).fetch(chr)` and the per-record attribute reads of the
  * whole-chromosome scans (LI/extract_reads_signature.py:107-145, LI/sig_extract.py:514-560,

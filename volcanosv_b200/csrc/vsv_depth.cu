@@ -139,3 +139,62 @@ extern "C" int vsv_genotype(vsv_ctx* ctx, const int32_t* read_start, const int32
   VSV_TRY(vsv_out_done(ctx, new_gt, ng, (size_t)n_cand));
   return vsv_end(ctx);
 }
+
+// --------------------------------------------------------------------------------
+// vsv_span_depth_noalloc: the span-depth entry for callers that cannot allocate
+// --------------------------------------------------------------------------------
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (CUDA graph capture, tight serving loops, harnesses that forbid it).  vsv_span_depth keeps two temporaries in the
+// context's arena (the ascending copy of the read ends and the radix sort's work space); here both live in ONE file-scope
+// device array of fixed size, so the call allocates nothing: no cudaMalloc / cudaFree, no arena, no allocating library
+// routine (cub::DeviceRadixSort is handed its work space).  Every GPU that loads the library holds the array until exit.
+//   * limit: n_reads <= VSV_NOALLOC_MAX_READS (2^21); more is VSV_E_CAPACITY.  n_win is unlimited (the caller owns S/E/depth).
+//   * the array is shared by every call on a device and keeps the last call's contents.  Nothing in it has to start at
+//     zero: the sort overwrites the n_reads ends it is about to read and clears its own counters on the stream.  Calls that
+//     overlap on the GPU (two streams or two contexts of one device) race on it: serialise them.
+//   * in host code `g_noalloc_scratch` is only a handle: the device address comes from cudaGetSymbolAddress, taken once per
+//     device with that device current (first call on the device; make that call outside a graph capture).
+#define VSV_NOALLOC_SORT_BYTES ((size_t)VSV_NOALLOC_MAX_READS * sizeof(int32_t))
+#define VSV_NOALLOC_WORK_BYTES (VSV_NOALLOC_SORT_BYTES + (size_t)(1 << 20))   // alternate key buffer + histograms of the sort
+#define VSV_NOALLOC_BYTES (VSV_NOALLOC_SORT_BYTES + VSV_NOALLOC_WORK_BYTES)   // 17 MiB
+static __device__ __align__(256) unsigned char g_noalloc_scratch[VSV_NOALLOC_BYTES];
+
+#define VSV_NOALLOC_MAX_DEVICES 64
+static unsigned char* g_noalloc_ptr[VSV_NOALLOC_MAX_DEVICES];   // device address of the array, per device (nullptr: not taken yet)
+
+extern "C" int vsv_span_depth_noalloc(vsv_ctx* ctx, const int32_t* read_start, const int32_t* read_end, int64_t n_reads,
+                                      const int32_t* S, const int32_t* E, int64_t n_win, int32_t* depth) {
+  if (!ctx) return VSV_E_ARG;
+  ctx->err.clear();
+  if (!ctx->device_io)
+    VSV_FAIL(ctx, VSV_E_ARG, "vsv_span_depth_noalloc: device pointers only (vsv_ctx_set_device_io(ctx, 1)): staging host buffers would allocate");
+  if (n_reads < 0 || n_win < 0 || (n_reads > 0 && (!read_start || !read_end)) || (n_win > 0 && (!S || !E || !depth)))
+    VSV_FAIL(ctx, VSV_E_ARG, "vsv_span_depth_noalloc: bad argument");
+  if (n_reads > (int64_t)VSV_NOALLOC_MAX_READS)
+    VSV_FAIL(ctx, VSV_E_CAPACITY, "vsv_span_depth_noalloc: " + std::to_string((long long)n_reads) + " reads exceed the fixed scratch of " +
+                                      std::to_string((long long)VSV_NOALLOC_MAX_READS) + " reads (VSV_NOALLOC_MAX_READS); use vsv_span_depth");
+  if (ctx->device < 0 || ctx->device >= VSV_NOALLOC_MAX_DEVICES) VSV_FAIL(ctx, VSV_E_ARG, "vsv_span_depth_noalloc: device index out of range");
+  if (n_win == 0) return VSV_OK;
+  VSV_CUDA(ctx, cudaSetDevice(ctx->device));
+  unsigned char* base = g_noalloc_ptr[ctx->device];
+  if (base == nullptr) {   // set-up, once per device, with that device current
+    void* p = nullptr;
+    VSV_CUDA(ctx, cudaGetSymbolAddress(&p, g_noalloc_scratch));
+    if (p == nullptr) VSV_FAIL(ctx, VSV_E_CUDA, "vsv_span_depth_noalloc: cudaGetSymbolAddress returned a null address");
+    base = g_noalloc_ptr[ctx->device] = (unsigned char*)p;
+  }
+  int32_t* sorted = reinterpret_cast<int32_t*>(base);
+  void* work = base + VSV_NOALLOC_SORT_BYTES;
+  if (n_reads > 0) {
+    size_t need = 0;
+    VSV_CUDA(ctx, cub::DeviceRadixSort::SortKeys(nullptr, need, read_end, sorted, (int)n_reads, 0, 32, ctx->stream));
+    if (need > VSV_NOALLOC_WORK_BYTES) VSV_FAIL(ctx, VSV_E_CAPACITY, "vsv_span_depth_noalloc: the sort's work space does not fit the fixed scratch");
+    size_t have = VSV_NOALLOC_WORK_BYTES;
+    VSV_CUDA(ctx, cub::DeviceRadixSort::SortKeys(work, have, read_end, sorted, (int)n_reads, 0, 32, ctx->stream));
+    ctx->launches += 6;
+  }
+  VSV_LAUNCH(ctx, k_span_depth_closed, (unsigned)vsv_cdiv(n_win, 256), 256, 0, read_start, read_end, (const int32_t*)sorted, n_reads, S, E,
+             n_win, depth);
+  VSV_CUDA(ctx, cudaGetLastError());
+  return VSV_OK;   // asynchronous on the context's stream, like every device-IO call
+}

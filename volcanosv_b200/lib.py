@@ -107,6 +107,7 @@ SIGNATURES = {
     "vsv_sync": [_vp],
     "vsv_alloc_pinned": [C.POINTER(_vp), C.c_size_t],
     "vsv_free_pinned": [_vp],
+    "vsv_span_depth_noalloc": [_vp, _vp, _vp, _i64, _vp, _vp, _i64, _vp],
     "vsv_get_timing": [_vp, C.POINTER(C.c_float), C.POINTER(_i64)],
     "vsv_version": [],
     "vsv_timer_start": [_vp],
