@@ -298,6 +298,23 @@ static inline int vsv_scan_grid(const vsv_ctx* ctx, int64_t n_wt) {
   return (int)g;
 }
 
+// one step of three interleaved inclusive warp scans: the shuffle's own predicate (source lane in range) guards the adds
+__device__ __forceinline__ void scan3_step(uint32_t& a, uint32_t& b, uint32_t& c, int d) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      ".reg .b32 t0, t1, t2;\n"
+      "shfl.sync.up.b32 t0|p, %0, %3, 0, 0xffffffff;\n"
+      "shfl.sync.up.b32 t1, %1, %3, 0, 0xffffffff;\n"
+      "shfl.sync.up.b32 t2, %2, %3, 0, 0xffffffff;\n"
+      "@p add.u32 %0, %0, t0;\n"
+      "@p add.u32 %1, %1, t1;\n"
+      "@p add.u32 %2, %2, t2;\n"
+      "}\n"
+      : "+r"(a), "+r"(b), "+r"(c)
+      : "r"(d));
+}
+
 // d = c + sum of (unsigned byte i of a) * (signed byte i of b)
 __device__ __forceinline__ uint32_t dp4a_us(uint32_t a, uint32_t b, uint32_t c) {
   uint32_t d;
@@ -348,6 +365,9 @@ static __global__ void __launch_bounds__(SCAN_THREADS, SCAN_CTAS_PER_SM) k_scan_
   if (gw < n_wt) cur = __ldg(p.wt_starts + gw);
   if (gw + TW < n_wt) nxt = __ldg(p.wt_starts + gw + TW);
   unsigned long long ch_next = 0, ch_end = 0;  // this warp's staging chunk (lane 0)
+  // record-start offsets of the CURRENT tile, loaded one tile ahead (the load's round trip hides behind a whole tile)
+  int64_t off_cur = 0;
+  if (lane <= cur.y - cur.x) off_cur = __ldg(p.op_off + cur.x + lane);
 
   int it = 0;
   for (uint32_t wt = gw; wt < n_wt; wt += TW, ++it) {
@@ -356,10 +376,11 @@ static __global__ void __launch_bounds__(SCAN_THREADS, SCAN_CTAS_PER_SM) k_scan_
     const int64_t wt_start = (int64_t)wt * WT_OPS;
     uint32_t* tl = s_ops[warp][stage];
 
-    // record starts inside this tile: issue the offset loads before waiting for the ops
+    // record starts inside this tile (offsets prefetched during the previous tile); next tile's offsets are issued here
     const int nst = cur.y - cur.x + 1;
-    int32_t sx = 0;
-    if (lane < nst) sx = (int32_t)(__ldg(p.op_off + cur.x + lane) - wt_start);
+    const int32_t sx = lane < nst ? (int32_t)(off_cur - wt_start) : 0;
+    int64_t off_nxt = 0;
+    if (lane <= nxt.y - nxt.x) off_nxt = __ldg(p.op_off + nxt.x + lane);
     int2 nn = make_int2(0, -1);
     if (wt + 2 * TW < n_wt) nn = __ldg(p.wt_starts + wt + 2 * TW);
 
@@ -530,24 +551,14 @@ static __global__ void __launch_bounds__(SCAN_THREADS, SCAN_CTAS_PER_SM) k_scan_
     // -- warp scans (inclusive) ---------------------------------------------------------------
     uint32_t ir = r, iq = q, ic = c;
 #pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-      const uint32_t a = __shfl_up_sync(FULL, ir, d);
-      const uint32_t b = __shfl_up_sync(FULL, iq, d);
-      const uint32_t e = __shfl_up_sync(FULL, ic, d);
-      if (lane >= d) { ir += a; iq += b; ic += e; }
-    }
+    for (int d = 1; d < 32; d <<= 1) scan3_step(ir, iq, ic, d);
     Sums ex = {ir - r, iq - q, 0, 0, 0};  // this lane's exclusive prefix inside the tile
     Sums tot = {__shfl_sync(FULL, ir, 31), __shfl_sync(FULL, iq, 31), 0, 0, 0};
     const uint32_t myoff = ic - c, coff = __shfl_sync(FULL, ic, 31);
     if (anyrare) {  // this warp saw N / H / P / ...: scan the rare sums too
       uint32_t i1 = xs.x1, i2 = xs.x2, i3 = xs.x3;
 #pragma unroll
-      for (int d = 1; d < 32; d <<= 1) {
-        const uint32_t a = __shfl_up_sync(FULL, i1, d);
-        const uint32_t b = __shfl_up_sync(FULL, i2, d);
-        const uint32_t e = __shfl_up_sync(FULL, i3, d);
-        if (lane >= d) { i1 += a; i2 += b; i3 += e; }
-      }
+      for (int d = 1; d < 32; d <<= 1) scan3_step(i1, i2, i3, d);
       ex.x1 = i1 - xs.x1; ex.x2 = i2 - xs.x2; ex.x3 = i3 - xs.x3;
       tot.x1 = __shfl_sync(FULL, i1, 31); tot.x2 = __shfl_sync(FULL, i2, 31); tot.x3 = __shfl_sync(FULL, i3, 31);
     }
@@ -624,6 +635,7 @@ static __global__ void __launch_bounds__(SCAN_THREADS, SCAN_CTAS_PER_SM) k_scan_
     }
     cur = nxt;
     nxt = nn;
+    off_cur = off_nxt;
   }
 }
 
