@@ -752,6 +752,103 @@ static __global__ void __launch_bounds__(TS_THREADS) k_ts_scan(const TileState* 
   }
 }
 
+// ---- the same scan in ONE launch: decoupled look-back over ticket-ordered blocks (resident shard engine) ----------------
+// Block b (ticket order, so every predecessor is running or done) publishes its aggregate, warp 0 polls 32 predecessor
+// descriptors at a time until it meets an inclusive prefix, folds them in index order (the operator is associative but not
+// commutative: a tile in which a record starts resets the sums) and publishes the block's inclusive prefix.  Descriptor =
+// flag (0 nothing, 1 aggregate, 2 inclusive prefix) + two 32-byte payloads; the host clears flags and ticket before the launch.
+struct __align__(16) TsDesc {
+  uint32_t flag, pad0, pad1, pad2;
+  TileState agg, inc;
+};
+__device__ __forceinline__ TileState ts_load_volatile(const TileState* p) {
+  uint4 a, b;
+  asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w) : "l"(p) : "memory");
+  asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w)
+               : "l"(reinterpret_cast<const uint4*>(p) + 1)
+               : "memory");
+  TileState t;
+  t.r = a.x; t.q = a.y; t.x1 = a.z; t.x2 = a.w; t.x3 = b.x; t.cnt_a = b.y; t.cnt_b = b.z; t.flag = b.w;
+  return t;
+}
+__device__ __forceinline__ TileState ts_shfl(const TileState& t, int src) {
+  TileState o;
+  o.r = __shfl_sync(0xffffffffu, t.r, src); o.q = __shfl_sync(0xffffffffu, t.q, src);
+  o.x1 = __shfl_sync(0xffffffffu, t.x1, src); o.x2 = __shfl_sync(0xffffffffu, t.x2, src);
+  o.x3 = __shfl_sync(0xffffffffu, t.x3, src); o.cnt_a = __shfl_sync(0xffffffffu, t.cnt_a, src);
+  o.cnt_b = __shfl_sync(0xffffffffu, t.cnt_b, src); o.flag = __shfl_sync(0xffffffffu, t.flag, src);
+  return o;
+}
+static __global__ void __launch_bounds__(TS_THREADS) k_ts_scan1(const TileState* __restrict__ in, int64_t n, TsDesc* __restrict__ desc,
+                                                           unsigned int* __restrict__ ticket, TileState* __restrict__ out) {
+  __shared__ TileState s_w[TS_THREADS / 32];
+  __shared__ TileState s_last[TS_THREADS / 32];
+  __shared__ TileState s_bex;
+  __shared__ unsigned int s_tile;
+  const TileStateOp op;
+  if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u);
+  __syncthreads();
+  const unsigned int tile = s_tile;
+  const int64_t base = (int64_t)tile * TS_BLOCK + (int64_t)threadIdx.x * TS_ITEMS;
+  TileState it[TS_ITEMS];
+  TileState v = ts_identity();
+#pragma unroll
+  for (int k = 0; k < TS_ITEMS; ++k) {
+    it[k] = ts_identity();
+    if (base + k < n) it[k] = ts_load(in + base + k);
+    v = op(v, it[k]);
+  }
+  TileState total;
+  const TileState inc = ts_block_scan(v, s_w, total);
+  TileState pre = ts_shfl_up(inc, 1);  // inclusive value of the previous thread
+  if ((threadIdx.x & 31) == 31) s_last[threadIdx.x >> 5] = inc;
+  if (threadIdx.x < 32) {              // warp 0: the look-back
+    const int lane = threadIdx.x;
+    TileState excl = ts_identity();
+    if (tile == 0) {
+      if (lane == 0) {
+        ts_store(&desc[0].inc, total);
+        __threadfence();
+        st_release_u32(&desc[0].flag, 2u);
+      }
+    } else {
+      if (lane == 0) {
+        ts_store(&desc[tile].agg, total);
+        __threadfence();
+        st_release_u32(&desc[tile].flag, 1u);
+      }
+      for (int64_t b0 = (int64_t)tile - 1;; b0 -= 32) {
+        const int64_t j = b0 - lane;     // lane 0 looks at the nearest predecessor
+        unsigned int f = 2u;
+        TileState val = ts_identity();
+        if (j >= 0) {
+          do { f = ld_acquire_u32(&desc[j].flag); } while (f == 0u);
+          val = ts_load_volatile(f == 2u ? &desc[j].inc : &desc[j].agg);
+        }
+        const unsigned int m2 = __ballot_sync(0xffffffffu, f == 2u);
+        const int last = m2 ? __ffs(m2) - 1 : 31;
+        for (int k = 0; k <= last; ++k) excl = op(ts_shfl(val, k), excl);   // older on the left
+        if (m2) break;
+      }
+      if (lane == 0) {
+        ts_store(&desc[tile].inc, op(excl, total));
+        __threadfence();
+        st_release_u32(&desc[tile].flag, 2u);
+      }
+    }
+    if (lane == 0) s_bex = excl;
+  }
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) pre = threadIdx.x == 0 ? ts_identity() : s_last[(threadIdx.x >> 5) - 1];
+  pre = op(s_bex, pre);
+#pragma unroll
+  for (int k = 0; k < TS_ITEMS; ++k) {
+    if (base + k < n) ts_store(out + base + k, pre);
+    pre = op(pre, it[k]);
+  }
+}
+
 // ---- sparse follow-up kernels (lane-dense: one thread per candidate / warp tile / record) ----
 // k_gate: one thread per staging slot.  A slot is live when the tile named in it (field b,
 // written by the streaming kernel) reserved a range that contains the slot: chunk tails and

@@ -1248,7 +1248,7 @@ extern "C" int vsv_shard_scan(vsv_shard* s) {
   VSV_TRY(dbuf_ensure(ctx, s->wstage, ((size_t)n_wt + 1) * sizeof(uint2)));
   VSV_TRY(dbuf_ensure(ctx, s->fstart, 2 * ((size_t)n_rec + 1) * sizeof(uint4)));
   VSV_TRY(dbuf_ensure(ctx, s->stage, (size_t)scap * sizeof(StageEntry)));
-  VSV_TRY(dbuf_ensure(ctx, s->blk, (size_t)nb * sizeof(TileState)));
+  VSV_TRY(dbuf_ensure(ctx, s->blk, (size_t)(nb + 1) * sizeof(TsDesc)));   // look-back descriptors; the slot after them holds the ticket
   VSV_TRY(dbuf_ensure(ctx, s->ref_end, (size_t)n_rec * 4));
   VSV_TRY(dbuf_ensure(ctx, s->readlen, (size_t)n_rec * 4));
   VSV_TRY(dbuf_ensure(ctx, s->in_bed, (size_t)n_rec));
@@ -1329,9 +1329,10 @@ extern "C" int vsv_shard_scan(vsv_shard* s) {
     const unsigned gs = (unsigned)std::min<int64_t>(vsv_cdiv(scap, 256), (int64_t)ctx->sm_count * 8);
     VSV_LAUNCH(ctx, k_gate<VSV_MODE_FUSED>, gs, 256, 0, p);
     const int64_t n_el = (int64_t)n_wt + 1;
-    VSV_LAUNCH(ctx, k_ts_reduce, (unsigned)nb, TS_THREADS, 0, (const TileState*)p.wt_agg, n_el, (TileState*)s->blk.p);
-    VSV_LAUNCH(ctx, k_ts_spine, 1, 1024, 0, (TileState*)s->blk.p, nb);
-    VSV_LAUNCH(ctx, k_ts_scan, (unsigned)nb, TS_THREADS, 0, (const TileState*)p.wt_agg, n_el, (const TileState*)s->blk.p, d_excl);
+    // segmented exclusive scan of the tile aggregates in one launch (decoupled look-back)
+    VSV_CUDA(ctx, cudaMemsetAsync(s->blk.p, 0, (size_t)(nb + 1) * sizeof(TsDesc), ctx->stream));
+    VSV_LAUNCH(ctx, k_ts_scan1, (unsigned)nb, TS_THREADS, 0, (const TileState*)p.wt_agg, n_el, (TsDesc*)s->blk.p,
+               reinterpret_cast<unsigned int*>((TsDesc*)s->blk.p + nb), d_excl);
     VSV_LAUNCH(ctx, k_emit<VSV_MODE_FUSED>, gs, 256, 0, p, (const TileState*)d_excl, (vsv_sig*)s->sig_reads.p, cap.r, (vsv_sig*)s->sig_cute.p,
                cap.c, st->nout);
     VSV_LAUNCH(ctx, k_shard_rec_totals, (unsigned)vsv_cdiv(n_rec, 256), 256, 0, p, (const TileState*)d_excl, bed, (int32_t*)s->ref_end.p,
